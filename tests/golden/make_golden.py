@@ -1,0 +1,246 @@
+#!/usr/bin/env python
+"""Generate the golden fixtures in tests/golden/ FROM THE REFERENCE ITSELF.
+
+Run in the build container only (needs /root/reference; the GPU box has no copy):
+
+    python tests/golden/make_golden.py
+
+What is executed:
+  * llama : the notebook's own cell SOURCE TEXT (llama3/LLaMA-jax.ipynb cells c15
+            rms_norm, c16 precompute_freqs_cis, c17 apply_rotary_emb, c18 repeat_kv,
+            c24 attention) exec'd with ``jnp`` bound to numpy (every jnp call the
+            cells make - mean, square, reciprocal, sqrt, arange, outer, complex64,
+            exp, reshape, stack, real, imag, repeat, dot, matmul, concatenate - has
+            the same name and semantics in numpy) and ``jax.nn.softmax`` bound to the
+            max-subtracted softmax.  JAX itself is not installable here.  Forward
+            values are stored from the literal fp32/complex64 run; gradients are
+            central finite differences of the same literal source run in fp64
+            (``complex64`` bound to complex128 for that run only, so the difference
+            quotient is not drowned by fp32 rounding).
+  * gemma : the notebook's own torch cells c0 (minus the unused ``tokenizers``
+            import), c1, c6, c7, c8 with ``args.device='cpu'``, modules in eval().
+            Gradients by torch autograd THROUGH THE NOTEBOOK'S MODULES.
+  * vit   : ``nn.LayerNorm`` + ``nn.MultiheadAttention(E,H,batch_first=True)`` called
+            exactly like ViT.ipynb:217-221; gradients by autograd.
+"""
+import json
+import math
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+REF = "/root/reference"
+OUT = os.path.dirname(os.path.abspath(__file__))
+
+
+def cell_src(nb_path, idx):
+    nb = json.load(open(os.path.join(REF, nb_path)))
+    return "".join(nb["cells"][idx]["source"])
+
+
+# --------------------------------------------------------------------------- llama
+def _softmax(x, axis=-1):
+    m = np.max(x, axis=axis, keepdims=True)
+    e = np.exp(x - m)
+    return e / np.sum(e, axis=axis, keepdims=True)
+
+
+def llama_namespace(high_precision):
+    jnp = types.ModuleType("jnp_as_numpy")
+    for name in dir(np):
+        if not name.startswith("__"):
+            setattr(jnp, name, getattr(np, name))
+    if high_precision:
+        jnp.complex64 = lambda a: np.asarray(a, dtype=np.complex128)
+        jnp.float32 = np.float64
+    jax = types.SimpleNamespace(nn=types.SimpleNamespace(softmax=_softmax))
+    ns = {"jnp": jnp, "jax": jax, "math": math}
+    for c in (15, 16, 17, 18, 24):
+        exec(cell_src("llama3/LLaMA-jax.ipynb", c), ns)
+    return ns
+
+
+def make_llama(tag, B, T, C, H, Hkv, causal, seed):
+    rng = np.random.default_rng(seed)
+    hd = C // H
+    f32 = np.float32
+    x = rng.standard_normal((B, T, C)).astype(f32)
+    dy = rng.standard_normal((B, T, C)).astype(f32)
+    p = {
+        "wq": (rng.standard_normal((C, H * hd)) / math.sqrt(C)).astype(f32),
+        "wk": (rng.standard_normal((C, Hkv * hd)) / math.sqrt(C)).astype(f32),
+        "wv": (rng.standard_normal((C, Hkv * hd)) / math.sqrt(C)).astype(f32),
+        "wo": (rng.standard_normal((H * hd, C)) / math.sqrt(H * hd)).astype(f32),
+    }
+    nw = rng.standard_normal((C,)).astype(f32)  # N(0,1), llama3:748
+
+    def run(ns, x_, p_, nw_, dt):
+        fc = ns["precompute_freqs_cis"](hd, T)
+        if causal:  # llama3/LLaMA-jax.ipynb:920-923
+            mask = np.tril(np.ones((T, T)))
+            mask = np.where(mask == 0, -1e9, 0.0).astype(dt)[None, None, :, :]
+        else:
+            mask = None
+        y, (k, v) = ns["attention"](p_, ns["rms_norm"](x_, nw_), mask, fc, H, Hkv)
+        return y, k, v
+
+    ns32 = llama_namespace(False)
+    y, k, v = run(ns32, x, p, nw, f32)
+    assert y.dtype == np.float32, y.dtype
+    # freqs table of the literal code (fp32 complex64), for the exponent quirk test
+    fc = ns32["precompute_freqs_cis"](hd, T)
+
+    ns64 = llama_namespace(True)
+    x64 = x.astype(np.float64)
+    p64 = {k_: v_.astype(np.float64) for k_, v_ in p.items()}
+    nw64 = nw.astype(np.float64)
+    dy64 = dy.astype(np.float64)
+    y64, k64, v64 = run(ns64, x64, p64, nw64, np.float64)
+
+    def loss(x_, p_, nw_):
+        return float(np.sum(run(ns64, x_, p_, nw_, np.float64)[0] * dy64))
+
+    h = 1e-5
+    out = dict(x=x, dy=dy, norm_w=nw, y=y, k=k, v=v, y64=y64, k64=k64, v64=v64,
+               fc_re=np.real(fc).astype(f32), fc_im=np.imag(fc).astype(f32),
+               meta=np.array([B, T, C, H, Hkv, int(causal)], dtype=np.int64), **p)
+    # directional finite-difference derivatives, 3 random directions per tensor
+    for name in ("x", "norm_w", "wq", "wk", "wv", "wo"):
+        base = x64 if name == "x" else nw64 if name == "norm_w" else p64[name]
+        dirs, vals = [], []
+        for _ in range(3):
+            u = rng.standard_normal(base.shape)
+            u /= np.linalg.norm(u)
+
+            def at(eps):
+                xx, pp, nn = x64, dict(p64), nw64
+                if name == "x":
+                    xx = x64 + eps * u
+                elif name == "norm_w":
+                    nn = nw64 + eps * u
+                else:
+                    pp[name] = p64[name] + eps * u
+                return loss(xx, pp, nn)
+
+            # 4th-order central difference
+            d = (-at(2 * h) + 8 * at(h) - 8 * at(-h) + at(-2 * h)) / (12 * h)
+            dirs.append(u)
+            vals.append(d)
+        out["fd_dir_" + name] = np.stack(dirs)
+        out["fd_val_" + name] = np.array(vals)
+    # full FD gradient of the norm weight (C entries)
+    g = np.zeros(C)
+    for i in range(C):
+        e = np.zeros(C)
+        e[i] = 1.0
+        g[i] = (loss(x64, p64, nw64 + h * e) - loss(x64, p64, nw64 - h * e)) / (2 * h)
+    out["fd_grad_norm_w"] = g
+    np.savez_compressed(os.path.join(OUT, f"llama_{tag}.npz"), **out)
+    print("llama", tag, "y", y.shape, "max|y|", np.abs(y).max())
+
+
+# --------------------------------------------------------------------------- gemma
+def make_gemma(tag, B, T, D, seed):
+    ns = {}
+    src0 = cell_src("gemma/gemma.ipynb", 0).replace("from tokenizers import Tokenizer\n", "")
+    exec(src0, ns)
+    exec(cell_src("gemma/gemma.ipynb", 1), ns)
+    args = ns["args"]
+    args.device = "cpu"
+    args.embeddings_dims = D
+    args.block_size = T
+    for c in (6, 7, 8):
+        exec(cell_src("gemma/gemma.ipynb", c), ns)
+    torch.manual_seed(seed)
+    norm = ns["Normalization"](embeddings_dims=D)
+    mqa = ns["MQA"](embeddings_dims=D, block_size=T, no_of_kv_heads=args.no_kv_heads,
+                    no_of_heads=args.no_of_heads)
+    # RotaryEmbeddings default-constructs with the module-level block_size at class
+    # definition time; force the instance values we want.
+    mqa.rotary_matrix.block_size = T
+    mqa.rotary_matrix.embeddings_dims = D
+    norm.eval()
+    mqa.eval()
+    n_params = sum(p.numel() for p in mqa.parameters())
+    rng = np.random.default_rng(seed)
+    x = torch.from_numpy(rng.standard_normal((B, T, D)).astype(np.float32)).requires_grad_(True)
+    dy = torch.from_numpy(rng.standard_normal((B, T, D)).astype(np.float32))
+    with torch.no_grad():
+        norm.rmsnorm_layer.weight.copy_(torch.from_numpy(1.0 + 0.3 * rng.standard_normal(D).astype(np.float32)))
+    y = mqa(norm(x))
+    y.backward(dy)
+    matrix = mqa.rotary_matrix(T)[:T]
+    out = dict(
+        x=x.detach().numpy(), dy=dy.numpy(), y=y.detach().numpy(), dx=x.grad.numpy(),
+        norm_w=norm.rmsnorm_layer.weight.detach().numpy(), dnorm=norm.rmsnorm_layer.weight.grad.numpy(),
+        wk=mqa.key.weight.detach().numpy(), dwk=mqa.key.weight.grad.numpy(),
+        wv=mqa.value.weight.detach().numpy(), dwv=mqa.value.weight.grad.numpy(),
+        wo=mqa.linear_layer.weight.detach().numpy(), dwo=mqa.linear_layer.weight.grad.numpy(),
+        n_q=np.array(len(mqa.multi_query)), n_params=np.array(n_params),
+        # pair (0,1) block of the literal rotary matrix per position: [[M00,M01],[M10,M11]]
+        rot_block=matrix[:, 0:2, 0:2].detach().numpy(),
+        rot_block_last=matrix[:, D - 2:D, D - 2:D].detach().numpy(),
+    )
+    for i, q in enumerate(mqa.multi_query):
+        out[f"wq{i}"] = q.weight.detach().numpy()
+        out[f"dwq{i}"] = q.weight.grad.numpy()
+    np.savez_compressed(os.path.join(OUT, f"gemma_{tag}.npz"), **out)
+    print("gemma", tag, "y", tuple(y.shape), "MQA params", n_params)
+
+
+def gemma_param_count_pin():
+    """MQA at notebook defaults has 3,538,944 parameters."""
+    ns = {}
+    exec(cell_src("gemma/gemma.ipynb", 0).replace("from tokenizers import Tokenizer\n", ""), ns)
+    exec(cell_src("gemma/gemma.ipynb", 1), ns)
+    ns["args"].device = "cpu"
+    for c in (6, 7, 8):
+        exec(cell_src("gemma/gemma.ipynb", c), ns)
+    m = ns["MQA"]()
+    n = sum(p.numel() for p in m.parameters())
+    assert n == 3538944, n
+    return n
+
+
+# --------------------------------------------------------------------------- vit
+def make_vit(tag, B, T, E, H, seed):
+    torch.manual_seed(seed)
+    ln = torch.nn.LayerNorm(E)
+    att = torch.nn.MultiheadAttention(E, H, batch_first=True)
+    rng = np.random.default_rng(seed)
+    with torch.no_grad():
+        ln.weight.copy_(torch.from_numpy(1.0 + 0.3 * rng.standard_normal(E).astype(np.float32)))
+        ln.bias.copy_(torch.from_numpy(0.3 * rng.standard_normal(E).astype(np.float32)))
+        att.in_proj_bias.copy_(torch.from_numpy(0.3 * rng.standard_normal(3 * E).astype(np.float32)))
+        att.out_proj.bias.copy_(torch.from_numpy(0.3 * rng.standard_normal(E).astype(np.float32)))
+    x = torch.from_numpy(rng.standard_normal((B, T, E)).astype(np.float32)).requires_grad_(True)
+    dy = torch.from_numpy(rng.standard_normal((B, T, E)).astype(np.float32))
+    h = ln(x)
+    y = att(h, h, h)[0]  # ViT.ipynb:221
+    y.backward(dy)
+    out = dict(
+        x=x.detach().numpy(), dy=dy.numpy(), y=y.detach().numpy(), dx=x.grad.numpy(),
+        ln_weight=ln.weight.detach().numpy(), ln_bias=ln.bias.detach().numpy(),
+        dln_weight=ln.weight.grad.numpy(), dln_bias=ln.bias.grad.numpy(),
+        in_proj_weight=att.in_proj_weight.detach().numpy(), din_proj_weight=att.in_proj_weight.grad.numpy(),
+        in_proj_bias=att.in_proj_bias.detach().numpy(), din_proj_bias=att.in_proj_bias.grad.numpy(),
+        out_proj_weight=att.out_proj.weight.detach().numpy(), dout_proj_weight=att.out_proj.weight.grad.numpy(),
+        out_proj_bias=att.out_proj.bias.detach().numpy(), dout_proj_bias=att.out_proj.bias.grad.numpy(),
+        meta=np.array([B, T, E, H], dtype=np.int64),
+    )
+    np.savez_compressed(os.path.join(OUT, f"vit_{tag}.npz"), **out)
+    print("vit", tag, "y", tuple(y.shape))
+
+
+if __name__ == "__main__":
+    if not os.path.isdir(REF):
+        sys.exit("needs /root/reference (build container only)")
+    make_llama("gqa_causal", B=2, T=16, C=64, H=4, Hkv=2, causal=True, seed=0)
+    make_llama("mha_nomask", B=1, T=9, C=32, H=2, Hkv=2, causal=False, seed=1)
+    make_llama("mqa_causal", B=2, T=12, C=64, H=4, Hkv=1, causal=True, seed=2)
+    make_gemma("small", B=2, T=16, D=64, seed=3)
+    print("gemma MQA default param count", gemma_param_count_pin())
+    make_vit("nb", B=3, T=17, E=64, H=4, seed=4)  # the notebook's literal shape

@@ -1,0 +1,146 @@
+"""CPU: pin the oracle restatements against fixtures made FROM THE REFERENCE
+(tests/golden/make_golden.py).  A wrong oracle is caught here, before any kernel
+is compared with it."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import llama_oracle, gemma_oracle, vit_oracle, gpt_oracle, max_rel_err
+
+T = torch.from_numpy
+
+
+def _load(golden_dir, name):
+    return dict(np.load(os.path.join(golden_dir, name)))
+
+
+@pytest.mark.parametrize("tag", ["gqa_causal", "mha_nomask", "mqa_causal"])
+def test_llama_forward_matches_literal_notebook_source(golden_dir, tag):
+    g = _load(golden_dir, f"llama_{tag}.npz")
+    B, Tn, C, H, Hkv, causal = (int(v) for v in g["meta"])
+    p = {"attention": {k: T(g[k]) for k in ("wq", "wk", "wv", "wo")}, "attention_norm": T(g["norm_w"])}
+    # fp32 oracle vs literal fp32 run (both carry fp32 rounding)
+    r32 = llama_oracle.block_fwd_bwd(p, T(g["x"]), T(g["dy"]), H, Hkv, causal=bool(causal), dtype=torch.float32)
+    for k in ("y", "k", "v"):
+        assert max_rel_err(r32[k], T(g[k])) < 2e-6, k
+    # fp64 oracle vs literal source run in fp64
+    r64 = llama_oracle.block_fwd_bwd(p, T(g["x"]), T(g["dy"]), H, Hkv, causal=bool(causal), dtype=torch.float64)
+    for k in ("y", "k", "v"):
+        # the only fp32 quantity left in the oracle's fp64 run is the cos/sin table
+        assert max_rel_err(r64[k], T(g[k + "64"])) < 1e-6, k
+
+
+@pytest.mark.parametrize("tag", ["gqa_causal", "mha_nomask", "mqa_causal"])
+def test_llama_gradients_match_finite_differences_of_notebook_source(golden_dir, tag):
+    g = _load(golden_dir, f"llama_{tag}.npz")
+    B, Tn, C, H, Hkv, causal = (int(v) for v in g["meta"])
+    p = {"attention": {k: T(g[k]) for k in ("wq", "wk", "wv", "wo")}, "attention_norm": T(g["norm_w"])}
+    r = llama_oracle.block_fwd_bwd(p, T(g["x"]), T(g["dy"]), H, Hkv, causal=bool(causal), dtype=torch.float64)
+    names = {"x": "dx", "norm_w": "dnorm", "wq": "dwq", "wk": "dwk", "wv": "dwv", "wo": "dwo"}
+    for name, gname in names.items():
+        grad = r[gname].numpy()
+        for u, fd in zip(g["fd_dir_" + name], g["fd_val_" + name]):
+            an = float(np.sum(grad * u))
+            assert abs(an - fd) <= 2e-6 * max(1.0, abs(fd)) + 1e-7, (name, an, fd)
+    assert max_rel_err(r["dnorm"], T(g["fd_grad_norm_w"])) < 1e-6
+
+
+def test_llama_freq_exponent_quirk(golden_dir):
+    """f_j = theta^(-j/hd), not the paper's theta^(-2j/hd) (llama3:564)."""
+    g = _load(golden_dir, "llama_gqa_causal.npz")
+    B, Tn, C, H, Hkv, causal = (int(v) for v in g["meta"])
+    hd = C // H
+    cos, sin = llama_oracle.precompute_freqs_cis(hd, Tn)
+    assert np.abs(cos.numpy() - g["fc_re"]).max() < 1e-6
+    assert np.abs(sin.numpy() - g["fc_im"]).max() < 1e-6
+    j = np.arange(hd // 2)
+    paper = np.cos(np.outer(np.arange(Tn), 10000.0 ** (-2 * j / hd)))
+    assert np.abs(paper - g["fc_re"]).max() > 1e-2  # the paper's table is a different table
+
+
+def test_llama_mask_and_repeat_semantics():
+    m = llama_oracle.make_mask(4)
+    assert m.shape == (1, 1, 4, 4) and m[0, 0, 0, 1] == -1e9 and m[0, 0, 1, 0] == 0
+    x = torch.arange(2 * 1 * 2 * 1).reshape(2, 1, 2, 1)
+    r = llama_oracle.repeat_kv(x, 2)
+    assert r[0, 0, :, 0].tolist() == [0, 0, 1, 1]  # consecutive grouping
+
+
+def test_gemma_matches_notebook_modules(golden_dir):
+    g = _load(golden_dir, "gemma_small.npz")
+    nq = int(g["n_q"])
+    p = {"wq": [T(g[f"wq{i}"]) for i in range(nq)], "wk": T(g["wk"]), "wv": T(g["wv"]),
+         "wo": T(g["wo"]), "norm_w": T(g["norm_w"])}
+    r = gemma_oracle.block_fwd_bwd(p, T(g["x"]), T(g["dy"]), dtype=torch.float32)
+    assert max_rel_err(r["y"], T(g["y"])) < 5e-6
+    assert max_rel_err(r["dx"], T(g["dx"])) < 2e-5
+    for k in ("dwk", "dwv", "dwo", "dnorm"):
+        assert max_rel_err(r[k], T(g[k])) < 2e-5, k
+    for i in range(nq):
+        assert max_rel_err(r["dwq"][i], T(g[f"dwq{i}"])) < 2e-5
+
+
+def test_gemma_rotary_is_not_a_rotation(golden_dir):
+    g = _load(golden_dir, "gemma_small.npz")
+    Tn, D = g["x"].shape[1], g["x"].shape[2]
+    cos, sin = gemma_oracle.rotary_coeffs(Tn, D)
+    blk = g["rot_block"]  # [T,2,2] literal matrix entries for pair (0,1)
+    assert np.abs(blk[:, 0, 0] - cos.numpy()).max() < 1e-6
+    assert np.abs(blk[:, 0, 1] - cos.numpy()).max() < 1e-6
+    assert np.abs(blk[:, 1, 0] + sin.numpy()).max() < 1e-6
+    assert np.abs(blk[:, 1, 1] - sin.numpy()).max() < 1e-6
+    assert np.abs(g["rot_block_last"] - blk).max() == 0  # same angle for every pair
+    assert int(g["n_params"]) == 2 * D * D + D * D + D * D + 2 * D * D
+
+
+def test_vit_matches_torch_modules(golden_dir):
+    g = _load(golden_dir, "vit_nb.npz")
+    B, Tn, E, H = (int(v) for v in g["meta"])
+    keys = ("in_proj_weight", "in_proj_bias", "out_proj_weight", "out_proj_bias", "ln_weight", "ln_bias")
+    p = {k: T(g[k]) for k in keys}
+    r = vit_oracle.block_fwd_bwd(p, T(g["x"]), T(g["dy"]), H, dtype=torch.float32)
+    assert max_rel_err(r["y"], T(g["y"])) < 5e-6
+    assert max_rel_err(r["dx"], T(g["dx"])) < 2e-5
+    for k in keys:
+        assert max_rel_err(r["d" + k], T(g["d" + k])) < 2e-5, k
+
+
+def test_gpt_restatement_agrees_with_vit_fixture_where_math_overlaps(golden_dir):
+    """GPT is unpinned (flax absent).  Weak cross-check: with the causal mask removed,
+    [in,out] kernels = transposed torch weights and zero qkv bias, the GPT restatement
+    is the same function as torch MHA."""
+    g = _load(golden_dir, "vit_nb.npz")
+    B, Tn, E, H = (int(v) for v in g["meta"])
+    x = T(g["x"]).double()
+    p_v = {k: T(g[k]).double() for k in ("in_proj_weight", "out_proj_weight", "out_proj_bias")}
+    p_v["in_proj_bias"] = torch.zeros(3 * E, dtype=torch.float64)
+    y_v = vit_oracle.mha(p_v, x, H)
+    p_g = {"qkv_kernel": p_v["in_proj_weight"].t().contiguous(), "proj_kernel": p_v["out_proj_weight"].t().contiguous(),
+           "proj_bias": p_v["out_proj_bias"]}
+    # bidirectional variant of the GPT function: feed T=1 slices is not possible, so
+    # compare the last query row only after making every other row causal-invisible:
+    y_g = gpt_oracle.causal_self_attention(p_g, x, H)
+    assert max_rel_err(y_g[:, -1], y_v[:, -1]) < 1e-12  # last row sees every key in both
+
+
+def test_gpt_layernorm_is_flax_semantics():
+    x = torch.randn(3, 5, 8, dtype=torch.float64)
+    s, b = torch.rand(8, dtype=torch.float64) + 0.5, torch.randn(8, dtype=torch.float64)
+    ref = torch.nn.functional.layer_norm(x, (8,), s, b, eps=1e-6)
+    assert max_rel_err(gpt_oracle.layer_norm(x, s, b), ref) < 1e-12
+
+
+def test_oracle_self_check_finite_difference_gemma_and_gpt():
+    """finite-difference spot checks so a wrong oracle is caught."""
+    rng = np.random.default_rng(7)
+    x = T(rng.standard_normal((1, 6, 16)))
+    dy = T(rng.standard_normal((1, 6, 16)))
+    p = gpt_oracle.init_block_params(rng, 16, dtype=torch.float64, nonzero_bias=True)
+    r = gpt_oracle.block_fwd_bwd(p, x, dy, 2, dtype=torch.float64)
+    u = T(rng.standard_normal((1, 6, 16)))
+    h = 1e-6
+    f = lambda xx: float((gpt_oracle.attention_block(p, xx, 2) * dy).sum())
+    fd = (f(x + h * u) - f(x - h * u)) / (2 * h)
+    assert abs(fd - float((r["dx"] * u).sum())) < 1e-6 * max(1, abs(fd))
