@@ -1,0 +1,391 @@
+#!/usr/bin/env python
+"""bench.py - attention-block forward+backward tokens/s (BASELINE.json's metric), one JSON line on stdout.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3|c1|c2|c2lit|c4|c4lit|c5] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+
+A "step" is one pass of the hot path (spb_block_fwd + spb_block_bwd, plus the NCCL all-reduce of the weight gradients
+when N > 1) over one batch of synthetic input.  Default workload: C3 = Llama-3-8B-shaped block (d4096, 32Q/8KV x 128,
+T2048, bf16) with B_local = 4 sequences per GPU (SURVEY 8d headline; weak scaling: global batch = 4 N).
+
+  value    : whole-job tokens/s with x, dy, weights resident in HBM, CUDA-event time, max over ranks.
+  e2e      : the same metric through the public API with HOST (pinned) x, dy each step and y, dx read back each step.
+  roofline : dominant kernel = the tcgen05 GEMM (81 % of C3's FLOPs): algorithmic FLOPs of the step's GEMM launches /
+             their device time, measured with CUDA events recorded at stage boundaries INSIDE the timed steps.
+  cpu_baseline : the torch-CPU oracle port of the notebook's op sequence on this box's host cores (bounded sample).
+  --impl reference : that CPU port alone, all host threads (JAX is not installable here, so kind = "port").
+
+Timing hygiene: >= 3 warm-up steps; the per-step working set (>= 0.8 GB at C3) is far larger than the 126 MB L2, so no
+explicit flush is needed (config.l2: "working set > L2"); clocks are sampled with nvidia-smi during the timed region.
+"""
+import argparse
+import ctypes as C
+import json
+import math
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (B_local, T, C, Hq, Hkv, hd, dtype, kind, description)
+    "c3": (4, 2048, 4096, 32, 8, 128, "bf16", "llama", "C3 Llama-3-8B-shaped block d4096 32Q/8KVx128 T2048 bf16, B_local=4 per GPU"),
+    "c1": (16, 128, 256, 4, 2, 64, "f32", "llama", "C1 llama3/LLaMA-jax.ipynb notebook dims B16 T128 d256 4Q/2KVx64 fp32"),
+    "c2": (64, 1024, 256, 1, 1, 256, "bf16", "gpt", "C2 gpt/gpt-jax.ipynb block scaled to B64 T1024 d256 1x256 bf16"),
+    "c2lit": (128, 256, 256, 1, 1, 256, "f32", "gpt", "C2-literal gpt notebook B128 T256 d256 1x256 fp32"),
+    "c4": (4, 4096, 2048, 8, 1, 256, "bf16", "llama", "C4 Gemma-2B-shaped MQA d2048 8Q/1KVx256 T4096 bf16 (standard RoPE)"),
+    "c4lit": (1, 4096, 768, 2, 1, 768, "bf16", "gemma", "C4-literal gemma notebook d768 2Q/1KVx768 T4096 bf16"),
+    "c5": (256, 197, 768, 12, 12, 64, "bf16", "vit", "C5 ViT-B/16 B256 T197 d768 12x64 bf16 non-causal"),
+}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"burst": d["bf16_tflops"], "sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "hbm": d["hbm_gbs"],
+                "source": "measured (MEASURED_PEAKS.json)"}
+    return {"burst": 1590.0, "sustained": 1400.0, "hbm": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            f = [c.strip() for c in r.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ synthetic problem
+def make_problem(wl, device, torch):
+    """Synthetic inputs of SURVEY 8(d): x, dy ~ N(0,1); projection weights N(0,1)/sqrt(fan_in); RMS weight N(0,1)
+    (llama3:748) or ones (gemma / LayerNorm scale); rounded to the activation dtype once."""
+    import solvingpapers_b200 as sp
+    from solvingpapers_b200 import _lib as L
+    B, T, Cm, Hq, Hkv, hd, dt, kind, _ = WORKLOADS[wl]
+    dtype = torch.bfloat16 if dt == "bf16" else torch.float32
+    gen = torch.Generator(device=device).manual_seed({"c1": 0, "c2": 1, "c2lit": 1, "c3": 2, "c4": 3, "c4lit": 3, "c5": 4}[wl])
+    nq, nkv = Hq * hd, Hkv * hd
+    ntot = nq + 2 * nkv
+
+    def n(*shape, scale=1.0):
+        return (torch.randn(*shape, generator=gen, device=device, dtype=torch.float32) * scale).to(dtype)
+
+    p = {}
+    if kind == "llama":
+        cfg = sp.BlockConfig(B, T, Cm, Hq, Hkv, hd, dtype=dtype, norm_kind=L.NORM_RMS, norm_eps=1e-6, rope=True, causal=True)
+        p["wqkv"] = n(Cm, ntot, scale=1 / math.sqrt(Cm)); p["wo"] = n(nq, Cm, scale=1 / math.sqrt(nq)); p["norm_w"] = n(Cm)
+        j = torch.arange(0, hd // 2, dtype=torch.float32)
+        ang = torch.outer(torch.arange(T, dtype=torch.float32), 1.0 / (10000.0 ** (j / hd)))  # llama3:564 exponent j/hd
+        p["rope"] = sp.llama_rope_table(torch.cos(ang), torch.sin(ang)).to(device)
+    elif kind == "gpt":
+        cfg = sp.BlockConfig(B, T, Cm, Hq, Hkv, hd, dtype=dtype, norm_kind=L.NORM_LAYER, norm_eps=1e-6, rope=False, causal=True,
+                             out_bias=True)
+        p["wqkv"] = n(Cm, ntot, scale=1 / math.sqrt(Cm)); p["wo"] = n(nq, Cm, scale=1 / math.sqrt(nq))
+        p["bo"] = torch.zeros(Cm, device=device, dtype=dtype)
+        p["norm_w"] = torch.ones(Cm, device=device, dtype=dtype); p["norm_b"] = torch.zeros(Cm, device=device, dtype=dtype)
+    elif kind == "gemma":
+        from solvingpapers_b200 import gemma
+        cfg = sp.BlockConfig(B, T, Cm, Hq, Hkv, hd, dtype=dtype, norm_kind=L.NORM_RMS, norm_eps=1e-6, norm_upcast=True, rope=True,
+                             causal=True, scale=1 / math.sqrt(Cm), weight_layout=L.W_OUT_IN)
+        p["wqkv"] = n(ntot, Cm, scale=1 / math.sqrt(Cm)); p["wo"] = n(Cm, nq, scale=1 / math.sqrt(nq))
+        p["norm_w"] = torch.ones(Cm, device=device, dtype=dtype)
+        c, s = gemma.rotary_coeffs(T, Cm, device)
+        p["rope"] = sp.gemma_rope_table(c, s, hd // 2)
+    else:  # vit
+        cfg = sp.BlockConfig(B, T, Cm, Hq, Hkv, hd, dtype=dtype, norm_kind=L.NORM_LAYER, norm_eps=1e-5, rope=False, causal=False,
+                             scale=hd ** -0.5, weight_layout=L.W_OUT_IN, qkv_bias=True, out_bias=True)
+        p["wqkv"] = n(ntot, Cm, scale=1 / math.sqrt(Cm)); p["wo"] = n(Cm, nq, scale=1 / math.sqrt(nq))
+        p["bqkv"] = torch.zeros(ntot, device=device, dtype=dtype); p["bo"] = torch.zeros(Cm, device=device, dtype=dtype)
+        p["norm_w"] = torch.ones(Cm, device=device, dtype=dtype); p["norm_b"] = torch.zeros(Cm, device=device, dtype=dtype)
+    x = n(B, T, Cm)
+    dy = n(B, T, Cm)
+    return cfg, p, x, dy
+
+
+# ------------------------------------------------------------------------------------------------ CPU port (oracle)
+def cpu_port_step(wl, torch, B):
+    """One fwd+bwd of the notebook's op sequence on the host (oracle port; materialised scores, repeated KV, autograd)."""
+    import numpy as np
+    from oracle import gemma_oracle, gpt_oracle, llama_oracle, vit_oracle
+    _, T, Cm, Hq, Hkv, hd, dt, kind, _ = WORKLOADS[wl]
+    rng = np.random.default_rng(0)
+    x = torch.from_numpy(rng.standard_normal((B, T, Cm)).astype(np.float32))
+    dy = torch.from_numpy(rng.standard_normal((B, T, Cm)).astype(np.float32))
+    if kind == "llama":
+        params = llama_oracle.init_block_params(rng, Cm, Hq, Hkv)
+        fn = lambda: llama_oracle.block_fwd_bwd(params, x, dy, Hq, Hkv, causal=True)
+    elif kind == "gpt":
+        params = gpt_oracle.init_block_params(rng, Cm)
+        fn = lambda: gpt_oracle.block_fwd_bwd(params, x, dy, Hq)
+    elif kind == "gemma":
+        params = gemma_oracle.init_block_params(rng, Cm, Hq)
+        fn = lambda: gemma_oracle.block_fwd_bwd(params, x, dy)
+    else:
+        params = vit_oracle.init_block_params(rng, Cm)
+        fn = lambda: vit_oracle.block_fwd_bwd(params, x, dy, Hq)
+    return fn, B * T
+
+
+def cpu_sample_batch(wl):
+    """Sequences per CPU step: 1 for the long-sequence shapes (scores are 0.5-2 GB per materialisation), a slice of the
+    batch for the short ones."""
+    B, T, *_ = WORKLOADS[wl]
+    return 1 if T >= 1024 else max(1, min(B, 8192 // T))
+
+
+def time_cpu(wl, torch, steps, warmup, budget_s=None):
+    torch.set_num_threads(os.cpu_count() or 1)
+    Bs = cpu_sample_batch(wl)
+    fn, tokens = cpu_port_step(wl, torch, Bs)
+    for _ in range(warmup):
+        fn()
+    t0 = time.perf_counter()
+    done = 0
+    for _ in range(steps):
+        fn()
+        done += 1
+        if budget_s is not None and time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return tokens * done / dt, dt / done * 1e3, done, Bs, tokens
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path.  JAX/flax are not installable (no network, no
+    wheel), so this is the torch-CPU oracle port of the notebook's op sequence (kind "port"), all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import torch
+    B, T, Cm, Hq, Hkv, hd, dt, kind, desc = WORKLOADS[args.workload]
+    val, ms, done, Bs, tokens = time_cpu(args.workload, torch, args.steps, args.warmup)
+    cores = torch.get_num_threads()
+    sample = f"{Bs} sequence(s) x T={T} per step ({tokens} tokens), fp32, {done} timed steps after {args.warmup} warm-up"
+    out = {"impl": "reference", "metric": "attn_block_fwd_bwd_tokens_per_s", "value": val, "unit": "tokens/s", "n_gpus": args.gpus,
+           "steps": done, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f32", "data": "synthetic",
+           "config": {"workload": desc, "note": "CPU port of the notebook's op sequence (JAX CPU path unavailable on this box: "
+                      "jax not installed, no network); per-step sample bounded, tokens/s is size-normalised"},
+           "cpu_baseline": {"value": val, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": sample},
+           "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------ ours
+GEMM_STAGES = ("gemm_qkv", "gemm_out", "gemm_dattn", "gemm_dwo", "gemm_dx", "gemm_dwqkv")
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import solvingpapers_b200 as sp
+    from solvingpapers_b200 import _lib as L
+    from solvingpapers_b200 import dist as spd
+
+    rank, local_rank, world = spd.env_rank_world()
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("for --gpus N > 1 launch with: python -m torch.distributed.run --nnodes=1 --nproc-per-node N "
+                         "--master-addr 127.0.0.1 --master-port P bench.py --gpus N ...")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (B200); there is no CPU fallback for the product path")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    lib = L.load()
+    comm = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+        comm = spd.Communicator(rank, world)
+
+    B, T, Cm, Hq, Hkv, hd, dt, kind, desc = WORKLOADS[args.workload]
+    cfg, params, x, dy = make_problem(args.workload, device, torch)
+    blk = sp.AttentionBlock(cfg, device=device, comm=comm.handle if comm else None)
+    grads = blk.alloc_grads(params)
+    grads["dx"] = torch.empty_like(x)
+    tokens_local = B * T
+
+    def step():
+        blk.forward(x, params)
+        blk.backward(dy, grads=grads)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    K, W = args.steps, max(args.warmup, 3)
+    for _ in range(W):
+        step()
+    barrier()
+    # ---- timed region: K steps, device-resident inputs, stage events recorded inside it
+    L.check(lib.spb_prof_enable(K), "spb_prof_enable")
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    time.sleep(0.25)
+    launches0 = lib.spb_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(K):
+        step()
+    e1.record()
+    barrier()
+    launches = lib.spb_launch_count() - launches0
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    # stage breakdown (device time between stage-boundary events of the timed steps)
+    stage_ms = {}
+    names = (C.c_char_p * 64)()
+    msbuf = (C.c_float * 64)()
+    for s in range(lib.spb_prof_steps()):
+        n = lib.spb_prof_read(s, 64, names, msbuf)
+        for i in range(max(n, 0)):
+            nm = names[i].decode()
+            stage_ms[nm] = stage_ms.get(nm, 0.0) + msbuf[i]
+    lib.spb_prof_enable(0)
+    stage_ms = {k: v / K for k, v in stage_ms.items()}
+    t_local = torch.tensor([ms_total], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t_local, op=dist.ReduceOp.MAX)
+    ms_total = float(t_local.item())
+    ms_step = ms_total / K
+    value = tokens_local * world * K / (ms_total * 1e-3)
+
+    # ---- e2e: public API, host buffers, H2D of x,dy and D2H of y,dx inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        xh, dyh = x.cpu().pin_memory(), dy.cpu().pin_memory()
+        yh, dxh = torch.empty_like(xh).pin_memory(), torch.empty_like(xh).pin_memory()
+        xd, dyd = torch.empty_like(x), torch.empty_like(dy)
+
+        def step_e2e():
+            xd.copy_(xh, non_blocking=True)
+            dyd.copy_(dyh, non_blocking=True)
+            y = blk.forward(xd, params)
+            blk.backward(dyd, grads=grads)
+            yh.copy_(y, non_blocking=True)
+            dxh.copy_(grads["dx"], non_blocking=True)
+
+        for _ in range(3):
+            step_e2e()
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for _ in range(K):
+            step_e2e()
+        f1.record()
+        barrier()
+        t2 = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        nbytes = x.numel() * x.element_size()
+        e2e = {"value": tokens_local * world * K / (float(t2.item()) * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": 2 * nbytes,
+               "d2h_bytes_per_step": 2 * nbytes, "ms_per_step": float(t2.item()) / K,
+               "what": "pinned host x,dy -> device; spb_block_fwd+bwd via AttentionBlock; y,dx -> pinned host; weights and weight grads stay in HBM"}
+
+    # ---- roofline of the dominant kernel family (tcgen05 GEMM; FLOPs per SURVEY 8d: 3*F_gemm per step)
+    pk = peaks()
+    N = B * T
+    f_gemm = 3.0 * (2.0 * N * Cm * cfg.n_tot + 2.0 * N * cfg.n_q * Cm)
+    gemm_ms = sum(stage_ms.get(s, 0.0) for s in GEMM_STAGES)
+    n_gemm = 6
+    total_flops = cfg.flops_fwd_bwd()
+    roof = {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05, all 6 GEMM stages of a step)" if dt == "bf16" else "gemm_simt_kernel (fp32 FFMA)",
+            "achieved": (f_gemm / 1e12) / (gemm_ms * 1e-3) if gemm_ms > 0 else None, "peak": pk["sustained"], "unit": "TFLOP/s",
+            "frac": None, "traffic": None, "peak_kind": "sustained bf16 cuBLAS, " + pk["source"], "peak_burst": pk["burst"],
+            "flops_per_launch": f_gemm / n_gemm, "avg_launch_ms": gemm_ms / n_gemm, "share_of_step": gemm_ms / ms_step if ms_step else None}
+    if roof["achieved"]:
+        roof["frac"] = roof["achieved"] / roof["peak"]
+    whole = {"tflops": total_flops * world / 1e12 / (ms_step * 1e-3), "frac_of_sustained_peak_per_gpu": total_flops / 1e12 / (ms_step * 1e-3) / pk["sustained"],
+             "frac_of_burst_peak_per_gpu": total_flops / 1e12 / (ms_step * 1e-3) / pk["burst"]}
+
+    out = {"metric": "attn_block_fwd_bwd_tokens_per_s", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": K, "warmup": W,
+           "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dt, "data": "synthetic",
+           "config": {"workload": desc, "global_batch": B * world, "seq_len": T, "parallelism": f"dp{world}" if world > 1 else "single",
+                      "l2": "per-step working set > 126 MB L2, no flush", "attn_impl": "auto", "flops_per_step_per_gpu": total_flops},
+           "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "block_tflops": whole,
+           "stages_ms": {k: round(v, 4) for k, v in sorted(stage_ms.items())}}
+
+    # ---- CPU baseline on rank 0 at N=1 only (bounded sample)
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            val, ms, done, Bs, tok = time_cpu(args.workload, torch, steps=3, warmup=1, budget_s=25.0)
+            out["cpu_baseline"] = {"value": val, "unit": "tokens/s", "cores": torch.get_num_threads(), "kind": "port",
+                                   "sample": f"{Bs} sequence(s) x T={T} ({tok} tokens) per step, fp32 torch-CPU oracle port, {done} timed step(s) after 1 warm-up"}
+        except Exception as ex:  # the baseline must never take the GPU number down with it
+            out["cpu_baseline"] = {"value": None, "unit": "tokens/s", "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {ex}"}
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if comm is not None:
+        barrier()
+        comm.close()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    a = parse()
+    sys.exit(run_reference(a) if a.impl == "reference" else run_ours(a))

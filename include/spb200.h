@@ -1,0 +1,206 @@
+/*
+ * spb200.h - C ABI of libspb200.so: the B200 (sm_100a) attention-block hot path.
+ *
+ * The reference (prashantpandeygit/solvingpapers) has NO native code and NO plugin
+ * registry; its "operator interface" for this path is a handful of Python function
+ * signatures.  Each entry point below cites the reference function it replaces
+ * (file:line = raw line of the .ipynb JSON under the reference checkout).  A host
+ * binding (ctypes today, jax.ffi where JAX exists - see INTEGRATION.md) maps the
+ * notebook's functions 1:1 onto these symbols.
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes; no torch / XLA types.
+ *  - every pointer is a DEVICE pointer unless said otherwise; the caller owns all
+ *    buffers (inputs, outputs and the workspace).  Nothing here allocates.
+ *  - work is enqueued on the cudaStream_t passed as `stream`; no call synchronises.
+ *  - return 0 = ok; < 0 = invalid argument / unsupported shape (see SPB_E_*);
+ *    > 0 = cudaError_t (or 1000 + ncclResult_t).  spb_last_error() has the text.
+ *    Unsupported shapes are an ERROR, never a silent slow path; there is no CPU
+ *    fallback anywhere in the library.
+ *  - activations are fp32 or bf16 (`dtype`); weight GRADIENTS are always fp32.
+ *  - N = B*T tokens; matrices are row-major with an explicit leading dimension.
+ */
+#ifndef SPB200_H
+#define SPB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* spb_stream_t; /* cudaStream_t */
+
+enum { SPB_F32 = 0, SPB_BF16 = 1 };
+enum { SPB_NORM_NONE = 0, SPB_NORM_RMS = 1, SPB_NORM_LAYER = 2 };
+enum { SPB_ROPE_NONE = 0, SPB_ROPE_TABLE = 1 };
+enum { SPB_W_IN_OUT = 0 /* jax/flax: y = x @ W[in,out] */, SPB_W_OUT_IN = 1 /* torch: y = x @ W[out,in]^T */ };
+enum { SPB_IMPL_AUTO = 0, SPB_IMPL_SIMT = 1, SPB_IMPL_TCGEN05 = 2 };
+
+enum {
+  SPB_OK = 0,
+  SPB_E_INVALID = -1,     /* null pointer, negative size, misaligned pointer */
+  SPB_E_UNSUPPORTED = -2, /* shape/dtype this build has no kernel for */
+  SPB_E_STATE = -3,       /* e.g. communicator not initialised, driver entry point missing */
+  SPB_E_LIMIT = -4        /* size beyond a documented fixed limit */
+};
+
+/* One attention block.  Mirrors the static arguments of
+ *   llama3/LLaMA-jax.ipynb:809  attention(params,x,mask,freqs_cis,n_heads,n_kv_heads,cache=None,position=0)
+ *   + :536 rms_norm(x, weight, eps=1e-6) as called at :881,
+ *   gpt/gpt-jax.ipynb:321-357 CausalSelfAttention + :414 nn.LayerNorm,
+ *   gemma/gemma.ipynb:218-259 MQA + :139-150 RMSNorm,
+ *   vision transformer/ViT.ipynb:205-208 LayerNorm + nn.MultiheadAttention.          */
+typedef struct spb_block_desc {
+  int32_t B, T, C;        /* x is [B,T,C] */
+  int32_t Hq, Hkv, hd;    /* q heads, kv heads (Hq % Hkv == 0), head dim; q width Hq*hd need not equal C (Gemma) */
+  int32_t dtype;          /* SPB_F32 | SPB_BF16: activations AND weights */
+  int32_t norm_kind;      /* SPB_NORM_* */
+  float   norm_eps;       /* inside the sqrt (llama3:538) */
+  int32_t norm_upcast;    /* 1: normalise in fp32, round to dtype, THEN multiply weight (gemma:148-150) */
+  int32_t rope_kind;      /* SPB_ROPE_TABLE: q,k pairs (2j,2j+1) <- 2x2 matrix from `rope` table */
+  int32_t causal;         /* mask is not None => causal; -1e9 add / -1e4 replace / -inf are all
+                             exp()==0 exactly, so masked tiles are skipped */
+  float   scale;          /* scores multiplied by this (1/sqrt(hd); Gemma 1/sqrt(768); ViT hd^-0.5) */
+  int32_t weight_layout;  /* SPB_W_IN_OUT | SPB_W_OUT_IN */
+  int32_t qkv_bias;       /* 1: bq,bk,bv present (ViT in_proj_bias) */
+  int32_t out_bias;       /* 1: bo present (GPT proj bias, ViT out_proj.bias) */
+  int32_t attn_impl;      /* SPB_IMPL_*: AUTO = tcgen05 flash kernels when dtype==bf16 and hd in {64,128}, else SIMT */
+  int32_t gemm_impl;      /* SPB_IMPL_*: AUTO = tcgen05 GEMM when dtype==bf16, SIMT fp32 GEMM when dtype==f32 */
+} spb_block_desc;
+
+/* Weights.  W_IN_OUT: wq is [C, Hq*hd] with row stride ldw_qkv, wk/wv are [C, Hkv*hd] with the same stride
+ * (separate arrays: ldw = their own width is NOT assumed - pass three pointers into one packed [C, Ntot] array,
+ * e.g. flax qkv/kernel [C,3C]: wk = wq + C, ldw_qkv = 3C; or three separate arrays via ldw_q/ldw_k/ldw_v).
+ * W_OUT_IN: wq is [Hq*hd, C], wk/wv [Hkv*hd, C], row stride C (torch in_proj_weight [3E,E]: wk = wq + E*E).
+ * wo: W_IN_OUT [Hq*hd, C]; W_OUT_IN [C, Hq*hd].                                                              */
+typedef struct spb_block_params {
+  const void* norm_w;  /* [C] dtype; RMS weight / LayerNorm scale */
+  const void* norm_b;  /* [C] dtype; LayerNorm bias or NULL */
+  const void* wq; const void* wk; const void* wv;
+  int64_t ldw_q, ldw_k, ldw_v;
+  const void* bq; const void* bk; const void* bv; /* [Hq*hd], [Hkv*hd], [Hkv*hd] dtype or NULL */
+  const void* wo; int64_t ldw_o;
+  const void* bo;      /* [C] dtype or NULL */
+  const float* rope;   /* [T, hd/2, 4] fp32 (a,b,c,d): o_even = a*x_even + b*x_odd ; o_odd = c*x_even + d*x_odd.
+                          Llama (llama3:563-567,592-601): (cos,-sin,sin,cos) with angle t*theta^(-j/hd).
+                          Gemma (gemma:182-200): (cos,cos,-sin,sin), one angle per position.  NULL if ROPE_NONE */
+} spb_block_params;
+
+/* Gradients (all fp32 except dx which has the activation dtype).  Same shapes/strides as the weights.
+ * Any pointer may be NULL to skip that gradient.  Buffers are OVERWRITTEN (not accumulated).           */
+typedef struct spb_block_grads {
+  void*  dx;            /* [B,T,C] dtype */
+  float* dnorm_w; float* dnorm_b;
+  float* dwq; float* dwk; float* dwv;
+  int64_t ldw_q, ldw_k, ldw_v;
+  float* dbq; float* dbk; float* dbv;
+  float* dwo; int64_t ldw_o;
+  float* dbo;
+} spb_block_grads;
+
+/* Byte offsets inside the caller-owned workspace (residuals of the forward that the backward reads, and scratch). */
+typedef struct spb_ws_layout {
+  size_t total;
+  size_t xhat;     /* [N, C] dtype: normalised input = GEMM operand                                  */
+  size_t stats;    /* [N, 2] f32: (mean, rstd)                                                       */
+  size_t qkv;      /* [N, ld_qkv] dtype, post-RoPE: q cols [0,Hq*hd), k [Hq*hd, +Hkv*hd), v after    */
+  size_t attn_o;   /* [N, Hq*hd] dtype: attention output before the out projection                   */
+  size_t lse;      /* [B, Hq, T] f32 log-sum-exp of the scaled scores                                */
+  size_t delta;    /* [B, Hq, T] f32 rowsum(dO*O)                 (backward)                         */
+  size_t dattn_o;  /* [N, Hq*hd] dtype                            (backward)                         */
+  size_t dqkv;     /* [N, ld_qkv] dtype                           (backward)                         */
+  size_t dq_acc;   /* [N, Hq*hd] f32 dQ accumulator of the tcgen05 flash backward                    */
+  size_t dxhat;    /* [N, C] dtype                                (backward)                         */
+  size_t partial;  /* f32 partial sums (norm-weight / bias column reductions)                         */
+  size_t partial_bytes;
+  int64_t ld_qkv;  /* (Hq + 2*Hkv) * hd */
+} spb_ws_layout;
+
+/* ---- library ------------------------------------------------------------------------------------ */
+const char* spb_version(void);
+const char* spb_last_error(void);                       /* thread-local text of the last non-zero return */
+int spb_device_info(int32_t* sm_count, int32_t* cc_major, int32_t* cc_minor, size_t* smem_optin);
+/* number of kernels this library has launched in this process (bench.py's gpu_launches) */
+int64_t spb_launch_count(void);
+
+/* Optional stage timing for bench.py's per-kernel roofline (no counterpart in the reference, which has no profiler
+ * hooks: SURVEY section 5).  spb_prof_enable(max_steps) creates CUDA events once (max_steps <= 0 turns it off);
+ * afterwards every spb_block_fwd starts a new step and both block calls record an event on the caller's stream at each
+ * stage boundary.  After synchronising, spb_prof_read(step, ...) returns the number of stages and fills names[]/ms[]
+ * with the device time between consecutive boundaries.  Not thread-safe; measurement aid only.                      */
+int spb_prof_enable(int max_steps);
+int spb_prof_steps(void);
+int spb_prof_read(int step, int max_n, const char** names, float* ms);
+
+/* ---- per-stage entry points (per-kernel parity tests, ncu) -------------------------------------- */
+
+/* llama3:536-538 rms_norm / gpt:414 nn.LayerNorm / gemma:139-150 RMSNorm / ViT:205 nn.LayerNorm.
+ * y[N,C] = norm(x[N,C]); stats[N,2] = (mean, rstd) saved for the backward (may be NULL).            */
+int spb_norm_fwd(int dtype, int norm_kind, int upcast, float eps, const void* x, const void* w, const void* b,
+                 void* y, float* stats, int64_t N, int32_t C, spb_stream_t stream);
+/* VJP of the above.  dw/db are fp32 [C]; `partial` is scratch of spb_norm_bwd_partial_bytes(N,C).    */
+size_t spb_norm_bwd_partial_bytes(int64_t N, int32_t C);
+int spb_norm_bwd(int dtype, int norm_kind, int upcast, const void* x, const void* w, const float* stats,
+                 const void* dy, void* dx, float* dw, float* db, void* partial, int64_t N, int32_t C,
+                 spb_stream_t stream);
+
+/* llama3:592-601 apply_rotary_emb (and gemma:241-242 M_t @ q_t) IN PLACE on x[N, heads*hd] (row stride ld):
+ * token n has position n % T; pair j of every head uses table[t][j].  transpose=1 applies the VJP (M^T).   */
+int spb_rope_apply(int dtype, void* x, int64_t ld, int64_t N, int32_t T, int32_t heads, int32_t hd,
+                   const float* table, int transpose, spb_stream_t stream);
+
+/* The jnp.dot / nn.Dense / nn.Linear of llama3:812-814,829, gpt:329-330, gemma:232-236, and their VJPs.
+ * D[M,N] (ldd) = opA(A) . opB(B) (+ bias[N]) (+ D if accumulate).
+ *   transA=0: A stored [M,K] (lda).   transA=1: A stored [K,M] (lda).
+ *   transB=0: B stored [K,N] (ldb).   transB=1: B stored [N,K] (ldb).
+ * in_dtype: A,B,bias element type; out_dtype: D element type (SPB_F32 for weight gradients).
+ * impl: AUTO = tcgen05 for bf16 inputs, SIMT for fp32 inputs.  tcgen05 needs 16-byte aligned pointers and
+ * lda/ldb multiples of 8 elements; M,N,K are arbitrary (TMA zero-fills the tails).                       */
+int spb_gemm(int in_dtype, int out_dtype, int impl, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda,
+             int transA, const void* Bm, int64_t ldb, int transB, void* D, int64_t ldd, const void* bias,
+             int accumulate, spb_stream_t stream);
+
+/* bias gradient: out[c] = sum_n x[n, c], x is [N, cols] (ld), out fp32; partial = scratch (same size rule). */
+int spb_colsum(int dtype, const void* x, int64_t ld, int64_t N, int32_t cols, float* out, void* partial,
+               spb_stream_t stream);
+
+/* llama3:820-828 (repeat_kv + transpose + QK^T/sqrt(hd) + mask + softmax + PV + merge heads), never
+ * materialising scores or repeated K/V.  q[N,Hq*hd] (ldq), k,v[N,Hkv*hd] (ldk,ldv), o[N,Hq*hd] (ldo),
+ * lse[B,Hq,T] fp32.  kv head of q head h is h / (Hq/Hkv)  (llama3:626-627 consecutive grouping).        */
+int spb_flash_fwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal,
+                  float scale, const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                  void* o, int64_t ldo, float* lse, spb_stream_t stream);
+/* VJP of the above (jax.value_and_grad at llama3:995 has no hand-written counterpart).
+ * delta[B,Hq,T] fp32 scratch; dq_acc: fp32 [N, Hq*hd] scratch (tcgen05 path only, may be NULL for SIMT). */
+int spb_flash_bwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal,
+                  float scale, const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                  const void* o, int64_t ldo, const void* d_o, int64_t lddo, const float* lse, float* delta,
+                  void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv, float* dq_acc,
+                  spb_stream_t stream);
+
+/* ---- the block ---------------------------------------------------------------------------------- */
+int spb_block_ws_layout(const spb_block_desc* d, spb_ws_layout* out);
+/* llama3:881  attention(params['attention'], rms_norm(x, params['attention_norm']), mask, freqs_cis, ...)
+ * y[B,T,C]; residuals (x-hat, stats, post-RoPE q|k|v, attention output, lse) are left in `ws`.
+ * The (k, v) "new_cache" of llama3:819 is the k / v column range of ws+layout.qkv.                    */
+int spb_block_fwd(const spb_block_desc* d, const spb_block_params* p, const void* x, void* y, void* ws,
+                  spb_stream_t stream);
+/* VJP of spb_block_fwd given dy[B,T,C]; reads the residuals spb_block_fwd left in `ws`.
+ * If `comm` != NULL the weight gradients are summed over ranks (ncclAllReduce, fp32) before returning
+ * control of the stream: dwo's all-reduce is launched on a side stream as soon as its GEMM is done and
+ * overlaps the attention backward.                                                        */
+int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void* x, const void* dy, void* ws,
+                  const spb_block_grads* g, void* comm, spb_stream_t stream);
+
+/* ---- data parallelism: batch-sharded, weight gradients all-reduced (no reference precedent) ---- */
+int spb_comm_unique_id(void* out128);                        /* HOST buffer, 128 bytes (ncclUniqueId)      */
+int spb_comm_init_rank(const void* id128, int nranks, int rank, void** comm_out);
+int spb_comm_allreduce_f32(void* comm, float* const* ptrs, const size_t* counts, int n, spb_stream_t stream);
+int spb_comm_destroy(void* comm);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPB200_H */

@@ -1,0 +1,256 @@
+"""Host side of the attention block: owns the workspace, marshals torch CUDA tensors into the C ABI
+(include/spb200.h) and exposes forward / backward.  torch is plumbing only (device memory, streams);
+all arithmetic happens in libspb200.so.  There is no fallback path.
+
+Mirrors the static arguments of the reference's block functions (llama3/LLaMA-jax.ipynb:809 attention +
+:536 rms_norm; gpt/gpt-jax.ipynb:321-357; gemma/gemma.ipynb:218-259; ViT.ipynb:205-221) - see BlockConfig.
+"""
+import ctypes as C
+import math
+from dataclasses import dataclass, field
+from typing import Optional
+
+import torch
+
+from . import _lib as L
+
+
+@dataclass
+class BlockConfig:
+    B: int
+    T: int
+    C: int
+    Hq: int
+    Hkv: int
+    hd: int
+    dtype: torch.dtype = torch.bfloat16
+    norm_kind: int = L.NORM_RMS
+    norm_eps: float = 1e-6
+    norm_upcast: bool = False
+    rope: bool = True
+    causal: bool = True
+    scale: Optional[float] = None
+    weight_layout: int = L.W_IN_OUT
+    qkv_bias: bool = False
+    out_bias: bool = False
+    attn_impl: int = L.IMPL_AUTO
+    gemm_impl: int = L.IMPL_AUTO
+
+    def desc(self) -> L.BlockDesc:
+        scale = self.scale if self.scale is not None else 1.0 / math.sqrt(self.hd)
+        return L.BlockDesc(self.B, self.T, self.C, self.Hq, self.Hkv, self.hd, _dt(self.dtype), self.norm_kind,
+                           self.norm_eps, int(self.norm_upcast), L.ROPE_TABLE if self.rope else L.ROPE_NONE,
+                           int(self.causal), scale, self.weight_layout, int(self.qkv_bias), int(self.out_bias),
+                           self.attn_impl, self.gemm_impl)
+
+    @property
+    def n_q(self):
+        return self.Hq * self.hd
+
+    @property
+    def n_kv(self):
+        return self.Hkv * self.hd
+
+    @property
+    def n_tot(self):
+        return self.n_q + 2 * self.n_kv
+
+    def flops_fwd_bwd(self) -> float:
+        """Algorithmic FLOPs of one forward+backward: 3*F_gemm + 3.5*F_attn."""
+        N = self.B * self.T
+        f_g = 2.0 * N * self.C * self.n_tot + 2.0 * N * self.n_q * self.C
+        m = (self.T + 1) / (2.0 * self.T) if self.causal else 1.0
+        f_a = 4.0 * self.B * self.Hq * self.T * self.T * self.hd * m
+        return 3.0 * f_g + 3.5 * f_a
+
+
+def _dt(dtype):
+    if dtype == torch.float32:
+        return L.F32
+    if dtype == torch.bfloat16:
+        return L.BF16
+    raise L.SpbError(f"unsupported dtype {dtype} (fp32 and bf16 only)")
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(None)
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def llama_rope_table(cos, sin):
+    """freqs_cis of llama3/LLaMA-jax.ipynb:563-567 as the library's 2x2 table: (c, -s, s, c) per (t, pair)."""
+    return torch.stack([cos, -sin, sin, cos], dim=-1).float().contiguous()
+
+
+def gemma_rope_table(cos_t, sin_t, pairs):
+    """The gemma notebook's matrix (gemma/gemma.ipynb:182-200): block [[c, c], [-s, s]], same angle for every pair."""
+    c = cos_t.float().reshape(-1, 1).expand(-1, pairs)
+    s = sin_t.float().reshape(-1, 1).expand(-1, pairs)
+    return torch.stack([c, c, -s, s], dim=-1).contiguous()
+
+
+class AttentionBlock:
+    """One pre-norm attention block bound to fixed shapes.  Weights are passed per call (they change every step)."""
+
+    def __init__(self, cfg: BlockConfig, device="cuda", comm=None):
+        if not torch.cuda.is_available():
+            raise L.SpbError("solvingpapers_b200 needs a CUDA device (B200, sm_100a); there is no CPU path")
+        self.cfg = cfg
+        self.lib = L.load()
+        self.device = torch.device(device)
+        self.d = cfg.desc()
+        self.layout = L.WsLayout()
+        L.check(self.lib.spb_block_ws_layout(C.byref(self.d), C.byref(self.layout)), "spb_block_ws_layout")
+        self.ws = torch.empty(self.layout.total, dtype=torch.uint8, device=self.device)
+        assert self.ws.data_ptr() % 256 == 0
+        self.comm = comm  # opaque handle from dist.Communicator or None
+        self._saved = None
+
+    # ---- views into the workspace --------------------------------------------------------------------
+    def _view(self, off, shape, dtype):
+        n = 1
+        for s in shape:
+            n *= s
+        return self.ws[off: off + n * torch.empty((), dtype=dtype).element_size()].view(dtype).view(*shape)
+
+    def qkv_view(self):
+        c = self.cfg
+        return self._view(self.layout.qkv, (c.B, c.T, c.n_tot), c.dtype)
+
+    def kv_cache(self):
+        """(k, v) of llama3/LLaMA-jax.ipynb:819: post-rotary, un-repeated, [B,T,Hkv,hd] (strided views)."""
+        c = self.cfg
+        qkv = self.qkv_view()
+        k = qkv[..., c.n_q: c.n_q + c.n_kv].unflatten(-1, (c.Hkv, c.hd))
+        v = qkv[..., c.n_q + c.n_kv:].unflatten(-1, (c.Hkv, c.hd))
+        return k, v
+
+    def lse_view(self):
+        c = self.cfg
+        return self._view(self.layout.lse, (c.B, c.Hq, c.T), torch.float32)
+
+    # ---- params ----------------------------------------------------------------------------------------
+    def _params(self, p):
+        c = self.cfg
+        P = L.BlockParams()
+        keep = []
+
+        def chk(t, name):
+            if t is None:
+                return None
+            if t.device.type != "cuda" or t.dtype != c.dtype:
+                raise L.SpbError(f"{name}: expected a {c.dtype} CUDA tensor, got {t.dtype} on {t.device}")
+            keep.append(t)
+            return t
+
+        if "wqkv" in p:
+            w = chk(p["wqkv"], "wqkv")
+            if w.stride(-1) != 1:
+                raise L.SpbError("wqkv must be row-major")
+            if c.weight_layout == L.W_IN_OUT:
+                wq, wk, wv = w[:, :c.n_q], w[:, c.n_q:c.n_q + c.n_kv], w[:, c.n_q + c.n_kv:]
+            else:
+                wq, wk, wv = w[:c.n_q], w[c.n_q:c.n_q + c.n_kv], w[c.n_q + c.n_kv:]
+        else:
+            wq, wk, wv = chk(p["wq"], "wq"), chk(p["wk"], "wk"), chk(p["wv"], "wv")
+        for t in (wq, wk, wv):
+            if t.stride(-1) != 1:
+                raise L.SpbError("weights must be row-major (last stride 1)")
+        P.wq, P.wk, P.wv = _ptr(wq), _ptr(wk), _ptr(wv)
+        P.ldw_q, P.ldw_k, P.ldw_v = wq.stride(0), wk.stride(0), wv.stride(0)
+        wo = chk(p["wo"], "wo")
+        P.wo, P.ldw_o = _ptr(wo), wo.stride(0)
+        if c.qkv_bias:
+            if "bqkv" in p:
+                b = chk(p["bqkv"], "bqkv")
+                bq, bk, bv = b[:c.n_q], b[c.n_q:c.n_q + c.n_kv], b[c.n_q + c.n_kv:]
+            else:
+                bq, bk, bv = chk(p["bq"], "bq"), chk(p["bk"], "bk"), chk(p["bv"], "bv")
+            P.bq, P.bk, P.bv = _ptr(bq), _ptr(bk), _ptr(bv)
+        if c.out_bias:
+            P.bo = _ptr(chk(p["bo"], "bo"))
+        if c.norm_kind != L.NORM_NONE:
+            P.norm_w = _ptr(chk(p["norm_w"], "norm_w"))
+            if c.norm_kind == L.NORM_LAYER and p.get("norm_b") is not None:
+                P.norm_b = _ptr(chk(p["norm_b"], "norm_b"))
+        if c.rope:
+            r = p["rope"]
+            if r.dtype != torch.float32 or tuple(r.shape) != (c.T, c.hd // 2, 4) or not r.is_contiguous():
+                raise L.SpbError(f"rope table must be contiguous fp32 [T, hd/2, 4], got {tuple(r.shape)} {r.dtype}")
+            keep.append(r)
+            P.rope = _ptr(r)
+        return P, keep
+
+    # ---- forward / backward -----------------------------------------------------------------------------
+    def forward(self, x, params):
+        c = self.cfg
+        if tuple(x.shape) != (c.B, c.T, c.C) or x.dtype != c.dtype or not x.is_contiguous():
+            raise L.SpbError(f"x must be contiguous {c.dtype} [{c.B},{c.T},{c.C}], got {tuple(x.shape)} {x.dtype}")
+        P, keep = self._params(params)
+        y = torch.empty_like(x)
+        L.check(self.lib.spb_block_fwd(C.byref(self.d), C.byref(P), _ptr(x), _ptr(y), _ptr(self.ws), _stream()),
+                "spb_block_fwd")
+        self._saved = (x, params, P, keep)
+        return y
+
+    def alloc_grads(self, params):
+        """fp32 gradient buffers with the same packing as the weights."""
+        c = self.cfg
+        dev = self.device
+        g = {"dx": None}
+        if "wqkv" in params:
+            g["dwqkv"] = torch.empty(params["wqkv"].shape, dtype=torch.float32, device=dev)
+        else:
+            for k in ("wq", "wk", "wv"):
+                g["d" + k] = torch.empty(params[k].shape, dtype=torch.float32, device=dev)
+        g["dwo"] = torch.empty(params["wo"].shape, dtype=torch.float32, device=dev)
+        if c.qkv_bias:
+            g["dbqkv"] = torch.empty(c.n_tot, dtype=torch.float32, device=dev)
+        if c.out_bias:
+            g["dbo"] = torch.empty(c.C, dtype=torch.float32, device=dev)
+        if c.norm_kind != L.NORM_NONE:
+            g["dnorm_w"] = torch.empty(c.C, dtype=torch.float32, device=dev)
+            if c.norm_kind == L.NORM_LAYER:
+                g["dnorm_b"] = torch.empty(c.C, dtype=torch.float32, device=dev)
+        return g
+
+    def backward(self, dy, grads=None, need_dx=True):
+        """VJP for the last forward().  Returns a dict of gradients (weight grads fp32, dx in the activation dtype)."""
+        if self._saved is None:
+            raise L.SpbError("backward() before forward()")
+        c = self.cfg
+        x, params, P, keep = self._saved
+        if tuple(dy.shape) != (c.B, c.T, c.C) or dy.dtype != c.dtype or not dy.is_contiguous():
+            raise L.SpbError("dy must match x")
+        g = grads if grads is not None else self.alloc_grads(params)
+        if need_dx and g.get("dx") is None:
+            g["dx"] = torch.empty_like(x)
+        G = L.BlockGrads()
+        G.dx = _ptr(g.get("dx"))
+        if "dwqkv" in g:
+            w = g["dwqkv"]
+            if c.weight_layout == L.W_IN_OUT:
+                dwq, dwk, dwv = w[:, :c.n_q], w[:, c.n_q:c.n_q + c.n_kv], w[:, c.n_q + c.n_kv:]
+            else:
+                dwq, dwk, dwv = w[:c.n_q], w[c.n_q:c.n_q + c.n_kv], w[c.n_q + c.n_kv:]
+        else:
+            dwq, dwk, dwv = g["dwq"], g["dwk"], g["dwv"]
+        G.dwq, G.dwk, G.dwv = _ptr(dwq), _ptr(dwk), _ptr(dwv)
+        G.ldw_q, G.ldw_k, G.ldw_v = dwq.stride(0), dwk.stride(0), dwv.stride(0)
+        G.dwo, G.ldw_o = _ptr(g["dwo"]), g["dwo"].stride(0)
+        if c.qkv_bias:
+            b = g["dbqkv"]
+            G.dbq, G.dbk, G.dbv = _ptr(b[:c.n_q]), _ptr(b[c.n_q:c.n_q + c.n_kv]), _ptr(b[c.n_q + c.n_kv:])
+        if c.out_bias:
+            G.dbo = _ptr(g["dbo"])
+        if c.norm_kind != L.NORM_NONE:
+            G.dnorm_w = _ptr(g["dnorm_w"])
+            if c.norm_kind == L.NORM_LAYER:
+                G.dnorm_b = _ptr(g["dnorm_b"])
+        comm = C.c_void_p(self.comm) if self.comm else C.c_void_p(None)
+        L.check(self.lib.spb_block_bwd(C.byref(self.d), C.byref(P), _ptr(x), _ptr(dy), _ptr(self.ws), C.byref(G), comm,
+                                       _stream()), "spb_block_bwd")
+        return g

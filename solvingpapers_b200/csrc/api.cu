@@ -1,0 +1,498 @@
+// api.cu - the C ABI of libspb200.so: argument checking, dispatch, and the block-level forward/backward that chains
+// the kernels on one stream.  No allocation, no synchronisation, no CPU fallback.
+#include <atomic>
+#include <cstdarg>
+#include <cstring>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace spb {
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int sm_count() {
+  static thread_local int cached_dev = -1, cached = 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev != cached_dev) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached = n;
+    cached_dev = dev;
+  }
+  return cached;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  // resolved through the runtime so the library has no link-time dependency on libcuda.so.1 (absent on CPU-only hosts)
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+int make_tmap_2d(CUtensorMap* map, const void* gptr, int elem_bytes, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                 uint32_t box_cols, bool swizzle128, bool is_float) {
+  EncodeTiledFn fn = encode_fn();
+  SPB_CHECK_ARG(fn != nullptr, SPB_E_STATE, "cuTensorMapEncodeTiled driver entry point not available");
+  SPB_CHECK_ARG(((uintptr_t)gptr % 16 == 0) && ((ld * elem_bytes) % 16 == 0), SPB_E_UNSUPPORTED,
+                "TMA operand must be 16-byte aligned with a 16-byte multiple row pitch (ptr=%p ld=%llu)", gptr,
+                (unsigned long long)ld);
+  const cuuint64_t dims[2] = {cols, rows};
+  const cuuint64_t strides[1] = {ld * (uint64_t)elem_bytes};
+  const cuuint32_t box[2] = {box_cols, box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  CUtensorMapDataType dt = is_float ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUresult r = fn(map, dt, 2, const_cast<void*>(gptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  SPB_CHECK_ARG(r == CUDA_SUCCESS, 700 + (int)r, "cuTensorMapEncodeTiled failed (CUresult %d; rows=%llu cols=%llu ld=%llu box=%ux%u)",
+                (int)r, (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_rows, box_cols);
+  return 0;
+}
+
+// ---- optional stage timing (bench.py's per-kernel roofline): CUDA events recorded on the caller's stream at stage
+// boundaries of spb_block_fwd / spb_block_bwd.  Off by default; events are created once in spb_prof_enable.
+constexpr int PROF_MARKS = 40;
+struct Prof {
+  bool on = false;
+  int max_steps = 0, step = -1;
+  cudaEvent_t* ev = nullptr;      // [max_steps][PROF_MARKS]
+  const char** names = nullptr;   // [max_steps][PROF_MARKS]
+  int* count = nullptr;           // [max_steps]
+};
+static Prof g_prof;
+
+static void prof_new_step() {
+  if (!g_prof.on) return;
+  g_prof.step += 1;
+  if (g_prof.step < g_prof.max_steps) g_prof.count[g_prof.step] = 0;
+}
+static void prof_mark(const char* name, cudaStream_t st) {
+  if (!g_prof.on || g_prof.step < 0 || g_prof.step >= g_prof.max_steps) return;
+  int& n = g_prof.count[g_prof.step];
+  if (n >= PROF_MARKS) return;
+  cudaEventRecord(g_prof.ev[g_prof.step * PROF_MARKS + n], st);
+  g_prof.names[g_prof.step * PROF_MARKS + n] = name;
+  ++n;
+}
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+static inline size_t esize(int dtype) { return dtype == SPB_BF16 ? 2 : 4; }
+
+static int check_desc(const spb_block_desc* d) {
+  SPB_CHECK_ARG(d != nullptr, SPB_E_INVALID, "block desc is NULL");
+  SPB_CHECK_ARG(d->B > 0 && d->T > 0 && d->C > 0 && d->Hq > 0 && d->Hkv > 0 && d->hd > 0, SPB_E_INVALID,
+                "block desc: non-positive dimension (B=%d T=%d C=%d Hq=%d Hkv=%d hd=%d)", d->B, d->T, d->C, d->Hq, d->Hkv, d->hd);
+  SPB_CHECK_ARG(d->Hq % d->Hkv == 0, SPB_E_INVALID, "block desc: Hq %d not a multiple of Hkv %d", d->Hq, d->Hkv);
+  SPB_CHECK_ARG(d->dtype == SPB_F32 || d->dtype == SPB_BF16, SPB_E_UNSUPPORTED, "block desc: dtype %d", d->dtype);
+  SPB_CHECK_ARG(d->norm_kind >= SPB_NORM_NONE && d->norm_kind <= SPB_NORM_LAYER, SPB_E_INVALID, "block desc: norm_kind %d", d->norm_kind);
+  SPB_CHECK_ARG(d->rope_kind == SPB_ROPE_NONE || d->rope_kind == SPB_ROPE_TABLE, SPB_E_INVALID, "block desc: rope_kind %d", d->rope_kind);
+  SPB_CHECK_ARG(d->rope_kind == SPB_ROPE_NONE || d->hd % 2 == 0, SPB_E_INVALID, "block desc: rotary needs an even head dim");
+  SPB_CHECK_ARG(d->weight_layout == SPB_W_IN_OUT || d->weight_layout == SPB_W_OUT_IN, SPB_E_INVALID, "block desc: weight_layout %d",
+                d->weight_layout);
+  return 0;
+}
+
+static int pick_gemm_impl(int impl, int dtype) {
+  if (impl == SPB_IMPL_AUTO) return dtype == SPB_BF16 ? SPB_IMPL_TCGEN05 : SPB_IMPL_SIMT;
+  return impl;
+}
+static int pick_attn_impl(int impl, int dtype, int hd) {
+  if (impl == SPB_IMPL_AUTO) return flash_tc_supported(dtype, hd) ? SPB_IMPL_TCGEN05 : SPB_IMPL_SIMT;
+  return impl;
+}
+
+}  // namespace spb
+
+using namespace spb;
+
+extern "C" {
+
+const char* spb_version(void) { return "spb200 0.1 (sm_100a)"; }
+const char* spb_last_error(void) { return g_err; }
+int64_t spb_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int spb_device_info(int32_t* sm, int32_t* cc_major, int32_t* cc_minor, size_t* smem_optin) {
+  int dev = 0;
+  SPB_CUDA(cudaGetDevice(&dev));
+  int v = 0;
+  if (sm) { SPB_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev)); *sm = v; }
+  if (cc_major) { SPB_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrComputeCapabilityMajor, dev)); *cc_major = v; }
+  if (cc_minor) { SPB_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrComputeCapabilityMinor, dev)); *cc_minor = v; }
+  if (smem_optin) { SPB_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev)); *smem_optin = (size_t)v; }
+  return 0;
+}
+
+int spb_prof_enable(int max_steps) {
+  if (g_prof.ev != nullptr) {
+    for (int i = 0; i < g_prof.max_steps * PROF_MARKS; ++i) cudaEventDestroy(g_prof.ev[i]);
+    delete[] g_prof.ev;
+    delete[] g_prof.names;
+    delete[] g_prof.count;
+    g_prof = Prof();
+  }
+  if (max_steps <= 0) return 0;
+  SPB_CHECK_ARG(max_steps <= 4096, SPB_E_LIMIT, "spb_prof_enable: at most 4096 steps");
+  g_prof.ev = new cudaEvent_t[(size_t)max_steps * PROF_MARKS];
+  g_prof.names = new const char*[(size_t)max_steps * PROF_MARKS];
+  g_prof.count = new int[max_steps];
+  for (int i = 0; i < max_steps * PROF_MARKS; ++i) SPB_CUDA(cudaEventCreate(&g_prof.ev[i]));
+  for (int i = 0; i < max_steps; ++i) g_prof.count[i] = 0;
+  g_prof.max_steps = max_steps;
+  g_prof.step = -1;
+  g_prof.on = true;
+  return 0;
+}
+
+int spb_prof_steps(void) { return g_prof.on ? (g_prof.step + 1 < g_prof.max_steps ? g_prof.step + 1 : g_prof.max_steps) : 0; }
+
+int spb_prof_read(int step, int max_n, const char** names, float* ms) {
+  SPB_CHECK_ARG(g_prof.on && step >= 0 && step < g_prof.max_steps && step <= g_prof.step, SPB_E_STATE, "spb_prof_read: no such step");
+  const int n = g_prof.count[step];
+  int out = 0;
+  for (int i = 0; i + 1 < n && out < max_n; ++i) {
+    float t = 0.f;
+    SPB_CUDA(cudaEventElapsedTime(&t, g_prof.ev[step * PROF_MARKS + i], g_prof.ev[step * PROF_MARKS + i + 1]));
+    names[out] = g_prof.names[step * PROF_MARKS + i];
+    ms[out] = t;
+    ++out;
+  }
+  return out;  // number of stages written (>= 0)
+}
+
+int spb_gemm(int in_dtype, int out_dtype, int impl, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA,
+             const void* Bm, int64_t ldb, int transB, void* D, int64_t ldd, const void* bias, int accumulate, spb_stream_t stream) {
+  SPB_CHECK_ARG(A && Bm && D, SPB_E_INVALID, "spb_gemm: null pointer");
+  SPB_CHECK_ARG(M >= 0 && N >= 0 && K > 0, SPB_E_INVALID, "spb_gemm: bad shape M=%lld N=%lld K=%lld", (long long)M, (long long)N, (long long)K);
+  SPB_CHECK_ARG(lda >= (transA ? M : K) && ldb >= (transB ? K : N) && ldd >= N, SPB_E_INVALID,
+                "spb_gemm: leading dimension smaller than the row length (lda=%lld ldb=%lld ldd=%lld)", (long long)lda, (long long)ldb,
+                (long long)ldd);
+  if (M == 0 || N == 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int use = pick_gemm_impl(impl, in_dtype);
+  if (use == SPB_IMPL_TCGEN05) {
+    SPB_CHECK_ARG(in_dtype == SPB_BF16, SPB_E_UNSUPPORTED, "spb_gemm: the tcgen05 GEMM takes bf16 operands (fp32 mode uses the FFMA GEMM)");
+    return gemm_tc(out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st);
+  }
+  SPB_CHECK_ARG(use == SPB_IMPL_SIMT, SPB_E_INVALID, "spb_gemm: impl %d", impl);
+  return gemm_simt(in_dtype, out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st);
+}
+
+int spb_flash_fwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal, float scale,
+                  const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv, void* o, int64_t ldo, float* lse,
+                  spb_stream_t stream) {
+  SPB_CHECK_ARG(q && k && v && o && lse, SPB_E_INVALID, "spb_flash_fwd: null pointer");
+  SPB_CHECK_ARG(B > 0 && T > 0 && Hq > 0 && Hkv > 0 && hd > 0 && Hq % Hkv == 0, SPB_E_INVALID, "spb_flash_fwd: bad shape");
+  SPB_CHECK_ARG(ldq >= (int64_t)Hq * hd && ldk >= (int64_t)Hkv * hd && ldv >= (int64_t)Hkv * hd && ldo >= (int64_t)Hq * hd, SPB_E_INVALID,
+                "spb_flash_fwd: leading dimension smaller than heads*hd");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int use = pick_attn_impl(impl, dtype, hd);
+  if (use == SPB_IMPL_TCGEN05) {
+    SPB_CHECK_ARG(flash_tc_supported(dtype, hd), SPB_E_UNSUPPORTED, "spb_flash_fwd: tcgen05 path needs bf16 and hd in {64,128} (dtype=%d hd=%d)", dtype, hd);
+    return flash_fwd_tc(B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
+  }
+  SPB_CHECK_ARG(use == SPB_IMPL_SIMT, SPB_E_INVALID, "spb_flash_fwd: impl %d", impl);
+  return attn_simt_fwd(dtype, B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
+}
+
+int spb_flash_bwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal, float scale,
+                  const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo,
+                  const void* d_o, int64_t lddo, const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk,
+                  void* dv, int64_t lddv, float* dq_acc, spb_stream_t stream) {
+  SPB_CHECK_ARG(q && k && v && o && d_o && lse && delta && dq && dk && dv, SPB_E_INVALID, "spb_flash_bwd: null pointer");
+  SPB_CHECK_ARG(B > 0 && T > 0 && Hq > 0 && Hkv > 0 && hd > 0 && Hq % Hkv == 0, SPB_E_INVALID, "spb_flash_bwd: bad shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int use = pick_attn_impl(impl, dtype, hd);
+  if (use == SPB_IMPL_TCGEN05) {
+    SPB_CHECK_ARG(flash_tc_supported(dtype, hd), SPB_E_UNSUPPORTED, "spb_flash_bwd: tcgen05 path needs bf16 and hd in {64,128} (dtype=%d hd=%d)", dtype, hd);
+    SPB_CHECK_ARG(dq_acc != nullptr, SPB_E_INVALID, "spb_flash_bwd: the tcgen05 path needs the fp32 dq_acc scratch");
+    return flash_bwd_tc(B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk, dv,
+                        lddv, dq_acc, st);
+  }
+  SPB_CHECK_ARG(use == SPB_IMPL_SIMT, SPB_E_INVALID, "spb_flash_bwd: impl %d", impl);
+  return attn_simt_bwd(dtype, B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk,
+                       dv, lddv, st);
+}
+
+// ------------------------------------------------------------------------------------------------ block
+int spb_block_ws_layout(const spb_block_desc* d, spb_ws_layout* out) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  SPB_CHECK_ARG(out != nullptr, SPB_E_INVALID, "spb_block_ws_layout: out is NULL");
+  const size_t N = (size_t)d->B * d->T, e = esize(d->dtype);
+  const size_t Nq = (size_t)d->Hq * d->hd, Nkv = (size_t)d->Hkv * d->hd, Ntot = Nq + 2 * Nkv;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off = align_up(off + bytes, 256);
+    return o;
+  };
+  memset(out, 0, sizeof(*out));
+  out->ld_qkv = (int64_t)Ntot;
+  out->xhat = take(N * d->C * e);
+  out->stats = take(N * 2 * sizeof(float));
+  out->qkv = take(N * Ntot * e);
+  out->attn_o = take(N * Nq * e);
+  out->lse = take((size_t)d->B * d->Hq * d->T * sizeof(float));
+  out->delta = take((size_t)d->B * d->Hq * d->T * sizeof(float));
+  out->dattn_o = take(N * Nq * e);
+  out->dqkv = take(N * Ntot * e);
+  out->dq_acc = take(N * Nq * sizeof(float));
+  out->dxhat = take(N * d->C * e);
+  size_t widest = Ntot > (size_t)d->C ? Ntot : (size_t)d->C;
+  out->partial_bytes = spb_norm_bwd_partial_bytes((int64_t)N, (int32_t)widest);
+  out->partial = take(out->partial_bytes);
+  out->total = off;
+  return 0;
+}
+
+int spb_block_fwd(const spb_block_desc* d, const spb_block_params* p, const void* x, void* y, void* ws, spb_stream_t stream) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  SPB_CHECK_ARG(p && x && y && ws, SPB_E_INVALID, "spb_block_fwd: null pointer");
+  SPB_CHECK_ARG(p->wq && p->wk && p->wv && p->wo, SPB_E_INVALID, "spb_block_fwd: null weight");
+  SPB_CHECK_ARG(d->norm_kind == SPB_NORM_NONE || p->norm_w, SPB_E_INVALID, "spb_block_fwd: norm weight is NULL");
+  SPB_CHECK_ARG(d->rope_kind == SPB_ROPE_NONE || p->rope, SPB_E_INVALID, "spb_block_fwd: rope table is NULL");
+  SPB_CHECK_ARG(!d->qkv_bias || (p->bq && p->bk && p->bv), SPB_E_INVALID, "spb_block_fwd: qkv_bias set but a bias pointer is NULL");
+  SPB_CHECK_ARG(!d->out_bias || p->bo, SPB_E_INVALID, "spb_block_fwd: out_bias set but bo is NULL");
+  spb_ws_layout L;
+  rc = spb_block_ws_layout(d, &L);
+  if (rc) return rc;
+  SPB_CHECK_ARG((uintptr_t)ws % 256 == 0, SPB_E_INVALID, "spb_block_fwd: workspace must be 256-byte aligned");
+  char* w8 = (char*)ws;
+  const int64_t N = (int64_t)d->B * d->T;
+  const int64_t Nq = (int64_t)d->Hq * d->hd, Nkv = (int64_t)d->Hkv * d->hd, Ntot = Nq + 2 * Nkv;
+  const size_t e = esize(d->dtype);
+  const int dt = d->dtype;
+  const int gimpl = d->gemm_impl;
+  const bool in_out = d->weight_layout == SPB_W_IN_OUT;
+
+  cudaStream_t pst = (cudaStream_t)stream;
+  prof_new_step();
+  prof_mark("norm_fwd", pst);
+  // 1. norm
+  const void* xin = x;
+  if (d->norm_kind != SPB_NORM_NONE) {
+    rc = spb_norm_fwd(dt, d->norm_kind, d->norm_upcast, d->norm_eps, x, p->norm_w, p->norm_b, w8 + L.xhat, (float*)(w8 + L.stats), N,
+                      d->C, stream);
+    if (rc) return rc;
+    xin = w8 + L.xhat;
+  }
+  // 2. QKV projection (one GEMM when the three weights are one packed array)
+  prof_mark("gemm_qkv", pst);
+  char* qkv = w8 + L.qkv;
+  const char *wq = (const char*)p->wq, *wk = (const char*)p->wk, *wv = (const char*)p->wv;
+  bool packed = p->ldw_q == p->ldw_k && p->ldw_k == p->ldw_v;
+  if (in_out) packed = packed && wk == wq + Nq * e && wv == wk + Nkv * e;
+  else packed = packed && wk == wq + Nq * p->ldw_q * e && wv == wk + Nkv * p->ldw_q * e;
+  if (d->qkv_bias) packed = packed && (const char*)p->bk == (const char*)p->bq + Nq * e && (const char*)p->bv == (const char*)p->bk + Nkv * e;
+  const int tB = in_out ? 0 : 1;
+  if (packed) {
+    rc = spb_gemm(dt, dt, gimpl, N, Ntot, d->C, xin, d->C, 0, wq, p->ldw_q, tB, qkv, Ntot, d->qkv_bias ? p->bq : nullptr, 0, stream);
+    if (rc) return rc;
+  } else {
+    rc = spb_gemm(dt, dt, gimpl, N, Nq, d->C, xin, d->C, 0, wq, p->ldw_q, tB, qkv, Ntot, d->qkv_bias ? p->bq : nullptr, 0, stream);
+    if (rc) return rc;
+    rc = spb_gemm(dt, dt, gimpl, N, Nkv, d->C, xin, d->C, 0, wk, p->ldw_k, tB, qkv + Nq * e, Ntot, d->qkv_bias ? p->bk : nullptr, 0, stream);
+    if (rc) return rc;
+    rc = spb_gemm(dt, dt, gimpl, N, Nkv, d->C, xin, d->C, 0, wv, p->ldw_v, tB, qkv + (Nq + Nkv) * e, Ntot, d->qkv_bias ? p->bv : nullptr, 0,
+                  stream);
+    if (rc) return rc;
+  }
+  // 3. rotary on the q|k column range
+  prof_mark("rope_fwd", pst);
+  if (d->rope_kind == SPB_ROPE_TABLE) {
+    rc = spb_rope_apply(dt, qkv, Ntot, N, d->T, d->Hq + d->Hkv, d->hd, p->rope, 0, stream);
+    if (rc) return rc;
+  }
+  // 4. attention
+  prof_mark("flash_fwd", pst);
+  rc = spb_flash_fwd(dt, d->attn_impl, d->B, d->T, d->Hq, d->Hkv, d->hd, d->causal, d->scale, qkv, Ntot, qkv + Nq * e, Ntot,
+                     qkv + (Nq + Nkv) * e, Ntot, w8 + L.attn_o, Nq, (float*)(w8 + L.lse), stream);
+  if (rc) return rc;
+  // 5. output projection
+  prof_mark("gemm_out", pst);
+  rc = spb_gemm(dt, dt, gimpl, N, d->C, Nq, w8 + L.attn_o, Nq, 0, p->wo, p->ldw_o, tB, y, d->C, d->out_bias ? p->bo : nullptr, 0, stream);
+  prof_mark("fwd_end", pst);
+  return rc;
+}
+
+int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void* x, const void* dy, void* ws,
+                  const spb_block_grads* g, void* comm, spb_stream_t stream) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  SPB_CHECK_ARG(p && x && dy && ws && g, SPB_E_INVALID, "spb_block_bwd: null pointer");
+  spb_ws_layout L;
+  rc = spb_block_ws_layout(d, &L);
+  if (rc) return rc;
+  char* w8 = (char*)ws;
+  const int64_t N = (int64_t)d->B * d->T;
+  const int64_t Nq = (int64_t)d->Hq * d->hd, Nkv = (int64_t)d->Hkv * d->hd, Ntot = Nq + 2 * Nkv;
+  const size_t e = esize(d->dtype);
+  const int dt = d->dtype;
+  const int gimpl = d->gemm_impl;
+  const bool in_out = d->weight_layout == SPB_W_IN_OUT;
+  const void* xin = (d->norm_kind != SPB_NORM_NONE) ? (const void*)(w8 + L.xhat) : x;
+  char* qkv = w8 + L.qkv;
+  char* dqkv = w8 + L.dqkv;
+  void* partial = w8 + L.partial;
+  cudaStream_t st = (cudaStream_t)stream;
+
+  // 1. d(attn_o) = dy . wo^T
+  prof_mark("gemm_dattn", st);
+  rc = spb_gemm(dt, dt, gimpl, N, Nq, d->C, dy, d->C, 0, p->wo, p->ldw_o, in_out ? 1 : 0, w8 + L.dattn_o, Nq, nullptr, 0, stream);
+  if (rc) return rc;
+  // 2. dwo, dbo
+  prof_mark("gemm_dwo", st);
+  if (g->dwo) {
+    if (in_out) rc = spb_gemm(dt, SPB_F32, gimpl, Nq, d->C, N, w8 + L.attn_o, Nq, 1, dy, d->C, 0, g->dwo, g->ldw_o, nullptr, 0, stream);
+    else rc = spb_gemm(dt, SPB_F32, gimpl, d->C, Nq, N, dy, d->C, 1, w8 + L.attn_o, Nq, 0, g->dwo, g->ldw_o, nullptr, 0, stream);
+    if (rc) return rc;
+  }
+  prof_mark("bias_grad", st);
+  if (g->dbo) {
+    rc = spb_colsum(dt, dy, d->C, N, d->C, g->dbo, partial, stream);
+    if (rc) return rc;
+  }
+  // data parallelism: dwo's all-reduce overlaps the attention backward (SURVEY 8e "Overlap")
+  if (comm != nullptr && (g->dwo || g->dbo)) {
+    float* ptrs[2];
+    size_t counts[2];
+    int n = 0;
+    if (g->dwo) {
+      const int64_t rows = in_out ? Nq : d->C, cols = in_out ? d->C : Nq;
+      SPB_CHECK_ARG(g->ldw_o == cols, SPB_E_UNSUPPORTED, "spb_block_bwd: all-reduce needs a contiguous dwo");
+      ptrs[n] = g->dwo;
+      counts[n++] = (size_t)(rows * cols);
+    }
+    if (g->dbo) {
+      ptrs[n] = g->dbo;
+      counts[n++] = (size_t)d->C;
+    }
+    rc = comm_allreduce_side(comm, ptrs, counts, n, st);
+    if (rc) return rc;
+  }
+  // 3. attention backward -> dq|dk|dv (post-rotary gradients)
+  prof_mark("flash_bwd", st);
+  rc = spb_flash_bwd(dt, d->attn_impl, d->B, d->T, d->Hq, d->Hkv, d->hd, d->causal, d->scale, qkv, Ntot, qkv + Nq * e, Ntot,
+                     qkv + (Nq + Nkv) * e, Ntot, w8 + L.attn_o, Nq, w8 + L.dattn_o, Nq, (const float*)(w8 + L.lse),
+                     (float*)(w8 + L.delta), dqkv, Ntot, dqkv + Nq * e, Ntot, dqkv + (Nq + Nkv) * e, Ntot, (float*)(w8 + L.dq_acc), stream);
+  if (rc) return rc;
+  // 4. rotary VJP
+  prof_mark("rope_bwd", st);
+  if (d->rope_kind == SPB_ROPE_TABLE) {
+    rc = spb_rope_apply(dt, dqkv, Ntot, N, d->T, d->Hq + d->Hkv, d->hd, p->rope, 1, stream);
+    if (rc) return rc;
+  }
+  // 5. qkv bias gradients
+  prof_mark("bias_grad", st);
+  if (g->dbq) { rc = spb_colsum(dt, dqkv, Ntot, N, (int32_t)Nq, g->dbq, partial, stream); if (rc) return rc; }
+  if (g->dbk) { rc = spb_colsum(dt, dqkv + Nq * e, Ntot, N, (int32_t)Nkv, g->dbk, partial, stream); if (rc) return rc; }
+  if (g->dbv) { rc = spb_colsum(dt, dqkv + (Nq + Nkv) * e, Ntot, N, (int32_t)Nkv, g->dbv, partial, stream); if (rc) return rc; }
+  // 6. d(xhat) = dqkv . Wqkv^T
+  prof_mark("gemm_dx", st);
+  const char *wq = (const char*)p->wq, *wk = (const char*)p->wk, *wv = (const char*)p->wv;
+  bool packed = p->ldw_q == p->ldw_k && p->ldw_k == p->ldw_v;
+  if (in_out) packed = packed && wk == wq + Nq * e && wv == wk + Nkv * e;
+  else packed = packed && wk == wq + Nq * p->ldw_q * e && wv == wk + Nkv * p->ldw_q * e;
+  void* dxhat = (d->norm_kind != SPB_NORM_NONE) ? (void*)(w8 + L.dxhat) : g->dx;
+  const int tBx = in_out ? 1 : 0;
+  if (dxhat != nullptr) {
+    if (packed) {
+      rc = spb_gemm(dt, dt, gimpl, N, d->C, Ntot, dqkv, Ntot, 0, wq, p->ldw_q, tBx, dxhat, d->C, nullptr, 0, stream);
+      if (rc) return rc;
+    } else {
+      rc = spb_gemm(dt, dt, gimpl, N, d->C, Nq, dqkv, Ntot, 0, wq, p->ldw_q, tBx, dxhat, d->C, nullptr, 0, stream);
+      if (rc) return rc;
+      rc = spb_gemm(dt, dt, gimpl, N, d->C, Nkv, dqkv + Nq * e, Ntot, 0, wk, p->ldw_k, tBx, dxhat, d->C, nullptr, 1, stream);
+      if (rc) return rc;
+      rc = spb_gemm(dt, dt, gimpl, N, d->C, Nkv, dqkv + (Nq + Nkv) * e, Ntot, 0, wv, p->ldw_v, tBx, dxhat, d->C, nullptr, 1, stream);
+      if (rc) return rc;
+    }
+  }
+  // 7. dWq, dWk, dWv
+  prof_mark("gemm_dwqkv", st);
+  bool gpacked = g->dwq && g->dwk && g->dwv && g->ldw_q == g->ldw_k && g->ldw_k == g->ldw_v;
+  if (gpacked) {
+    if (in_out) gpacked = g->dwk == g->dwq + Nq && g->dwv == g->dwk + Nkv;
+    else gpacked = g->dwk == g->dwq + Nq * g->ldw_q && g->dwv == g->dwk + Nkv * g->ldw_q;
+  }
+  auto dw_gemm = [&](float* dw, int64_t ldw, const char* dcols, int64_t width) -> int {
+    if (dw == nullptr) return 0;
+    if (in_out) return spb_gemm(dt, SPB_F32, gimpl, d->C, width, N, xin, d->C, 1, dcols, Ntot, 0, dw, ldw, nullptr, 0, stream);
+    return spb_gemm(dt, SPB_F32, gimpl, width, d->C, N, dcols, Ntot, 1, xin, d->C, 0, dw, ldw, nullptr, 0, stream);
+  };
+  if (gpacked) {
+    rc = dw_gemm(g->dwq, g->ldw_q, dqkv, Ntot);
+    if (rc) return rc;
+  } else {
+    rc = dw_gemm(g->dwq, g->ldw_q, dqkv, Nq);
+    if (rc) return rc;
+    rc = dw_gemm(g->dwk, g->ldw_k, dqkv + Nq * e, Nkv);
+    if (rc) return rc;
+    rc = dw_gemm(g->dwv, g->ldw_v, dqkv + (Nq + Nkv) * e, Nkv);
+    if (rc) return rc;
+  }
+  // 8. norm VJP
+  prof_mark("norm_bwd", st);
+  if (d->norm_kind != SPB_NORM_NONE) {
+    rc = spb_norm_bwd(dt, d->norm_kind, d->norm_upcast, x, p->norm_w, (const float*)(w8 + L.stats), w8 + L.dxhat, g->dx, g->dnorm_w,
+                      g->dnorm_b, partial, N, d->C, stream);
+    if (rc) return rc;
+  }
+  // 9. remaining all-reduces, then join the side stream
+  prof_mark("allreduce", st);
+  if (comm != nullptr) {
+    float* ptrs[8];
+    size_t counts[8];
+    int n = 0;
+    if (gpacked) {
+      const int64_t rows = in_out ? d->C : Ntot, cols = in_out ? Ntot : d->C;
+      SPB_CHECK_ARG(g->ldw_q == cols, SPB_E_UNSUPPORTED, "spb_block_bwd: all-reduce needs a contiguous packed dWqkv");
+      ptrs[n] = g->dwq;
+      counts[n++] = (size_t)(rows * cols);
+    } else {
+      float* dws[3] = {g->dwq, g->dwk, g->dwv};
+      const int64_t lds[3] = {g->ldw_q, g->ldw_k, g->ldw_v};
+      const int64_t widths[3] = {Nq, Nkv, Nkv};
+      for (int i = 0; i < 3; ++i) {
+        if (!dws[i]) continue;
+        const int64_t rows = in_out ? d->C : widths[i], cols = in_out ? widths[i] : d->C;
+        SPB_CHECK_ARG(lds[i] == cols, SPB_E_UNSUPPORTED, "spb_block_bwd: all-reduce needs contiguous dWq/dWk/dWv");
+        ptrs[n] = dws[i];
+        counts[n++] = (size_t)(rows * cols);
+      }
+    }
+    if (g->dbq) { ptrs[n] = g->dbq; counts[n++] = (size_t)Nq; }
+    if (g->dbk) { ptrs[n] = g->dbk; counts[n++] = (size_t)Nkv; }
+    if (g->dbv) { ptrs[n] = g->dbv; counts[n++] = (size_t)Nkv; }
+    if (g->dnorm_w && d->norm_kind != SPB_NORM_NONE) { ptrs[n] = g->dnorm_w; counts[n++] = (size_t)d->C; }
+    if (g->dnorm_b && d->norm_kind == SPB_NORM_LAYER) { ptrs[n] = g->dnorm_b; counts[n++] = (size_t)d->C; }
+    rc = comm_allreduce_join(comm, ptrs, counts, n, st);
+    if (rc) return rc;
+  }
+  prof_mark("bwd_end", st);
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,94 @@
+// gemm_simt.cu - fp32-accurate FFMA GEMM for the fp32 parity mode (BASELINE tolerance 1e-4; one-pass TF32 tensor
+// cores cannot meet it, SURVEY hard part 2).  Also accepts bf16 inputs so the block can be bisected on the GPU.
+// D[M,N] = opA(A) . opB(B) (+bias) (+D).  64x64 tile, BK=16, 256 threads, 4x4 micro-tile, generic strides.
+#include "common.cuh"
+
+namespace spb {
+
+constexpr int SG_BM = 64, SG_BN = 64, SG_BK = 16;
+
+template <typename TI, typename TO>
+__global__ void __launch_bounds__(256) gemm_simt_kernel(int M, int N, int K, const TI* __restrict__ A, int64_t sAm, int64_t sAk,
+                                                        const TI* __restrict__ B, int64_t sBk, int64_t sBn, TO* __restrict__ D,
+                                                        int64_t ldd, const TI* __restrict__ bias, int accumulate) {
+  __shared__ float As[SG_BK][SG_BM + 4];
+  __shared__ float Bs[SG_BK][SG_BN + 4];
+  const int tid = threadIdx.x;
+  const int m0 = blockIdx.y * SG_BM, n0 = blockIdx.x * SG_BN;
+  const int tm = (tid / 16) * 4, tn = (tid % 16) * 4;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int k0 = 0; k0 < K; k0 += SG_BK) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int e = tid + i * 256;
+      int m, k;
+      if (sAk == 1) { k = e % SG_BK; m = e / SG_BK; } else { m = e % SG_BM; k = e / SG_BM; }
+      const int gm = m0 + m, gk = k0 + k;
+      As[k][m] = (gm < M && gk < K) ? to_f32<TI>(A[gm * sAm + gk * sAk]) : 0.f;
+      int n, kb;
+      if (sBk == 1) { kb = e % SG_BK; n = e / SG_BK; } else { n = e % SG_BN; kb = e / SG_BN; }
+      const int gn = n0 + n, gkb = k0 + kb;
+      Bs[kb][n] = (gn < N && gkb < K) ? to_f32<TI>(B[gkb * sBk + gn * sBn]) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < SG_BK; ++k) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = As[k][tm + i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = Bs[k][tn + j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int gm = m0 + tm + i;
+    if (gm >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int gn = n0 + tn + j;
+      if (gn >= N) continue;
+      float v = acc[i][j];
+      if (bias != nullptr) v += to_f32<TI>(bias[gn]);
+      TO* p = D + gm * ldd + gn;
+      if (accumulate) v += to_f32<TO>(*p);
+      *p = from_f32<TO>(v);
+    }
+  }
+}
+
+template <typename TI, typename TO>
+static int gemm_simt_launch(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb,
+                            int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st) {
+  const int64_t sAm = transA ? 1 : lda, sAk = transA ? lda : 1;
+  const int64_t sBk = transB ? 1 : ldb, sBn = transB ? ldb : 1;
+  dim3 grid((unsigned)((N + SG_BN - 1) / SG_BN), (unsigned)((M + SG_BM - 1) / SG_BM));
+  gemm_simt_kernel<TI, TO><<<grid, 256, 0, st>>>((int)M, (int)N, (int)K, (const TI*)A, sAm, sAk, (const TI*)B, sBk, sBn, (TO*)D,
+                                                 ldd, (const TI*)bias, accumulate);
+  SPB_LAUNCH_CHECK();
+  return 0;
+}
+
+int gemm_simt(int in_dtype, int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B,
+              int64_t ldb, int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st) {
+  SPB_CHECK_ARG(M < (1LL << 31) && N < (1LL << 31) && K < (1LL << 31), SPB_E_LIMIT, "gemm_simt: dimension beyond 2^31");
+  if (in_dtype == SPB_F32 && out_dtype == SPB_F32)
+    return gemm_simt_launch<float, float>(M, N, K, A, lda, transA, B, ldb, transB, D, ldd, bias, accumulate, st);
+  if (in_dtype == SPB_BF16 && out_dtype == SPB_BF16)
+    return gemm_simt_launch<__nv_bfloat16, __nv_bfloat16>(M, N, K, A, lda, transA, B, ldb, transB, D, ldd, bias, accumulate, st);
+  if (in_dtype == SPB_BF16 && out_dtype == SPB_F32)
+    return gemm_simt_launch<__nv_bfloat16, float>(M, N, K, A, lda, transA, B, ldb, transB, D, ldd, bias, accumulate, st);
+  SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "gemm_simt: in_dtype %d / out_dtype %d", in_dtype, out_dtype);
+}
+
+}  // namespace spb

@@ -1,0 +1,307 @@
+// gemm_tc.cu - K2: the projections (llama3:812-814,829) and their VJPs as ONE hand-written tcgen05 GEMM.
+//   D[M,N] = opA(A) . opB(B) (+bias) (+D),  bf16 operands, fp32 accumulation in TMEM, bf16 or fp32 output.
+// Design (sm_100a):
+//   * persistent CTAs (grid = min(work items, #SM)), 128 x BN output tile (BN = 256 or 128), BK = 64;
+//   * warp 0 = TMA producer (cp.async.bulk.tensor, 128-byte swizzle, 4-6 stage mbarrier ring),
+//     warp 1 = MMA issuer (one thread, tcgen05.mma kind::f16, M=128 N=BN K=16) and TMEM owner,
+//     warps 2-5 = epilogue (tcgen05.ld 32x32b -> bias / accumulate / convert -> global), double-buffered TMEM
+//     accumulators (2 x BN columns) so the epilogue of tile i overlaps the main loop of tile i+1;
+//   * both operand majors without transpose copies: the [in,out] JAX weights (B is N-contiguous), X^T / dY^T for dW
+//     (both MN-major) are expressed by the UMMA major bits + a TMA box per 64-column chunk (SURVEY 8b weight-layout note);
+//   * split-K (fp32 atomic accumulate into a zeroed output) when a weight-gradient GEMM has fewer tiles than SMs
+//     (d=256 models: dW is 2x3 tiles with K = 65536 tokens).
+// Roofline: tensor pipe. Algorithmic FLOPs 2*M*N*K.
+#include "common.cuh"
+
+namespace spb {
+
+constexpr int GT_BM = 128, GT_BK = 64, GT_THREADS = 192;
+
+struct GemmTcArgs {
+  void* D;
+  int64_t ldd;
+  const __nv_bfloat16* bias;
+  int out_f32, accumulate, atomic, vec_ok;
+  int M, N;
+  int a_mn, b_mn;
+  int num_m, num_n, kb_total, kb_per_split, splits;
+};
+
+template <int BN>
+struct GemmTcCfg {
+  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int A_BYTES = GT_BM * GT_BK * 2;
+  static constexpr int B_BYTES = BN * GT_BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // +1024: manual 1 KB alignment
+  static constexpr int TMEM_COLS = 2 * BN;
+};
+
+__device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row, int col0, const uint32_t* r) {
+  // 32 consecutive fp32 accumulator columns of one output row
+  const int ncol = min(32, p.N - col0);
+  float v[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+  if (p.bias != nullptr) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (i < ncol) v[i] += __bfloat162float(p.bias[col0 + i]);
+  }
+  if (p.out_f32) {
+    float* d = reinterpret_cast<float*>(p.D) + (int64_t)row * p.ldd + col0;
+    if (p.atomic) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (i < ncol) atomicAdd(d + i, v[i]);
+    } else if (p.vec_ok && ncol == 32) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        float4 o = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+        if (p.accumulate) {
+          const float4 old = *reinterpret_cast<const float4*>(d + i);
+          o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+        }
+        *reinterpret_cast<float4*>(d + i) = o;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (i < ncol) d[i] = p.accumulate ? d[i] + v[i] : v[i];
+    }
+  } else {
+    __nv_bfloat16* d = reinterpret_cast<__nv_bfloat16*>(p.D) + (int64_t)row * p.ldd + col0;
+    if (p.vec_ok && ncol == 32) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+        if (p.accumulate) {
+          const uint4 old = *reinterpret_cast<const uint4*>(d + i);
+          const float2 a = unpack_bf16(old.x), b = unpack_bf16(old.y), c = unpack_bf16(old.z), e = unpack_bf16(old.w);
+          v[i] += a.x; v[i + 1] += a.y; v[i + 2] += b.x; v[i + 3] += b.y;
+          v[i + 4] += c.x; v[i + 5] += c.y; v[i + 6] += e.x; v[i + 7] += e.y;
+        }
+        uint4 o;
+        o.x = pack_bf16(v[i], v[i + 1]);
+        o.y = pack_bf16(v[i + 2], v[i + 3]);
+        o.z = pack_bf16(v[i + 4], v[i + 5]);
+        o.w = pack_bf16(v[i + 6], v[i + 7]);
+        *reinterpret_cast<uint4*>(d + i) = o;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (i < ncol) d[i] = __float2bfloat16_rn(p.accumulate ? __bfloat162float(d[i]) + v[i] : v[i]);
+    }
+  }
+}
+
+template <int BN>
+__global__ void __launch_bounds__(GT_THREADS, 1)
+    gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmTcArgs p) {
+  using Cfg = GemmTcCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + Cfg::STAGES * Cfg::A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+  uint64_t* empty = full + Cfg::STAGES;
+  uint64_t* tfull = empty + Cfg::STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < Cfg::STAGES; ++s) {
+        mbar_init(&full[s], 1);
+        mbar_init(&empty[s], 1);
+      }
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(&tfull[a], 1);
+        mbar_init(&tempty[a], 4);
+      }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int tiles = p.num_m * p.num_n;
+  const int total_items = tiles * p.splits;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+        const int split = item / tiles, tile = item % tiles;
+        const int m0 = (tile % p.num_m) * GT_BM, n0 = (tile / p.num_m) * BN;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full[stage], Cfg::STAGE_BYTES);
+          uint8_t* a = sA + stage * Cfg::A_BYTES;
+          uint8_t* b = sB + stage * Cfg::B_BYTES;
+          if (!p.a_mn) {
+            tma_load_2d(a, &tmA, &full[stage], kb * GT_BK, m0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < GT_BM / 64; ++c) tma_load_2d(a + c * (GT_BK * 128), &tmA, &full[stage], m0 + c * 64, kb * GT_BK);
+          }
+          if (!p.b_mn) {
+            tma_load_2d(b, &tmB, &full[stage], kb * GT_BK, n0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BN / 64; ++c) tma_load_2d(b + c * (GT_BK * 128), &tmB, &full[stage], n0 + c * 64, kb * GT_BK);
+          }
+          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(GT_BM, BN, p.a_mn, p.b_mn);
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+        const int split = item / tiles;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(sA + stage * Cfg::A_BYTES);
+          const uint32_t b_addr = smem_u32(sB + stage * Cfg::B_BYTES);
+#pragma unroll
+          for (int k = 0; k < GT_BK / 16; ++k) {
+            const uint64_t adesc = p.a_mn ? umma_desc_mnmajor(a_addr + k * 2048, GT_BK) : umma_desc_kmajor(a_addr + k * 32);
+            const uint64_t bdesc = p.b_mn ? umma_desc_mnmajor(b_addr + k * 2048, GT_BK) : umma_desc_kmajor(b_addr + k * 32);
+            umma_bf16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty[stage]);  // frees the smem slot when these MMAs have read it
+          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull[acc]);  // accumulator complete -> epilogue
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------------ epilogue (warps 2..5 -> TMEM lane quarters 2,3,0,1)
+    const int q = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+      const int tile = item % tiles;
+      const int m0 = (tile % p.num_m) * GT_BM, n0 = (tile / p.num_m) * BN;
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      const int row = m0 + q * 32 + lane;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= p.N) break;  // warp-uniform
+        uint32_t r[32];
+        SPB_TMEM_LD_32(taddr + (uint32_t)(c * 32), r);
+        tmem_ld_wait();
+        if (row < p.M) gemm_tc_store_chunk(p, row, col0, r);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+template <int BN>
+static int gemm_tc_launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmTcArgs& args, cudaStream_t st) {
+  using Cfg = GemmTcCfg<BN>;
+  SPB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+  const int items = args.num_m * args.num_n * args.splits;
+  const int grid = items < sm_count() ? items : sm_count();
+  gemm_tc_kernel<BN><<<grid, GT_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, args);
+  SPB_LAUNCH_CHECK();
+  return 0;
+}
+
+int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb,
+            int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st) {
+  SPB_CHECK_ARG(M < (1LL << 31) && N < (1LL << 31) && K < (1LL << 31), SPB_E_LIMIT, "gemm_tc: dimension beyond 2^31");
+  SPB_CHECK_ARG(M > 0 && N > 0 && K > 0, SPB_E_INVALID, "gemm_tc: empty problem");
+  SPB_CHECK_ARG(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && (lda % 8 == 0) && (ldb % 8 == 0), SPB_E_UNSUPPORTED,
+                "gemm_tc: TMA needs 16-byte aligned operands and leading dimensions that are multiples of 8 (lda=%lld ldb=%lld)",
+                (long long)lda, (long long)ldb);
+  SPB_CHECK_ARG(out_dtype == SPB_F32 || out_dtype == SPB_BF16, SPB_E_UNSUPPORTED, "gemm_tc: out_dtype %d", out_dtype);
+  const int BN = (N > 128) ? 256 : 128;
+  GemmTcArgs args{};
+  args.D = D;
+  args.ldd = ldd;
+  args.bias = (const __nv_bfloat16*)bias;
+  args.out_f32 = (out_dtype == SPB_F32);
+  args.accumulate = accumulate;
+  args.M = (int)M;
+  args.N = (int)N;
+  // transA=0: A stored [M,K] -> K-major.  transA=1: stored [K,M] -> MN-major.
+  // transB=0: B stored [K,N] -> MN-major (N contiguous).  transB=1: stored [N,K] -> K-major.
+  args.a_mn = transA ? 1 : 0;
+  args.b_mn = transB ? 0 : 1;
+  args.num_m = (int)((M + GT_BM - 1) / GT_BM);
+  args.num_n = (int)((N + BN - 1) / BN);
+  args.kb_total = (int)((K + GT_BK - 1) / GT_BK);
+  const int esz = args.out_f32 ? 4 : 2;
+  args.vec_ok = ((uintptr_t)D % 16 == 0) && ((ldd * esz) % 16 == 0);
+  // split-K only for plain fp32 outputs (weight gradients) that would leave most SMs idle
+  int splits = 1;
+  const int tiles = args.num_m * args.num_n;
+  if (args.out_f32 && bias == nullptr && !accumulate && tiles * 2 <= sm_count() && args.kb_total >= 16) {
+    splits = sm_count() / tiles;
+    const int max_splits = args.kb_total / 8;  // at least 8 k-blocks (512 k) per split
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+  }
+  args.kb_per_split = (args.kb_total + splits - 1) / splits;
+  args.splits = (args.kb_total + args.kb_per_split - 1) / args.kb_per_split;
+  args.atomic = args.splits > 1;
+  if (args.atomic) {
+    SPB_CUDA(cudaMemset2DAsync(D, (size_t)ldd * 4, 0, (size_t)N * 4, (size_t)M, st));
+  }
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!args.a_mn) rc = make_tmap_2d(&tmA, A, 2, (uint64_t)M, (uint64_t)K, (uint64_t)lda, GT_BM, GT_BK, true, false);
+  else rc = make_tmap_2d(&tmA, A, 2, (uint64_t)K, (uint64_t)M, (uint64_t)lda, GT_BK, 64, true, false);
+  if (rc) return rc;
+  if (!args.b_mn) rc = make_tmap_2d(&tmB, B, 2, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, (uint32_t)BN, GT_BK, true, false);
+  else rc = make_tmap_2d(&tmB, B, 2, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, GT_BK, 64, true, false);
+  if (rc) return rc;
+  if (BN == 256) return gemm_tc_launch<256>(tmA, tmB, args, st);
+  return gemm_tc_launch<128>(tmA, tmB, args, st);
+}
+
+}  // namespace spb

@@ -1,0 +1,35 @@
+// kernels.h - internal launcher declarations (one per .cu); the C ABI in api.cu dispatches to these.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace spb {
+
+int gemm_simt(int in_dtype, int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B,
+              int64_t ldb, int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st);
+int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb,
+            int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st);
+
+int attn_simt_fwd(int dtype, int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq,
+                  const void* k, int64_t ldk, const void* v, int64_t ldv, void* o, int64_t ldo, float* lse, cudaStream_t st);
+int attn_simt_bwd(int dtype, int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq,
+                  const void* k, int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o,
+                  int64_t lddo, const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv,
+                  int64_t lddv, cudaStream_t st);
+
+// tcgen05 flash attention (bf16, hd in {64,128})
+bool flash_tc_supported(int dtype, int hd);
+int flash_fwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k,
+                 int64_t ldk, const void* v, int64_t ldv, void* o, int64_t ldo, float* lse, cudaStream_t st);
+int flash_bwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k,
+                 int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o, int64_t lddo,
+                 const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
+                 float* dq_acc, cudaStream_t st);
+
+// comm.cu
+// all-reduce on the communicator's side stream, ordered after everything already enqueued on `main`
+int comm_allreduce_side(void* comm, float* const* ptrs, const size_t* counts, int n, cudaStream_t main);
+// all-reduce on `main`, then make `main` wait for the side stream's outstanding all-reduce
+int comm_allreduce_join(void* comm, float* const* ptrs, const size_t* counts, int n, cudaStream_t main);
+
+}  // namespace spb

@@ -1,0 +1,526 @@
+// norm_rope.cu - K1: the memory-bound kernels of the block.
+//   * norm forward  (RMSNorm llama3:536-538 / gemma:139-150, LayerNorm flax + torch): one warp per row, the row is
+//     read ONCE with 128-bit loads into registers, reduced with warp shuffles in fp32, written once.
+//   * norm backward (dx: one warp per row; dweight/dbias: coalesced column-sum kernel + deterministic 2nd stage).
+//   * rotary (llama3:592-601 adjacent-pair rotation; gemma:182-200 "rotary" = general 2x2 per (t,pair) table),
+//     in place on the q|k column range of the packed qkv buffer, 128-bit loads, and its transpose for the VJP.
+// Algorithmic bytes: norm fwd 2*N*C*e (+8N stats); norm bwd dx 3*N*C*e; rope 2*N*cols*e.
+#include "common.cuh"
+
+namespace spb {
+
+template <typename T>
+struct Vec;  // 128-bit vector of T
+template <>
+struct Vec<float> {
+  static constexpr int N = 4;
+  float4 v;
+  __device__ __forceinline__ void load(const float* p) { v = *reinterpret_cast<const float4*>(p); }
+  __device__ __forceinline__ void store(float* p) const { *reinterpret_cast<float4*>(p) = v; }
+  __device__ __forceinline__ void unpack(float* f) const { f[0] = v.x; f[1] = v.y; f[2] = v.z; f[3] = v.w; }
+  __device__ __forceinline__ void pack(const float* f) { v = make_float4(f[0], f[1], f[2], f[3]); }
+};
+template <>
+struct Vec<__nv_bfloat16> {
+  static constexpr int N = 8;
+  uint4 v;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { v = *reinterpret_cast<const uint4*>(p); }
+  __device__ __forceinline__ void store(__nv_bfloat16* p) const { *reinterpret_cast<uint4*>(p) = v; }
+  __device__ __forceinline__ void unpack(float* f) const {
+    float2 a = unpack_bf16(v.x), b = unpack_bf16(v.y), c = unpack_bf16(v.z), d = unpack_bf16(v.w);
+    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+  }
+  __device__ __forceinline__ void pack(const float* f) {
+    v.x = pack_bf16(f[0], f[1]); v.y = pack_bf16(f[2], f[3]); v.z = pack_bf16(f[4], f[5]); v.w = pack_bf16(f[6], f[7]);
+  }
+};
+
+constexpr int NORM_WARPS = 4;
+
+// ------------------------------------------------------------------------------------------------ norm forward
+// VPL = 128-bit vectors per lane held in registers (C <= 32*VPL*Vec::N).
+template <typename T, int VPL>
+__global__ void __launch_bounds__(NORM_WARPS * 32) norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ w,
+                                                                    const T* __restrict__ b, T* __restrict__ y,
+                                                                    float* __restrict__ stats, int64_t N, int C,
+                                                                    float eps, int kind, int upcast) {
+  constexpr int VN = Vec<T>::N;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * NORM_WARPS + (threadIdx.x >> 5);
+  if (row >= N) return;
+  const T* xr = x + row * C;
+  float f[VPL][VN];
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    if (c < C) {
+      Vec<T> v;
+      v.load(xr + c);
+      v.unpack(f[i]);
+    } else {
+#pragma unroll
+      for (int e = 0; e < VN; ++e) f[i][e] = 0.f;
+    }
+  }
+  float mean = 0.f;
+  if (kind == SPB_NORM_LAYER) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i)
+#pragma unroll
+      for (int e = 0; e < VN; ++e) s += f[i][e];
+    mean = warp_sum(s) / (float)C;
+  }
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    if (c < C) {
+#pragma unroll
+      for (int e = 0; e < VN; ++e) {
+        const float d = f[i][e] - mean;
+        ss += d * d;
+      }
+    }
+  }
+  const float var = warp_sum(ss) / (float)C;
+  const float rstd = 1.0f / sqrtf(var + eps);
+  if (stats != nullptr && lane == 0) {
+    stats[2 * row] = mean;
+    stats[2 * row + 1] = rstd;
+  }
+  T* yr = y + row * C;
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    if (c < C) {
+      Vec<T> wv;
+      wv.load(w + c);
+      float wf[VN], o[VN];
+      wv.unpack(wf);
+      if (kind == SPB_NORM_LAYER) {
+        float bf[VN];
+        if (b != nullptr) {
+          Vec<T> bv;
+          bv.load(b + c);
+          bv.unpack(bf);
+        } else {
+#pragma unroll
+          for (int e = 0; e < VN; ++e) bf[e] = 0.f;
+        }
+#pragma unroll
+        for (int e = 0; e < VN; ++e) o[e] = (f[i][e] - mean) * rstd * wf[e] + bf[e];
+      } else if (upcast) {  // gemma:148-150: round the normalised value to T first, then multiply by the weight
+#pragma unroll
+        for (int e = 0; e < VN; ++e) o[e] = to_f32<T>(from_f32<T>(f[i][e] * rstd)) * wf[e];
+      } else {  // llama3:538: (x * weight) * 1/sqrt(var + eps)
+#pragma unroll
+        for (int e = 0; e < VN; ++e) o[e] = (f[i][e] * wf[e]) * rstd;
+      }
+      Vec<T> ov;
+      ov.pack(o);
+      ov.store(yr + c);
+    }
+  }
+}
+
+// Generic (any C, scalar) fallback shape: one warp per row, two passes over the row (second pass hits L1/L2).
+template <typename T>
+__global__ void __launch_bounds__(NORM_WARPS * 32) norm_fwd_generic_kernel(const T* __restrict__ x, const T* __restrict__ w,
+                                                                            const T* __restrict__ b, T* __restrict__ y,
+                                                                            float* __restrict__ stats, int64_t N, int C,
+                                                                            float eps, int kind, int upcast) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * NORM_WARPS + (threadIdx.x >> 5);
+  if (row >= N) return;
+  const T* xr = x + row * C;
+  float mean = 0.f;
+  if (kind == SPB_NORM_LAYER) {
+    float s = 0.f;
+    for (int c = lane; c < C; c += 32) s += to_f32<T>(xr[c]);
+    mean = warp_sum(s) / (float)C;
+  }
+  float ss = 0.f;
+  for (int c = lane; c < C; c += 32) {
+    const float d = to_f32<T>(xr[c]) - mean;
+    ss += d * d;
+  }
+  const float rstd = 1.0f / sqrtf(warp_sum(ss) / (float)C + eps);
+  if (stats != nullptr && lane == 0) {
+    stats[2 * row] = mean;
+    stats[2 * row + 1] = rstd;
+  }
+  T* yr = y + row * C;
+  for (int c = lane; c < C; c += 32) {
+    const float xv = to_f32<T>(xr[c]), wv = to_f32<T>(w[c]);
+    float o;
+    if (kind == SPB_NORM_LAYER) o = (xv - mean) * rstd * wv + (b ? to_f32<T>(b[c]) : 0.f);
+    else if (upcast) o = to_f32<T>(from_f32<T>(xv * rstd)) * wv;
+    else o = (xv * wv) * rstd;
+    yr[c] = from_f32<T>(o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ norm backward (dx)
+// RMS  : y = x*w*r,            g = dy*w,  dx = r*g - x * r^3 * mean(g*x)
+// LAYER: y = (x-m)*r*w + b,    g = dy*w,  xh = (x-m)*r,  dx = r*(g - mean(g) - xh*mean(g*xh))
+template <typename T, int VPL>
+__global__ void __launch_bounds__(NORM_WARPS * 32) norm_bwd_dx_kernel(const T* __restrict__ x, const T* __restrict__ w,
+                                                                       const float* __restrict__ stats,
+                                                                       const T* __restrict__ dy, T* __restrict__ dx,
+                                                                       int64_t N, int C, int kind) {
+  constexpr int VN = Vec<T>::N;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * NORM_WARPS + (threadIdx.x >> 5);
+  if (row >= N) return;
+  const float mean = stats[2 * row], rstd = stats[2 * row + 1];
+  // the row of x and dy stays packed in registers (read from HBM once); w is re-read from L1
+  Vec<T> xv[VPL], dv[VPL];
+  float s_g = 0.f, s_gx = 0.f;
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    if (c < C) {
+      xv[i].load(x + row * C + c);
+      dv[i].load(dy + row * C + c);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    if (c < C) {
+      Vec<T> wv;
+      wv.load(w + c);
+      float xf[VN], g[VN], wf[VN];
+      xv[i].unpack(xf);
+      dv[i].unpack(g);
+      wv.unpack(wf);
+#pragma unroll
+      for (int e = 0; e < VN; ++e) {
+        const float gv = g[e] * wf[e];
+        const float xn = (kind == SPB_NORM_LAYER) ? (xf[e] - mean) * rstd : xf[e];
+        s_g += gv;
+        s_gx += gv * xn;
+      }
+    }
+  }
+  s_g = warp_sum(s_g) / (float)C;
+  s_gx = warp_sum(s_gx) / (float)C;
+  const float r3 = rstd * rstd * rstd;
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    if (c < C) {
+      Vec<T> wv;
+      wv.load(w + c);
+      float xf[VN], g[VN], wf[VN], o[VN];
+      xv[i].unpack(xf);
+      dv[i].unpack(g);
+      wv.unpack(wf);
+#pragma unroll
+      for (int e = 0; e < VN; ++e) {
+        const float gv = g[e] * wf[e];
+        if (kind == SPB_NORM_LAYER) o[e] = rstd * (gv - s_g - (xf[e] - mean) * rstd * s_gx);
+        else o[e] = rstd * gv - xf[e] * r3 * s_gx;
+      }
+      Vec<T> ov;
+      ov.pack(o);
+      ov.store(dx + row * C + c);
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(NORM_WARPS * 32) norm_bwd_dx_generic_kernel(const T* __restrict__ x, const T* __restrict__ w,
+                                                                               const float* __restrict__ stats,
+                                                                               const T* __restrict__ dy, T* __restrict__ dx,
+                                                                               int64_t N, int C, int kind) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * NORM_WARPS + (threadIdx.x >> 5);
+  if (row >= N) return;
+  const float mean = stats[2 * row], rstd = stats[2 * row + 1];
+  const T* xr = x + row * C;
+  const T* dr = dy + row * C;
+  float s_g = 0.f, s_gx = 0.f;
+  for (int c = lane; c < C; c += 32) {
+    const float gv = to_f32<T>(dr[c]) * to_f32<T>(w[c]);
+    const float xv = (kind == SPB_NORM_LAYER) ? (to_f32<T>(xr[c]) - mean) * rstd : to_f32<T>(xr[c]);
+    s_g += gv;
+    s_gx += gv * xv;
+  }
+  s_g = warp_sum(s_g) / (float)C;
+  s_gx = warp_sum(s_gx) / (float)C;
+  const float r3 = rstd * rstd * rstd;
+  for (int c = lane; c < C; c += 32) {
+    const float gv = to_f32<T>(dr[c]) * to_f32<T>(w[c]);
+    float o;
+    if (kind == SPB_NORM_LAYER) {
+      const float xh = (to_f32<T>(xr[c]) - mean) * rstd;
+      o = rstd * (gv - s_g - xh * s_gx);
+    } else {
+      o = rstd * gv - to_f32<T>(xr[c]) * r3 * s_gx;
+    }
+    dx[row * C + c] = from_f32<T>(o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ column sums
+// partial[chunk][c]          = sum over the chunk's rows of  a[row][c]                       (MODE 0: bias grads)
+// partial[chunk][c]          = sum of dy[row][c] * xn[row][c]   with xn = x*rstd  (RMS) or (x-mean)*rstd (LAYER)
+// partial[chunks + chunk][c] = sum of dy[row][c]                                            (MODE 1: norm dw, db)
+// Threads run along columns (coalesced); each thread keeps its column's running sum in a register.
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256) colsum_partial_kernel(const T* __restrict__ a, int64_t lda, const T* __restrict__ x,
+                                                             const float* __restrict__ stats, int kind, int64_t N, int C,
+                                                             int rows_per_chunk, int chunks, float* __restrict__ partial) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int chunk = blockIdx.y;
+  if (c >= C) return;
+  const int64_t r0 = (int64_t)chunk * rows_per_chunk;
+  int64_t r1 = r0 + rows_per_chunk;
+  if (r1 > N) r1 = N;
+  float s0 = 0.f, s1 = 0.f;
+  for (int64_t r = r0; r < r1; ++r) {
+    const float av = to_f32<T>(a[r * lda + c]);
+    if (MODE == 1) {
+      const float mean = (kind == SPB_NORM_LAYER) ? stats[2 * r] : 0.f;
+      const float rstd = stats[2 * r + 1];
+      s0 += av * ((to_f32<T>(x[r * (int64_t)C + c]) - mean) * rstd);
+      s1 += av;
+    } else {
+      s0 += av;
+    }
+  }
+  partial[(int64_t)chunk * C + c] = s0;
+  if (MODE == 1) partial[((int64_t)chunks + chunk) * C + c] = s1;
+}
+
+__global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restrict__ partial, int chunks, int C,
+                                                           float* __restrict__ out0, float* __restrict__ out1) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  if (out0 != nullptr) {
+    float s = 0.f;
+    for (int k = 0; k < chunks; ++k) s += partial[(int64_t)k * C + c];
+    out0[c] = s;
+  }
+  if (out1 != nullptr) {
+    float s = 0.f;
+    for (int k = 0; k < chunks; ++k) s += partial[((int64_t)chunks + k) * C + c];
+    out1[c] = s;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ rotary
+// x[N, heads*hd] (row stride ld) in place; one thread per 128-bit vector (bf16: 4 pairs, f32: 2 pairs).
+// table[t][j] = (a,b,c,d):  o_even = a*x_even + b*x_odd,  o_odd = c*x_even + d*x_odd;  transpose swaps b and c.
+template <typename T>
+__global__ void __launch_bounds__(256) rope_kernel(T* __restrict__ x, int64_t ld, int64_t N, int T_len, int heads, int hd,
+                                                   const float4* __restrict__ table, int transpose) {
+  constexpr int VN = Vec<T>::N;
+  const int vec_per_row = heads * hd / VN;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= N * vec_per_row) return;
+  const int64_t n = idx / vec_per_row;
+  const int col = (int)(idx % vec_per_row) * VN;
+  const int t = (int)(n % T_len);
+  const int pair0 = (col % hd) >> 1;
+  T* p = x + n * ld + col;
+  Vec<T> v;
+  v.load(p);
+  float f[VN];
+  v.unpack(f);
+#pragma unroll
+  for (int e = 0; e < VN; e += 2) {
+    const float4 m = table[(int64_t)t * (hd >> 1) + pair0 + (e >> 1)];
+    const float bb = transpose ? m.z : m.y, cc = transpose ? m.y : m.z;
+    const float xe = f[e], xo = f[e + 1];
+    f[e] = m.x * xe + bb * xo;
+    f[e + 1] = cc * xe + m.w * xo;
+  }
+  v.pack(f);
+  v.store(p);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) rope_generic_kernel(T* __restrict__ x, int64_t ld, int64_t N, int T_len, int heads,
+                                                           int hd, const float4* __restrict__ table, int transpose) {
+  const int pairs_per_row = heads * hd / 2;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= N * pairs_per_row) return;
+  const int64_t n = idx / pairs_per_row;
+  const int pr = (int)(idx % pairs_per_row);
+  const int t = (int)(n % T_len);
+  const int j = pr % (hd >> 1);
+  T* p = x + n * ld + 2 * pr;
+  const float4 m = table[(int64_t)t * (hd >> 1) + j];
+  const float bb = transpose ? m.z : m.y, cc = transpose ? m.y : m.z;
+  const float xe = to_f32<T>(p[0]), xo = to_f32<T>(p[1]);
+  p[0] = from_f32<T>(m.x * xe + bb * xo);
+  p[1] = from_f32<T>(cc * xe + m.w * xo);
+}
+
+// ------------------------------------------------------------------------------------------------ host launchers
+void colsum_plan(int64_t N, int* chunks, int* rows_per_chunk);
+
+template <typename T>
+static int norm_fwd_launch(const void* x, const void* w, const void* b, void* y, float* stats, int64_t N, int C, float eps,
+                           int kind, int upcast, cudaStream_t st) {
+  constexpr int VN = Vec<T>::N;
+  const unsigned grid = (unsigned)((N + NORM_WARPS - 1) / NORM_WARPS);
+  const bool vec_ok = (C % VN == 0) && ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0) && ((uintptr_t)w % 16 == 0) &&
+                      (b == nullptr || (uintptr_t)b % 16 == 0);
+  const int vpl = (C + 32 * VN - 1) / (32 * VN);
+#define SPB_NF(V)                                                                                                        \
+  norm_fwd_kernel<T, V><<<grid, NORM_WARPS * 32, 0, st>>>((const T*)x, (const T*)w, (const T*)b, (T*)y, stats, N, C, eps, \
+                                                          kind, upcast)
+  if (vec_ok && vpl <= 1) SPB_NF(1);
+  else if (vec_ok && vpl <= 2) SPB_NF(2);
+  else if (vec_ok && vpl <= 4) SPB_NF(4);
+  else if (vec_ok && vpl <= 8) SPB_NF(8);
+  else if (vec_ok && vpl <= 16) SPB_NF(16);
+  else if (vec_ok && vpl <= 32 && sizeof(T) == 4) { if constexpr (sizeof(T) == 4) SPB_NF(32); }
+  else
+    norm_fwd_generic_kernel<T><<<grid, NORM_WARPS * 32, 0, st>>>((const T*)x, (const T*)w, (const T*)b, (T*)y, stats, N, C,
+                                                                 eps, kind, upcast);
+#undef SPB_NF
+  SPB_LAUNCH_CHECK();
+  return 0;
+}
+
+template <typename T>
+static int norm_bwd_launch(const void* x, const void* w, const float* stats, const void* dy, void* dx, float* dw, float* db,
+                           void* partial, int64_t N, int C, int kind, cudaStream_t st) {
+  constexpr int VN = Vec<T>::N;
+  if (dx != nullptr) {
+    const unsigned grid = (unsigned)((N + NORM_WARPS - 1) / NORM_WARPS);
+    const bool vec_ok = (C % VN == 0) && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) && ((uintptr_t)dx % 16 == 0) &&
+                        ((uintptr_t)w % 16 == 0);
+    const int vpl = (C + 32 * VN - 1) / (32 * VN);
+#define SPB_NB(V) \
+  norm_bwd_dx_kernel<T, V><<<grid, NORM_WARPS * 32, 0, st>>>((const T*)x, (const T*)w, stats, (const T*)dy, (T*)dx, N, C, kind)
+    if (vec_ok && vpl <= 1) SPB_NB(1);
+    else if (vec_ok && vpl <= 2) SPB_NB(2);
+    else if (vec_ok && vpl <= 4) SPB_NB(4);
+    else if (vec_ok && vpl <= 8) SPB_NB(8);
+    else if (vec_ok && vpl <= 16) SPB_NB(16);
+    else
+      norm_bwd_dx_generic_kernel<T><<<grid, NORM_WARPS * 32, 0, st>>>((const T*)x, (const T*)w, stats, (const T*)dy, (T*)dx,
+                                                                      N, C, kind);
+#undef SPB_NB
+    SPB_LAUNCH_CHECK();
+  }
+  if (dw != nullptr || db != nullptr) {
+    SPB_CHECK_ARG(partial != nullptr, SPB_E_INVALID, "norm_bwd: partial scratch is NULL");
+    int chunks, rpc;
+    colsum_plan(N, &chunks, &rpc);
+    dim3 grid((C + 255) / 256, chunks);
+    colsum_partial_kernel<T, 1><<<grid, 256, 0, st>>>((const T*)dy, C, (const T*)x, stats, kind, N, C, rpc, chunks,
+                                                      (float*)partial);
+    SPB_LAUNCH_CHECK();
+    colsum_final_kernel<<<(C + 255) / 256, 256, 0, st>>>((const float*)partial, chunks, C, dw, db);
+    SPB_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+void colsum_plan(int64_t N, int* chunks, int* rows_per_chunk) {
+  // enough chunks to fill the machine for narrow matrices, few enough that the 2nd stage stays negligible
+  int64_t ch = (N + 31) / 32;
+  if (ch > 592) ch = 592;  // 4 * 148
+  if (ch < 1) ch = 1;
+  const int64_t rpc = (N + ch - 1) / ch;
+  *rows_per_chunk = (int)(rpc < 1 ? 1 : rpc);
+  *chunks = (int)((N + *rows_per_chunk - 1) / *rows_per_chunk);
+  if (*chunks < 1) *chunks = 1;
+}
+
+template <typename T>
+static int colsum_launch(const void* x, int64_t ld, int64_t N, int cols, float* out, void* partial, cudaStream_t st) {
+  int chunks, rpc;
+  colsum_plan(N, &chunks, &rpc);
+  dim3 grid((cols + 255) / 256, chunks);
+  colsum_partial_kernel<T, 0><<<grid, 256, 0, st>>>((const T*)x, ld, nullptr, nullptr, 0, N, cols, rpc, chunks, (float*)partial);
+  SPB_LAUNCH_CHECK();
+  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, st>>>((const float*)partial, chunks, cols, out, nullptr);
+  SPB_LAUNCH_CHECK();
+  return 0;
+}
+
+template <typename T>
+static int rope_launch(void* x, int64_t ld, int64_t N, int T_len, int heads, int hd, const float* table, int transpose,
+                       cudaStream_t st) {
+  constexpr int VN = Vec<T>::N;
+  const bool vec_ok = (hd % VN == 0) && (ld % VN == 0) && ((uintptr_t)x % 16 == 0);
+  if (vec_ok) {
+    const int64_t total = N * (heads * hd / VN);
+    rope_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((T*)x, ld, N, T_len, heads, hd, (const float4*)table,
+                                                                     transpose);
+  } else {
+    const int64_t total = N * (heads * hd / 2);
+    rope_generic_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((T*)x, ld, N, T_len, heads, hd,
+                                                                             (const float4*)table, transpose);
+  }
+  SPB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace spb
+
+// ------------------------------------------------------------------------------------------------ C ABI
+extern "C" {
+
+int spb_norm_fwd(int dtype, int norm_kind, int upcast, float eps, const void* x, const void* w, const void* b, void* y,
+                 float* stats, int64_t N, int32_t C, spb_stream_t stream) {
+  SPB_CHECK_ARG(x && w && y, SPB_E_INVALID, "spb_norm_fwd: null pointer");
+  SPB_CHECK_ARG(N >= 0 && C > 0, SPB_E_INVALID, "spb_norm_fwd: bad shape N=%lld C=%d", (long long)N, C);
+  SPB_CHECK_ARG(norm_kind == SPB_NORM_RMS || norm_kind == SPB_NORM_LAYER, SPB_E_INVALID, "spb_norm_fwd: bad norm_kind %d", norm_kind);
+  if (N == 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == SPB_F32) return spb::norm_fwd_launch<float>(x, w, b, y, stats, N, C, eps, norm_kind, upcast, st);
+  if (dtype == SPB_BF16) return spb::norm_fwd_launch<__nv_bfloat16>(x, w, b, y, stats, N, C, eps, norm_kind, upcast, st);
+  SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "spb_norm_fwd: dtype %d", dtype);
+}
+
+size_t spb_norm_bwd_partial_bytes(int64_t N, int32_t C) {
+  int chunks, rpc;
+  spb::colsum_plan(N < 1 ? 1 : N, &chunks, &rpc);
+  return (size_t)2 * chunks * (size_t)C * sizeof(float);
+}
+
+int spb_norm_bwd(int dtype, int norm_kind, int upcast, const void* x, const void* w, const float* stats, const void* dy,
+                 void* dx, float* dw, float* db, void* partial, int64_t N, int32_t C, spb_stream_t stream) {
+  (void)upcast;  // the VJP ignores the intermediate rounding of the gemma variant
+  SPB_CHECK_ARG(x && w && stats && dy, SPB_E_INVALID, "spb_norm_bwd: null pointer");
+  SPB_CHECK_ARG(N >= 0 && C > 0, SPB_E_INVALID, "spb_norm_bwd: bad shape");
+  SPB_CHECK_ARG(norm_kind == SPB_NORM_RMS || norm_kind == SPB_NORM_LAYER, SPB_E_INVALID, "spb_norm_bwd: bad norm_kind %d", norm_kind);
+  if (N == 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == SPB_F32) return spb::norm_bwd_launch<float>(x, w, stats, dy, dx, dw, db, partial, N, C, norm_kind, st);
+  if (dtype == SPB_BF16) return spb::norm_bwd_launch<__nv_bfloat16>(x, w, stats, dy, dx, dw, db, partial, N, C, norm_kind, st);
+  SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "spb_norm_bwd: dtype %d", dtype);
+}
+
+int spb_colsum(int dtype, const void* x, int64_t ld, int64_t N, int32_t cols, float* out, void* partial, spb_stream_t stream) {
+  SPB_CHECK_ARG(x && out && partial, SPB_E_INVALID, "spb_colsum: null pointer");
+  SPB_CHECK_ARG(N > 0 && cols > 0 && ld >= cols, SPB_E_INVALID, "spb_colsum: bad shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == SPB_F32) return spb::colsum_launch<float>(x, ld, N, cols, out, partial, st);
+  if (dtype == SPB_BF16) return spb::colsum_launch<__nv_bfloat16>(x, ld, N, cols, out, partial, st);
+  SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "spb_colsum: dtype %d", dtype);
+}
+
+int spb_rope_apply(int dtype, void* x, int64_t ld, int64_t N, int32_t T, int32_t heads, int32_t hd, const float* table,
+                   int transpose, spb_stream_t stream) {
+  SPB_CHECK_ARG(x && table, SPB_E_INVALID, "spb_rope_apply: null pointer");
+  SPB_CHECK_ARG(N >= 0 && T > 0 && heads > 0 && hd > 0 && hd % 2 == 0 && ld >= (int64_t)heads * hd, SPB_E_INVALID,
+                "spb_rope_apply: bad shape (hd must be even)");
+  SPB_CHECK_ARG((uintptr_t)table % 16 == 0, SPB_E_INVALID, "spb_rope_apply: table must be 16-byte aligned");
+  if (N == 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == SPB_F32) return spb::rope_launch<float>(x, ld, N, T, heads, hd, table, transpose, st);
+  if (dtype == SPB_BF16) return spb::rope_launch<__nv_bfloat16>(x, ld, N, T, heads, hd, table, transpose, st);
+  SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "spb_rope_apply: dtype %d", dtype);
+}
+
+}  // extern "C"

@@ -1,0 +1,81 @@
+"""Drop-in for the hot-path functions of llama3/LLaMA-jax.ipynb: SAME names, argument order, defaults and error
+behaviour as the notebook's cells (c15 rms_norm :536, c16 precompute_freqs_cis :563, c17 apply_rotary_emb :592,
+c18 repeat_kv :626, c24 attention :809) - arrays are torch CUDA tensors because JAX is not installable in this
+image (the jax.ffi face of the same library is in jax_ffi.py / INTEGRATION.md).  Differentiable through
+torch.autograd the way the notebook's functions are through jax.value_and_grad (:995).
+
+Contract carried over from tracing: under jit the mask is a tracer whose values cannot be read, so
+``mask is not None`` means CAUSAL and ``None`` means bidirectional; the tensor itself is ignored.
+``cache is not None`` or ``position != 0`` raise: the notebook never exercises that branch and the library has
+no slow path.
+"""
+import math
+
+import torch
+
+from . import _lib as L
+from .autograd import BlockFn, NormFn, RopeFn
+from .block import BlockConfig, llama_rope_table
+
+
+def rms_norm(x, weight, eps=1e-6):
+    """llama3/LLaMA-jax.ipynb:536-538."""
+    return NormFn.apply(L.NORM_RMS, float(eps), False, x, weight, None)
+
+
+def precompute_freqs_cis(dim: int, end: int, theta: float = 10000.0, device="cuda"):
+    """llama3/LLaMA-jax.ipynb:563-567 (host-side table; fp32 math in the notebook's op order, exponent j/dim).
+    Returns complex64 [end, dim//2]."""
+    freqs = 1.0 / (theta ** (torch.arange(0, dim // 2, dtype=torch.float32) / dim))
+    t = torch.arange(end, dtype=torch.float32)
+    freqs = torch.outer(t, freqs)
+    return torch.polar(torch.ones_like(freqs), freqs).to(device)
+
+
+def _table(freqs_cis):
+    return llama_rope_table(freqs_cis.real, freqs_cis.imag)
+
+
+def apply_rotary_emb(xq, xk, freqs_cis):
+    """llama3/LLaMA-jax.ipynb:592-601; xq [B,T,Hq,hd], xk [B,T,Hkv,hd], freqs_cis [T, hd/2] complex64."""
+    tab = _table(freqs_cis)
+    return RopeFn.apply(xq, tab), RopeFn.apply(xk, tab)
+
+
+def repeat_kv(x, n_rep):
+    """llama3/LLaMA-jax.ipynb:626-627.  Kept for API parity only: attention() never materialises repeated K/V
+    (the kernels index kv_head = q_head // n_rep)."""
+    return x if n_rep == 1 else torch.repeat_interleave(x, n_rep, dim=2)
+
+
+def _cfg(x, n_heads, n_kv_heads, head_dim, mask, norm, eps=1e-6, attn_impl=L.IMPL_AUTO, gemm_impl=L.IMPL_AUTO):
+    B, T, C = x.shape
+    return BlockConfig(B=B, T=T, C=C, Hq=n_heads, Hkv=n_kv_heads, hd=head_dim, dtype=x.dtype,
+                       norm_kind=L.NORM_RMS if norm else L.NORM_NONE, norm_eps=eps, rope=True,
+                       causal=mask is not None, scale=1.0 / math.sqrt(head_dim), weight_layout=L.W_IN_OUT,
+                       attn_impl=attn_impl, gemm_impl=gemm_impl)
+
+
+def attention(params, x, mask, freqs_cis, n_heads, n_kv_heads, cache=None, position=0, comm=None):
+    """llama3/LLaMA-jax.ipynb:809-829.  Returns (out [B,T,C], (k, v)) with k, v post-rotary, un-repeated."""
+    if cache is not None or position != 0:
+        raise NotImplementedError("KV-cache decode (cache / position) is not on the training hot path and has no kernel")
+    B, T, C = x.shape
+    cfg = _cfg(x, n_heads, n_kv_heads, C // n_heads, mask, norm=False)
+    tab = _table(freqs_cis[position:position + T])
+    names = ("wq", "wk", "wv", "wo", "rope")
+    y, k, v = BlockFn.apply(cfg, names, comm, x, params["wq"], params["wk"], params["wv"], params["wo"], tab)
+    return y, (k, v)
+
+
+def attention_block(block_params, x, mask, freqs_cis, n_heads, n_kv_heads, eps=1e-6, comm=None):
+    """The fused hot path exactly as transformer_block calls it (llama3/LLaMA-jax.ipynb:881):
+    ``attention(params['attention'], rms_norm(x, params['attention_norm']), mask, freqs_cis, n_heads, n_kv_heads)``
+    - one C-ABI call forward, one backward."""
+    B, T, C = x.shape
+    cfg = _cfg(x, n_heads, n_kv_heads, C // n_heads, mask, norm=True, eps=eps)
+    tab = _table(freqs_cis[:T])
+    a = block_params["attention"]
+    names = ("wq", "wk", "wv", "wo", "norm_w", "rope")
+    y, k, v = BlockFn.apply(cfg, names, comm, x, a["wq"], a["wk"], a["wv"], a["wo"], block_params["attention_norm"], tab)
+    return y, (k, v)
