@@ -472,10 +472,10 @@ extern "C" {
 
 int spb_norm_fwd(int dtype, int norm_kind, int upcast, float eps, const void* x, const void* w, const void* b, void* y,
                  float* stats, int64_t N, int32_t C, spb_stream_t stream) {
-  SPB_CHECK_ARG(x && w && y, SPB_E_INVALID, "spb_norm_fwd: null pointer");
   SPB_CHECK_ARG(N >= 0 && C > 0, SPB_E_INVALID, "spb_norm_fwd: bad shape N=%lld C=%d", (long long)N, C);
   SPB_CHECK_ARG(norm_kind == SPB_NORM_RMS || norm_kind == SPB_NORM_LAYER, SPB_E_INVALID, "spb_norm_fwd: bad norm_kind %d", norm_kind);
-  if (N == 0) return 0;
+  if (N == 0) return 0;  // empty input: nothing to do (and its pointers may legitimately be NULL)
+  SPB_CHECK_ARG(x && w && y, SPB_E_INVALID, "spb_norm_fwd: null pointer");
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == SPB_F32) return spb::norm_fwd_launch<float>(x, w, b, y, stats, N, C, eps, norm_kind, upcast, st);
   if (dtype == SPB_BF16) return spb::norm_fwd_launch<__nv_bfloat16>(x, w, b, y, stats, N, C, eps, norm_kind, upcast, st);
@@ -491,10 +491,10 @@ size_t spb_norm_bwd_partial_bytes(int64_t N, int32_t C) {
 int spb_norm_bwd(int dtype, int norm_kind, int upcast, const void* x, const void* w, const float* stats, const void* dy,
                  void* dx, float* dw, float* db, void* partial, int64_t N, int32_t C, spb_stream_t stream) {
   (void)upcast;  // the VJP ignores the intermediate rounding of the gemma variant
-  SPB_CHECK_ARG(x && w && stats && dy, SPB_E_INVALID, "spb_norm_bwd: null pointer");
   SPB_CHECK_ARG(N >= 0 && C > 0, SPB_E_INVALID, "spb_norm_bwd: bad shape");
   SPB_CHECK_ARG(norm_kind == SPB_NORM_RMS || norm_kind == SPB_NORM_LAYER, SPB_E_INVALID, "spb_norm_bwd: bad norm_kind %d", norm_kind);
-  if (N == 0) return 0;
+  SPB_CHECK_ARG(N > 0, SPB_E_INVALID, "spb_norm_bwd: empty input (the weight gradient of an empty batch is undefined here)");
+  SPB_CHECK_ARG(x && w && stats && dy, SPB_E_INVALID, "spb_norm_bwd: null pointer");
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == SPB_F32) return spb::norm_bwd_launch<float>(x, w, stats, dy, dx, dw, db, partial, N, C, norm_kind, st);
   if (dtype == SPB_BF16) return spb::norm_bwd_launch<__nv_bfloat16>(x, w, stats, dy, dx, dw, db, partial, N, C, norm_kind, st);

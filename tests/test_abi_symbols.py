@@ -45,7 +45,7 @@ def test_version_and_argument_errors_without_a_gpu():
     lib = _lib.load()
     assert b"sm_100a" in lib.spb_version()
     # argument validation happens before any CUDA call
-    rc = lib.spb_norm_fwd(0, 1, 0, 1e-6, None, None, None, None, None, 4, 8, None)
+    rc = lib.spb_norm_fwd(0, 1, 0, 1e-6, None, None, None, None, None, 4, 8, None)  # N=4 rows, null pointers
     assert rc == -1 and b"null pointer" in lib.spb_last_error()
     d = _lib.BlockDesc(B=1, T=8, C=8, Hq=3, Hkv=2, hd=4)
     lay = _lib.WsLayout()
