@@ -166,6 +166,19 @@ int spb_gemm(int in_dtype, int out_dtype, int impl, int64_t M, int64_t N, int64_
 int spb_colsum(int dtype, const void* x, int64_t ld, int64_t N, int32_t cols, float* out, void* partial,
                spb_stream_t stream);
 
+/* spb_colsum without caller-provided scratch.  No counterpart in the reference (it has no native code); it exists for
+ * hosts that have no way to hand this library scratch memory: an XLA/jax.ffi handler that was registered without a
+ * scratch result (XLA owns every buffer and the handler may not cudaMalloc), or a process whose own pool has already
+ * claimed all of HBM so that any further driver allocation fails or stalls the device.  The two-stage reduction's
+ * partial sums live in a fixed 4 MiB array inside the library image (every GPU that loads the library carries it until
+ * the process exits).  Limits: cols <= 8192 (wider matrices return SPB_E_LIMIT - use spb_colsum); any N.
+ * This call performs no cudaMalloc/cudaFree and calls no allocating routine.  The first call on each device looks up
+ * the array's device address (cudaGetSymbolAddress) and caches it - make that first call before starting any stream
+ * capture.  Every call on a device shares the one array: calls that can overlap on the GPU (different streams, or
+ * different host threads) race on it and must be ordered by the caller.  Nothing in the array has to start at zero
+ * (stage one overwrites every partial that stage two reads), so stale contents from the previous call are harmless.   */
+int spb_colsum_static(int dtype, const void* x, int64_t ld, int64_t N, int32_t cols, float* out, spb_stream_t stream);
+
 /* llama3:820-828 (repeat_kv + transpose + QK^T/sqrt(hd) + mask + softmax + PV + merge heads), never
  * materialising scores or repeated K/V.  q[N,Hq*hd] (ldq), k,v[N,Hkv*hd] (ldk,ldv), o[N,Hq*hd] (ldo),
  * lse[B,Hq,T] fp32.  kv head of q head h is h / (Hq/Hkv)  (llama3:626-627 consecutive grouping).        */

@@ -56,6 +56,7 @@ SIGNATURES = {
     "spb_gemm": (C.c_int, [C.c_int, C.c_int, C.c_int, i64, i64, i64, vp, i64, C.c_int, vp, i64, C.c_int, vp, i64, vp,
                            C.c_int, vp]),
     "spb_colsum": (C.c_int, [C.c_int, vp, i64, i64, i32, vp, vp, vp]),
+    "spb_colsum_static": (C.c_int, [C.c_int, vp, i64, i64, i32, vp, vp]),
     "spb_flash_fwd": (C.c_int, [C.c_int, C.c_int, i32, i32, i32, i32, i32, C.c_int, f32, vp, i64, vp, i64, vp, i64, vp,
                                 i64, vp, vp]),
     "spb_flash_bwd": (C.c_int, [C.c_int, C.c_int, i32, i32, i32, i32, i32, C.c_int, f32, vp, i64, vp, i64, vp, i64, vp,

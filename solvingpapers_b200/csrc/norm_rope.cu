@@ -5,6 +5,8 @@
 //   * rotary (llama3:592-601 adjacent-pair rotation; gemma:182-200 "rotary" = general 2x2 per (t,pair) table),
 //     in place on the q|k column range of the packed qkv buffer, 128-bit loads, and its transpose for the VJP.
 // Algorithmic bytes: norm fwd 2*N*C*e (+8N stats); norm bwd dx 3*N*C*e; rope 2*N*cols*e.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace spb {
@@ -465,6 +467,51 @@ static int rope_launch(void* x, int64_t ld, int64_t N, int T_len, int heads, int
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------ allocation-free column sum
+// Scratch for spb_colsum_static lives in the library image itself, so a caller that cannot obtain device memory can still
+// run the two-stage column sum.  4 MiB per GPU that loads the library, resident until the process exits.
+constexpr size_t COLSUM_STATIC_FLOATS = (size_t)1 << 20;
+constexpr int COLSUM_STATIC_MAX_COLS = 8192;  // => at least 128 row chunks always fit
+constexpr int COLSUM_STATIC_MAX_DEVICES = 64;
+static __device__ __align__(256) float g_colsum_static_scratch[COLSUM_STATIC_FLOATS];
+
+// In host code `g_colsum_static_scratch` is only a handle for the symbol, never an address a kernel may use: the device
+// address is looked up once per device (with that device current) and cached.
+static int colsum_static_scratch_addr(float** out) {
+  static std::mutex mu;
+  static float* addr[COLSUM_STATIC_MAX_DEVICES] = {};
+  int dev = 0;
+  SPB_CUDA(cudaGetDevice(&dev));
+  SPB_CHECK_ARG(dev >= 0 && dev < COLSUM_STATIC_MAX_DEVICES, SPB_E_LIMIT, "spb_colsum_static: device ordinal %d beyond %d", dev,
+                COLSUM_STATIC_MAX_DEVICES);
+  std::lock_guard<std::mutex> lk(mu);
+  if (addr[dev] == nullptr) {
+    float* p = nullptr;
+    SPB_CUDA(cudaGetSymbolAddress((void**)&p, g_colsum_static_scratch));
+    SPB_CHECK_ARG(p != nullptr, SPB_E_STATE, "spb_colsum_static: cudaGetSymbolAddress returned a null address");
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return 0;
+}
+
+template <typename T>
+static int colsum_static_launch(const void* x, int64_t ld, int64_t N, int cols, float* out, float* scratch, cudaStream_t st) {
+  int chunks, rpc;
+  colsum_plan(N, &chunks, &rpc);
+  const int max_chunks = (int)(COLSUM_STATIC_FLOATS / (size_t)cols);  // >= 128 because cols <= 8192
+  if (chunks > max_chunks) {
+    rpc = (int)((N + max_chunks - 1) / max_chunks);
+    chunks = (int)((N + rpc - 1) / rpc);
+  }
+  dim3 grid((cols + 255) / 256, chunks);
+  colsum_partial_kernel<T, 0><<<grid, 256, 0, st>>>((const T*)x, ld, nullptr, nullptr, 0, N, cols, rpc, chunks, scratch);
+  SPB_LAUNCH_CHECK();
+  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, st>>>(scratch, chunks, cols, out, nullptr);
+  SPB_LAUNCH_CHECK();
+  return 0;
+}
+
 }  // namespace spb
 
 // ------------------------------------------------------------------------------------------------ C ABI
@@ -521,6 +568,22 @@ int spb_rope_apply(int dtype, void* x, int64_t ld, int64_t N, int32_t T, int32_t
   if (dtype == SPB_F32) return spb::rope_launch<float>(x, ld, N, T, heads, hd, table, transpose, st);
   if (dtype == SPB_BF16) return spb::rope_launch<__nv_bfloat16>(x, ld, N, T, heads, hd, table, transpose, st);
   SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "spb_rope_apply: dtype %d", dtype);
+}
+
+// Column sum for callers that have no way to get scratch memory: out[c] = sum_n x[n, c], fp32.  See include/spb200.h.
+int spb_colsum_static(int dtype, const void* x, int64_t ld, int64_t N, int32_t cols, float* out, spb_stream_t stream) {
+  SPB_CHECK_ARG(x && out, SPB_E_INVALID, "spb_colsum_static: null pointer");
+  SPB_CHECK_ARG(N > 0 && cols > 0 && ld >= cols, SPB_E_INVALID, "spb_colsum_static: bad shape");
+  SPB_CHECK_ARG(cols <= spb::COLSUM_STATIC_MAX_COLS, SPB_E_LIMIT,
+                "spb_colsum_static: %d columns is beyond the fixed scratch (at most %d columns; use spb_colsum with your own "
+                "scratch for wider matrices)", cols, spb::COLSUM_STATIC_MAX_COLS);
+  float* scratch = nullptr;
+  int rc = spb::colsum_static_scratch_addr(&scratch);  // first call on a device resolves the symbol's device address
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == SPB_F32) return spb::colsum_static_launch<float>(x, ld, N, cols, out, scratch, st);
+  if (dtype == SPB_BF16) return spb::colsum_static_launch<__nv_bfloat16>(x, ld, N, cols, out, scratch, st);
+  SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "spb_colsum_static: dtype %d", dtype);
 }
 
 }  // extern "C"
