@@ -121,6 +121,10 @@ static int pick_attn_impl(int impl, int dtype, int hd) {
   if (impl == SPB_IMPL_AUTO) return flash_tc_supported(dtype, hd) ? SPB_IMPL_TCGEN05 : SPB_IMPL_SIMT;
   return impl;
 }
+static int pick_attn_bwd_impl(int impl, int dtype, int hd) {
+  if (impl == SPB_IMPL_AUTO) return flash_bwd_tc_supported(dtype, hd) ? SPB_IMPL_TCGEN05 : SPB_IMPL_SIMT;
+  return impl;
+}
 
 }  // namespace spb
 
@@ -222,9 +226,9 @@ int spb_flash_bwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t
   SPB_CHECK_ARG(q && k && v && o && d_o && lse && delta && dq && dk && dv, SPB_E_INVALID, "spb_flash_bwd: null pointer");
   SPB_CHECK_ARG(B > 0 && T > 0 && Hq > 0 && Hkv > 0 && hd > 0 && Hq % Hkv == 0, SPB_E_INVALID, "spb_flash_bwd: bad shape");
   cudaStream_t st = (cudaStream_t)stream;
-  const int use = pick_attn_impl(impl, dtype, hd);
+  const int use = pick_attn_bwd_impl(impl, dtype, hd);
   if (use == SPB_IMPL_TCGEN05) {
-    SPB_CHECK_ARG(flash_tc_supported(dtype, hd), SPB_E_UNSUPPORTED, "spb_flash_bwd: tcgen05 path needs bf16 and hd in {64,128} (dtype=%d hd=%d)", dtype, hd);
+    SPB_CHECK_ARG(flash_bwd_tc_supported(dtype, hd), SPB_E_UNSUPPORTED, "spb_flash_bwd: tcgen05 path needs bf16 and hd in {64,128} (dtype=%d hd=%d)", dtype, hd);
     SPB_CHECK_ARG(dq_acc != nullptr, SPB_E_INVALID, "spb_flash_bwd: the tcgen05 path needs the fp32 dq_acc scratch");
     return flash_bwd_tc(B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk, dv,
                         lddv, dq_acc, st);

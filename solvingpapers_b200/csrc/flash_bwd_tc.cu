@@ -1,0 +1,474 @@
+// flash_bwd_tc.cu - K4: flash attention backward on tcgen05 (bf16, hd in {64,128}).  VJP of llama3:820-828; the notebook
+// has no hand-written backward (jax.value_and_grad, llama3:995) and XLA's saves the [B,H,T,T] probabilities - here they
+// are recomputed tile by tile from (q, k, v, lse).
+//
+// One CTA owns one KV tile (128 rows) of one (batch, kv head) and loops over the q heads of its group and the 64-row Q
+// tiles that can see it (causal: from the diagonal on).  Everything is computed TRANSPOSED so that a thread owns a KV row
+// in the element-wise phase and an hd column in the dQ phase:
+//   (1) S^T  = K  Q^T          M=128(kv) N=64(q)  K=hd     A=K  (K-major)   B=Q_i  (K-major)
+//   (2) dP^T = V  dO^T         M=128     N=64     K=hd     A=V  (K-major)   B=dO_i (K-major)
+//       P^T = exp2(S^T*c - lse*log2e),  dS^T = P^T o (dP^T - delta) * scale      [threads; bf16 -> smem, UMMA layout]
+//   (3) dV  += P^T  dO_i       M=128(kv) N=hd     K=64(q)  A=P^T (K-major)  B=dO_i (MN-major: same smem tile as (2))
+//   (4) dK  += dS^T Q_i        M=128     N=hd     K=64     A=dS^T(K-major)  B=Q_i  (MN-major: same tile as (1))
+//   (5) dQ^T = K^T  dS         M=128(hd) N=64(q)  K=128(kv) A=K (MN-major view of the resident K tile)
+//                                                           B=dS^T buffer read MN-major
+// dV and dK accumulate in TMEM over ALL iterations (the GQA group sum of repeat_kv's VJP happens there); dQ^T is drained
+// every iteration: thread d adds column d of 64 query rows into the fp32 dq accumulator - 32 lanes hit 32 consecutive
+// floats, one coalesced 128-byte reduction per warp instruction.  TMEM: S^T 64 + dP^T 64 + dV hd + dK hd + dQ^T 64 <= 448.
+// Warps: 0 = TMA producer (K,V once; Q_i,dO_i double buffered), 1 = MMA issuer, 2-5 = element-wise / drain / epilogue.
+// Scratch: delta[B,Hq,T] (rowsum(dO*O), prep kernel) and dq_acc[N,Hq*hd] fp32 (zeroed per call, converted at the end).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace spb {
+
+constexpr int FB_THREADS = 192;
+constexpr float FB_LOG2E = 1.4426950408889634f;
+
+__device__ __forceinline__ float fb_exp2(float x) {
+  float y;
+  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int HD>
+struct FaBwdCfg {
+  static constexpr int CH = HD / 64;
+  static constexpr int K_BYTES = 2 * 16384;        // always two 64-column chunks: for hd=64 the second one is zeros (M=128 view of K^T)
+  static constexpr int V_BYTES = CH * 16384;
+  static constexpr int Q_BYTES = CH * 8192;        // 64 rows x HD
+  static constexpr int PT_BYTES = 16384;           // 128 kv rows x 64 q columns
+  static constexpr int OFF_K = 0;
+  static constexpr int OFF_V = OFF_K + K_BYTES;
+  static constexpr int OFF_Q = OFF_V + V_BYTES;    // 2 stages
+  static constexpr int OFF_DO = OFF_Q + 2 * Q_BYTES;
+  static constexpr int OFF_PT = OFF_DO + 2 * Q_BYTES;
+  static constexpr int OFF_DST = OFF_PT + PT_BYTES;
+  static constexpr int OFF_LSE = OFF_DST + PT_BYTES;  // [2][64] lse*log2e, then [2][64] delta
+  static constexpr int OFF_BAR = OFF_LSE + 4 * 64 * 4;
+  static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
+  static constexpr int TM_ST = 0, TM_DPT = 64, TM_DV = 128, TM_DK = 256, TM_DQT = 384;
+  static constexpr int TMEM_COLS = 512;
+  static constexpr int DQ_WARPS = HD / 32;         // warps that own a valid hd row of dQ^T
+};
+
+struct FaBwdArgs {
+  const float* lse;
+  const float* delta;
+  float* dq_acc;
+  int64_t ld_acc;
+  __nv_bfloat16* dk;
+  int64_t lddk;
+  __nv_bfloat16* dv;
+  int64_t lddv;
+  int T, Hq, Hkv, causal;
+  float scale, scale_log2;
+};
+
+template <int HD>
+__global__ void __launch_bounds__(FB_THREADS, 1)
+    flash_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
+                        const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmDO, const FaBwdArgs p) {
+  using Cfg = FaBwdCfg<HD>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sK = smem + Cfg::OFF_K;
+  uint8_t* sV = smem + Cfg::OFF_V;
+  uint8_t* sQ = smem + Cfg::OFF_Q;
+  uint8_t* sDO = smem + Cfg::OFF_DO;
+  uint8_t* sPT = smem + Cfg::OFF_PT;
+  uint8_t* sDST = smem + Cfg::OFF_DST;
+  float* sLse = reinterpret_cast<float*>(smem + Cfg::OFF_LSE);  // [2][64]
+  float* sDelta = sLse + 128;                                    // [2][64]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
+  uint64_t* kv_full = bars;         // [1]
+  uint64_t* qdo_full = bars + 1;    // [2]
+  uint64_t* qdo_empty = bars + 3;   // [2]
+  uint64_t* sdp_full = bars + 5;
+  uint64_t* sdp_empty = bars + 6;
+  uint64_t* pds_full = bars + 7;
+  uint64_t* pds_empty = bars + 8;
+  uint64_t* dq_full = bars + 9;
+  uint64_t* dq_empty = bars + 10;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+
+  const int nt = blockIdx.x, g = blockIdx.y, b = blockIdx.z;
+  const int kv0 = nt * 128;
+  const int n_rep = p.Hq / p.Hkv;
+  const int n_q64 = (p.T + 63) / 64;
+  const int i_start = p.causal ? (kv0 / 64) : 0;
+  const int n_i = n_q64 - i_start;
+  const int n_it = n_rep * n_i;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmK);
+    prefetch_tmap(&tmV);
+    prefetch_tmap(&tmQ);
+    prefetch_tmap(&tmDO);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(kv_full, 1);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&qdo_full[i], 1);
+        mbar_init(&qdo_empty[i], 1);
+      }
+      mbar_init(sdp_full, 1);
+      mbar_init(sdp_empty, 4);
+      mbar_init(pds_full, 4);
+      mbar_init(pds_empty, 1);
+      mbar_init(dq_full, 1);
+      mbar_init(dq_empty, Cfg::DQ_WARPS);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    tmem_relinquish();
+  }
+  if (HD == 64 && warp >= 2) {
+    // zero the second 64-column chunk of the K buffer: rows 64..127 of the M=128 view of K^T
+    uint4* z = reinterpret_cast<uint4*>(sK + 16384);
+    for (int i = threadIdx.x - 64; i < 16384 / 16; i += 128) z[i] = make_uint4(0, 0, 0, 0);
+    fence_proxy_async_smem();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      const int row_kv = b * p.T + kv0;
+      mbar_arrive_expect_tx(kv_full, Cfg::CH * 16384 * 2);
+#pragma unroll
+      for (int c = 0; c < Cfg::CH; ++c) {
+        tma_load_2d(sK + c * 16384, &tmK, kv_full, g * HD + c * 64, row_kv);
+        tma_load_2d(sV + c * 16384, &tmV, kv_full, g * HD + c * 64, row_kv);
+      }
+      for (int it = 0; it < n_it; ++it) {
+        const int st = it & 1;
+        const uint32_t u = (it >> 1) & 1;
+        const int h = g * n_rep + it / n_i;
+        const int row_q = b * p.T + (i_start + it % n_i) * 64;
+        mbar_wait(&qdo_empty[st], u ^ 1);
+        mbar_arrive_expect_tx(&qdo_full[st], 2 * Cfg::Q_BYTES);
+#pragma unroll
+        for (int c = 0; c < Cfg::CH; ++c) {
+          tma_load_2d(sQ + st * Cfg::Q_BYTES + c * 8192, &tmQ, &qdo_full[st], h * HD + c * 64, row_q);
+          tma_load_2d(sDO + st * Cfg::Q_BYTES + c * 8192, &tmDO, &qdo_full[st], h * HD + c * 64, row_q);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc_s = umma_idesc_bf16(128, 64, 0, 0);
+      const uint32_t idesc_g = umma_idesc_bf16(128, HD, 0, 1);
+      const uint32_t idesc_q = umma_idesc_bf16(128, 64, 1, 1);
+      const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV), pt_addr = smem_u32(sPT), dst_addr = smem_u32(sDST);
+      mbar_wait(kv_full, 0);
+      auto issue_s = [&](int it) {
+        const int st = it & 1;
+        mbar_wait(&qdo_full[st], (it >> 1) & 1);
+        mbar_wait(sdp_empty, (it & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t q_addr = smem_u32(sQ + st * Cfg::Q_BYTES), do_addr = smem_u32(sDO + st * Cfg::Q_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
+          umma_bf16(tmem_base + Cfg::TM_ST, umma_desc_kmajor(k_addr + aoff), umma_desc_kmajor(q_addr + boff), idesc_s, kk > 0 ? 1u : 0u);
+        }
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
+          umma_bf16(tmem_base + Cfg::TM_DPT, umma_desc_kmajor(v_addr + aoff), umma_desc_kmajor(do_addr + boff), idesc_s, kk > 0 ? 1u : 0u);
+        }
+        umma_commit(sdp_full);
+      };
+      auto issue_g = [&](int it) {
+        const int st = it & 1;
+        mbar_wait(pds_full, it & 1);
+        mbar_wait(dq_empty, (it & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t q_addr = smem_u32(sQ + st * Cfg::Q_BYTES), do_addr = smem_u32(sDO + st * Cfg::Q_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)  // dV += P^T dO
+          umma_bf16(tmem_base + Cfg::TM_DV, umma_desc_kmajor(pt_addr + kk * 32), umma_desc_mnmajor(do_addr + kk * 2048, 64), idesc_g,
+                    (it > 0 || kk > 0) ? 1u : 0u);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)  // dK += dS^T Q
+          umma_bf16(tmem_base + Cfg::TM_DK, umma_desc_kmajor(dst_addr + kk * 32), umma_desc_mnmajor(q_addr + kk * 2048, 64), idesc_g,
+                    (it > 0 || kk > 0) ? 1u : 0u);
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)  // dQ^T = K^T dS
+          umma_bf16(tmem_base + Cfg::TM_DQT, umma_desc_mnmajor(k_addr + kk * 2048, 128), umma_desc_mnmajor(dst_addr + kk * 2048, 128),
+                    idesc_q, kk > 0 ? 1u : 0u);
+        umma_commit(&qdo_empty[st]);
+        umma_commit(pds_empty);
+        umma_commit(dq_full);
+      };
+      issue_s(0);
+      for (int it = 0; it < n_it; ++it) {
+        if (it + 1 < n_it) issue_s(it + 1);
+        issue_g(it);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------------ element-wise, dQ drain, epilogue (warps 2..5)
+    const int qd = warp & 3;
+    const int r = qd * 32 + lane;  // kv row in phase A, hd column in the dQ phase; both = TMEM lane
+    const int ct = threadIdx.x - 64;  // 0..127
+    const int kv_idx = kv0 + r;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
+    for (int it = 0; it < n_it; ++it) {
+      const int st = it & 1;
+      const int h = g * n_rep + it / n_i;
+      const int q0 = (i_start + it % n_i) * 64;
+      // stage lse*log2e and delta of the 64 query rows (double buffered; one named barrier per iteration)
+      {
+        const int c = ct & 63;
+        const int qi = q0 + c;
+        const float* src = (ct < 64) ? p.lse : p.delta;
+        float val = 0.f;
+        if (qi < p.T) val = src[((int64_t)b * p.Hq + h) * p.T + qi];
+        if (ct < 64) sLse[st * 64 + c] = val * FB_LOG2E;
+        else sDelta[st * 64 + c] = val;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+
+      // ---- phase A: P^T and dS^T rows
+      mbar_wait(sdp_full, it & 1);
+      tc_fence_after();
+      float sT[64], dpT[64];
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t raw[32];
+        SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_ST + c * 32), raw);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) sT[c * 32 + i] = __uint_as_float(raw[i]);
+        SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_DPT + c * 32), raw);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) dpT[c * 32 + i] = __uint_as_float(raw[i]);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(sdp_empty);
+
+      const bool need_mask = (p.causal && q0 < kv0 + 128) || (q0 + 64 > p.T) || (kv0 + 128 > p.T);
+#pragma unroll
+      for (int i = 0; i < 64; ++i) {
+        float pv = fb_exp2(sT[i] * p.scale_log2 - sLse[st * 64 + i]);
+        if (need_mask) {
+          const int qi = q0 + i;
+          if ((p.causal && kv_idx > qi) || qi >= p.T || kv_idx >= p.T) pv = 0.f;
+        }
+        sT[i] = pv;
+        dpT[i] = pv * (dpT[i] - sDelta[st * 64 + i]) * p.scale;
+      }
+      mbar_wait(pds_empty, (it & 1) ^ 1);  // MMAs (3)(4)(5) of the previous iteration have finished reading P^T / dS^T
+      uint8_t* prow = sPT + r * 128;
+      uint8_t* drow = sDST + r * 128;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        uint4 v;
+        v.x = pack_bf16(sT[c * 8 + 0], sT[c * 8 + 1]);
+        v.y = pack_bf16(sT[c * 8 + 2], sT[c * 8 + 3]);
+        v.z = pack_bf16(sT[c * 8 + 4], sT[c * 8 + 5]);
+        v.w = pack_bf16(sT[c * 8 + 6], sT[c * 8 + 7]);
+        *reinterpret_cast<uint4*>(prow + ((c ^ (r & 7)) << 4)) = v;
+        uint4 w;
+        w.x = pack_bf16(dpT[c * 8 + 0], dpT[c * 8 + 1]);
+        w.y = pack_bf16(dpT[c * 8 + 2], dpT[c * 8 + 3]);
+        w.z = pack_bf16(dpT[c * 8 + 4], dpT[c * 8 + 5]);
+        w.w = pack_bf16(dpT[c * 8 + 6], dpT[c * 8 + 7]);
+        *reinterpret_cast<uint4*>(drow + ((c ^ (r & 7)) << 4)) = w;
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pds_full);
+
+      // ---- dQ phase: thread r owns hd column r of dQ^T; 64 query rows per iteration
+      if (qd < Cfg::DQ_WARPS) {  // warp-uniform (hd=64: only two warps hold real rows)
+        mbar_wait(dq_full, it & 1);
+        tc_fence_after();
+        float dq[64];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t raw[32];
+          SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_DQT + c * 32), raw);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) dq[c * 32 + i] = __uint_as_float(raw[i]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(dq_empty);
+        float* acc = p.dq_acc + ((int64_t)b * p.T + q0) * p.ld_acc + (int64_t)h * HD + r;
+#pragma unroll 8
+        for (int i = 0; i < 64; ++i)
+          if (q0 + i < p.T) atomicAdd(acc + (int64_t)i * p.ld_acc, dq[i]);
+      }
+    }
+    // ---- epilogue: dV, dK rows -> bf16 -> global.  The last dq_full commit covers every MMA issued before it.
+    if (qd >= Cfg::DQ_WARPS) {  // warps that skipped the dQ phase still need the completion guarantee
+      mbar_wait(dq_full, (n_it - 1) & 1);
+    }
+    tc_fence_after();
+    const bool valid = kv_idx < p.T;
+    __nv_bfloat16* dvrow = p.dv + ((int64_t)b * p.T + kv_idx) * p.lddv + (int64_t)g * HD;
+    __nv_bfloat16* dkrow = p.dk + ((int64_t)b * p.T + kv_idx) * p.lddk + (int64_t)g * HD;
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      __nv_bfloat16* orow = which ? dkrow : dvrow;
+      const int tm = which ? Cfg::TM_DK : Cfg::TM_DV;
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t o[32];
+        SPB_TMEM_LD_32(lane_base + (uint32_t)(tm + c * 32), o);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 8) {
+            uint4 v;
+            v.x = pack_bf16(__uint_as_float(o[i]), __uint_as_float(o[i + 1]));
+            v.y = pack_bf16(__uint_as_float(o[i + 2]), __uint_as_float(o[i + 3]));
+            v.z = pack_bf16(__uint_as_float(o[i + 4]), __uint_as_float(o[i + 5]));
+            v.w = pack_bf16(__uint_as_float(o[i + 6]), __uint_as_float(o[i + 7]));
+            *reinterpret_cast<uint4*>(orow + c * 32 + i) = v;
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+// delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]; one warp per (token, head) row, 4-byte loads (bf16x2)
+template <int HD>
+__global__ void __launch_bounds__(256) flash_bwd_prep_kernel(const __nv_bfloat16* __restrict__ o, int64_t ldo,
+                                                             const __nv_bfloat16* __restrict__ d_o, int64_t lddo,
+                                                             float* __restrict__ delta, int B, int T, int Hq) {
+  const int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  const int64_t total = (int64_t)B * T * Hq;
+  if (w >= total) return;
+  const int h = (int)(w % Hq);
+  const int64_t tok = w / Hq;
+  const uint32_t* orow = reinterpret_cast<const uint32_t*>(o + tok * ldo + (int64_t)h * HD);
+  const uint32_t* drow = reinterpret_cast<const uint32_t*>(d_o + tok * lddo + (int64_t)h * HD);
+  float s = 0.f;
+#pragma unroll
+  for (int i = lane; i < HD / 2; i += 32) {
+    const float2 a = unpack_bf16(orow[i]), c = unpack_bf16(drow[i]);
+    s += a.x * c.x + a.y * c.y;
+  }
+  s = warp_sum(s);
+  if (lane == 0) {
+    const int64_t bb = tok / T, t = tok % T;
+    delta[(bb * Hq + h) * T + t] = s;
+  }
+}
+
+// dq[n, c] = bf16(dq_acc[n, c]); 8 elements per thread
+__global__ void __launch_bounds__(256) flash_bwd_dq_convert_kernel(const float* __restrict__ acc, int64_t ld_acc,
+                                                                   __nv_bfloat16* __restrict__ dq, int64_t lddq, int64_t N,
+                                                                   int cols) {
+  const int vec_per_row = cols / 8;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= N * vec_per_row) return;
+  const int64_t n = idx / vec_per_row;
+  const int c = (int)(idx % vec_per_row) * 8;
+  const float4 a = *reinterpret_cast<const float4*>(acc + n * ld_acc + c);
+  const float4 b = *reinterpret_cast<const float4*>(acc + n * ld_acc + c + 4);
+  uint4 v;
+  v.x = pack_bf16(a.x, a.y);
+  v.y = pack_bf16(a.z, a.w);
+  v.z = pack_bf16(b.x, b.y);
+  v.w = pack_bf16(b.z, b.w);
+  *reinterpret_cast<uint4*>(dq + n * lddq + c) = v;
+}
+
+bool flash_bwd_tc_supported(int dtype, int hd) { return dtype == SPB_BF16 && (hd == 64 || hd == 128); }
+
+template <int HD>
+static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float scale, const void* q, int64_t ldq, const void* k,
+                               int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o, int64_t lddo,
+                               const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
+                               float* dq_acc, cudaStream_t st) {
+  using Cfg = FaBwdCfg<HD>;
+  const int64_t N = (int64_t)B * Tn;
+  const int64_t ld_acc = (int64_t)Hq * HD;
+  // scratch: dq accumulator starts at zero; delta = rowsum(dO * O)
+  SPB_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)N * ld_acc * sizeof(float), st));
+  {
+    const int64_t rows = N * Hq;
+    flash_bwd_prep_kernel<HD><<<(unsigned)((rows + 7) / 8), 256, 0, st>>>((const __nv_bfloat16*)o, ldo, (const __nv_bfloat16*)d_o, lddo,
+                                                                          delta, B, Tn, Hq);
+    SPB_LAUNCH_CHECK();
+  }
+  CUtensorMap tmK, tmV, tmQ, tmDO;
+  int rc;
+  if ((rc = make_tmap_2d(&tmK, k, 2, (uint64_t)N, (uint64_t)Hkv * HD, (uint64_t)ldk, 128, 64, true, false))) return rc;
+  if ((rc = make_tmap_2d(&tmV, v, 2, (uint64_t)N, (uint64_t)Hkv * HD, (uint64_t)ldv, 128, 64, true, false))) return rc;
+  if ((rc = make_tmap_2d(&tmQ, q, 2, (uint64_t)N, (uint64_t)Hq * HD, (uint64_t)ldq, 64, 64, true, false))) return rc;
+  if ((rc = make_tmap_2d(&tmDO, d_o, 2, (uint64_t)N, (uint64_t)Hq * HD, (uint64_t)lddo, 64, 64, true, false))) return rc;
+  FaBwdArgs a;
+  a.lse = lse;
+  a.delta = delta;
+  a.dq_acc = dq_acc;
+  a.ld_acc = ld_acc;
+  a.dk = (__nv_bfloat16*)dk;
+  a.lddk = lddk;
+  a.dv = (__nv_bfloat16*)dv;
+  a.lddv = lddv;
+  a.T = Tn;
+  a.Hq = Hq;
+  a.Hkv = Hkv;
+  a.causal = causal;
+  a.scale = scale;
+  a.scale_log2 = scale * FB_LOG2E;
+  SPB_CUDA(cudaFuncSetAttribute(flash_bwd_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+  dim3 grid((Tn + 127) / 128, Hkv, B);
+  flash_bwd_tc_kernel<HD><<<grid, FB_THREADS, Cfg::SMEM_BYTES, st>>>(tmK, tmV, tmQ, tmDO, a);
+  SPB_LAUNCH_CHECK();
+  {
+    const int cols = Hq * HD;
+    const int64_t total = N * (cols / 8);
+    flash_bwd_dq_convert_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(dq_acc, ld_acc, (__nv_bfloat16*)dq, lddq, N, cols);
+    SPB_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+int flash_bwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k,
+                 int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o, int64_t lddo,
+                 const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
+                 float* dq_acc, cudaStream_t st) {
+  const void* ptrs[8] = {q, k, v, o, d_o, dq, dk, dv};
+  const int64_t lds[8] = {ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv};
+  for (int i = 0; i < 8; ++i)
+    SPB_CHECK_ARG(((uintptr_t)ptrs[i] % 16 == 0) && (lds[i] % 8 == 0), SPB_E_UNSUPPORTED,
+                  "flash backward (tcgen05): operand %d must be 16-byte aligned with a leading dimension multiple of 8", i);
+  SPB_CHECK_ARG((uintptr_t)dq_acc % 16 == 0, SPB_E_INVALID, "flash backward (tcgen05): dq_acc must be 16-byte aligned");
+  if (hd == 128)
+    return flash_bwd_tc_launch<128>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk,
+                                    dv, lddv, dq_acc, st);
+  if (hd == 64)
+    return flash_bwd_tc_launch<64>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk, dv,
+                                   lddv, dq_acc, st);
+  SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "flash backward (tcgen05): hd %d", hd);
+}
+
+}  // namespace spb

@@ -19,6 +19,7 @@ int attn_simt_bwd(int dtype, int B, int Tn, int Hq, int Hkv, int hd, int causal,
 
 // tcgen05 flash attention (bf16, hd in {64,128})
 bool flash_tc_supported(int dtype, int hd);
+bool flash_bwd_tc_supported(int dtype, int hd);
 int flash_fwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k,
                  int64_t ldk, const void* v, int64_t ldv, void* o, int64_t ldo, float* lse, cudaStream_t st);
 int flash_bwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k,

@@ -237,3 +237,33 @@ def test_attention_simt(dtype, B, T, Hq, Hkv, hd, causal):
     errs = _attn_case(dtype, B, T, Hq, Hkv, hd, causal, L.IMPL_SIMT)
     for k, e in errs.items():
         assert e < tol(dtype), (k, errs)
+
+
+@pytest.mark.parametrize("B,T,Hq,Hkv,hd,causal", [
+    (2, 128, 4, 2, 64, True),     # C1 shape in bf16
+    (1, 197, 3, 3, 64, False),    # ViT-B/16: ragged T, bidirectional
+    (2, 256, 4, 1, 128, True),    # MQA, two KV tiles, diagonal masking
+    (1, 384, 8, 2, 128, True),    # Llama-8B head geometry (4 q heads per kv head)
+    (1, 200, 2, 2, 128, False),   # ragged, hd 128
+    (1, 1, 2, 2, 64, True),       # single token
+    (1, 130, 2, 1, 64, True),     # just past one tile
+])
+def test_attention_tcgen05_flash(B, T, Hq, Hkv, hd, causal):
+    """tcgen05 flash forward + backward (bf16) against the oracle math; bf16-mode tolerance 2e-2."""
+    L = _L()
+    errs = _attn_case(torch.bfloat16, B, T, Hq, Hkv, hd, causal, L.IMPL_TCGEN05)
+    for k, e in errs.items():
+        assert e < TOL_BF16, (k, errs)
+
+
+def test_attention_tcgen05_is_deterministic_forward_and_rejects_unsupported():
+    ops, L = _ops(), _L()
+    q = rnd((1, 256, 2, 128), 3, torch.bfloat16).to(DEV)
+    o1, l1 = ops.flash_fwd(q, q, q, True, 0.1, impl=L.IMPL_TCGEN05)
+    o2, l2 = ops.flash_fwd(q, q, q, True, 0.1, impl=L.IMPL_TCGEN05)
+    assert torch.equal(o1, o2) and torch.equal(l1, l2)
+    with pytest.raises(L.SpbError):  # fp32 has no tcgen05 attention: error, not a silent slow path
+        ops.flash_fwd(q.float(), q.float(), q.float(), True, 0.1, impl=L.IMPL_TCGEN05)
+    q256 = rnd((1, 64, 1, 256), 4, torch.bfloat16).to(DEV)
+    with pytest.raises(L.SpbError):
+        ops.flash_fwd(q256, q256, q256, True, 0.1, impl=L.IMPL_TCGEN05)

@@ -1,11 +1,23 @@
 #!/bin/bash
-# One GPU-box visit: diagnostics + tests + bench, each in its own process with its own timeout; logs to gpurun_out/.
+# One GPU-box visit: tests + bench (+ optional ncu passes), each in its own process with its own timeout; logs to gpurun_out/.
 mkdir -p gpurun_out
-nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw,memory.total --format=csv > gpurun_out/smi.log 2>&1
-timeout 300 python tools/diag_gemm.py > gpurun_out/diag_gemm.log 2>&1; echo "diag_gemm rc=$?" >> gpurun_out/diag_gemm.log
-timeout 900 python -m pytest tests/test_gpu_kernels.py -q -m gpu -k "not tcgen05" --timeout 300 -p no:cacheprovider > gpurun_out/t1.log 2>&1
-timeout 600 python -m pytest tests/test_gpu_kernels.py -q -m gpu -k "tcgen05" --timeout 120 -p no:cacheprovider > gpurun_out/t2.log 2>&1
-timeout 1200 python -m pytest tests/test_gpu_block.py tests/test_gpu_dropin.py tests/test_gpu_dp.py -q -m gpu --timeout 600 -p no:cacheprovider > gpurun_out/t3.log 2>&1
-timeout 900 python bench.py --steps 5 --warmup 3 > gpurun_out/bench.log 2> gpurun_out/bench.err
-for f in diag_gemm t1 t2 t3; do echo "=== $f"; tail -n 40 gpurun_out/$f.log; done
-echo "=== bench"; cat gpurun_out/bench.log; tail -n 15 gpurun_out/bench.err
+timeout 1500 python -m pytest tests -q -m gpu --timeout 600 -p no:cacheprovider > gpurun_out/tests_gpu.log 2>&1; echo "pytest rc=$?"
+tail -n 15 gpurun_out/tests_gpu.log
+timeout 900 python bench.py --steps 20 --warmup 5 > gpurun_out/bench.log 2> gpurun_out/bench.err; echo "bench rc=$?"
+cat gpurun_out/bench.log; tail -n 5 gpurun_out/bench.err
+if [ "$1" == "ncu" ]; then
+  timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/plain.log 2>&1 &&
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
+      python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_launches.log 2>&1
+  echo "ncu launches rc=$?"
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_tc_kernel -s 12 -c 3 -o gpurun_out/prof_gemm -f \
+      python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_gemm.log 2>&1
+  echo "ncu gemm rc=$?"
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:flash_ -s 4 -c 4 -o gpurun_out/prof_flash -f \
+      python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_flash.log 2>&1
+  echo "ncu flash rc=$?"
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:"norm_|rope_" -s 8 -c 6 -o gpurun_out/prof_norm -f \
+      python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_norm.log 2>&1
+  echo "ncu norm rc=$?"
+  ls -la gpurun_out/
+fi
