@@ -126,6 +126,27 @@ static int pick_attn_bwd_impl(int impl, int dtype, int hd) {
   return impl;
 }
 
+// GEMM dispatch shared by spb_gemm and the block: with `rope` the rotary runs in the tcgen05 epilogue (fp32 accumulators,
+// no extra HBM pass) or, on the FFMA path, as the separate in-place kernel right after the GEMM - same arithmetic.
+static int gemm_any(int in_dtype, int out_dtype, int impl, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA,
+                    const void* Bm, int64_t ldb, int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st,
+                    const float* rope, int rope_cols, int rope_T, int rope_hd) {
+  const int use = pick_gemm_impl(impl, in_dtype);
+  if (use == SPB_IMPL_TCGEN05) {
+    SPB_CHECK_ARG(in_dtype == SPB_BF16, SPB_E_UNSUPPORTED, "spb_gemm: the tcgen05 GEMM takes bf16 operands (fp32 mode uses the FFMA GEMM)");
+    if (rope == nullptr || rope_hd % 32 == 0)
+      return gemm_tc(out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st, rope, rope_cols, rope_T, rope_hd);
+    // head dims that do not tile the 32-column epilogue chunk (e.g. 16): GEMM, then the in-place rotary kernel
+    int rc = gemm_tc(out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st);
+    if (rc) return rc;
+    return spb_rope_apply(out_dtype, D, ldd, M, rope_T, rope_cols / rope_hd, rope_hd, rope, 0, (spb_stream_t)st);
+  }
+  SPB_CHECK_ARG(use == SPB_IMPL_SIMT, SPB_E_INVALID, "spb_gemm: impl %d", impl);
+  int rc = gemm_simt(in_dtype, out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st);
+  if (rc || rope == nullptr) return rc;
+  return spb_rope_apply(out_dtype, D, ldd, M, rope_T, rope_cols / rope_hd, rope_hd, rope, 0, (spb_stream_t)st);
+}
+
 }  // namespace spb
 
 using namespace spb;
@@ -192,14 +213,8 @@ int spb_gemm(int in_dtype, int out_dtype, int impl, int64_t M, int64_t N, int64_
                 "spb_gemm: leading dimension smaller than the row length (lda=%lld ldb=%lld ldd=%lld)", (long long)lda, (long long)ldb,
                 (long long)ldd);
   if (M == 0 || N == 0) return 0;
-  cudaStream_t st = (cudaStream_t)stream;
-  const int use = pick_gemm_impl(impl, in_dtype);
-  if (use == SPB_IMPL_TCGEN05) {
-    SPB_CHECK_ARG(in_dtype == SPB_BF16, SPB_E_UNSUPPORTED, "spb_gemm: the tcgen05 GEMM takes bf16 operands (fp32 mode uses the FFMA GEMM)");
-    return gemm_tc(out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st);
-  }
-  SPB_CHECK_ARG(use == SPB_IMPL_SIMT, SPB_E_INVALID, "spb_gemm: impl %d", impl);
-  return gemm_simt(in_dtype, out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st);
+  return gemm_any(in_dtype, out_dtype, impl, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, (cudaStream_t)stream,
+                  nullptr, 0, 0, 0);
 }
 
 int spb_flash_fwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal, float scale,
@@ -219,10 +234,24 @@ int spb_flash_fwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t
   return attn_simt_fwd(dtype, B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
 }
 
+// `rope` != NULL: also apply the rotary VJP to dq and dk (fused into the tcgen05 kernels; separate in-place kernels otherwise)
+static int flash_bwd_any(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal, float scale,
+                         const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo,
+                         const void* d_o, int64_t lddo, const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk,
+                         void* dv, int64_t lddv, float* dq_acc, spb_stream_t stream, const float* rope);
+
 int spb_flash_bwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal, float scale,
                   const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo,
                   const void* d_o, int64_t lddo, const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk,
                   void* dv, int64_t lddv, float* dq_acc, spb_stream_t stream) {
+  return flash_bwd_any(dtype, impl, B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk,
+                       lddk, dv, lddv, dq_acc, stream, nullptr);
+}
+
+static int flash_bwd_any(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal, float scale,
+                         const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo,
+                         const void* d_o, int64_t lddo, const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk,
+                         void* dv, int64_t lddv, float* dq_acc, spb_stream_t stream, const float* rope) {
   SPB_CHECK_ARG(q && k && v && o && d_o && lse && delta && dq && dk && dv, SPB_E_INVALID, "spb_flash_bwd: null pointer");
   SPB_CHECK_ARG(B > 0 && T > 0 && Hq > 0 && Hkv > 0 && hd > 0 && Hq % Hkv == 0, SPB_E_INVALID, "spb_flash_bwd: bad shape");
   cudaStream_t st = (cudaStream_t)stream;
@@ -231,11 +260,15 @@ int spb_flash_bwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t
     SPB_CHECK_ARG(flash_bwd_tc_supported(dtype, hd), SPB_E_UNSUPPORTED, "spb_flash_bwd: tcgen05 path needs bf16 and hd in {64,128} (dtype=%d hd=%d)", dtype, hd);
     SPB_CHECK_ARG(dq_acc != nullptr, SPB_E_INVALID, "spb_flash_bwd: the tcgen05 path needs the fp32 dq_acc scratch");
     return flash_bwd_tc(B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk, dv,
-                        lddv, dq_acc, st);
+                        lddv, dq_acc, st, rope);
   }
   SPB_CHECK_ARG(use == SPB_IMPL_SIMT, SPB_E_INVALID, "spb_flash_bwd: impl %d", impl);
-  return attn_simt_bwd(dtype, B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk,
-                       dv, lddv, st);
+  int rc = attn_simt_bwd(dtype, B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk,
+                         lddk, dv, lddv, st);
+  if (rc || rope == nullptr) return rc;
+  rc = spb_rope_apply(dtype, dq, lddq, (int64_t)B * T, T, Hq, hd, rope, 1, stream);
+  if (rc) return rc;
+  return spb_rope_apply(dtype, dk, lddk, (int64_t)B * T, T, Hkv, hd, rope, 1, stream);
 }
 
 // ------------------------------------------------------------------------------------------------ block
@@ -311,22 +344,21 @@ int spb_block_fwd(const spb_block_desc* d, const spb_block_params* p, const void
   else packed = packed && wk == wq + Nq * p->ldw_q * e && wv == wk + Nkv * p->ldw_q * e;
   if (d->qkv_bias) packed = packed && (const char*)p->bk == (const char*)p->bq + Nq * e && (const char*)p->bv == (const char*)p->bk + Nkv * e;
   const int tB = in_out ? 0 : 1;
+  // 3. rotary on the q|k column range: fused into the projection (tcgen05 epilogue / kernel right after the FFMA GEMM)
+  const float* rope = d->rope_kind == SPB_ROPE_TABLE ? p->rope : nullptr;
   if (packed) {
-    rc = spb_gemm(dt, dt, gimpl, N, Ntot, d->C, xin, d->C, 0, wq, p->ldw_q, tB, qkv, Ntot, d->qkv_bias ? p->bq : nullptr, 0, stream);
+    rc = gemm_any(dt, dt, gimpl, N, Ntot, d->C, xin, d->C, 0, wq, p->ldw_q, tB, qkv, Ntot, d->qkv_bias ? p->bq : nullptr, 0, pst, rope,
+                  (int)(Nq + Nkv), d->T, d->hd);
     if (rc) return rc;
   } else {
-    rc = spb_gemm(dt, dt, gimpl, N, Nq, d->C, xin, d->C, 0, wq, p->ldw_q, tB, qkv, Ntot, d->qkv_bias ? p->bq : nullptr, 0, stream);
+    rc = gemm_any(dt, dt, gimpl, N, Nq, d->C, xin, d->C, 0, wq, p->ldw_q, tB, qkv, Ntot, d->qkv_bias ? p->bq : nullptr, 0, pst, rope,
+                  (int)Nq, d->T, d->hd);
     if (rc) return rc;
-    rc = spb_gemm(dt, dt, gimpl, N, Nkv, d->C, xin, d->C, 0, wk, p->ldw_k, tB, qkv + Nq * e, Ntot, d->qkv_bias ? p->bk : nullptr, 0, stream);
+    rc = gemm_any(dt, dt, gimpl, N, Nkv, d->C, xin, d->C, 0, wk, p->ldw_k, tB, qkv + Nq * e, Ntot, d->qkv_bias ? p->bk : nullptr, 0, pst,
+                  rope, (int)Nkv, d->T, d->hd);
     if (rc) return rc;
     rc = spb_gemm(dt, dt, gimpl, N, Nkv, d->C, xin, d->C, 0, wv, p->ldw_v, tB, qkv + (Nq + Nkv) * e, Ntot, d->qkv_bias ? p->bv : nullptr, 0,
                   stream);
-    if (rc) return rc;
-  }
-  // 3. rotary on the q|k column range
-  prof_mark("rope_fwd", pst);
-  if (d->rope_kind == SPB_ROPE_TABLE) {
-    rc = spb_rope_apply(dt, qkv, Ntot, N, d->T, d->Hq + d->Hkv, d->hd, p->rope, 0, stream);
     if (rc) return rc;
   }
   // 4. attention
@@ -398,16 +430,12 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
   }
   // 3. attention backward -> dq|dk|dv (post-rotary gradients)
   prof_mark("flash_bwd", st);
-  rc = spb_flash_bwd(dt, d->attn_impl, d->B, d->T, d->Hq, d->Hkv, d->hd, d->causal, d->scale, qkv, Ntot, qkv + Nq * e, Ntot,
+  // 4. rotary VJP on dq, dk: fused into the attention backward (dK epilogue + dQ fp32->bf16 conversion)
+  rc = flash_bwd_any(dt, d->attn_impl, d->B, d->T, d->Hq, d->Hkv, d->hd, d->causal, d->scale, qkv, Ntot, qkv + Nq * e, Ntot,
                      qkv + (Nq + Nkv) * e, Ntot, w8 + L.attn_o, Nq, w8 + L.dattn_o, Nq, (const float*)(w8 + L.lse),
-                     (float*)(w8 + L.delta), dqkv, Ntot, dqkv + Nq * e, Ntot, dqkv + (Nq + Nkv) * e, Ntot, (float*)(w8 + L.dq_acc), stream);
+                     (float*)(w8 + L.delta), dqkv, Ntot, dqkv + Nq * e, Ntot, dqkv + (Nq + Nkv) * e, Ntot, (float*)(w8 + L.dq_acc), stream,
+                     d->rope_kind == SPB_ROPE_TABLE ? p->rope : nullptr);
   if (rc) return rc;
-  // 4. rotary VJP
-  prof_mark("rope_bwd", st);
-  if (d->rope_kind == SPB_ROPE_TABLE) {
-    rc = spb_rope_apply(dt, dqkv, Ntot, N, d->T, d->Hq + d->Hkv, d->hd, p->rope, 1, stream);
-    if (rc) return rc;
-  }
   // 5. qkv bias gradients
   prof_mark("bias_grad", st);
   if (g->dbq) { rc = spb_colsum(dt, dqkv, Ntot, N, (int32_t)Nq, g->dbq, partial, stream); if (rc) return rc; }

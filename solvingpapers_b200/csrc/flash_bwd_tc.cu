@@ -13,16 +13,21 @@
 //   (5) dQ^T = K^T  dS         M=128(hd) N=64(q)  K=128(kv) A=K (MN-major view of the resident K tile)
 //                                                           B=dS^T buffer read MN-major
 // dV and dK accumulate in TMEM over ALL iterations (the GQA group sum of repeat_kv's VJP happens there); dQ^T is drained
-// every iteration: thread d adds column d of 64 query rows into the fp32 dq accumulator - 32 lanes hit 32 consecutive
-// floats, one coalesced 128-byte reduction per warp instruction.  TMEM: S^T 64 + dP^T 64 + dV hd + dK hd + dQ^T 64 <= 448.
-// Warps: 0 = TMA producer (K,V once; Q_i,dO_i double buffered), 1 = MMA issuer, 2-5 = element-wise / drain / epilogue.
+// every iteration: thread d owns column d of 64 query rows, the tile is transposed through shared memory and added to the
+// fp32 dq accumulator with one TMA bulk reduce-add (cp.reduce.async.bulk.tensor).  TMEM: S^T 64 + dP^T 64 + dV hd + dK hd +
+// dQ^T 64 <= 448 columns.
+// Warps: 0 = TMA producer (K,V once; Q_i,dO_i double buffered), 1 = MMA issuer, 2-5 and 6-9 = two element-wise groups (each
+// owns 32 of the 64 query columns of every KV row: P^T, dS^T into double-buffered smem; at the end one stores dV, the
+// other dK), 10-13 = dQ-drain group - the three phases of an iteration overlap: the tensor pipe runs S(it+1) and G(it)
+// back to back while the element-wise groups work on it+1 and the drain group reduces it.
+// CTAs are ordered heaviest first (causal: KV tile 0 sees every Q tile), blockIdx.z = KV tile.
 // Scratch: delta[B,Hq,T] (rowsum(dO*O), prep kernel) and dq_acc[N,Hq*hd] fp32 (zeroed per call, converted at the end).
 #include "common.cuh"
 #include "kernels.h"
 
 namespace spb {
 
-constexpr int FB_THREADS = 192;
+constexpr int FB_THREADS = 448;  // warp 0 TMA, warp 1 MMA, warps 2-9 two element-wise groups, warps 10-13 dQ-drain group
 constexpr float FB_LOG2E = 1.4426950408889634f;
 
 __device__ __forceinline__ float fb_exp2(float x) {
@@ -43,8 +48,10 @@ struct FaBwdCfg {
   static constexpr int OFF_Q = OFF_V + V_BYTES;    // 2 stages
   static constexpr int OFF_DO = OFF_Q + 2 * Q_BYTES;
   static constexpr int OFF_PT = OFF_DO + 2 * Q_BYTES;
-  static constexpr int OFF_DST = OFF_PT + PT_BYTES;
-  static constexpr int OFF_LSE = OFF_DST + PT_BYTES;  // [2][64] lse*log2e, then [2][64] delta
+  static constexpr int OFF_DST = OFF_PT + 2 * PT_BYTES;   // P^T and dS^T are double buffered
+  static constexpr int OFF_DQS = OFF_DST + 2 * PT_BYTES;  // fp32 [64 q rows][HD] staging tile for the TMA reduce-add of dQ
+  static constexpr int DQS_BYTES = 64 * HD * 4;
+  static constexpr int OFF_LSE = OFF_DQS + DQS_BYTES;     // [2][64] lse*log2e, then [2][64] delta
   static constexpr int OFF_BAR = OFF_LSE + 4 * 64 * 4;
   static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
   static constexpr int TM_ST = 0, TM_DPT = 64, TM_DV = 128, TM_DK = 256, TM_DQT = 384;
@@ -63,12 +70,14 @@ struct FaBwdArgs {
   int64_t lddv;
   int T, Hq, Hkv, causal;
   float scale, scale_log2;
+  const float4* rope;  // optional: apply the rotary VJP (M^T) to dK rows in the epilogue (dQ gets it in the convert kernel)
 };
 
 template <int HD>
 __global__ void __launch_bounds__(FB_THREADS, 1)
     flash_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
-                        const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmDO, const FaBwdArgs p) {
+                        const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmDO,
+                        const __grid_constant__ CUtensorMap tmDQ, const FaBwdArgs p) {
   using Cfg = FaBwdCfg<HD>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -78,6 +87,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
   uint8_t* sDO = smem + Cfg::OFF_DO;
   uint8_t* sPT = smem + Cfg::OFF_PT;
   uint8_t* sDST = smem + Cfg::OFF_DST;
+  float* sDQ = reinterpret_cast<float*>(smem + Cfg::OFF_DQS);
   float* sLse = reinterpret_cast<float*>(smem + Cfg::OFF_LSE);  // [2][64]
   float* sDelta = sLse + 128;                                    // [2][64]
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
@@ -86,16 +96,16 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
   uint64_t* qdo_empty = bars + 3;   // [2]
   uint64_t* sdp_full = bars + 5;
   uint64_t* sdp_empty = bars + 6;
-  uint64_t* pds_full = bars + 7;
-  uint64_t* pds_empty = bars + 8;
-  uint64_t* dq_full = bars + 9;
-  uint64_t* dq_empty = bars + 10;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+  uint64_t* pds_full = bars + 7;    // [2]
+  uint64_t* pds_empty = bars + 9;   // [2]
+  uint64_t* dq_full = bars + 11;
+  uint64_t* dq_empty = bars + 12;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
-  const int nt = blockIdx.x, g = blockIdx.y, b = blockIdx.z;
+  const int nt = blockIdx.z, g = blockIdx.x, b = blockIdx.y;  // z is the slowest-varying index: heavy KV tiles are scheduled first
   const int kv0 = nt * 128;
   const int n_rep = p.Hq / p.Hkv;
   const int n_q64 = (p.T + 63) / 64;
@@ -108,6 +118,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
     prefetch_tmap(&tmV);
     prefetch_tmap(&tmQ);
     prefetch_tmap(&tmDO);
+    prefetch_tmap(&tmDQ);
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -117,9 +128,11 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         mbar_init(&qdo_empty[i], 1);
       }
       mbar_init(sdp_full, 1);
-      mbar_init(sdp_empty, 4);
-      mbar_init(pds_full, 4);
-      mbar_init(pds_empty, 1);
+      mbar_init(sdp_empty, 8);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&pds_full[i], 8);
+        mbar_init(&pds_empty[i], 1);
+      }
       mbar_init(dq_full, 1);
       mbar_init(dq_empty, Cfg::DQ_WARPS);
       fence_barrier_init();
@@ -131,7 +144,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
   if (HD == 64 && warp >= 2) {
     // zero the second 64-column chunk of the K buffer: rows 64..127 of the M=128 view of K^T
     uint4* z = reinterpret_cast<uint4*>(sK + 16384);
-    for (int i = threadIdx.x - 64; i < 16384 / 16; i += 128) z[i] = make_uint4(0, 0, 0, 0);
+    for (int i = threadIdx.x - 64; i < 16384 / 16; i += FB_THREADS - 64) z[i] = make_uint4(0, 0, 0, 0);
     fence_proxy_async_smem();
   }
   tc_fence_before();
@@ -170,7 +183,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       const uint32_t idesc_s = umma_idesc_bf16(128, 64, 0, 0);
       const uint32_t idesc_g = umma_idesc_bf16(128, HD, 0, 1);
       const uint32_t idesc_q = umma_idesc_bf16(128, 64, 1, 1);
-      const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV), pt_addr = smem_u32(sPT), dst_addr = smem_u32(sDST);
+      const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV);
       mbar_wait(kv_full, 0);
       auto issue_s = [&](int it) {
         const int st = it & 1;
@@ -192,10 +205,11 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       };
       auto issue_g = [&](int it) {
         const int st = it & 1;
-        mbar_wait(pds_full, it & 1);
+        mbar_wait(&pds_full[st], (it >> 1) & 1);
         mbar_wait(dq_empty, (it & 1) ^ 1);
         tc_fence_after();
         const uint32_t q_addr = smem_u32(sQ + st * Cfg::Q_BYTES), do_addr = smem_u32(sDO + st * Cfg::Q_BYTES);
+        const uint32_t pt_addr = smem_u32(sPT + st * Cfg::PT_BYTES), dst_addr = smem_u32(sDST + st * Cfg::PT_BYTES);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dV += P^T dO
           umma_bf16(tmem_base + Cfg::TM_DV, umma_desc_kmajor(pt_addr + kk * 32), umma_desc_mnmajor(do_addr + kk * 2048, 64), idesc_g,
@@ -209,7 +223,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
           umma_bf16(tmem_base + Cfg::TM_DQT, umma_desc_mnmajor(k_addr + kk * 2048, 128), umma_desc_mnmajor(dst_addr + kk * 2048, 128),
                     idesc_q, kk > 0 ? 1u : 0u);
         umma_commit(&qdo_empty[st]);
-        umma_commit(pds_empty);
+        umma_commit(&pds_empty[st]);
         umma_commit(dq_full);
       };
       issue_s(0);
@@ -219,85 +233,128 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       }
     }
     __syncwarp();
-  } else {
-    // ------------------------------------------------------------------ element-wise, dQ drain, epilogue (warps 2..5)
+  } else if (warp < 10) {
+    // ------------------------------------------------------------------ element-wise groups (warps 2..5: q columns 0..31, 6..9: 32..63)
+    const int wg = (warp - 2) >> 2;
     const int qd = warp & 3;
-    const int r = qd * 32 + lane;  // kv row in phase A, hd column in the dQ phase; both = TMEM lane
-    const int ct = threadIdx.x - 64;  // 0..127
+    const int r = qd * 32 + lane;     // kv row = TMEM lane
+    const int ct = threadIdx.x - 64;  // 0..255
     const int kv_idx = kv0 + r;
+    const int cbase = wg * 32;        // first of this group's 32 query columns
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
+    // lse*log2e / delta of the 64 query rows of an iteration are staged in shared memory (double buffered).  The global
+    // loads for iteration it+1 are issued at the top of iteration it and land while it computes (their latency used to
+    // sit on the critical path of every iteration).
+    auto fetch_stat = [&](int it) -> float {
+      if (ct >= 128 || it >= n_it) return 0.f;
+      const int h = g * n_rep + it / n_i;
+      const int qi = (i_start + it % n_i) * 64 + (ct & 63);
+      if (qi >= p.T) return 0.f;
+      const float v = ((ct < 64) ? p.lse : p.delta)[((int64_t)b * p.Hq + h) * p.T + qi];
+      return (ct < 64) ? v * FB_LOG2E : v;
+    };
+    auto put_stat = [&](int it, float v) {
+      if (ct < 64) sLse[(it & 1) * 64 + ct] = v;
+      else if (ct < 128) sDelta[(it & 1) * 64 + (ct - 64)] = v;
+    };
+    put_stat(0, fetch_stat(0));
+    const float2 sc2 = make_float2(p.scale_log2, p.scale_log2);
+    const float2 scale2 = make_float2(p.scale, p.scale);
     for (int it = 0; it < n_it; ++it) {
       const int st = it & 1;
-      const int h = g * n_rep + it / n_i;
       const int q0 = (i_start + it % n_i) * 64;
-      // stage lse*log2e and delta of the 64 query rows (double buffered; one named barrier per iteration)
-      {
-        const int c = ct & 63;
-        const int qi = q0 + c;
-        const float* src = (ct < 64) ? p.lse : p.delta;
-        float val = 0.f;
-        if (qi < p.T) val = src[((int64_t)b * p.Hq + h) * p.T + qi];
-        if (ct < 64) sLse[st * 64 + c] = val * FB_LOG2E;
-        else sDelta[st * 64 + c] = val;
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      const float stat_next = fetch_stat(it + 1);
+      asm volatile("bar.sync 1, 256;" ::: "memory");  // stage st is complete; stage st^1 is no longer being read
 
-      // ---- phase A: P^T and dS^T rows
       mbar_wait(sdp_full, it & 1);
       tc_fence_after();
-      float sT[64], dpT[64];
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t raw[32];
-        SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_ST + c * 32), raw);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) sT[c * 32 + i] = __uint_as_float(raw[i]);
-        SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_DPT + c * 32), raw);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) dpT[c * 32 + i] = __uint_as_float(raw[i]);
-      }
+      uint32_t rs[32], rd[32];
+      SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_ST + cbase), rs);
+      SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_DPT + cbase), rd);
+      tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(sdp_empty);
+      if (lane == 0) mbar_arrive(sdp_empty);  // S^T / dP^T may be overwritten by iteration it+1
 
       const bool need_mask = (p.causal && q0 < kv0 + 128) || (q0 + 64 > p.T) || (kv0 + 128 > p.T);
+      const float2* lse2 = reinterpret_cast<const float2*>(sLse + st * 64 + cbase);
+      const float2* del2 = reinterpret_cast<const float2*>(sDelta + st * 64 + cbase);
+      uint32_t pkp[16], pkd[16];
 #pragma unroll
-      for (int i = 0; i < 64; ++i) {
-        float pv = fb_exp2(sT[i] * p.scale_log2 - sLse[st * 64 + i]);
+      for (int i = 0; i < 32; i += 2) {
+        const float2 l2 = lse2[i >> 1], d2 = del2[i >> 1];
+        const float2 x = __ffma2_rn(make_float2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, make_float2(-l2.x, -l2.y));
+        float2 pv = make_float2(fb_exp2(x.x), fb_exp2(x.y));
         if (need_mask) {
-          const int qi = q0 + i;
-          if ((p.causal && kv_idx > qi) || qi >= p.T || kv_idx >= p.T) pv = 0.f;
+          const int qi = q0 + cbase + i;
+          const bool kv_dead = kv_idx >= p.T;
+          if (kv_dead || qi >= p.T || (p.causal && kv_idx > qi)) pv.x = 0.f;
+          if (kv_dead || qi + 1 >= p.T || (p.causal && kv_idx > qi + 1)) pv.y = 0.f;
         }
-        sT[i] = pv;
-        dpT[i] = pv * (dpT[i] - sDelta[st * 64 + i]) * p.scale;
+        const float2 dd = __fadd2_rn(make_float2(__uint_as_float(rd[i]), __uint_as_float(rd[i + 1])), make_float2(-d2.x, -d2.y));
+        const float2 ds = __fmul2_rn(__fmul2_rn(pv, dd), scale2);
+        pkp[i >> 1] = pack_bf16(pv.x, pv.y);
+        pkd[i >> 1] = pack_bf16(ds.x, ds.y);
       }
-      mbar_wait(pds_empty, (it & 1) ^ 1);  // MMAs (3)(4)(5) of the previous iteration have finished reading P^T / dS^T
-      uint8_t* prow = sPT + r * 128;
-      uint8_t* drow = sDST + r * 128;
+      put_stat(it + 1, stat_next);  // visible to everyone after the next iteration's bar.sync
+      mbar_wait(&pds_empty[st], ((it >> 1) & 1) ^ 1);  // MMAs of iteration it-2 have finished reading this P^T / dS^T stage
+      uint8_t* prow = sPT + st * Cfg::PT_BYTES + r * 128;
+      uint8_t* drow = sDST + st * Cfg::PT_BYTES + r * 128;
 #pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        uint4 v;
-        v.x = pack_bf16(sT[c * 8 + 0], sT[c * 8 + 1]);
-        v.y = pack_bf16(sT[c * 8 + 2], sT[c * 8 + 3]);
-        v.z = pack_bf16(sT[c * 8 + 4], sT[c * 8 + 5]);
-        v.w = pack_bf16(sT[c * 8 + 6], sT[c * 8 + 7]);
-        *reinterpret_cast<uint4*>(prow + ((c ^ (r & 7)) << 4)) = v;
-        uint4 w;
-        w.x = pack_bf16(dpT[c * 8 + 0], dpT[c * 8 + 1]);
-        w.y = pack_bf16(dpT[c * 8 + 2], dpT[c * 8 + 3]);
-        w.z = pack_bf16(dpT[c * 8 + 4], dpT[c * 8 + 5]);
-        w.w = pack_bf16(dpT[c * 8 + 6], dpT[c * 8 + 7]);
-        *reinterpret_cast<uint4*>(drow + ((c ^ (r & 7)) << 4)) = w;
+      for (int c = 0; c < 4; ++c) {
+        const int slot = ((wg * 4 + c) ^ (r & 7)) << 4;
+        *reinterpret_cast<uint4*>(prow + slot) = make_uint4(pkp[c * 4], pkp[c * 4 + 1], pkp[c * 4 + 2], pkp[c * 4 + 3]);
+        *reinterpret_cast<uint4*>(drow + slot) = make_uint4(pkd[c * 4], pkd[c * 4 + 1], pkd[c * 4 + 2], pkd[c * 4 + 3]);
       }
       fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(pds_full);
-
-      // ---- dQ phase: thread r owns hd column r of dQ^T; 64 query rows per iteration
-      if (qd < Cfg::DQ_WARPS) {  // warp-uniform (hd=64: only two warps hold real rows)
+      if (lane == 0) mbar_arrive(&pds_full[st]);
+    }
+    // ---- epilogue: group 0 stores dV, group 1 stores dK (rows -> bf16 -> global).  The last pds_empty commit covers
+    // every MMA issued before it.
+    mbar_wait(&pds_empty[(n_it - 1) & 1], ((n_it - 1) >> 1) & 1);
+    tc_fence_after();
+    const bool valid = kv_idx < p.T;
+    const int which = wg;  // 0: dV, 1: dK
+    __nv_bfloat16* orow = (which ? p.dk + ((int64_t)b * p.T + kv_idx) * p.lddk : p.dv + ((int64_t)b * p.T + kv_idx) * p.lddv) + (int64_t)g * HD;
+    const int tm = which ? Cfg::TM_DK : Cfg::TM_DV;
+#pragma unroll
+    for (int c = 0; c < HD / 32; ++c) {
+      uint32_t o[32];
+      SPB_TMEM_LD_32(lane_base + (uint32_t)(tm + c * 32), o);
+      tmem_ld_wait();
+      if (valid) {
+        if (which == 1 && p.rope != nullptr) {  // dK: transpose of the 2x2 rotary block, table row = position kv_idx
+          const float4* tab = p.rope + (int64_t)kv_idx * (HD / 2) + c * 16;
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            const float4 m = tab[i >> 1];
+            const float xe = __uint_as_float(o[i]), xo = __uint_as_float(o[i + 1]);
+            o[i] = __float_as_uint(m.x * xe + m.z * xo);
+            o[i + 1] = __float_as_uint(m.y * xe + m.w * xo);
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 32; i += 8) {
+          uint4 v;
+          v.x = pack_bf16(__uint_as_float(o[i]), __uint_as_float(o[i + 1]));
+          v.y = pack_bf16(__uint_as_float(o[i + 2]), __uint_as_float(o[i + 3]));
+          v.z = pack_bf16(__uint_as_float(o[i + 4]), __uint_as_float(o[i + 5]));
+          v.w = pack_bf16(__uint_as_float(o[i + 6]), __uint_as_float(o[i + 7]));
+          *reinterpret_cast<uint4*>(orow + c * 32 + i) = v;
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ drain group (warps 10..13): reduce dQ^T every iteration
+    const int qd = warp & 3;
+    const int r = qd * 32 + lane;  // hd column of dQ = TMEM lane of dQ^T
+    const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
+    if (qd < Cfg::DQ_WARPS) {  // warp-uniform (hd=64: only two warps hold real rows)
+      for (int it = 0; it < n_it; ++it) {
+        const int h = g * n_rep + it / n_i;
+        const int q0 = (i_start + it % n_i) * 64;
         mbar_wait(dq_full, it & 1);
         tc_fence_after();
         float dq[64];
@@ -311,42 +368,24 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(dq_empty);
-        float* acc = p.dq_acc + ((int64_t)b * p.T + q0) * p.ld_acc + (int64_t)h * HD + r;
-#pragma unroll 8
-        for (int i = 0; i < 64; ++i)
-          if (q0 + i < p.T) atomicAdd(acc + (int64_t)i * p.ld_acc, dq[i]);
-      }
-    }
-    // ---- epilogue: dV, dK rows -> bf16 -> global.  The last dq_full commit covers every MMA issued before it.
-    if (qd >= Cfg::DQ_WARPS) {  // warps that skipped the dQ phase still need the completion guarantee
-      mbar_wait(dq_full, (n_it - 1) & 1);
-    }
-    tc_fence_after();
-    const bool valid = kv_idx < p.T;
-    __nv_bfloat16* dvrow = p.dv + ((int64_t)b * p.T + kv_idx) * p.lddv + (int64_t)g * HD;
-    __nv_bfloat16* dkrow = p.dk + ((int64_t)b * p.T + kv_idx) * p.lddk + (int64_t)g * HD;
+        if (lane == 0) mbar_arrive(dq_empty);  // dQ^T may be overwritten by iteration it+1 while the reduction is in flight
+        // transpose through shared memory ([q][d] fp32, lanes write consecutive d: conflict-free) and let the TMA engine do
+        // ONE bulk reduce-add of the 64 x hd tile into the fp32 dq accumulator (per-thread fp32 atomics were the v2
+        // bottleneck: ~1 float atomic / clk / SM).  Rows past the sequence end hold exact zeros (their P^T is masked).
+        constexpr int NB = Cfg::DQ_WARPS * 32;
+        const bool leader = (qd == 0 && lane == 0);
+        if (leader && it > 0) tma_store_wait_read<0>();  // previous reduce has finished reading the staging tile
+        asm volatile("bar.sync 2, %0;" ::"n"(NB) : "memory");
 #pragma unroll
-    for (int which = 0; which < 2; ++which) {
-      __nv_bfloat16* orow = which ? dkrow : dvrow;
-      const int tm = which ? Cfg::TM_DK : Cfg::TM_DV;
-#pragma unroll
-      for (int c = 0; c < HD / 32; ++c) {
-        uint32_t o[32];
-        SPB_TMEM_LD_32(lane_base + (uint32_t)(tm + c * 32), o);
-        tmem_ld_wait();
-        if (valid) {
-#pragma unroll
-          for (int i = 0; i < 32; i += 8) {
-            uint4 v;
-            v.x = pack_bf16(__uint_as_float(o[i]), __uint_as_float(o[i + 1]));
-            v.y = pack_bf16(__uint_as_float(o[i + 2]), __uint_as_float(o[i + 3]));
-            v.z = pack_bf16(__uint_as_float(o[i + 4]), __uint_as_float(o[i + 5]));
-            v.w = pack_bf16(__uint_as_float(o[i + 6]), __uint_as_float(o[i + 7]));
-            *reinterpret_cast<uint4*>(orow + c * 32 + i) = v;
-          }
+        for (int i = 0; i < 64; ++i) sDQ[i * HD + r] = dq[i];
+        fence_proxy_async_smem();
+        asm volatile("bar.sync 2, %0;" ::"n"(NB) : "memory");
+        if (leader) {
+          tma_reduce_add_2d(&tmDQ, sDQ, h * HD, b * p.T + q0);
+          tma_store_commit();
         }
       }
+      if (qd == 0 && lane == 0) tma_store_wait_read<0>();
     }
   }
 
@@ -384,14 +423,23 @@ __global__ void __launch_bounds__(256) flash_bwd_prep_kernel(const __nv_bfloat16
 // dq[n, c] = bf16(dq_acc[n, c]); 8 elements per thread
 __global__ void __launch_bounds__(256) flash_bwd_dq_convert_kernel(const float* __restrict__ acc, int64_t ld_acc,
                                                                    __nv_bfloat16* __restrict__ dq, int64_t lddq, int64_t N,
-                                                                   int cols) {
+                                                                   int cols, const float4* __restrict__ rope, int T, int hd) {
   const int vec_per_row = cols / 8;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= N * vec_per_row) return;
   const int64_t n = idx / vec_per_row;
   const int c = (int)(idx % vec_per_row) * 8;
-  const float4 a = *reinterpret_cast<const float4*>(acc + n * ld_acc + c);
-  const float4 b = *reinterpret_cast<const float4*>(acc + n * ld_acc + c + 4);
+  float4 a = *reinterpret_cast<const float4*>(acc + n * ld_acc + c);
+  float4 b = *reinterpret_cast<const float4*>(acc + n * ld_acc + c + 4);
+  if (rope != nullptr) {  // rotary VJP fused into the fp32 -> bf16 conversion
+    const float4* tab = rope + (int64_t)(n % T) * (hd >> 1) + ((c % hd) >> 1);
+    const float4 m0 = tab[0], m1 = tab[1], m2 = tab[2], m3 = tab[3];
+    float xe, xo;
+    xe = a.x; xo = a.y; a.x = m0.x * xe + m0.z * xo; a.y = m0.y * xe + m0.w * xo;
+    xe = a.z; xo = a.w; a.z = m1.x * xe + m1.z * xo; a.w = m1.y * xe + m1.w * xo;
+    xe = b.x; xo = b.y; b.x = m2.x * xe + m2.z * xo; b.y = m2.y * xe + m2.w * xo;
+    xe = b.z; xo = b.w; b.z = m3.x * xe + m3.z * xo; b.w = m3.y * xe + m3.w * xo;
+  }
   uint4 v;
   v.x = pack_bf16(a.x, a.y);
   v.y = pack_bf16(a.z, a.w);
@@ -406,7 +454,7 @@ template <int HD>
 static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float scale, const void* q, int64_t ldq, const void* k,
                                int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o, int64_t lddo,
                                const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
-                               float* dq_acc, cudaStream_t st) {
+                               float* dq_acc, cudaStream_t st, const float* rope) {
   using Cfg = FaBwdCfg<HD>;
   const int64_t N = (int64_t)B * Tn;
   const int64_t ld_acc = (int64_t)Hq * HD;
@@ -424,6 +472,8 @@ static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
   if ((rc = make_tmap_2d(&tmV, v, 2, (uint64_t)N, (uint64_t)Hkv * HD, (uint64_t)ldv, 128, 64, true, false))) return rc;
   if ((rc = make_tmap_2d(&tmQ, q, 2, (uint64_t)N, (uint64_t)Hq * HD, (uint64_t)ldq, 64, 64, true, false))) return rc;
   if ((rc = make_tmap_2d(&tmDO, d_o, 2, (uint64_t)N, (uint64_t)Hq * HD, (uint64_t)lddo, 64, 64, true, false))) return rc;
+  CUtensorMap tmDQ;
+  if ((rc = make_tmap_2d(&tmDQ, dq_acc, 4, (uint64_t)N, (uint64_t)Hq * HD, (uint64_t)ld_acc, 64, HD, false, true))) return rc;
   FaBwdArgs a;
   a.lse = lse;
   a.delta = delta;
@@ -439,14 +489,15 @@ static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
   a.causal = causal;
   a.scale = scale;
   a.scale_log2 = scale * FB_LOG2E;
+  a.rope = (const float4*)rope;
   SPB_CUDA(cudaFuncSetAttribute(flash_bwd_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-  dim3 grid((Tn + 127) / 128, Hkv, B);
-  flash_bwd_tc_kernel<HD><<<grid, FB_THREADS, Cfg::SMEM_BYTES, st>>>(tmK, tmV, tmQ, tmDO, a);
+  dim3 grid(Hkv, B, (Tn + 127) / 128);
+  flash_bwd_tc_kernel<HD><<<grid, FB_THREADS, Cfg::SMEM_BYTES, st>>>(tmK, tmV, tmQ, tmDO, tmDQ, a);
   SPB_LAUNCH_CHECK();
   {
     const int cols = Hq * HD;
     const int64_t total = N * (cols / 8);
-    flash_bwd_dq_convert_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(dq_acc, ld_acc, (__nv_bfloat16*)dq, lddq, N, cols);
+    flash_bwd_dq_convert_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(dq_acc, ld_acc, (__nv_bfloat16*)dq, lddq, N, cols, (const float4*)rope, Tn, HD);
     SPB_LAUNCH_CHECK();
   }
   return 0;
@@ -455,7 +506,7 @@ static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
 int flash_bwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k,
                  int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o, int64_t lddo,
                  const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
-                 float* dq_acc, cudaStream_t st) {
+                 float* dq_acc, cudaStream_t st, const float* rope) {
   const void* ptrs[8] = {q, k, v, o, d_o, dq, dk, dv};
   const int64_t lds[8] = {ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv};
   for (int i = 0; i < 8; ++i)
@@ -464,10 +515,10 @@ int flash_bwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale
   SPB_CHECK_ARG((uintptr_t)dq_acc % 16 == 0, SPB_E_INVALID, "flash backward (tcgen05): dq_acc must be 16-byte aligned");
   if (hd == 128)
     return flash_bwd_tc_launch<128>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk,
-                                    dv, lddv, dq_acc, st);
+                                    dv, lddv, dq_acc, st, rope);
   if (hd == 64)
     return flash_bwd_tc_launch<64>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk, dv,
-                                   lddv, dq_acc, st);
+                                   lddv, dq_acc, st, rope);
   SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "flash backward (tcgen05): hd %d", hd);
 }
 

@@ -1,24 +1,25 @@
-// flash_tc.cu - K3/K4: flash-style causal GQA attention on tcgen05 (bf16, hd in {64,128}); replaces the materialised
+// flash_tc.cu - K3: flash-style causal GQA attention forward on tcgen05 (bf16, hd in {64,128}); replaces the materialised
 // scores of llama3:820-828 (and gpt:344-353, ViT's nn.MultiheadAttention).  Scores never leave the SM.
 //
-// Forward (one CTA = 128 query rows of one (batch, q head)):
-//   warp 0   TMA producer: Q tile once, then K / V tiles of 128 rows, double buffered (mbarrier full/empty rings)
-//   warp 1   MMA issuer (one thread): S = Q K^T (M128 N128 K=hd) into one of two TMEM S buffers, O += P V (M128 N=hd
-//            K128) into the TMEM O accumulator; QK^T of tile j+1 is issued BEFORE PV of tile j so the tensor pipe works
-//            while the softmax warps are busy with tile j
-//   warps 2-5 softmax: thread = one query row (TMEM lane): tcgen05.ld the S row, online softmax in registers (exp2 with
-//            the 1/sqrt(hd)*log2(e) factor folded in), lazy rescaling of O (only when the running max grows by > 2^8,
-//            decided per warp), P written as bf16 into shared memory in the 128B-swizzled K-major UMMA layout
-//   causal tile skipping: KV tiles above the diagonal are never loaded; the diagonal tile and the ragged last tile are
-//   masked by index (-1e9 additive / -1e4 replacing / -inf masks of the notebooks all give exp()==0 exactly).
+// One CTA = 256 query rows (two 128-row tiles) of one (batch, q head); the two tiles ping-pong on the tensor pipe:
+//   warp 0    TMA producer: the two Q tiles once, then K / V tiles of 128 rows (K double buffered, V single)
+//   warp 1    MMA issuer (one thread): per KV tile  S0 = Q0 K^T, S1 = Q1 K^T  (M128 N128 K=hd, each into its own TMEM S
+//             buffer), then  O0 += P0 V, O1 += P1 V  (M128 N=hd K128, TMEM accumulators): while one tile is in its
+//             softmax the tensor pipe works on the other
+//   warps 2-5 softmax of tile 0, warps 6-9 softmax of tile 1: thread = one query row (TMEM lane).  Two passes over the S
+//             row in TMEM (tcgen05.ld): pass 1 row max, pass 2 exp2 / sum / bf16 P into shared memory in the 128B-swizzled
+//             K-major UMMA layout; 1/sqrt(hd)*log2(e) folded into one FFMA; lazy rescaling of O (only when the running
+//             max grows by more than 2^8, decided per warp)
+//   causal tile skipping: KV tiles above a tile's diagonal are neither loaded nor multiplied; diagonal and ragged last
+//   tiles are masked by index (-1e9 additive / -1e4 replacing / -inf masks of the notebooks all give exp()==0 exactly).
 //   GQA: kv head = q head / (Hq/Hkv) is just the TMA column coordinate (llama3:626-627 repeat_kv never materialised).
-// Algorithmic FLOPs: 4*B*Hq*T^2*hd*m forward (m = (T+1)/2T causal).
+// TMEM: S0 [0,128) S1 [128,256) O0 [256,256+hd) O1 [384,384+hd).  Algorithmic FLOPs: 4*B*Hq*T^2*hd*m (m=(T+1)/2T causal).
 #include "common.cuh"
 #include "kernels.h"
 
 namespace spb {
 
-constexpr int FA_THREADS = 192;
+constexpr int FA_THREADS = 320;
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 
@@ -34,13 +35,13 @@ struct FaFwdCfg {
   static constexpr int TILE_BYTES = 128 * HD * 2;   // 128 rows x HD bf16
   static constexpr int CHUNK_BYTES = 128 * 128;     // 128 rows x 128 B
   static constexpr int P_BYTES = 128 * 128 * 2;
-  static constexpr int OFF_Q = 0;
-  static constexpr int OFF_K = OFF_Q + TILE_BYTES;
-  static constexpr int OFF_V = OFF_K + 2 * TILE_BYTES;
-  static constexpr int OFF_P = OFF_V + 2 * TILE_BYTES;
+  static constexpr int OFF_Q = 0;                       // 2 tiles
+  static constexpr int OFF_K = OFF_Q + 2 * TILE_BYTES;  // 2 stages
+  static constexpr int OFF_V = OFF_K + 2 * TILE_BYTES;  // 1 stage
+  static constexpr int OFF_P = OFF_V + TILE_BYTES;      // 2 tiles
   static constexpr int OFF_BAR = OFF_P + 2 * P_BYTES;
   static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
-  static constexpr int TMEM_COLS = 512;  // S0 [0,128) S1 [128,256) O [256, 256+HD)
+  static constexpr int TMEM_COLS = 512;
 };
 
 struct FaFwdArgs {
@@ -64,26 +65,33 @@ __global__ void __launch_bounds__(FA_THREADS, 1)
   uint8_t* sP = smem + Cfg::OFF_P;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
   uint64_t* q_full = bars;            // [1]
-  uint64_t* k_full = bars + 1;        // [2]
+  uint64_t* k_full = bars + 1;        // [2] stages
   uint64_t* k_empty = bars + 3;       // [2]
-  uint64_t* v_full = bars + 5;        // [2]
-  uint64_t* v_empty = bars + 7;       // [2]
-  uint64_t* s_full = bars + 9;        // [2]
-  uint64_t* s_empty = bars + 11;      // [2]
-  uint64_t* p_full = bars + 13;       // [2]
-  uint64_t* pv_done = bars + 15;      // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
+  uint64_t* v_full = bars + 5;        // [1]
+  uint64_t* v_empty = bars + 6;       // [1]
+  uint64_t* s_full = bars + 7;        // [2] per q tile
+  uint64_t* s_empty = bars + 9;       // [2]
+  uint64_t* p_full = bars + 11;       // [2]
+  uint64_t* pv_done = bars + 13;      // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
-  const int n_qt = (int)gridDim.x;
-  const int qt = p.causal ? (n_qt - 1 - (int)blockIdx.x) : (int)blockIdx.x;  // heavy (late) causal tiles first
+  const int n_qp = (int)gridDim.x;
+  const int qp = p.causal ? (n_qp - 1 - (int)blockIdx.x) : (int)blockIdx.x;  // heavy (late) causal tiles first
   const int h = blockIdx.y, b = blockIdx.z;
   const int kvh = h / (p.Hq / p.Hkv);
-  const int q0 = qt * 128;
+  const int q0 = qp * 256;
   const int n_kv_all = (p.T + 127) / 128;
-  const int n_kv = p.causal ? min(n_kv_all, qt + 1) : n_kv_all;
+  // per q tile: number of KV tiles it attends to (0 = the tile lies entirely past the end of the sequence)
+  int n_kv_t[2];
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    const bool live = q0 + t * 128 < p.T;
+    n_kv_t[t] = !live ? 0 : (p.causal ? min(n_kv_all, 2 * qp + t + 1) : n_kv_all);
+  }
+  const int n_kv = max(n_kv_t[0], n_kv_t[1]);
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmQ);
@@ -93,11 +101,11 @@ __global__ void __launch_bounds__(FA_THREADS, 1)
   if (warp == 1) {
     if (lane == 0) {
       mbar_init(q_full, 1);
+      mbar_init(v_full, 1);
+      mbar_init(v_empty, 1);
       for (int i = 0; i < 2; ++i) {
         mbar_init(&k_full[i], 1);
         mbar_init(&k_empty[i], 1);
-        mbar_init(&v_full[i], 1);
-        mbar_init(&v_empty[i], 1);
         mbar_init(&s_full[i], 1);
         mbar_init(&s_empty[i], 4);
         mbar_init(&p_full[i], 4);
@@ -113,29 +121,32 @@ __global__ void __launch_bounds__(FA_THREADS, 1)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_O = tmem_base + 256;
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      const int row_q = b * p.T + q0;
-      mbar_arrive_expect_tx(q_full, Cfg::TILE_BYTES);
+      const int n_live = (n_kv_t[0] > 0) + (n_kv_t[1] > 0);
+      mbar_arrive_expect_tx(q_full, n_live * Cfg::TILE_BYTES);
 #pragma unroll
-      for (int c = 0; c < Cfg::CH; ++c) tma_load_2d(sQ + c * Cfg::CHUNK_BYTES, &tmQ, q_full, h * HD + c * 64, row_q);
+      for (int t = 0; t < 2; ++t) {
+        if (n_kv_t[t] > 0) {
+#pragma unroll
+          for (int c = 0; c < Cfg::CH; ++c)
+            tma_load_2d(sQ + t * Cfg::TILE_BYTES + c * Cfg::CHUNK_BYTES, &tmQ, q_full, h * HD + c * 64, b * p.T + q0 + t * 128);
+        }
+      }
       for (int j = 0; j < n_kv; ++j) {
         const int bf = j & 1;
-        const uint32_t u = (j >> 1) & 1;
         const int row_kv = b * p.T + j * 128;
-        mbar_wait(&k_empty[bf], u ^ 1);
+        mbar_wait(&k_empty[bf], ((j >> 1) & 1) ^ 1);
         mbar_arrive_expect_tx(&k_full[bf], Cfg::TILE_BYTES);
 #pragma unroll
         for (int c = 0; c < Cfg::CH; ++c)
           tma_load_2d(sK + bf * Cfg::TILE_BYTES + c * Cfg::CHUNK_BYTES, &tmK, &k_full[bf], kvh * HD + c * 64, row_kv);
-        mbar_wait(&v_empty[bf], u ^ 1);
-        mbar_arrive_expect_tx(&v_full[bf], Cfg::TILE_BYTES);
+        mbar_wait(v_empty, (j & 1) ^ 1);
+        mbar_arrive_expect_tx(v_full, Cfg::TILE_BYTES);
 #pragma unroll
-        for (int c = 0; c < Cfg::CH; ++c)
-          tma_load_2d(sV + bf * Cfg::TILE_BYTES + c * Cfg::CHUNK_BYTES, &tmV, &v_full[bf], kvh * HD + c * 64, row_kv);
+        for (int c = 0; c < Cfg::CH; ++c) tma_load_2d(sV + c * Cfg::CHUNK_BYTES, &tmV, v_full, kvh * HD + c * 64, row_kv);
       }
     }
     __syncwarp();
@@ -144,90 +155,100 @@ __global__ void __launch_bounds__(FA_THREADS, 1)
     if (lane == 0) {
       const uint32_t idesc_qk = umma_idesc_bf16(128, 128, 0, 0);  // A = Q (K-major), B = K (K-major)
       const uint32_t idesc_pv = umma_idesc_bf16(128, HD, 0, 1);   // A = P (K-major), B = V (MN-major: hd contiguous)
-      const uint32_t q_addr = smem_u32(sQ);
       mbar_wait(q_full, 0);
-      auto issue_qk = [&](int j) {
-        const int bf = j & 1;
-        const uint32_t u = (j >> 1) & 1;
-        mbar_wait(&k_full[bf], u);
-        mbar_wait(&s_empty[bf], u ^ 1);
+      const uint32_t v_addr = smem_u32(sV);
+      auto qk_t = [&](int j, int t) {  // S_t = Q_t K(j)^T
+        if (j >= n_kv_t[t]) return;
+        mbar_wait(&s_empty[t], (j & 1) ^ 1);  // the softmax group has finished reading S_t of the previous KV tile
         tc_fence_after();
-        const uint32_t k_addr = smem_u32(sK + bf * Cfg::TILE_BYTES);
+        const uint32_t q_addr = smem_u32(sQ + t * Cfg::TILE_BYTES);
+        const uint32_t k_addr = smem_u32(sK + (j & 1) * Cfg::TILE_BYTES);
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
           const uint32_t off = (kk >> 2) * Cfg::CHUNK_BYTES + (kk & 3) * 32;
-          umma_bf16(tmem_base + bf * 128, umma_desc_kmajor(q_addr + off), umma_desc_kmajor(k_addr + off), idesc_qk, kk > 0 ? 1u : 0u);
+          umma_bf16(tmem_base + t * 128, umma_desc_kmajor(q_addr + off), umma_desc_kmajor(k_addr + off), idesc_qk, kk > 0 ? 1u : 0u);
         }
-        umma_commit(&k_empty[bf]);
-        umma_commit(&s_full[bf]);
+        umma_commit(&s_full[t]);
       };
-      auto issue_pv = [&](int j) {
-        const int bf = j & 1;
-        const uint32_t u = (j >> 1) & 1;
-        mbar_wait(&v_full[bf], u);
-        mbar_wait(&p_full[bf], u);
+      auto pv_t = [&](int j, int t) {  // O_t += P_t V(j)
+        if (j >= n_kv_t[t]) return;
+        mbar_wait(&p_full[t], j & 1);
         tc_fence_after();
-        const uint32_t p_addr = smem_u32(sP + bf * Cfg::P_BYTES);
-        const uint32_t v_addr = smem_u32(sV + bf * Cfg::TILE_BYTES);
+        const uint32_t p_addr = smem_u32(sP + t * Cfg::P_BYTES);
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           const uint32_t aoff = (kk >> 2) * Cfg::CHUNK_BYTES + (kk & 3) * 32;
-          umma_bf16(tmem_O, umma_desc_kmajor(p_addr + aoff), umma_desc_mnmajor(v_addr + kk * 2048, 128), idesc_pv,
+          umma_bf16(tmem_base + 256 + t * 128, umma_desc_kmajor(p_addr + aoff), umma_desc_mnmajor(v_addr + kk * 2048, 128), idesc_pv,
                     (j > 0 || kk > 0) ? 1u : 0u);
         }
-        umma_commit(&v_empty[bf]);
-        umma_commit(&pv_done[bf]);
+        umma_commit(&pv_done[t]);
       };
-      issue_qk(0);
+      // issue order per KV tile j:  PV0(j) QK0(j+1) PV1(j) QK1(j+1)  - each tile's MMAs follow its own softmax, the other
+      // tile's MMAs fill the tensor pipe meanwhile
+      mbar_wait(&k_full[0], 0);
+      qk_t(0, 0);
+      qk_t(0, 1);
+      umma_commit(&k_empty[0]);
       for (int j = 0; j < n_kv; ++j) {
-        if (j + 1 < n_kv) issue_qk(j + 1);
-        issue_pv(j);
+        const bool more = j + 1 < n_kv;
+        mbar_wait(v_full, j & 1);
+        pv_t(j, 0);
+        if (more) {
+          mbar_wait(&k_full[(j + 1) & 1], ((j + 1) >> 1) & 1);
+          qk_t(j + 1, 0);
+        }
+        pv_t(j, 1);
+        if (more) {
+          qk_t(j + 1, 1);
+          umma_commit(&k_empty[(j + 1) & 1]);
+        }
+        umma_commit(v_empty);
       }
     }
     __syncwarp();
   } else {
-    // ------------------------------------------------------------------ softmax + epilogue (warps 2..5 -> lane quarters 2,3,0,1)
+    // ------------------------------------------------------------------ softmax + epilogue: warps 2-5 tile 0, warps 6-9 tile 1
+    const int t = (warp - 2) >> 2;
     const int qd = warp & 3;
     const int r = qd * 32 + lane;      // row inside the tile = TMEM lane
-    const int q_idx = q0 + r;
+    const int q_idx = q0 + t * 128 + r;
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
+    const uint32_t tS = lane_base + (uint32_t)(t * 128);
+    const uint32_t tO = lane_base + (uint32_t)(256 + t * 128);
+    const int n_mine = n_kv_t[t];
     float m = -INFINITY, l = 0.f;
-    float s[128];
-    for (int j = 0; j < n_kv; ++j) {
-      const int bf = j & 1;
-      const uint32_t u = (j >> 1) & 1;
-      mbar_wait(&s_full[bf], u);
+    for (int j = 0; j < n_mine; ++j) {
+      mbar_wait(&s_full[t], j & 1);
       tc_fence_after();
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        uint32_t raw[32];
-        SPB_TMEM_LD_32(lane_base + (uint32_t)(bf * 128 + c * 32), raw);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(raw[i]);
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&s_empty[bf]);  // S buffer may be overwritten by QK^T of tile j+2
-
       const int kv0 = j * 128;
-      const bool need_mask = (p.causal && j == qt) || (kv0 + 128 > p.T);
-      float tmax = -INFINITY;
-      if (need_mask) {
+      const bool need_mask = (p.causal && kv0 + 127 > q0 + t * 128) || (kv0 + 128 > p.T);
+      // number of leading KV columns of this tile that row q_idx may attend to (everything else is masked)
+      int n_valid = p.T - kv0;
+      if (p.causal) n_valid = min(n_valid, q_idx - kv0 + 1);
+      // ---- pass 1: row max of the raw scores (scale > 0, so scaling commutes with max); two 32-column TMEM loads in flight
+      float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll 1
+      for (int c2 = 0; c2 < 2; ++c2) {
+        uint32_t ra[32], rb[32];
+        SPB_TMEM_LD_32(tS + (uint32_t)(c2 * 64), ra);
+        SPB_TMEM_LD_32(tS + (uint32_t)(c2 * 64 + 32), rb);
+        tmem_ld_wait();
+        if (need_mask) {
+          const int lim = n_valid - c2 * 64;
 #pragma unroll
-        for (int i = 0; i < 128; ++i) {
-          const int kv = kv0 + i;
-          const bool dead = (p.causal && kv > q_idx) || (kv >= p.T);
-          s[i] = dead ? -INFINITY : s[i] * p.scale_log2;
-          tmax = fmaxf(tmax, s[i]);
-        }
-      } else {
+          for (int i = 0; i < 32; ++i) {
+            mx0 = fmaxf(mx0, i < lim ? __uint_as_float(ra[i]) : -INFINITY);
+            mx1 = fmaxf(mx1, i + 32 < lim ? __uint_as_float(rb[i]) : -INFINITY);
+          }
+        } else {
 #pragma unroll
-        for (int i = 0; i < 128; ++i) {
-          s[i] *= p.scale_log2;
-          tmax = fmaxf(tmax, s[i]);
+          for (int i = 0; i < 32; ++i) {
+            mx0 = fmaxf(mx0, __uint_as_float(ra[i]));
+            mx1 = fmaxf(mx1, __uint_as_float(rb[i]));
+          }
         }
       }
+      const float tmax = fmaxf(mx0, mx1) * p.scale_log2;
       if (j == 0) {
         m = tmax;
       } else {
@@ -240,71 +261,91 @@ __global__ void __launch_bounds__(FA_THREADS, 1)
             m = tmax;
           }
           l *= alpha;
-          mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);  // O must hold every PV issued so far
+          mbar_wait(&pv_done[t], (j - 1) & 1);  // O_t must hold every PV issued so far
           tc_fence_after();
-#pragma unroll
+#pragma unroll 1
           for (int c = 0; c < HD / 32; ++c) {
             uint32_t o[32];
-            SPB_TMEM_LD_32(lane_base + (uint32_t)(256 + c * 32), o);
+            SPB_TMEM_LD_32(tO + (uint32_t)(c * 32), o);
             tmem_ld_wait();
 #pragma unroll
             for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-            SPB_TMEM_ST_32(lane_base + (uint32_t)(256 + c * 32), o);
+            SPB_TMEM_ST_32(tO + (uint32_t)(c * 32), o);
           }
           tmem_st_wait();
         }
       }
-      float sum = 0.f;
+      // ---- pass 2: p = exp2(s*c - m) (packed fp32x2 FFMA), row sum, bf16 P into shared memory (UMMA K-major, 128B swizzle)
+      if (j >= 1) mbar_wait(&pv_done[t], (j - 1) & 1);  // PV_t(j-1) has finished reading the P buffer
+      uint8_t* prow = sP + t * Cfg::P_BYTES + r * 128;
+      const float2 sc2 = make_float2(p.scale_log2, p.scale_log2);
+      const float2 nm2 = make_float2(-m, -m);
+      float2 sum2 = make_float2(0.f, 0.f);
+#pragma unroll 1
+      for (int c2 = 0; c2 < 2; ++c2) {
+        uint32_t ra[32], rb[32];
+        SPB_TMEM_LD_32(tS + (uint32_t)(c2 * 64), ra);
+        SPB_TMEM_LD_32(tS + (uint32_t)(c2 * 64 + 32), rb);
+        tmem_ld_wait();
+        const int lim = need_mask ? n_valid - c2 * 64 : 64;
+        uint32_t pk[32];  // 64 bf16
 #pragma unroll
-      for (int i = 0; i < 128; ++i) {
-        s[i] = fast_exp2(s[i] - m);
-        sum += s[i];
-      }
-      l += sum;
-      if (j >= 2) mbar_wait(&pv_done[bf], ((j - 2) >> 1) & 1);  // PV(j-2) has finished reading this P buffer
-      uint8_t* prow = sP + bf * Cfg::P_BYTES + r * 128;
-#pragma unroll
-      for (int t = 0; t < 2; ++t) {
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          const float* f = &s[t * 64 + c * 8];
-          uint4 v;
-          v.x = pack_bf16(f[0], f[1]);
-          v.y = pack_bf16(f[2], f[3]);
-          v.z = pack_bf16(f[4], f[5]);
-          v.w = pack_bf16(f[6], f[7]);
-          *reinterpret_cast<uint4*>(prow + t * Cfg::CHUNK_BYTES + ((c ^ (r & 7)) << 4)) = v;
+        for (int i = 0; i < 32; i += 2) {
+          const float2 xa = __ffma2_rn(make_float2(__uint_as_float(ra[i]), __uint_as_float(ra[i + 1])), sc2, nm2);
+          const float2 xb = __ffma2_rn(make_float2(__uint_as_float(rb[i]), __uint_as_float(rb[i + 1])), sc2, nm2);
+          float2 pa = make_float2(fast_exp2(xa.x), fast_exp2(xa.y));
+          float2 pb = make_float2(fast_exp2(xb.x), fast_exp2(xb.y));
+          if (need_mask) {
+            if (i >= lim) pa.x = 0.f;
+            if (i + 1 >= lim) pa.y = 0.f;
+            if (i + 32 >= lim) pb.x = 0.f;
+            if (i + 33 >= lim) pb.y = 0.f;
+          }
+          sum2 = __fadd2_rn(sum2, __fadd2_rn(pa, pb));
+          pk[i >> 1] = pack_bf16(pa.x, pa.y);
+          pk[16 + (i >> 1)] = pack_bf16(pb.x, pb.y);
         }
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          *reinterpret_cast<uint4*>(prow + c2 * Cfg::CHUNK_BYTES + ((u ^ (r & 7)) << 4)) =
+              make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
       }
-      fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
+      const float sum = sum2.x + sum2.y;
+      l += sum;
       tc_fence_before();
+      fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
       __syncwarp();
-      if (lane == 0) mbar_arrive(&p_full[bf]);
+      if (lane == 0) {
+        mbar_arrive(&s_empty[t]);  // S_t may be overwritten by QK^T of the next KV tile
+        mbar_arrive(&p_full[t]);
+      }
     }
     // epilogue: O / l -> bf16 -> global; lse = m*ln2 + ln(l)
-    mbar_wait(&pv_done[(n_kv - 1) & 1], ((n_kv - 1) >> 1) & 1);
-    tc_fence_after();
-    const float inv = 1.0f / l;
-    const bool valid = q_idx < p.T;
-    __nv_bfloat16* orow = p.o + ((int64_t)b * p.T + q_idx) * p.ldo + (int64_t)h * HD;
+    if (n_mine > 0) {
+      mbar_wait(&pv_done[t], (n_mine - 1) & 1);
+      tc_fence_after();
+      const float inv = 1.0f / l;
+      const bool valid = q_idx < p.T;
+      __nv_bfloat16* orow = p.o + ((int64_t)b * p.T + q_idx) * p.ldo + (int64_t)h * HD;
 #pragma unroll
-    for (int c = 0; c < HD / 32; ++c) {
-      uint32_t o[32];
-      SPB_TMEM_LD_32(lane_base + (uint32_t)(256 + c * 32), o);
-      tmem_ld_wait();
-      if (valid) {
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t o[32];
+        SPB_TMEM_LD_32(tO + (uint32_t)(c * 32), o);
+        tmem_ld_wait();
+        if (valid) {
 #pragma unroll
-        for (int i = 0; i < 32; i += 8) {
-          uint4 v;
-          v.x = pack_bf16(__uint_as_float(o[i]) * inv, __uint_as_float(o[i + 1]) * inv);
-          v.y = pack_bf16(__uint_as_float(o[i + 2]) * inv, __uint_as_float(o[i + 3]) * inv);
-          v.z = pack_bf16(__uint_as_float(o[i + 4]) * inv, __uint_as_float(o[i + 5]) * inv);
-          v.w = pack_bf16(__uint_as_float(o[i + 6]) * inv, __uint_as_float(o[i + 7]) * inv);
-          *reinterpret_cast<uint4*>(orow + c * 32 + i) = v;
+          for (int i = 0; i < 32; i += 8) {
+            uint4 v;
+            v.x = pack_bf16(__uint_as_float(o[i]) * inv, __uint_as_float(o[i + 1]) * inv);
+            v.y = pack_bf16(__uint_as_float(o[i + 2]) * inv, __uint_as_float(o[i + 3]) * inv);
+            v.z = pack_bf16(__uint_as_float(o[i + 4]) * inv, __uint_as_float(o[i + 5]) * inv);
+            v.w = pack_bf16(__uint_as_float(o[i + 6]) * inv, __uint_as_float(o[i + 7]) * inv);
+            *reinterpret_cast<uint4*>(orow + c * 32 + i) = v;
+          }
         }
       }
+      if (valid) p.lse[((int64_t)b * p.Hq + h) * p.T + q_idx] = m * LN2 + logf(l);
     }
-    if (valid) p.lse[((int64_t)b * p.Hq + h) * p.T + q_idx] = m * LN2 + logf(l);
   }
 
   tc_fence_before();
@@ -341,7 +382,7 @@ static int flash_fwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
   a.causal = causal;
   a.scale_log2 = scale * LOG2E;
   SPB_CUDA(cudaFuncSetAttribute(flash_fwd_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-  dim3 grid((Tn + 127) / 128, Hq, B);
+  dim3 grid((Tn + 255) / 256, Hq, B);
   flash_fwd_tc_kernel<HD><<<grid, FA_THREADS, Cfg::SMEM_BYTES, st>>>(tmQ, tmK, tmV, a);
   SPB_LAUNCH_CHECK();
   return 0;

@@ -21,24 +21,72 @@ struct GemmTcArgs {
   void* D;
   int64_t ldd;
   const __nv_bfloat16* bias;
+  const float4* rope;  // optional fused rotary epilogue (llama3:592-601): table [T, hd/2] of (a,b,c,d), applied to columns < rope_cols
+  int rope_cols, rope_T, rope_hd;
   int out_f32, accumulate, atomic, vec_ok;
   int M, N;
   int a_mn, b_mn;
-  int num_m, num_n, kb_total, kb_per_split, splits;
+  // work items: the first `full_tiles` tiles (whole waves) run over the whole K range; the remaining tail tiles are each
+  // split along K into `tail_parts` parts that add into a pre-zeroed fp32 output with atomics, so the last, partial wave
+  // costs 1/tail_parts of a wave (also covers few-tile weight gradients: full_tiles = 0).
+  int num_m, num_n, kb_total, full_tiles, tail_parts, kb_per_part, total_items;
 };
+
+struct GemmTcItem {
+  int m0, n0, kb0, kb1, atomic;
+};
+
+// Tile raster: groups of GT_GROUP_M row-blocks, row-block fastest inside a group, so that the ~148 concurrently resident
+// tiles share a few A row-panels and B column-panels that stay in the 126 MB L2 (ncu r01b: 5.7x DRAM re-reads without it).
+constexpr int GT_GROUP_M = 16;
+__device__ __forceinline__ void gemm_tc_tile_coords(const GemmTcArgs& p, int tile, int& m_blk, int& n_blk) {
+  const int group_sz = GT_GROUP_M * p.num_n;
+  const int gid = tile / group_sz;
+  const int first_m = gid * GT_GROUP_M;
+  const int gm = min(p.num_m - first_m, GT_GROUP_M);
+  const int in_group = tile - gid * group_sz;
+  m_blk = first_m + in_group % gm;
+  n_blk = in_group / gm;
+}
+template <int BN>
+__device__ __forceinline__ GemmTcItem gemm_tc_item(const GemmTcArgs& p, int item) {
+  GemmTcItem it;
+  int tile = item, part = 0;
+  it.atomic = 0;
+  it.kb0 = 0;
+  it.kb1 = p.kb_total;
+  if (item >= p.full_tiles) {
+    const int j = item - p.full_tiles;
+    tile = p.full_tiles + j / p.tail_parts;
+    part = j % p.tail_parts;
+    it.kb0 = part * p.kb_per_part;
+    it.kb1 = min(it.kb0 + p.kb_per_part, p.kb_total);
+    it.atomic = p.tail_parts > 1;
+  }
+  int m_blk, n_blk;
+  gemm_tc_tile_coords(p, tile, m_blk, n_blk);
+  it.m0 = m_blk * GT_BM;
+  it.n0 = n_blk * BN;
+  return it;
+}
 
 template <int BN>
 struct GemmTcCfg {
-  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 192 ? 4 : 6);
   static constexpr int A_BYTES = GT_BM * GT_BK * 2;
   static constexpr int B_BYTES = BN * GT_BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_BYTES = 256;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // +1024: manual 1 KB alignment
-  static constexpr int TMEM_COLS = 2 * BN;
+  // rotary epilogue: each epilogue warp stages the table slice of its 32 rows x 16 pairs, pair-major with an XOR swizzle:
+  // entry (row r, pair i) at 16-byte slot i*32 + (r ^ i) - both the cooperative writes and the per-row reads are conflict-free
+  static constexpr int ROPE_WARP_BYTES = 32 * 16 * 16;
+  static constexpr int ROPE_BYTES = 4 * ROPE_WARP_BYTES;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + ROPE_BYTES + 1024;  // +1024: manual 1 KB alignment
+  static constexpr int TMEM_COLS = (BN == 192) ? 512 : 2 * BN;  // power of two; accumulator stage a sits at column a*BN
 };
 
-__device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row, int col0, const uint32_t* r) {
+__device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row, int col0, const uint32_t* r,
+                                                    const uint8_t* rope_row, int lane_in_warp, int atomic) {
   // 32 consecutive fp32 accumulator columns of one output row
   const int ncol = min(32, p.N - col0);
   float v[32];
@@ -49,9 +97,22 @@ __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row
     for (int i = 0; i < 32; ++i)
       if (i < ncol) v[i] += __bfloat162float(p.bias[col0 + i]);
   }
+  if (rope_row != nullptr) {
+    // adjacent pairs (2j, 2j+1) of one head live in this thread's registers; rotate the fp32 accumulators in place.
+    // rope_row = the warp's staged table slice (32 rows x 16 pairs, swizzled), loaded coalesced by the warp.
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) {
+      if (col0 + i < p.rope_cols && i + 1 < ncol) {
+        const float4 m = *reinterpret_cast<const float4*>(rope_row + ((((i >> 1) << 5) + (lane_in_warp ^ (i >> 1))) << 4));
+        const float xe = v[i], xo = v[i + 1];
+        v[i] = m.x * xe + m.y * xo;
+        v[i + 1] = m.z * xe + m.w * xo;
+      }
+    }
+  }
   if (p.out_f32) {
     float* d = reinterpret_cast<float*>(p.D) + (int64_t)row * p.ldd + col0;
-    if (p.atomic) {
+    if (atomic) {
 #pragma unroll
       for (int i = 0; i < 32; ++i)
         if (i < ncol) atomicAdd(d + i, v[i]);
@@ -109,6 +170,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
   uint64_t* tfull = empty + Cfg::STAGES;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint8_t* sRope = smem + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BAR_BYTES;
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -138,8 +200,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int tiles = p.num_m * p.num_n;
-  const int total_items = tiles * p.splits;
+  const int total_items = p.total_items;
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -147,11 +208,9 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
       int stage = 0;
       uint32_t phase = 0;
       for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-        const int split = item / tiles, tile = item % tiles;
-        const int m0 = (tile % p.num_m) * GT_BM, n0 = (tile / p.num_m) * BN;
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
-        for (int kb = kb0; kb < kb1; ++kb) {
+        const GemmTcItem wi = gemm_tc_item<BN>(p, item);
+        const int m0 = wi.m0, n0 = wi.n0;
+        for (int kb = wi.kb0; kb < wi.kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           mbar_arrive_expect_tx(&full[stage], Cfg::STAGE_BYTES);
           uint8_t* a = sA + stage * Cfg::A_BYTES;
@@ -180,9 +239,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
       for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-        const int split = item / tiles;
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        const GemmTcItem wi = gemm_tc_item<BN>(p, item);
+        const int kb0 = wi.kb0, kb1 = wi.kb1;
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
@@ -212,8 +270,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-      const int tile = item % tiles;
-      const int m0 = (tile % p.num_m) * GT_BM, n0 = (tile / p.num_m) * BN;
+      const GemmTcItem wi = gemm_tc_item<BN>(p, item);
+      const int m0 = wi.m0, n0 = wi.n0;
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const int row = m0 + q * 32 + lane;
@@ -224,8 +282,30 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
         if (col0 >= p.N) break;  // warp-uniform
         uint32_t r[32];
         SPB_TMEM_LD_32(taddr + (uint32_t)(c * 32), r);
+        const uint8_t* rope_row = nullptr;
+        if (p.rope != nullptr && col0 < p.rope_cols) {  // warp-uniform
+          // stage table[t(row)][pair0 .. pair0+15] for the warp's 32 rows: 2 rows (2 x 256 B) per load instruction
+          uint8_t* wbuf = sRope + (warp - 2) * Cfg::ROPE_WARP_BYTES;
+          const int pair0 = (col0 % p.rope_hd) >> 1;
+          const int half = lane >> 4, l16 = lane & 15;
+          // phase 1: all 16 coalesced global loads in flight (the table is L2 resident); phase 2: swizzled smem stores
+          float4 tm[16];
+          const bool pair_ok = pair0 + l16 < (p.rope_hd >> 1);
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            const int grow = m0 + q * 32 + 2 * k + half;
+            tm[k] = make_float4(1.f, 0.f, 0.f, 1.f);
+            if (grow < p.M && pair_ok) tm[k] = __ldg(p.rope + (int64_t)(grow % p.rope_T) * (p.rope_hd >> 1) + pair0 + l16);
+          }
+          __syncwarp();  // previous chunk's readers are done with the buffer
+#pragma unroll
+          for (int k = 0; k < 16; ++k)
+            *reinterpret_cast<float4*>(wbuf + (((l16 << 5) + ((2 * k + half) ^ l16)) << 4)) = tm[k];
+          __syncwarp();
+          rope_row = wbuf;
+        }
         tmem_ld_wait();
-        if (row < p.M) gemm_tc_store_chunk(p, row, col0, r);
+        if (row < p.M) gemm_tc_store_chunk(p, row, col0, r, rope_row, lane, wi.atomic);
       }
       tc_fence_before();
       __syncwarp();
@@ -240,30 +320,90 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
 }
 
+// zero the tail tiles that will be accumulated with atomics (one CTA per tail tile)
 template <int BN>
-static int gemm_tc_launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmTcArgs& args, cudaStream_t st) {
+__global__ void __launch_bounds__(256) gemm_tc_zero_tail_kernel(const GemmTcArgs p) {
+  int m_blk, n_blk;
+  gemm_tc_tile_coords(p, p.full_tiles + (int)blockIdx.x, m_blk, n_blk);
+  float* d = reinterpret_cast<float*>(p.D);
+  const int m0 = m_blk * GT_BM, n0 = n_blk * BN;
+  for (int e = threadIdx.x; e < GT_BM * BN; e += 256) {
+    const int r = m0 + e / BN, c = n0 + e % BN;
+    if (r < p.M && c < p.N) d[(int64_t)r * p.ldd + c] = 0.f;
+  }
+}
+
+template <int BN>
+static int gemm_tc_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int64_t K, GemmTcArgs args, bool may_split,
+                          cudaStream_t st) {
   using Cfg = GemmTcCfg<BN>;
+  const int G = sm_count();
+  args.num_n = (args.N + BN - 1) / BN;
+  const int tiles = args.num_m * args.num_n;
+  args.full_tiles = tiles;
+  args.tail_parts = 1;
+  args.kb_per_part = args.kb_total;
+  if (may_split) {
+    const int full = (tiles / G) * G, R = tiles - full;
+    // measured (r01d): with row-per-thread fp32 atomics the K-split of a tail wave costs more than it saves on 768-tile
+    // problems, so it is used only when the whole problem is a partial wave (few-tile weight gradients, d=256 models)
+    if (full == 0 && R > 0 && R * 2 <= G && args.kb_total >= 16) {
+      int parts = G / R;
+      const int max_parts = args.kb_total / 8;  // at least 8 k-blocks (512 k) per part
+      if (parts > max_parts) parts = max_parts;
+      if (parts > 1) {
+        args.kb_per_part = (args.kb_total + parts - 1) / parts;
+        args.tail_parts = (args.kb_total + args.kb_per_part - 1) / args.kb_per_part;
+        args.full_tiles = full;
+      }
+    }
+  }
+  args.total_items = args.full_tiles + (tiles - args.full_tiles) * args.tail_parts;
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!args.a_mn) rc = make_tmap_2d(&tmA, A, 2, (uint64_t)args.M, (uint64_t)K, (uint64_t)lda, GT_BM, GT_BK, true, false);
+  else rc = make_tmap_2d(&tmA, A, 2, (uint64_t)K, (uint64_t)args.M, (uint64_t)lda, GT_BK, 64, true, false);
+  if (rc) return rc;
+  if (!args.b_mn) rc = make_tmap_2d(&tmB, B, 2, (uint64_t)args.N, (uint64_t)K, (uint64_t)ldb, (uint32_t)BN, GT_BK, true, false);
+  else rc = make_tmap_2d(&tmB, B, 2, (uint64_t)K, (uint64_t)args.N, (uint64_t)ldb, GT_BK, 64, true, false);
+  if (rc) return rc;
+  if (args.tail_parts > 1) {
+    gemm_tc_zero_tail_kernel<BN><<<tiles - args.full_tiles, 256, 0, st>>>(args);
+    SPB_LAUNCH_CHECK();
+  }
   SPB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-  const int items = args.num_m * args.num_n * args.splits;
-  const int grid = items < sm_count() ? items : sm_count();
+  const int grid = args.total_items < G ? args.total_items : G;
   gemm_tc_kernel<BN><<<grid, GT_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, args);
   SPB_LAUNCH_CHECK();
   return 0;
 }
 
+static double gemm_tc_wave_eff(int64_t M, int64_t N, int bn, int G) {
+  const int64_t tiles = ((M + GT_BM - 1) / GT_BM) * ((N + bn - 1) / bn);
+  const int64_t waves = (tiles + G - 1) / G;
+  const double useful = (double)M * (double)N;  // output elements actually needed
+  return useful / ((double)waves * G * GT_BM * bn);
+}
+
 int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb,
-            int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st) {
+            int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st, const float* rope, int rope_cols,
+            int rope_T, int rope_hd) {
   SPB_CHECK_ARG(M < (1LL << 31) && N < (1LL << 31) && K < (1LL << 31), SPB_E_LIMIT, "gemm_tc: dimension beyond 2^31");
   SPB_CHECK_ARG(M > 0 && N > 0 && K > 0, SPB_E_INVALID, "gemm_tc: empty problem");
   SPB_CHECK_ARG(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && (lda % 8 == 0) && (ldb % 8 == 0), SPB_E_UNSUPPORTED,
                 "gemm_tc: TMA needs 16-byte aligned operands and leading dimensions that are multiples of 8 (lda=%lld ldb=%lld)",
                 (long long)lda, (long long)ldb);
   SPB_CHECK_ARG(out_dtype == SPB_F32 || out_dtype == SPB_BF16, SPB_E_UNSUPPORTED, "gemm_tc: out_dtype %d", out_dtype);
-  const int BN = (N > 128) ? 256 : 128;
   GemmTcArgs args{};
   args.D = D;
   args.ldd = ldd;
   args.bias = (const __nv_bfloat16*)bias;
+  args.rope = (const float4*)rope;
+  args.rope_cols = rope_cols;
+  args.rope_T = rope_T > 0 ? rope_T : 1;
+  args.rope_hd = rope_hd > 0 ? rope_hd : 2;
+  SPB_CHECK_ARG(rope == nullptr || (!accumulate && rope_hd % 32 == 0 && (uintptr_t)rope % 16 == 0), SPB_E_INVALID,
+                "gemm_tc: the fused rotary epilogue needs a head dim that is a multiple of 32, a 16-byte aligned table and no accumulation");
   args.out_f32 = (out_dtype == SPB_F32);
   args.accumulate = accumulate;
   args.M = (int)M;
@@ -273,35 +413,22 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
   args.a_mn = transA ? 1 : 0;
   args.b_mn = transB ? 0 : 1;
   args.num_m = (int)((M + GT_BM - 1) / GT_BM);
-  args.num_n = (int)((N + BN - 1) / BN);
   args.kb_total = (int)((K + GT_BK - 1) / GT_BK);
   const int esz = args.out_f32 ? 4 : 2;
   args.vec_ok = ((uintptr_t)D % 16 == 0) && ((ldd * esz) % 16 == 0);
-  // split-K only for plain fp32 outputs (weight gradients) that would leave most SMs idle
-  int splits = 1;
-  const int tiles = args.num_m * args.num_n;
-  if (args.out_f32 && bias == nullptr && !accumulate && tiles * 2 <= sm_count() && args.kb_total >= 16) {
-    splits = sm_count() / tiles;
-    const int max_splits = args.kb_total / 8;  // at least 8 k-blocks (512 k) per split
-    if (splits > max_splits) splits = max_splits;
-    if (splits < 1) splits = 1;
+  // K-split of the tail wave needs a plain fp32 output (weight gradients)
+  const bool may_split = args.out_f32 && bias == nullptr && rope == nullptr && !accumulate;
+  // tile width: 256 unless a 192-wide tile fills the waves of this problem clearly better (e.g. 8192 x 6144: 94 % -> 99 %)
+  int BN = (N > 128) ? 256 : 128;
+  if (BN == 256 && !may_split) {
+    const int G = sm_count();
+    // measured (r01d): the 192-wide tile runs at 1219 TF/s vs 1342 TF/s for 256 on 8192x6144x4096 despite 99 % vs 94 % wave
+    // efficiency (lower arithmetic intensity per smem byte), so it is only taken for a much larger gain
+    if (gemm_tc_wave_eff(M, N, 192, G) > gemm_tc_wave_eff(M, N, 256, G) + 0.15) BN = 192;
   }
-  args.kb_per_split = (args.kb_total + splits - 1) / splits;
-  args.splits = (args.kb_total + args.kb_per_split - 1) / args.kb_per_split;
-  args.atomic = args.splits > 1;
-  if (args.atomic) {
-    SPB_CUDA(cudaMemset2DAsync(D, (size_t)ldd * 4, 0, (size_t)N * 4, (size_t)M, st));
-  }
-  CUtensorMap tmA, tmB;
-  int rc;
-  if (!args.a_mn) rc = make_tmap_2d(&tmA, A, 2, (uint64_t)M, (uint64_t)K, (uint64_t)lda, GT_BM, GT_BK, true, false);
-  else rc = make_tmap_2d(&tmA, A, 2, (uint64_t)K, (uint64_t)M, (uint64_t)lda, GT_BK, 64, true, false);
-  if (rc) return rc;
-  if (!args.b_mn) rc = make_tmap_2d(&tmB, B, 2, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, (uint32_t)BN, GT_BK, true, false);
-  else rc = make_tmap_2d(&tmB, B, 2, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, GT_BK, 64, true, false);
-  if (rc) return rc;
-  if (BN == 256) return gemm_tc_launch<256>(tmA, tmB, args, st);
-  return gemm_tc_launch<128>(tmA, tmB, args, st);
+  if (BN == 256) return gemm_tc_launch<256>(A, lda, B, ldb, K, args, may_split, st);
+  if (BN == 192) return gemm_tc_launch<192>(A, lda, B, ldb, K, args, may_split, st);
+  return gemm_tc_launch<128>(A, lda, B, ldb, K, args, may_split, st);
 }
 
 }  // namespace spb

@@ -7,8 +7,10 @@ namespace spb {
 
 int gemm_simt(int in_dtype, int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B,
               int64_t ldb, int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st);
+// rope != nullptr: fused rotary epilogue on output columns < rope_cols (row n has position n % rope_T)
 int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb,
-            int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st);
+            int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st, const float* rope = nullptr,
+            int rope_cols = 0, int rope_T = 0, int rope_hd = 0);
 
 int attn_simt_fwd(int dtype, int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq,
                   const void* k, int64_t ldk, const void* v, int64_t ldv, void* o, int64_t ldo, float* lse, cudaStream_t st);
@@ -25,7 +27,7 @@ int flash_fwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale
 int flash_bwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k,
                  int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o, int64_t lddo,
                  const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
-                 float* dq_acc, cudaStream_t st);
+                 float* dq_acc, cudaStream_t st, const float* rope = nullptr);  // rope: fused rotary VJP on dq and dk
 
 // comm.cu
 // all-reduce on the communicator's side stream, ordered after everything already enqueued on `main`

@@ -1,7 +1,7 @@
 // norm_rope.cu - K1: the memory-bound kernels of the block.
-//   * norm forward  (RMSNorm llama3:536-538 / gemma:139-150, LayerNorm flax + torch): one warp per row, the row is
-//     read ONCE with 128-bit loads into registers, reduced with warp shuffles in fp32, written once.
-//   * norm backward (dx: one warp per row; dweight/dbias: coalesced column-sum kernel + deterministic 2nd stage).
+//   * norm forward  (RMSNorm llama3:536-538 / gemma:139-150, LayerNorm flax + torch): 1-8 warps per row, the row is
+//     read ONCE with 128-bit loads and kept packed in registers, reduced with warp shuffles in fp32, written once.
+//   * norm backward (dx: same structure; dweight/dbias: coalesced column-sum kernel + deterministic 2nd stage).
 //   * rotary (llama3:592-601 adjacent-pair rotation; gemma:182-200 "rotary" = general 2x2 per (t,pair) table),
 //     in place on the q|k column range of the packed qkv buffer, 128-bit loads, and its transpose for the VJP.
 // Algorithmic bytes: norm fwd 2*N*C*e (+8N stats); norm bwd dx 3*N*C*e; rope 2*N*cols*e.
@@ -40,65 +40,89 @@ struct Vec<__nv_bfloat16> {
 constexpr int NORM_WARPS = 4;
 
 // ------------------------------------------------------------------------------------------------ norm forward
-// VPL = 128-bit vectors per lane held in registers (C <= 32*VPL*Vec::N).
-template <typename T, int VPL>
-__global__ void __launch_bounds__(NORM_WARPS * 32) norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ w,
-                                                                    const T* __restrict__ b, T* __restrict__ y,
-                                                                    float* __restrict__ stats, int64_t N, int C,
-                                                                    float eps, int kind, int upcast) {
+// 256-thread CTA = 8 warps; WPR warps share one row (8/WPR rows per CTA), every thread keeps VPT 128-bit vectors of the row
+// PACKED in registers (<= 16 registers), so occupancy stays high and the whole machine has loads in flight: the row is
+// read from HBM once and written once.  Row reductions: warp shuffles, then (WPR > 1) one shared-memory exchange.
+constexpr int NR_THREADS = 256;
+
+template <int WPR>
+__device__ __forceinline__ float row_reduce(float v, float* red, int warp) {
+  v = warp_sum(v);
+  if (WPR > 1) {
+    if ((threadIdx.x & 31) == 0) red[warp] = v;
+    __syncthreads();
+    const int base = (warp / WPR) * WPR;
+    v = 0.f;
+#pragma unroll
+    for (int j = 0; j < WPR; ++j) v += red[base + j];
+  }
+  return v;
+}
+
+template <typename T, int VPT, int WPR>
+__global__ void __launch_bounds__(NR_THREADS) norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ w,
+                                                               const T* __restrict__ b, T* __restrict__ y,
+                                                               float* __restrict__ stats, int64_t N, int C, float eps,
+                                                               int kind, int upcast) {
   constexpr int VN = Vec<T>::N;
-  const int lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * NORM_WARPS + (threadIdx.x >> 5);
-  if (row >= N) return;
+  constexpr int RPC = 8 / WPR;
+  __shared__ float red[2][8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int w_in = warp % WPR;
+  const int64_t row = (int64_t)blockIdx.x * RPC + warp / WPR;
+  const bool active = row < N;
   const T* xr = x + row * C;
-  float f[VPL][VN];
+  Vec<T> xv[VPT];
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) {
-    const int c = (i * 32 + lane) * VN;
-    if (c < C) {
-      Vec<T> v;
-      v.load(xr + c);
-      v.unpack(f[i]);
-    } else {
-#pragma unroll
-      for (int e = 0; e < VN; ++e) f[i][e] = 0.f;
-    }
+  for (int k = 0; k < VPT; ++k) {
+    const int c = ((k * WPR + w_in) * 32 + lane) * VN;
+    if (active && c < C) xv[k].load(xr + c);
   }
   float mean = 0.f;
   if (kind == SPB_NORM_LAYER) {
     float s = 0.f;
 #pragma unroll
-    for (int i = 0; i < VPL; ++i)
+    for (int k = 0; k < VPT; ++k) {
+      const int c = ((k * WPR + w_in) * 32 + lane) * VN;
+      if (active && c < C) {
+        float f[VN];
+        xv[k].unpack(f);
 #pragma unroll
-      for (int e = 0; e < VN; ++e) s += f[i][e];
-    mean = warp_sum(s) / (float)C;
+        for (int e = 0; e < VN; ++e) s += f[e];
+      }
+    }
+    mean = row_reduce<WPR>(s, red[0], warp) / (float)C;
   }
   float ss = 0.f;
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) {
-    const int c = (i * 32 + lane) * VN;
-    if (c < C) {
+  for (int k = 0; k < VPT; ++k) {
+    const int c = ((k * WPR + w_in) * 32 + lane) * VN;
+    if (active && c < C) {
+      float f[VN];
+      xv[k].unpack(f);
 #pragma unroll
       for (int e = 0; e < VN; ++e) {
-        const float d = f[i][e] - mean;
+        const float d = f[e] - mean;
         ss += d * d;
       }
     }
   }
-  const float var = warp_sum(ss) / (float)C;
+  const float var = row_reduce<WPR>(ss, red[1], warp) / (float)C;
   const float rstd = 1.0f / sqrtf(var + eps);
-  if (stats != nullptr && lane == 0) {
+  if (!active) return;
+  if (stats != nullptr && lane == 0 && w_in == 0) {
     stats[2 * row] = mean;
     stats[2 * row + 1] = rstd;
   }
   T* yr = y + row * C;
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) {
-    const int c = (i * 32 + lane) * VN;
+  for (int k = 0; k < VPT; ++k) {
+    const int c = ((k * WPR + w_in) * 32 + lane) * VN;
     if (c < C) {
       Vec<T> wv;
       wv.load(w + c);
-      float wf[VN], o[VN];
+      float f[VN], wf[VN], o[VN];
+      xv[k].unpack(f);
       wv.unpack(wf);
       if (kind == SPB_NORM_LAYER) {
         float bf[VN];
@@ -111,13 +135,13 @@ __global__ void __launch_bounds__(NORM_WARPS * 32) norm_fwd_kernel(const T* __re
           for (int e = 0; e < VN; ++e) bf[e] = 0.f;
         }
 #pragma unroll
-        for (int e = 0; e < VN; ++e) o[e] = (f[i][e] - mean) * rstd * wf[e] + bf[e];
+        for (int e = 0; e < VN; ++e) o[e] = (f[e] - mean) * rstd * wf[e] + bf[e];
       } else if (upcast) {  // gemma:148-150: round the normalised value to T first, then multiply by the weight
 #pragma unroll
-        for (int e = 0; e < VN; ++e) o[e] = to_f32<T>(from_f32<T>(f[i][e] * rstd)) * wf[e];
+        for (int e = 0; e < VN; ++e) o[e] = to_f32<T>(from_f32<T>(f[e] * rstd)) * wf[e];
       } else {  // llama3:538: (x * weight) * 1/sqrt(var + eps)
 #pragma unroll
-        for (int e = 0; e < VN; ++e) o[e] = (f[i][e] * wf[e]) * rstd;
+        for (int e = 0; e < VN; ++e) o[e] = (f[e] * wf[e]) * rstd;
       }
       Vec<T> ov;
       ov.pack(o);
@@ -166,36 +190,42 @@ __global__ void __launch_bounds__(NORM_WARPS * 32) norm_fwd_generic_kernel(const
 // ------------------------------------------------------------------------------------------------ norm backward (dx)
 // RMS  : y = x*w*r,            g = dy*w,  dx = r*g - x * r^3 * mean(g*x)
 // LAYER: y = (x-m)*r*w + b,    g = dy*w,  xh = (x-m)*r,  dx = r*(g - mean(g) - xh*mean(g*xh))
-template <typename T, int VPL>
-__global__ void __launch_bounds__(NORM_WARPS * 32) norm_bwd_dx_kernel(const T* __restrict__ x, const T* __restrict__ w,
-                                                                       const float* __restrict__ stats,
-                                                                       const T* __restrict__ dy, T* __restrict__ dx,
-                                                                       int64_t N, int C, int kind) {
+template <typename T, int VPT, int WPR>
+__global__ void __launch_bounds__(NR_THREADS) norm_bwd_dx_kernel(const T* __restrict__ x, const T* __restrict__ w,
+                                                                  const float* __restrict__ stats, const T* __restrict__ dy,
+                                                                  T* __restrict__ dx, int64_t N, int C, int kind) {
   constexpr int VN = Vec<T>::N;
-  const int lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * NORM_WARPS + (threadIdx.x >> 5);
-  if (row >= N) return;
-  const float mean = stats[2 * row], rstd = stats[2 * row + 1];
-  // the row of x and dy stays packed in registers (read from HBM once); w is re-read from L1
-  Vec<T> xv[VPL], dv[VPL];
-  float s_g = 0.f, s_gx = 0.f;
+  constexpr int RPC = 8 / WPR;
+  __shared__ float red[2][8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int w_in = warp % WPR;
+  const int64_t row = (int64_t)blockIdx.x * RPC + warp / WPR;
+  const bool active = row < N;
+  float mean = 0.f, rstd = 0.f;
+  if (active) {
+    mean = stats[2 * row];
+    rstd = stats[2 * row + 1];
+  }
+  // x and dy of the row stay packed in registers (read from HBM once); w is re-read from L1/L2
+  Vec<T> xv[VPT], dv[VPT];
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) {
-    const int c = (i * 32 + lane) * VN;
-    if (c < C) {
-      xv[i].load(x + row * C + c);
-      dv[i].load(dy + row * C + c);
+  for (int k = 0; k < VPT; ++k) {
+    const int c = ((k * WPR + w_in) * 32 + lane) * VN;
+    if (active && c < C) {
+      xv[k].load(x + row * C + c);
+      dv[k].load(dy + row * C + c);
     }
   }
+  float s_g = 0.f, s_gx = 0.f;
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) {
-    const int c = (i * 32 + lane) * VN;
-    if (c < C) {
+  for (int k = 0; k < VPT; ++k) {
+    const int c = ((k * WPR + w_in) * 32 + lane) * VN;
+    if (active && c < C) {
       Vec<T> wv;
       wv.load(w + c);
       float xf[VN], g[VN], wf[VN];
-      xv[i].unpack(xf);
-      dv[i].unpack(g);
+      xv[k].unpack(xf);
+      dv[k].unpack(g);
       wv.unpack(wf);
 #pragma unroll
       for (int e = 0; e < VN; ++e) {
@@ -206,18 +236,19 @@ __global__ void __launch_bounds__(NORM_WARPS * 32) norm_bwd_dx_kernel(const T* _
       }
     }
   }
-  s_g = warp_sum(s_g) / (float)C;
-  s_gx = warp_sum(s_gx) / (float)C;
+  s_g = row_reduce<WPR>(s_g, red[0], warp) / (float)C;
+  s_gx = row_reduce<WPR>(s_gx, red[1], warp) / (float)C;
+  if (!active) return;
   const float r3 = rstd * rstd * rstd;
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) {
-    const int c = (i * 32 + lane) * VN;
+  for (int k = 0; k < VPT; ++k) {
+    const int c = ((k * WPR + w_in) * 32 + lane) * VN;
     if (c < C) {
       Vec<T> wv;
       wv.load(w + c);
       float xf[VN], g[VN], wf[VN], o[VN];
-      xv[i].unpack(xf);
-      dv[i].unpack(g);
+      xv[k].unpack(xf);
+      dv[k].unpack(g);
       wv.unpack(wf);
 #pragma unroll
       for (int e = 0; e < VN; ++e) {
@@ -365,27 +396,35 @@ __global__ void __launch_bounds__(256) rope_generic_kernel(T* __restrict__ x, in
 // ------------------------------------------------------------------------------------------------ host launchers
 void colsum_plan(int64_t N, int* chunks, int* rows_per_chunk);
 
+// (VPT, WPR) for a row of nv 128-bit vectors: at most 4 vectors per thread, up to 8 warps per row
+#define SPB_NORM_DISPATCH(nv, CALL) \
+  do {                              \
+    if ((nv) <= 32) CALL(1, 1);     \
+    else if ((nv) <= 64) CALL(2, 1);  \
+    else if ((nv) <= 128) CALL(4, 1); \
+    else if ((nv) <= 256) CALL(4, 2); \
+    else if ((nv) <= 512) CALL(4, 4); \
+    else CALL(4, 8);                \
+  } while (0)
+
 template <typename T>
 static int norm_fwd_launch(const void* x, const void* w, const void* b, void* y, float* stats, int64_t N, int C, float eps,
                            int kind, int upcast, cudaStream_t st) {
   constexpr int VN = Vec<T>::N;
-  const unsigned grid = (unsigned)((N + NORM_WARPS - 1) / NORM_WARPS);
-  const bool vec_ok = (C % VN == 0) && ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0) && ((uintptr_t)w % 16 == 0) &&
-                      (b == nullptr || (uintptr_t)b % 16 == 0);
-  const int vpl = (C + 32 * VN - 1) / (32 * VN);
-#define SPB_NF(V)                                                                                                        \
-  norm_fwd_kernel<T, V><<<grid, NORM_WARPS * 32, 0, st>>>((const T*)x, (const T*)w, (const T*)b, (T*)y, stats, N, C, eps, \
-                                                          kind, upcast)
-  if (vec_ok && vpl <= 1) SPB_NF(1);
-  else if (vec_ok && vpl <= 2) SPB_NF(2);
-  else if (vec_ok && vpl <= 4) SPB_NF(4);
-  else if (vec_ok && vpl <= 8) SPB_NF(8);
-  else if (vec_ok && vpl <= 16) SPB_NF(16);
-  else if (vec_ok && vpl <= 32 && sizeof(T) == 4) { if constexpr (sizeof(T) == 4) SPB_NF(32); }
-  else
+  const bool vec_ok = (C % VN == 0) && (C / VN <= 1024) && ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0) &&
+                      ((uintptr_t)w % 16 == 0) && (b == nullptr || (uintptr_t)b % 16 == 0);
+  if (vec_ok) {
+    const int nv = C / VN;
+#define SPB_NF(V, W)                                                                                                      \
+  norm_fwd_kernel<T, V, W><<<(unsigned)((N + (8 / W) - 1) / (8 / W)), NR_THREADS, 0, st>>>((const T*)x, (const T*)w, (const T*)b, \
+                                                                                           (T*)y, stats, N, C, eps, kind, upcast)
+    SPB_NORM_DISPATCH(nv, SPB_NF);
+#undef SPB_NF
+  } else {
+    const unsigned grid = (unsigned)((N + NORM_WARPS - 1) / NORM_WARPS);
     norm_fwd_generic_kernel<T><<<grid, NORM_WARPS * 32, 0, st>>>((const T*)x, (const T*)w, (const T*)b, (T*)y, stats, N, C,
                                                                  eps, kind, upcast);
-#undef SPB_NF
+  }
   SPB_LAUNCH_CHECK();
   return 0;
 }
@@ -395,21 +434,20 @@ static int norm_bwd_launch(const void* x, const void* w, const float* stats, con
                            void* partial, int64_t N, int C, int kind, cudaStream_t st) {
   constexpr int VN = Vec<T>::N;
   if (dx != nullptr) {
-    const unsigned grid = (unsigned)((N + NORM_WARPS - 1) / NORM_WARPS);
-    const bool vec_ok = (C % VN == 0) && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) && ((uintptr_t)dx % 16 == 0) &&
-                        ((uintptr_t)w % 16 == 0);
-    const int vpl = (C + 32 * VN - 1) / (32 * VN);
-#define SPB_NB(V) \
-  norm_bwd_dx_kernel<T, V><<<grid, NORM_WARPS * 32, 0, st>>>((const T*)x, (const T*)w, stats, (const T*)dy, (T*)dx, N, C, kind)
-    if (vec_ok && vpl <= 1) SPB_NB(1);
-    else if (vec_ok && vpl <= 2) SPB_NB(2);
-    else if (vec_ok && vpl <= 4) SPB_NB(4);
-    else if (vec_ok && vpl <= 8) SPB_NB(8);
-    else if (vec_ok && vpl <= 16) SPB_NB(16);
-    else
+    const bool vec_ok = (C % VN == 0) && (C / VN <= 1024) && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) &&
+                        ((uintptr_t)dx % 16 == 0) && ((uintptr_t)w % 16 == 0);
+    if (vec_ok) {
+      const int nv = C / VN;
+#define SPB_NB(V, W)                                                                                                         \
+  norm_bwd_dx_kernel<T, V, W><<<(unsigned)((N + (8 / W) - 1) / (8 / W)), NR_THREADS, 0, st>>>((const T*)x, (const T*)w, stats, \
+                                                                                              (const T*)dy, (T*)dx, N, C, kind)
+      SPB_NORM_DISPATCH(nv, SPB_NB);
+#undef SPB_NB
+    } else {
+      const unsigned grid = (unsigned)((N + NORM_WARPS - 1) / NORM_WARPS);
       norm_bwd_dx_generic_kernel<T><<<grid, NORM_WARPS * 32, 0, st>>>((const T*)x, (const T*)w, stats, (const T*)dy, (T*)dx,
                                                                       N, C, kind);
-#undef SPB_NB
+    }
     SPB_LAUNCH_CHECK();
   }
   if (dw != nullptr || db != nullptr) {
