@@ -441,27 +441,10 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
   if (g->dbq) { rc = spb_colsum(dt, dqkv, Ntot, N, (int32_t)Nq, g->dbq, partial, stream); if (rc) return rc; }
   if (g->dbk) { rc = spb_colsum(dt, dqkv + Nq * e, Ntot, N, (int32_t)Nkv, g->dbk, partial, stream); if (rc) return rc; }
   if (g->dbv) { rc = spb_colsum(dt, dqkv + (Nq + Nkv) * e, Ntot, N, (int32_t)Nkv, g->dbv, partial, stream); if (rc) return rc; }
-  // 6. d(xhat) = dqkv . Wqkv^T
-  prof_mark("gemm_dx", st);
   const char *wq = (const char*)p->wq, *wk = (const char*)p->wk, *wv = (const char*)p->wv;
   bool packed = p->ldw_q == p->ldw_k && p->ldw_k == p->ldw_v;
   if (in_out) packed = packed && wk == wq + Nq * e && wv == wk + Nkv * e;
   else packed = packed && wk == wq + Nq * p->ldw_q * e && wv == wk + Nkv * p->ldw_q * e;
-  void* dxhat = (d->norm_kind != SPB_NORM_NONE) ? (void*)(w8 + L.dxhat) : g->dx;
-  const int tBx = in_out ? 1 : 0;
-  if (dxhat != nullptr) {
-    if (packed) {
-      rc = spb_gemm(dt, dt, gimpl, N, d->C, Ntot, dqkv, Ntot, 0, wq, p->ldw_q, tBx, dxhat, d->C, nullptr, 0, stream);
-      if (rc) return rc;
-    } else {
-      rc = spb_gemm(dt, dt, gimpl, N, d->C, Nq, dqkv, Ntot, 0, wq, p->ldw_q, tBx, dxhat, d->C, nullptr, 0, stream);
-      if (rc) return rc;
-      rc = spb_gemm(dt, dt, gimpl, N, d->C, Nkv, dqkv + Nq * e, Ntot, 0, wk, p->ldw_k, tBx, dxhat, d->C, nullptr, 1, stream);
-      if (rc) return rc;
-      rc = spb_gemm(dt, dt, gimpl, N, d->C, Nkv, dqkv + (Nq + Nkv) * e, Ntot, 0, wv, p->ldw_v, tBx, dxhat, d->C, nullptr, 1, stream);
-      if (rc) return rc;
-    }
-  }
   // 7. dWq, dWk, dWv
   prof_mark("gemm_dwqkv", st);
   bool gpacked = g->dwq && g->dwk && g->dwv && g->ldw_q == g->ldw_k && g->ldw_k == g->ldw_v;
@@ -485,15 +468,7 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
     rc = dw_gemm(g->dwv, g->ldw_v, dqkv + (Nq + Nkv) * e, Nkv);
     if (rc) return rc;
   }
-  // 8. norm VJP
-  prof_mark("norm_bwd", st);
-  if (d->norm_kind != SPB_NORM_NONE) {
-    rc = spb_norm_bwd(dt, d->norm_kind, d->norm_upcast, x, p->norm_w, (const float*)(w8 + L.stats), w8 + L.dxhat, g->dx, g->dnorm_w,
-                      g->dnorm_b, partial, N, d->C, stream);
-    if (rc) return rc;
-  }
-  // 9. remaining all-reduces, then join the side stream
-  prof_mark("allreduce", st);
+  // data parallelism: the (large) dWqkv all-reduce goes to the side stream and overlaps the dx GEMM and the norm VJP
   if (comm != nullptr) {
     float* ptrs[8];
     size_t counts[8];
@@ -518,6 +493,41 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
     if (g->dbq) { ptrs[n] = g->dbq; counts[n++] = (size_t)Nq; }
     if (g->dbk) { ptrs[n] = g->dbk; counts[n++] = (size_t)Nkv; }
     if (g->dbv) { ptrs[n] = g->dbv; counts[n++] = (size_t)Nkv; }
+    if (n > 0) {
+      rc = comm_allreduce_side(comm, ptrs, counts, n, st);
+      if (rc) return rc;
+    }
+  }
+  // 6. d(xhat) = dqkv . Wqkv^T
+  prof_mark("gemm_dx", st);
+  void* dxhat = (d->norm_kind != SPB_NORM_NONE) ? (void*)(w8 + L.dxhat) : g->dx;
+  const int tBx = in_out ? 1 : 0;
+  if (dxhat != nullptr) {
+    if (packed) {
+      rc = spb_gemm(dt, dt, gimpl, N, d->C, Ntot, dqkv, Ntot, 0, wq, p->ldw_q, tBx, dxhat, d->C, nullptr, 0, stream);
+      if (rc) return rc;
+    } else {
+      rc = spb_gemm(dt, dt, gimpl, N, d->C, Nq, dqkv, Ntot, 0, wq, p->ldw_q, tBx, dxhat, d->C, nullptr, 0, stream);
+      if (rc) return rc;
+      rc = spb_gemm(dt, dt, gimpl, N, d->C, Nkv, dqkv + Nq * e, Ntot, 0, wk, p->ldw_k, tBx, dxhat, d->C, nullptr, 1, stream);
+      if (rc) return rc;
+      rc = spb_gemm(dt, dt, gimpl, N, d->C, Nkv, dqkv + (Nq + Nkv) * e, Ntot, 0, wv, p->ldw_v, tBx, dxhat, d->C, nullptr, 1, stream);
+      if (rc) return rc;
+    }
+  }
+  // 8. norm VJP
+  prof_mark("norm_bwd", st);
+  if (d->norm_kind != SPB_NORM_NONE) {
+    rc = spb_norm_bwd(dt, d->norm_kind, d->norm_upcast, x, p->norm_w, (const float*)(w8 + L.stats), w8 + L.dxhat, g->dx, g->dnorm_w,
+                      g->dnorm_b, partial, N, d->C, stream);
+    if (rc) return rc;
+  }
+  // 9. the small norm gradients on the main stream, then join the side stream
+  prof_mark("allreduce", st);
+  if (comm != nullptr) {
+    float* ptrs[2];
+    size_t counts[2];
+    int n = 0;
     if (g->dnorm_w && d->norm_kind != SPB_NORM_NONE) { ptrs[n] = g->dnorm_w; counts[n++] = (size_t)d->C; }
     if (g->dnorm_b && d->norm_kind == SPB_NORM_LAYER) { ptrs[n] = g->dnorm_b; counts[n++] = (size_t)d->C; }
     rc = comm_allreduce_join(comm, ptrs, counts, n, st);
