@@ -22,12 +22,17 @@
 // back to back while the element-wise groups work on it+1 and the drain group reduces it.
 // CTAs are ordered heaviest first (causal: KV tile 0 sees every Q tile), blockIdx.z = KV tile.
 // Scratch: delta[B,Hq,T] (rowsum(dO*O), prep kernel) and dq_acc[N,Hq*hd] fp32 (zeroed per call, converted at the end).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
 namespace spb {
 
-constexpr int FB_THREADS = 448;  // warp 0 TMA, warp 1 MMA, warps 2-9 two element-wise groups, warps 10-13 dQ-drain group
+constexpr int FB_AGROUPS = 2;                         // element-wise warpgroups; each owns 64 / FB_AGROUPS query columns
+constexpr int FB_ACOLS = 64 / FB_AGROUPS;
+constexpr int FB_ATHREADS = FB_AGROUPS * 128;
+constexpr int FB_THREADS = 64 + FB_ATHREADS + 128;  // warp 0 TMA, warp 1 MMA, element-wise groups, dQ-drain group (last 4 warps)
 constexpr float FB_LOG2E = 1.4426950408889634f;
 
 __device__ __forceinline__ float fb_exp2(float x) {
@@ -45,11 +50,16 @@ struct FaBwdCfg {
   static constexpr int PT_BYTES = 16384;           // 128 kv rows x 64 q columns
   static constexpr int OFF_K = 0;
   static constexpr int OFF_V = OFF_K + K_BYTES;
-  static constexpr int OFF_Q = OFF_V + V_BYTES;    // 2 stages
-  static constexpr int OFF_DO = OFF_Q + 2 * Q_BYTES;
-  static constexpr int OFF_PT = OFF_DO + 2 * Q_BYTES;
-  static constexpr int OFF_DST = OFF_PT + 2 * PT_BYTES;   // P^T and dS^T are double buffered
-  static constexpr int OFF_DQS = OFF_DST + 2 * PT_BYTES;  // fp32 [64 q rows][HD] staging tile for the TMA reduce-add of dQ
+  // Q_i / dO_i ring: a TMA load takes ~1 us from issue to landed data, and a stage is only released when the MMA group of
+  // its iteration has completed, so with 2 stages the ring - not the tensor pipe - set the pace (r01 ablation: 2750 clk per
+  // iteration with all math switched off).  3 stages (4 at hd=64) fit because P^T / dS^T are single buffered: the next
+  // iteration's element-wise phase reaches its shared-memory writes after the current MMA group has drained.
+  static constexpr int NSTAGE = (HD == 128) ? 3 : 4;
+  static constexpr int OFF_Q = OFF_V + V_BYTES;
+  static constexpr int OFF_DO = OFF_Q + NSTAGE * Q_BYTES;
+  static constexpr int OFF_PT = OFF_DO + NSTAGE * Q_BYTES;
+  static constexpr int OFF_DST = OFF_PT + PT_BYTES;
+  static constexpr int OFF_DQS = OFF_DST + PT_BYTES;      // fp32 [64 q rows][HD] staging tile for the TMA reduce-add of dQ
   static constexpr int DQS_BYTES = 64 * HD * 4;
   static constexpr int OFF_LSE = OFF_DQS + DQS_BYTES;     // [2][64] lse*log2e, then [2][64] delta
   static constexpr int OFF_BAR = OFF_LSE + 4 * 64 * 4;
@@ -71,6 +81,8 @@ struct FaBwdArgs {
   int T, Hq, Hkv, causal;
   float scale, scale_log2;
   const float4* rope;  // optional: apply the rotary VJP (M^T) to dK rows in the epilogue (dQ gets it in the convert kernel)
+  int ablate;          // timing experiments only (env SPB_FB_ABLATE, results become wrong): 1 skip dV MMAs, 2 skip dK MMAs,
+                       // 4 skip dQ^T MMAs, 8 skip the dQ smem staging + TMA reduce, 16 skip the dP^T MMAs, 32 skip exp/dS math
 };
 
 template <int HD>
@@ -91,16 +103,17 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
   float* sLse = reinterpret_cast<float*>(smem + Cfg::OFF_LSE);  // [2][64]
   float* sDelta = sLse + 128;                                    // [2][64]
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
-  uint64_t* kv_full = bars;         // [1]
-  uint64_t* qdo_full = bars + 1;    // [2]
-  uint64_t* qdo_empty = bars + 3;   // [2]
-  uint64_t* sdp_full = bars + 5;
-  uint64_t* sdp_empty = bars + 6;
-  uint64_t* pds_full = bars + 7;    // [2]
-  uint64_t* pds_empty = bars + 9;   // [2]
-  uint64_t* dq_full = bars + 11;
-  uint64_t* dq_empty = bars + 12;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  constexpr int NS = Cfg::NSTAGE;
+  uint64_t* kv_full = bars;               // [1]
+  uint64_t* qdo_full = bars + 1;          // [NS]
+  uint64_t* qdo_empty = bars + 1 + NS;    // [NS]
+  uint64_t* sdp_full = bars + 1 + 2 * NS;
+  uint64_t* sdp_empty = sdp_full + 1;
+  uint64_t* pds_full = sdp_full + 2;
+  uint64_t* pds_empty = sdp_full + 3;
+  uint64_t* dq_full = sdp_full + 4;
+  uint64_t* dq_empty = sdp_full + 5;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sdp_full + 6);
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -123,16 +136,14 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
   if (warp == 1) {
     if (lane == 0) {
       mbar_init(kv_full, 1);
-      for (int i = 0; i < 2; ++i) {
+      for (int i = 0; i < NS; ++i) {
         mbar_init(&qdo_full[i], 1);
         mbar_init(&qdo_empty[i], 1);
       }
       mbar_init(sdp_full, 1);
-      mbar_init(sdp_empty, 8);
-      for (int i = 0; i < 2; ++i) {
-        mbar_init(&pds_full[i], 8);
-        mbar_init(&pds_empty[i], 1);
-      }
+      mbar_init(sdp_empty, 4 * FB_AGROUPS);
+      mbar_init(pds_full, 4 * FB_AGROUPS);
+      mbar_init(pds_empty, 1);
       mbar_init(dq_full, 1);
       mbar_init(dq_empty, Cfg::DQ_WARPS);
       fence_barrier_init();
@@ -163,8 +174,8 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         tma_load_2d(sV + c * 16384, &tmV, kv_full, g * HD + c * 64, row_kv);
       }
       for (int it = 0; it < n_it; ++it) {
-        const int st = it & 1;
-        const uint32_t u = (it >> 1) & 1;
+        const int st = it % NS;
+        const uint32_t u = (it / NS) & 1;
         const int h = g * n_rep + it / n_i;
         const int row_q = b * p.T + (i_start + it % n_i) * 64;
         mbar_wait(&qdo_empty[st], u ^ 1);
@@ -186,8 +197,8 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV);
       mbar_wait(kv_full, 0);
       auto issue_s = [&](int it) {
-        const int st = it & 1;
-        mbar_wait(&qdo_full[st], (it >> 1) & 1);
+        const int st = it % NS;
+        mbar_wait(&qdo_full[st], (it / NS) & 1);
         mbar_wait(sdp_empty, (it & 1) ^ 1);
         tc_fence_after();
         const uint32_t q_addr = smem_u32(sQ + st * Cfg::Q_BYTES), do_addr = smem_u32(sDO + st * Cfg::Q_BYTES);
@@ -196,6 +207,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
           const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
           umma_bf16(tmem_base + Cfg::TM_ST, umma_desc_kmajor(k_addr + aoff), umma_desc_kmajor(q_addr + boff), idesc_s, kk > 0 ? 1u : 0u);
         }
+        if (!(p.ablate & 16))
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
           const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
@@ -204,26 +216,29 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         umma_commit(sdp_full);
       };
       auto issue_g = [&](int it) {
-        const int st = it & 1;
-        mbar_wait(&pds_full[st], (it >> 1) & 1);
+        const int st = it % NS;
+        mbar_wait(pds_full, it & 1);
         mbar_wait(dq_empty, (it & 1) ^ 1);
         tc_fence_after();
         const uint32_t q_addr = smem_u32(sQ + st * Cfg::Q_BYTES), do_addr = smem_u32(sDO + st * Cfg::Q_BYTES);
-        const uint32_t pt_addr = smem_u32(sPT + st * Cfg::PT_BYTES), dst_addr = smem_u32(sDST + st * Cfg::PT_BYTES);
+        const uint32_t pt_addr = smem_u32(sPT), dst_addr = smem_u32(sDST);
+        if (!(p.ablate & 1))
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dV += P^T dO
           umma_bf16(tmem_base + Cfg::TM_DV, umma_desc_kmajor(pt_addr + kk * 32), umma_desc_mnmajor(do_addr + kk * 2048, 64), idesc_g,
                     (it > 0 || kk > 0) ? 1u : 0u);
+        if (!(p.ablate & 2))
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dK += dS^T Q
           umma_bf16(tmem_base + Cfg::TM_DK, umma_desc_kmajor(dst_addr + kk * 32), umma_desc_mnmajor(q_addr + kk * 2048, 64), idesc_g,
                     (it > 0 || kk > 0) ? 1u : 0u);
+        if (!(p.ablate & 4))
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)  // dQ^T = K^T dS
           umma_bf16(tmem_base + Cfg::TM_DQT, umma_desc_mnmajor(k_addr + kk * 2048, 128), umma_desc_mnmajor(dst_addr + kk * 2048, 128),
                     idesc_q, kk > 0 ? 1u : 0u);
         umma_commit(&qdo_empty[st]);
-        umma_commit(&pds_empty[st]);
+        umma_commit(pds_empty);
         umma_commit(dq_full);
       };
       issue_s(0);
@@ -233,14 +248,14 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       }
     }
     __syncwarp();
-  } else if (warp < 10) {
-    // ------------------------------------------------------------------ element-wise groups (warps 2..5: q columns 0..31, 6..9: 32..63)
+  } else if (warp < 2 + 4 * FB_AGROUPS) {
+    // ------------------------------------------------------------------ element-wise groups (FB_AGROUPS x 4 warps, FB_ACOLS query columns each)
     const int wg = (warp - 2) >> 2;
     const int qd = warp & 3;
     const int r = qd * 32 + lane;     // kv row = TMEM lane
-    const int ct = threadIdx.x - 64;  // 0..255
+    const int ct = threadIdx.x - 64;  // 0 .. FB_ATHREADS-1
     const int kv_idx = kv0 + r;
-    const int cbase = wg * 32;        // first of this group's 32 query columns
+    const int cbase = wg * FB_ACOLS;  // first of this group's query columns
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
     // lse*log2e / delta of the 64 query rows of an iteration are staged in shared memory (double buffered).  The global
     // loads for iteration it+1 are issued at the top of iteration it and land while it computes (their latency used to
@@ -250,11 +265,10 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       const int h = g * n_rep + it / n_i;
       const int qi = (i_start + it % n_i) * 64 + (ct & 63);
       if (qi >= p.T) return 0.f;
-      const float v = ((ct < 64) ? p.lse : p.delta)[((int64_t)b * p.Hq + h) * p.T + qi];
-      return (ct < 64) ? v * FB_LOG2E : v;
+      return ((ct < 64) ? p.lse : p.delta)[((int64_t)b * p.Hq + h) * p.T + qi];  // consumed in put_stat, a whole iteration later
     };
     auto put_stat = [&](int it, float v) {
-      if (ct < 64) sLse[(it & 1) * 64 + ct] = v;
+      if (ct < 64) sLse[(it & 1) * 64 + ct] = v * FB_LOG2E;
       else if (ct < 128) sDelta[(it & 1) * 64 + (ct - 64)] = v;
     };
     put_stat(0, fetch_stat(0));
@@ -264,13 +278,18 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       const int st = it & 1;
       const int q0 = (i_start + it % n_i) * 64;
       const float stat_next = fetch_stat(it + 1);
-      asm volatile("bar.sync 1, 256;" ::: "memory");  // stage st is complete; stage st^1 is no longer being read
+      asm volatile("bar.sync 1, %0;" ::"n"(FB_ATHREADS) : "memory");  // stage st is complete; stage st^1 is no longer being read
 
       mbar_wait(sdp_full, it & 1);
       tc_fence_after();
-      uint32_t rs[32], rd[32];
-      SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_ST + cbase), rs);
-      SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_DPT + cbase), rd);
+      uint32_t rs[FB_ACOLS], rd[FB_ACOLS];
+      if (FB_ACOLS == 32) {
+        SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_ST + cbase), rs);
+        SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_DPT + cbase), rd);
+      } else {
+        SPB_TMEM_LD_16(lane_base + (uint32_t)(Cfg::TM_ST + cbase), rs);
+        SPB_TMEM_LD_16(lane_base + (uint32_t)(Cfg::TM_DPT + cbase), rd);
+      }
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
@@ -279,9 +298,13 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       const bool need_mask = (p.causal && q0 < kv0 + 128) || (q0 + 64 > p.T) || (kv0 + 128 > p.T);
       const float2* lse2 = reinterpret_cast<const float2*>(sLse + st * 64 + cbase);
       const float2* del2 = reinterpret_cast<const float2*>(sDelta + st * 64 + cbase);
-      uint32_t pkp[16], pkd[16];
+      uint32_t pkp[FB_ACOLS / 2], pkd[FB_ACOLS / 2];
+      if (p.ablate & 32) {
 #pragma unroll
-      for (int i = 0; i < 32; i += 2) {
+        for (int i = 0; i < FB_ACOLS / 2; ++i) pkp[i] = pkd[i] = rs[i] ^ rd[i];
+      } else
+#pragma unroll
+      for (int i = 0; i < FB_ACOLS; i += 2) {
         const float2 l2 = lse2[i >> 1], d2 = del2[i >> 1];
         const float2 x = __ffma2_rn(make_float2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, make_float2(-l2.x, -l2.y));
         float2 pv = make_float2(fb_exp2(x.x), fb_exp2(x.y));
@@ -297,26 +320,26 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         pkd[i >> 1] = pack_bf16(ds.x, ds.y);
       }
       put_stat(it + 1, stat_next);  // visible to everyone after the next iteration's bar.sync
-      mbar_wait(&pds_empty[st], ((it >> 1) & 1) ^ 1);  // MMAs of iteration it-2 have finished reading this P^T / dS^T stage
-      uint8_t* prow = sPT + st * Cfg::PT_BYTES + r * 128;
-      uint8_t* drow = sDST + st * Cfg::PT_BYTES + r * 128;
+      mbar_wait(pds_empty, (it & 1) ^ 1);  // the MMA group of iteration it-1 has finished reading P^T / dS^T
+      uint8_t* prow = sPT + r * 128;
+      uint8_t* drow = sDST + r * 128;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        const int slot = ((wg * 4 + c) ^ (r & 7)) << 4;
+      for (int c = 0; c < FB_ACOLS / 8; ++c) {
+        const int slot = ((wg * (FB_ACOLS / 8) + c) ^ (r & 7)) << 4;
         *reinterpret_cast<uint4*>(prow + slot) = make_uint4(pkp[c * 4], pkp[c * 4 + 1], pkp[c * 4 + 2], pkp[c * 4 + 3]);
         *reinterpret_cast<uint4*>(drow + slot) = make_uint4(pkd[c * 4], pkd[c * 4 + 1], pkd[c * 4 + 2], pkd[c * 4 + 3]);
       }
       fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&pds_full[st]);
+      if (lane == 0) mbar_arrive(pds_full);
     }
     // ---- epilogue: group 0 stores dV, group 1 stores dK (rows -> bf16 -> global).  The last pds_empty commit covers
     // every MMA issued before it.
-    mbar_wait(&pds_empty[(n_it - 1) & 1], ((n_it - 1) >> 1) & 1);
+    mbar_wait(pds_empty, (n_it - 1) & 1);
     tc_fence_after();
-    const bool valid = kv_idx < p.T;
-    const int which = wg;  // 0: dV, 1: dK
+    const bool valid = kv_idx < p.T && wg < 2;
+    const int which = wg & 1;  // group 0: dV, group 1: dK (further groups only wait for completion)
     __nv_bfloat16* orow = (which ? p.dk + ((int64_t)b * p.T + kv_idx) * p.lddk : p.dv + ((int64_t)b * p.T + kv_idx) * p.lddv) + (int64_t)g * HD;
     const int tm = which ? Cfg::TM_DK : Cfg::TM_DV;
 #pragma unroll
@@ -372,6 +395,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         // transpose through shared memory ([q][d] fp32, lanes write consecutive d: conflict-free) and let the TMA engine do
         // ONE bulk reduce-add of the 64 x hd tile into the fp32 dq accumulator (per-thread fp32 atomics were the v2
         // bottleneck: ~1 float atomic / clk / SM).  Rows past the sequence end hold exact zeros (their P^T is masked).
+        if (p.ablate & 8) continue;
         constexpr int NB = Cfg::DQ_WARPS * 32;
         const bool leader = (qd == 0 && lane == 0);
         if (leader && it > 0) tma_store_wait_read<0>();  // previous reduce has finished reading the staging tile
@@ -490,6 +514,10 @@ static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
   a.scale = scale;
   a.scale_log2 = scale * FB_LOG2E;
   a.rope = (const float4*)rope;
+  {
+    const char* ab = getenv("SPB_FB_ABLATE");
+    a.ablate = ab ? atoi(ab) : 0;
+  }
   SPB_CUDA(cudaFuncSetAttribute(flash_bwd_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
   dim3 grid(Hkv, B, (Tn + 127) / 128);
   flash_bwd_tc_kernel<HD><<<grid, FB_THREADS, Cfg::SMEM_BYTES, st>>>(tmK, tmV, tmQ, tmDO, tmDQ, a);
