@@ -66,7 +66,7 @@ typedef struct spb_block_desc {
   int32_t weight_layout;  /* SPB_W_IN_OUT | SPB_W_OUT_IN */
   int32_t qkv_bias;       /* 1: bq,bk,bv present (ViT in_proj_bias) */
   int32_t out_bias;       /* 1: bo present (GPT proj bias, ViT out_proj.bias) */
-  int32_t attn_impl;      /* SPB_IMPL_*: AUTO = tcgen05 flash kernels when dtype==bf16 and hd in {64,128}, else SIMT */
+  int32_t attn_impl;      /* SPB_IMPL_*: AUTO = tcgen05 flash kernels when dtype==bf16 and hd in {64,128,256}, else SIMT */
   int32_t gemm_impl;      /* SPB_IMPL_*: AUTO = tcgen05 GEMM when dtype==bf16, SIMT fp32 GEMM when dtype==f32 */
 } spb_block_desc;
 

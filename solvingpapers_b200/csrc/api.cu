@@ -227,7 +227,7 @@ int spb_flash_fwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t
   cudaStream_t st = (cudaStream_t)stream;
   const int use = pick_attn_impl(impl, dtype, hd);
   if (use == SPB_IMPL_TCGEN05) {
-    SPB_CHECK_ARG(flash_tc_supported(dtype, hd), SPB_E_UNSUPPORTED, "spb_flash_fwd: tcgen05 path needs bf16 and hd in {64,128} (dtype=%d hd=%d)", dtype, hd);
+    SPB_CHECK_ARG(flash_tc_supported(dtype, hd), SPB_E_UNSUPPORTED, "spb_flash_fwd: tcgen05 path needs bf16 and hd in {64,128,256} (dtype=%d hd=%d)", dtype, hd);
     return flash_fwd_tc(B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
   }
   SPB_CHECK_ARG(use == SPB_IMPL_SIMT, SPB_E_INVALID, "spb_flash_fwd: impl %d", impl);
@@ -257,7 +257,7 @@ static int flash_bwd_any(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, 
   cudaStream_t st = (cudaStream_t)stream;
   const int use = pick_attn_bwd_impl(impl, dtype, hd);
   if (use == SPB_IMPL_TCGEN05) {
-    SPB_CHECK_ARG(flash_bwd_tc_supported(dtype, hd), SPB_E_UNSUPPORTED, "spb_flash_bwd: tcgen05 path needs bf16 and hd in {64,128} (dtype=%d hd=%d)", dtype, hd);
+    SPB_CHECK_ARG(flash_bwd_tc_supported(dtype, hd), SPB_E_UNSUPPORTED, "spb_flash_bwd: tcgen05 path needs bf16 and hd in {64,128,256} (dtype=%d hd=%d)", dtype, hd);
     SPB_CHECK_ARG(dq_acc != nullptr, SPB_E_INVALID, "spb_flash_bwd: the tcgen05 path needs the fp32 dq_acc scratch");
     return flash_bwd_tc(B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk, dv,
                         lddv, dq_acc, st, rope);

@@ -44,7 +44,12 @@ __device__ __forceinline__ float fb_exp2(float x) {
 template <int HD>
 struct FaBwdCfg {
   static constexpr int CH = HD / 64;
-  static constexpr int K_BYTES = 2 * 16384;        // always two 64-column chunks: for hd=64 the second one is zeros (M=128 view of K^T)
+  // hd=256: dV + dK alone would fill TMEM, so two CTAs share a KV tile and each owns one 128-column half (z) of the dV, dK
+  // and dQ outputs; both recompute the full S^T / dP^T (contraction over all 256 dims): 7 instead of 5 matmul units.
+  static constexpr int HS = (HD == 256) ? 2 : 1;
+  static constexpr int HDZ = HD / HS;              // output columns per CTA
+  static constexpr int ZCH = HDZ / 64;             // 64-column chunks per output half
+  static constexpr int K_BYTES = (CH < 2 ? 2 : CH) * 16384;  // hd=64: the second chunk is zeros (M=128 view of K^T)
   static constexpr int V_BYTES = CH * 16384;
   static constexpr int Q_BYTES = CH * 8192;        // 64 rows x HD
   static constexpr int PT_BYTES = 16384;           // 128 kv rows x 64 q columns
@@ -54,19 +59,20 @@ struct FaBwdCfg {
   // its iteration has completed, so with 2 stages the ring - not the tensor pipe - set the pace (r01 ablation: 2750 clk per
   // iteration with all math switched off).  3 stages (4 at hd=64) fit because P^T / dS^T are single buffered: the next
   // iteration's element-wise phase reaches its shared-memory writes after the current MMA group has drained.
-  static constexpr int NSTAGE = (HD == 128) ? 3 : 4;
+  static constexpr int NSTAGE = (HD == 128) ? 3 : (HD == 64 ? 4 : 1);  // hd=256: K, V (128 KB) leave room for one 64 KB stage
   static constexpr int OFF_Q = OFF_V + V_BYTES;
   static constexpr int OFF_DO = OFF_Q + NSTAGE * Q_BYTES;
   static constexpr int OFF_PT = OFF_DO + NSTAGE * Q_BYTES;
   static constexpr int OFF_DST = OFF_PT + PT_BYTES;
   static constexpr int OFF_DQS = OFF_DST + PT_BYTES;      // fp32 [64 q rows][HD] staging tile for the TMA reduce-add of dQ
-  static constexpr int DQS_BYTES = 64 * HD * 4;
+  static constexpr bool USE_DQS = (HD != 256);     // hd=256 has no room for the staging tile: coalesced fp32 atomics instead
+  static constexpr int DQS_BYTES = USE_DQS ? 64 * HD * 4 : 0;
   static constexpr int OFF_LSE = OFF_DQS + DQS_BYTES;     // [2][64] lse*log2e, then [2][64] delta
   static constexpr int OFF_BAR = OFF_LSE + 4 * 64 * 4;
   static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
   static constexpr int TM_ST = 0, TM_DPT = 64, TM_DV = 128, TM_DK = 256, TM_DQT = 384;
   static constexpr int TMEM_COLS = 512;
-  static constexpr int DQ_WARPS = HD / 32;         // warps that own a valid hd row of dQ^T
+  static constexpr int DQ_WARPS = HDZ / 32;        // warps that own a valid hd row of dQ^T
 };
 
 struct FaBwdArgs {
@@ -118,7 +124,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
-  const int nt = blockIdx.z, g = blockIdx.x, b = blockIdx.y;  // z is the slowest-varying index: heavy KV tiles are scheduled first
+  const int nt = blockIdx.z, g = blockIdx.x / Cfg::HS, z = blockIdx.x % Cfg::HS, b = blockIdx.y;  // blockIdx.z slowest: heavy KV tiles first
   const int kv0 = nt * 128;
   const int n_rep = p.Hq / p.Hkv;
   const int n_q64 = (p.T + 63) / 64;
@@ -192,7 +198,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
       const uint32_t idesc_s = umma_idesc_bf16(128, 64, 0, 0);
-      const uint32_t idesc_g = umma_idesc_bf16(128, HD, 0, 1);
+      const uint32_t idesc_g = umma_idesc_bf16(128, Cfg::HDZ, 0, 1);
       const uint32_t idesc_q = umma_idesc_bf16(128, 64, 1, 1);
       const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV);
       mbar_wait(kv_full, 0);
@@ -225,17 +231,17 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         if (!(p.ablate & 1))
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dV += P^T dO
-          umma_bf16(tmem_base + Cfg::TM_DV, umma_desc_kmajor(pt_addr + kk * 32), umma_desc_mnmajor(do_addr + kk * 2048, 64), idesc_g,
+          umma_bf16(tmem_base + Cfg::TM_DV, umma_desc_kmajor(pt_addr + kk * 32), umma_desc_mnmajor(do_addr + z * Cfg::ZCH * 8192 + kk * 2048, 64), idesc_g,
                     (it > 0 || kk > 0) ? 1u : 0u);
         if (!(p.ablate & 2))
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dK += dS^T Q
-          umma_bf16(tmem_base + Cfg::TM_DK, umma_desc_kmajor(dst_addr + kk * 32), umma_desc_mnmajor(q_addr + kk * 2048, 64), idesc_g,
+          umma_bf16(tmem_base + Cfg::TM_DK, umma_desc_kmajor(dst_addr + kk * 32), umma_desc_mnmajor(q_addr + z * Cfg::ZCH * 8192 + kk * 2048, 64), idesc_g,
                     (it > 0 || kk > 0) ? 1u : 0u);
         if (!(p.ablate & 4))
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)  // dQ^T = K^T dS
-          umma_bf16(tmem_base + Cfg::TM_DQT, umma_desc_mnmajor(k_addr + kk * 2048, 128), umma_desc_mnmajor(dst_addr + kk * 2048, 128),
+          umma_bf16(tmem_base + Cfg::TM_DQT, umma_desc_mnmajor(k_addr + z * Cfg::ZCH * 16384 + kk * 2048, 128), umma_desc_mnmajor(dst_addr + kk * 2048, 128),
                     idesc_q, kk > 0 ? 1u : 0u);
         umma_commit(&qdo_empty[st]);
         umma_commit(pds_empty);
@@ -243,8 +249,13 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       };
       issue_s(0);
       for (int it = 0; it < n_it; ++it) {
-        if (it + 1 < n_it) issue_s(it + 1);
-        issue_g(it);
+        if (NS >= 2) {  // S^T / dP^T of the next iteration first: the tensor pipe stays busy while the element-wise groups work
+          if (it + 1 < n_it) issue_s(it + 1);
+          issue_g(it);
+        } else {        // single Q/dO stage (hd=256): the stage of iteration it+1 only loads after G(it) has released it
+          issue_g(it);
+          if (it + 1 < n_it) issue_s(it + 1);
+        }
       }
     }
     __syncwarp();
@@ -340,16 +351,16 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
     tc_fence_after();
     const bool valid = kv_idx < p.T && wg < 2;
     const int which = wg & 1;  // group 0: dV, group 1: dK (further groups only wait for completion)
-    __nv_bfloat16* orow = (which ? p.dk + ((int64_t)b * p.T + kv_idx) * p.lddk : p.dv + ((int64_t)b * p.T + kv_idx) * p.lddv) + (int64_t)g * HD;
+    __nv_bfloat16* orow = (which ? p.dk + ((int64_t)b * p.T + kv_idx) * p.lddk : p.dv + ((int64_t)b * p.T + kv_idx) * p.lddv) + (int64_t)g * HD + z * Cfg::HDZ;
     const int tm = which ? Cfg::TM_DK : Cfg::TM_DV;
 #pragma unroll
-    for (int c = 0; c < HD / 32; ++c) {
+    for (int c = 0; c < Cfg::HDZ / 32; ++c) {
       uint32_t o[32];
       SPB_TMEM_LD_32(lane_base + (uint32_t)(tm + c * 32), o);
       tmem_ld_wait();
       if (valid) {
         if (which == 1 && p.rope != nullptr) {  // dK: transpose of the 2x2 rotary block, table row = position kv_idx
-          const float4* tab = p.rope + (int64_t)kv_idx * (HD / 2) + c * 16;
+          const float4* tab = p.rope + (int64_t)kv_idx * (HD / 2) + z * (Cfg::HDZ / 2) + c * 16;
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
             const float4 m = tab[i >> 1];
@@ -396,16 +407,24 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         // ONE bulk reduce-add of the 64 x hd tile into the fp32 dq accumulator (per-thread fp32 atomics were the v2
         // bottleneck: ~1 float atomic / clk / SM).  Rows past the sequence end hold exact zeros (their P^T is masked).
         if (p.ablate & 8) continue;
+        if constexpr (!Cfg::USE_DQS) {
+          // no staging tile at hd=256: thread r adds column z*HDZ + r of 64 query rows; 32 lanes hit 32 consecutive floats
+          float* acc = p.dq_acc + ((int64_t)b * p.T + q0) * p.ld_acc + (int64_t)h * HD + z * Cfg::HDZ + r;
+#pragma unroll
+          for (int i = 0; i < 64; ++i)
+            if (q0 + i < p.T) atomicAdd(acc + (int64_t)i * p.ld_acc, dq[i]);
+          continue;
+        }
         constexpr int NB = Cfg::DQ_WARPS * 32;
         const bool leader = (qd == 0 && lane == 0);
         if (leader && it > 0) tma_store_wait_read<0>();  // previous reduce has finished reading the staging tile
         asm volatile("bar.sync 2, %0;" ::"n"(NB) : "memory");
 #pragma unroll
-        for (int i = 0; i < 64; ++i) sDQ[i * HD + r] = dq[i];
+        for (int i = 0; i < 64; ++i) sDQ[i * Cfg::HDZ + r] = dq[i];
         fence_proxy_async_smem();
         asm volatile("bar.sync 2, %0;" ::"n"(NB) : "memory");
         if (leader) {
-          tma_reduce_add_2d(&tmDQ, sDQ, h * HD, b * p.T + q0);
+          tma_reduce_add_2d(&tmDQ, sDQ, h * HD + z * Cfg::HDZ, b * p.T + q0);
           tma_store_commit();
         }
       }
@@ -472,7 +491,7 @@ __global__ void __launch_bounds__(256) flash_bwd_dq_convert_kernel(const float* 
   *reinterpret_cast<uint4*>(dq + n * lddq + c) = v;
 }
 
-bool flash_bwd_tc_supported(int dtype, int hd) { return dtype == SPB_BF16 && (hd == 64 || hd == 128); }
+bool flash_bwd_tc_supported(int dtype, int hd) { return dtype == SPB_BF16 && (hd == 64 || hd == 128 || hd == 256); }
 
 template <int HD>
 static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float scale, const void* q, int64_t ldq, const void* k,
@@ -497,7 +516,7 @@ static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
   if ((rc = make_tmap_2d(&tmQ, q, 2, (uint64_t)N, (uint64_t)Hq * HD, (uint64_t)ldq, 64, 64, true, false))) return rc;
   if ((rc = make_tmap_2d(&tmDO, d_o, 2, (uint64_t)N, (uint64_t)Hq * HD, (uint64_t)lddo, 64, 64, true, false))) return rc;
   CUtensorMap tmDQ;
-  if ((rc = make_tmap_2d(&tmDQ, dq_acc, 4, (uint64_t)N, (uint64_t)Hq * HD, (uint64_t)ld_acc, 64, HD, false, true))) return rc;
+  if ((rc = make_tmap_2d(&tmDQ, dq_acc, 4, (uint64_t)N, (uint64_t)Hq * HD, (uint64_t)ld_acc, 64, Cfg::HDZ, false, true))) return rc;
   FaBwdArgs a;
   a.lse = lse;
   a.delta = delta;
@@ -519,7 +538,7 @@ static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
     a.ablate = ab ? atoi(ab) : 0;
   }
   SPB_CUDA(cudaFuncSetAttribute(flash_bwd_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-  dim3 grid(Hkv, B, (Tn + 127) / 128);
+  dim3 grid(Hkv * Cfg::HS, B, (Tn + 127) / 128);
   flash_bwd_tc_kernel<HD><<<grid, FB_THREADS, Cfg::SMEM_BYTES, st>>>(tmK, tmV, tmQ, tmDO, tmDQ, a);
   SPB_LAUNCH_CHECK();
   {
@@ -543,6 +562,9 @@ int flash_bwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale
   SPB_CHECK_ARG((uintptr_t)dq_acc % 16 == 0, SPB_E_INVALID, "flash backward (tcgen05): dq_acc must be 16-byte aligned");
   if (hd == 128)
     return flash_bwd_tc_launch<128>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk,
+                                    dv, lddv, dq_acc, st, rope);
+  if (hd == 256)
+    return flash_bwd_tc_launch<256>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk,
                                     dv, lddv, dq_acc, st, rope);
   if (hd == 64)
     return flash_bwd_tc_launch<64>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk, dv,

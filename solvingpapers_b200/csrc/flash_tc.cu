@@ -19,7 +19,6 @@
 
 namespace spb {
 
-constexpr int FA_THREADS = 320;
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 
@@ -31,17 +30,21 @@ __device__ __forceinline__ float fast_exp2(float x) {
 
 template <int HD>
 struct FaFwdCfg {
+  static constexpr int NT = (HD <= 128) ? 2 : 1;    // query tiles per CTA (hd=256: O alone needs 256 TMEM columns -> one tile)
+  static constexpr int KST = (HD <= 128) ? 2 : 1;   // K stages (hd=256: Q, K, V tiles are 64 KB each)
   static constexpr int CH = HD / 64;                // 64-column chunks per Q/K/V tile
   static constexpr int TILE_BYTES = 128 * HD * 2;   // 128 rows x HD bf16
   static constexpr int CHUNK_BYTES = 128 * 128;     // 128 rows x 128 B
   static constexpr int P_BYTES = 128 * 128 * 2;
-  static constexpr int OFF_Q = 0;                       // 2 tiles
-  static constexpr int OFF_K = OFF_Q + 2 * TILE_BYTES;  // 2 stages
-  static constexpr int OFF_V = OFF_K + 2 * TILE_BYTES;  // 1 stage
-  static constexpr int OFF_P = OFF_V + TILE_BYTES;      // 2 tiles
-  static constexpr int OFF_BAR = OFF_P + 2 * P_BYTES;
+  static constexpr int OFF_Q = 0;
+  static constexpr int OFF_K = OFF_Q + NT * TILE_BYTES;
+  static constexpr int OFF_V = OFF_K + KST * TILE_BYTES;  // 1 stage
+  static constexpr int OFF_P = OFF_V + TILE_BYTES;
+  static constexpr int OFF_BAR = OFF_P + NT * P_BYTES;
   static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
   static constexpr int TMEM_COLS = 512;
+  static constexpr int TM_O0 = (NT == 2) ? 256 : 128;     // O_t at TM_O0 + t*128 (NT=2) / one 256-column O at 128 (NT=1)
+  static constexpr int THREADS = 64 + NT * 128;
 };
 
 struct FaFwdArgs {
@@ -53,7 +56,7 @@ struct FaFwdArgs {
 };
 
 template <int HD>
-__global__ void __launch_bounds__(FA_THREADS, 1)
+__global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
     flash_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                         const __grid_constant__ CUtensorMap tmV, const FaFwdArgs p) {
   using Cfg = FaFwdCfg<HD>;
@@ -78,18 +81,19 @@ __global__ void __launch_bounds__(FA_THREADS, 1)
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
+  constexpr int NT = Cfg::NT, KST = Cfg::KST;
   const int n_qp = (int)gridDim.x;
   const int qp = p.causal ? (n_qp - 1 - (int)blockIdx.x) : (int)blockIdx.x;  // heavy (late) causal tiles first
   const int h = blockIdx.y, b = blockIdx.z;
   const int kvh = h / (p.Hq / p.Hkv);
-  const int q0 = qp * 256;
+  const int q0 = qp * (NT * 128);
   const int n_kv_all = (p.T + 127) / 128;
   // per q tile: number of KV tiles it attends to (0 = the tile lies entirely past the end of the sequence)
-  int n_kv_t[2];
+  int n_kv_t[2] = {0, 0};
 #pragma unroll
-  for (int t = 0; t < 2; ++t) {
+  for (int t = 0; t < NT; ++t) {
     const bool live = q0 + t * 128 < p.T;
-    n_kv_t[t] = !live ? 0 : (p.causal ? min(n_kv_all, 2 * qp + t + 1) : n_kv_all);
+    n_kv_t[t] = !live ? 0 : (p.causal ? min(n_kv_all, NT * qp + t + 1) : n_kv_all);
   }
   const int n_kv = max(n_kv_t[0], n_kv_t[1]);
 
@@ -128,7 +132,7 @@ __global__ void __launch_bounds__(FA_THREADS, 1)
       const int n_live = (n_kv_t[0] > 0) + (n_kv_t[1] > 0);
       mbar_arrive_expect_tx(q_full, n_live * Cfg::TILE_BYTES);
 #pragma unroll
-      for (int t = 0; t < 2; ++t) {
+      for (int t = 0; t < NT; ++t) {
         if (n_kv_t[t] > 0) {
 #pragma unroll
           for (int c = 0; c < Cfg::CH; ++c)
@@ -136,9 +140,9 @@ __global__ void __launch_bounds__(FA_THREADS, 1)
         }
       }
       for (int j = 0; j < n_kv; ++j) {
-        const int bf = j & 1;
+        const int bf = j % KST;
         const int row_kv = b * p.T + j * 128;
-        mbar_wait(&k_empty[bf], ((j >> 1) & 1) ^ 1);
+        mbar_wait(&k_empty[bf], ((j / KST) & 1) ^ 1);
         mbar_arrive_expect_tx(&k_full[bf], Cfg::TILE_BYTES);
 #pragma unroll
         for (int c = 0; c < Cfg::CH; ++c)
@@ -162,7 +166,7 @@ __global__ void __launch_bounds__(FA_THREADS, 1)
         mbar_wait(&s_empty[t], (j & 1) ^ 1);  // the softmax group has finished reading S_t of the previous KV tile
         tc_fence_after();
         const uint32_t q_addr = smem_u32(sQ + t * Cfg::TILE_BYTES);
-        const uint32_t k_addr = smem_u32(sK + (j & 1) * Cfg::TILE_BYTES);
+        const uint32_t k_addr = smem_u32(sK + (j % KST) * Cfg::TILE_BYTES);
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
           const uint32_t off = (kk >> 2) * Cfg::CHUNK_BYTES + (kk & 3) * 32;
@@ -178,7 +182,7 @@ __global__ void __launch_bounds__(FA_THREADS, 1)
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           const uint32_t aoff = (kk >> 2) * Cfg::CHUNK_BYTES + (kk & 3) * 32;
-          umma_bf16(tmem_base + 256 + t * 128, umma_desc_kmajor(p_addr + aoff), umma_desc_mnmajor(v_addr + kk * 2048, 128), idesc_pv,
+          umma_bf16(tmem_base + Cfg::TM_O0 + t * 128, umma_desc_kmajor(p_addr + aoff), umma_desc_mnmajor(v_addr + kk * 2048, 128), idesc_pv,
                     (j > 0 || kk > 0) ? 1u : 0u);
         }
         umma_commit(&pv_done[t]);
@@ -187,20 +191,20 @@ __global__ void __launch_bounds__(FA_THREADS, 1)
       // tile's MMAs fill the tensor pipe meanwhile
       mbar_wait(&k_full[0], 0);
       qk_t(0, 0);
-      qk_t(0, 1);
+      if (NT == 2) qk_t(0, 1);
       umma_commit(&k_empty[0]);
       for (int j = 0; j < n_kv; ++j) {
         const bool more = j + 1 < n_kv;
         mbar_wait(v_full, j & 1);
         pv_t(j, 0);
         if (more) {
-          mbar_wait(&k_full[(j + 1) & 1], ((j + 1) >> 1) & 1);
+          mbar_wait(&k_full[(j + 1) % KST], ((j + 1) / KST) & 1);
           qk_t(j + 1, 0);
         }
-        pv_t(j, 1);
+        if (NT == 2) pv_t(j, 1);
         if (more) {
-          qk_t(j + 1, 1);
-          umma_commit(&k_empty[(j + 1) & 1]);
+          if (NT == 2) qk_t(j + 1, 1);
+          umma_commit(&k_empty[(j + 1) % KST]);
         }
         umma_commit(v_empty);
       }
@@ -214,7 +218,7 @@ __global__ void __launch_bounds__(FA_THREADS, 1)
     const int q_idx = q0 + t * 128 + r;
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
     const uint32_t tS = lane_base + (uint32_t)(t * 128);
-    const uint32_t tO = lane_base + (uint32_t)(256 + t * 128);
+    const uint32_t tO = lane_base + (uint32_t)(Cfg::TM_O0 + t * 128);
     const int n_mine = n_kv_t[t];
     float m = -INFINITY, l = 0.f;
     for (int j = 0; j < n_mine; ++j) {
@@ -353,7 +357,7 @@ __global__ void __launch_bounds__(FA_THREADS, 1)
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
 }
 
-bool flash_tc_supported(int dtype, int hd) { return dtype == SPB_BF16 && (hd == 64 || hd == 128); }
+bool flash_tc_supported(int dtype, int hd) { return dtype == SPB_BF16 && (hd == 64 || hd == 128 || hd == 256); }
 
 static int fa_check_operand(const void* ptr, int64_t ld, const char* name) {
   SPB_CHECK_ARG(((uintptr_t)ptr % 16 == 0) && (ld % 8 == 0), SPB_E_UNSUPPORTED,
@@ -382,8 +386,9 @@ static int flash_fwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
   a.causal = causal;
   a.scale_log2 = scale * LOG2E;
   SPB_CUDA(cudaFuncSetAttribute(flash_fwd_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-  dim3 grid((Tn + 255) / 256, Hq, B);
-  flash_fwd_tc_kernel<HD><<<grid, FA_THREADS, Cfg::SMEM_BYTES, st>>>(tmQ, tmK, tmV, a);
+  SPB_CHECK_ARG(scale > 0.f, SPB_E_INVALID, "flash forward (tcgen05): scale must be positive");
+  dim3 grid((Tn + Cfg::NT * 128 - 1) / (Cfg::NT * 128), Hq, B);
+  flash_fwd_tc_kernel<HD><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(tmQ, tmK, tmV, a);
   SPB_LAUNCH_CHECK();
   return 0;
 }
@@ -396,6 +401,7 @@ int flash_fwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale
     return rc;
   if (hd == 128) return flash_fwd_tc_launch<128>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
   if (hd == 64) return flash_fwd_tc_launch<64>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
+  if (hd == 256) return flash_fwd_tc_launch<256>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
   SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "flash forward (tcgen05): hd %d", hd);
 }
 

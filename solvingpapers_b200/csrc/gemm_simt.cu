@@ -10,7 +10,7 @@ constexpr int SG_BM = 64, SG_BN = 64, SG_BK = 16;
 template <typename TI, typename TO>
 __global__ void __launch_bounds__(256) gemm_simt_kernel(int M, int N, int K, const TI* __restrict__ A, int64_t sAm, int64_t sAk,
                                                         const TI* __restrict__ B, int64_t sBk, int64_t sBn, TO* __restrict__ D,
-                                                        int64_t ldd, const TI* __restrict__ bias, int accumulate) {
+                                                        int64_t ldd, const TI* __restrict__ bias, int accumulate, int k_per_split) {
   __shared__ float As[SG_BK][SG_BM + 4];
   __shared__ float Bs[SG_BK][SG_BN + 4];
   const int tid = threadIdx.x;
@@ -22,18 +22,23 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(int M, int N, int K, con
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
 
-  for (int k0 = 0; k0 < K; k0 += SG_BK) {
+  // split-K: blockIdx.z owns [kbeg, kend); with more than one split the partial sums are added atomically into a zeroed
+  // fp32 output (weight gradients of the d=256 models: 256x768 outputs, K = tokens)
+  const int kbeg = blockIdx.z * k_per_split;
+  const int kend = min(K, kbeg + k_per_split);
+  const bool split = gridDim.z > 1;
+  for (int k0 = kbeg; k0 < kend; k0 += SG_BK) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int e = tid + i * 256;
       int m, k;
       if (sAk == 1) { k = e % SG_BK; m = e / SG_BK; } else { m = e % SG_BM; k = e / SG_BM; }
       const int gm = m0 + m, gk = k0 + k;
-      As[k][m] = (gm < M && gk < K) ? to_f32<TI>(A[gm * sAm + gk * sAk]) : 0.f;
+      As[k][m] = (gm < M && gk < kend) ? to_f32<TI>(A[gm * sAm + gk * sAk]) : 0.f;
       int n, kb;
       if (sBk == 1) { kb = e % SG_BK; n = e / SG_BK; } else { n = e % SG_BN; kb = e / SG_BN; }
       const int gn = n0 + n, gkb = k0 + kb;
-      Bs[kb][n] = (gn < N && gkb < K) ? to_f32<TI>(B[gkb * sBk + gn * sBn]) : 0.f;
+      Bs[kb][n] = (gn < N && gkb < kend) ? to_f32<TI>(B[gkb * sBk + gn * sBn]) : 0.f;
     }
     __syncthreads();
 #pragma unroll
@@ -59,8 +64,12 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(int M, int N, int K, con
       const int gn = n0 + tn + j;
       if (gn >= N) continue;
       float v = acc[i][j];
-      if (bias != nullptr) v += to_f32<TI>(bias[gn]);
       TO* p = D + gm * ldd + gn;
+      if (split) {
+        if constexpr (sizeof(TO) == 4) atomicAdd(reinterpret_cast<float*>(p), v);
+        continue;
+      }
+      if (bias != nullptr) v += to_f32<TI>(bias[gn]);
       if (accumulate) v += to_f32<TO>(*p);
       *p = from_f32<TO>(v);
     }
@@ -73,8 +82,21 @@ static int gemm_simt_launch(int64_t M, int64_t N, int64_t K, const void* A, int6
   const int64_t sAm = transA ? 1 : lda, sAk = transA ? lda : 1;
   const int64_t sBk = transB ? 1 : ldb, sBn = transB ? ldb : 1;
   dim3 grid((unsigned)((N + SG_BN - 1) / SG_BN), (unsigned)((M + SG_BM - 1) / SG_BM));
+  int splits = 1;
+  const int64_t tiles = (int64_t)grid.x * grid.y;
+  if (sizeof(TO) == 4 && bias == nullptr && !accumulate && tiles < 2 * sm_count() && K >= 2048) {
+    splits = (int)((2 * sm_count() + tiles - 1) / tiles);
+    const int max_splits = (int)(K / 512);
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+  }
+  int k_per_split = (int)((K + splits - 1) / splits);
+  k_per_split = (k_per_split + SG_BK - 1) / SG_BK * SG_BK;
+  splits = (int)((K + k_per_split - 1) / k_per_split);
+  grid.z = splits;
+  if (splits > 1) SPB_CUDA(cudaMemset2DAsync(D, (size_t)ldd * sizeof(TO), 0, (size_t)N * sizeof(TO), (size_t)M, st));
   gemm_simt_kernel<TI, TO><<<grid, 256, 0, st>>>((int)M, (int)N, (int)K, (const TI*)A, sAm, sAk, (const TI*)B, sBk, sBn, (TO*)D,
-                                                 ldd, (const TI*)bias, accumulate);
+                                                 ldd, (const TI*)bias, accumulate, k_per_split);
   SPB_LAUNCH_CHECK();
   return 0;
 }

@@ -328,6 +328,54 @@ __global__ void __launch_bounds__(256) colsum_partial_kernel(const T* __restrict
   if (MODE == 1) partial[((int64_t)chunks + chunk) * C + c] = s1;
 }
 
+// Vectorised variant: each thread owns Vec<T>::N consecutive columns (one 128-bit load per row and operand).
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256) colsum_partial_vec_kernel(const T* __restrict__ a, int64_t lda, const T* __restrict__ x,
+                                                                 const float* __restrict__ stats, int kind, int64_t N, int C,
+                                                                 int rows_per_chunk, int chunks, float* __restrict__ partial) {
+  constexpr int VN = Vec<T>::N;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) * VN;
+  const int chunk = blockIdx.y;
+  if (c >= C) return;
+  const int64_t r0 = (int64_t)chunk * rows_per_chunk;
+  int64_t r1 = r0 + rows_per_chunk;
+  if (r1 > N) r1 = N;
+  float s0[VN], s1[VN];
+#pragma unroll
+  for (int e = 0; e < VN; ++e) s0[e] = s1[e] = 0.f;
+#pragma unroll 4
+  for (int64_t r = r0; r < r1; ++r) {
+    Vec<T> av;
+    av.load(a + r * lda + c);
+    float af[VN];
+    av.unpack(af);
+    if (MODE == 1) {
+      Vec<T> xv;
+      xv.load(x + r * (int64_t)C + c);
+      float xf[VN];
+      xv.unpack(xf);
+      const float mean = (kind == SPB_NORM_LAYER) ? stats[2 * r] : 0.f;
+      const float rstd = stats[2 * r + 1];
+#pragma unroll
+      for (int e = 0; e < VN; ++e) {
+        s0[e] += af[e] * ((xf[e] - mean) * rstd);
+        s1[e] += af[e];
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < VN; ++e) s0[e] += af[e];
+    }
+  }
+  float* p0 = partial + (int64_t)chunk * C + c;
+#pragma unroll
+  for (int e = 0; e < VN; e += 4) *reinterpret_cast<float4*>(p0 + e) = make_float4(s0[e], s0[e + 1], s0[e + 2], s0[e + 3]);
+  if (MODE == 1) {
+    float* p1 = partial + ((int64_t)chunks + chunk) * C + c;
+#pragma unroll
+    for (int e = 0; e < VN; e += 4) *reinterpret_cast<float4*>(p1 + e) = make_float4(s1[e], s1[e + 1], s1[e + 2], s1[e + 3]);
+  }
+}
+
 __global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restrict__ partial, int chunks, int C,
                                                            float* __restrict__ out0, float* __restrict__ out1) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -454,9 +502,15 @@ static int norm_bwd_launch(const void* x, const void* w, const float* stats, con
     SPB_CHECK_ARG(partial != nullptr, SPB_E_INVALID, "norm_bwd: partial scratch is NULL");
     int chunks, rpc;
     colsum_plan(N, &chunks, &rpc);
-    dim3 grid((C + 255) / 256, chunks);
-    colsum_partial_kernel<T, 1><<<grid, 256, 0, st>>>((const T*)dy, C, (const T*)x, stats, kind, N, C, rpc, chunks,
-                                                      (float*)partial);
+    if (C % VN == 0 && (uintptr_t)dy % 16 == 0 && (uintptr_t)x % 16 == 0 && (uintptr_t)partial % 16 == 0) {
+      dim3 grid((C / VN + 255) / 256, chunks);
+      colsum_partial_vec_kernel<T, 1><<<grid, 256, 0, st>>>((const T*)dy, C, (const T*)x, stats, kind, N, C, rpc, chunks,
+                                                            (float*)partial);
+    } else {
+      dim3 grid((C + 255) / 256, chunks);
+      colsum_partial_kernel<T, 1><<<grid, 256, 0, st>>>((const T*)dy, C, (const T*)x, stats, kind, N, C, rpc, chunks,
+                                                        (float*)partial);
+    }
     SPB_LAUNCH_CHECK();
     colsum_final_kernel<<<(C + 255) / 256, 256, 0, st>>>((const float*)partial, chunks, C, dw, db);
     SPB_LAUNCH_CHECK();
@@ -477,10 +531,16 @@ void colsum_plan(int64_t N, int* chunks, int* rows_per_chunk) {
 
 template <typename T>
 static int colsum_launch(const void* x, int64_t ld, int64_t N, int cols, float* out, void* partial, cudaStream_t st) {
+  constexpr int VN = Vec<T>::N;
   int chunks, rpc;
   colsum_plan(N, &chunks, &rpc);
-  dim3 grid((cols + 255) / 256, chunks);
-  colsum_partial_kernel<T, 0><<<grid, 256, 0, st>>>((const T*)x, ld, nullptr, nullptr, 0, N, cols, rpc, chunks, (float*)partial);
+  if (cols % VN == 0 && ld % VN == 0 && (uintptr_t)x % 16 == 0 && (uintptr_t)partial % 16 == 0) {
+    dim3 grid((cols / VN + 255) / 256, chunks);
+    colsum_partial_vec_kernel<T, 0><<<grid, 256, 0, st>>>((const T*)x, ld, nullptr, nullptr, 0, N, cols, rpc, chunks, (float*)partial);
+  } else {
+    dim3 grid((cols + 255) / 256, chunks);
+    colsum_partial_kernel<T, 0><<<grid, 256, 0, st>>>((const T*)x, ld, nullptr, nullptr, 0, N, cols, rpc, chunks, (float*)partial);
+  }
   SPB_LAUNCH_CHECK();
   colsum_final_kernel<<<(cols + 255) / 256, 256, 0, st>>>((const float*)partial, chunks, cols, out, nullptr);
   SPB_LAUNCH_CHECK();

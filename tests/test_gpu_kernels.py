@@ -247,6 +247,9 @@ def test_attention_simt(dtype, B, T, Hq, Hkv, hd, causal):
     (1, 200, 2, 2, 128, False),   # ragged, hd 128
     (1, 1, 2, 2, 64, True),       # single token
     (1, 130, 2, 1, 64, True),     # just past one tile
+    (2, 256, 1, 1, 256, True),    # GPT notebook geometry: one head of 256 (single-tile forward, hd-split backward)
+    (1, 200, 4, 1, 256, True),    # Gemma-2B-shaped MQA, ragged
+    (1, 128, 2, 2, 256, False),   # hd 256 bidirectional
 ])
 def test_attention_tcgen05_flash(B, T, Hq, Hkv, hd, causal):
     """tcgen05 flash forward + backward (bf16) against the oracle math; bf16-mode tolerance 2e-2."""
@@ -264,6 +267,6 @@ def test_attention_tcgen05_is_deterministic_forward_and_rejects_unsupported():
     assert torch.equal(o1, o2) and torch.equal(l1, l2)
     with pytest.raises(L.SpbError):  # fp32 has no tcgen05 attention: error, not a silent slow path
         ops.flash_fwd(q.float(), q.float(), q.float(), True, 0.1, impl=L.IMPL_TCGEN05)
-    q256 = rnd((1, 64, 1, 256), 4, torch.bfloat16).to(DEV)
-    with pytest.raises(L.SpbError):
-        ops.flash_fwd(q256, q256, q256, True, 0.1, impl=L.IMPL_TCGEN05)
+    q768 = rnd((1, 64, 1, 768), 4, torch.bfloat16).to(DEV)
+    with pytest.raises(L.SpbError):  # hd 768 (Gemma literal) has no tcgen05 tiling: explicit request is an error
+        ops.flash_fwd(q768, q768, q768, True, 0.1, impl=L.IMPL_TCGEN05)

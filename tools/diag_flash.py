@@ -119,8 +119,13 @@ if __name__ == "__main__":
     ok &= case(2, 197, 3, 3, 64, False, bwd)
     ok &= case(1, 200, 2, 2, 128, True, bwd)
     ok &= case(1, 2048, 8, 2, 128, True, bwd)
+    ok &= case(1, 128, 1, 1, 256, False, bwd)
+    ok &= case(2, 384, 2, 1, 256, True, bwd)
+    ok &= case(1, 1024, 4, 1, 256, True, bwd)
     print("ALL OK" if ok else "SOME FAILED")
     if ok:
         timeit(4, 2048, 32, 8, 128, True, bwd)
         timeit(4, 2048, 32, 8, 128, False, bwd)
         timeit(16, 1024, 12, 12, 64, False, bwd)
+        timeit(64, 1024, 1, 1, 256, True, bwd)
+        timeit(4, 4096, 8, 1, 256, True, bwd)
