@@ -438,9 +438,14 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
   if (rc) return rc;
   // 5. qkv bias gradients
   prof_mark("bias_grad", st);
-  if (g->dbq) { rc = spb_colsum(dt, dqkv, Ntot, N, (int32_t)Nq, g->dbq, partial, stream); if (rc) return rc; }
-  if (g->dbk) { rc = spb_colsum(dt, dqkv + Nq * e, Ntot, N, (int32_t)Nkv, g->dbk, partial, stream); if (rc) return rc; }
-  if (g->dbv) { rc = spb_colsum(dt, dqkv + (Nq + Nkv) * e, Ntot, N, (int32_t)Nkv, g->dbv, partial, stream); if (rc) return rc; }
+  if (g->dbq && g->dbk && g->dbv && g->dbk == g->dbq + Nq && g->dbv == g->dbk + Nkv) {  // packed bias gradient: one pass over dqkv
+    rc = spb_colsum(dt, dqkv, Ntot, N, (int32_t)Ntot, g->dbq, partial, stream);
+    if (rc) return rc;
+  } else {
+    if (g->dbq) { rc = spb_colsum(dt, dqkv, Ntot, N, (int32_t)Nq, g->dbq, partial, stream); if (rc) return rc; }
+    if (g->dbk) { rc = spb_colsum(dt, dqkv + Nq * e, Ntot, N, (int32_t)Nkv, g->dbk, partial, stream); if (rc) return rc; }
+    if (g->dbv) { rc = spb_colsum(dt, dqkv + (Nq + Nkv) * e, Ntot, N, (int32_t)Nkv, g->dbv, partial, stream); if (rc) return rc; }
+  }
   const char *wq = (const char*)p->wq, *wk = (const char*)p->wk, *wv = (const char*)p->wv;
   bool packed = p->ldw_q == p->ldw_k && p->ldw_k == p->ldw_v;
   if (in_out) packed = packed && wk == wq + Nq * e && wv == wk + Nkv * e;

@@ -14,6 +14,8 @@
 //   tiles are masked by index (-1e9 additive / -1e4 replacing / -inf masks of the notebooks all give exp()==0 exactly).
 //   GQA: kv head = q head / (Hq/Hkv) is just the TMA column coordinate (llama3:626-627 repeat_kv never materialised).
 // TMEM: S0 [0,128) S1 [128,256) O0 [256,256+hd) O1 [384,384+hd).  Algorithmic FLOPs: 4*B*Hq*T^2*hd*m (m=(T+1)/2T causal).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -28,19 +30,22 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
-template <int HD>
+// PT = true: P (bf16) is written back into tensor memory over the S columns it came from and feeds the PV MMA as a TMEM
+// A operand (no shared-memory round trip, which frees 64 KB for a second V stage).  PT = false keeps P in shared memory.
+template <int HD, bool PT>
 struct FaFwdCfg {
   static constexpr int NT = (HD <= 128) ? 2 : 1;    // query tiles per CTA (hd=256: O alone needs 256 TMEM columns -> one tile)
   static constexpr int KST = (HD <= 128) ? 2 : 1;   // K stages (hd=256: Q, K, V tiles are 64 KB each)
+  static constexpr int VST = (HD <= 128 && PT) ? 2 : 1;
   static constexpr int CH = HD / 64;                // 64-column chunks per Q/K/V tile
   static constexpr int TILE_BYTES = 128 * HD * 2;   // 128 rows x HD bf16
   static constexpr int CHUNK_BYTES = 128 * 128;     // 128 rows x 128 B
   static constexpr int P_BYTES = 128 * 128 * 2;
   static constexpr int OFF_Q = 0;
   static constexpr int OFF_K = OFF_Q + NT * TILE_BYTES;
-  static constexpr int OFF_V = OFF_K + KST * TILE_BYTES;  // 1 stage
-  static constexpr int OFF_P = OFF_V + TILE_BYTES;
-  static constexpr int OFF_BAR = OFF_P + NT * P_BYTES;
+  static constexpr int OFF_V = OFF_K + KST * TILE_BYTES;
+  static constexpr int OFF_P = OFF_V + VST * TILE_BYTES;
+  static constexpr int OFF_BAR = OFF_P + (PT ? 0 : NT * P_BYTES);
   static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
   static constexpr int TMEM_COLS = 512;
   static constexpr int TM_O0 = (NT == 2) ? 256 : 128;     // O_t at TM_O0 + t*128 (NT=2) / one 256-column O at 128 (NT=1)
@@ -55,11 +60,11 @@ struct FaFwdArgs {
   float scale_log2;  // scale * log2(e)
 };
 
-template <int HD>
-__global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
+template <int HD, bool PT>
+__global__ void __launch_bounds__(FaFwdCfg<HD, PT>::THREADS, 1)
     flash_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                         const __grid_constant__ CUtensorMap tmV, const FaFwdArgs p) {
-  using Cfg = FaFwdCfg<HD>;
+  using Cfg = FaFwdCfg<HD, PT>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sQ = smem + Cfg::OFF_Q;
@@ -70,18 +75,18 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
   uint64_t* q_full = bars;            // [1]
   uint64_t* k_full = bars + 1;        // [2] stages
   uint64_t* k_empty = bars + 3;       // [2]
-  uint64_t* v_full = bars + 5;        // [1]
-  uint64_t* v_empty = bars + 6;       // [1]
-  uint64_t* s_full = bars + 7;        // [2] per q tile
-  uint64_t* s_empty = bars + 9;       // [2]
-  uint64_t* p_full = bars + 11;       // [2]
-  uint64_t* pv_done = bars + 13;      // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+  uint64_t* v_full = bars + 5;        // [2] stages
+  uint64_t* v_empty = bars + 7;       // [2]
+  uint64_t* s_full = bars + 9;        // [2] per q tile
+  uint64_t* s_empty = bars + 11;      // [2]
+  uint64_t* p_full = bars + 13;       // [2]
+  uint64_t* pv_done = bars + 15;      // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
-  constexpr int NT = Cfg::NT, KST = Cfg::KST;
+  constexpr int NT = Cfg::NT, KST = Cfg::KST, VST = Cfg::VST;
   const int n_qp = (int)gridDim.x;
   const int qp = p.causal ? (n_qp - 1 - (int)blockIdx.x) : (int)blockIdx.x;  // heavy (late) causal tiles first
   const int h = blockIdx.y, b = blockIdx.z;
@@ -105,9 +110,9 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
   if (warp == 1) {
     if (lane == 0) {
       mbar_init(q_full, 1);
-      mbar_init(v_full, 1);
-      mbar_init(v_empty, 1);
       for (int i = 0; i < 2; ++i) {
+        mbar_init(&v_full[i], 1);
+        mbar_init(&v_empty[i], 1);
         mbar_init(&k_full[i], 1);
         mbar_init(&k_empty[i], 1);
         mbar_init(&s_full[i], 1);
@@ -147,10 +152,12 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
 #pragma unroll
         for (int c = 0; c < Cfg::CH; ++c)
           tma_load_2d(sK + bf * Cfg::TILE_BYTES + c * Cfg::CHUNK_BYTES, &tmK, &k_full[bf], kvh * HD + c * 64, row_kv);
-        mbar_wait(v_empty, (j & 1) ^ 1);
-        mbar_arrive_expect_tx(v_full, Cfg::TILE_BYTES);
+        const int vf = j % VST;
+        mbar_wait(&v_empty[vf], ((j / VST) & 1) ^ 1);
+        mbar_arrive_expect_tx(&v_full[vf], Cfg::TILE_BYTES);
 #pragma unroll
-        for (int c = 0; c < Cfg::CH; ++c) tma_load_2d(sV + c * Cfg::CHUNK_BYTES, &tmV, v_full, kvh * HD + c * 64, row_kv);
+        for (int c = 0; c < Cfg::CH; ++c)
+          tma_load_2d(sV + vf * Cfg::TILE_BYTES + c * Cfg::CHUNK_BYTES, &tmV, &v_full[vf], kvh * HD + c * 64, row_kv);
       }
     }
     __syncwarp();
@@ -160,10 +167,11 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
       const uint32_t idesc_qk = umma_idesc_bf16(128, 128, 0, 0);  // A = Q (K-major), B = K (K-major)
       const uint32_t idesc_pv = umma_idesc_bf16(128, HD, 0, 1);   // A = P (K-major), B = V (MN-major: hd contiguous)
       mbar_wait(q_full, 0);
-      const uint32_t v_addr = smem_u32(sV);
       auto qk_t = [&](int j, int t) {  // S_t = Q_t K(j)^T
         if (j >= n_kv_t[t]) return;
-        mbar_wait(&s_empty[t], (j & 1) ^ 1);  // the softmax group has finished reading S_t of the previous KV tile
+        // S_t is free: PT: PV_t(j-1), issued earlier on this in-order pipe, was the last reader of the P that aliases it;
+        // smem P: the softmax group signalled that it has finished reading S_t of the previous KV tile
+        if (!PT) mbar_wait(&s_empty[t], (j & 1) ^ 1);
         tc_fence_after();
         const uint32_t q_addr = smem_u32(sQ + t * Cfg::TILE_BYTES);
         const uint32_t k_addr = smem_u32(sK + (j % KST) * Cfg::TILE_BYTES);
@@ -178,12 +186,20 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
         if (j >= n_kv_t[t]) return;
         mbar_wait(&p_full[t], j & 1);
         tc_fence_after();
-        const uint32_t p_addr = smem_u32(sP + t * Cfg::P_BYTES);
+        const uint32_t v_addr = smem_u32(sV + (j % VST) * Cfg::TILE_BYTES);
+        if (PT) {
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-          const uint32_t aoff = (kk >> 2) * Cfg::CHUNK_BYTES + (kk & 3) * 32;
-          umma_bf16(tmem_base + Cfg::TM_O0 + t * 128, umma_desc_kmajor(p_addr + aoff), umma_desc_mnmajor(v_addr + kk * 2048, 128), idesc_pv,
-                    (j > 0 || kk > 0) ? 1u : 0u);
+          for (int kk = 0; kk < 8; ++kk)  // A = P_t from tensor memory: 16 bf16 of K per 8 columns
+            umma_bf16_ts(tmem_base + Cfg::TM_O0 + t * 128, tmem_base + t * 128 + kk * 8, umma_desc_mnmajor(v_addr + kk * 2048, 128),
+                         idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+        } else {
+          const uint32_t p_addr = smem_u32(sP + t * Cfg::P_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk) {
+            const uint32_t aoff = (kk >> 2) * Cfg::CHUNK_BYTES + (kk & 3) * 32;
+            umma_bf16(tmem_base + Cfg::TM_O0 + t * 128, umma_desc_kmajor(p_addr + aoff), umma_desc_mnmajor(v_addr + kk * 2048, 128),
+                      idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+          }
         }
         umma_commit(&pv_done[t]);
       };
@@ -195,7 +211,7 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
       umma_commit(&k_empty[0]);
       for (int j = 0; j < n_kv; ++j) {
         const bool more = j + 1 < n_kv;
-        mbar_wait(v_full, j & 1);
+        mbar_wait(&v_full[j % VST], (j / VST) & 1);
         pv_t(j, 0);
         if (more) {
           mbar_wait(&k_full[(j + 1) % KST], ((j + 1) / KST) & 1);
@@ -206,7 +222,7 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
           if (NT == 2) qk_t(j + 1, 1);
           umma_commit(&k_empty[(j + 1) % KST]);
         }
-        umma_commit(v_empty);
+        umma_commit(&v_empty[j % VST]);
       }
     }
     __syncwarp();
@@ -280,7 +296,7 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
         }
       }
       // ---- pass 2: p = exp2(s*c - m) (packed fp32x2 FFMA), row sum, bf16 P into shared memory (UMMA K-major, 128B swizzle)
-      if (j >= 1) mbar_wait(&pv_done[t], (j - 1) & 1);  // PV_t(j-1) has finished reading the P buffer
+      if (!PT && j >= 1) mbar_wait(&pv_done[t], (j - 1) & 1);  // PV_t(j-1) has finished reading the smem P buffer
       uint8_t* prow = sP + t * Cfg::P_BYTES + r * 128;
       const float2 sc2 = make_float2(p.scale_log2, p.scale_log2);
       const float2 nm2 = make_float2(-m, -m);
@@ -309,18 +325,25 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
           pk[i >> 1] = pack_bf16(pa.x, pa.y);
           pk[16 + (i >> 1)] = pack_bf16(pb.x, pb.y);
         }
+        if (PT) {
+          // P words 32*c2 .. 32*c2+31 overwrite S columns this thread has already consumed (S cols 0..63 are in registers
+          // or done when c2 = 0; cols 32..63 were consumed in the c2 = 0 round)
+          SPB_TMEM_ST_32(tS + (uint32_t)(c2 * 32), pk);
+        } else {
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
-          *reinterpret_cast<uint4*>(prow + c2 * Cfg::CHUNK_BYTES + ((u ^ (r & 7)) << 4)) =
-              make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+          for (int u = 0; u < 8; ++u)
+            *reinterpret_cast<uint4*>(prow + c2 * Cfg::CHUNK_BYTES + ((u ^ (r & 7)) << 4)) =
+                make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+        }
       }
+      if (PT) tmem_st_wait();
       const float sum = sum2.x + sum2.y;
       l += sum;
       tc_fence_before();
-      fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
+      if (!PT) fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
       __syncwarp();
       if (lane == 0) {
-        mbar_arrive(&s_empty[t]);  // S_t may be overwritten by QK^T of the next KV tile
+        if (!PT) mbar_arrive(&s_empty[t]);  // S_t may be overwritten by QK^T of the next KV tile
         mbar_arrive(&p_full[t]);
       }
     }
@@ -366,10 +389,10 @@ static int fa_check_operand(const void* ptr, int64_t ld, const char* name) {
   return 0;
 }
 
-template <int HD>
+template <int HD, bool PT>
 static int flash_fwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float scale, const void* q, int64_t ldq, const void* k,
                                int64_t ldk, const void* v, int64_t ldv, void* o, int64_t ldo, float* lse, cudaStream_t st) {
-  using Cfg = FaFwdCfg<HD>;
+  using Cfg = FaFwdCfg<HD, PT>;
   CUtensorMap tmQ, tmK, tmV;
   int rc;
   const uint64_t rows = (uint64_t)B * Tn;
@@ -385,10 +408,10 @@ static int flash_fwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
   a.Hkv = Hkv;
   a.causal = causal;
   a.scale_log2 = scale * LOG2E;
-  SPB_CUDA(cudaFuncSetAttribute(flash_fwd_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+  SPB_CUDA(cudaFuncSetAttribute(flash_fwd_tc_kernel<HD, PT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
   SPB_CHECK_ARG(scale > 0.f, SPB_E_INVALID, "flash forward (tcgen05): scale must be positive");
   dim3 grid((Tn + Cfg::NT * 128 - 1) / (Cfg::NT * 128), Hq, B);
-  flash_fwd_tc_kernel<HD><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(tmQ, tmK, tmV, a);
+  flash_fwd_tc_kernel<HD, PT><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(tmQ, tmK, tmV, a);
   SPB_LAUNCH_CHECK();
   return 0;
 }
@@ -399,9 +422,14 @@ int flash_fwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale
   if ((rc = fa_check_operand(q, ldq, "q")) || (rc = fa_check_operand(k, ldk, "k")) || (rc = fa_check_operand(v, ldv, "v")) ||
       (rc = fa_check_operand(o, ldo, "o")))
     return rc;
-  if (hd == 128) return flash_fwd_tc_launch<128>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
-  if (hd == 64) return flash_fwd_tc_launch<64>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
-  if (hd == 256) return flash_fwd_tc_launch<256>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
+  static const bool p_smem = getenv("SPB_FA_PSMEM") != nullptr;  // A/B switch for timing experiments: keep P in shared memory
+#define SPB_FA_GO(H)                                                                                                         \
+  return p_smem ? flash_fwd_tc_launch<H, false>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st)          \
+                : flash_fwd_tc_launch<H, true>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st)
+  if (hd == 128) SPB_FA_GO(128);
+  if (hd == 64) SPB_FA_GO(64);
+  if (hd == 256) SPB_FA_GO(256);
+#undef SPB_FA_GO
   SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "flash forward (tcgen05): hd %d", hd);
 }
 

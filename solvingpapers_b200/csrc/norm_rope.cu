@@ -328,44 +328,69 @@ __global__ void __launch_bounds__(256) colsum_partial_kernel(const T* __restrict
   if (MODE == 1) partial[((int64_t)chunks + chunk) * C + c] = s1;
 }
 
-// Vectorised variant: each thread owns Vec<T>::N consecutive columns (one 128-bit load per row and operand).
+// Vectorised variant: each thread owns Vec<T>::N consecutive columns (one 128-bit load per row and operand).  The 256
+// threads of a block are arranged as TPR column-threads x 256/TPR row-lanes, so narrow matrices (C = 256: 32 column
+// threads) still keep every thread busy; the row-lanes are combined through shared memory at the end.
 template <typename T, int MODE>
 __global__ void __launch_bounds__(256) colsum_partial_vec_kernel(const T* __restrict__ a, int64_t lda, const T* __restrict__ x,
                                                                  const float* __restrict__ stats, int kind, int64_t N, int C,
-                                                                 int rows_per_chunk, int chunks, float* __restrict__ partial) {
+                                                                 int rows_per_chunk, int chunks, int tpr,
+                                                                 float* __restrict__ partial) {
   constexpr int VN = Vec<T>::N;
-  const int c = (blockIdx.x * blockDim.x + threadIdx.x) * VN;
+  __shared__ float red[(MODE == 1 ? 2 : 1) * 256 * VN];
+  const int tx = threadIdx.x % tpr, ty = threadIdx.x / tpr, rlanes = 256 / tpr;
+  const int c = (blockIdx.x * tpr + tx) * VN;
   const int chunk = blockIdx.y;
-  if (c >= C) return;
+  const bool live = c < C;
   const int64_t r0 = (int64_t)chunk * rows_per_chunk;
   int64_t r1 = r0 + rows_per_chunk;
   if (r1 > N) r1 = N;
   float s0[VN], s1[VN];
 #pragma unroll
   for (int e = 0; e < VN; ++e) s0[e] = s1[e] = 0.f;
-#pragma unroll 4
-  for (int64_t r = r0; r < r1; ++r) {
-    Vec<T> av;
-    av.load(a + r * lda + c);
-    float af[VN];
-    av.unpack(af);
-    if (MODE == 1) {
-      Vec<T> xv;
-      xv.load(x + r * (int64_t)C + c);
-      float xf[VN];
-      xv.unpack(xf);
-      const float mean = (kind == SPB_NORM_LAYER) ? stats[2 * r] : 0.f;
-      const float rstd = stats[2 * r + 1];
+  if (live) {
+#pragma unroll 2
+    for (int64_t r = r0 + ty; r < r1; r += rlanes) {
+      Vec<T> av;
+      av.load(a + r * lda + c);
+      float af[VN];
+      av.unpack(af);
+      if (MODE == 1) {
+        Vec<T> xv;
+        xv.load(x + r * (int64_t)C + c);
+        float xf[VN];
+        xv.unpack(xf);
+        const float mean = (kind == SPB_NORM_LAYER) ? stats[2 * r] : 0.f;
+        const float rstd = stats[2 * r + 1];
 #pragma unroll
-      for (int e = 0; e < VN; ++e) {
-        s0[e] += af[e] * ((xf[e] - mean) * rstd);
-        s1[e] += af[e];
+        for (int e = 0; e < VN; ++e) {
+          s0[e] += af[e] * ((xf[e] - mean) * rstd);
+          s1[e] += af[e];
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < VN; ++e) s0[e] += af[e];
       }
-    } else {
-#pragma unroll
-      for (int e = 0; e < VN; ++e) s0[e] += af[e];
     }
   }
+  if (rlanes > 1) {  // block-uniform
+#pragma unroll
+    for (int e = 0; e < VN; ++e) {
+      red[(e * 256) + threadIdx.x] = s0[e];
+      if (MODE == 1) red[(VN + e) * 256 + threadIdx.x] = s1[e];
+    }
+    __syncthreads();
+    if (ty == 0) {
+      for (int l = 1; l < rlanes; ++l) {
+#pragma unroll
+        for (int e = 0; e < VN; ++e) {
+          s0[e] += red[(e * 256) + l * tpr + tx];
+          if (MODE == 1) s1[e] += red[(VN + e) * 256 + l * tpr + tx];
+        }
+      }
+    }
+  }
+  if (!live || ty != 0) return;
   float* p0 = partial + (int64_t)chunk * C + c;
 #pragma unroll
   for (int e = 0; e < VN; e += 4) *reinterpret_cast<float4*>(p0 + e) = make_float4(s0[e], s0[e + 1], s0[e + 2], s0[e + 3]);
@@ -374,6 +399,13 @@ __global__ void __launch_bounds__(256) colsum_partial_vec_kernel(const T* __rest
 #pragma unroll
     for (int e = 0; e < VN; e += 4) *reinterpret_cast<float4*>(p1 + e) = make_float4(s1[e], s1[e + 1], s1[e + 2], s1[e + 3]);
   }
+}
+
+// column threads per block for a matrix of nvec 128-bit column vectors: power of two in [8, 256]
+static int colsum_tpr(int nvec) {
+  int t = 8;
+  while (t < 256 && t < nvec) t <<= 1;
+  return t;
 }
 
 __global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restrict__ partial, int chunks, int C,
@@ -503,8 +535,9 @@ static int norm_bwd_launch(const void* x, const void* w, const float* stats, con
     int chunks, rpc;
     colsum_plan(N, &chunks, &rpc);
     if (C % VN == 0 && (uintptr_t)dy % 16 == 0 && (uintptr_t)x % 16 == 0 && (uintptr_t)partial % 16 == 0) {
-      dim3 grid((C / VN + 255) / 256, chunks);
-      colsum_partial_vec_kernel<T, 1><<<grid, 256, 0, st>>>((const T*)dy, C, (const T*)x, stats, kind, N, C, rpc, chunks,
+      const int tpr = colsum_tpr(C / VN);
+      dim3 grid((C / VN + tpr - 1) / tpr, chunks);
+      colsum_partial_vec_kernel<T, 1><<<grid, 256, 0, st>>>((const T*)dy, C, (const T*)x, stats, kind, N, C, rpc, chunks, tpr,
                                                             (float*)partial);
     } else {
       dim3 grid((C + 255) / 256, chunks);
@@ -535,8 +568,10 @@ static int colsum_launch(const void* x, int64_t ld, int64_t N, int cols, float* 
   int chunks, rpc;
   colsum_plan(N, &chunks, &rpc);
   if (cols % VN == 0 && ld % VN == 0 && (uintptr_t)x % 16 == 0 && (uintptr_t)partial % 16 == 0) {
-    dim3 grid((cols / VN + 255) / 256, chunks);
-    colsum_partial_vec_kernel<T, 0><<<grid, 256, 0, st>>>((const T*)x, ld, nullptr, nullptr, 0, N, cols, rpc, chunks, (float*)partial);
+    const int tpr = colsum_tpr(cols / VN);
+    dim3 grid((cols / VN + tpr - 1) / tpr, chunks);
+    colsum_partial_vec_kernel<T, 0><<<grid, 256, 0, st>>>((const T*)x, ld, nullptr, nullptr, 0, N, cols, rpc, chunks, tpr,
+                                                          (float*)partial);
   } else {
     dim3 grid((cols + 255) / 256, chunks);
     colsum_partial_kernel<T, 0><<<grid, 256, 0, st>>>((const T*)x, ld, nullptr, nullptr, 0, N, cols, rpc, chunks, (float*)partial);
