@@ -11,6 +11,8 @@
 //   * split-K (fp32 atomic accumulate into a zeroed output) when a weight-gradient GEMM has fewer tiles than SMs
 //     (d=256 models: dW is 2x3 tiles with K = 65536 tokens).
 // Roofline: tensor pipe. Algorithmic FLOPs 2*M*N*K.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace spb {
@@ -113,9 +115,7 @@ __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row
   if (p.out_f32) {
     float* d = reinterpret_cast<float*>(p.D) + (int64_t)row * p.ldd + col0;
     if (atomic) {
-#pragma unroll
-      for (int i = 0; i < 32; ++i)
-        if (i < ncol) atomicAdd(d + i, v[i]);
+      // handled by gemm_tc_atomic_chunk (warp-cooperative, coalesced); never reached
     } else if (p.vec_ok && ncol == 32) {
 #pragma unroll
       for (int i = 0; i < 32; i += 4) {
@@ -155,6 +155,63 @@ __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row
         if (i < ncol) d[i] = __float2bfloat16_rn(p.accumulate ? __bfloat162float(d[i]) + v[i] : v[i]);
     }
   }
+}
+
+// K-split tail tiles: the warp's 32x32 fp32 chunk is transposed through shared memory (pitch 33: conflict-free) so that
+// each atomic instruction adds 32 consecutive floats of ONE output row - a single coalesced 128-byte reduction - instead
+// of 32 scattered 4-byte atomics (row-per-thread), which cost more than the split saved (r01d).
+__device__ __forceinline__ void gemm_tc_atomic_chunk(const GemmTcArgs& p, int row0, int col0, const uint32_t* r, float* wbuf, int lane) {
+  __syncwarp();
+#pragma unroll
+  for (int i = 0; i < 32; ++i) wbuf[lane * 33 + i] = __uint_as_float(r[i]);
+  __syncwarp();
+  const int col = col0 + lane;
+  if (col < p.N) {
+    float* d = reinterpret_cast<float*>(p.D) + (int64_t)row0 * p.ldd + col;
+#pragma unroll 4
+    for (int rr = 0; rr < 32; ++rr)
+      if (row0 + rr < p.M) atomicAdd(d + (int64_t)rr * p.ldd, wbuf[rr * 33 + lane]);
+  }
+}
+
+// Drain one 128 x NCOLS fp32 accumulator (this warp: TMEM lanes q*32 .. q*32+31 = tile rows) through the epilogue.
+// m0 = first output row of the CTA's 128-row slab, n0 = first output column; warp_buf = this warp's 8 KB staging buffer.
+template <int NCOLS>
+__device__ __forceinline__ void gemm_tc_drain(const GemmTcArgs& p, int atomic, int m0, int n0, uint32_t taddr, uint8_t* warp_buf, int q,
+                                              int lane) {
+  const int row = m0 + q * 32 + lane;
+#pragma unroll 1
+      for (int c = 0; c < NCOLS / 32; ++c) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= p.N) break;  // warp-uniform
+        uint32_t r[32];
+        SPB_TMEM_LD_32(taddr + (uint32_t)(c * 32), r);
+        const uint8_t* rope_row = nullptr;
+        if (p.rope != nullptr && col0 < p.rope_cols) {  // warp-uniform
+          // stage table[t(row)][pair0 .. pair0+15] for the warp's 32 rows: 2 rows (2 x 256 B) per load instruction
+          uint8_t* wbuf = warp_buf;
+          const int pair0 = (col0 % p.rope_hd) >> 1;
+          const int half = lane >> 4, l16 = lane & 15;
+          // phase 1: all 16 coalesced global loads in flight (the table is L2 resident); phase 2: swizzled smem stores
+          float4 tm[16];
+          const bool pair_ok = pair0 + l16 < (p.rope_hd >> 1);
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            const int grow = m0 + q * 32 + 2 * k + half;
+            tm[k] = make_float4(1.f, 0.f, 0.f, 1.f);
+            if (grow < p.M && pair_ok) tm[k] = __ldg(p.rope + (int64_t)(grow % p.rope_T) * (p.rope_hd >> 1) + pair0 + l16);
+          }
+          __syncwarp();  // previous chunk's readers are done with the buffer
+#pragma unroll
+          for (int k = 0; k < 16; ++k)
+            *reinterpret_cast<float4*>(wbuf + (((l16 << 5) + ((2 * k + half) ^ l16)) << 4)) = tm[k];
+          __syncwarp();
+          rope_row = wbuf;
+        }
+        tmem_ld_wait();
+        if (atomic) gemm_tc_atomic_chunk(p, m0 + q * 32, col0, r, reinterpret_cast<float*>(warp_buf), lane);
+        else if (row < p.M) gemm_tc_store_chunk(p, row, col0, r, rope_row, lane, 0);
+      }
 }
 
 template <int BN>
@@ -274,39 +331,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
       const int m0 = wi.m0, n0 = wi.n0;
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
-      const int row = m0 + q * 32 + lane;
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        const int col0 = n0 + c * 32;
-        if (col0 >= p.N) break;  // warp-uniform
-        uint32_t r[32];
-        SPB_TMEM_LD_32(taddr + (uint32_t)(c * 32), r);
-        const uint8_t* rope_row = nullptr;
-        if (p.rope != nullptr && col0 < p.rope_cols) {  // warp-uniform
-          // stage table[t(row)][pair0 .. pair0+15] for the warp's 32 rows: 2 rows (2 x 256 B) per load instruction
-          uint8_t* wbuf = sRope + (warp - 2) * Cfg::ROPE_WARP_BYTES;
-          const int pair0 = (col0 % p.rope_hd) >> 1;
-          const int half = lane >> 4, l16 = lane & 15;
-          // phase 1: all 16 coalesced global loads in flight (the table is L2 resident); phase 2: swizzled smem stores
-          float4 tm[16];
-          const bool pair_ok = pair0 + l16 < (p.rope_hd >> 1);
-#pragma unroll
-          for (int k = 0; k < 16; ++k) {
-            const int grow = m0 + q * 32 + 2 * k + half;
-            tm[k] = make_float4(1.f, 0.f, 0.f, 1.f);
-            if (grow < p.M && pair_ok) tm[k] = __ldg(p.rope + (int64_t)(grow % p.rope_T) * (p.rope_hd >> 1) + pair0 + l16);
-          }
-          __syncwarp();  // previous chunk's readers are done with the buffer
-#pragma unroll
-          for (int k = 0; k < 16; ++k)
-            *reinterpret_cast<float4*>(wbuf + (((l16 << 5) + ((2 * k + half) ^ l16)) << 4)) = tm[k];
-          __syncwarp();
-          rope_row = wbuf;
-        }
-        tmem_ld_wait();
-        if (row < p.M) gemm_tc_store_chunk(p, row, col0, r, rope_row, lane, wi.atomic);
-      }
+      gemm_tc_drain<BN>(p, wi.atomic, m0, n0, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN), sRope + (warp - 2) * Cfg::ROPE_WARP_BYTES, q, lane);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[acc]);
@@ -320,14 +345,248 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
 }
 
+template <int BN, int BMT>
+__global__ void gemm_tc_zero_tail_kernel(const GemmTcArgs p);
+
+// ------------------------------------------------------------------------------------------------ CTA-pair variant
+// 256 x 256 output tile per pair of CTAs (cluster (2,1,1), tcgen05 cta_group::2): each CTA stages its own 128 rows of A and
+// only HALF of B (128 of the 256 N rows) per k-block - 32 KB instead of 48 KB per 128 x 256 x 64 MACs - which cuts the
+// shared-memory fill traffic and the L2->SM bytes per FLOP by a third and leaves room for 6 pipeline stages.  The leader
+// CTA (rank 0) issues every MMA for the pair; commits are multicast to both CTAs' barriers; each CTA drains its own
+// 128 x 256 TMEM accumulator.  Full-K tiles only (no K-split), BN = 256.
+struct GemmTc2Cfg {
+  static constexpr int BN = 256;
+  static constexpr int STAGES = 6;
+  static constexpr int A_BYTES = GT_BM * GT_BK * 2;        // this CTA's 128 rows
+  static constexpr int B_BYTES = (BN / 2) * GT_BK * 2;     // this CTA's half of the N rows
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;    // per CTA
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int ROPE_WARP_BYTES = 32 * 16 * 16;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 4 * ROPE_WARP_BYTES + 1024;
+  static constexpr int TMEM_COLS = 512;
+};
+
+// work item -> (tile, k-block range, atomic): whole waves run full-K tiles, the tail wave's tiles are split along K
+__device__ __forceinline__ void gemm_tc2_item(const GemmTcArgs& p, int item, int& tile, int& kb0, int& kb1, int& atomic) {
+  tile = item;
+  kb0 = 0;
+  kb1 = p.kb_total;
+  atomic = 0;
+  if (item >= p.full_tiles) {
+    const int j = item - p.full_tiles;
+    tile = p.full_tiles + j / p.tail_parts;
+    kb0 = (j % p.tail_parts) * p.kb_per_part;
+    kb1 = min(kb0 + p.kb_per_part, p.kb_total);
+    atomic = p.tail_parts > 1;
+  }
+}
+
+__global__ void __launch_bounds__(GT_THREADS, 1)
+    gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmTcArgs p) {
+  using Cfg = GemmTc2Cfg;
+  constexpr int BN = Cfg::BN;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + Cfg::STAGES * Cfg::A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+  uint64_t* empty = full + Cfg::STAGES;
+  uint64_t* tfull = empty + Cfg::STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint8_t* sRope = smem + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BAR_BYTES;
+
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < Cfg::STAGES; ++s) {
+        mbar_init(&full[s], 2);   // leader: its own expect_tx arrive + the peer's remote arrive
+        mbar_init(&empty[s], 1);  // multicast commit from the leader's MMA thread
+      }
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(&tfull[a], 1);
+        mbar_init(&tempty[a], 8);  // leader: 4 epilogue warps of each CTA
+      }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc_2sm(tmem_slot, Cfg::TMEM_COLS);
+    tmem_relinquish_2sm();
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_items = p.total_items;  // 256 x 256 tiles
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer (both CTAs, own halves)
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = pair; item < total_items; item += npairs) {
+        int tile, kb0, kb1, atomic, m_blk, n_blk;
+        gemm_tc2_item(p, item, tile, kb0, kb1, atomic);
+        gemm_tc_tile_coords(p, tile, m_blk, n_blk);
+        const int m0 = m_blk * 256 + (int)rank * 128, n0 = n_blk * BN + (int)rank * (BN / 2);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * Cfg::STAGE_BYTES);
+          else mbar_arrive_remote(&full[stage], 0);
+          uint8_t* a = sA + stage * Cfg::A_BYTES;
+          uint8_t* b = sB + stage * Cfg::B_BYTES;
+          if (!p.a_mn) {
+            tma_load_2d_2sm(a, &tmA, &full[stage], kb * GT_BK, m0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < 2; ++c) tma_load_2d_2sm(a + c * (GT_BK * 128), &tmA, &full[stage], m0 + c * 64, kb * GT_BK);
+          }
+          if (!p.b_mn) {
+            tma_load_2d_2sm(b, &tmB, &full[stage], kb * GT_BK, n0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < 2; ++c) tma_load_2d_2sm(b + c * (GT_BK * 128), &tmB, &full[stage], n0 + c * 64, kb * GT_BK);
+          }
+          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (leader CTA only)
+    if (lane == 0 && rank == 0) {
+      const uint32_t idesc = umma_idesc_bf16(256, BN, p.a_mn, p.b_mn);
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int item = pair; item < total_items; item += npairs) {
+        int tile, kb0, kb1, atomic;
+        gemm_tc2_item(p, item, tile, kb0, kb1, atomic);
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(sA + stage * Cfg::A_BYTES);
+          const uint32_t b_addr = smem_u32(sB + stage * Cfg::B_BYTES);
+#pragma unroll
+          for (int k = 0; k < GT_BK / 16; ++k) {
+            const uint64_t adesc = p.a_mn ? umma_desc_mnmajor(a_addr + k * 2048, GT_BK) : umma_desc_kmajor(a_addr + k * 32);
+            const uint64_t bdesc = p.b_mn ? umma_desc_mnmajor(b_addr + k * 2048, GT_BK) : umma_desc_kmajor(b_addr + k * 32);
+            umma_bf16_2sm(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit_2sm_mc(&empty[stage], 3);  // frees the slot in BOTH CTAs
+          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_2sm_mc(&tfull[acc], 3);  // accumulators complete -> both epilogues
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------------ epilogue: each CTA drains its own 128 x 256 accumulator
+    const int q = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int item = pair; item < total_items; item += npairs) {
+      int tile, kb0, kb1, atomic, m_blk, n_blk;
+      gemm_tc2_item(p, item, tile, kb0, kb1, atomic);
+      gemm_tc_tile_coords(p, tile, m_blk, n_blk);
+      const int m0 = m_blk * 256 + (int)rank * 128, n0 = n_blk * BN;
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      gemm_tc_drain<BN>(p, atomic, m0, n0, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN), sRope + (warp - 2) * Cfg::ROPE_WARP_BYTES,
+                        q, lane);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (rank == 0) mbar_arrive(&tempty[acc]);
+        else mbar_arrive_remote(&tempty[acc], 0);
+      }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) tmem_dealloc_2sm(tmem_base, Cfg::TMEM_COLS);
+}
+
+static int gemm_tc2_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int64_t K, GemmTcArgs args, bool may_split,
+                           cudaStream_t st) {
+  using Cfg = GemmTc2Cfg;
+  const int G = sm_count();
+  args.num_m = (args.M + 255) / 256;          // 256-row tiles
+  args.num_n = (args.N + Cfg::BN - 1) / Cfg::BN;
+  const int tiles = args.num_m * args.num_n;
+  int pairs = G / 2;
+  if (pairs > tiles) pairs = tiles;
+  args.full_tiles = tiles;
+  args.tail_parts = 1;
+  args.kb_per_part = args.kb_total;
+  if (may_split) {  // fp32 weight gradients: split the tail wave's tiles along K (coalesced fp32 atomics into zeroed tiles)
+    const int full = (tiles / pairs) * pairs, R = tiles - full;
+    if (R > 0 && R * 2 <= pairs && args.kb_total >= 16) {
+      int parts = pairs / R;
+      const int max_parts = args.kb_total / 8;
+      if (parts > max_parts) parts = max_parts;
+      if (parts > 1) {
+        args.kb_per_part = (args.kb_total + parts - 1) / parts;
+        args.tail_parts = (args.kb_total + args.kb_per_part - 1) / args.kb_per_part;
+        args.full_tiles = full;
+      }
+    }
+  }
+  args.total_items = args.full_tiles + (tiles - args.full_tiles) * args.tail_parts;
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!args.a_mn) rc = make_tmap_2d(&tmA, A, 2, (uint64_t)args.M, (uint64_t)K, (uint64_t)lda, GT_BM, GT_BK, true, false);
+  else rc = make_tmap_2d(&tmA, A, 2, (uint64_t)K, (uint64_t)args.M, (uint64_t)lda, GT_BK, 64, true, false);
+  if (rc) return rc;
+  if (!args.b_mn) rc = make_tmap_2d(&tmB, B, 2, (uint64_t)args.N, (uint64_t)K, (uint64_t)ldb, Cfg::BN / 2, GT_BK, true, false);
+  else rc = make_tmap_2d(&tmB, B, 2, (uint64_t)K, (uint64_t)args.N, (uint64_t)ldb, GT_BK, 64, true, false);
+  if (rc) return rc;
+  if (args.tail_parts > 1) {
+    gemm_tc_zero_tail_kernel<Cfg::BN, 256><<<tiles - args.full_tiles, 256, 0, st>>>(args);
+    SPB_LAUNCH_CHECK();
+  }
+  SPB_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(GT_THREADS);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  SPB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc2_kernel, tmA, tmB, args));
+  SPB_LAUNCH_CHECK();
+  return 0;
+}
+
 // zero the tail tiles that will be accumulated with atomics (one CTA per tail tile)
-template <int BN>
+template <int BN, int BMT = GT_BM>
 __global__ void __launch_bounds__(256) gemm_tc_zero_tail_kernel(const GemmTcArgs p) {
   int m_blk, n_blk;
   gemm_tc_tile_coords(p, p.full_tiles + (int)blockIdx.x, m_blk, n_blk);
   float* d = reinterpret_cast<float*>(p.D);
-  const int m0 = m_blk * GT_BM, n0 = n_blk * BN;
-  for (int e = threadIdx.x; e < GT_BM * BN; e += 256) {
+  const int m0 = m_blk * BMT, n0 = n_blk * BN;
+  for (int e = threadIdx.x; e < BMT * BN; e += 256) {
     const int r = m0 + e / BN, c = n0 + e % BN;
     if (r < p.M && c < p.N) d[(int64_t)r * p.ldd + c] = 0.f;
   }
@@ -345,9 +604,7 @@ static int gemm_tc_launch(const void* A, int64_t lda, const void* B, int64_t ldb
   args.kb_per_part = args.kb_total;
   if (may_split) {
     const int full = (tiles / G) * G, R = tiles - full;
-    // measured (r01d): with row-per-thread fp32 atomics the K-split of a tail wave costs more than it saves on 768-tile
-    // problems, so it is used only when the whole problem is a partial wave (few-tile weight gradients, d=256 models)
-    if (full == 0 && R > 0 && R * 2 <= G && args.kb_total >= 16) {
+    if (R > 0 && R * 2 <= G && args.kb_total >= 16) {
       int parts = G / R;
       const int max_parts = args.kb_total / 8;  // at least 8 k-blocks (512 k) per part
       if (parts > max_parts) parts = max_parts;
@@ -426,6 +683,10 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
     // efficiency (lower arithmetic intensity per smem byte), so it is only taken for a much larger gain
     if (gemm_tc_wave_eff(M, N, 192, G) > gemm_tc_wave_eff(M, N, 256, G) + 0.15) BN = 192;
   }
+  // CTA-pair kernel: large problems with at least one 256 x 256 tile per pair (SPB_GEMM_2CTA=0 forces the single-CTA kernel)
+  static const int use_pair = [] { const char* e = getenv("SPB_GEMM_2CTA"); return e ? atoi(e) : 1; }();
+  if (use_pair && BN == 256 && M >= 256 && N >= 256 && ((M + 255) / 256) * ((N + 255) / 256) >= sm_count() / 2)
+    return gemm_tc2_launch(A, lda, B, ldb, K, args, may_split, st);
   if (BN == 256) return gemm_tc_launch<256>(A, lda, B, ldb, K, args, may_split, st);
   if (BN == 192) return gemm_tc_launch<192>(A, lda, B, ldb, K, args, may_split, st);
   return gemm_tc_launch<128>(A, lda, B, ldb, K, args, may_split, st);

@@ -46,5 +46,10 @@ if __name__ == "__main__":
     for (tA, tB) in ((False, True), (False, False), (True, True), (True, False)):
         for (M, N, K) in ((128, 128, 16), (128, 128, 64), (128, 256, 64), (128, 256, 256), (256, 512, 512)):
             case(M, N, K, tA, tB)
+    # big enough for the CTA-pair kernel (>= 74 tiles of 256x256), all majors, ragged edges, fp32 out
+    for (tA, tB) in ((False, True), (False, False), (True, True), (True, False)):
+        case(2560, 2048, 512, tA, tB)
+    case(2504, 1992, 520, False, True)
+    case(2504, 1992, 520, True, False, torch.float32)
     case(256, 768, 16384, True, False, torch.float32)
     case(4096, 6144, 4096, False, False)
