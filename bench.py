@@ -386,11 +386,25 @@ def run_ours(args):
     N = B * T
     f_gemm = 3.0 * (2.0 * N * Cm * cfg.n_tot + 2.0 * N * cfg.n_q * Cm)
     gemm_ms = sum(stage_ms.get(s, 0.0) for s in GEMM_STAGES)
+    e_, nt_, nq_ = x.element_size(), cfg.n_tot, cfg.n_q
+    gemm_bytes = ((N * Cm + Cm * nt_ + N * nt_) * e_ + (N * nq_ + nq_ * Cm + N * Cm) * e_ + (N * Cm + nq_ * Cm + N * nq_) * e_ +
+                  (N * nq_ + N * Cm) * e_ + nq_ * Cm * 4 + (N * nt_ + Cm * nt_ + N * Cm) * e_ + (N * Cm + N * nt_) * e_ + Cm * nt_ * 4)  # A+B+D of the 6 GEMMs
     n_gemm = 6
     total_flops = cfg.flops_fwd_bwd()
-    roof = {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05, all 6 GEMM stages of a step)" if dt == "bf16" else "gemm_simt_kernel (fp32 FFMA)",
+    # traffic: DRAM bytes per launch of the dominant kernel from the committed ncu --set full summary (tools/ncu_summary.py)
+    traffic = None
+    try:
+        summ = json.load(open(os.path.join(ROOT, "profiles", "ncu_summary_latest.json")))["kernels"]
+        gk = [v for k, v in summ.items() if "gemm_tc" in k and "zero" not in k]
+        if gk and dt == "bf16" and args.workload == "c3":
+            traffic = sum(v["dram_bytes_per_launch"] * v["launches"] for v in gk) / sum(v["launches"] for v in gk)
+    except Exception:
+        traffic = None
+    roof = {"bound": "tensor", "kernel": "gemm_tc kernels (tcgen05, all 6 GEMM stages of a step)" if dt == "bf16" else "gemm_simt_kernel (fp32 FFMA)",
             "achieved": (f_gemm / 1e12) / (gemm_ms * 1e-3) if gemm_ms > 0 else None, "peak": pk["sustained"], "unit": "TFLOP/s",
-            "frac": None, "traffic": None, "peak_kind": "sustained bf16 cuBLAS, " + pk["source"], "peak_burst": pk["burst"],
+            "frac": None, "traffic": traffic, "traffic_unit": "DRAM bytes per GEMM launch (ncu, profiles/ncu_summary_latest.json)",
+            "algorithmic_bytes_per_launch": gemm_bytes / n_gemm,
+            "peak_kind": "sustained bf16 cuBLAS, " + pk["source"], "peak_burst": pk["burst"],
             "flops_per_launch": f_gemm / n_gemm, "avg_launch_ms": gemm_ms / n_gemm, "share_of_step": gemm_ms / ms_step if ms_step else None}
     if roof["achieved"]:
         roof["frac"] = roof["achieved"] / roof["peak"]

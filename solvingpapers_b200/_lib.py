@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libspb200.so")
+LIB_PATH = os.environ.get("SPB_LIB_PATH") or os.path.join(HERE, "libspb200.so")  # override: A/B experiments only
 
 F32, BF16 = 0, 1
 NORM_NONE, NORM_RMS, NORM_LAYER = 0, 1, 2

@@ -586,6 +586,16 @@ __global__ void __launch_bounds__(256) gemm_tc_zero_tail_kernel(const GemmTcArgs
   gemm_tc_tile_coords(p, p.full_tiles + (int)blockIdx.x, m_blk, n_blk);
   float* d = reinterpret_cast<float*>(p.D);
   const int m0 = m_blk * BMT, n0 = n_blk * BN;
+  if (p.vec_ok) {  // 16-byte aligned rows: float4 stores
+    for (int e = threadIdx.x; e < BMT * (BN / 4); e += 256) {
+      const int r = m0 + e / (BN / 4), c = n0 + (e % (BN / 4)) * 4;
+      if (r >= p.M || c >= p.N) continue;
+      float* q = d + (int64_t)r * p.ldd + c;
+      if (c + 4 <= p.N) *reinterpret_cast<float4*>(q) = make_float4(0.f, 0.f, 0.f, 0.f);
+      else for (int i = 0; c + i < p.N; ++i) q[i] = 0.f;
+    }
+    return;
+  }
   for (int e = threadIdx.x; e < BMT * BN; e += 256) {
     const int r = m0 + e / BN, c = n0 + e % BN;
     if (r < p.M && c < p.N) d[(int64_t)r * p.ldd + c] = 0.f;

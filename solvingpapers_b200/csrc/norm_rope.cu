@@ -474,7 +474,7 @@ __global__ void __launch_bounds__(256) rope_generic_kernel(T* __restrict__ x, in
 }
 
 // ------------------------------------------------------------------------------------------------ host launchers
-void colsum_plan(int64_t N, int* chunks, int* rows_per_chunk);
+void colsum_plan(int64_t N, int* chunks, int* rows_per_chunk, int col_blocks = 1);
 
 // (VPT, WPR) for a row of nv 128-bit vectors: at most 4 vectors per thread, up to 8 warps per row
 #define SPB_NORM_DISPATCH(nv, CALL) \
@@ -536,6 +536,7 @@ static int norm_bwd_launch(const void* x, const void* w, const float* stats, con
     colsum_plan(N, &chunks, &rpc);
     if (C % VN == 0 && (uintptr_t)dy % 16 == 0 && (uintptr_t)x % 16 == 0 && (uintptr_t)partial % 16 == 0) {
       const int tpr = colsum_tpr(C / VN);
+      colsum_plan(N, &chunks, &rpc, (C / VN + tpr - 1) / tpr);
       dim3 grid((C / VN + tpr - 1) / tpr, chunks);
       colsum_partial_vec_kernel<T, 1><<<grid, 256, 0, st>>>((const T*)dy, C, (const T*)x, stats, kind, N, C, rpc, chunks, tpr,
                                                             (float*)partial);
@@ -551,10 +552,14 @@ static int norm_bwd_launch(const void* x, const void* w, const float* stats, con
   return 0;
 }
 
-void colsum_plan(int64_t N, int* chunks, int* rows_per_chunk) {
-  // enough chunks to fill the machine for narrow matrices, few enough that the 2nd stage stays negligible
+void colsum_plan(int64_t N, int* chunks, int* rows_per_chunk, int col_blocks) {
+  // enough chunks to fill the machine for narrow matrices, few enough that the 2nd stage (one thread per column looping
+  // over the chunks) stays negligible for wide ones: about 4 waves of blocks in total
   int64_t ch = (N + 31) / 32;
-  if (ch > 592) ch = 592;  // 4 * 148
+  int64_t cap = 592 / (col_blocks < 1 ? 1 : col_blocks);  // 4 * 148 blocks
+  if (cap < 16) cap = 16;
+  if (cap > 592) cap = 592;
+  if (ch > cap) ch = cap;
   if (ch < 1) ch = 1;
   const int64_t rpc = (N + ch - 1) / ch;
   *rows_per_chunk = (int)(rpc < 1 ? 1 : rpc);
@@ -569,6 +574,7 @@ static int colsum_launch(const void* x, int64_t ld, int64_t N, int cols, float* 
   colsum_plan(N, &chunks, &rpc);
   if (cols % VN == 0 && ld % VN == 0 && (uintptr_t)x % 16 == 0 && (uintptr_t)partial % 16 == 0) {
     const int tpr = colsum_tpr(cols / VN);
+    colsum_plan(N, &chunks, &rpc, (cols / VN + tpr - 1) / tpr);
     dim3 grid((cols / VN + tpr - 1) / tpr, chunks);
     colsum_partial_vec_kernel<T, 0><<<grid, 256, 0, st>>>((const T*)x, ld, nullptr, nullptr, 0, N, cols, rpc, chunks, tpr,
                                                           (float*)partial);
