@@ -40,3 +40,53 @@ def test_block_bwd_with_size1_communicator_matches_no_communicator():
         assert torch.equal(t.cpu(), torch.arange(10, dtype=torch.float32))
     finally:
         comm.close()
+
+
+def _two_rank_worker(rank, world, port, out):
+    import os
+    import torch.distributed as tdist
+    import solvingpapers_b200 as sp
+    from solvingpapers_b200 import dist as spd
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    tdist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    comm = spd.Communicator(rank, world)
+    B, T, C, H, Hkv = 4, 128, 256, 4, 2
+    hd = C // H
+    gen = torch.Generator().manual_seed(0)  # same seed on both ranks: replicated weights, same global batch
+    cos, sin = llama_oracle.precompute_freqs_cis(hd, T)
+    dev = lambda t: t.bfloat16().cuda()
+    p = {"wqkv": dev(torch.randn(C, (H + 2 * Hkv) * hd, generator=gen) / 16), "wo": dev(torch.randn(H * hd, C, generator=gen) / 16),
+         "norm_w": dev(torch.randn(C, generator=gen)), "rope": sp.llama_rope_table(cos, sin).cuda()}
+    x, dy = dev(torch.randn(B, T, C, generator=gen)), dev(torch.randn(B, T, C, generator=gen))
+    per = B // world
+    blk = sp.AttentionBlock(sp.BlockConfig(per, T, C, H, Hkv, hd, dtype=torch.bfloat16), comm=comm.handle)
+    blk.forward(spd.shard_batch(x, world, rank).contiguous(), p)
+    g = blk.backward(spd.shard_batch(dy, world, rank).contiguous())
+    torch.cuda.synchronize()
+    if rank == 0:
+        full = sp.AttentionBlock(sp.BlockConfig(B, T, C, H, Hkv, hd, dtype=torch.bfloat16))
+        full.forward(x, p)
+        ref = full.backward(dy)
+        errs = {k: max_rel_err(g[k], ref[k]) for k in ("dwqkv", "dwo", "dnorm_w")}
+        errs["dx"] = max_rel_err(g["dx"], ref["dx"][:per])
+        torch.save(errs, out)
+    tdist.barrier()
+    comm.close()
+    tdist.destroy_process_group()
+
+
+def test_two_gpu_allreduced_gradients_equal_full_batch_gradients(tmp_path):
+    """"8-GPU allreduced dW == 1-GPU full-batch dW" - here with the GPUs this box has (needs >= 2)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs (run under gpurun --gpus 2)")
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    out = str(tmp_path / "errs.pt")
+    mp.spawn(_two_rank_worker, args=(2, port, out), nprocs=2, join=True)
+    errs = torch.load(out)
+    assert max(errs.values()) < 2e-2, errs
