@@ -238,7 +238,7 @@ int spb_flash_fwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t
 static int flash_bwd_any(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal, float scale,
                          const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo,
                          const void* d_o, int64_t lddo, const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk,
-                         void* dv, int64_t lddv, float* dq_acc, spb_stream_t stream, const float* rope);
+                         void* dv, int64_t lddv, float* dq_acc, spb_stream_t stream, const float* rope, int phase = 3);
 
 int spb_flash_bwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal, float scale,
                   const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo,
@@ -251,7 +251,7 @@ int spb_flash_bwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t
 static int flash_bwd_any(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal, float scale,
                          const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo,
                          const void* d_o, int64_t lddo, const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk,
-                         void* dv, int64_t lddv, float* dq_acc, spb_stream_t stream, const float* rope) {
+                         void* dv, int64_t lddv, float* dq_acc, spb_stream_t stream, const float* rope, int phase) {
   SPB_CHECK_ARG(q && k && v && o && d_o && lse && delta && dq && dk && dv, SPB_E_INVALID, "spb_flash_bwd: null pointer");
   SPB_CHECK_ARG(B > 0 && T > 0 && Hq > 0 && Hkv > 0 && hd > 0 && Hq % Hkv == 0, SPB_E_INVALID, "spb_flash_bwd: bad shape");
   cudaStream_t st = (cudaStream_t)stream;
@@ -260,9 +260,10 @@ static int flash_bwd_any(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, 
     SPB_CHECK_ARG(flash_bwd_tc_supported(dtype, hd), SPB_E_UNSUPPORTED, "spb_flash_bwd: tcgen05 path needs bf16 and hd in {64,128,256} (dtype=%d hd=%d)", dtype, hd);
     SPB_CHECK_ARG(dq_acc != nullptr, SPB_E_INVALID, "spb_flash_bwd: the tcgen05 path needs the fp32 dq_acc scratch");
     return flash_bwd_tc(B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk, dv,
-                        lddv, dq_acc, st, rope);
+                        lddv, dq_acc, st, rope, phase);
   }
   SPB_CHECK_ARG(use == SPB_IMPL_SIMT, SPB_E_INVALID, "spb_flash_bwd: impl %d", impl);
+  if (!(phase & FB_PHASE_MAIN)) return 0;  // the FFMA path has no separate preparation
   int rc = attn_simt_bwd(dtype, B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk,
                          lddk, dv, lddv, st);
   if (rc || rope == nullptr) return rc;

@@ -24,6 +24,8 @@
 // Scratch: delta[B,Hq,T] (rowsum(dO*O), prep kernel) and dq_acc[N,Hq*hd] fp32 (zeroed per call, converted at the end).
 #include <cstdlib>
 
+#include <type_traits>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -310,25 +312,34 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       const float2* lse2 = reinterpret_cast<const float2*>(sLse + st * 64 + cbase);
       const float2* del2 = reinterpret_cast<const float2*>(sDelta + st * 64 + cbase);
       uint32_t pkp[FB_ACOLS / 2], pkd[FB_ACOLS / 2];
+      // two explicit instantiations: left to one loop with `if (need_mask)` inside, the compiler if-converts the mask and
+      // every tile pays its compares and selects (ncu r01h: 1.4 ISETP/PLOP3 per exp); only diagonal/ragged tiles need them
+      auto elementwise = [&](auto masked) {
+        constexpr bool MASKED = decltype(masked)::value;
+#pragma unroll
+        for (int i = 0; i < FB_ACOLS; i += 2) {
+          const float2 l2 = lse2[i >> 1], d2 = del2[i >> 1];
+          const float2 x = __ffma2_rn(make_float2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, make_float2(-l2.x, -l2.y));
+          float2 pv = make_float2(fb_exp2(x.x), fb_exp2(x.y));
+          if (MASKED) {
+            const int qi = q0 + cbase + i;
+            const bool kv_dead = kv_idx >= p.T;
+            if (kv_dead || qi >= p.T || (p.causal && kv_idx > qi)) pv.x = 0.f;
+            if (kv_dead || qi + 1 >= p.T || (p.causal && kv_idx > qi + 1)) pv.y = 0.f;
+          }
+          const float2 dd = __fadd2_rn(make_float2(__uint_as_float(rd[i]), __uint_as_float(rd[i + 1])), make_float2(-d2.x, -d2.y));
+          const float2 ds = __fmul2_rn(__fmul2_rn(pv, dd), scale2);
+          pkp[i >> 1] = pack_bf16(pv.x, pv.y);
+          pkd[i >> 1] = pack_bf16(ds.x, ds.y);
+        }
+      };
       if (p.ablate & 32) {
 #pragma unroll
         for (int i = 0; i < FB_ACOLS / 2; ++i) pkp[i] = pkd[i] = rs[i] ^ rd[i];
-      } else
-#pragma unroll
-      for (int i = 0; i < FB_ACOLS; i += 2) {
-        const float2 l2 = lse2[i >> 1], d2 = del2[i >> 1];
-        const float2 x = __ffma2_rn(make_float2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, make_float2(-l2.x, -l2.y));
-        float2 pv = make_float2(fb_exp2(x.x), fb_exp2(x.y));
-        if (need_mask) {
-          const int qi = q0 + cbase + i;
-          const bool kv_dead = kv_idx >= p.T;
-          if (kv_dead || qi >= p.T || (p.causal && kv_idx > qi)) pv.x = 0.f;
-          if (kv_dead || qi + 1 >= p.T || (p.causal && kv_idx > qi + 1)) pv.y = 0.f;
-        }
-        const float2 dd = __fadd2_rn(make_float2(__uint_as_float(rd[i]), __uint_as_float(rd[i + 1])), make_float2(-d2.x, -d2.y));
-        const float2 ds = __fmul2_rn(__fmul2_rn(pv, dd), scale2);
-        pkp[i >> 1] = pack_bf16(pv.x, pv.y);
-        pkd[i >> 1] = pack_bf16(ds.x, ds.y);
+      } else if (need_mask) {
+        elementwise(std::true_type{});
+      } else {
+        elementwise(std::false_type{});
       }
       put_stat(it + 1, stat_next);  // visible to everyone after the next iteration's bar.sync
       mbar_wait(pds_empty, (it & 1) ^ 1);  // the MMA group of iteration it-1 has finished reading P^T / dS^T
@@ -497,18 +508,20 @@ template <int HD>
 static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float scale, const void* q, int64_t ldq, const void* k,
                                int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o, int64_t lddo,
                                const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
-                               float* dq_acc, cudaStream_t st, const float* rope) {
+                               float* dq_acc, cudaStream_t st, const float* rope, int phase) {
   using Cfg = FaBwdCfg<HD>;
   const int64_t N = (int64_t)B * Tn;
   const int64_t ld_acc = (int64_t)Hq * HD;
-  // scratch: dq accumulator starts at zero; delta = rowsum(dO * O)
-  SPB_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)N * ld_acc * sizeof(float), st));
-  {
+  // phase 1 (FB_PHASE_PRE): the scratch the main kernel needs - dq accumulator zeroed, delta = rowsum(dO * O).  It only
+  // depends on o and d_o, so the block backward runs it on a helper stream beside the dwo GEMM.
+  if (phase & FB_PHASE_PRE) {
+    SPB_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)N * ld_acc * sizeof(float), st));
     const int64_t rows = N * Hq;
     flash_bwd_prep_kernel<HD><<<(unsigned)((rows + 7) / 8), 256, 0, st>>>((const __nv_bfloat16*)o, ldo, (const __nv_bfloat16*)d_o, lddo,
                                                                           delta, B, Tn, Hq);
     SPB_LAUNCH_CHECK();
   }
+  if (!(phase & FB_PHASE_MAIN)) return 0;
   CUtensorMap tmK, tmV, tmQ, tmDO;
   int rc;
   if ((rc = make_tmap_2d(&tmK, k, 2, (uint64_t)N, (uint64_t)Hkv * HD, (uint64_t)ldk, 128, 64, true, false))) return rc;
@@ -553,7 +566,7 @@ static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
 int flash_bwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k,
                  int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o, int64_t lddo,
                  const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
-                 float* dq_acc, cudaStream_t st, const float* rope) {
+                 float* dq_acc, cudaStream_t st, const float* rope, int phase) {
   const void* ptrs[8] = {q, k, v, o, d_o, dq, dk, dv};
   const int64_t lds[8] = {ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv};
   for (int i = 0; i < 8; ++i)
@@ -562,13 +575,13 @@ int flash_bwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale
   SPB_CHECK_ARG((uintptr_t)dq_acc % 16 == 0, SPB_E_INVALID, "flash backward (tcgen05): dq_acc must be 16-byte aligned");
   if (hd == 128)
     return flash_bwd_tc_launch<128>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk,
-                                    dv, lddv, dq_acc, st, rope);
+                                    dv, lddv, dq_acc, st, rope, phase);
   if (hd == 256)
     return flash_bwd_tc_launch<256>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk,
-                                    dv, lddv, dq_acc, st, rope);
+                                    dv, lddv, dq_acc, st, rope, phase);
   if (hd == 64)
     return flash_bwd_tc_launch<64>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk, dv,
-                                   lddv, dq_acc, st, rope);
+                                   lddv, dq_acc, st, rope, phase);
   SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "flash backward (tcgen05): hd %d", hd);
 }
 

@@ -24,10 +24,11 @@ bool flash_tc_supported(int dtype, int hd);
 bool flash_bwd_tc_supported(int dtype, int hd);
 int flash_fwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k,
                  int64_t ldk, const void* v, int64_t ldv, void* o, int64_t ldo, float* lse, cudaStream_t st);
+constexpr int FB_PHASE_PRE = 1, FB_PHASE_MAIN = 2;  // flash_bwd_tc phases: scratch preparation / main kernel + dq conversion
 int flash_bwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k,
                  int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o, int64_t lddo,
                  const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
-                 float* dq_acc, cudaStream_t st, const float* rope = nullptr);  // rope: fused rotary VJP on dq and dk
+                 float* dq_acc, cudaStream_t st, const float* rope = nullptr, int phase = 3);  // rope: fused rotary VJP on dq and dk
 
 // comm.cu
 // all-reduce on the communicator's side stream, ordered after everything already enqueued on `main`

@@ -263,6 +263,136 @@ __global__ void __launch_bounds__(NR_THREADS) norm_bwd_dx_kernel(const T* __rest
   }
 }
 
+// Fused backward: dx AND the per-CTA partial column sums of dweight (and dbias for LayerNorm) in ONE pass over x and dy
+// (3*N*C*e bytes instead of 5).  A CTA walks `groups_per_cta` consecutive row groups; a thread always owns the same
+// columns, and its share of dw/db lives in SHARED memory (thread-private float4 slots, lane-consecutive: conflict-free),
+// not in registers - the first version kept 32-64 accumulators per thread, fell to 2 CTAs/SM and ran at 1.4 TB/s; this one
+// keeps the register footprint of the plain dx kernel.  At the end the CTA's row lanes are combined and one row of
+// partial[] is written (2nd stage: colsum_final_kernel).
+template <typename T, int VPT, int WPR, bool LAYER>
+__global__ void __launch_bounds__(NR_THREADS, 4) norm_bwd_fused_kernel(const T* __restrict__ x, const T* __restrict__ w,
+                                                                        const float* __restrict__ stats, const T* __restrict__ dy,
+                                                                        T* __restrict__ dx, int64_t N, int C, int64_t row_groups,
+                                                                        int groups_per_cta, float* __restrict__ partial) {
+  constexpr int VN = Vec<T>::N;
+  constexpr int RPC = 8 / WPR;
+  constexpr int Q = VN / 4;                        // float4 slots per vector
+  constexpr int PLANE = 8 * VPT * Q * 32;          // float4 slots of one plane (dw; LayerNorm adds a db plane)
+  extern __shared__ float4 fused_acc[];
+  __shared__ float red[4][8];  // [iteration parity][s_g, s_gx]: a slow warp may still read the previous row's sums
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int w_in = warp % WPR, rlane = warp / WPR;
+  for (int i = threadIdx.x; i < (LAYER ? 2 : 1) * PLANE; i += NR_THREADS) fused_acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  // (thread-private slots: no barrier needed before the thread's own read-modify-writes)
+  float4* mine = fused_acc + (warp * VPT * Q) * 32 + lane;  // slot (k, h) at mine[(k*Q + h) * 32]
+  __syncthreads();
+  const int64_t g0 = (int64_t)blockIdx.x * groups_per_cta;
+  const int64_t g1 = g0 + groups_per_cta < row_groups ? g0 + groups_per_cta : row_groups;
+  int par = 0;
+  for (int64_t rg = g0; rg < g1; ++rg) {
+    const int64_t row = rg * RPC + rlane;
+    const bool active = row < N;
+    float mean = 0.f, rstd = 0.f;
+    if (active) {
+      if (LAYER) mean = stats[2 * row];
+      rstd = stats[2 * row + 1];
+    }
+    Vec<T> xv[VPT], dv[VPT];
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      const int c = ((k * WPR + w_in) * 32 + lane) * VN;
+      if (active && c < C) {
+        xv[k].load(x + row * C + c);
+        dv[k].load(dy + row * C + c);
+      }
+    }
+    float s_g = 0.f, s_gx = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      const int c = ((k * WPR + w_in) * 32 + lane) * VN;
+      if (active && c < C) {
+        Vec<T> wv;
+        wv.load(w + c);
+        float xf[VN], g[VN], wf[VN];
+        xv[k].unpack(xf);
+        dv[k].unpack(g);
+        wv.unpack(wf);
+#pragma unroll
+        for (int h = 0; h < Q; ++h) {
+          float4 a = mine[(k * Q + h) * 32];
+          float* af = reinterpret_cast<float*>(&a);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float xh = LAYER ? (xf[4 * h + e] - mean) * rstd : xf[4 * h + e] * rstd;
+            const float gv = g[4 * h + e] * wf[4 * h + e];
+            af[e] += g[4 * h + e] * xh;
+            s_g += gv;
+            s_gx += gv * xh;
+          }
+          mine[(k * Q + h) * 32] = a;
+          if (LAYER) {
+            float4 bsum = mine[PLANE + (k * Q + h) * 32];
+            bsum.x += g[4 * h];
+            bsum.y += g[4 * h + 1];
+            bsum.z += g[4 * h + 2];
+            bsum.w += g[4 * h + 3];
+            mine[PLANE + (k * Q + h) * 32] = bsum;
+          }
+        }
+      }
+    }
+    if (LAYER) s_g = row_reduce<WPR>(s_g, red[par], warp) / (float)C;
+    s_gx = row_reduce<WPR>(s_gx, red[par + 1], warp) / (float)C;
+    par ^= 2;
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      const int c = ((k * WPR + w_in) * 32 + lane) * VN;
+      if (active && c < C) {
+        Vec<T> wv;
+        wv.load(w + c);
+        float xf[VN], g[VN], wf[VN], o[VN];
+        xv[k].unpack(xf);
+        dv[k].unpack(g);
+        wv.unpack(wf);
+#pragma unroll
+        for (int e = 0; e < VN; ++e) {
+          const float gv = g[e] * wf[e];
+          const float xh = LAYER ? (xf[e] - mean) * rstd : xf[e] * rstd;
+          o[e] = LAYER ? rstd * (gv - s_g - xh * s_gx) : rstd * (gv - xh * s_gx);
+        }
+        Vec<T> ov;
+        ov.pack(o);
+        ov.store(dx + row * C + c);
+      }
+    }
+  }
+  // combine the CTA's row lanes: the warps of row lane 0 add the slots of the same columns in the other lanes and write this
+  // CTA's row of the partial sums - partial[blockIdx][c] (dw) and partial[gridDim + blockIdx][c] (db)
+  __syncthreads();
+  if (rlane == 0) {
+#pragma unroll
+    for (int pl = 0; pl < (LAYER ? 2 : 1); ++pl) {
+      float* out = partial + ((int64_t)pl * gridDim.x + blockIdx.x) * (int64_t)C;
+#pragma unroll
+      for (int k = 0; k < VPT; ++k) {
+        const int c = ((k * WPR + w_in) * 32 + lane) * VN;
+        if (c < C) {
+#pragma unroll
+          for (int h = 0; h < Q; ++h) {
+            float4 a = mine[pl * PLANE + (k * Q + h) * 32];
+#pragma unroll
+            for (int l = 1; l < RPC; ++l) {
+              const float4 t = mine[pl * PLANE + (l * WPR * VPT * Q) * 32 + (k * Q + h) * 32];
+              a.x += t.x; a.y += t.y; a.z += t.z; a.w += t.w;
+            }
+            *reinterpret_cast<float4*>(out + c + 4 * h) = a;
+          }
+        }
+      }
+    }
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(NORM_WARPS * 32) norm_bwd_dx_generic_kernel(const T* __restrict__ x, const T* __restrict__ w,
                                                                                const float* __restrict__ stats,
@@ -474,6 +604,7 @@ __global__ void __launch_bounds__(256) rope_generic_kernel(T* __restrict__ x, in
 }
 
 // ------------------------------------------------------------------------------------------------ host launchers
+constexpr int COLSUM_MAX_CHUNKS = 592;  // 4 * 148; upper bound of every column-sum plan (sizes the partial scratch)
 void colsum_plan(int64_t N, int* chunks, int* rows_per_chunk, int col_blocks = 1);
 
 // (VPT, WPR) for a row of nv 128-bit vectors: at most 4 vectors per thread, up to 8 warps per row
@@ -513,9 +644,45 @@ template <typename T>
 static int norm_bwd_launch(const void* x, const void* w, const float* stats, const void* dy, void* dx, float* dw, float* db,
                            void* partial, int64_t N, int C, int kind, cudaStream_t st) {
   constexpr int VN = Vec<T>::N;
+  const bool vec_ok = (C % VN == 0) && (C / VN <= 1024) && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) &&
+                      ((uintptr_t)dx % 16 == 0) && ((uintptr_t)w % 16 == 0);
+  if (dx != nullptr && vec_ok && (dw != nullptr || db != nullptr) && partial != nullptr && (uintptr_t)partial % 16 == 0 &&
+      (kind == SPB_NORM_LAYER || db == nullptr)) {
+    // one fused pass: dx + per-CTA partial sums of dw (db), then the deterministic 2nd stage
+    const int nv = C / VN;
+    int64_t row_groups = 0;
+    int grid = 0, gpc = 1;
+#define SPB_NBF_ONE(V, W, L)                                                                                                    \
+  do {                                                                                                                          \
+    const size_t smem = (size_t)(L ? 2 : 1) * 8 * V * (VN / 4) * 32 * sizeof(float4);                                           \
+    if (smem > 48 * 1024)                                                                                                       \
+      SPB_CUDA(cudaFuncSetAttribute(norm_bwd_fused_kernel<T, V, W, L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    row_groups = (N + (8 / W) - 1) / (8 / W);                                                                                   \
+    /* one full wave of CTAs when there are enough rows; never more partial rows than the scratch holds */                  \
+    int occ = 1;                                                                                                                \
+    SPB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, norm_bwd_fused_kernel<T, V, W, L>, NR_THREADS, smem));         \
+    int64_t want = (int64_t)(occ < 1 ? 1 : occ) * sm_count();                                                                   \
+    if (want > COLSUM_MAX_CHUNKS) want = COLSUM_MAX_CHUNKS;                                                                     \
+    gpc = (int)((row_groups + want - 1) / want);                                                                                \
+    if (gpc < 1) gpc = 1;                                                                                                       \
+    grid = (int)((row_groups + gpc - 1) / gpc);                                                                                 \
+    norm_bwd_fused_kernel<T, V, W, L><<<grid, NR_THREADS, smem, st>>>((const T*)x, (const T*)w, stats, (const T*)dy, (T*)dx, N, C, \
+                                                                      row_groups, gpc, (float*)partial);                        \
+  } while (0)
+#define SPB_NBF(V, W)                                          \
+  do {                                                         \
+    if (kind == SPB_NORM_LAYER) SPB_NBF_ONE(V, W, true);       \
+    else SPB_NBF_ONE(V, W, false);                             \
+  } while (0)
+    SPB_NORM_DISPATCH(nv, SPB_NBF);
+#undef SPB_NBF
+#undef SPB_NBF_ONE
+    SPB_LAUNCH_CHECK();
+    colsum_final_kernel<<<(C + 255) / 256, 256, 0, st>>>((const float*)partial, grid, C, dw, kind == SPB_NORM_LAYER ? db : nullptr);
+    SPB_LAUNCH_CHECK();
+    return 0;
+  }
   if (dx != nullptr) {
-    const bool vec_ok = (C % VN == 0) && (C / VN <= 1024) && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) &&
-                        ((uintptr_t)dx % 16 == 0) && ((uintptr_t)w % 16 == 0);
     if (vec_ok) {
       const int nv = C / VN;
 #define SPB_NB(V, W)                                                                                                         \
@@ -669,9 +836,13 @@ int spb_norm_fwd(int dtype, int norm_kind, int upcast, float eps, const void* x,
 }
 
 size_t spb_norm_bwd_partial_bytes(int64_t N, int32_t C) {
+  // 2 planes (dweight, dbias) x the most partial rows any plan uses: the column-sum chunks or the fused kernel's CTAs
   int chunks, rpc;
   spb::colsum_plan(N < 1 ? 1 : N, &chunks, &rpc);
-  return (size_t)2 * chunks * (size_t)C * sizeof(float);
+  const int64_t groups = N < 1 ? 1 : N;  // fused kernel: <= one CTA per row group, capped
+  int64_t rows = groups < spb::COLSUM_MAX_CHUNKS ? groups : spb::COLSUM_MAX_CHUNKS;
+  if (rows < chunks) rows = chunks;
+  return (size_t)2 * (size_t)rows * (size_t)C * sizeof(float);
 }
 
 int spb_norm_bwd(int dtype, int norm_kind, int upcast, const void* x, const void* w, const float* stats, const void* dy,
