@@ -1,17 +1,23 @@
-// flash_tc.cu - K3: flash-style causal GQA attention forward on tcgen05 (bf16, hd in {64,128}); replaces the materialised
-// scores of llama3:820-828 (and gpt:344-353, ViT's nn.MultiheadAttention).  Scores never leave the SM.
+// flash_tc.cu - K3: flash-style causal GQA attention forward on tcgen05 (bf16, hd in {64,128,256}); replaces the
+// materialised scores of llama3:820-828 (and gpt:344-353, ViT's nn.MultiheadAttention).  Scores never leave the SM.
 //
-// One CTA = 256 query rows (two 128-row tiles) of one (batch, q head); the two tiles ping-pong on the tensor pipe:
-//   warp 0    TMA producer: the two Q tiles once, then K / V tiles of 128 rows (K double buffered, V single)
-//   warp 1    MMA issuer (one thread): per KV tile  S0 = Q0 K^T, S1 = Q1 K^T  (M128 N128 K=hd, each into its own TMEM S
-//             buffer), then  O0 += P0 V, O1 += P1 V  (M128 N=hd K128, TMEM accumulators): while one tile is in its
-//             softmax the tensor pipe works on the other
-//   warps 2-5 softmax of tile 0, warps 6-9 softmax of tile 1: thread = one query row (TMEM lane).  Two passes over the S
-//             row in TMEM (tcgen05.ld): pass 1 row max, pass 2 exp2 / sum / bf16 P into shared memory in the 128B-swizzled
-//             K-major UMMA layout; 1/sqrt(hd)*log2(e) folded into one FFMA; lazy rescaling of O (only when the running
-//             max grows by more than 2^8, decided per warp)
+// One CTA = 256 query rows (two 128-row tiles; one tile at hd=256) of one (batch, q head):
+//   warp 0    TMA producer: the Q tiles once, then K / V tiles of 128 rows (double buffered)
+//   warp 1    MMA issuer (one thread): per KV tile  S_t = Q_t K^T (M128 N128 K=hd, own TMEM buffer per tile) and
+//             O_t += P_t V (M128 N=hd K128; P_t is read from tensor memory, where it overwrote S_t)
+//   warps 2-9 softmax.  ALL eight warps work on ONE tile at a time and alternate between the two tiles: warp w owns TMEM
+//             lane quadrant w%4 (32 query rows) and column half (w-2)/4 (64 of the 128 KV columns), i.e. two threads
+//             share a row.  So a tile's softmax takes half as long, and while the tensor pipe runs PV_t / S_t(next) the
+//             whole softmax crew is busy with the other tile - the r01 kernel gave each tile its own four warps, both
+//             tiles' softmaxes ran concurrently at half speed each and every tile waited for its own MMAs afterwards
+//             (ablation: MMA time and softmax time were additive).
+//             Per tile: 64 S values -> registers (two tcgen05.ld, one wait), row max (halves combined through shared
+//             memory + one named barrier, which also orders every S load before any P store), exp2 with
+//             1/sqrt(hd)*log2(e) folded into one packed FFMA, bf16 P back into tensor memory, lazy rescaling of O (only
+//             when the running max grows by more than 2^8, decided per warp; each thread rescales its half of hd)
 //   causal tile skipping: KV tiles above a tile's diagonal are neither loaded nor multiplied; diagonal and ragged last
-//   tiles are masked by index (-1e9 additive / -1e4 replacing / -inf masks of the notebooks all give exp()==0 exactly).
+//   tiles are classified per 32-column chunk and warp (fully visible: plain code; partly: per-element select; invisible:
+//   zeros, no exp) - (-1e9 additive / -1e4 replacing / -inf masks of the notebooks all give exp()==0 exactly).
 //   GQA: kv head = q head / (Hq/Hkv) is just the TMA column coordinate (llama3:626-627 repeat_kv never materialised).
 // TMEM: S0 [0,128) S1 [128,256) O0 [256,256+hd) O1 [384,384+hd).  Algorithmic FLOPs: 4*B*Hq*T^2*hd*m (m=(T+1)/2T causal).
 #include <cstdlib>
@@ -21,35 +27,69 @@
 
 namespace spb {
 
+// Timeline tracing for kernel development (tools/diag_trace_fwd.py): compiled in only with -DSPB_FA_TRACE, into a separate
+// library; CTA (0,0,0) logs (clock, event id) per role.  The product build contains none of it.
+#ifdef SPB_FA_TRACE
+constexpr int FA_TRACE_ROLES = 4, FA_TRACE_EVENTS = 2048;
+__device__ unsigned long long g_fa_trace[FA_TRACE_ROLES * FA_TRACE_EVENTS];
+#define FA_TRACE_DECL(role) int tr_n = 0; const bool tr_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0); const int tr_role = (role)
+#define FA_TRACE(id)                                                                                                  \
+  do {                                                                                                                \
+    if (tr_on && tr_n < FA_TRACE_EVENTS) g_fa_trace[tr_role * FA_TRACE_EVENTS + tr_n++] = ((unsigned long long)clock64() << 8) | (unsigned)(id); \
+  } while (0)
+#else
+#define FA_TRACE_DECL(role)
+#define FA_TRACE(id)
+#endif
+
+// exp2 on the FMA pipe for a pair of values (x <= ~2^7): Cody-Waite split with the 1.5*2^23 rounding trick, degree-3
+// minimax polynomial of 2^f on [-0.5, 0.5] (max relative error 7.5e-5), exponent added with integer arithmetic.
+#ifndef SPB_FA_POLY_EVERY
+#define SPB_FA_POLY_EVERY 2  // one pair of every 2nd group of four elements = 25 % of the exps; 0 disables
+#endif
+constexpr int FA_POLY_EVERY = SPB_FA_POLY_EVERY;
+__device__ __forceinline__ float2 fa_exp2_poly2(float2 x) {
+  x.x = fmaxf(x.x, -126.0f);
+  x.y = fmaxf(x.y, -126.0f);
+  const float2 magic = make_float2(12582912.0f, 12582912.0f);
+  const float2 t = __fadd2_rn(x, magic);                                     // low mantissa bits = round(x)
+  const float2 n = __fadd2_rn(t, make_float2(-12582912.0f, -12582912.0f));   // round(x) as a float
+  const float2 f = __fadd2_rn(x, make_float2(-n.x, -n.y));                   // x - round(x) in [-0.5, 0.5]
+  float2 r = __ffma2_rn(f, make_float2(0.0551716573536396f, 0.0551716573536396f), make_float2(0.2426111400127411f, 0.2426111400127411f));
+  r = __ffma2_rn(r, f, make_float2(0.6932609677314758f, 0.6932609677314758f));
+  r = __ffma2_rn(r, f, make_float2(0.9999280571937561f, 0.9999280571937561f));
+  return make_float2(__uint_as_float(__float_as_uint(r.x) + (__float_as_uint(t.x) << 23)),
+                     __uint_as_float(__float_as_uint(r.y) + (__float_as_uint(t.y) << 23)));
+}
+
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 
 __device__ __forceinline__ float fast_exp2(float x) {
   float y;
-  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
 
-// PT = true: P (bf16) is written back into tensor memory over the S columns it came from and feeds the PV MMA as a TMEM
-// A operand (no shared-memory round trip, which frees 64 KB for a second V stage).  PT = false keeps P in shared memory.
-template <int HD, bool PT>
+template <int HD>
 struct FaFwdCfg {
   static constexpr int NT = (HD <= 128) ? 2 : 1;    // query tiles per CTA (hd=256: O alone needs 256 TMEM columns -> one tile)
   static constexpr int KST = (HD <= 128) ? 2 : 1;   // K stages (hd=256: Q, K, V tiles are 64 KB each)
-  static constexpr int VST = (HD <= 128 && PT) ? 2 : 1;
+  static constexpr int VST = (HD <= 128) ? 2 : 1;
   static constexpr int CH = HD / 64;                // 64-column chunks per Q/K/V tile
   static constexpr int TILE_BYTES = 128 * HD * 2;   // 128 rows x HD bf16
   static constexpr int CHUNK_BYTES = 128 * 128;     // 128 rows x 128 B
-  static constexpr int P_BYTES = 128 * 128 * 2;
   static constexpr int OFF_Q = 0;
   static constexpr int OFF_K = OFF_Q + NT * TILE_BYTES;
   static constexpr int OFF_V = OFF_K + KST * TILE_BYTES;
-  static constexpr int OFF_P = OFF_V + VST * TILE_BYTES;
-  static constexpr int OFF_BAR = OFF_P + (PT ? 0 : NT * P_BYTES);
+  static constexpr int OFF_X = OFF_V + VST * TILE_BYTES;   // row-max / row-sum exchange: [2 buffers][2 halves][128 rows] fp32
+  static constexpr int OFF_BAR = OFF_X + 2 * 2 * 128 * 4;
   static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
   static constexpr int TMEM_COLS = 512;
   static constexpr int TM_O0 = (NT == 2) ? 256 : 128;     // O_t at TM_O0 + t*128 (NT=2) / one 256-column O at 128 (NT=1)
-  static constexpr int THREADS = 64 + NT * 128;
+  static constexpr int SM_WARPS = 8;                      // softmax warps
+  static constexpr int THREADS = 64 + SM_WARPS * 32;
+  static constexpr int OH = HD / 2;                       // O columns per softmax thread (two threads share a row)
 };
 
 struct FaFwdArgs {
@@ -60,17 +100,17 @@ struct FaFwdArgs {
   float scale_log2;  // scale * log2(e)
 };
 
-template <int HD, bool PT>
-__global__ void __launch_bounds__(FaFwdCfg<HD, PT>::THREADS, 1)
+template <int HD>
+__global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
     flash_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                         const __grid_constant__ CUtensorMap tmV, const FaFwdArgs p) {
-  using Cfg = FaFwdCfg<HD, PT>;
+  using Cfg = FaFwdCfg<HD>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sQ = smem + Cfg::OFF_Q;
   uint8_t* sK = smem + Cfg::OFF_K;
   uint8_t* sV = smem + Cfg::OFF_V;
-  uint8_t* sP = smem + Cfg::OFF_P;
+  float* sX = reinterpret_cast<float*>(smem + Cfg::OFF_X);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
   uint64_t* q_full = bars;            // [1]
   uint64_t* k_full = bars + 1;        // [2] stages
@@ -78,18 +118,21 @@ __global__ void __launch_bounds__(FaFwdCfg<HD, PT>::THREADS, 1)
   uint64_t* v_full = bars + 5;        // [2] stages
   uint64_t* v_empty = bars + 7;       // [2]
   uint64_t* s_full = bars + 9;        // [2] per q tile
-  uint64_t* s_empty = bars + 11;      // [2]
-  uint64_t* p_full = bars + 13;       // [2]
-  uint64_t* pv_done = bars + 15;      // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
+  uint64_t* p_full = bars + 11;       // [2]
+  uint64_t* pv_done = bars + 13;      // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
   constexpr int NT = Cfg::NT, KST = Cfg::KST, VST = Cfg::VST;
-  const int n_qp = (int)gridDim.x;
-  const int qp = p.causal ? (n_qp - 1 - (int)blockIdx.x) : (int)blockIdx.x;  // heavy (late) causal tiles first
-  const int h = blockIdx.y, b = blockIdx.z;
+  // grid (Hq, B, query tile pairs): the hardware hands out CTAs in linear blockIdx order, so with the tile pair in the
+  // slowest dimension ALL heavy (late) causal pairs run first and the short ones fill the tail (longest-processing-time
+  // order; with the pair in blockIdx.x a 31-unit CTA could start last: ~11 % of the kernel in a schedule simulation);
+  // neighbouring CTAs are the q heads of one KV group at the same position, so K/V tiles are shared through L2
+  const int n_qp = (int)gridDim.z;
+  const int qp = p.causal ? (n_qp - 1 - (int)blockIdx.z) : (int)blockIdx.z;
+  const int h = blockIdx.x, b = blockIdx.y;
   const int kvh = h / (p.Hq / p.Hkv);
   const int q0 = qp * (NT * 128);
   const int n_kv_all = (p.T + 127) / 128;
@@ -116,8 +159,7 @@ __global__ void __launch_bounds__(FaFwdCfg<HD, PT>::THREADS, 1)
         mbar_init(&k_full[i], 1);
         mbar_init(&k_empty[i], 1);
         mbar_init(&s_full[i], 1);
-        mbar_init(&s_empty[i], 4);
-        mbar_init(&p_full[i], 4);
+        mbar_init(&p_full[i], Cfg::SM_WARPS);
         mbar_init(&pv_done[i], 1);
       }
       fence_barrier_init();
@@ -133,6 +175,7 @@ __global__ void __launch_bounds__(FaFwdCfg<HD, PT>::THREADS, 1)
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
+    FA_TRACE_DECL(0);
     if (lane == 0) {
       const int n_live = (n_kv_t[0] > 0) + (n_kv_t[1] > 0);
       mbar_arrive_expect_tx(q_full, n_live * Cfg::TILE_BYTES);
@@ -148,12 +191,14 @@ __global__ void __launch_bounds__(FaFwdCfg<HD, PT>::THREADS, 1)
         const int bf = j % KST;
         const int row_kv = b * p.T + j * 128;
         mbar_wait(&k_empty[bf], ((j / KST) & 1) ^ 1);
+        FA_TRACE(1);
         mbar_arrive_expect_tx(&k_full[bf], Cfg::TILE_BYTES);
 #pragma unroll
         for (int c = 0; c < Cfg::CH; ++c)
           tma_load_2d(sK + bf * Cfg::TILE_BYTES + c * Cfg::CHUNK_BYTES, &tmK, &k_full[bf], kvh * HD + c * 64, row_kv);
         const int vf = j % VST;
         mbar_wait(&v_empty[vf], ((j / VST) & 1) ^ 1);
+        FA_TRACE(2);
         mbar_arrive_expect_tx(&v_full[vf], Cfg::TILE_BYTES);
 #pragma unroll
         for (int c = 0; c < Cfg::CH; ++c)
@@ -163,15 +208,14 @@ __global__ void __launch_bounds__(FaFwdCfg<HD, PT>::THREADS, 1)
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
+    FA_TRACE_DECL(1);
     if (lane == 0) {
       const uint32_t idesc_qk = umma_idesc_bf16(128, 128, 0, 0);  // A = Q (K-major), B = K (K-major)
-      const uint32_t idesc_pv = umma_idesc_bf16(128, HD, 0, 1);   // A = P (K-major), B = V (MN-major: hd contiguous)
+      const uint32_t idesc_pv = umma_idesc_bf16(128, HD, 0, 1);   // A = P (tensor memory), B = V (MN-major: hd contiguous)
       mbar_wait(q_full, 0);
       auto qk_t = [&](int j, int t) {  // S_t = Q_t K(j)^T
         if (j >= n_kv_t[t]) return;
-        // S_t is free: PT: PV_t(j-1), issued earlier on this in-order pipe, was the last reader of the P that aliases it;
-        // smem P: the softmax group signalled that it has finished reading S_t of the previous KV tile
-        if (!PT) mbar_wait(&s_empty[t], (j & 1) ^ 1);
+        // S_t is free: PV_t(j-1), issued earlier on this in-order pipe, was the last reader of the P that aliases it
         tc_fence_after();
         const uint32_t q_addr = smem_u32(sQ + t * Cfg::TILE_BYTES);
         const uint32_t k_addr = smem_u32(sK + (j % KST) * Cfg::TILE_BYTES);
@@ -181,30 +225,23 @@ __global__ void __launch_bounds__(FaFwdCfg<HD, PT>::THREADS, 1)
           umma_bf16(tmem_base + t * 128, umma_desc_kmajor(q_addr + off), umma_desc_kmajor(k_addr + off), idesc_qk, kk > 0 ? 1u : 0u);
         }
         umma_commit(&s_full[t]);
+        FA_TRACE(10 + t);  // QK_t issued
       };
       auto pv_t = [&](int j, int t) {  // O_t += P_t V(j)
         if (j >= n_kv_t[t]) return;
         mbar_wait(&p_full[t], j & 1);
+        FA_TRACE(12 + t);  // p_full[t] seen
         tc_fence_after();
         const uint32_t v_addr = smem_u32(sV + (j % VST) * Cfg::TILE_BYTES);
-        if (PT) {
 #pragma unroll
-          for (int kk = 0; kk < 8; ++kk)  // A = P_t from tensor memory: 16 bf16 of K per 8 columns
-            umma_bf16_ts(tmem_base + Cfg::TM_O0 + t * 128, tmem_base + t * 128 + kk * 8, umma_desc_mnmajor(v_addr + kk * 2048, 128),
-                         idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
-        } else {
-          const uint32_t p_addr = smem_u32(sP + t * Cfg::P_BYTES);
-#pragma unroll
-          for (int kk = 0; kk < 8; ++kk) {
-            const uint32_t aoff = (kk >> 2) * Cfg::CHUNK_BYTES + (kk & 3) * 32;
-            umma_bf16(tmem_base + Cfg::TM_O0 + t * 128, umma_desc_kmajor(p_addr + aoff), umma_desc_mnmajor(v_addr + kk * 2048, 128),
-                      idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
-          }
-        }
+        for (int kk = 0; kk < 8; ++kk)  // A = P_t from tensor memory: 16 bf16 of K per 8 columns
+          umma_bf16_ts(tmem_base + Cfg::TM_O0 + t * 128, tmem_base + t * 128 + kk * 8, umma_desc_mnmajor(v_addr + kk * 2048, 128),
+                       idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
         umma_commit(&pv_done[t]);
+        FA_TRACE(14 + t);  // PV_t issued
       };
-      // issue order per KV tile j:  PV0(j) QK0(j+1) PV1(j) QK1(j+1)  - each tile's MMAs follow its own softmax, the other
-      // tile's MMAs fill the tensor pipe meanwhile
+      // issue order per KV tile j:  PV0(j) QK0(j+1) PV1(j) QK1(j+1)  - the softmax crew alternates between the tiles in
+      // the same order, so a tile's MMAs run while the other tile is in its softmax
       mbar_wait(&k_full[0], 0);
       qk_t(0, 0);
       if (NT == 2) qk_t(0, 1);
@@ -212,9 +249,11 @@ __global__ void __launch_bounds__(FaFwdCfg<HD, PT>::THREADS, 1)
       for (int j = 0; j < n_kv; ++j) {
         const bool more = j + 1 < n_kv;
         mbar_wait(&v_full[j % VST], (j / VST) & 1);
+        FA_TRACE(16);  // v_full seen
         pv_t(j, 0);
         if (more) {
           mbar_wait(&k_full[(j + 1) % KST], ((j + 1) / KST) & 1);
+          FA_TRACE(17);  // k_full seen
           qk_t(j + 1, 0);
         }
         if (NT == 2) pv_t(j, 1);
@@ -227,135 +266,170 @@ __global__ void __launch_bounds__(FaFwdCfg<HD, PT>::THREADS, 1)
     }
     __syncwarp();
   } else {
-    // ------------------------------------------------------------------ softmax + epilogue: warps 2-5 tile 0, warps 6-9 tile 1
-    const int t = (warp - 2) >> 2;
-    const int qd = warp & 3;
-    const int r = qd * 32 + lane;      // row inside the tile = TMEM lane
-    const int q_idx = q0 + t * 128 + r;
+    // ------------------------------------------------------------------ softmax + epilogue: warps 2-9, one tile at a time
+    const int qd = warp & 3;            // TMEM lane quadrant this warp may touch (hardware rule: warp % 4)
+    const int half = (warp - 2) >> 2;   // which 64 KV columns of S/P and which hd/2 columns of O this thread owns
+    const int r = qd * 32 + lane;       // row inside the tile = TMEM lane
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
-    const uint32_t tS = lane_base + (uint32_t)(t * 128);
-    const uint32_t tO = lane_base + (uint32_t)(Cfg::TM_O0 + t * 128);
-    const int n_mine = n_kv_t[t];
-    float m = -INFINITY, l = 0.f;
-    for (int j = 0; j < n_mine; ++j) {
-      mbar_wait(&s_full[t], j & 1);
-      tc_fence_after();
+    float m_t[2] = {-INFINITY, -INFINITY}, l_t[2] = {0.f, 0.f};
+    int xbuf = 0;
+    FA_TRACE_DECL(warp == 2 ? 2 : (warp == 6 ? 3 : 0));
+#ifdef SPB_FA_TRACE
+    const bool tr_keep = tr_on && (warp == 2 || warp == 6);
+#define FA_TRACE_S(id) do { if (tr_keep) FA_TRACE(id); } while (0)
+#else
+#define FA_TRACE_S(id)
+#endif
+    auto exchange = [&](float mine) -> float {  // combine a per-row value of the two column halves (all 256 threads call it)
+      float* buf = sX + xbuf * 256;
+      buf[half * 128 + r] = mine;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      xbuf ^= 1;
+      return buf[(half ^ 1) * 128 + r];
+    };
+    // visible columns of this thread's 64 in unit (j,t): n_valid leading ones when the tile needs masking at all
+    auto geometry = [&](int j, int t, bool& need_mask, int& n_valid) {
       const int kv0 = j * 128;
-      const bool need_mask = (p.causal && kv0 + 127 > q0 + t * 128) || (kv0 + 128 > p.T);
-      // number of leading KV columns of this tile that row q_idx may attend to (everything else is masked)
-      int n_valid = p.T - kv0;
-      if (p.causal) n_valid = min(n_valid, q_idx - kv0 + 1);
-      // ---- pass 1: row max of the raw scores (scale > 0, so scaling commutes with max); two 32-column TMEM loads in flight
-      float mx0 = -INFINITY, mx1 = -INFINITY;
-#pragma unroll 1
-      for (int c2 = 0; c2 < 2; ++c2) {
-        uint32_t ra[32], rb[32];
-        SPB_TMEM_LD_32(tS + (uint32_t)(c2 * 64), ra);
-        SPB_TMEM_LD_32(tS + (uint32_t)(c2 * 64 + 32), rb);
-        tmem_ld_wait();
-        if (need_mask) {
-          const int lim = n_valid - c2 * 64;
+      need_mask = (p.causal && kv0 + 127 > q0 + t * 128) || (kv0 + 128 > p.T);
+      n_valid = p.T - kv0;
+      if (p.causal) n_valid = min(n_valid, q0 + t * 128 + r - kv0 + 1);
+      n_valid -= half * 64;
+    };
+    auto row_max = [&](const uint32_t(&s)[64], bool need_mask, int n_valid) -> float {
+      // row max of the raw scores over the visible ones of 64 columns (scale > 0, so scaling commutes with max)
+      float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      if (!need_mask) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            mx0 = fmaxf(mx0, i < lim ? __uint_as_float(ra[i]) : -INFINITY);
-            mx1 = fmaxf(mx1, i + 32 < lim ? __uint_as_float(rb[i]) : -INFINITY);
-          }
-        } else {
+        for (int i = 0; i < 64; i += 8) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            mx0 = fmaxf(mx0, __uint_as_float(ra[i]));
-            mx1 = fmaxf(mx1, __uint_as_float(rb[i]));
-          }
+          for (int c = 0; c < 4; ++c) mx[c] = fmaxf(mx[c], fmaxf(__uint_as_float(s[i + 2 * c]), __uint_as_float(s[i + 2 * c + 1])));
         }
-      }
-      const float tmax = fmaxf(mx0, mx1) * p.scale_log2;
-      if (j == 0) {
-        m = tmax;
       } else {
-        // lazy rescale: keep the stale max while the true max is at most 2^8 above it (p <= 256, harmless in fp32/bf16)
-        const bool grow = tmax > m + 8.0f;
-        if (__any_sync(0xffffffffu, grow)) {
-          float alpha = 1.0f;
-          if (grow) {
-            alpha = fast_exp2(m - tmax);
-            m = tmax;
-          }
-          l *= alpha;
-          mbar_wait(&pv_done[t], (j - 1) & 1);  // O_t must hold every PV issued so far
-          tc_fence_after();
-#pragma unroll 1
-          for (int c = 0; c < HD / 32; ++c) {
-            uint32_t o[32];
-            SPB_TMEM_LD_32(tO + (uint32_t)(c * 32), o);
-            tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-            SPB_TMEM_ST_32(tO + (uint32_t)(c * 32), o);
-          }
-          tmem_st_wait();
-        }
+        for (int i = 0; i < 64; ++i) mx[i & 3] = fmaxf(mx[i & 3], i < n_valid ? __uint_as_float(s[i]) : -INFINITY);
       }
-      // ---- pass 2: p = exp2(s*c - m) (packed fp32x2 FFMA), row sum, bf16 P into shared memory (UMMA K-major, 128B swizzle)
-      if (!PT && j >= 1) mbar_wait(&pv_done[t], (j - 1) & 1);  // PV_t(j-1) has finished reading the smem P buffer
-      uint8_t* prow = sP + t * Cfg::P_BYTES + r * 128;
-      const float2 sc2 = make_float2(p.scale_log2, p.scale_log2);
-      const float2 nm2 = make_float2(-m, -m);
-      float2 sum2 = make_float2(0.f, 0.f);
-#pragma unroll 1
-      for (int c2 = 0; c2 < 2; ++c2) {
-        uint32_t ra[32], rb[32];
-        SPB_TMEM_LD_32(tS + (uint32_t)(c2 * 64), ra);
-        SPB_TMEM_LD_32(tS + (uint32_t)(c2 * 64 + 32), rb);
+      return fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+    };
+    for (int j = 0; j < n_kv; ++j) {
+#pragma unroll
+      for (int t = 0; t < NT; ++t) {
+        if (j >= n_kv_t[t]) continue;  // CTA-uniform
+        const uint32_t tS = lane_base + (uint32_t)(t * 128 + half * 64);
+        const uint32_t tP = lane_base + (uint32_t)(t * 128 + half * 32);
+        const uint32_t tO = lane_base + (uint32_t)(Cfg::TM_O0 + t * 128 + half * Cfg::OH);
+        FA_TRACE_S(20 + t);  // start waiting for S_t
+        mbar_wait(&s_full[t], j & 1);
+        FA_TRACE_S(22 + t);  // S_t seen
+        tc_fence_after();
+        uint32_t s[64];
+        SPB_TMEM_LD_32(tS, s);
+        SPB_TMEM_LD_32(tS + 32u, (s + 32));
         tmem_ld_wait();
-        const int lim = need_mask ? n_valid - c2 * 64 : 64;
-        uint32_t pk[32];  // 64 bf16
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          const float2 xa = __ffma2_rn(make_float2(__uint_as_float(ra[i]), __uint_as_float(ra[i + 1])), sc2, nm2);
-          const float2 xb = __ffma2_rn(make_float2(__uint_as_float(rb[i]), __uint_as_float(rb[i + 1])), sc2, nm2);
-          float2 pa = make_float2(fast_exp2(xa.x), fast_exp2(xa.y));
-          float2 pb = make_float2(fast_exp2(xb.x), fast_exp2(xb.y));
-          if (need_mask) {
-            if (i >= lim) pa.x = 0.f;
-            if (i + 1 >= lim) pa.y = 0.f;
-            if (i + 32 >= lim) pb.x = 0.f;
-            if (i + 33 >= lim) pb.y = 0.f;
-          }
-          sum2 = __fadd2_rn(sum2, __fadd2_rn(pa, pb));
-          pk[i >> 1] = pack_bf16(pa.x, pa.y);
-          pk[16 + (i >> 1)] = pack_bf16(pb.x, pb.y);
-        }
-        if (PT) {
-          // P words 32*c2 .. 32*c2+31 overwrite S columns this thread has already consumed (S cols 0..63 are in registers
-          // or done when c2 = 0; cols 32..63 were consumed in the c2 = 0 round)
-          SPB_TMEM_ST_32(tS + (uint32_t)(c2 * 32), pk);
+        bool need_mask;
+        int n_valid;
+        geometry(j, t, need_mask, n_valid);
+        const float mine = row_max(s, need_mask, n_valid);
+        FA_TRACE_S(25);  // local max done
+        // the barrier inside also orders every S load of this tile before any P store below (P aliases S)
+        const float tmax = fmaxf(mine, exchange(mine)) * p.scale_log2;
+        FA_TRACE_S(26);  // exchanged
+        float m = m_t[t];
+        if (j == 0) {
+          m = tmax;
         } else {
+          // lazy rescale: keep the stale max while the true max is at most 2^8 above it (p <= 256, harmless in fp32/bf16);
+          // both threads of a row see the same tmax and take the same decision
+          const bool grow = tmax > m + 8.0f;
+          if (__any_sync(0xffffffffu, grow)) {
+            float alpha = 1.0f;
+            if (grow) {
+              alpha = fast_exp2(m - tmax);
+              m = tmax;
+            }
+            l_t[t] *= alpha;
+            mbar_wait(&pv_done[t], (j - 1) & 1);  // O_t must hold every PV issued so far
+            tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < Cfg::OH / 16; ++c) {
+              uint32_t o[16];
+              SPB_TMEM_LD_16(tO + (uint32_t)(c * 16), o);
+              tmem_ld_wait();
 #pragma unroll
-          for (int u = 0; u < 8; ++u)
-            *reinterpret_cast<uint4*>(prow + c2 * Cfg::CHUNK_BYTES + ((u ^ (r & 7)) << 4)) =
-                make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+              for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+              SPB_TMEM_ST_16(tO + (uint32_t)(c * 16), o);
+            }
+            tmem_st_wait();
+          }
         }
-      }
-      if (PT) tmem_st_wait();
-      const float sum = sum2.x + sum2.y;
-      l += sum;
-      tc_fence_before();
-      if (!PT) fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
-      __syncwarp();
-      if (lane == 0) {
-        if (!PT) mbar_arrive(&s_empty[t]);  // S_t may be overwritten by QK^T of the next KV tile
-        mbar_arrive(&p_full[t]);
+        m_t[t] = m;
+        // ---- p = exp2(s*c - m) (packed fp32x2 FFMA), row sum, bf16 P -> tensor memory words [half*32, half*32+32) of S_t.
+        // The exp phase is bound by the 16/clk/SM MUFU pipe, so every FA_POLY_EVERY-th group of four sends one pair through
+        // a degree-3 polynomial on the FMA pipe instead (fa_exp2_poly2: 7.5e-5 relative error, far below P's bf16 rounding)
+        const float2 sc2 = make_float2(p.scale_log2, p.scale_log2);
+        const float2 nm2 = make_float2(-m, -m);
+        float2 sum2 = make_float2(0.f, 0.f), sum2b = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {  // 32 columns -> 16 packed words per tcgen05.st
+          uint32_t pk[16];
+          int mode = 0;  // 0 = all 32 visible, 1 = masked per element, 2 = none visible (warp-uniform)
+          const int lq = n_valid - 32 * q;
+          if (need_mask) mode = __all_sync(0xffffffffu, lq >= 32) ? 0 : (__all_sync(0xffffffffu, lq <= 0) ? 2 : 1);
+          if (mode == 0) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              const float2 xa = __ffma2_rn(make_float2(__uint_as_float(s[32 * q + i]), __uint_as_float(s[32 * q + i + 1])), sc2, nm2);
+              const float2 xb = __ffma2_rn(make_float2(__uint_as_float(s[32 * q + i + 2]), __uint_as_float(s[32 * q + i + 3])), sc2, nm2);
+              const float2 pa = make_float2(fast_exp2(xa.x), fast_exp2(xa.y));
+              const float2 pb = (FA_POLY_EVERY > 0 && ((i >> 2) % (FA_POLY_EVERY > 0 ? FA_POLY_EVERY : 1)) == 0)
+                                    ? fa_exp2_poly2(xb)
+                                    : make_float2(fast_exp2(xb.x), fast_exp2(xb.y));
+              sum2 = __fadd2_rn(sum2, pa);
+              sum2b = __fadd2_rn(sum2b, pb);
+              pk[i >> 1] = pack_bf16(pa.x, pa.y);
+              pk[(i >> 1) + 1] = pack_bf16(pb.x, pb.y);
+            }
+          } else if (mode == 1) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              const float2 xa = __ffma2_rn(make_float2(__uint_as_float(s[32 * q + i]), __uint_as_float(s[32 * q + i + 1])), sc2, nm2);
+              float2 pa = make_float2(fast_exp2(xa.x), fast_exp2(xa.y));
+              if (i >= lq) pa.x = 0.f;
+              if (i + 1 >= lq) pa.y = 0.f;
+              sum2 = __fadd2_rn(sum2, pa);
+              pk[i >> 1] = pack_bf16(pa.x, pa.y);
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) pk[i] = 0u;
+          }
+          SPB_TMEM_ST_16(tP + (uint32_t)(q * 16), pk);
+        }
+        FA_TRACE_S(27);  // exp done
+        tmem_st_wait();
+        FA_TRACE_S(28);  // P stored
+        sum2 = __fadd2_rn(sum2, sum2b);
+        l_t[t] += sum2.x + sum2.y;
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_full[t]);
+        FA_TRACE_S(29);  // arrived
       }
     }
-    // epilogue: O / l -> bf16 -> global; lse = m*ln2 + ln(l)
-    if (n_mine > 0) {
+    // epilogue: O / l -> bf16 -> global (each thread its hd/2 columns); lse = m*ln2 + ln(l)
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      const int n_mine = n_kv_t[t];
+      if (n_mine == 0) continue;  // CTA-uniform
+      const float l = l_t[t] + exchange(l_t[t]);
+      const uint32_t tO = lane_base + (uint32_t)(Cfg::TM_O0 + t * 128 + half * Cfg::OH);
+      const int q_idx = q0 + t * 128 + r;
       mbar_wait(&pv_done[t], (n_mine - 1) & 1);
       tc_fence_after();
       const float inv = 1.0f / l;
       const bool valid = q_idx < p.T;
-      __nv_bfloat16* orow = p.o + ((int64_t)b * p.T + q_idx) * p.ldo + (int64_t)h * HD;
+      __nv_bfloat16* orow = p.o + ((int64_t)b * p.T + q_idx) * p.ldo + (int64_t)h * HD + half * Cfg::OH;
 #pragma unroll
-      for (int c = 0; c < HD / 32; ++c) {
+      for (int c = 0; c < Cfg::OH / 32; ++c) {
         uint32_t o[32];
         SPB_TMEM_LD_32(tO + (uint32_t)(c * 32), o);
         tmem_ld_wait();
@@ -371,7 +445,7 @@ __global__ void __launch_bounds__(FaFwdCfg<HD, PT>::THREADS, 1)
           }
         }
       }
-      if (valid) p.lse[((int64_t)b * p.Hq + h) * p.T + q_idx] = m * LN2 + logf(l);
+      if (valid && half == 0) p.lse[((int64_t)b * p.Hq + h) * p.T + q_idx] = m_t[t] * LN2 + logf(l);
     }
   }
 
@@ -389,10 +463,10 @@ static int fa_check_operand(const void* ptr, int64_t ld, const char* name) {
   return 0;
 }
 
-template <int HD, bool PT>
+template <int HD>
 static int flash_fwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float scale, const void* q, int64_t ldq, const void* k,
                                int64_t ldk, const void* v, int64_t ldv, void* o, int64_t ldo, float* lse, cudaStream_t st) {
-  using Cfg = FaFwdCfg<HD, PT>;
+  using Cfg = FaFwdCfg<HD>;
   CUtensorMap tmQ, tmK, tmV;
   int rc;
   const uint64_t rows = (uint64_t)B * Tn;
@@ -408,10 +482,11 @@ static int flash_fwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
   a.Hkv = Hkv;
   a.causal = causal;
   a.scale_log2 = scale * LOG2E;
-  SPB_CUDA(cudaFuncSetAttribute(flash_fwd_tc_kernel<HD, PT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+  SPB_CUDA(cudaFuncSetAttribute(flash_fwd_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
   SPB_CHECK_ARG(scale > 0.f, SPB_E_INVALID, "flash forward (tcgen05): scale must be positive");
-  dim3 grid((Tn + Cfg::NT * 128 - 1) / (Cfg::NT * 128), Hq, B);
-  flash_fwd_tc_kernel<HD, PT><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(tmQ, tmK, tmV, a);
+  SPB_CHECK_ARG(B <= 65535 && (Tn + Cfg::NT * 128 - 1) / (Cfg::NT * 128) <= 65535, SPB_E_LIMIT, "flash forward (tcgen05): B or T/256 beyond 65535");
+  dim3 grid(Hq, B, (Tn + Cfg::NT * 128 - 1) / (Cfg::NT * 128));
+  flash_fwd_tc_kernel<HD><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(tmQ, tmK, tmV, a);
   SPB_LAUNCH_CHECK();
   return 0;
 }
@@ -422,15 +497,24 @@ int flash_fwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale
   if ((rc = fa_check_operand(q, ldq, "q")) || (rc = fa_check_operand(k, ldk, "k")) || (rc = fa_check_operand(v, ldv, "v")) ||
       (rc = fa_check_operand(o, ldo, "o")))
     return rc;
-  static const bool p_smem = getenv("SPB_FA_PSMEM") != nullptr;  // A/B switch for timing experiments: keep P in shared memory
-#define SPB_FA_GO(H)                                                                                                         \
-  return p_smem ? flash_fwd_tc_launch<H, false>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st)          \
-                : flash_fwd_tc_launch<H, true>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st)
-  if (hd == 128) SPB_FA_GO(128);
-  if (hd == 64) SPB_FA_GO(64);
-  if (hd == 256) SPB_FA_GO(256);
-#undef SPB_FA_GO
+  if (hd == 128) return flash_fwd_tc_launch<128>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
+  if (hd == 64) return flash_fwd_tc_launch<64>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
+  if (hd == 256) return flash_fwd_tc_launch<256>(B, Tn, Hq, Hkv, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
   SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "flash forward (tcgen05): hd %d", hd);
 }
 
 }  // namespace spb
+
+#ifdef SPB_FA_TRACE
+extern "C" int spb_debug_fa_trace_read(unsigned long long* dst, int n) {
+  const int total = spb::FA_TRACE_ROLES * spb::FA_TRACE_EVENTS;
+  if (n > total) n = total;
+  return (int)cudaMemcpyFromSymbol(dst, spb::g_fa_trace, sizeof(unsigned long long) * n);
+}
+extern "C" int spb_debug_fa_trace_clear() {
+  void* p = nullptr;
+  cudaError_t e = cudaGetSymbolAddress(&p, spb::g_fa_trace);
+  if (e != cudaSuccess) return (int)e;
+  return (int)cudaMemset(p, 0, sizeof(unsigned long long) * spb::FA_TRACE_ROLES * spb::FA_TRACE_EVENTS);
+}
+#endif
