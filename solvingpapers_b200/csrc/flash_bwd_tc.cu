@@ -31,6 +31,21 @@
 
 namespace spb {
 
+// Timeline tracing for kernel development (tools/diag_trace_bwd.py): compiled in only with -DSPB_FB_TRACE, into a separate
+// library; CTA (0,0,0) logs (clock, event id) per role.  The product build contains none of it.
+#ifdef SPB_FB_TRACE
+constexpr int FB_TRACE_ROLES = 4, FB_TRACE_EVENTS = 4096;
+__device__ unsigned long long g_fb_trace[FB_TRACE_ROLES * FB_TRACE_EVENTS];
+#define FB_TRACE_DECL(role, keep) int tr_n = 0; const bool tr_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (keep)); const int tr_role = (role)
+#define FB_TRACE(id)                                                                                                  \
+  do {                                                                                                                \
+    if (tr_on && tr_n < FB_TRACE_EVENTS) g_fb_trace[tr_role * FB_TRACE_EVENTS + tr_n++] = ((unsigned long long)clock64() << 8) | (unsigned)(id); \
+  } while (0)
+#else
+#define FB_TRACE_DECL(role, keep)
+#define FB_TRACE(id)
+#endif
+
 constexpr int FB_AGROUPS = 2;                         // element-wise warpgroups; each owns 64 / FB_AGROUPS query columns
 constexpr int FB_ACOLS = 64 / FB_AGROUPS;
 constexpr int FB_ATHREADS = FB_AGROUPS * 128;
@@ -173,6 +188,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
+    FB_TRACE_DECL(0, true);
     if (lane == 0) {
       const int row_kv = b * p.T + kv0;
       mbar_arrive_expect_tx(kv_full, Cfg::CH * 16384 * 2);
@@ -187,6 +203,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         const int h = g * n_rep + it / n_i;
         const int row_q = b * p.T + (i_start + it % n_i) * 64;
         mbar_wait(&qdo_empty[st], u ^ 1);
+        FB_TRACE(1);
         mbar_arrive_expect_tx(&qdo_full[st], 2 * Cfg::Q_BYTES);
 #pragma unroll
         for (int c = 0; c < Cfg::CH; ++c) {
@@ -197,57 +214,67 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // ------------------------------------------------------------------ MMA issuer (whole warp, uniform; one elected lane issues)
+    FB_TRACE_DECL(1, true);
+    {
       const uint32_t idesc_s = umma_idesc_bf16(128, 64, 0, 0);
       const uint32_t idesc_g = umma_idesc_bf16(128, Cfg::HDZ, 0, 1);
       const uint32_t idesc_q = umma_idesc_bf16(128, 64, 1, 1);
       const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV);
+      // descriptors: built once; a k-step only adds a constant to the 14-bit start-address field (no carry out of it:
+      // shared-memory addresses stay below 256 KB)
+      const uint64_t dK_k = umma_desc_kmajor(k_addr), dV_k = umma_desc_kmajor(v_addr);
+      const uint64_t dK_mn = umma_desc_mnmajor(k_addr + z * Cfg::ZCH * 16384, 128);
+      const uint64_t dPT = umma_desc_kmajor(smem_u32(sPT)), dDST_k = umma_desc_kmajor(smem_u32(sDST));
+      const uint64_t dDST_mn = umma_desc_mnmajor(smem_u32(sDST), 128);
       mbar_wait(kv_full, 0);
       auto issue_s = [&](int it) {
         const int st = it % NS;
         mbar_wait(&qdo_full[st], (it / NS) & 1);
+        FB_TRACE(10);
         mbar_wait(sdp_empty, (it & 1) ^ 1);
+        FB_TRACE(11);
         tc_fence_after();
-        const uint32_t q_addr = smem_u32(sQ + st * Cfg::Q_BYTES), do_addr = smem_u32(sDO + st * Cfg::Q_BYTES);
+        const uint64_t dQ_k = umma_desc_kmajor(smem_u32(sQ + st * Cfg::Q_BYTES)), dDO_k = umma_desc_kmajor(smem_u32(sDO + st * Cfg::Q_BYTES));
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
           const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
-          umma_bf16(tmem_base + Cfg::TM_ST, umma_desc_kmajor(k_addr + aoff), umma_desc_kmajor(q_addr + boff), idesc_s, kk > 0 ? 1u : 0u);
+          umma_bf16_w(tmem_base + Cfg::TM_ST, dK_k + (aoff >> 4), dQ_k + (boff >> 4), idesc_s, kk > 0 ? 1u : 0u);
         }
         if (!(p.ablate & 16))
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
           const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
-          umma_bf16(tmem_base + Cfg::TM_DPT, umma_desc_kmajor(v_addr + aoff), umma_desc_kmajor(do_addr + boff), idesc_s, kk > 0 ? 1u : 0u);
+          umma_bf16_w(tmem_base + Cfg::TM_DPT, dV_k + (aoff >> 4), dDO_k + (boff >> 4), idesc_s, kk > 0 ? 1u : 0u);
         }
-        umma_commit(sdp_full);
+        umma_commit_w(sdp_full);
+        FB_TRACE(12);
       };
       auto issue_g = [&](int it) {
         const int st = it % NS;
         mbar_wait(pds_full, it & 1);
+        FB_TRACE(13);
         mbar_wait(dq_empty, (it & 1) ^ 1);
+        FB_TRACE(14);
         tc_fence_after();
-        const uint32_t q_addr = smem_u32(sQ + st * Cfg::Q_BYTES), do_addr = smem_u32(sDO + st * Cfg::Q_BYTES);
-        const uint32_t pt_addr = smem_u32(sPT), dst_addr = smem_u32(sDST);
+        const uint64_t dDO_mn = umma_desc_mnmajor(smem_u32(sDO + st * Cfg::Q_BYTES) + z * Cfg::ZCH * 8192, 64);
+        const uint64_t dQ_mn = umma_desc_mnmajor(smem_u32(sQ + st * Cfg::Q_BYTES) + z * Cfg::ZCH * 8192, 64);
         if (!(p.ablate & 1))
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dV += P^T dO
-          umma_bf16(tmem_base + Cfg::TM_DV, umma_desc_kmajor(pt_addr + kk * 32), umma_desc_mnmajor(do_addr + z * Cfg::ZCH * 8192 + kk * 2048, 64), idesc_g,
-                    (it > 0 || kk > 0) ? 1u : 0u);
+          umma_bf16_w(tmem_base + Cfg::TM_DV, dPT + ((kk * 32) >> 4), dDO_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
         if (!(p.ablate & 2))
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dK += dS^T Q
-          umma_bf16(tmem_base + Cfg::TM_DK, umma_desc_kmajor(dst_addr + kk * 32), umma_desc_mnmajor(q_addr + z * Cfg::ZCH * 8192 + kk * 2048, 64), idesc_g,
-                    (it > 0 || kk > 0) ? 1u : 0u);
+          umma_bf16_w(tmem_base + Cfg::TM_DK, dDST_k + ((kk * 32) >> 4), dQ_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
         if (!(p.ablate & 4))
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)  // dQ^T = K^T dS
-          umma_bf16(tmem_base + Cfg::TM_DQT, umma_desc_mnmajor(k_addr + z * Cfg::ZCH * 16384 + kk * 2048, 128), umma_desc_mnmajor(dst_addr + kk * 2048, 128),
-                    idesc_q, kk > 0 ? 1u : 0u);
-        umma_commit(&qdo_empty[st]);
-        umma_commit(pds_empty);
-        umma_commit(dq_full);
+          umma_bf16_w(tmem_base + Cfg::TM_DQT, dK_mn + ((kk * 2048) >> 4), dDST_mn + ((kk * 2048) >> 4), idesc_q, kk > 0 ? 1u : 0u);
+        umma_commit_w(&qdo_empty[st]);
+        umma_commit_w(pds_empty);
+        umma_commit_w(dq_full);
+        FB_TRACE(15);
       };
       issue_s(0);
       for (int it = 0; it < n_it; ++it) {
@@ -284,6 +311,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       if (ct < 64) sLse[(it & 1) * 64 + ct] = v * FB_LOG2E;
       else if (ct < 128) sDelta[(it & 1) * 64 + (ct - 64)] = v;
     };
+    FB_TRACE_DECL(2, warp == 2);
     put_stat(0, fetch_stat(0));
     const float2 sc2 = make_float2(p.scale_log2, p.scale_log2);
     const float2 scale2 = make_float2(p.scale, p.scale);
@@ -292,8 +320,9 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       const int q0 = (i_start + it % n_i) * 64;
       const float stat_next = fetch_stat(it + 1);
       asm volatile("bar.sync 1, %0;" ::"n"(FB_ATHREADS) : "memory");  // stage st is complete; stage st^1 is no longer being read
-
+      FB_TRACE(20);
       mbar_wait(sdp_full, it & 1);
+      FB_TRACE(21);
       tc_fence_after();
       uint32_t rs[FB_ACOLS], rd[FB_ACOLS];
       if (FB_ACOLS == 32) {
@@ -307,6 +336,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(sdp_empty);  // S^T / dP^T may be overwritten by iteration it+1
+      FB_TRACE(22);
 
       const bool need_mask = (p.causal && q0 < kv0 + 128) || (q0 + 64 > p.T) || (kv0 + 128 > p.T);
       const float2* lse2 = reinterpret_cast<const float2*>(sLse + st * 64 + cbase);
@@ -341,8 +371,10 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       } else {
         elementwise(std::false_type{});
       }
+      FB_TRACE(23);
       put_stat(it + 1, stat_next);  // visible to everyone after the next iteration's bar.sync
-      mbar_wait(pds_empty, (it & 1) ^ 1);  // the MMA group of iteration it-1 has finished reading P^T / dS^T
+      mbar_wait(pds_empty, (it & 1) ^ 1);
+      FB_TRACE(24);  // the MMA group of iteration it-1 has finished reading P^T / dS^T
       uint8_t* prow = sPT + r * 128;
       uint8_t* drow = sDST + r * 128;
 #pragma unroll
@@ -355,6 +387,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(pds_full);
+      FB_TRACE(25);
     }
     // ---- epilogue: group 0 stores dV, group 1 stores dK (rows -> bf16 -> global).  The last pds_empty commit covers
     // every MMA issued before it.
@@ -396,11 +429,13 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
     const int qd = warp & 3;
     const int r = qd * 32 + lane;  // hd column of dQ = TMEM lane of dQ^T
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
+    FB_TRACE_DECL(3, qd == 0);
     if (qd < Cfg::DQ_WARPS) {  // warp-uniform (hd=64: only two warps hold real rows)
       for (int it = 0; it < n_it; ++it) {
         const int h = g * n_rep + it / n_i;
         const int q0 = (i_start + it % n_i) * 64;
         mbar_wait(dq_full, it & 1);
+        FB_TRACE(30);
         tc_fence_after();
         float dq[64];
 #pragma unroll
@@ -414,6 +449,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(dq_empty);  // dQ^T may be overwritten by iteration it+1 while the reduction is in flight
+        FB_TRACE(31);
         // transpose through shared memory ([q][d] fp32, lanes write consecutive d: conflict-free) and let the TMA engine do
         // ONE bulk reduce-add of the 64 x hd tile into the fp32 dq accumulator (per-thread fp32 atomics were the v2
         // bottleneck: ~1 float atomic / clk / SM).  Rows past the sequence end hold exact zeros (their P^T is masked).
@@ -434,10 +470,12 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         for (int i = 0; i < 64; ++i) sDQ[i * Cfg::HDZ + r] = dq[i];
         fence_proxy_async_smem();
         asm volatile("bar.sync 2, %0;" ::"n"(NB) : "memory");
+        FB_TRACE(32);
         if (leader) {
           tma_reduce_add_2d(&tmDQ, sDQ, h * HD + z * Cfg::HDZ, b * p.T + q0);
           tma_store_commit();
         }
+        FB_TRACE(33);
       }
       if (qd == 0 && lane == 0) tma_store_wait_read<0>();
     }
@@ -586,3 +624,17 @@ int flash_bwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale
 }
 
 }  // namespace spb
+
+#ifdef SPB_FB_TRACE
+extern "C" int spb_debug_fb_trace_read(unsigned long long* dst, int n) {
+  const int total = spb::FB_TRACE_ROLES * spb::FB_TRACE_EVENTS;
+  if (n > total) n = total;
+  return (int)cudaMemcpyFromSymbol(dst, spb::g_fb_trace, sizeof(unsigned long long) * n);
+}
+extern "C" int spb_debug_fb_trace_clear() {
+  void* p = nullptr;
+  cudaError_t e = cudaGetSymbolAddress(&p, spb::g_fb_trace);
+  if (e != cudaSuccess) return (int)e;
+  return (int)cudaMemset(p, 0, sizeof(unsigned long long) * spb::FB_TRACE_ROLES * spb::FB_TRACE_EVENTS);
+}
+#endif

@@ -207,9 +207,9 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
+    // ------------------------------------------------------------------ MMA issuer (whole warp, uniform; one elected lane issues)
     FA_TRACE_DECL(1);
-    if (lane == 0) {
+    {
       const uint32_t idesc_qk = umma_idesc_bf16(128, 128, 0, 0);  // A = Q (K-major), B = K (K-major)
       const uint32_t idesc_pv = umma_idesc_bf16(128, HD, 0, 1);   // A = P (tensor memory), B = V (MN-major: hd contiguous)
       mbar_wait(q_full, 0);
@@ -217,14 +217,14 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
         if (j >= n_kv_t[t]) return;
         // S_t is free: PV_t(j-1), issued earlier on this in-order pipe, was the last reader of the P that aliases it
         tc_fence_after();
-        const uint32_t q_addr = smem_u32(sQ + t * Cfg::TILE_BYTES);
-        const uint32_t k_addr = smem_u32(sK + (j % KST) * Cfg::TILE_BYTES);
+        const uint64_t dq = umma_desc_kmajor(smem_u32(sQ + t * Cfg::TILE_BYTES));
+        const uint64_t dk = umma_desc_kmajor(smem_u32(sK + (j % KST) * Cfg::TILE_BYTES));
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
           const uint32_t off = (kk >> 2) * Cfg::CHUNK_BYTES + (kk & 3) * 32;
-          umma_bf16(tmem_base + t * 128, umma_desc_kmajor(q_addr + off), umma_desc_kmajor(k_addr + off), idesc_qk, kk > 0 ? 1u : 0u);
+          umma_bf16_w(tmem_base + t * 128, dq + (off >> 4), dk + (off >> 4), idesc_qk, kk > 0 ? 1u : 0u);
         }
-        umma_commit(&s_full[t]);
+        umma_commit_w(&s_full[t]);
         FA_TRACE(10 + t);  // QK_t issued
       };
       auto pv_t = [&](int j, int t) {  // O_t += P_t V(j)
@@ -232,12 +232,12 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
         mbar_wait(&p_full[t], j & 1);
         FA_TRACE(12 + t);  // p_full[t] seen
         tc_fence_after();
-        const uint32_t v_addr = smem_u32(sV + (j % VST) * Cfg::TILE_BYTES);
+        const uint64_t dv = umma_desc_mnmajor(smem_u32(sV + (j % VST) * Cfg::TILE_BYTES), 128);
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)  // A = P_t from tensor memory: 16 bf16 of K per 8 columns
-          umma_bf16_ts(tmem_base + Cfg::TM_O0 + t * 128, tmem_base + t * 128 + kk * 8, umma_desc_mnmajor(v_addr + kk * 2048, 128),
-                       idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
-        umma_commit(&pv_done[t]);
+          umma_bf16_ts_w(tmem_base + Cfg::TM_O0 + t * 128, tmem_base + t * 128 + kk * 8, dv + ((kk * 2048) >> 4), idesc_pv,
+                         (j > 0 || kk > 0) ? 1u : 0u);
+        umma_commit_w(&pv_done[t]);
         FA_TRACE(14 + t);  // PV_t issued
       };
       // issue order per KV tile j:  PV0(j) QK0(j+1) PV1(j) QK1(j+1)  - the softmax crew alternates between the tiles in
@@ -245,7 +245,7 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
       mbar_wait(&k_full[0], 0);
       qk_t(0, 0);
       if (NT == 2) qk_t(0, 1);
-      umma_commit(&k_empty[0]);
+      umma_commit_w(&k_empty[0]);
       for (int j = 0; j < n_kv; ++j) {
         const bool more = j + 1 < n_kv;
         mbar_wait(&v_full[j % VST], (j / VST) & 1);
@@ -259,9 +259,9 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
         if (NT == 2) pv_t(j, 1);
         if (more) {
           if (NT == 2) qk_t(j + 1, 1);
-          umma_commit(&k_empty[(j + 1) % KST]);
+          umma_commit_w(&k_empty[(j + 1) % KST]);
         }
-        umma_commit(&v_empty[j % VST]);
+        umma_commit_w(&v_empty[j % VST]);
       }
     }
     __syncwarp();

@@ -290,8 +290,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // ------------------------------------------------------------------ MMA issuer (whole warp, uniform; one elected lane issues)
+    {
       const uint32_t idesc = umma_idesc_bf16(GT_BM, BN, p.a_mn, p.b_mn);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
@@ -306,16 +306,17 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
           tc_fence_after();
           const uint32_t a_addr = smem_u32(sA + stage * Cfg::A_BYTES);
           const uint32_t b_addr = smem_u32(sB + stage * Cfg::B_BYTES);
+          // descriptor of the stage's first k-step; a k-step adds a constant to the start-address field
+          const uint64_t adesc0 = p.a_mn ? umma_desc_mnmajor(a_addr, GT_BK) : umma_desc_kmajor(a_addr);
+          const uint64_t bdesc0 = p.b_mn ? umma_desc_mnmajor(b_addr, GT_BK) : umma_desc_kmajor(b_addr);
+          const uint32_t astep = p.a_mn ? (2048u >> 4) : (32u >> 4), bstep = p.b_mn ? (2048u >> 4) : (32u >> 4);
 #pragma unroll
-          for (int k = 0; k < GT_BK / 16; ++k) {
-            const uint64_t adesc = p.a_mn ? umma_desc_mnmajor(a_addr + k * 2048, GT_BK) : umma_desc_kmajor(a_addr + k * 32);
-            const uint64_t bdesc = p.b_mn ? umma_desc_mnmajor(b_addr + k * 2048, GT_BK) : umma_desc_kmajor(b_addr + k * 32);
-            umma_bf16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-          }
-          umma_commit(&empty[stage]);  // frees the smem slot when these MMAs have read it
+          for (int k = 0; k < GT_BK / 16; ++k)
+            umma_bf16_w(d_tmem, adesc0 + (uint64_t)(k * astep), bdesc0 + (uint64_t)(k * bstep), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          umma_commit_w(&empty[stage]);  // frees the smem slot when these MMAs have read it
           if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull[acc]);  // accumulator complete -> epilogue
+        umma_commit_w(&tfull[acc]);  // accumulator complete -> epilogue
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
@@ -462,8 +463,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer (leader CTA only)
-    if (lane == 0 && rank == 0) {
+    // ------------------------------------------------------------------ MMA issuer (leader CTA only; whole warp, one elected lane issues)
+    if (rank == 0) {
       const uint32_t idesc = umma_idesc_bf16(256, BN, p.a_mn, p.b_mn);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
@@ -478,16 +479,16 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
           tc_fence_after();
           const uint32_t a_addr = smem_u32(sA + stage * Cfg::A_BYTES);
           const uint32_t b_addr = smem_u32(sB + stage * Cfg::B_BYTES);
+          const uint64_t adesc0 = p.a_mn ? umma_desc_mnmajor(a_addr, GT_BK) : umma_desc_kmajor(a_addr);
+          const uint64_t bdesc0 = p.b_mn ? umma_desc_mnmajor(b_addr, GT_BK) : umma_desc_kmajor(b_addr);
+          const uint32_t astep = p.a_mn ? (2048u >> 4) : (32u >> 4), bstep = p.b_mn ? (2048u >> 4) : (32u >> 4);
 #pragma unroll
-          for (int k = 0; k < GT_BK / 16; ++k) {
-            const uint64_t adesc = p.a_mn ? umma_desc_mnmajor(a_addr + k * 2048, GT_BK) : umma_desc_kmajor(a_addr + k * 32);
-            const uint64_t bdesc = p.b_mn ? umma_desc_mnmajor(b_addr + k * 2048, GT_BK) : umma_desc_kmajor(b_addr + k * 32);
-            umma_bf16_2sm(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-          }
-          umma_commit_2sm_mc(&empty[stage], 3);  // frees the slot in BOTH CTAs
+          for (int k = 0; k < GT_BK / 16; ++k)
+            umma_bf16_2sm_w(d_tmem, adesc0 + (uint64_t)(k * astep), bdesc0 + (uint64_t)(k * bstep), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          umma_commit_2sm_mc_w(&empty[stage], 3);  // frees the slot in BOTH CTAs
           if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit_2sm_mc(&tfull[acc], 3);  // accumulators complete -> both epilogues
+        umma_commit_2sm_mc_w(&tfull[acc], 3);  // accumulators complete -> both epilogues
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
