@@ -79,8 +79,7 @@ struct FaBwdCfg {
   static constexpr int NSTAGE = (HD == 128) ? 3 : (HD == 64 ? 4 : 1);  // hd=256: K, V (128 KB) leave room for one 64 KB stage
   static constexpr int OFF_Q = OFF_V + V_BYTES;
   static constexpr int OFF_DO = OFF_Q + NSTAGE * Q_BYTES;
-  static constexpr int OFF_PT = OFF_DO + NSTAGE * Q_BYTES;
-  static constexpr int OFF_DST = OFF_PT + PT_BYTES;
+  static constexpr int OFF_DST = OFF_DO + NSTAGE * Q_BYTES;   // dS^T in shared memory: only the dQ^T MMA reads it (as its B operand)
   static constexpr int OFF_DQS = OFF_DST + PT_BYTES;      // fp32 [64 q rows][HD] staging tile for the TMA reduce-add of dQ
   static constexpr bool USE_DQS = (HD != 256);     // hd=256 has no room for the staging tile: coalesced fp32 atomics instead
   static constexpr int DQS_BYTES = USE_DQS ? 64 * HD * 4 : 0;
@@ -88,6 +87,10 @@ struct FaBwdCfg {
   static constexpr int OFF_BAR = OFF_LSE + 4 * 64 * 4;
   static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
   static constexpr int TM_ST = 0, TM_DPT = 64, TM_DV = 128, TM_DK = 256, TM_DQT = 384;
+  // bf16 P^T and dS^T (128 kv lanes x 64 q = 32 packed columns each): the A operands of the dV / dK MMAs come from tensor
+  // memory, not shared memory - the kernel is bound by shared-memory bandwidth (~340 KB of operand, staging and TMA traffic
+  // per iteration at ~128 B/clk; r01 ablations), and this takes 48 KB per iteration off it
+  static constexpr int TM_P = 448, TM_DS = 480;
   static constexpr int TMEM_COLS = 512;
   static constexpr int DQ_WARPS = HDZ / 32;        // warps that own a valid hd row of dQ^T
 };
@@ -120,7 +123,6 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
   uint8_t* sV = smem + Cfg::OFF_V;
   uint8_t* sQ = smem + Cfg::OFF_Q;
   uint8_t* sDO = smem + Cfg::OFF_DO;
-  uint8_t* sPT = smem + Cfg::OFF_PT;
   uint8_t* sDST = smem + Cfg::OFF_DST;
   float* sDQ = reinterpret_cast<float*>(smem + Cfg::OFF_DQS);
   float* sLse = reinterpret_cast<float*>(smem + Cfg::OFF_LSE);  // [2][64]
@@ -225,7 +227,6 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       // shared-memory addresses stay below 256 KB)
       const uint64_t dK_k = umma_desc_kmajor(k_addr), dV_k = umma_desc_kmajor(v_addr);
       const uint64_t dK_mn = umma_desc_mnmajor(k_addr + z * Cfg::ZCH * 16384, 128);
-      const uint64_t dPT = umma_desc_kmajor(smem_u32(sPT)), dDST_k = umma_desc_kmajor(smem_u32(sDST));
       const uint64_t dDST_mn = umma_desc_mnmajor(smem_u32(sDST), 128);
       mbar_wait(kv_full, 0);
       auto issue_s = [&](int it) {
@@ -262,11 +263,11 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         if (!(p.ablate & 1))
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dV += P^T dO
-          umma_bf16_w(tmem_base + Cfg::TM_DV, dPT + ((kk * 32) >> 4), dDO_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
+          umma_bf16_ts_w(tmem_base + Cfg::TM_DV, tmem_base + Cfg::TM_P + kk * 8, dDO_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
         if (!(p.ablate & 2))
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dK += dS^T Q
-          umma_bf16_w(tmem_base + Cfg::TM_DK, dDST_k + ((kk * 32) >> 4), dQ_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
+          umma_bf16_ts_w(tmem_base + Cfg::TM_DK, tmem_base + Cfg::TM_DS + kk * 8, dQ_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
         if (!(p.ablate & 4))
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)  // dQ^T = K^T dS
@@ -375,14 +376,18 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       put_stat(it + 1, stat_next);  // visible to everyone after the next iteration's bar.sync
       mbar_wait(pds_empty, (it & 1) ^ 1);
       FB_TRACE(24);  // the MMA group of iteration it-1 has finished reading P^T / dS^T
-      uint8_t* prow = sPT + r * 128;
+      static_assert(FB_ACOLS == 32, "the tensor-memory stores below move 16 packed words per thread");
+      // P^T and dS^T -> tensor memory (A operands of the dV / dK MMAs): lane = kv row, word w = query columns 2w, 2w+1
+      SPB_TMEM_ST_16(lane_base + (uint32_t)(Cfg::TM_P + cbase / 2), pkp);
+      SPB_TMEM_ST_16(lane_base + (uint32_t)(Cfg::TM_DS + cbase / 2), pkd);
+      // dS^T also -> shared memory (UMMA K-major, 128B swizzle): B operand of the dQ^T MMA
       uint8_t* drow = sDST + r * 128;
 #pragma unroll
       for (int c = 0; c < FB_ACOLS / 8; ++c) {
         const int slot = ((wg * (FB_ACOLS / 8) + c) ^ (r & 7)) << 4;
-        *reinterpret_cast<uint4*>(prow + slot) = make_uint4(pkp[c * 4], pkp[c * 4 + 1], pkp[c * 4 + 2], pkp[c * 4 + 3]);
         *reinterpret_cast<uint4*>(drow + slot) = make_uint4(pkd[c * 4], pkd[c * 4 + 1], pkd[c * 4 + 2], pkd[c * 4 + 3]);
       }
+      tmem_st_wait();
       fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();
