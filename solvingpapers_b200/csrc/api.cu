@@ -126,15 +126,22 @@ static int pick_attn_bwd_impl(int impl, int dtype, int hd) {
   return impl;
 }
 
-// GEMM dispatch shared by spb_gemm and the block: with `rope` the rotary runs in the tcgen05 epilogue (fp32 accumulators,
-// no extra HBM pass) or, on the FFMA path, as the separate in-place kernel right after the GEMM - same arithmetic.
+// GEMM dispatch shared by spb_gemm and the block: with `rope` the rotary runs as the in-place kernel right after the GEMM
+// (default) or in the tcgen05 epilogue on the fp32 accumulators (SPB_ROPE_FUSE=1).
 static int gemm_any(int in_dtype, int out_dtype, int impl, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA,
                     const void* Bm, int64_t ldb, int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st,
                     const float* rope, int rope_cols, int rope_T, int rope_hd) {
   const int use = pick_gemm_impl(impl, in_dtype);
   if (use == SPB_IMPL_TCGEN05) {
     SPB_CHECK_ARG(in_dtype == SPB_BF16, SPB_E_UNSUPPORTED, "spb_gemm: the tcgen05 GEMM takes bf16 operands (fp32 mode uses the FFMA GEMM)");
-    if (rope == nullptr || rope_hd % 32 == 0)
+    // Measured at C3 after the GEMM reached ~1.6 PFLOP/s in-step: GEMM + the head-looping in-place rotary kernel (0.303 ms)
+    // beats the fused epilogue (0.328 ms) - the GEMM main loop saturates shared-memory bandwidth, and the epilogue's table
+    // staging competes for it.  SPB_ROPE_FUSE=1 selects the fused epilogue (kept for hosts where the extra pass costs more).
+    static const bool fuse_rope = [] {
+      const char* e = getenv("SPB_ROPE_FUSE");
+      return e != nullptr && atoi(e) != 0;
+    }();
+    if (rope == nullptr || (rope_hd % 32 == 0 && fuse_rope))
       return gemm_tc(out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st, rope, rope_cols, rope_T, rope_hd);
     // head dims that do not tile the 32-column epilogue chunk (e.g. 16): GEMM, then the in-place rotary kernel
     int rc = gemm_tc(out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st);

@@ -491,58 +491,82 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
 }
 
-// delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]; one warp per (token, head) row, 4-byte loads (bf16x2)
+// delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]; HD/8 lanes per (token, head) row, one 128-bit load per lane and operand
 template <int HD>
 __global__ void __launch_bounds__(256) flash_bwd_prep_kernel(const __nv_bfloat16* __restrict__ o, int64_t ldo,
                                                              const __nv_bfloat16* __restrict__ d_o, int64_t lddo,
                                                              float* __restrict__ delta, int B, int T, int Hq) {
-  const int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
+  constexpr int TPR = HD / 8;  // lanes per row: 8, 16 or 32
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t w = idx / TPR;
+  const int c = (int)(idx % TPR) * 8;
   const int64_t total = (int64_t)B * T * Hq;
-  if (w >= total) return;
-  const int h = (int)(w % Hq);
-  const int64_t tok = w / Hq;
-  const uint32_t* orow = reinterpret_cast<const uint32_t*>(o + tok * ldo + (int64_t)h * HD);
-  const uint32_t* drow = reinterpret_cast<const uint32_t*>(d_o + tok * lddo + (int64_t)h * HD);
   float s = 0.f;
-#pragma unroll
-  for (int i = lane; i < HD / 2; i += 32) {
-    const float2 a = unpack_bf16(orow[i]), c = unpack_bf16(drow[i]);
-    s += a.x * c.x + a.y * c.y;
+  int h = 0;
+  int64_t tok = 0;
+  if (w < total) {
+    h = (int)(w % Hq);
+    tok = w / Hq;
+    const uint4 a = *reinterpret_cast<const uint4*>(o + tok * ldo + (int64_t)h * HD + c);
+    const uint4 g = *reinterpret_cast<const uint4*>(d_o + tok * lddo + (int64_t)h * HD + c);
+    const float2 a0 = unpack_bf16(a.x), a1 = unpack_bf16(a.y), a2 = unpack_bf16(a.z), a3 = unpack_bf16(a.w);
+    const float2 g0 = unpack_bf16(g.x), g1 = unpack_bf16(g.y), g2 = unpack_bf16(g.z), g3 = unpack_bf16(g.w);
+    s = a0.x * g0.x + a0.y * g0.y + a1.x * g1.x + a1.y * g1.y + a2.x * g2.x + a2.y * g2.y + a3.x * g3.x + a3.y * g3.y;
   }
-  s = warp_sum(s);
-  if (lane == 0) {
+#pragma unroll
+  for (int off = TPR / 2; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+  if (w < total && c == 0) {
     const int64_t bb = tok / T, t = tok % T;
     delta[(bb * Hq + h) * T + t] = s;
   }
 }
 
-// dq[n, c] = bf16(dq_acc[n, c]); 8 elements per thread
+// dq[n, c] = bf16(dq_acc[n, c]) with the rotary VJP fused; a thread owns (row n, one 8-column position inside a head) and
+// walks over HPT heads, so the four table entries it needs are fetched once (they are the same for every head of a row).
+template <int HPT>
 __global__ void __launch_bounds__(256) flash_bwd_dq_convert_kernel(const float* __restrict__ acc, int64_t ld_acc,
                                                                    __nv_bfloat16* __restrict__ dq, int64_t lddq, int64_t N,
-                                                                   int cols, const float4* __restrict__ rope, int T, int hd) {
-  const int vec_per_row = cols / 8;
+                                                                   int heads, const float4* __restrict__ rope, int T, int hd) {
+  const int vph = hd / 8;  // 8-column vectors per head row
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= N * vec_per_row) return;
-  const int64_t n = idx / vec_per_row;
-  const int c = (int)(idx % vec_per_row) * 8;
-  float4 a = *reinterpret_cast<const float4*>(acc + n * ld_acc + c);
-  float4 b = *reinterpret_cast<const float4*>(acc + n * ld_acc + c + 4);
-  if (rope != nullptr) {  // rotary VJP fused into the fp32 -> bf16 conversion
-    const float4* tab = rope + (int64_t)(n % T) * (hd >> 1) + ((c % hd) >> 1);
-    const float4 m0 = tab[0], m1 = tab[1], m2 = tab[2], m3 = tab[3];
-    float xe, xo;
-    xe = a.x; xo = a.y; a.x = m0.x * xe + m0.z * xo; a.y = m0.y * xe + m0.w * xo;
-    xe = a.z; xo = a.w; a.z = m1.x * xe + m1.z * xo; a.w = m1.y * xe + m1.w * xo;
-    xe = b.x; xo = b.y; b.x = m2.x * xe + m2.z * xo; b.y = m2.y * xe + m2.w * xo;
-    xe = b.z; xo = b.w; b.z = m3.x * xe + m3.z * xo; b.w = m3.y * xe + m3.w * xo;
+  if (idx >= N * vph) return;
+  const int64_t n = idx / vph;
+  const int v = (int)(idx % vph);
+  float4 m0, m1, m2, m3;
+  if (rope != nullptr) {
+    const float4* tab = rope + (int64_t)(n % T) * (hd >> 1) + v * 4;
+    m0 = tab[0]; m1 = tab[1]; m2 = tab[2]; m3 = tab[3];
   }
-  uint4 v;
-  v.x = pack_bf16(a.x, a.y);
-  v.y = pack_bf16(a.z, a.w);
-  v.z = pack_bf16(b.x, b.y);
-  v.w = pack_bf16(b.z, b.w);
-  *reinterpret_cast<uint4*>(dq + n * lddq + c) = v;
+  const int h0 = blockIdx.y * HPT;
+  const float* src = acc + n * ld_acc + (int64_t)h0 * hd + v * 8;
+  __nv_bfloat16* dst = dq + n * lddq + (int64_t)h0 * hd + v * 8;
+  float4 a[HPT], b[HPT];
+#pragma unroll
+  for (int h = 0; h < HPT; ++h) {
+    if (h0 + h < heads) {
+      a[h] = *reinterpret_cast<const float4*>(src + (int64_t)h * hd);
+      b[h] = *reinterpret_cast<const float4*>(src + (int64_t)h * hd + 4);
+    }
+  }
+#pragma unroll
+  for (int h = 0; h < HPT; ++h) {
+    if (h0 + h < heads) {
+      float4 x = a[h], y = b[h];
+      if (rope != nullptr) {  // transpose of the 2x2 rotary block
+        float xe, xo;
+        xe = x.x; xo = x.y; x.x = m0.x * xe + m0.z * xo; x.y = m0.y * xe + m0.w * xo;
+        xe = x.z; xo = x.w; x.z = m1.x * xe + m1.z * xo; x.w = m1.y * xe + m1.w * xo;
+        xe = y.x; xo = y.y; y.x = m2.x * xe + m2.z * xo; y.y = m2.y * xe + m2.w * xo;
+        xe = y.z; xo = y.w; y.z = m3.x * xe + m3.z * xo; y.w = m3.y * xe + m3.w * xo;
+      }
+      uint4 o;
+      o.x = pack_bf16(x.x, x.y);
+      o.y = pack_bf16(x.z, x.w);
+      o.z = pack_bf16(y.x, y.y);
+      o.w = pack_bf16(y.z, y.w);
+      *reinterpret_cast<uint4*>(dst + (int64_t)h * hd) = o;
+    }
+  }
 }
 
 bool flash_bwd_tc_supported(int dtype, int hd) { return dtype == SPB_BF16 && (hd == 64 || hd == 128 || hd == 256); }
@@ -559,8 +583,8 @@ static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
   // depends on o and d_o, so the block backward runs it on a helper stream beside the dwo GEMM.
   if (phase & FB_PHASE_PRE) {
     SPB_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)N * ld_acc * sizeof(float), st));
-    const int64_t rows = N * Hq;
-    flash_bwd_prep_kernel<HD><<<(unsigned)((rows + 7) / 8), 256, 0, st>>>((const __nv_bfloat16*)o, ldo, (const __nv_bfloat16*)d_o, lddo,
+    const int64_t lanes = N * Hq * (HD / 8);
+    flash_bwd_prep_kernel<HD><<<(unsigned)((lanes + 255) / 256), 256, 0, st>>>((const __nv_bfloat16*)o, ldo, (const __nv_bfloat16*)d_o, lddo,
                                                                           delta, B, Tn, Hq);
     SPB_LAUNCH_CHECK();
   }
@@ -598,9 +622,10 @@ static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
   flash_bwd_tc_kernel<HD><<<grid, FB_THREADS, Cfg::SMEM_BYTES, st>>>(tmK, tmV, tmQ, tmDO, tmDQ, a);
   SPB_LAUNCH_CHECK();
   {
-    const int cols = Hq * HD;
-    const int64_t total = N * (cols / 8);
-    flash_bwd_dq_convert_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(dq_acc, ld_acc, (__nv_bfloat16*)dq, lddq, N, cols, (const float4*)rope, Tn, HD);
+    constexpr int HPT = 4;
+    const int64_t total = N * (HD / 8);
+    dim3 cgrid((unsigned)((total + 255) / 256), (unsigned)((Hq + HPT - 1) / HPT));
+    flash_bwd_dq_convert_kernel<HPT><<<cgrid, 256, 0, st>>>(dq_acc, ld_acc, (__nv_bfloat16*)dq, lddq, N, Hq, (const float4*)rope, Tn, HD);
     SPB_LAUNCH_CHECK();
   }
   return 0;

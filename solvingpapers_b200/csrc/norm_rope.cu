@@ -585,6 +585,53 @@ __global__ void __launch_bounds__(256) rope_kernel(T* __restrict__ x, int64_t ld
   v.store(p);
 }
 
+// Head-looping variant: a thread owns (row n, one 128-bit vector position inside a head) and walks over a group of heads.
+// Every head of a row uses the same table entries, so they are fetched ONCE into registers; the plain kernel above reads
+// 64 B of table per 16 B of data (bf16), which made it run at ~2.9 TB/s.  HPT heads per thread keep enough loads in flight.
+template <typename T, int HPT>
+__global__ void __launch_bounds__(256) rope_heads_kernel(T* __restrict__ x, int64_t ld, int64_t N, int T_len, int heads, int hd,
+                                                         const float4* __restrict__ table, int transpose) {
+  constexpr int VN = Vec<T>::N;
+  const int vph = hd / VN;  // vectors per head row
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= N * vph) return;
+  const int64_t n = idx / vph;
+  const int v = (int)(idx % vph);
+  const int t = (int)(n % T_len);
+  float4 m[VN / 2];
+#pragma unroll
+  for (int e = 0; e < VN / 2; ++e) {
+    m[e] = table[(int64_t)t * (hd >> 1) + v * (VN / 2) + e];
+    if (transpose) {
+      const float tmp = m[e].y;
+      m[e].y = m[e].z;
+      m[e].z = tmp;
+    }
+  }
+  const int h0 = blockIdx.y * HPT;
+  T* p = x + n * ld + (int64_t)h0 * hd + v * VN;
+  Vec<T> vec[HPT];
+#pragma unroll
+  for (int h = 0; h < HPT; ++h)
+    if (h0 + h < heads) vec[h].load(p + (int64_t)h * hd);
+#pragma unroll
+  for (int h = 0; h < HPT; ++h) {
+    if (h0 + h < heads) {
+      float f[VN];
+      vec[h].unpack(f);
+#pragma unroll
+      for (int e = 0; e < VN; e += 2) {
+        const float4 mm = m[e >> 1];
+        const float xe = f[e], xo = f[e + 1];
+        f[e] = mm.x * xe + mm.y * xo;
+        f[e + 1] = mm.z * xe + mm.w * xo;
+      }
+      vec[h].pack(f);
+      vec[h].store(p + (int64_t)h * hd);
+    }
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) rope_generic_kernel(T* __restrict__ x, int64_t ld, int64_t N, int T_len, int heads,
                                                            int hd, const float4* __restrict__ table, int transpose) {
@@ -760,7 +807,12 @@ static int rope_launch(void* x, int64_t ld, int64_t N, int T_len, int heads, int
                        cudaStream_t st) {
   constexpr int VN = Vec<T>::N;
   const bool vec_ok = (hd % VN == 0) && (ld % VN == 0) && ((uintptr_t)x % 16 == 0);
-  if (vec_ok) {
+  if (vec_ok && heads >= 4) {
+    constexpr int HPT = 8;
+    const int64_t total = N * (hd / VN);
+    dim3 grid((unsigned)((total + 255) / 256), (unsigned)((heads + HPT - 1) / HPT));
+    rope_heads_kernel<T, HPT><<<grid, 256, 0, st>>>((T*)x, ld, N, T_len, heads, hd, (const float4*)table, transpose);
+  } else if (vec_ok) {
     const int64_t total = N * (heads * hd / VN);
     rope_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((T*)x, ld, N, T_len, heads, hd, (const float4*)table,
                                                                      transpose);

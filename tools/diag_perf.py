@@ -44,6 +44,12 @@ if __name__ == "__main__":
     gemm_case("dx", N, Cm, Ntot, False, True)
     gemm_case("dwo", Nq, Cm, N, True, False, torch.float32)
     gemm_case("dwqkv", Cm, Ntot, N, True, False, torch.float32)
+    gemm_case("dwo-bf", Nq, Cm, N, True, False)            # same operands, bf16 output: isolates the fp32 epilogue / tail split
+    gemm_case("dwqkv-bf", Cm, Ntot, N, True, False)
+    gemm_case("mn-k", Nq, Cm, N, True, True)               # A MN-major, B K-major
+    gemm_case("k-mn", Nq, Cm, N, False, False)             # A K-major, B MN-major (the forward's majors, dW shape)
+    if "--gemm-only" in sys.argv:
+        sys.exit(0)
     gemm_case("sq8k", 8192, 8192, 8192, False, True)
     # block-level with and without the fused rotary (rope=False -> no rotary at all, shows the epilogue's cost)
     for rope in (True, False):
