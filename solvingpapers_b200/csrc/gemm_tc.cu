@@ -157,9 +157,28 @@ __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row
   }
 }
 
-// K-split tail tiles: the warp's 32x32 fp32 chunk is transposed through shared memory (pitch 33: conflict-free) so that
-// each atomic instruction adds 32 consecutive floats of ONE output row - a single coalesced 128-byte reduction - instead
-// of 32 scattered 4-byte atomics (row-per-thread), which cost more than the split saved (r01d).
+// K-split tail tiles: the warp's 32x32 fp32 chunk goes to shared memory (rows of 128 B, 128B-swizzled: conflict-free) and
+// ONE TMA bulk reduce-add (cp.reduce.async.bulk.tensor) adds it to the zeroed output tile; the TMA unit clips rows and
+// columns past M / N.  Per-lane fp32 atomics run at ~1 element per clock and SM: with them a half-K tail part took as long
+// as a full tile and the split bought nothing (dwo at C3: 4096x4096x8192, 3.46 waves, 1293 TFLOP/s = the 4-wave time).
+__device__ __forceinline__ void gemm_tc_reduce_chunk(const CUtensorMap* tmD, int row0, int col0, const uint32_t* r, uint8_t* wbuf2, int c,
+                                                     int lane) {
+  uint8_t* wbuf = wbuf2 + (c & 1) * 4096;   // two 4 KB staging buffers per warp: a reduce is in flight while the next chunk is staged
+  if (lane == 0) tma_store_wait_read<1>();  // the reduce issued two chunks ago has finished reading this buffer
+  __syncwarp();
+  uint8_t* rowp = wbuf + lane * 128;
+#pragma unroll
+  for (int u = 0; u < 8; ++u)
+    *reinterpret_cast<uint4*>(rowp + ((u ^ (lane & 7)) << 4)) = make_uint4(r[4 * u], r[4 * u + 1], r[4 * u + 2], r[4 * u + 3]);
+  fence_proxy_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    tma_reduce_add_2d(tmD, wbuf, col0, row0);
+    tma_store_commit();
+  }
+}
+// fallback when the output is not TMA-addressable (unaligned base or row pitch): coalesced fp32 atomics through a pitch-33
+// shared-memory transpose
 __device__ __forceinline__ void gemm_tc_atomic_chunk(const GemmTcArgs& p, int row0, int col0, const uint32_t* r, float* wbuf, int lane) {
   __syncwarp();
 #pragma unroll
@@ -177,8 +196,8 @@ __device__ __forceinline__ void gemm_tc_atomic_chunk(const GemmTcArgs& p, int ro
 // Drain one 128 x NCOLS fp32 accumulator (this warp: TMEM lanes q*32 .. q*32+31 = tile rows) through the epilogue.
 // m0 = first output row of the CTA's 128-row slab, n0 = first output column; warp_buf = this warp's 8 KB staging buffer.
 template <int NCOLS>
-__device__ __forceinline__ void gemm_tc_drain(const GemmTcArgs& p, int atomic, int m0, int n0, uint32_t taddr, uint8_t* warp_buf, int q,
-                                              int lane) {
+__device__ __forceinline__ void gemm_tc_drain(const GemmTcArgs& p, const CUtensorMap* tmD, int atomic, int m0, int n0, uint32_t taddr,
+                                              uint8_t* warp_buf, int q, int lane) {
   const int row = m0 + q * 32 + lane;
 #pragma unroll 1
       for (int c = 0; c < NCOLS / 32; ++c) {
@@ -209,25 +228,27 @@ __device__ __forceinline__ void gemm_tc_drain(const GemmTcArgs& p, int atomic, i
           rope_row = wbuf;
         }
         tmem_ld_wait();
-        if (atomic) gemm_tc_atomic_chunk(p, m0 + q * 32, col0, r, reinterpret_cast<float*>(warp_buf), lane);
+        if (atomic && p.vec_ok) gemm_tc_reduce_chunk(tmD, m0 + q * 32, col0, r, warp_buf, c, lane);
+        else if (atomic) gemm_tc_atomic_chunk(p, m0 + q * 32, col0, r, reinterpret_cast<float*>(warp_buf), lane);
         else if (row < p.M) gemm_tc_store_chunk(p, row, col0, r, rope_row, lane, 0);
       }
 }
 
 template <int BN>
 __global__ void __launch_bounds__(GT_THREADS, 1)
-    gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmTcArgs p) {
+    gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                   const __grid_constant__ CUtensorMap tmD, const GemmTcArgs p) {
   using Cfg = GemmTcCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
   uint8_t* sB = smem + Cfg::STAGES * Cfg::A_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 4 * Cfg::ROPE_WARP_BYTES);
   uint64_t* empty = full + Cfg::STAGES;
   uint64_t* tfull = empty + Cfg::STAGES;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-  uint8_t* sRope = smem + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BAR_BYTES;
+  uint8_t* sRope = smem + Cfg::STAGES * Cfg::STAGE_BYTES;  // 4 x 8 KB warp staging buffers, 1 KB aligned (TMA 128B swizzle)
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -332,13 +353,14 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
       const int m0 = wi.m0, n0 = wi.n0;
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
-      gemm_tc_drain<BN>(p, wi.atomic, m0, n0, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN), sRope + (warp - 2) * Cfg::ROPE_WARP_BYTES, q, lane);
+      gemm_tc_drain<BN>(p, &tmD, wi.atomic, m0, n0, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN), sRope + (warp - 2) * Cfg::ROPE_WARP_BYTES, q, lane);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[acc]);
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
+    if (lane == 0) tma_store_wait_read<0>();  // bulk reduce-adds of a K-split tail tile still read this warp's staging buffer
   }
 
   tc_fence_before();
@@ -383,19 +405,20 @@ __device__ __forceinline__ void gemm_tc2_item(const GemmTcArgs& p, int item, int
 }
 
 __global__ void __launch_bounds__(GT_THREADS, 1)
-    gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmTcArgs p) {
+    gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmD, const GemmTcArgs p) {
   using Cfg = GemmTc2Cfg;
   constexpr int BN = Cfg::BN;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
   uint8_t* sB = smem + Cfg::STAGES * Cfg::A_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 4 * Cfg::ROPE_WARP_BYTES);
   uint64_t* empty = full + Cfg::STAGES;
   uint64_t* tfull = empty + Cfg::STAGES;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-  uint8_t* sRope = smem + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BAR_BYTES;
+  uint8_t* sRope = smem + Cfg::STAGES * Cfg::STAGE_BYTES;  // 4 x 8 KB warp staging buffers, 1 KB aligned (TMA 128B swizzle)
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -506,8 +529,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
       const int m0 = m_blk * 256 + (int)rank * 128, n0 = n_blk * BN;
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
-      gemm_tc_drain<BN>(p, atomic, m0, n0, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN), sRope + (warp - 2) * Cfg::ROPE_WARP_BYTES,
-                        q, lane);
+      gemm_tc_drain<BN>(p, &tmD, atomic, m0, n0, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN),
+                        sRope + (warp - 2) * Cfg::ROPE_WARP_BYTES, q, lane);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) {
@@ -517,6 +540,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
+    if (lane == 0) tma_store_wait_read<0>();  // bulk reduce-adds of a K-split tail tile still read this warp's staging buffer
   }
 
   tc_fence_before();
@@ -558,7 +582,9 @@ static int gemm_tc2_launch(const void* A, int64_t lda, const void* B, int64_t ld
   if (!args.b_mn) rc = make_tmap_2d(&tmB, B, 2, (uint64_t)args.N, (uint64_t)K, (uint64_t)ldb, Cfg::BN / 2, GT_BK, true, false);
   else rc = make_tmap_2d(&tmB, B, 2, (uint64_t)K, (uint64_t)args.N, (uint64_t)ldb, GT_BK, 64, true, false);
   if (rc) return rc;
+  CUtensorMap tmD = tmA;  // only dereferenced by K-split tail parts
   if (args.tail_parts > 1) {
+    if (args.vec_ok && (rc = make_tmap_2d(&tmD, args.D, 4, (uint64_t)args.M, (uint64_t)args.N, (uint64_t)args.ldd, 32, 32, true, true))) return rc;
     gemm_tc_zero_tail_kernel<Cfg::BN, 256><<<tiles - args.full_tiles, 256, 0, st>>>(args);
     SPB_LAUNCH_CHECK();
   }
@@ -575,7 +601,7 @@ static int gemm_tc2_launch(const void* A, int64_t lda, const void* B, int64_t ld
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  SPB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc2_kernel, tmA, tmB, args));
+  SPB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc2_kernel, tmA, tmB, tmD, args));
   SPB_LAUNCH_CHECK();
   return 0;
 }
@@ -635,13 +661,15 @@ static int gemm_tc_launch(const void* A, int64_t lda, const void* B, int64_t ldb
   if (!args.b_mn) rc = make_tmap_2d(&tmB, B, 2, (uint64_t)args.N, (uint64_t)K, (uint64_t)ldb, (uint32_t)BN, GT_BK, true, false);
   else rc = make_tmap_2d(&tmB, B, 2, (uint64_t)K, (uint64_t)args.N, (uint64_t)ldb, GT_BK, 64, true, false);
   if (rc) return rc;
+  CUtensorMap tmD = tmA;  // only dereferenced by K-split tail parts
   if (args.tail_parts > 1) {
+    if (args.vec_ok && (rc = make_tmap_2d(&tmD, args.D, 4, (uint64_t)args.M, (uint64_t)args.N, (uint64_t)args.ldd, 32, 32, true, true))) return rc;
     gemm_tc_zero_tail_kernel<BN><<<tiles - args.full_tiles, 256, 0, st>>>(args);
     SPB_LAUNCH_CHECK();
   }
   SPB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
   const int grid = args.total_items < G ? args.total_items : G;
-  gemm_tc_kernel<BN><<<grid, GT_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, args);
+  gemm_tc_kernel<BN><<<grid, GT_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, tmD, args);
   SPB_LAUNCH_CHECK();
   return 0;
 }
