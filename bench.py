@@ -208,6 +208,41 @@ def time_cpu(wl, torch, steps, warmup, budget_s=None):
     return tokens * done / dt, dt / done * 1e3, done, Bs, tokens
 
 
+_ALL_CPUS = None
+
+
+def bind_near_gpu(torch, idx):
+    """Run this process (and so its pinned host buffers, which are placed by first touch) on the CPUs of the NUMA node the
+    GPU hangs off: host<->device copies then stay on the local PCIe root.  Returns a description for the JSON line."""
+    global _ALL_CPUS
+    try:
+        pr = torch.cuda.get_device_properties(idx)
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        base = f"/sys/bus/pci/devices/{bdf}"
+        node = int(open(base + "/numa_node").read().strip())
+        cpulist = open(base + "/local_cpulist").read().strip()
+        cpus = set()
+        for part in cpulist.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        _ALL_CPUS = os.sched_getaffinity(0)
+        cpus &= _ALL_CPUS
+        if node < 0 or not cpus or cpus == _ALL_CPUS:
+            return f"not changed (GPU {bdf}: numa_node {node}, local cpus {cpulist or '-'})"
+        os.sched_setaffinity(0, cpus)
+        return f"cpus {cpulist} (NUMA node {node}, local to GPU {bdf})"
+    except Exception as ex:  # no sysfs / no such attribute: leave the affinity alone
+        return f"not changed ({type(ex).__name__})"
+
+
+def unbind_cpus():
+    if _ALL_CPUS:
+        os.sched_setaffinity(0, _ALL_CPUS)
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU implementation of the path.  JAX/flax are not installable (no network, no
     wheel), so this is the torch-CPU oracle port of the notebook's op sequence (kind "port"), all host threads."""
@@ -252,6 +287,7 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device (B200); there is no CPU fallback for the product path")
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
+    host_affinity = bind_near_gpu(torch, local_rank)
     lib = L.load()
     comm = None
     if world > 1:
@@ -375,7 +411,7 @@ def run_ours(args):
             dist.all_reduce(t2, op=dist.ReduceOp.MAX)
         nbytes = x.numel() * x.element_size()
         e2e = {"value": tokens_local * world * K / (float(t2.item()) * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": 2 * nbytes,
-               "d2h_bytes_per_step": 2 * nbytes, "ms_per_step": float(t2.item()) / K,
+               "d2h_bytes_per_step": 2 * nbytes, "ms_per_step": float(t2.item()) / K, "host_affinity": host_affinity,
                "what": "every step: pinned host x,dy -> device, spb_block_fwd+bwd via AttentionBlock, y,dx -> pinned host; copies on their "
                        "own streams with double-buffered staging (overlap with the previous/next step's kernels); weights and weight "
                        "grads stay in HBM"}
@@ -419,6 +455,7 @@ def run_ours(args):
            "stages_ms": {k: round(v, 4) for k, v in sorted(stage_ms.items())}}
 
     # ---- CPU baseline on rank 0 at N=1 only (bounded sample)
+    unbind_cpus()  # the CPU baseline below uses every host core
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             val, ms, done, Bs, tok = time_cpu(args.workload, torch, steps=3, warmup=1, budget_s=25.0)

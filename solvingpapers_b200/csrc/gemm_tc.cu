@@ -585,7 +585,7 @@ static int gemm_tc2_launch(const void* A, int64_t lda, const void* B, int64_t ld
   CUtensorMap tmD = tmA;  // only dereferenced by K-split tail parts
   if (args.tail_parts > 1) {
     if (args.vec_ok && (rc = make_tmap_2d(&tmD, args.D, 4, (uint64_t)args.M, (uint64_t)args.N, (uint64_t)args.ldd, 32, 32, true, true))) return rc;
-    gemm_tc_zero_tail_kernel<Cfg::BN, 256><<<tiles - args.full_tiles, 256, 0, st>>>(args);
+    gemm_tc_zero_tail_kernel<Cfg::BN, 256><<<dim3(tiles - args.full_tiles, 256 / 32), 256, 0, st>>>(args);
     SPB_LAUNCH_CHECK();
   }
   SPB_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
@@ -606,15 +606,15 @@ static int gemm_tc2_launch(const void* A, int64_t lda, const void* B, int64_t ld
   return 0;
 }
 
-// zero the tail tiles that will be accumulated with atomics (one CTA per tail tile)
+// zero the tail tiles that the K-split parts will reduce into: blockIdx.x = tail tile, blockIdx.y = 32-row slab of it
 template <int BN, int BMT = GT_BM>
 __global__ void __launch_bounds__(256) gemm_tc_zero_tail_kernel(const GemmTcArgs p) {
   int m_blk, n_blk;
   gemm_tc_tile_coords(p, p.full_tiles + (int)blockIdx.x, m_blk, n_blk);
   float* d = reinterpret_cast<float*>(p.D);
-  const int m0 = m_blk * BMT, n0 = n_blk * BN;
+  const int m0 = m_blk * BMT + (int)blockIdx.y * 32, n0 = n_blk * BN;
   if (p.vec_ok) {  // 16-byte aligned rows: float4 stores
-    for (int e = threadIdx.x; e < BMT * (BN / 4); e += 256) {
+    for (int e = threadIdx.x; e < 32 * (BN / 4); e += 256) {
       const int r = m0 + e / (BN / 4), c = n0 + (e % (BN / 4)) * 4;
       if (r >= p.M || c >= p.N) continue;
       float* q = d + (int64_t)r * p.ldd + c;
@@ -623,7 +623,7 @@ __global__ void __launch_bounds__(256) gemm_tc_zero_tail_kernel(const GemmTcArgs
     }
     return;
   }
-  for (int e = threadIdx.x; e < BMT * BN; e += 256) {
+  for (int e = threadIdx.x; e < 32 * BN; e += 256) {
     const int r = m0 + e / BN, c = n0 + e % BN;
     if (r < p.M && c < p.N) d[(int64_t)r * p.ldd + c] = 0.f;
   }
@@ -664,7 +664,7 @@ static int gemm_tc_launch(const void* A, int64_t lda, const void* B, int64_t ldb
   CUtensorMap tmD = tmA;  // only dereferenced by K-split tail parts
   if (args.tail_parts > 1) {
     if (args.vec_ok && (rc = make_tmap_2d(&tmD, args.D, 4, (uint64_t)args.M, (uint64_t)args.N, (uint64_t)args.ldd, 32, 32, true, true))) return rc;
-    gemm_tc_zero_tail_kernel<BN><<<tiles - args.full_tiles, 256, 0, st>>>(args);
+    gemm_tc_zero_tail_kernel<BN><<<dim3(tiles - args.full_tiles, GT_BM / 32), 256, 0, st>>>(args);
     SPB_LAUNCH_CHECK();
   }
   SPB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));

@@ -538,19 +538,35 @@ static int colsum_tpr(int nvec) {
   return t;
 }
 
+// 2nd stage: out[c] = sum over the partial rows.  32 columns x 8 row lanes per block (the r01i launch list showed the
+// one-thread-per-column version - 16 blocks walking 592 rows serially - taking as long as the fused first stage: 43 us).
 __global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restrict__ partial, int chunks, int C,
                                                            float* __restrict__ out0, float* __restrict__ out1) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  if (out0 != nullptr) {
-    float s = 0.f;
-    for (int k = 0; k < chunks; ++k) s += partial[(int64_t)k * C + c];
-    out0[c] = s;
+  __shared__ float red[2][8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
+  float s0 = 0.f, s1 = 0.f;
+  if (c < C) {
+    if (out0 != nullptr) {
+#pragma unroll 4
+      for (int k = ty; k < chunks; k += 8) s0 += partial[(int64_t)k * C + c];
+    }
+    if (out1 != nullptr) {
+#pragma unroll 4
+      for (int k = ty; k < chunks; k += 8) s1 += partial[((int64_t)chunks + k) * C + c];
+    }
   }
-  if (out1 != nullptr) {
-    float s = 0.f;
-    for (int k = 0; k < chunks; ++k) s += partial[((int64_t)chunks + k) * C + c];
-    out1[c] = s;
+  red[0][ty][tx] = s0;
+  red[1][ty][tx] = s1;
+  __syncthreads();
+  if (ty == 0 && c < C) {
+#pragma unroll
+    for (int l = 1; l < 8; ++l) {
+      s0 += red[0][l][tx];
+      s1 += red[1][l][tx];
+    }
+    if (out0 != nullptr) out0[c] = s0;
+    if (out1 != nullptr) out1[c] = s1;
   }
 }
 
@@ -725,7 +741,7 @@ static int norm_bwd_launch(const void* x, const void* w, const float* stats, con
 #undef SPB_NBF
 #undef SPB_NBF_ONE
     SPB_LAUNCH_CHECK();
-    colsum_final_kernel<<<(C + 255) / 256, 256, 0, st>>>((const float*)partial, grid, C, dw, kind == SPB_NORM_LAYER ? db : nullptr);
+    colsum_final_kernel<<<(C + 31) / 32, 256, 0, st>>>((const float*)partial, grid, C, dw, kind == SPB_NORM_LAYER ? db : nullptr);
     SPB_LAUNCH_CHECK();
     return 0;
   }
@@ -760,7 +776,7 @@ static int norm_bwd_launch(const void* x, const void* w, const float* stats, con
                                                         (float*)partial);
     }
     SPB_LAUNCH_CHECK();
-    colsum_final_kernel<<<(C + 255) / 256, 256, 0, st>>>((const float*)partial, chunks, C, dw, db);
+    colsum_final_kernel<<<(C + 31) / 32, 256, 0, st>>>((const float*)partial, chunks, C, dw, db);
     SPB_LAUNCH_CHECK();
   }
   return 0;
@@ -797,7 +813,7 @@ static int colsum_launch(const void* x, int64_t ld, int64_t N, int cols, float* 
     colsum_partial_kernel<T, 0><<<grid, 256, 0, st>>>((const T*)x, ld, nullptr, nullptr, 0, N, cols, rpc, chunks, (float*)partial);
   }
   SPB_LAUNCH_CHECK();
-  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, st>>>((const float*)partial, chunks, cols, out, nullptr);
+  colsum_final_kernel<<<(cols + 31) / 32, 256, 0, st>>>((const float*)partial, chunks, cols, out, nullptr);
   SPB_LAUNCH_CHECK();
   return 0;
 }
@@ -865,7 +881,7 @@ static int colsum_static_launch(const void* x, int64_t ld, int64_t N, int cols, 
   dim3 grid((cols + 255) / 256, chunks);
   colsum_partial_kernel<T, 0><<<grid, 256, 0, st>>>((const T*)x, ld, nullptr, nullptr, 0, N, cols, rpc, chunks, scratch);
   SPB_LAUNCH_CHECK();
-  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, st>>>(scratch, chunks, cols, out, nullptr);
+  colsum_final_kernel<<<(cols + 31) / 32, 256, 0, st>>>(scratch, chunks, cols, out, nullptr);
   SPB_LAUNCH_CHECK();
   return 0;
 }
