@@ -80,9 +80,12 @@ struct FaBwdCfg {
   static constexpr int OFF_Q = OFF_V + V_BYTES;
   static constexpr int OFF_DO = OFF_Q + NSTAGE * Q_BYTES;
   static constexpr int OFF_DST = OFF_DO + NSTAGE * Q_BYTES;   // dS^T in shared memory: only the dQ^T MMA reads it (as its B operand)
-  static constexpr int OFF_DQS = OFF_DST + PT_BYTES;      // fp32 [64 q rows][HD] staging tile for the TMA reduce-add of dQ
-  static constexpr bool USE_DQS = (HD != 256);     // hd=256 has no room for the staging tile: coalesced fp32 atomics instead
-  static constexpr int DQS_BYTES = USE_DQS ? 64 * HD * 4 : 0;
+  // fp32 [DQS_ROWS q rows][HDZ] staging tile for the TMA reduce-add of dQ: all 64 rows at once, or - at hd=256, where K, V
+  // and the Q/dO stage leave 16 KB - in two rounds of 32 rows (per-lane fp32 atomics, the previous hd=256 path, run at
+  // ~1 element per clock and SM and made that backward 2x slower than the hd=128 one)
+  static constexpr int OFF_DQS = OFF_DST + PT_BYTES;
+  static constexpr int DQS_ROWS = (HD == 256) ? 32 : 64;
+  static constexpr int DQS_BYTES = DQS_ROWS * HDZ * 4;
   static constexpr int OFF_LSE = OFF_DQS + DQS_BYTES;     // [2][64] lse*log2e, then [2][64] delta
   static constexpr int OFF_BAR = OFF_LSE + 4 * 64 * 4;
   static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
@@ -459,26 +462,21 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         // ONE bulk reduce-add of the 64 x hd tile into the fp32 dq accumulator (per-thread fp32 atomics were the v2
         // bottleneck: ~1 float atomic / clk / SM).  Rows past the sequence end hold exact zeros (their P^T is masked).
         if (p.ablate & 8) continue;
-        if constexpr (!Cfg::USE_DQS) {
-          // no staging tile at hd=256: thread r adds column z*HDZ + r of 64 query rows; 32 lanes hit 32 consecutive floats
-          float* acc = p.dq_acc + ((int64_t)b * p.T + q0) * p.ld_acc + (int64_t)h * HD + z * Cfg::HDZ + r;
-#pragma unroll
-          for (int i = 0; i < 64; ++i)
-            if (q0 + i < p.T) atomicAdd(acc + (int64_t)i * p.ld_acc, dq[i]);
-          continue;
-        }
         constexpr int NB = Cfg::DQ_WARPS * 32;
         const bool leader = (qd == 0 && lane == 0);
-        if (leader && it > 0) tma_store_wait_read<0>();  // previous reduce has finished reading the staging tile
-        asm volatile("bar.sync 2, %0;" ::"n"(NB) : "memory");
 #pragma unroll
-        for (int i = 0; i < 64; ++i) sDQ[i * Cfg::HDZ + r] = dq[i];
-        fence_proxy_async_smem();
-        asm volatile("bar.sync 2, %0;" ::"n"(NB) : "memory");
-        FB_TRACE(32);
-        if (leader) {
-          tma_reduce_add_2d(&tmDQ, sDQ, h * HD + z * Cfg::HDZ, b * p.T + q0);
-          tma_store_commit();
+        for (int rd = 0; rd < 64 / Cfg::DQS_ROWS; ++rd) {
+          if (leader && (it > 0 || rd > 0)) tma_store_wait_read<0>();  // previous reduce has finished reading the staging tile
+          asm volatile("bar.sync 2, %0;" ::"n"(NB) : "memory");
+#pragma unroll
+          for (int i = 0; i < Cfg::DQS_ROWS; ++i) sDQ[i * Cfg::HDZ + r] = dq[rd * Cfg::DQS_ROWS + i];
+          fence_proxy_async_smem();
+          asm volatile("bar.sync 2, %0;" ::"n"(NB) : "memory");
+          if (rd == 64 / Cfg::DQS_ROWS - 1) FB_TRACE(32);
+          if (leader) {
+            tma_reduce_add_2d(&tmDQ, sDQ, h * HD + z * Cfg::HDZ, b * p.T + q0 + rd * Cfg::DQS_ROWS);
+            tma_store_commit();
+          }
         }
         FB_TRACE(33);
       }
@@ -596,7 +594,7 @@ static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
   if ((rc = make_tmap_2d(&tmQ, q, 2, (uint64_t)N, (uint64_t)Hq * HD, (uint64_t)ldq, 64, 64, true, false))) return rc;
   if ((rc = make_tmap_2d(&tmDO, d_o, 2, (uint64_t)N, (uint64_t)Hq * HD, (uint64_t)lddo, 64, 64, true, false))) return rc;
   CUtensorMap tmDQ;
-  if ((rc = make_tmap_2d(&tmDQ, dq_acc, 4, (uint64_t)N, (uint64_t)Hq * HD, (uint64_t)ld_acc, 64, Cfg::HDZ, false, true))) return rc;
+  if ((rc = make_tmap_2d(&tmDQ, dq_acc, 4, (uint64_t)N, (uint64_t)Hq * HD, (uint64_t)ld_acc, Cfg::DQS_ROWS, Cfg::HDZ, false, true))) return rc;
   FaBwdArgs a;
   a.lse = lse;
   a.delta = delta;
