@@ -406,36 +406,6 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
   prof_mark("gemm_dattn", st);
   rc = spb_gemm(dt, dt, gimpl, N, Nq, d->C, dy, d->C, 0, p->wo, p->ldw_o, in_out ? 1 : 0, w8 + L.dattn_o, Nq, nullptr, 0, stream);
   if (rc) return rc;
-  // 2. dwo, dbo
-  prof_mark("gemm_dwo", st);
-  if (g->dwo) {
-    if (in_out) rc = spb_gemm(dt, SPB_F32, gimpl, Nq, d->C, N, w8 + L.attn_o, Nq, 1, dy, d->C, 0, g->dwo, g->ldw_o, nullptr, 0, stream);
-    else rc = spb_gemm(dt, SPB_F32, gimpl, d->C, Nq, N, dy, d->C, 1, w8 + L.attn_o, Nq, 0, g->dwo, g->ldw_o, nullptr, 0, stream);
-    if (rc) return rc;
-  }
-  prof_mark("bias_grad", st);
-  if (g->dbo) {
-    rc = spb_colsum(dt, dy, d->C, N, d->C, g->dbo, partial, stream);
-    if (rc) return rc;
-  }
-  // data parallelism: dwo's all-reduce overlaps the attention backward (SURVEY 8e "Overlap")
-  if (comm != nullptr && (g->dwo || g->dbo)) {
-    float* ptrs[2];
-    size_t counts[2];
-    int n = 0;
-    if (g->dwo) {
-      const int64_t rows = in_out ? Nq : d->C, cols = in_out ? d->C : Nq;
-      SPB_CHECK_ARG(g->ldw_o == cols, SPB_E_UNSUPPORTED, "spb_block_bwd: all-reduce needs a contiguous dwo");
-      ptrs[n] = g->dwo;
-      counts[n++] = (size_t)(rows * cols);
-    }
-    if (g->dbo) {
-      ptrs[n] = g->dbo;
-      counts[n++] = (size_t)d->C;
-    }
-    rc = comm_allreduce_side(comm, ptrs, counts, n, st);
-    if (rc) return rc;
-  }
   // 3. attention backward -> dq|dk|dv (post-rotary gradients)
   prof_mark("flash_bwd", st);
   // 4. rotary VJP on dq, dk: fused into the attention backward (dK epilogue + dQ fp32->bf16 conversion)
@@ -510,6 +480,38 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
       rc = comm_allreduce_side(comm, ptrs, counts, n, st);
       if (rc) return rc;
     }
+  }
+  // 2. dwo, dbo - scheduled here, between the dWqkv and dx GEMMs: both gradient all-reduces (dWqkv 100 MB, dWo 64 MB at C3)
+  // then have GEMM work behind them to hide under (with dWo right after the dattn GEMM the large dWqkv all-reduce only had
+  // the dx GEMM + norm backward left and ~0.1 ms of it was exposed), and d(attn_o) goes straight into the attention backward
+  prof_mark("gemm_dwo", st);
+  if (g->dwo) {
+    if (in_out) rc = spb_gemm(dt, SPB_F32, gimpl, Nq, d->C, N, w8 + L.attn_o, Nq, 1, dy, d->C, 0, g->dwo, g->ldw_o, nullptr, 0, stream);
+    else rc = spb_gemm(dt, SPB_F32, gimpl, d->C, Nq, N, dy, d->C, 1, w8 + L.attn_o, Nq, 0, g->dwo, g->ldw_o, nullptr, 0, stream);
+    if (rc) return rc;
+  }
+  prof_mark("bias_grad", st);
+  if (g->dbo) {
+    rc = spb_colsum(dt, dy, d->C, N, d->C, g->dbo, partial, stream);
+    if (rc) return rc;
+  }
+  // data parallelism: dwo's all-reduce overlaps the dx GEMM and the norm backward (SURVEY 8e "Overlap")
+  if (comm != nullptr && (g->dwo || g->dbo)) {
+    float* ptrs[2];
+    size_t counts[2];
+    int n = 0;
+    if (g->dwo) {
+      const int64_t rows = in_out ? Nq : d->C, cols = in_out ? d->C : Nq;
+      SPB_CHECK_ARG(g->ldw_o == cols, SPB_E_UNSUPPORTED, "spb_block_bwd: all-reduce needs a contiguous dwo");
+      ptrs[n] = g->dwo;
+      counts[n++] = (size_t)(rows * cols);
+    }
+    if (g->dbo) {
+      ptrs[n] = g->dbo;
+      counts[n++] = (size_t)d->C;
+    }
+    rc = comm_allreduce_side(comm, ptrs, counts, n, st);
+    if (rc) return rc;
   }
   // 6. d(xhat) = dqkv . Wqkv^T
   prof_mark("gemm_dx", st);
