@@ -53,6 +53,9 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--residual", default="off", choices=["off", "fused", "separate"],
+                    help="SURVEY 8 row f1: also produce h = x + block(x) and dx + dy - inside the kernels' epilogues (fused) or "
+                         "with two extra element-wise passes after the block (separate); off = the block alone (headline)")
     return ap.parse_args()
 
 
@@ -297,14 +300,22 @@ def run_ours(args):
 
     B, T, Cm, Hq, Hkv, hd, dt, kind, desc = WORKLOADS[args.workload]
     cfg, params, x, dy = make_problem(args.workload, device, torch)
+    if args.residual == "fused":
+        import dataclasses
+        cfg = dataclasses.replace(cfg, residual=True)
     blk = sp.AttentionBlock(cfg, device=device, comm=comm.handle if comm else None)
     grads = blk.alloc_grads(params)
     grads["dx"] = torch.empty_like(x)
     tokens_local = B * T
+    h_sep = torch.empty_like(x) if args.residual == "separate" else None
 
     def step():
-        blk.forward(x, params)
+        y = blk.forward(x, params)
+        if h_sep is not None:
+            torch.add(x, y, out=h_sep)          # the caller's `h = x + attention(...)` as its own pass
         blk.backward(dy, grads=grads)
+        if h_sep is not None:
+            grads["dx"].add_(dy)                # ... and its gradient
 
     def barrier():
         torch.cuda.synchronize()
@@ -450,7 +461,7 @@ def run_ours(args):
     out = {"metric": "attn_block_fwd_bwd_tokens_per_s", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": K, "warmup": W,
            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dt, "data": "synthetic",
            "config": {"workload": desc, "global_batch": B * world, "seq_len": T, "parallelism": f"dp{world}" if world > 1 else "single",
-                      "l2": "per-step working set > 126 MB L2, no flush", "attn_impl": "auto", "flops_per_step_per_gpu": total_flops},
+                      "l2": "per-step working set > 126 MB L2, no flush", "attn_impl": "auto", "residual": args.residual, "flops_per_step_per_gpu": total_flops},
            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "block_tflops": whole,
            "stages_ms": {k: round(v, 4) for k, v in sorted(stage_ms.items())}}
 

@@ -68,6 +68,10 @@ typedef struct spb_block_desc {
   int32_t out_bias;       /* 1: bo present (GPT proj bias, ViT out_proj.bias) */
   int32_t attn_impl;      /* SPB_IMPL_*: AUTO = tcgen05 flash kernels when dtype==bf16 and hd in {64,128,256}, else SIMT */
   int32_t gemm_impl;      /* SPB_IMPL_*: AUTO = tcgen05 GEMM when dtype==bf16, SIMT fp32 GEMM when dtype==f32 */
+  int32_t residual;       /* 0: y = block(x) (what `attention` returns, llama3:809-829).  1: y = x + block(x), the caller's
+                             `h = x + attention(...)` (llama3:885, gpt:420, gemma:335, ViT:222) fused into the output
+                             projection's epilogue; spb_block_bwd then returns dx = d block/dx + dy (fused into the norm
+                             VJP's store).  SURVEY section 8 row f1 */
 } spb_block_desc;
 
 /* Weights.  W_IN_OUT: wq is [C, Hq*hd] with row stride ldw_qkv, wk/wv are [C, Hkv*hd] with the same stride

@@ -117,9 +117,10 @@ def init_block_params(rng, dim, n_heads, n_kv_heads, dtype=torch.float32):
 
 
 def block_fwd_bwd(block_params, x, dy, n_heads, n_kv_heads, causal=True, dtype=torch.float32,
-                  theta=10000.0):
+                  theta=10000.0, residual=False):
     """Forward + autograd backward of the block in ``dtype`` (fp32 or fp64).
-    Returns dict with y, k, v, dx, dwq, dwk, dwv, dwo, dnorm."""
+    Returns dict with y, k, v, dx, dwq, dwk, dwv, dwo, dnorm.
+    residual=True follows the caller, transformer_block llama3:881-885: ``h = x + attention(p, rms_norm(x, w), ...)``."""
     B, T, C = x.shape
     hd = C // n_heads
     p = {
@@ -130,6 +131,8 @@ def block_fwd_bwd(block_params, x, dy, n_heads, n_kv_heads, causal=True, dtype=t
     fc = precompute_freqs_cis(hd, T, theta, dtype=dtype)
     mask = make_mask(T, dtype) if causal else None
     y, (k, v) = attention_block(p, xx, mask, fc, n_heads, n_kv_heads)
+    if residual:
+        y = xx + y  # llama3:885
     y.backward(dy.to(dtype))
     a = p["attention"]
     return {

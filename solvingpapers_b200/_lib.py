@@ -20,7 +20,7 @@ class BlockDesc(C.Structure):
     _fields_ = [("B", i32), ("T", i32), ("C", i32), ("Hq", i32), ("Hkv", i32), ("hd", i32), ("dtype", i32),
                 ("norm_kind", i32), ("norm_eps", f32), ("norm_upcast", i32), ("rope_kind", i32), ("causal", i32),
                 ("scale", f32), ("weight_layout", i32), ("qkv_bias", i32), ("out_bias", i32), ("attn_impl", i32),
-                ("gemm_impl", i32)]
+                ("gemm_impl", i32), ("residual", i32)]
 
 
 class BlockParams(C.Structure):

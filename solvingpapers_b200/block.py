@@ -35,13 +35,14 @@ class BlockConfig:
     out_bias: bool = False
     attn_impl: int = L.IMPL_AUTO
     gemm_impl: int = L.IMPL_AUTO
+    residual: bool = False  # y = x + block(x) and dx += dy inside the kernels (the reference's `h = x + attention(...)`, llama3:885)
 
     def desc(self) -> L.BlockDesc:
         scale = self.scale if self.scale is not None else 1.0 / math.sqrt(self.hd)
         return L.BlockDesc(self.B, self.T, self.C, self.Hq, self.Hkv, self.hd, _dt(self.dtype), self.norm_kind,
                            self.norm_eps, int(self.norm_upcast), L.ROPE_TABLE if self.rope else L.ROPE_NONE,
                            int(self.causal), scale, self.weight_layout, int(self.qkv_bias), int(self.out_bias),
-                           self.attn_impl, self.gemm_impl)
+                           self.attn_impl, self.gemm_impl, int(self.residual))
 
     @property
     def n_q(self):

@@ -110,6 +110,7 @@ static int check_desc(const spb_block_desc* d) {
   SPB_CHECK_ARG(d->rope_kind == SPB_ROPE_NONE || d->hd % 2 == 0, SPB_E_INVALID, "block desc: rotary needs an even head dim");
   SPB_CHECK_ARG(d->weight_layout == SPB_W_IN_OUT || d->weight_layout == SPB_W_OUT_IN, SPB_E_INVALID, "block desc: weight_layout %d",
                 d->weight_layout);
+  SPB_CHECK_ARG(d->residual == 0 || d->residual == 1, SPB_E_INVALID, "block desc: residual %d", d->residual);
   return 0;
 }
 
@@ -130,8 +131,9 @@ static int pick_attn_bwd_impl(int impl, int dtype, int hd) {
 // (default) or in the tcgen05 epilogue on the fp32 accumulators (SPB_ROPE_FUSE=1).
 static int gemm_any(int in_dtype, int out_dtype, int impl, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA,
                     const void* Bm, int64_t ldb, int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st,
-                    const float* rope, int rope_cols, int rope_T, int rope_hd) {
+                    const float* rope, int rope_cols, int rope_T, int rope_hd, const void* residual = nullptr, int64_t ldr = 0) {
   const int use = pick_gemm_impl(impl, in_dtype);
+  SPB_CHECK_ARG(residual == nullptr || rope == nullptr, SPB_E_INVALID, "gemm: residual and rotary epilogues are exclusive");
   if (use == SPB_IMPL_TCGEN05) {
     SPB_CHECK_ARG(in_dtype == SPB_BF16, SPB_E_UNSUPPORTED, "spb_gemm: the tcgen05 GEMM takes bf16 operands (fp32 mode uses the FFMA GEMM)");
     // Measured at C3 after the GEMM reached ~1.6 PFLOP/s in-step: GEMM + the head-looping in-place rotary kernel (0.303 ms)
@@ -142,14 +144,15 @@ static int gemm_any(int in_dtype, int out_dtype, int impl, int64_t M, int64_t N,
       return e != nullptr && atoi(e) != 0;
     }();
     if (rope == nullptr || (rope_hd % 32 == 0 && fuse_rope))
-      return gemm_tc(out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st, rope, rope_cols, rope_T, rope_hd);
+      return gemm_tc(out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st, rope, rope_cols, rope_T, rope_hd,
+                     residual, ldr);
     // head dims that do not tile the 32-column epilogue chunk (e.g. 16): GEMM, then the in-place rotary kernel
     int rc = gemm_tc(out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st);
     if (rc) return rc;
     return spb_rope_apply(out_dtype, D, ldd, M, rope_T, rope_cols / rope_hd, rope_hd, rope, 0, (spb_stream_t)st);
   }
   SPB_CHECK_ARG(use == SPB_IMPL_SIMT, SPB_E_INVALID, "spb_gemm: impl %d", impl);
-  int rc = gemm_simt(in_dtype, out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st);
+  int rc = gemm_simt(in_dtype, out_dtype, M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, st, residual, ldr);
   if (rc || rope == nullptr) return rc;
   return spb_rope_apply(out_dtype, D, ldd, M, rope_T, rope_cols / rope_hd, rope_hd, rope, 0, (spb_stream_t)st);
 }
@@ -376,7 +379,9 @@ int spb_block_fwd(const spb_block_desc* d, const spb_block_params* p, const void
   if (rc) return rc;
   // 5. output projection
   prof_mark("gemm_out", pst);
-  rc = spb_gemm(dt, dt, gimpl, N, d->C, Nq, w8 + L.attn_o, Nq, 0, p->wo, p->ldw_o, tB, y, d->C, d->out_bias ? p->bo : nullptr, 0, stream);
+  // residual = 1: y = x + attn . wo (llama3:885 `h = x + attention(...)`), added in the GEMM epilogue
+  rc = gemm_any(dt, dt, gimpl, N, d->C, Nq, w8 + L.attn_o, Nq, 0, p->wo, p->ldw_o, tB, y, d->C, d->out_bias ? p->bo : nullptr, 0, pst, nullptr,
+                0, 0, 0, d->residual ? x : nullptr, d->C);
   prof_mark("fwd_end", pst);
   return rc;
 }
@@ -517,12 +522,14 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
   prof_mark("gemm_dx", st);
   void* dxhat = (d->norm_kind != SPB_NORM_NONE) ? (void*)(w8 + L.dxhat) : g->dx;
   const int tBx = in_out ? 1 : 0;
+  // residual = 1: dx = d(block)/dx + dy; without a norm the dx GEMM's epilogue adds dy, with one the norm VJP's dx store does
+  const void* dx_res = (d->residual && d->norm_kind == SPB_NORM_NONE) ? dy : nullptr;
   if (dxhat != nullptr) {
     if (packed) {
-      rc = spb_gemm(dt, dt, gimpl, N, d->C, Ntot, dqkv, Ntot, 0, wq, p->ldw_q, tBx, dxhat, d->C, nullptr, 0, stream);
+      rc = gemm_any(dt, dt, gimpl, N, d->C, Ntot, dqkv, Ntot, 0, wq, p->ldw_q, tBx, dxhat, d->C, nullptr, 0, st, nullptr, 0, 0, 0, dx_res, d->C);
       if (rc) return rc;
     } else {
-      rc = spb_gemm(dt, dt, gimpl, N, d->C, Nq, dqkv, Ntot, 0, wq, p->ldw_q, tBx, dxhat, d->C, nullptr, 0, stream);
+      rc = gemm_any(dt, dt, gimpl, N, d->C, Nq, dqkv, Ntot, 0, wq, p->ldw_q, tBx, dxhat, d->C, nullptr, 0, st, nullptr, 0, 0, 0, dx_res, d->C);
       if (rc) return rc;
       rc = spb_gemm(dt, dt, gimpl, N, d->C, Nkv, dqkv + Nq * e, Ntot, 0, wk, p->ldw_k, tBx, dxhat, d->C, nullptr, 1, stream);
       if (rc) return rc;
@@ -533,8 +540,8 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
   // 8. norm VJP
   prof_mark("norm_bwd", st);
   if (d->norm_kind != SPB_NORM_NONE) {
-    rc = spb_norm_bwd(dt, d->norm_kind, d->norm_upcast, x, p->norm_w, (const float*)(w8 + L.stats), w8 + L.dxhat, g->dx, g->dnorm_w,
-                      g->dnorm_b, partial, N, d->C, stream);
+    rc = norm_bwd_add(dt, d->norm_kind, d->norm_upcast, x, p->norm_w, (const float*)(w8 + L.stats), w8 + L.dxhat, g->dx, g->dnorm_w,
+                      g->dnorm_b, partial, N, d->C, d->residual ? dy : nullptr, st);
     if (rc) return rc;
   }
   // 9. the small norm gradients on the main stream, then join the side stream

@@ -10,7 +10,8 @@ constexpr int SG_BM = 64, SG_BN = 64, SG_BK = 16;
 template <typename TI, typename TO>
 __global__ void __launch_bounds__(256) gemm_simt_kernel(int M, int N, int K, const TI* __restrict__ A, int64_t sAm, int64_t sAk,
                                                         const TI* __restrict__ B, int64_t sBk, int64_t sBn, TO* __restrict__ D,
-                                                        int64_t ldd, const TI* __restrict__ bias, int accumulate, int k_per_split) {
+                                                        int64_t ldd, const TI* __restrict__ bias, int accumulate, int k_per_split,
+                                                        const TO* __restrict__ residual, int64_t ldr) {
   __shared__ float As[SG_BK][SG_BM + 4];
   __shared__ float Bs[SG_BK][SG_BN + 4];
   const int tid = threadIdx.x;
@@ -70,7 +71,8 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(int M, int N, int K, con
         continue;
       }
       if (bias != nullptr) v += to_f32<TI>(bias[gn]);
-      if (accumulate) v += to_f32<TO>(*p);
+      if (residual != nullptr) v += to_f32<TO>(residual[gm * ldr + gn]);
+      else if (accumulate) v += to_f32<TO>(*p);
       *p = from_f32<TO>(v);
     }
   }
@@ -78,13 +80,14 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(int M, int N, int K, con
 
 template <typename TI, typename TO>
 static int gemm_simt_launch(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb,
-                            int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st) {
+                            int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st, const void* residual,
+                            int64_t ldr) {
   const int64_t sAm = transA ? 1 : lda, sAk = transA ? lda : 1;
   const int64_t sBk = transB ? 1 : ldb, sBn = transB ? ldb : 1;
   dim3 grid((unsigned)((N + SG_BN - 1) / SG_BN), (unsigned)((M + SG_BM - 1) / SG_BM));
   int splits = 1;
   const int64_t tiles = (int64_t)grid.x * grid.y;
-  if (sizeof(TO) == 4 && bias == nullptr && !accumulate && tiles < 2 * sm_count() && K >= 2048) {
+  if (sizeof(TO) == 4 && bias == nullptr && !accumulate && residual == nullptr && tiles < 2 * sm_count() && K >= 2048) {
     splits = (int)((2 * sm_count() + tiles - 1) / tiles);
     const int max_splits = (int)(K / 512);
     if (splits > max_splits) splits = max_splits;
@@ -96,20 +99,21 @@ static int gemm_simt_launch(int64_t M, int64_t N, int64_t K, const void* A, int6
   grid.z = splits;
   if (splits > 1) SPB_CUDA(cudaMemset2DAsync(D, (size_t)ldd * sizeof(TO), 0, (size_t)N * sizeof(TO), (size_t)M, st));
   gemm_simt_kernel<TI, TO><<<grid, 256, 0, st>>>((int)M, (int)N, (int)K, (const TI*)A, sAm, sAk, (const TI*)B, sBk, sBn, (TO*)D,
-                                                 ldd, (const TI*)bias, accumulate, k_per_split);
+                                                 ldd, (const TI*)bias, accumulate, k_per_split, (const TO*)residual, ldr);
   SPB_LAUNCH_CHECK();
   return 0;
 }
 
 int gemm_simt(int in_dtype, int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B,
-              int64_t ldb, int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st) {
+              int64_t ldb, int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st, const void* residual,
+              int64_t ldr) {
   SPB_CHECK_ARG(M < (1LL << 31) && N < (1LL << 31) && K < (1LL << 31), SPB_E_LIMIT, "gemm_simt: dimension beyond 2^31");
   if (in_dtype == SPB_F32 && out_dtype == SPB_F32)
-    return gemm_simt_launch<float, float>(M, N, K, A, lda, transA, B, ldb, transB, D, ldd, bias, accumulate, st);
+    return gemm_simt_launch<float, float>(M, N, K, A, lda, transA, B, ldb, transB, D, ldd, bias, accumulate, st, residual, ldr);
   if (in_dtype == SPB_BF16 && out_dtype == SPB_BF16)
-    return gemm_simt_launch<__nv_bfloat16, __nv_bfloat16>(M, N, K, A, lda, transA, B, ldb, transB, D, ldd, bias, accumulate, st);
+    return gemm_simt_launch<__nv_bfloat16, __nv_bfloat16>(M, N, K, A, lda, transA, B, ldb, transB, D, ldd, bias, accumulate, st, residual, ldr);
   if (in_dtype == SPB_BF16 && out_dtype == SPB_F32)
-    return gemm_simt_launch<__nv_bfloat16, float>(M, N, K, A, lda, transA, B, ldb, transB, D, ldd, bias, accumulate, st);
+    return gemm_simt_launch<__nv_bfloat16, float>(M, N, K, A, lda, transA, B, ldb, transB, D, ldd, bias, accumulate, st, residual, ldr);
   SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "gemm_simt: in_dtype %d / out_dtype %d", in_dtype, out_dtype);
 }
 

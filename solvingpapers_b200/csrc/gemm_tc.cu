@@ -26,6 +26,8 @@ struct GemmTcArgs {
   const float4* rope;  // optional fused rotary epilogue (llama3:592-601): table [T, hd/2] of (a,b,c,d), applied to columns < rope_cols
   int rope_cols, rope_T, rope_hd;
   int out_f32, accumulate, atomic, vec_ok;
+  const void* addsrc;  // accumulate: what is added to the product - D itself (NULL) or a separate [M,N] array of D's type
+  int64_t ld_add;      //            (the residual stream: y = x + attn . wo)
   int M, N;
   int a_mn, b_mn;
   // work items: the first `full_tiles` tiles (whole waves) run over the whole K range; the remaining tail tiles are each
@@ -114,6 +116,7 @@ __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row
   }
   if (p.out_f32) {
     float* d = reinterpret_cast<float*>(p.D) + (int64_t)row * p.ldd + col0;
+    const float* a = p.addsrc ? reinterpret_cast<const float*>(p.addsrc) + (int64_t)row * p.ld_add + col0 : d;
     if (atomic) {
       // handled by gemm_tc_atomic_chunk (warp-cooperative, coalesced); never reached
     } else if (p.vec_ok && ncol == 32) {
@@ -121,7 +124,7 @@ __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row
       for (int i = 0; i < 32; i += 4) {
         float4 o = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
         if (p.accumulate) {
-          const float4 old = *reinterpret_cast<const float4*>(d + i);
+          const float4 old = *reinterpret_cast<const float4*>(a + i);
           o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
         }
         *reinterpret_cast<float4*>(d + i) = o;
@@ -129,17 +132,18 @@ __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row
     } else {
 #pragma unroll
       for (int i = 0; i < 32; ++i)
-        if (i < ncol) d[i] = p.accumulate ? d[i] + v[i] : v[i];
+        if (i < ncol) d[i] = p.accumulate ? a[i] + v[i] : v[i];
     }
   } else {
     __nv_bfloat16* d = reinterpret_cast<__nv_bfloat16*>(p.D) + (int64_t)row * p.ldd + col0;
+    const __nv_bfloat16* a = p.addsrc ? reinterpret_cast<const __nv_bfloat16*>(p.addsrc) + (int64_t)row * p.ld_add + col0 : d;
     if (p.vec_ok && ncol == 32) {
 #pragma unroll
       for (int i = 0; i < 32; i += 8) {
         if (p.accumulate) {
-          const uint4 old = *reinterpret_cast<const uint4*>(d + i);
-          const float2 a = unpack_bf16(old.x), b = unpack_bf16(old.y), c = unpack_bf16(old.z), e = unpack_bf16(old.w);
-          v[i] += a.x; v[i + 1] += a.y; v[i + 2] += b.x; v[i + 3] += b.y;
+          const uint4 old = *reinterpret_cast<const uint4*>(a + i);
+          const float2 a0 = unpack_bf16(old.x), b = unpack_bf16(old.y), c = unpack_bf16(old.z), e = unpack_bf16(old.w);
+          v[i] += a0.x; v[i + 1] += a0.y; v[i + 2] += b.x; v[i + 3] += b.y;
           v[i + 4] += c.x; v[i + 5] += c.y; v[i + 6] += e.x; v[i + 7] += e.y;
         }
         uint4 o;
@@ -152,7 +156,7 @@ __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row
     } else {
 #pragma unroll
       for (int i = 0; i < 32; ++i)
-        if (i < ncol) d[i] = __float2bfloat16_rn(p.accumulate ? __bfloat162float(d[i]) + v[i] : v[i]);
+        if (i < ncol) d[i] = __float2bfloat16_rn(p.accumulate ? __bfloat162float(a[i]) + v[i] : v[i]);
     }
   }
 }
@@ -683,7 +687,7 @@ static double gemm_tc_wave_eff(int64_t M, int64_t N, int bn, int G) {
 
 int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb,
             int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st, const float* rope, int rope_cols,
-            int rope_T, int rope_hd) {
+            int rope_T, int rope_hd, const void* residual, int64_t ldr) {
   SPB_CHECK_ARG(M < (1LL << 31) && N < (1LL << 31) && K < (1LL << 31), SPB_E_LIMIT, "gemm_tc: dimension beyond 2^31");
   SPB_CHECK_ARG(M > 0 && N > 0 && K > 0, SPB_E_INVALID, "gemm_tc: empty problem");
   SPB_CHECK_ARG(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && (lda % 8 == 0) && (ldb % 8 == 0), SPB_E_UNSUPPORTED,
@@ -701,7 +705,9 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
   SPB_CHECK_ARG(rope == nullptr || (!accumulate && rope_hd % 32 == 0 && (uintptr_t)rope % 16 == 0), SPB_E_INVALID,
                 "gemm_tc: the fused rotary epilogue needs a head dim that is a multiple of 32, a 16-byte aligned table and no accumulation");
   args.out_f32 = (out_dtype == SPB_F32);
-  args.accumulate = accumulate;
+  args.accumulate = accumulate || residual != nullptr;
+  args.addsrc = residual;
+  args.ld_add = ldr;
   args.M = (int)M;
   args.N = (int)N;
   // transA=0: A stored [M,K] -> K-major.  transA=1: stored [K,M] -> MN-major.
@@ -711,9 +717,10 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
   args.num_m = (int)((M + GT_BM - 1) / GT_BM);
   args.kb_total = (int)((K + GT_BK - 1) / GT_BK);
   const int esz = args.out_f32 ? 4 : 2;
-  args.vec_ok = ((uintptr_t)D % 16 == 0) && ((ldd * esz) % 16 == 0);
+  args.vec_ok = ((uintptr_t)D % 16 == 0) && ((ldd * esz) % 16 == 0) &&
+                (residual == nullptr || (((uintptr_t)residual % 16 == 0) && ((ldr * esz) % 16 == 0)));
   // K-split of the tail wave needs a plain fp32 output (weight gradients)
-  const bool may_split = args.out_f32 && bias == nullptr && rope == nullptr && !accumulate;
+  const bool may_split = args.out_f32 && bias == nullptr && rope == nullptr && !args.accumulate;
   // tile width: 256 unless a 192-wide tile fills the waves of this problem clearly better (e.g. 8192 x 6144: 94 % -> 99 %)
   int BN = (N > 128) ? 256 : 128;
   if (BN == 256 && !may_split) {

@@ -6,11 +6,13 @@
 namespace spb {
 
 int gemm_simt(int in_dtype, int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B,
-              int64_t ldb, int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st);
+              int64_t ldb, int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st,
+              const void* residual = nullptr, int64_t ldr = 0);
 // rope != nullptr: fused rotary epilogue on output columns < rope_cols (row n has position n % rope_T)
 int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb,
             int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st, const float* rope = nullptr,
-            int rope_cols = 0, int rope_T = 0, int rope_hd = 0);
+            int rope_cols = 0, int rope_T = 0, int rope_hd = 0, const void* residual = nullptr, int64_t ldr = 0);
+// residual != nullptr (both GEMMs): D = A.B (+bias) + residual, residual [M,N] of D's type with row stride ldr
 
 int attn_simt_fwd(int dtype, int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq,
                   const void* k, int64_t ldk, const void* v, int64_t ldv, void* o, int64_t ldo, float* lse, cudaStream_t st);
@@ -32,6 +34,8 @@ int flash_bwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale
 
 // comm.cu
 // all-reduce on the communicator's side stream, ordered after everything already enqueued on `main`
+int norm_bwd_add(int dtype, int norm_kind, int upcast, const void* x, const void* w, const float* stats, const void* dy, void* dx,
+                 float* dw, float* db, void* partial, int64_t N, int32_t C, const void* add, cudaStream_t st);
 int comm_allreduce_side(void* comm, float* const* ptrs, const size_t* counts, int n, cudaStream_t main);
 // all-reduce on `main`, then make `main` wait for the side stream's outstanding all-reduce
 int comm_allreduce_join(void* comm, float* const* ptrs, const size_t* counts, int n, cudaStream_t main);

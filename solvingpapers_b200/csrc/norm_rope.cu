@@ -193,7 +193,8 @@ __global__ void __launch_bounds__(NORM_WARPS * 32) norm_fwd_generic_kernel(const
 template <typename T, int VPT, int WPR>
 __global__ void __launch_bounds__(NR_THREADS) norm_bwd_dx_kernel(const T* __restrict__ x, const T* __restrict__ w,
                                                                   const float* __restrict__ stats, const T* __restrict__ dy,
-                                                                  T* __restrict__ dx, int64_t N, int C, int kind) {
+                                                                  T* __restrict__ dx, int64_t N, int C, int kind,
+                                                                  const T* __restrict__ add) {
   constexpr int VN = Vec<T>::N;
   constexpr int RPC = 8 / WPR;
   __shared__ float red[2][8];
@@ -256,6 +257,14 @@ __global__ void __launch_bounds__(NR_THREADS) norm_bwd_dx_kernel(const T* __rest
         if (kind == SPB_NORM_LAYER) o[e] = rstd * (gv - s_g - (xf[e] - mean) * rstd * s_gx);
         else o[e] = rstd * gv - xf[e] * r3 * s_gx;
       }
+      if (add != nullptr) {  // gradient of the residual branch (h = x + block(x)): dx += dy_block
+        Vec<T> av;
+        av.load(add + row * C + c);
+        float af[VN];
+        av.unpack(af);
+#pragma unroll
+        for (int e = 0; e < VN; ++e) o[e] += af[e];
+      }
       Vec<T> ov;
       ov.pack(o);
       ov.store(dx + row * C + c);
@@ -273,7 +282,8 @@ template <typename T, int VPT, int WPR, bool LAYER>
 __global__ void __launch_bounds__(NR_THREADS, 4) norm_bwd_fused_kernel(const T* __restrict__ x, const T* __restrict__ w,
                                                                         const float* __restrict__ stats, const T* __restrict__ dy,
                                                                         T* __restrict__ dx, int64_t N, int C, int64_t row_groups,
-                                                                        int groups_per_cta, float* __restrict__ partial) {
+                                                                        int groups_per_cta, float* __restrict__ partial,
+                                                                        const T* __restrict__ add) {
   constexpr int VN = Vec<T>::N;
   constexpr int RPC = 8 / WPR;
   constexpr int Q = VN / 4;                        // float4 slots per vector
@@ -360,6 +370,14 @@ __global__ void __launch_bounds__(NR_THREADS, 4) norm_bwd_fused_kernel(const T* 
           const float xh = LAYER ? (xf[e] - mean) * rstd : xf[e] * rstd;
           o[e] = LAYER ? rstd * (gv - s_g - xh * s_gx) : rstd * (gv - xh * s_gx);
         }
+        if (add != nullptr) {  // gradient of the residual branch (h = x + block(x)): dx += dy_block
+          Vec<T> av;
+          av.load(add + row * C + c);
+          float af[VN];
+          av.unpack(af);
+#pragma unroll
+          for (int e = 0; e < VN; ++e) o[e] += af[e];
+        }
         Vec<T> ov;
         ov.pack(o);
         ov.store(dx + row * C + c);
@@ -397,7 +415,7 @@ template <typename T>
 __global__ void __launch_bounds__(NORM_WARPS * 32) norm_bwd_dx_generic_kernel(const T* __restrict__ x, const T* __restrict__ w,
                                                                                const float* __restrict__ stats,
                                                                                const T* __restrict__ dy, T* __restrict__ dx,
-                                                                               int64_t N, int C, int kind) {
+                                                                               int64_t N, int C, int kind, const T* __restrict__ add) {
   const int lane = threadIdx.x & 31;
   const int64_t row = (int64_t)blockIdx.x * NORM_WARPS + (threadIdx.x >> 5);
   if (row >= N) return;
@@ -423,6 +441,7 @@ __global__ void __launch_bounds__(NORM_WARPS * 32) norm_bwd_dx_generic_kernel(co
     } else {
       o = rstd * gv - to_f32<T>(xr[c]) * r3 * s_gx;
     }
+    if (add != nullptr) o += to_f32<T>(add[row * C + c]);
     dx[row * C + c] = from_f32<T>(o);
   }
 }
@@ -705,10 +724,10 @@ static int norm_fwd_launch(const void* x, const void* w, const void* b, void* y,
 
 template <typename T>
 static int norm_bwd_launch(const void* x, const void* w, const float* stats, const void* dy, void* dx, float* dw, float* db,
-                           void* partial, int64_t N, int C, int kind, cudaStream_t st) {
+                           void* partial, int64_t N, int C, int kind, cudaStream_t st, const void* add) {
   constexpr int VN = Vec<T>::N;
   const bool vec_ok = (C % VN == 0) && (C / VN <= 1024) && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) &&
-                      ((uintptr_t)dx % 16 == 0) && ((uintptr_t)w % 16 == 0);
+                      ((uintptr_t)dx % 16 == 0) && ((uintptr_t)w % 16 == 0) && ((uintptr_t)add % 16 == 0);
   if (dx != nullptr && vec_ok && (dw != nullptr || db != nullptr) && partial != nullptr && (uintptr_t)partial % 16 == 0 &&
       (kind == SPB_NORM_LAYER || db == nullptr)) {
     // one fused pass: dx + per-CTA partial sums of dw (db), then the deterministic 2nd stage
@@ -730,7 +749,7 @@ static int norm_bwd_launch(const void* x, const void* w, const float* stats, con
     if (gpc < 1) gpc = 1;                                                                                                       \
     grid = (int)((row_groups + gpc - 1) / gpc);                                                                                 \
     norm_bwd_fused_kernel<T, V, W, L><<<grid, NR_THREADS, smem, st>>>((const T*)x, (const T*)w, stats, (const T*)dy, (T*)dx, N, C, \
-                                                                      row_groups, gpc, (float*)partial);                        \
+                                                                      row_groups, gpc, (float*)partial, (const T*)add);         \
   } while (0)
 #define SPB_NBF(V, W)                                          \
   do {                                                         \
@@ -750,13 +769,13 @@ static int norm_bwd_launch(const void* x, const void* w, const float* stats, con
       const int nv = C / VN;
 #define SPB_NB(V, W)                                                                                                         \
   norm_bwd_dx_kernel<T, V, W><<<(unsigned)((N + (8 / W) - 1) / (8 / W)), NR_THREADS, 0, st>>>((const T*)x, (const T*)w, stats, \
-                                                                                              (const T*)dy, (T*)dx, N, C, kind)
+                                                                                              (const T*)dy, (T*)dx, N, C, kind, (const T*)add)
       SPB_NORM_DISPATCH(nv, SPB_NB);
 #undef SPB_NB
     } else {
       const unsigned grid = (unsigned)((N + NORM_WARPS - 1) / NORM_WARPS);
       norm_bwd_dx_generic_kernel<T><<<grid, NORM_WARPS * 32, 0, st>>>((const T*)x, (const T*)w, stats, (const T*)dy, (T*)dx,
-                                                                      N, C, kind);
+                                                                      N, C, kind, (const T*)add);
     }
     SPB_LAUNCH_CHECK();
   }
@@ -886,7 +905,23 @@ static int colsum_static_launch(const void* x, int64_t ld, int64_t N, int cols, 
   return 0;
 }
 
+// spb_norm_bwd with an optional term added to dx: `add` [N,C] (same dtype) is the gradient arriving through the residual
+// branch h = x + block(x) (llama3:885), fused into the dx store instead of a separate 3-pass add kernel.
+int norm_bwd_add(int dtype, int norm_kind, int upcast, const void* x, const void* w, const float* stats, const void* dy, void* dx,
+                 float* dw, float* db, void* partial, int64_t N, int32_t C, const void* add, cudaStream_t st) {
+  (void)upcast;  // the VJP ignores the intermediate rounding of the gemma variant
+  SPB_CHECK_ARG(N >= 0 && C > 0, SPB_E_INVALID, "spb_norm_bwd: bad shape");
+  SPB_CHECK_ARG(norm_kind == SPB_NORM_RMS || norm_kind == SPB_NORM_LAYER, SPB_E_INVALID, "spb_norm_bwd: bad norm_kind %d", norm_kind);
+  SPB_CHECK_ARG(N > 0, SPB_E_INVALID, "spb_norm_bwd: empty input (the weight gradient of an empty batch is undefined here)");
+  SPB_CHECK_ARG(x && w && stats && dy, SPB_E_INVALID, "spb_norm_bwd: null pointer");
+  if (dtype == SPB_F32) return norm_bwd_launch<float>(x, w, stats, dy, dx, dw, db, partial, N, C, norm_kind, st, add);
+  if (dtype == SPB_BF16) return norm_bwd_launch<__nv_bfloat16>(x, w, stats, dy, dx, dw, db, partial, N, C, norm_kind, st, add);
+  SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "spb_norm_bwd: dtype %d", dtype);
+}
+
 }  // namespace spb
+
+
 
 // ------------------------------------------------------------------------------------------------ C ABI
 extern "C" {
@@ -915,15 +950,7 @@ size_t spb_norm_bwd_partial_bytes(int64_t N, int32_t C) {
 
 int spb_norm_bwd(int dtype, int norm_kind, int upcast, const void* x, const void* w, const float* stats, const void* dy,
                  void* dx, float* dw, float* db, void* partial, int64_t N, int32_t C, spb_stream_t stream) {
-  (void)upcast;  // the VJP ignores the intermediate rounding of the gemma variant
-  SPB_CHECK_ARG(N >= 0 && C > 0, SPB_E_INVALID, "spb_norm_bwd: bad shape");
-  SPB_CHECK_ARG(norm_kind == SPB_NORM_RMS || norm_kind == SPB_NORM_LAYER, SPB_E_INVALID, "spb_norm_bwd: bad norm_kind %d", norm_kind);
-  SPB_CHECK_ARG(N > 0, SPB_E_INVALID, "spb_norm_bwd: empty input (the weight gradient of an empty batch is undefined here)");
-  SPB_CHECK_ARG(x && w && stats && dy, SPB_E_INVALID, "spb_norm_bwd: null pointer");
-  cudaStream_t st = (cudaStream_t)stream;
-  if (dtype == SPB_F32) return spb::norm_bwd_launch<float>(x, w, stats, dy, dx, dw, db, partial, N, C, norm_kind, st);
-  if (dtype == SPB_BF16) return spb::norm_bwd_launch<__nv_bfloat16>(x, w, stats, dy, dx, dw, db, partial, N, C, norm_kind, st);
-  SPB_CHECK_ARG(false, SPB_E_UNSUPPORTED, "spb_norm_bwd: dtype %d", dtype);
+  return spb::norm_bwd_add(dtype, norm_kind, upcast, x, w, stats, dy, dx, dw, db, partial, N, C, nullptr, (cudaStream_t)stream);
 }
 
 int spb_colsum(int dtype, const void* x, int64_t ld, int64_t N, int32_t cols, float* out, void* partial, spb_stream_t stream) {

@@ -48,12 +48,12 @@ def repeat_kv(x, n_rep):
     return x if n_rep == 1 else torch.repeat_interleave(x, n_rep, dim=2)
 
 
-def _cfg(x, n_heads, n_kv_heads, head_dim, mask, norm, eps=1e-6, attn_impl=L.IMPL_AUTO, gemm_impl=L.IMPL_AUTO):
+def _cfg(x, n_heads, n_kv_heads, head_dim, mask, norm, eps=1e-6, attn_impl=L.IMPL_AUTO, gemm_impl=L.IMPL_AUTO, residual=False):
     B, T, C = x.shape
     return BlockConfig(B=B, T=T, C=C, Hq=n_heads, Hkv=n_kv_heads, hd=head_dim, dtype=x.dtype,
                        norm_kind=L.NORM_RMS if norm else L.NORM_NONE, norm_eps=eps, rope=True,
                        causal=mask is not None, scale=1.0 / math.sqrt(head_dim), weight_layout=L.W_IN_OUT,
-                       attn_impl=attn_impl, gemm_impl=gemm_impl)
+                       attn_impl=attn_impl, gemm_impl=gemm_impl, residual=residual)
 
 
 def attention(params, x, mask, freqs_cis, n_heads, n_kv_heads, cache=None, position=0, comm=None):
@@ -68,12 +68,14 @@ def attention(params, x, mask, freqs_cis, n_heads, n_kv_heads, cache=None, posit
     return y, (k, v)
 
 
-def attention_block(block_params, x, mask, freqs_cis, n_heads, n_kv_heads, eps=1e-6, comm=None):
+def attention_block(block_params, x, mask, freqs_cis, n_heads, n_kv_heads, eps=1e-6, comm=None, residual=False):
     """The fused hot path exactly as transformer_block calls it (llama3/LLaMA-jax.ipynb:881):
     ``attention(params['attention'], rms_norm(x, params['attention_norm']), mask, freqs_cis, n_heads, n_kv_heads)``
-    - one C-ABI call forward, one backward."""
+    - one C-ABI call forward, one backward.  residual=True returns ``x + attention(...)``, the next line of the caller
+    (``h = x + attn_output``, :885), with the add inside the output projection's epilogue (and ``dx += dy`` inside the norm
+    VJP) instead of two extra passes over [B,T,C]."""
     B, T, C = x.shape
-    cfg = _cfg(x, n_heads, n_kv_heads, C // n_heads, mask, norm=True, eps=eps)
+    cfg = _cfg(x, n_heads, n_kv_heads, C // n_heads, mask, norm=True, eps=eps, residual=residual)
     tab = _table(freqs_cis[:T])
     a = block_params["attention"]
     names = ("wq", "wk", "wv", "wo", "norm_w", "rope")

@@ -34,7 +34,7 @@ def test_library_has_no_link_dependency_on_driver_or_nccl():
 
 def test_struct_sizes_match_header():
     from solvingpapers_b200 import _lib
-    assert ctypes.sizeof(_lib.BlockDesc) == 18 * 4
+    assert ctypes.sizeof(_lib.BlockDesc) == 19 * 4
     assert ctypes.sizeof(_lib.BlockParams) == 15 * 8
     assert ctypes.sizeof(_lib.BlockGrads) == 15 * 8
     assert ctypes.sizeof(_lib.WsLayout) == 14 * 8

@@ -34,7 +34,8 @@ def _check(got, ref, dtype, names):
     return errs
 
 
-def run_llama(B, T, C, H, Hkv, dtype, causal=True, seed=0, attn_impl=0, gemm_impl=0, packed=False, params=None, x=None, dy=None):
+def run_llama(B, T, C, H, Hkv, dtype, causal=True, seed=0, attn_impl=0, gemm_impl=0, packed=False, params=None, x=None, dy=None,
+              residual=False):
     sp, L = _sp()
     rng = np.random.default_rng(seed)
     hd = C // H
@@ -47,9 +48,9 @@ def run_llama(B, T, C, H, Hkv, dtype, causal=True, seed=0, attn_impl=0, gemm_imp
     a = {k: rd(v) for k, v in params["attention"].items()}
     pr = {"attention": a, "attention_norm": rd(params["attention_norm"])}
     xr, dyr = rd(x), rd(dy)
-    ref = llama_oracle.block_fwd_bwd(pr, xr, dyr, H, Hkv, causal=causal, dtype=torch.float32)
+    ref = llama_oracle.block_fwd_bwd(pr, xr, dyr, H, Hkv, causal=causal, dtype=torch.float32, residual=residual)
     cfg = sp.BlockConfig(B=B, T=T, C=C, Hq=H, Hkv=Hkv, hd=hd, dtype=dtype, norm_kind=L.NORM_RMS, norm_eps=1e-6, rope=True,
-                         causal=causal, weight_layout=L.W_IN_OUT, attn_impl=attn_impl, gemm_impl=gemm_impl)
+                         causal=causal, weight_layout=L.W_IN_OUT, attn_impl=attn_impl, gemm_impl=gemm_impl, residual=residual)
     blk = sp.AttentionBlock(cfg)
     cos, sin = llama_oracle.precompute_freqs_cis(hd, T)
     dev = lambda t: t.to(dtype).to(DEV)
@@ -105,6 +106,43 @@ def test_c1_llama_notebook_default_dims_fp32():
 def test_llama_block_bf16(B, T, C, H, Hkv, packed):
     got, ref = run_llama(B, T, C, H, Hkv, torch.bfloat16, seed=1, packed=packed)
     _check(got, ref, torch.bfloat16, NAMES)
+
+
+@pytest.mark.parametrize("dtype,B,T,C,H,Hkv", [(torch.bfloat16, 2, 256, 512, 8, 2), (torch.bfloat16, 1, 200, 256, 4, 4),
+                                               (torch.float32, 2, 128, 256, 4, 2)])
+def test_llama_block_with_fused_residual(dtype, B, T, C, H, Hkv):
+    """h = x + attention(...) (llama3:885) in the out-projection epilogue, dx += dy in the norm VJP's store."""
+    got, ref = run_llama(B, T, C, H, Hkv, dtype, packed=True, residual=True)
+    _check(got, ref, dtype, NAMES)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_block_without_norm_with_fused_residual(dtype):
+    """residual with norm_kind NONE: the dx GEMM's epilogue adds dy (no norm VJP kernel runs)."""
+    sp, L = _sp()
+    B, T, C, H, Hkv = 2, 128, 256, 4, 2
+    hd = C // H
+    rng = np.random.default_rng(11)
+    params = llama_oracle.init_block_params(rng, C, H, Hkv)
+    rd = lambda t: t.to(dtype).float()
+    a = {k: rd(v).requires_grad_(True) for k, v in params["attention"].items()}
+    x = rd(T_(rng.standard_normal((B, T, C)).astype(np.float32))).requires_grad_(True)
+    dy = rd(T_(rng.standard_normal((B, T, C)).astype(np.float32)))
+    fc = llama_oracle.precompute_freqs_cis(hd, T)
+    y_ref, _ = llama_oracle.attention(a, x, llama_oracle.make_mask(T), fc, H, Hkv)
+    y_ref = x + y_ref
+    y_ref.backward(dy)
+    cfg = sp.BlockConfig(B=B, T=T, C=C, Hq=H, Hkv=Hkv, hd=hd, dtype=dtype, norm_kind=L.NORM_NONE, rope=True, causal=True,
+                         weight_layout=L.W_IN_OUT, residual=True)
+    blk = sp.AttentionBlock(cfg)
+    dev = lambda t: t.detach().to(dtype).to(DEV)
+    p = {"wq": dev(a["wq"]), "wk": dev(a["wk"]), "wv": dev(a["wv"]), "wo": dev(a["wo"]), "rope": sp.llama_rope_table(*fc).to(DEV)}
+    y = blk.forward(dev(x), p)
+    g = blk.backward(dev(dy))
+    torch.cuda.synchronize()
+    got = {"y": y, "dx": g["dx"], "dwq": g["dwq"], "dwk": g["dwk"], "dwv": g["dwv"], "dwo": g["dwo"]}
+    ref = {"y": y_ref.detach(), "dx": x.grad, "dwq": a["wq"].grad, "dwk": a["wk"].grad, "dwv": a["wv"].grad, "dwo": a["wo"].grad}
+    _check(got, ref, dtype, tuple(got))
 
 
 def test_llama_block_bf16_noncausal_mask_none():
