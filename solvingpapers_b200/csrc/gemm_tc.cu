@@ -26,6 +26,7 @@ struct GemmTcArgs {
   const float4* rope;  // optional fused rotary epilogue (llama3:592-601): table [T, hd/2] of (a,b,c,d), applied to columns < rope_cols
   int rope_cols, rope_T, rope_hd;
   int out_f32, accumulate, atomic, vec_ok;
+  int group_m;         // tile raster: row-blocks per group (see gemm_tc_tile_coords)
   const void* addsrc;  // accumulate: what is added to the product - D itself (NULL) or a separate [M,N] array of D's type
   int64_t ld_add;      //            (the residual stream: y = x + attn . wo)
   int M, N;
@@ -43,11 +44,18 @@ struct GemmTcItem {
 // Tile raster: groups of GT_GROUP_M row-blocks, row-block fastest inside a group, so that the ~148 concurrently resident
 // tiles share a few A row-panels and B column-panels that stay in the 126 MB L2 (ncu r01b: 5.7x DRAM re-reads without it).
 constexpr int GT_GROUP_M = 16;
+static int gemm_group_m(int dflt) {  // SPB_GEMM_GROUP_M: timing experiments
+  static const int env = [] {
+    const char* e = getenv("SPB_GEMM_GROUP_M");
+    return e ? atoi(e) : 0;
+  }();
+  return env > 0 ? env : dflt;
+}
 __device__ __forceinline__ void gemm_tc_tile_coords(const GemmTcArgs& p, int tile, int& m_blk, int& n_blk) {
-  const int group_sz = GT_GROUP_M * p.num_n;
+  const int group_sz = p.group_m * p.num_n;
   const int gid = tile / group_sz;
-  const int first_m = gid * GT_GROUP_M;
-  const int gm = min(p.num_m - first_m, GT_GROUP_M);
+  const int first_m = gid * p.group_m;
+  const int gm = min(p.num_m - first_m, p.group_m);
   const int in_group = tile - gid * group_sz;
   m_blk = first_m + in_group % gm;
   n_blk = in_group / gm;
@@ -557,6 +565,7 @@ static int gemm_tc2_launch(const void* A, int64_t lda, const void* B, int64_t ld
   using Cfg = GemmTc2Cfg;
   const int G = sm_count();
   args.num_m = (args.M + 255) / 256;          // 256-row tiles
+  args.group_m = gemm_group_m(GT_GROUP_M);  // 4 / 8 / 12 / 16 measured within +-2 % of each other on the C3 GEMMs (r01i)
   args.num_n = (args.N + Cfg::BN - 1) / Cfg::BN;
   const int tiles = args.num_m * args.num_n;
   int pairs = G / 2;
@@ -637,6 +646,7 @@ template <int BN>
 static int gemm_tc_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int64_t K, GemmTcArgs args, bool may_split,
                           cudaStream_t st) {
   using Cfg = GemmTcCfg<BN>;
+  args.group_m = gemm_group_m(GT_GROUP_M);
   const int G = sm_count();
   args.num_n = (args.N + BN - 1) / BN;
   const int tiles = args.num_m * args.num_n;
