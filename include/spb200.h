@@ -211,6 +211,58 @@ int spb_block_fwd(const spb_block_desc* d, const spb_block_params* p, const void
 int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void* x, const void* dy, void* ws,
                   const spb_block_grads* g, void* comm, spb_stream_t stream);
 
+/* ---- the gated feed-forward sub-block ---------------------------------------- */
+/* llama3:886,890  ffn_output = feed_forward(params['ffn'], rms_norm(h, params['ffn_norm']));  out = h + ffn_output
+ * llama3:854-855  feed_forward(p, x) = dot(silu(dot(x, p['w3'])) * dot(x, p['w1']), p['w2'])
+ * Weights as init_ffn_weights stores them (llama3:713-718): w1, w3 [C, H], w2 [H, C] for SPB_W_IN_OUT (H = 4*C in the
+ * notebook); SPB_W_OUT_IN: w1, w3 [H, C], w2 [C, H].                                                              */
+#define SPB_ACT_SWIGLU 0   /* silu(x.w3) * (x.w1)  - the only activation built so far (GeGLU / GELU-MLP: not yet) */
+
+typedef struct spb_ffn_desc {
+  int32_t N, C, H;        /* tokens (B*T), model width, hidden width */
+  int32_t dtype;          /* SPB_F32 | SPB_BF16: activations AND weights */
+  int32_t norm_kind;      /* SPB_NORM_*: the ffn_norm in front (SPB_NORM_NONE = plain feed_forward(x)) */
+  float   norm_eps;
+  int32_t norm_upcast;
+  int32_t act;            /* SPB_ACT_* */
+  int32_t weight_layout;  /* SPB_W_IN_OUT | SPB_W_OUT_IN */
+  int32_t residual;       /* 1: y = h + ffn(norm(h)) (llama3:890) in the w2 GEMM's epilogue; backward dx += dy */
+  int32_t gemm_impl;      /* SPB_IMPL_* */
+} spb_ffn_desc;
+
+typedef struct spb_ffn_params {
+  const void* norm_w; const void* norm_b;     /* [C] dtype */
+  const void* w1; const void* w3; int64_t ldw_13;  /* same row stride for both; packed [C, 2H] (w3 = w1 + H) is one GEMM */
+  const void* w2; int64_t ldw_2;
+} spb_ffn_params;
+
+typedef struct spb_ffn_grads {
+  void*  dx;                                  /* [N, C] dtype */
+  float* dnorm_w; float* dnorm_b;             /* [C] */
+  float* dw1; float* dw3; int64_t ldw_13;     /* fp32, same layout as the weights */
+  float* dw2; int64_t ldw_2;
+} spb_ffn_grads;
+
+/* Byte offsets inside the caller-owned workspace */
+typedef struct spb_ffn_ws {
+  size_t total;
+  size_t xhat;     /* [N, C] dtype normalised input (unused when norm_kind == NONE)        */
+  size_t stats;    /* [N, 2] f32                                                            */
+  size_t g13;      /* [N, 2H] dtype: x.w1 in columns [0,H), x.w3 in [H,2H)  (residual)      */
+  size_t act;      /* [N, H] dtype: silu(g3)*g1 = the w2 GEMM's operand     (residual)      */
+  size_t dact;     /* [N, H] dtype                                           (backward)     */
+  size_t dg13;     /* [N, 2H] dtype                                          (backward)     */
+  size_t dxhat;    /* [N, C] dtype                                           (backward)     */
+  size_t partial;  /* f32 partial sums of the norm-weight gradient                          */
+  size_t partial_bytes;
+} spb_ffn_ws;
+
+int spb_ffn_ws_layout(const spb_ffn_desc* d, spb_ffn_ws* out);
+int spb_ffn_fwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, void* y, void* ws, spb_stream_t stream);
+/* VJP given dy [N, C]; with `comm` the weight gradients are summed over ranks like spb_block_bwd's. */
+int spb_ffn_bwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, const void* dy, void* ws,
+                const spb_ffn_grads* g, void* comm, spb_stream_t stream);
+
 /* ---- data parallelism: batch-sharded, weight gradients all-reduced (no reference precedent) ---- */
 int spb_comm_unique_id(void* out128);                        /* HOST buffer, 128 bytes (ncclUniqueId)      */
 int spb_comm_init_rank(const void* id128, int nranks, int rank, void** comm_out);

@@ -140,3 +140,44 @@ def block_fwd_bwd(block_params, x, dy, n_heads, n_kv_heads, causal=True, dtype=t
         "dwq": a["wq"].grad, "dwk": a["wk"].grad, "dwv": a["wv"].grad, "dwo": a["wo"].grad,
         "dnorm": p["attention_norm"].grad,
     }
+
+
+# ---- the gated feed-forward sub-block -----------------------------------------------
+def feed_forward(params, x):
+    """llama3/LLaMA-jax.ipynb:854-855 - ``jnp.dot(jax.nn.silu(jnp.dot(x, w3)) * jnp.dot(x, w1), w2)``; weights [in, out]
+    (init_ffn_weights :713-718: w1, w3 [dim, 4*dim], w2 [4*dim, dim])."""
+    return torch.matmul(torch.nn.functional.silu(torch.matmul(x, params["w3"])) * torch.matmul(x, params["w1"]), params["w2"])
+
+
+def ffn_block(block_params, h, residual=True):
+    """Second half of transformer_block, llama3/LLaMA-jax.ipynb:886,890:
+    ``ffn_output = feed_forward(params['ffn'], rms_norm(h, params['ffn_norm']))``; ``out = h + ffn_output``."""
+    out = feed_forward(block_params["ffn"], rms_norm(h, block_params["ffn_norm"]))
+    return h + out if residual else out
+
+
+def init_ffn_params(rng, dim, hidden=None, dtype=torch.float32):
+    """llama3/LLaMA-jax.ipynb:713-718 (N(0,1)/sqrt(fan_in), hidden = 4*dim) and :749 (ffn_norm ~ N(0,1))."""
+    hidden = 4 * dim if hidden is None else hidden
+
+    def w(shape, scale=None):
+        scale = 1.0 / math.sqrt(shape[0]) if scale is None else scale
+        return torch.from_numpy(rng.standard_normal(shape) * scale).to(dtype)
+
+    return {"ffn": {"w1": w((dim, hidden)), "w2": w((hidden, dim)), "w3": w((dim, hidden))}, "ffn_norm": w((dim,), scale=1.0)}
+
+
+def ffn_fwd_bwd(block_params, h, dy, dtype=torch.float32, residual=True, norm=True):
+    """Forward + autograd backward of the feed-forward sub-block.  Returns dict with y, dx, dw1, dw2, dw3, dnorm."""
+    f = {k: v.detach().to(dtype).requires_grad_(True) for k, v in block_params["ffn"].items()}
+    nw = block_params["ffn_norm"].detach().to(dtype).requires_grad_(True)
+    hh = h.detach().to(dtype).requires_grad_(True)
+    if norm:
+        y = ffn_block({"ffn": f, "ffn_norm": nw}, hh, residual=residual)
+    else:
+        y = feed_forward(f, hh)
+        if residual:
+            y = hh + y
+    y.backward(dy.to(dtype))
+    return {"y": y.detach(), "dx": hh.grad, "dw1": f["w1"].grad, "dw2": f["w2"].grad, "dw3": f["w3"].grad,
+            "dnorm": nw.grad if norm else None}

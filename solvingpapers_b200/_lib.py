@@ -40,6 +40,27 @@ class WsLayout(C.Structure):
                 ("ld_qkv", i64)]
 
 
+class FfnDesc(C.Structure):
+    _fields_ = [("N", i32), ("C", i32), ("H", i32), ("dtype", i32), ("norm_kind", i32), ("norm_eps", f32), ("norm_upcast", i32),
+                ("act", i32), ("weight_layout", i32), ("residual", i32), ("gemm_impl", i32)]
+
+
+class FfnParams(C.Structure):
+    _fields_ = [("norm_w", vp), ("norm_b", vp), ("w1", vp), ("w3", vp), ("ldw_13", i64), ("w2", vp), ("ldw_2", i64)]
+
+
+class FfnGrads(C.Structure):
+    _fields_ = [("dx", vp), ("dnorm_w", vp), ("dnorm_b", vp), ("dw1", vp), ("dw3", vp), ("ldw_13", i64), ("dw2", vp),
+                ("ldw_2", i64)]
+
+
+class FfnWs(C.Structure):
+    _fields_ = [("total", sz), ("xhat", sz), ("stats", sz), ("g13", sz), ("act", sz), ("dact", sz), ("dg13", sz), ("dxhat", sz),
+                ("partial", sz), ("partial_bytes", sz)]
+
+
+ACT_SWIGLU = 0
+
 # name -> (restype, argtypes); every symbol include/spb200.h declares
 SIGNATURES = {
     "spb_version": (C.c_char_p, []),
@@ -64,6 +85,9 @@ SIGNATURES = {
     "spb_block_ws_layout": (C.c_int, [C.POINTER(BlockDesc), C.POINTER(WsLayout)]),
     "spb_block_fwd": (C.c_int, [C.POINTER(BlockDesc), C.POINTER(BlockParams), vp, vp, vp, vp]),
     "spb_block_bwd": (C.c_int, [C.POINTER(BlockDesc), C.POINTER(BlockParams), vp, vp, vp, C.POINTER(BlockGrads), vp, vp]),
+    "spb_ffn_ws_layout": (C.c_int, [C.POINTER(FfnDesc), C.POINTER(FfnWs)]),
+    "spb_ffn_fwd": (C.c_int, [C.POINTER(FfnDesc), C.POINTER(FfnParams), vp, vp, vp, vp]),
+    "spb_ffn_bwd": (C.c_int, [C.POINTER(FfnDesc), C.POINTER(FfnParams), vp, vp, vp, C.POINTER(FfnGrads), vp, vp]),
     "spb_comm_unique_id": (C.c_int, [vp]),
     "spb_comm_init_rank": (C.c_int, [vp, C.c_int, C.c_int, C.POINTER(vp)]),
     "spb_comm_allreduce_f32": (C.c_int, [vp, C.POINTER(vp), C.POINTER(sz), C.c_int, vp]),

@@ -559,4 +559,194 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
   return 0;
 }
 
+
+// ------------------------------------------------------------------------------------------------ feed-forward sub-block
+static int check_ffn_desc(const spb_ffn_desc* d) {
+  SPB_CHECK_ARG(d != nullptr, SPB_E_INVALID, "ffn desc is NULL");
+  SPB_CHECK_ARG(d->N > 0 && d->C > 0 && d->H > 0, SPB_E_INVALID, "ffn desc: non-positive dimension (N=%d C=%d H=%d)", d->N, d->C, d->H);
+  SPB_CHECK_ARG(d->dtype == SPB_F32 || d->dtype == SPB_BF16, SPB_E_UNSUPPORTED, "ffn desc: dtype %d", d->dtype);
+  SPB_CHECK_ARG(d->norm_kind >= SPB_NORM_NONE && d->norm_kind <= SPB_NORM_LAYER, SPB_E_INVALID, "ffn desc: norm_kind %d", d->norm_kind);
+  SPB_CHECK_ARG(d->act == SPB_ACT_SWIGLU, SPB_E_UNSUPPORTED, "ffn desc: activation %d (only SPB_ACT_SWIGLU is built)", d->act);
+  SPB_CHECK_ARG(d->weight_layout == SPB_W_IN_OUT || d->weight_layout == SPB_W_OUT_IN, SPB_E_INVALID, "ffn desc: weight_layout %d",
+                d->weight_layout);
+  SPB_CHECK_ARG(d->residual == 0 || d->residual == 1, SPB_E_INVALID, "ffn desc: residual %d", d->residual);
+  return 0;
+}
+
+int spb_ffn_ws_layout(const spb_ffn_desc* d, spb_ffn_ws* out) {
+  int rc = check_ffn_desc(d);
+  if (rc) return rc;
+  SPB_CHECK_ARG(out != nullptr, SPB_E_INVALID, "spb_ffn_ws_layout: out is NULL");
+  const size_t N = (size_t)d->N, e = esize(d->dtype), C = (size_t)d->C, H = (size_t)d->H;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off = align_up(off + bytes, 256);
+    return o;
+  };
+  memset(out, 0, sizeof(*out));
+  out->xhat = take(N * C * e);
+  out->stats = take(N * 2 * sizeof(float));
+  out->g13 = take(N * 2 * H * e);
+  out->act = take(N * H * e);
+  out->dact = take(N * H * e);
+  out->dg13 = take(N * 2 * H * e);
+  out->dxhat = take(N * C * e);
+  out->partial_bytes = spb_norm_bwd_partial_bytes((int64_t)N, d->C);
+  out->partial = take(out->partial_bytes);
+  out->total = off;
+  return 0;
+}
+
+// is [w1 | w3] one packed array?  in_out: [C, 2H] (w3 = w1 + H);  out_in: [2H, C] (w3 = w1 + H rows)
+static bool ffn_packed(const spb_ffn_desc* d, const void* w1, const void* w3, int64_t ld) {
+  const size_t e = esize(d->dtype);
+  if (d->weight_layout == SPB_W_IN_OUT) return (const char*)w3 == (const char*)w1 + (size_t)d->H * e;
+  return (const char*)w3 == (const char*)w1 + (size_t)d->H * (size_t)ld * e;
+}
+
+int spb_ffn_fwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, void* y, void* ws, spb_stream_t stream) {
+  int rc = check_ffn_desc(d);
+  if (rc) return rc;
+  SPB_CHECK_ARG(p && x && y && ws && p->w1 && p->w3 && p->w2, SPB_E_INVALID, "spb_ffn_fwd: null pointer");
+  spb_ffn_ws L;
+  rc = spb_ffn_ws_layout(d, &L);
+  if (rc) return rc;
+  char* w8 = (char*)ws;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int dt = d->dtype, gimpl = d->gemm_impl;
+  const int64_t N = d->N, C = d->C, H = d->H;
+  const size_t e = esize(dt);
+  const bool in_out = d->weight_layout == SPB_W_IN_OUT;
+  const int tB = in_out ? 0 : 1;
+  // 1. ffn_norm (llama3:886 rms_norm(h, params['ffn_norm']))
+  const void* xin = x;
+  if (d->norm_kind != SPB_NORM_NONE) {
+    SPB_CHECK_ARG(p->norm_w != nullptr, SPB_E_INVALID, "spb_ffn_fwd: norm_w is NULL");
+    rc = spb_norm_fwd(dt, d->norm_kind, d->norm_upcast, d->norm_eps, x, p->norm_w, p->norm_b, w8 + L.xhat, (float*)(w8 + L.stats), N, d->C,
+                      stream);
+    if (rc) return rc;
+    xin = w8 + L.xhat;
+  }
+  // 2. g13 = [x.w1 | x.w3]  (llama3:855: the two inner dots)
+  char* g13 = w8 + L.g13;
+  if (ffn_packed(d, p->w1, p->w3, p->ldw_13)) {
+    rc = gemm_any(dt, dt, gimpl, N, 2 * H, C, xin, C, 0, p->w1, p->ldw_13, tB, g13, 2 * H, nullptr, 0, st, nullptr, 0, 0, 0);
+    if (rc) return rc;
+  } else {
+    rc = gemm_any(dt, dt, gimpl, N, H, C, xin, C, 0, p->w1, p->ldw_13, tB, g13, 2 * H, nullptr, 0, st, nullptr, 0, 0, 0);
+    if (rc) return rc;
+    rc = gemm_any(dt, dt, gimpl, N, H, C, xin, C, 0, p->w3, p->ldw_13, tB, g13 + H * e, 2 * H, nullptr, 0, st, nullptr, 0, 0, 0);
+    if (rc) return rc;
+  }
+  // 3. a = silu(g3) * g1
+  rc = swiglu_fwd(dt, g13, 2 * H, w8 + L.act, H, N, (int)H, st);
+  if (rc) return rc;
+  // 4. y = a . w2 (+ h: llama3:890 out = h + ffn_output, in the epilogue)
+  return gemm_any(dt, dt, gimpl, N, C, H, w8 + L.act, H, 0, p->w2, p->ldw_2, tB, y, C, nullptr, 0, st, nullptr, 0, 0, 0,
+                  d->residual ? x : nullptr, C);
+}
+
+int spb_ffn_bwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, const void* dy, void* ws, const spb_ffn_grads* g,
+                void* comm, spb_stream_t stream) {
+  int rc = check_ffn_desc(d);
+  if (rc) return rc;
+  SPB_CHECK_ARG(p && x && dy && ws && g && p->w1 && p->w3 && p->w2, SPB_E_INVALID, "spb_ffn_bwd: null pointer");
+  spb_ffn_ws L;
+  rc = spb_ffn_ws_layout(d, &L);
+  if (rc) return rc;
+  char* w8 = (char*)ws;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int dt = d->dtype, gimpl = d->gemm_impl;
+  const int64_t N = d->N, C = d->C, H = d->H;
+  const size_t e = esize(dt);
+  const bool in_out = d->weight_layout == SPB_W_IN_OUT;
+  const void* xin = (d->norm_kind != SPB_NORM_NONE) ? (const void*)(w8 + L.xhat) : x;
+  char* g13 = w8 + L.g13;
+  char* dg13 = w8 + L.dg13;
+  const bool packed = ffn_packed(d, p->w1, p->w3, p->ldw_13);
+  // 1. da = dy . w2^T
+  rc = gemm_any(dt, dt, gimpl, N, H, C, dy, C, 0, p->w2, p->ldw_2, in_out ? 1 : 0, w8 + L.dact, H, nullptr, 0, st, nullptr, 0, 0, 0);
+  if (rc) return rc;
+  // 2. dg13 from da and the saved pre-activations
+  rc = swiglu_bwd(dt, g13, 2 * H, w8 + L.dact, H, dg13, 2 * H, N, (int)H, st);
+  if (rc) return rc;
+  // 3. weight gradients (fp32): dw13 = xin^T . dg13 first (the larger all-reduce gets the most work behind it), then dw2 = a^T . dy
+  bool gpacked = g->dw1 && g->dw3 && (in_out ? g->dw3 == g->dw1 + H : g->dw3 == g->dw1 + H * g->ldw_13);
+  auto dw13 = [&](float* dw, const char* dcols, int64_t width) -> int {
+    if (dw == nullptr) return 0;
+    if (in_out) return spb_gemm(dt, SPB_F32, gimpl, C, width, N, xin, C, 1, dcols, 2 * H, 0, dw, g->ldw_13, nullptr, 0, stream);
+    return spb_gemm(dt, SPB_F32, gimpl, width, C, N, dcols, 2 * H, 1, xin, C, 0, dw, g->ldw_13, nullptr, 0, stream);
+  };
+  if (gpacked) {
+    rc = dw13(g->dw1, dg13, 2 * H);
+    if (rc) return rc;
+  } else {
+    rc = dw13(g->dw1, dg13, H);
+    if (rc) return rc;
+    rc = dw13(g->dw3, dg13 + H * e, H);
+    if (rc) return rc;
+  }
+  if (comm != nullptr && (g->dw1 || g->dw3)) {
+    float* ptrs[2];
+    size_t counts[2];
+    int n = 0;
+    const int64_t rows = in_out ? C : H, cols = in_out ? H : C;
+    if (gpacked) {
+      SPB_CHECK_ARG(g->ldw_13 == (in_out ? 2 * H : C), SPB_E_UNSUPPORTED, "spb_ffn_bwd: all-reduce needs contiguous weight gradients");
+      ptrs[n] = g->dw1;
+      counts[n++] = (size_t)(2 * H * C);
+    } else {
+      SPB_CHECK_ARG(g->ldw_13 == cols, SPB_E_UNSUPPORTED, "spb_ffn_bwd: all-reduce needs contiguous weight gradients");
+      if (g->dw1) { ptrs[n] = g->dw1; counts[n++] = (size_t)(rows * cols); }
+      if (g->dw3) { ptrs[n] = g->dw3; counts[n++] = (size_t)(rows * cols); }
+    }
+    rc = comm_allreduce_side(comm, ptrs, counts, n, st);
+    if (rc) return rc;
+  }
+  if (g->dw2) {
+    if (in_out) rc = spb_gemm(dt, SPB_F32, gimpl, H, C, N, w8 + L.act, H, 1, dy, C, 0, g->dw2, g->ldw_2, nullptr, 0, stream);
+    else rc = spb_gemm(dt, SPB_F32, gimpl, C, H, N, dy, C, 1, w8 + L.act, H, 0, g->dw2, g->ldw_2, nullptr, 0, stream);
+    if (rc) return rc;
+    if (comm != nullptr) {
+      SPB_CHECK_ARG(g->ldw_2 == (in_out ? C : H), SPB_E_UNSUPPORTED, "spb_ffn_bwd: all-reduce needs a contiguous dw2");
+      float* ptrs[1] = {g->dw2};
+      size_t counts[1] = {(size_t)(H * C)};
+      rc = comm_allreduce_side(comm, ptrs, counts, 1, st);
+      if (rc) return rc;
+    }
+  }
+  // 4. dxhat = dg13 . [w1 | w3]^T  (+ dy through the residual when there is no norm)
+  void* dxhat = (d->norm_kind != SPB_NORM_NONE) ? (void*)(w8 + L.dxhat) : g->dx;
+  const void* dx_res = (d->residual && d->norm_kind == SPB_NORM_NONE) ? dy : nullptr;
+  const int tBx = in_out ? 1 : 0;
+  if (dxhat != nullptr) {
+    if (packed) {
+      rc = gemm_any(dt, dt, gimpl, N, C, 2 * H, dg13, 2 * H, 0, p->w1, p->ldw_13, tBx, dxhat, C, nullptr, 0, st, nullptr, 0, 0, 0, dx_res, C);
+      if (rc) return rc;
+    } else {
+      rc = gemm_any(dt, dt, gimpl, N, C, H, dg13, 2 * H, 0, p->w1, p->ldw_13, tBx, dxhat, C, nullptr, 0, st, nullptr, 0, 0, 0, dx_res, C);
+      if (rc) return rc;
+      rc = gemm_any(dt, dt, gimpl, N, C, H, dg13 + H * e, 2 * H, 0, p->w3, p->ldw_13, tBx, dxhat, C, nullptr, 1, st, nullptr, 0, 0, 0);
+      if (rc) return rc;
+    }
+  }
+  // 5. norm VJP (+ dy through the residual)
+  if (d->norm_kind != SPB_NORM_NONE) {
+    rc = norm_bwd_add(dt, d->norm_kind, d->norm_upcast, x, p->norm_w, (const float*)(w8 + L.stats), w8 + L.dxhat, g->dx, g->dnorm_w,
+                      g->dnorm_b, w8 + L.partial, N, d->C, d->residual ? dy : nullptr, st);
+    if (rc) return rc;
+  }
+  if (comm != nullptr) {
+    float* ptrs[2];
+    size_t counts[2];
+    int n = 0;
+    if (g->dnorm_w && d->norm_kind != SPB_NORM_NONE) { ptrs[n] = g->dnorm_w; counts[n++] = (size_t)d->C; }
+    if (g->dnorm_b && d->norm_kind == SPB_NORM_LAYER) { ptrs[n] = g->dnorm_b; counts[n++] = (size_t)d->C; }
+    rc = comm_allreduce_join(comm, ptrs, counts, n, st);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
 }  // extern "C"

@@ -81,3 +81,24 @@ def attention_block(block_params, x, mask, freqs_cis, n_heads, n_kv_heads, eps=1
     names = ("wq", "wk", "wv", "wo", "norm_w", "rope")
     y, k, v = BlockFn.apply(cfg, names, comm, x, a["wq"], a["wk"], a["wv"], a["wo"], block_params["attention_norm"], tab)
     return y, (k, v)
+
+
+def feed_forward(params, x, comm=None):
+    """llama3/LLaMA-jax.ipynb:854-855: ``dot(silu(dot(x, w3)) * dot(x, w1), w2)`` with w1, w3 [C, 4C], w2 [4C, C]."""
+    from .ffn import FfnConfig, FfnFn
+    C_ = x.shape[-1]
+    cfg = FfnConfig(N=x.numel() // C_, C=C_, H=params["w1"].shape[1], dtype=x.dtype, norm_kind=L.NORM_NONE)
+    y = FfnFn.apply(cfg, ("w1", "w3", "w2"), comm, x.reshape(-1, C_), params["w1"], params["w3"], params["w2"])
+    return y.reshape(x.shape)
+
+
+def ffn_block(block_params, h, eps=1e-6, comm=None, residual=True):
+    """The second half of transformer_block (llama3/LLaMA-jax.ipynb:886-890):
+    ``out = h + feed_forward(params['ffn'], rms_norm(h, params['ffn_norm']))`` - one C-ABI call forward, one backward,
+    the residual add in the w2 GEMM's epilogue (residual=False returns the ffn output alone)."""
+    from .ffn import FfnConfig, FfnFn
+    C_ = h.shape[-1]
+    f = block_params["ffn"]
+    cfg = FfnConfig(N=h.numel() // C_, C=C_, H=f["w1"].shape[1], dtype=h.dtype, norm_kind=L.NORM_RMS, norm_eps=eps, residual=residual)
+    y = FfnFn.apply(cfg, ("w1", "w3", "w2", "norm_w"), comm, h.reshape(-1, C_), f["w1"], f["w3"], f["w2"], block_params["ffn_norm"])
+    return y.reshape(h.shape)

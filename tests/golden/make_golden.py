@@ -142,6 +142,66 @@ def make_llama(tag, B, T, C, H, Hkv, causal, seed):
     print("llama", tag, "y", y.shape, "max|y|", np.abs(y).max())
 
 
+def make_llama_ffn(tag, B, T, C, seed):
+    """the notebook's own feed_forward cell (c25) and the two lines of transformer_block that use it
+    (llama3/LLaMA-jax.ipynb:886,890: ffn_output = feed_forward(params['ffn'], rms_norm(h, params['ffn_norm'])); out = h + ffn_output),
+    executed with jnp bound to numpy; fp32 outputs, fp64 outputs, finite-difference directional derivatives."""
+    rng = np.random.default_rng(seed)
+    f32 = np.float32
+    Hh = 4 * C  # init_ffn_weights, llama3:716-718
+    h_in = rng.standard_normal((B, T, C)).astype(f32)
+    dy = rng.standard_normal((B, T, C)).astype(f32)
+    p = {"w1": (rng.standard_normal((C, Hh)) / math.sqrt(C)).astype(f32), "w2": (rng.standard_normal((Hh, C)) / math.sqrt(Hh)).astype(f32),
+         "w3": (rng.standard_normal((C, Hh)) / math.sqrt(C)).astype(f32)}
+    nw = rng.standard_normal((C,)).astype(f32)
+
+    def namespace(high):
+        ns = llama_namespace(high)
+        ns["jax"].nn.silu = lambda z: z / (1.0 + np.exp(-z))
+        exec(cell_src("llama3/LLaMA-jax.ipynb", 25), ns)
+        return ns
+
+    def run(ns, h_, p_, nw_):
+        ffn_output = ns["feed_forward"](p_, ns["rms_norm"](h_, nw_))  # :886
+        return h_ + ffn_output, ffn_output                             # :890
+
+    ns32, ns64 = namespace(False), namespace(True)
+    out32, ffn32 = run(ns32, h_in, p, nw)
+    assert out32.dtype == np.float32
+    h64, dy64, nw64 = h_in.astype(np.float64), dy.astype(np.float64), nw.astype(np.float64)
+    p64 = {k_: v_.astype(np.float64) for k_, v_ in p.items()}
+    out64, ffn64 = run(ns64, h64, p64, nw64)
+
+    def loss(h_, p_, nw_):
+        return float(np.sum(run(ns64, h_, p_, nw_)[0] * dy64))
+
+    hstep = 1e-5
+    out = dict(h=h_in, dy=dy, norm_w=nw, out=out32, ffn=ffn32, out64=out64, ffn64=ffn64, meta=np.array([B, T, C, Hh], dtype=np.int64), **p)
+    for name in ("h", "norm_w", "w1", "w2", "w3"):
+        base = h64 if name == "h" else nw64 if name == "norm_w" else p64[name]
+        dirs, vals = [], []
+        for _ in range(3):
+            u = rng.standard_normal(base.shape)
+            u /= np.linalg.norm(u)
+
+            def at(eps):
+                hh, pp, nn = h64, dict(p64), nw64
+                if name == "h":
+                    hh = h64 + eps * u
+                elif name == "norm_w":
+                    nn = nw64 + eps * u
+                else:
+                    pp[name] = p64[name] + eps * u
+                return loss(hh, pp, nn)
+
+            vals.append((-at(2 * hstep) + 8 * at(hstep) - 8 * at(-hstep) + at(-2 * hstep)) / (12 * hstep))
+            dirs.append(u)
+        out["fd_dir_" + name] = np.stack(dirs)
+        out["fd_val_" + name] = np.array(vals)
+    np.savez_compressed(os.path.join(OUT, f"llama_ffn_{tag}.npz"), **out)
+    print("llama ffn", tag, "out", out32.shape, "max|out|", np.abs(out32).max())
+
+
 # --------------------------------------------------------------------------- gemma
 def make_gemma(tag, B, T, D, seed):
     ns = {}
@@ -241,6 +301,7 @@ if __name__ == "__main__":
     make_llama("gqa_causal", B=2, T=16, C=64, H=4, Hkv=2, causal=True, seed=0)
     make_llama("mha_nomask", B=1, T=9, C=32, H=2, Hkv=2, causal=False, seed=1)
     make_llama("mqa_causal", B=2, T=12, C=64, H=4, Hkv=1, causal=True, seed=2)
+    make_llama_ffn("small", B=2, T=12, C=32, seed=5)
     make_gemma("small", B=2, T=16, D=64, seed=3)
     print("gemma MQA default param count", gemma_param_count_pin())
     make_vit("nb", B=3, T=17, E=64, H=4, seed=4)  # the notebook's literal shape

@@ -47,6 +47,24 @@ def test_llama_gradients_match_finite_differences_of_notebook_source(golden_dir,
     assert max_rel_err(r["dnorm"], T(g["fd_grad_norm_w"])) < 1e-6
 
 
+def test_llama_ffn_matches_literal_notebook_source_and_its_finite_differences(golden_dir):
+    """oracle feed_forward / ffn_block against the notebook's own feed_forward cell (llama3:854-855) and the two
+    lines of transformer_block that call it (:886,:890) - fp32 and fp64 forward, fp64 directional derivatives."""
+    g = _load(golden_dir, "llama_ffn_small.npz")
+    p = {"ffn": {k: T(g[k]) for k in ("w1", "w2", "w3")}, "ffn_norm": T(g["norm_w"])}
+    r32 = llama_oracle.ffn_fwd_bwd(p, T(g["h"]), T(g["dy"]), dtype=torch.float32)
+    assert max_rel_err(r32["y"], T(g["out"])) < 2e-6
+    assert max_rel_err(llama_oracle.ffn_block(p, T(g["h"]), residual=False), T(g["ffn"])) < 2e-6
+    r64 = llama_oracle.ffn_fwd_bwd(p, T(g["h"]), T(g["dy"]), dtype=torch.float64)
+    assert max_rel_err(r64["y"], T(g["out64"])) < 1e-12
+    names = {"h": "dx", "norm_w": "dnorm", "w1": "dw1", "w2": "dw2", "w3": "dw3"}
+    for name, gname in names.items():
+        grad = r64[gname].numpy()
+        for u, fd in zip(g["fd_dir_" + name], g["fd_val_" + name]):
+            an = float(np.sum(grad * u))
+            assert abs(an - fd) <= 2e-6 * max(1.0, abs(fd)) + 1e-7, (name, an, fd)
+
+
 def test_llama_freq_exponent_quirk(golden_dir):
     """f_j = theta^(-j/hd), not the paper's theta^(-2j/hd) (llama3:564)."""
     g = _load(golden_dir, "llama_gqa_causal.npz")
