@@ -216,7 +216,11 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
  * llama3:854-855  feed_forward(p, x) = dot(silu(dot(x, p['w3'])) * dot(x, p['w1']), p['w2'])
  * Weights as init_ffn_weights stores them (llama3:713-718): w1, w3 [C, H], w2 [H, C] for SPB_W_IN_OUT (H = 4*C in the
  * notebook); SPB_W_OUT_IN: w1, w3 [H, C], w2 [C, H].                                                              */
-#define SPB_ACT_SWIGLU 0   /* silu(x.w3) * (x.w1)  - the only activation built so far (GeGLU / GELU-MLP: not yet) */
+#define SPB_ACT_SWIGLU    0  /* silu(x.w3) * (x.w1), w2                                   llama3:854-855                   */
+#define SPB_ACT_GEGLU     1  /* gelu_erf(x.w3) * (x.w1), w2: w3 = linear_layer1 (gate), w1 = linear_layer2 (value),
+                                w2 = linear_layer3, torch [out,in] weights                  gemma:277-285                    */
+#define SPB_ACT_GELU_TANH 2  /* plain MLP gelu_tanh(x.w1 + b1).w2 + b2 (flax nn.gelu default approximate=True); w3 unused
+                                                                                           gpt:381-388                      */
 
 typedef struct spb_ffn_desc {
   int32_t N, C, H;        /* tokens (B*T), model width, hidden width */
@@ -234,6 +238,8 @@ typedef struct spb_ffn_params {
   const void* norm_w; const void* norm_b;     /* [C] dtype */
   const void* w1; const void* w3; int64_t ldw_13;  /* same row stride for both; packed [C, 2H] (w3 = w1 + H) is one GEMM */
   const void* w2; int64_t ldw_2;
+  const void* b1;     /* [H] dtype or NULL: bias of the up projection (SPB_ACT_GELU_TANH: flax nn.Dense default use_bias) */
+  const void* b2;     /* [C] dtype or NULL: bias of the down projection                                                  */
 } spb_ffn_params;
 
 typedef struct spb_ffn_grads {
@@ -241,6 +247,7 @@ typedef struct spb_ffn_grads {
   float* dnorm_w; float* dnorm_b;             /* [C] */
   float* dw1; float* dw3; int64_t ldw_13;     /* fp32, same layout as the weights */
   float* dw2; int64_t ldw_2;
+  float* db1; float* db2;                     /* [H], [C] fp32 or NULL */
 } spb_ffn_grads;
 
 /* Byte offsets inside the caller-owned workspace */
@@ -248,7 +255,7 @@ typedef struct spb_ffn_ws {
   size_t total;
   size_t xhat;     /* [N, C] dtype normalised input (unused when norm_kind == NONE)        */
   size_t stats;    /* [N, 2] f32                                                            */
-  size_t g13;      /* [N, 2H] dtype: x.w1 in columns [0,H), x.w3 in [H,2H)  (residual)      */
+  size_t g13;      /* [N, 2H] dtype: x.w1 in columns [0,H), x.w3 in [H,2H)  (residual); [N, H] for the plain MLP */
   size_t act;      /* [N, H] dtype: silu(g3)*g1 = the w2 GEMM's operand     (residual)      */
   size_t dact;     /* [N, H] dtype                                           (backward)     */
   size_t dg13;     /* [N, 2H] dtype                                          (backward)     */

@@ -97,3 +97,31 @@ def block_fwd_bwd(params, x, dy, dtype=torch.float32):
         "y": y.detach(), "dx": xx.grad, "dwq": [w.grad for w in p["wq"]],
         "dwk": p["wk"].grad, "dwv": p["wv"].grad, "dwo": p["wo"].grad, "dnorm": p["norm_w"].grad,
     }
+
+
+# ---- GeGLU feed-forward ------------------------------------------------------------
+def geglu(params, x):
+    """gemma/gemma.ipynb:281-286 - ``linear_layer3(gelu(linear_layer1(x)) * linear_layer2(x))``; torch ``nn.Linear(bias=False)``
+    weights are [out, in] (:277-279, hidden = 4 * embeddings_dims :276); ``nn.functional.gelu`` default = exact erf form."""
+    gelu_res = torch.nn.functional.gelu(torch.matmul(x, params["linear_layer1"].t()))
+    x_v = torch.matmul(x, params["linear_layer2"].t())
+    return torch.matmul(gelu_res * x_v, params["linear_layer3"].t())
+
+
+def init_geglu_params(rng, D, dtype=torch.float32):
+    """torch nn.Linear default init is U(-1/sqrt(in), 1/sqrt(in)); any fixed distribution serves parity."""
+    Hh = 4 * D
+
+    def u(out_f, in_f):
+        b = 1.0 / math.sqrt(in_f)
+        return torch.from_numpy(rng.uniform(-b, b, size=(out_f, in_f))).to(dtype)
+
+    return {"linear_layer1": u(Hh, D), "linear_layer2": u(Hh, D), "linear_layer3": u(D, Hh)}
+
+
+def geglu_fwd_bwd(params, x, dy, dtype=torch.float32):
+    p = {k: v.detach().to(dtype).requires_grad_(True) for k, v in params.items()}
+    xx = x.detach().to(dtype).requires_grad_(True)
+    y = geglu(p, xx)
+    y.backward(dy.to(dtype))
+    return {"y": y.detach(), "dx": xx.grad, "dl1": p["linear_layer1"].grad, "dl2": p["linear_layer2"].grad, "dl3": p["linear_layer3"].grad}

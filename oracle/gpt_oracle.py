@@ -9,6 +9,7 @@ Third-party semantics restated from flax.linen's published behaviour:
   * ``nn.Dense(n, use_bias)``: x @ kernel[in,out] (+ bias).
 """
 import math
+import numpy as np
 import torch
 
 
@@ -76,3 +77,27 @@ def block_fwd_bwd(params, x, dy, num_heads, dtype=torch.float32):
         "dqkv_kernel": p["qkv_kernel"].grad, "dproj_kernel": p["proj_kernel"].grad,
         "dproj_bias": p["proj_bias"].grad, "dln_scale": p["ln_scale"].grad, "dln_bias": p["ln_bias"].grad,
     }
+
+
+# ---- the GELU MLP --------------------------------------------------------------------
+def mlp(params, x):
+    """gpt/gpt-jax.ipynb:385-389 with deterministic=True (dropout off): ``fc2(nn.gelu(fc1(x)))``; flax ``nn.Dense`` = x @ kernel
+    + bias with kernel [in, out] (:381-382, hidden = 4 * emb_dim); flax ``nn.gelu`` defaults to approximate=True (tanh form)."""
+    hdn = torch.nn.functional.gelu(torch.matmul(x, params["fc1_kernel"]) + params["fc1_bias"], approximate="tanh")
+    return torch.matmul(hdn, params["fc2_kernel"]) + params["fc2_bias"]
+
+
+def init_mlp_params(rng, dim, dtype=torch.float32, nonzero_bias=True):
+    """flax Dense: lecun_normal kernel, zero bias; non-zero biases here so that the bias path is exercised."""
+    Hh = 4 * dim
+    w = lambda i, o: torch.from_numpy(rng.standard_normal((i, o)) / math.sqrt(i)).to(dtype)
+    b = lambda n: torch.from_numpy(rng.standard_normal((n,)) * 0.1 if nonzero_bias else np.zeros((n,))).to(dtype)
+    return {"fc1_kernel": w(dim, Hh), "fc1_bias": b(Hh), "fc2_kernel": w(Hh, dim), "fc2_bias": b(dim)}
+
+
+def mlp_fwd_bwd(params, x, dy, dtype=torch.float32):
+    p = {k: v.detach().to(dtype).requires_grad_(True) for k, v in params.items()}
+    xx = x.detach().to(dtype).requires_grad_(True)
+    y = mlp(p, xx)
+    y.backward(dy.to(dtype))
+    return {"y": y.detach(), "dx": xx.grad, **{"d" + k: v.grad for k, v in p.items()}}

@@ -181,3 +181,11 @@ def ffn_fwd_bwd(block_params, h, dy, dtype=torch.float32, residual=True, norm=Tr
     y.backward(dy.to(dtype))
     return {"y": y.detach(), "dx": hh.grad, "dw1": f["w1"].grad, "dw2": f["w2"].grad, "dw3": f["w3"].grad,
             "dnorm": nw.grad if norm else None}
+
+
+def transformer_block(params, x, mask, freqs_cis, n_heads, n_kv_heads):
+    """llama3/LLaMA-jax.ipynb:880-891 with training=False (the only way the notebook calls it, :927)."""
+    attn_output, new_cache = attention(params["attention"], rms_norm(x, params["attention_norm"]), mask, freqs_cis, n_heads, n_kv_heads)
+    h = x + attn_output
+    ffn_output = feed_forward(params["ffn"], rms_norm(h, params["ffn_norm"]))
+    return h + ffn_output, new_cache

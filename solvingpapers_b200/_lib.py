@@ -46,12 +46,13 @@ class FfnDesc(C.Structure):
 
 
 class FfnParams(C.Structure):
-    _fields_ = [("norm_w", vp), ("norm_b", vp), ("w1", vp), ("w3", vp), ("ldw_13", i64), ("w2", vp), ("ldw_2", i64)]
+    _fields_ = [("norm_w", vp), ("norm_b", vp), ("w1", vp), ("w3", vp), ("ldw_13", i64), ("w2", vp), ("ldw_2", i64), ("b1", vp),
+                ("b2", vp)]
 
 
 class FfnGrads(C.Structure):
     _fields_ = [("dx", vp), ("dnorm_w", vp), ("dnorm_b", vp), ("dw1", vp), ("dw3", vp), ("ldw_13", i64), ("dw2", vp),
-                ("ldw_2", i64)]
+                ("ldw_2", i64), ("db1", vp), ("db2", vp)]
 
 
 class FfnWs(C.Structure):
@@ -59,7 +60,7 @@ class FfnWs(C.Structure):
                 ("partial", sz), ("partial_bytes", sz)]
 
 
-ACT_SWIGLU = 0
+ACT_SWIGLU, ACT_GEGLU, ACT_GELU_TANH = 0, 1, 2
 
 # name -> (restype, argtypes); every symbol include/spb200.h declares
 SIGNATURES = {

@@ -566,7 +566,8 @@ static int check_ffn_desc(const spb_ffn_desc* d) {
   SPB_CHECK_ARG(d->N > 0 && d->C > 0 && d->H > 0, SPB_E_INVALID, "ffn desc: non-positive dimension (N=%d C=%d H=%d)", d->N, d->C, d->H);
   SPB_CHECK_ARG(d->dtype == SPB_F32 || d->dtype == SPB_BF16, SPB_E_UNSUPPORTED, "ffn desc: dtype %d", d->dtype);
   SPB_CHECK_ARG(d->norm_kind >= SPB_NORM_NONE && d->norm_kind <= SPB_NORM_LAYER, SPB_E_INVALID, "ffn desc: norm_kind %d", d->norm_kind);
-  SPB_CHECK_ARG(d->act == SPB_ACT_SWIGLU, SPB_E_UNSUPPORTED, "ffn desc: activation %d (only SPB_ACT_SWIGLU is built)", d->act);
+  SPB_CHECK_ARG(d->act == SPB_ACT_SWIGLU || d->act == SPB_ACT_GEGLU || d->act == SPB_ACT_GELU_TANH, SPB_E_UNSUPPORTED,
+                "ffn desc: activation %d (SPB_ACT_SWIGLU, SPB_ACT_GEGLU, SPB_ACT_GELU_TANH)", d->act);
   SPB_CHECK_ARG(d->weight_layout == SPB_W_IN_OUT || d->weight_layout == SPB_W_OUT_IN, SPB_E_INVALID, "ffn desc: weight_layout %d",
                 d->weight_layout);
   SPB_CHECK_ARG(d->residual == 0 || d->residual == 1, SPB_E_INVALID, "ffn desc: residual %d", d->residual);
@@ -592,7 +593,7 @@ int spb_ffn_ws_layout(const spb_ffn_desc* d, spb_ffn_ws* out) {
   out->dact = take(N * H * e);
   out->dg13 = take(N * 2 * H * e);
   out->dxhat = take(N * C * e);
-  out->partial_bytes = spb_norm_bwd_partial_bytes((int64_t)N, d->C);
+  out->partial_bytes = spb_norm_bwd_partial_bytes((int64_t)N, d->C > d->H ? d->C : d->H);  // also the bias column sums ([H] wide)
   out->partial = take(out->partial_bytes);
   out->total = off;
   return 0;
@@ -608,7 +609,8 @@ static bool ffn_packed(const spb_ffn_desc* d, const void* w1, const void* w3, in
 int spb_ffn_fwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, void* y, void* ws, spb_stream_t stream) {
   int rc = check_ffn_desc(d);
   if (rc) return rc;
-  SPB_CHECK_ARG(p && x && y && ws && p->w1 && p->w3 && p->w2, SPB_E_INVALID, "spb_ffn_fwd: null pointer");
+  const bool gated = d->act != SPB_ACT_GELU_TANH;
+  SPB_CHECK_ARG(p && x && y && ws && p->w1 && (p->w3 || !gated) && p->w2, SPB_E_INVALID, "spb_ffn_fwd: null pointer");
   spb_ffn_ws L;
   rc = spb_ffn_ws_layout(d, &L);
   if (rc) return rc;
@@ -628,22 +630,26 @@ int spb_ffn_fwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, v
     if (rc) return rc;
     xin = w8 + L.xhat;
   }
-  // 2. g13 = [x.w1 | x.w3]  (llama3:855: the two inner dots)
+  // 2. pre-activations: gated kinds g13 = [x.w1 | x.w3] (llama3:855: the two inner dots); plain MLP g = x.w1 + b1 (gpt:386)
   char* g13 = w8 + L.g13;
-  if (ffn_packed(d, p->w1, p->w3, p->ldw_13)) {
-    rc = gemm_any(dt, dt, gimpl, N, 2 * H, C, xin, C, 0, p->w1, p->ldw_13, tB, g13, 2 * H, nullptr, 0, st, nullptr, 0, 0, 0);
+  const int64_t G = gated ? 2 * H : H;
+  if (!gated) {
+    rc = gemm_any(dt, dt, gimpl, N, H, C, xin, C, 0, p->w1, p->ldw_13, tB, g13, G, p->b1, 0, st, nullptr, 0, 0, 0);
+    if (rc) return rc;
+  } else if (ffn_packed(d, p->w1, p->w3, p->ldw_13)) {
+    rc = gemm_any(dt, dt, gimpl, N, 2 * H, C, xin, C, 0, p->w1, p->ldw_13, tB, g13, G, nullptr, 0, st, nullptr, 0, 0, 0);
     if (rc) return rc;
   } else {
-    rc = gemm_any(dt, dt, gimpl, N, H, C, xin, C, 0, p->w1, p->ldw_13, tB, g13, 2 * H, nullptr, 0, st, nullptr, 0, 0, 0);
+    rc = gemm_any(dt, dt, gimpl, N, H, C, xin, C, 0, p->w1, p->ldw_13, tB, g13, G, nullptr, 0, st, nullptr, 0, 0, 0);
     if (rc) return rc;
-    rc = gemm_any(dt, dt, gimpl, N, H, C, xin, C, 0, p->w3, p->ldw_13, tB, g13 + H * e, 2 * H, nullptr, 0, st, nullptr, 0, 0, 0);
+    rc = gemm_any(dt, dt, gimpl, N, H, C, xin, C, 0, p->w3, p->ldw_13, tB, g13 + H * e, G, nullptr, 0, st, nullptr, 0, 0, 0);
     if (rc) return rc;
   }
-  // 3. a = silu(g3) * g1
-  rc = swiglu_fwd(dt, g13, 2 * H, w8 + L.act, H, N, (int)H, st);
+  // 3. a = act(gate) * value   /   a = act(g)
+  rc = ffn_act_fwd(dt, d->act, g13, G, w8 + L.act, H, N, (int)H, st);
   if (rc) return rc;
   // 4. y = a . w2 (+ h: llama3:890 out = h + ffn_output, in the epilogue)
-  return gemm_any(dt, dt, gimpl, N, C, H, w8 + L.act, H, 0, p->w2, p->ldw_2, tB, y, C, nullptr, 0, st, nullptr, 0, 0, 0,
+  return gemm_any(dt, dt, gimpl, N, C, H, w8 + L.act, H, 0, p->w2, p->ldw_2, tB, y, C, p->b2, 0, st, nullptr, 0, 0, 0,
                   d->residual ? x : nullptr, C);
 }
 
@@ -651,7 +657,8 @@ int spb_ffn_bwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, c
                 void* comm, spb_stream_t stream) {
   int rc = check_ffn_desc(d);
   if (rc) return rc;
-  SPB_CHECK_ARG(p && x && dy && ws && g && p->w1 && p->w3 && p->w2, SPB_E_INVALID, "spb_ffn_bwd: null pointer");
+  const bool gated = d->act != SPB_ACT_GELU_TANH;
+  SPB_CHECK_ARG(p && x && dy && ws && g && p->w1 && (p->w3 || !gated) && p->w2, SPB_E_INVALID, "spb_ffn_bwd: null pointer");
   spb_ffn_ws L;
   rc = spb_ffn_ws_layout(d, &L);
   if (rc) return rc;
@@ -664,19 +671,30 @@ int spb_ffn_bwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, c
   const void* xin = (d->norm_kind != SPB_NORM_NONE) ? (const void*)(w8 + L.xhat) : x;
   char* g13 = w8 + L.g13;
   char* dg13 = w8 + L.dg13;
-  const bool packed = ffn_packed(d, p->w1, p->w3, p->ldw_13);
+  const bool packed = gated && ffn_packed(d, p->w1, p->w3, p->ldw_13);
+  const int64_t G = gated ? 2 * H : H;
+  void* partial = w8 + L.partial;
+  // 0. bias gradient of the down projection: db2 = column sums of dy
+  if (g->db2) {
+    rc = spb_colsum(dt, dy, C, N, (int32_t)C, g->db2, partial, stream);
+    if (rc) return rc;
+  }
   // 1. da = dy . w2^T
   rc = gemm_any(dt, dt, gimpl, N, H, C, dy, C, 0, p->w2, p->ldw_2, in_out ? 1 : 0, w8 + L.dact, H, nullptr, 0, st, nullptr, 0, 0, 0);
   if (rc) return rc;
   // 2. dg13 from da and the saved pre-activations
-  rc = swiglu_bwd(dt, g13, 2 * H, w8 + L.dact, H, dg13, 2 * H, N, (int)H, st);
+  rc = ffn_act_bwd(dt, d->act, g13, G, w8 + L.dact, H, dg13, G, N, (int)H, st);
   if (rc) return rc;
+  if (g->db1) {  // bias gradient of the up projection: column sums of dg
+    rc = spb_colsum(dt, dg13, G, N, (int32_t)H, g->db1, partial, stream);
+    if (rc) return rc;
+  }
   // 3. weight gradients (fp32): dw13 = xin^T . dg13 first (the larger all-reduce gets the most work behind it), then dw2 = a^T . dy
-  bool gpacked = g->dw1 && g->dw3 && (in_out ? g->dw3 == g->dw1 + H : g->dw3 == g->dw1 + H * g->ldw_13);
+  bool gpacked = gated && g->dw1 && g->dw3 && (in_out ? g->dw3 == g->dw1 + H : g->dw3 == g->dw1 + H * g->ldw_13);
   auto dw13 = [&](float* dw, const char* dcols, int64_t width) -> int {
     if (dw == nullptr) return 0;
-    if (in_out) return spb_gemm(dt, SPB_F32, gimpl, C, width, N, xin, C, 1, dcols, 2 * H, 0, dw, g->ldw_13, nullptr, 0, stream);
-    return spb_gemm(dt, SPB_F32, gimpl, width, C, N, dcols, 2 * H, 1, xin, C, 0, dw, g->ldw_13, nullptr, 0, stream);
+    if (in_out) return spb_gemm(dt, SPB_F32, gimpl, C, width, N, xin, C, 1, dcols, G, 0, dw, g->ldw_13, nullptr, 0, stream);
+    return spb_gemm(dt, SPB_F32, gimpl, width, C, N, dcols, G, 1, xin, C, 0, dw, g->ldw_13, nullptr, 0, stream);
   };
   if (gpacked) {
     rc = dw13(g->dw1, dg13, 2 * H);
@@ -684,10 +702,12 @@ int spb_ffn_bwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, c
   } else {
     rc = dw13(g->dw1, dg13, H);
     if (rc) return rc;
-    rc = dw13(g->dw3, dg13 + H * e, H);
-    if (rc) return rc;
+    if (gated) {
+      rc = dw13(g->dw3, dg13 + H * e, H);
+      if (rc) return rc;
+    }
   }
-  if (comm != nullptr && (g->dw1 || g->dw3)) {
+  if (comm != nullptr && (g->dw1 || (gated && g->dw3))) {
     float* ptrs[2];
     size_t counts[2];
     int n = 0;
@@ -699,7 +719,7 @@ int spb_ffn_bwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, c
     } else {
       SPB_CHECK_ARG(g->ldw_13 == cols, SPB_E_UNSUPPORTED, "spb_ffn_bwd: all-reduce needs contiguous weight gradients");
       if (g->dw1) { ptrs[n] = g->dw1; counts[n++] = (size_t)(rows * cols); }
-      if (g->dw3) { ptrs[n] = g->dw3; counts[n++] = (size_t)(rows * cols); }
+      if (gated && g->dw3) { ptrs[n] = g->dw3; counts[n++] = (size_t)(rows * cols); }
     }
     rc = comm_allreduce_side(comm, ptrs, counts, n, st);
     if (rc) return rc;
@@ -722,19 +742,21 @@ int spb_ffn_bwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, c
   const int tBx = in_out ? 1 : 0;
   if (dxhat != nullptr) {
     if (packed) {
-      rc = gemm_any(dt, dt, gimpl, N, C, 2 * H, dg13, 2 * H, 0, p->w1, p->ldw_13, tBx, dxhat, C, nullptr, 0, st, nullptr, 0, 0, 0, dx_res, C);
+      rc = gemm_any(dt, dt, gimpl, N, C, 2 * H, dg13, G, 0, p->w1, p->ldw_13, tBx, dxhat, C, nullptr, 0, st, nullptr, 0, 0, 0, dx_res, C);
       if (rc) return rc;
     } else {
-      rc = gemm_any(dt, dt, gimpl, N, C, H, dg13, 2 * H, 0, p->w1, p->ldw_13, tBx, dxhat, C, nullptr, 0, st, nullptr, 0, 0, 0, dx_res, C);
+      rc = gemm_any(dt, dt, gimpl, N, C, H, dg13, G, 0, p->w1, p->ldw_13, tBx, dxhat, C, nullptr, 0, st, nullptr, 0, 0, 0, dx_res, C);
       if (rc) return rc;
-      rc = gemm_any(dt, dt, gimpl, N, C, H, dg13 + H * e, 2 * H, 0, p->w3, p->ldw_13, tBx, dxhat, C, nullptr, 1, st, nullptr, 0, 0, 0);
-      if (rc) return rc;
+      if (gated) {
+        rc = gemm_any(dt, dt, gimpl, N, C, H, dg13 + H * e, G, 0, p->w3, p->ldw_13, tBx, dxhat, C, nullptr, 1, st, nullptr, 0, 0, 0);
+        if (rc) return rc;
+      }
     }
   }
   // 5. norm VJP (+ dy through the residual)
   if (d->norm_kind != SPB_NORM_NONE) {
     rc = norm_bwd_add(dt, d->norm_kind, d->norm_upcast, x, p->norm_w, (const float*)(w8 + L.stats), w8 + L.dxhat, g->dx, g->dnorm_w,
-                      g->dnorm_b, w8 + L.partial, N, d->C, d->residual ? dy : nullptr, st);
+                      g->dnorm_b, partial, N, d->C, d->residual ? dy : nullptr, st);
     if (rc) return rc;
   }
   if (comm != nullptr) {
@@ -745,6 +767,15 @@ int spb_ffn_bwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, c
     if (g->dnorm_b && d->norm_kind == SPB_NORM_LAYER) { ptrs[n] = g->dnorm_b; counts[n++] = (size_t)d->C; }
     rc = comm_allreduce_join(comm, ptrs, counts, n, st);
     if (rc) return rc;
+    if (g->db1 || g->db2) {  // bias gradients: small, on the main stream
+      float* bp[2];
+      size_t bc[2];
+      int nb = 0;
+      if (g->db1) { bp[nb] = g->db1; bc[nb++] = (size_t)H; }
+      if (g->db2) { bp[nb] = g->db2; bc[nb++] = (size_t)C; }
+      rc = spb_comm_allreduce_f32(comm, bp, bc, nb, stream);
+      if (rc) return rc;
+    }
   }
   return 0;
 }

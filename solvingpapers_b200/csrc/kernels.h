@@ -34,9 +34,9 @@ int flash_bwd_tc(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale
 
 // comm.cu
 // all-reduce on the communicator's side stream, ordered after everything already enqueued on `main`
-int swiglu_fwd(int dtype, const void* g13, int64_t ld13, void* a, int64_t lda, int64_t N, int H, cudaStream_t st);
-int swiglu_bwd(int dtype, const void* g13, int64_t ld13, const void* da, int64_t lda, void* dg13, int64_t ldd, int64_t N, int H,
-               cudaStream_t st);
+int ffn_act_fwd(int dtype, int act, const void* g, int64_t ldg, void* a, int64_t lda, int64_t N, int H, cudaStream_t st);
+int ffn_act_bwd(int dtype, int act, const void* g, int64_t ldg, const void* da, int64_t lda, void* dg, int64_t ldd, int64_t N, int H,
+                cudaStream_t st);
 int norm_bwd_add(int dtype, int norm_kind, int upcast, const void* x, const void* w, const float* stats, const void* dy, void* dx,
                  float* dw, float* db, void* partial, int64_t N, int32_t C, const void* add, cudaStream_t st);
 int comm_allreduce_side(void* comm, float* const* ptrs, const size_t* counts, int n, cudaStream_t main);

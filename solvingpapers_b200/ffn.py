@@ -41,13 +41,19 @@ class FfnConfig:
         return L.FfnDesc(self.N, self.C, self.H, _dt(self.dtype), self.norm_kind, self.norm_eps, int(self.norm_upcast), self.act,
                          self.weight_layout, int(self.residual), self.gemm_impl)
 
+    @property
+    def gated(self):
+        return self.act != L.ACT_GELU_TANH
+
     def flops_fwd_bwd(self):
-        return 3.0 * 3.0 * 2.0 * self.N * self.C * self.H  # three contractions, forward + two backward GEMMs each
+        n_mm = 3.0 if self.gated else 2.0  # contractions; each costs forward + two backward GEMMs
+        return n_mm * 3.0 * 2.0 * self.N * self.C * self.H
 
 
 class FeedForward:
     """One feed-forward sub-block bound to fixed shapes; weights are passed per call.
-    params: {"w13": [C, 2H] packed (w1 | w3)}  or  {"w1": [C,H], "w3": [C,H]};  "w2": [H, C];  "norm_w" (and "norm_b")."""
+    params: {"w13": [C, 2H] packed (w1 | w3)}  or  {"w1": [C,H], "w3": [C,H]};  "w2": [H, C];  "norm_w" (and "norm_b");
+    the plain MLP (ACT_GELU_TANH) takes "w1", "w2" and optional biases "b1" [H], "b2" [C]; W_OUT_IN transposes every weight."""
 
     def __init__(self, cfg: FfnConfig, device="cuda", comm=None):
         if not torch.cuda.is_available():
@@ -75,15 +81,18 @@ class FeedForward:
             return t
 
         P = L.FfnParams()
-        if "w13" in p:
+        if not c.gated:
+            w1, w3 = chk(p["w1"], "w1"), None
+        elif "w13" in p:
             w = chk(p["w13"], "w13")
             w1, w3 = (w[:, :c.H], w[:, c.H:]) if c.weight_layout == L.W_IN_OUT else (w[:c.H], w[c.H:])
         else:
             w1, w3 = chk(p["w1"], "w1"), chk(p["w3"], "w3")
-        if w1.stride(0) != w3.stride(0):
+        if w3 is not None and w1.stride(0) != w3.stride(0):
             raise L.SpbError("w1 and w3 must share a row stride")
         w2 = chk(p["w2"], "w2")
         P.w1, P.w3, P.ldw_13 = _ptr(w1), _ptr(w3), w1.stride(0)
+        P.b1, P.b2 = _ptr(chk(p.get("b1"), "b1")), _ptr(chk(p.get("b2"), "b2"))
         P.w2, P.ldw_2 = _ptr(w2), w2.stride(0)
         if c.norm_kind != L.NORM_NONE:
             P.norm_w = _ptr(chk(p["norm_w"], "norm_w"))
@@ -109,7 +118,11 @@ class FeedForward:
             g["dw13"] = torch.empty(tuple(params["w13"].shape), **f32)
         else:
             g["dw1"] = torch.empty(tuple(params["w1"].shape), **f32)
-            g["dw3"] = torch.empty(tuple(params["w3"].shape), **f32)
+            if c.gated:
+                g["dw3"] = torch.empty(tuple(params["w3"].shape), **f32)
+        for b in ("b1", "b2"):
+            if params.get(b) is not None:
+                g["d" + b] = torch.empty(tuple(params[b].shape), **f32)
         if c.norm_kind != L.NORM_NONE:
             g["dnorm_w"] = torch.empty(c.C, **f32)
             if c.norm_kind == L.NORM_LAYER:
@@ -131,9 +144,10 @@ class FeedForward:
             w = g["dw13"]
             d1, d3 = (w[:, :c.H], w[:, c.H:]) if c.weight_layout == L.W_IN_OUT else (w[:c.H], w[c.H:])
         else:
-            d1, d3 = g["dw1"], g["dw3"]
+            d1, d3 = g["dw1"], g.get("dw3")
         G.dw1, G.dw3, G.ldw_13 = _ptr(d1), _ptr(d3), d1.stride(0)
         G.dw2, G.ldw_2 = _ptr(g["dw2"]), g["dw2"].stride(0)
+        G.db1, G.db2 = _ptr(g.get("db1")), _ptr(g.get("db2"))
         st = torch.cuda.current_stream(self.device).cuda_stream
         L.check(self.lib.spb_ffn_bwd(C.byref(self.d), C.byref(P), _ptr(x), _ptr(dy.contiguous()), _ptr(self.ws), C.byref(G),
                                      C.c_void_p(self.comm) if self.comm else None, C.c_void_p(st)), "spb_ffn_bwd")
@@ -170,6 +184,7 @@ class FfnFn(torch.autograd.Function):
         g = ff.backward(dy.contiguous())
         out = []
         for n in ctx.names:
-            gn = {"w13": "dw13", "w1": "dw1", "w3": "dw3", "w2": "dw2", "norm_w": "dnorm_w", "norm_b": "dnorm_b"}.get(n)
+            gn = {"w13": "dw13", "w1": "dw1", "w3": "dw3", "w2": "dw2", "norm_w": "dnorm_w", "norm_b": "dnorm_b", "b1": "db1",
+                  "b2": "db2"}.get(n)
             out.append(g[gn].to(ctx.params[n].dtype) if gn in g else None)
         return (None, None, None, g["dx"], *out)

@@ -63,3 +63,24 @@ class MQA:
         return y
 
     __call__ = forward
+
+
+class GeGLU:
+    """gemma/gemma.ipynb:269-286, same call surface: ``GeGLU(...)(x)`` = linear_layer3(gelu(linear_layer1(x)) * linear_layer2(x)).
+    `params` holds the torch ``nn.Linear`` weights as they are stored, [out, in]: linear_layer1, linear_layer2 [4D, D],
+    linear_layer3 [D, 4D] (one spb_ffn_fwd / spb_ffn_bwd pair, erf-GELU gate kernel)."""
+
+    def __init__(self, params, comm=None):
+        self.params, self.comm = params, comm
+
+    def __call__(self, x):
+        from .ffn import FfnConfig, FfnFn
+        p = self.params
+        D = x.shape[-1]
+        cfg = FfnConfig(N=x.numel() // D, C=D, H=p["linear_layer1"].shape[0], dtype=x.dtype, norm_kind=L.NORM_NONE, act=L.ACT_GEGLU,
+                        weight_layout=L.W_OUT_IN)
+        # gate = linear_layer1 (w3), value = linear_layer2 (w1), down projection = linear_layer3 (w2)
+        y = FfnFn.apply(cfg, ("w3", "w1", "w2"), self.comm, x.reshape(-1, D), p["linear_layer1"], p["linear_layer2"], p["linear_layer3"])
+        return y.reshape(x.shape)
+
+    forward = __call__

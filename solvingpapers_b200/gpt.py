@@ -41,3 +41,25 @@ class CausalSelfAttention:
         y, _, _ = BlockFn.apply(self._cfg(x, True), ("wqkv", "wo", "bo", "norm_w", "norm_b"), None, x, a["qkv"]["kernel"],
                                 a["proj"]["kernel"], a["proj"]["bias"], params["ln1"]["scale"], params["ln1"]["bias"])
         return y
+
+
+class MLP:
+    """gpt/gpt-jax.ipynb:376-389 with deterministic=True: ``fc2(nn.gelu(fc1(x)))``.  `params` is the flax parameter tree of the
+    module: {'fc1': {'kernel' [C,4C], 'bias' [4C]}, 'fc2': {'kernel' [4C,C], 'bias' [C]}} (one spb_ffn_fwd /
+    spb_ffn_bwd pair: bias in the GEMM epilogues, tanh-GELU kernel, bias gradients as column sums)."""
+
+    def __init__(self, emb_dim=None, dropout_rate=0.0, comm=None):
+        self.emb_dim, self.dropout_rate, self.comm = emb_dim, dropout_rate, comm
+
+    def apply(self, variables, x, deterministic=True):
+        if not deterministic and self.dropout_rate != 0.0:
+            raise NotImplementedError("dropout has no kernel (its RNG stream cannot match flax's); call with deterministic=True")
+        from .ffn import FfnConfig, FfnFn
+        p = variables.get("params", variables)
+        C_ = x.shape[-1]
+        cfg = FfnConfig(N=x.numel() // C_, C=C_, H=p["fc1"]["kernel"].shape[1], dtype=x.dtype, norm_kind=L.NORM_NONE, act=L.ACT_GELU_TANH)
+        y = FfnFn.apply(cfg, ("w1", "b1", "w2", "b2"), self.comm, x.reshape(-1, C_), p["fc1"]["kernel"], p["fc1"]["bias"], p["fc2"]["kernel"],
+                        p["fc2"]["bias"])
+        return y.reshape(x.shape)
+
+    __call__ = apply

@@ -102,3 +102,17 @@ def ffn_block(block_params, h, eps=1e-6, comm=None, residual=True):
     cfg = FfnConfig(N=h.numel() // C_, C=C_, H=f["w1"].shape[1], dtype=h.dtype, norm_kind=L.NORM_RMS, norm_eps=eps, residual=residual)
     y = FfnFn.apply(cfg, ("w1", "w3", "w2", "norm_w"), comm, h.reshape(-1, C_), f["w1"], f["w3"], f["w2"], block_params["ffn_norm"])
     return y.reshape(h.shape)
+
+
+def transformer_block(params, x, mask, freqs_cis, n_heads, n_kv_heads, cache=None, position=0, training=False, dropout_rate=0.0,
+                      key=None, comm=None):
+    """llama3/LLaMA-jax.ipynb:880-891, same signature.  Two C-ABI calls forward (attention block with ``h = x + attn`` in its
+    output projection's epilogue, feed-forward sub-block with ``out = h + ffn`` in the w2 GEMM's epilogue) and two backward.
+    The notebook always calls it with ``training=False`` (:927; ``dropout_rate=0.0`` :358): the dropout branch has no kernel."""
+    if training and dropout_rate != 0.0:
+        raise NotImplementedError("dropout inside transformer_block is dead code in the notebook (training=False, llama3:927) and has no kernel")
+    if cache is not None or position != 0:
+        raise NotImplementedError("KV-cache decode (cache / position) is not on the training hot path and has no kernel")
+    h, new_cache = attention_block(params, x, mask, freqs_cis, n_heads, n_kv_heads, comm=comm, residual=True)
+    out = ffn_block(params, h, comm=comm, residual=True)
+    return out, new_cache

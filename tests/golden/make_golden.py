@@ -251,6 +251,31 @@ def make_gemma(tag, B, T, D, seed):
     print("gemma", tag, "y", tuple(y.shape), "MQA params", n_params)
 
 
+def make_gemma_geglu(tag, B, T, D, seed):
+    """the notebook's own GeGLU module (gemma/gemma.ipynb cell 9, :269-286) run forward + backward on CPU."""
+    ns = {}
+    exec(cell_src("gemma/gemma.ipynb", 0).replace("from tokenizers import Tokenizer\n", ""), ns)
+    exec(cell_src("gemma/gemma.ipynb", 1), ns)
+    args = ns["args"]
+    args.device = "cpu"
+    args.embeddings_dims = D
+    args.block_size = T
+    exec(cell_src("gemma/gemma.ipynb", 9), ns)
+    torch.manual_seed(seed)
+    m = ns["GeGLU"](block_size=T, embeddings_dims=D)
+    rng = np.random.default_rng(seed)
+    x = torch.from_numpy(rng.standard_normal((B, T, D)).astype(np.float32)).requires_grad_(True)
+    dy = torch.from_numpy(rng.standard_normal((B, T, D)).astype(np.float32))
+    y = m(x)
+    y.backward(dy)
+    out = dict(x=x.detach().numpy(), dy=dy.numpy(), y=y.detach().numpy(), dx=x.grad.numpy(), meta=np.array([B, T, D], dtype=np.int64))
+    for i, lin in enumerate((m.linear_layer1, m.linear_layer2, m.linear_layer3), 1):
+        out[f"l{i}"] = lin.weight.detach().numpy()
+        out[f"dl{i}"] = lin.weight.grad.numpy()
+    np.savez_compressed(os.path.join(OUT, f"gemma_geglu_{tag}.npz"), **out)
+    print("gemma geglu", tag, "y", tuple(y.shape))
+
+
 def gemma_param_count_pin():
     """MQA at notebook defaults has 3,538,944 parameters."""
     ns = {}
@@ -303,5 +328,6 @@ if __name__ == "__main__":
     make_llama("mqa_causal", B=2, T=12, C=64, H=4, Hkv=1, causal=True, seed=2)
     make_llama_ffn("small", B=2, T=12, C=32, seed=5)
     make_gemma("small", B=2, T=16, D=64, seed=3)
+    make_gemma_geglu("small", B=2, T=12, D=32, seed=6)
     print("gemma MQA default param count", gemma_param_count_pin())
     make_vit("nb", B=3, T=17, E=64, H=4, seed=4)  # the notebook's literal shape

@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 import torch
 
-from oracle import llama_oracle, max_rel_err
+from oracle import gemma_oracle, gpt_oracle, llama_oracle, max_rel_err
 from oracle.metrics import TOL_BF16, TOL_F32
 
 pytestmark = pytest.mark.gpu
@@ -118,6 +118,94 @@ def test_ffn_autograd_mirror_matches_oracle():
     got = {"y": out.detach(), "dx": hd.grad, "dw1": bp["ffn"]["w1"].grad, "dw2": bp["ffn"]["w2"].grad, "dw3": bp["ffn"]["w3"].grad,
            "dnorm": bp["ffn_norm"].grad}
     _check(got, ref, torch.float32)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_whole_transformer_block_mirror_matches_oracle(dtype):
+    """llama.transformer_block (llama3:880-891): attention block + feed-forward sub-block, both residual adds inside the kernels,
+    forward and backward through torch autograd against the oracle's transformer_block."""
+    from solvingpapers_b200 import llama as spl
+    rng = np.random.default_rng(6)
+    B, Tn, C, H, Hkv = 2, 128, 256, 4, 2
+    params = {**llama_oracle.init_block_params(rng, C, H, Hkv), **llama_oracle.init_ffn_params(rng, C)}
+    x = T_(rng.standard_normal((B, Tn, C)).astype(np.float32))
+    dy = T_(rng.standard_normal((B, Tn, C)).astype(np.float32))
+    rd = lambda t: t.to(dtype).float()
+    flat = lambda p, f: {k: (flat(v, f) if isinstance(v, dict) else f(v)) for k, v in p.items()}
+    pr = flat(params, lambda t: rd(t).clone().requires_grad_(True))
+    xr = rd(x).clone().requires_grad_(True)
+    fc = llama_oracle.precompute_freqs_cis(C // H, Tn)
+    out_ref, _ = llama_oracle.transformer_block(pr, xr, llama_oracle.make_mask(Tn), fc, H, Hkv)
+    out_ref.backward(rd(dy))
+    pd = flat(params, lambda t: t.detach().to(dtype).to(DEV).requires_grad_(True))
+    xd = x.detach().to(dtype).to(DEV).requires_grad_(True)
+    fcd = spl.precompute_freqs_cis(C // H, Tn)
+    out, (k, v) = spl.transformer_block(pd, xd, torch.ones(1), fcd, H, Hkv)
+    out.backward(dy.to(dtype).to(DEV))
+    torch.cuda.synchronize()
+    got = {"out": out.detach(), "dx": xd.grad}
+    ref = {"out": out_ref.detach(), "dx": xr.grad}
+    for grp in ("attention", "ffn"):
+        for name in params[grp]:
+            got[f"d{grp}.{name}"] = pd[grp][name].grad
+            ref[f"d{grp}.{name}"] = pr[grp][name].grad
+    for name in ("attention_norm", "ffn_norm"):
+        got["d" + name] = pd[name].grad
+        ref["d" + name] = pr[name].grad
+    _check(got, ref, dtype)
+
+
+def test_gemma_geglu_fp32_against_golden_from_notebook_module(golden_dir):
+    """GeGLU (gemma:269-286): kernels against the outputs AND gradients of the notebook's own torch module."""
+    from solvingpapers_b200 import gemma as spg
+    g = dict(np.load(os.path.join(golden_dir, "gemma_geglu_small.npz")))
+    p = {f"linear_layer{i}": T_(g[f"l{i}"]).to(DEV).requires_grad_(True) for i in (1, 2, 3)}
+    x = T_(g["x"]).to(DEV).requires_grad_(True)
+    y = spg.GeGLU(p)(x)
+    y.backward(T_(g["dy"]).to(DEV))
+    got = {"y": y.detach(), "dx": x.grad, "dl1": p["linear_layer1"].grad, "dl2": p["linear_layer2"].grad, "dl3": p["linear_layer3"].grad}
+    _check(got, {k: T_(g[k]) for k in got}, torch.float32)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_gemma_geglu_literal_width_768(dtype):
+    from solvingpapers_b200 import gemma as spg
+    rng = np.random.default_rng(7)
+    D, B, Tn = 768, 2, 96
+    params = gemma_oracle.init_geglu_params(rng, D)
+    x = T_(rng.standard_normal((B, Tn, D)).astype(np.float32))
+    dy = T_(rng.standard_normal((B, Tn, D)).astype(np.float32))
+    rd = lambda t: t.to(dtype).float()
+    ref = gemma_oracle.geglu_fwd_bwd({k: rd(v) for k, v in params.items()}, rd(x), rd(dy))
+    p = {k: v.to(dtype).to(DEV).requires_grad_(True) for k, v in params.items()}
+    xd = x.to(dtype).to(DEV).requires_grad_(True)
+    y = spg.GeGLU(p)(xd)
+    y.backward(dy.to(dtype).to(DEV))
+    got = {"y": y.detach(), "dx": xd.grad, "dl1": p["linear_layer1"].grad, "dl2": p["linear_layer2"].grad, "dl3": p["linear_layer3"].grad}
+    _check(got, ref, dtype)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_gpt_mlp_with_biases(dtype):
+    """GELU MLP (gpt:376-389): flax parameter tree, non-zero biases, tanh GELU; C2 width 256."""
+    from solvingpapers_b200 import gpt as spgpt
+    rng = np.random.default_rng(8)
+    C, B, Tn = 256, 4, 100
+    params = gpt_oracle.init_mlp_params(rng, C)
+    x = T_(rng.standard_normal((B, Tn, C)).astype(np.float32))
+    dy = T_(rng.standard_normal((B, Tn, C)).astype(np.float32))
+    rd = lambda t: t.to(dtype).float()
+    ref = gpt_oracle.mlp_fwd_bwd({k: rd(v) for k, v in params.items()}, rd(x), rd(dy))
+    d = lambda t: t.to(dtype).to(DEV).requires_grad_(True)
+    tree = {"params": {"fc1": {"kernel": d(params["fc1_kernel"]), "bias": d(params["fc1_bias"])},
+                       "fc2": {"kernel": d(params["fc2_kernel"]), "bias": d(params["fc2_bias"])}}}
+    xd = d(x)
+    y = spgpt.MLP(emb_dim=C, dropout_rate=0.1).apply(tree, xd, deterministic=True)
+    y.backward(dy.to(dtype).to(DEV))
+    t = tree["params"]
+    got = {"y": y.detach(), "dx": xd.grad, "dfc1_kernel": t["fc1"]["kernel"].grad, "dfc1_bias": t["fc1"]["bias"].grad,
+           "dfc2_kernel": t["fc2"]["kernel"].grad, "dfc2_bias": t["fc2"]["bias"].grad}
+    _check(got, ref, dtype)
 
 
 def test_ffn_rejects_unknown_activation_and_bad_shapes():

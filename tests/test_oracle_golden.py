@@ -100,6 +100,36 @@ def test_gemma_matches_notebook_modules(golden_dir):
         assert max_rel_err(r["dwq"][i], T(g[f"dwq{i}"])) < 2e-5
 
 
+def test_gemma_geglu_matches_notebook_module(golden_dir):
+    """oracle geglu() against the notebook's own GeGLU module (gemma:269-286) - forward and every gradient."""
+    g = _load(golden_dir, "gemma_geglu_small.npz")
+    p = {"linear_layer1": T(g["l1"]), "linear_layer2": T(g["l2"]), "linear_layer3": T(g["l3"])}
+    r = gemma_oracle.geglu_fwd_bwd(p, T(g["x"]), T(g["dy"]), dtype=torch.float32)
+    for k, ref in (("y", "y"), ("dx", "dx"), ("dl1", "dl1"), ("dl2", "dl2"), ("dl3", "dl3")):
+        assert max_rel_err(r[k], T(g[ref])) < 5e-6, k
+
+
+def test_gpt_mlp_restatement_finite_differences():
+    """The flax MLP (gpt:376-389) cannot run here (no jax/flax): the restatement's backward is checked by fp64 central differences
+    and its tanh-GELU against the closed form flax documents for approximate=True."""
+    rng = np.random.default_rng(0)
+    p = gpt_oracle.init_mlp_params(rng, 16, dtype=torch.float64)
+    x = torch.from_numpy(rng.standard_normal((3, 5, 16)))
+    dy = torch.from_numpy(rng.standard_normal((3, 5, 16)))
+    r = gpt_oracle.mlp_fwd_bwd(p, x, dy, dtype=torch.float64)
+    z = x @ p["fc1_kernel"] + p["fc1_bias"]
+    gelu = 0.5 * z * (1 + torch.tanh(np.sqrt(2 / np.pi) * (z + 0.044715 * z ** 3)))
+    assert max_rel_err(r["y"], gelu @ p["fc2_kernel"] + p["fc2_bias"]) < 1e-12
+    loss = lambda pp, xx: float(torch.sum(gpt_oracle.mlp(pp, xx) * dy))
+    h = 1e-6
+    for name in ("fc1_kernel", "fc1_bias", "fc2_kernel", "fc2_bias"):
+        u = torch.from_numpy(rng.standard_normal(tuple(p[name].shape)))
+        u /= u.norm()
+        fd = (loss({**p, name: p[name] + h * u}, x) - loss({**p, name: p[name] - h * u}, x)) / (2 * h)
+        an = float(torch.sum(r["d" + name] * u))
+        assert abs(an - fd) <= 1e-6 * max(1.0, abs(fd)), (name, an, fd)
+
+
 def test_gemma_rotary_is_not_a_rotation(golden_dir):
     g = _load(golden_dir, "gemma_small.npz")
     Tn, D = g["x"].shape[1], g["x"].shape[2]
