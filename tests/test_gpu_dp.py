@@ -70,6 +70,21 @@ def _two_rank_worker(rank, world, port, out):
         ref = full.backward(dy)
         errs = {k: max_rel_err(g[k], ref[k]) for k in ("dwqkv", "dwo", "dnorm_w")}
         errs["dx"] = max_rel_err(g["dx"], ref["dx"][:per])
+    # the feed-forward sub-block's gradient all-reduce: sharded tokens, summed dw13 / dw2 / dnorm
+    Hh = 4 * C
+    pf = {"w13": dev(torch.randn(C, 2 * Hh, generator=gen) / 16), "w2": dev(torch.randn(Hh, C, generator=gen) / 32),
+          "norm_w": dev(torch.randn(C, generator=gen))}
+    xs, dys = spd.shard_batch(x, world, rank).reshape(-1, C).contiguous(), spd.shard_batch(dy, world, rank).reshape(-1, C).contiguous()
+    ff = sp.FeedForward(sp.FfnConfig(N=per * T, C=C, H=Hh, residual=True), comm=comm.handle)
+    ff.forward(xs, pf)
+    gf = ff.backward(dys)
+    torch.cuda.synchronize()
+    if rank == 0:
+        full = sp.FeedForward(sp.FfnConfig(N=B * T, C=C, H=Hh, residual=True))
+        full.forward(x.reshape(-1, C).contiguous(), pf)
+        ref = full.backward(dy.reshape(-1, C).contiguous())
+        errs.update({"ffn_" + k: max_rel_err(gf[k], ref[k]) for k in ("dw13", "dw2", "dnorm_w")})
+        errs["ffn_dx"] = max_rel_err(gf["dx"], ref["dx"][:per * T])
         torch.save(errs, out)
     tdist.barrier()
     comm.close()
