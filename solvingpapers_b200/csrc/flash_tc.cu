@@ -5,9 +5,10 @@
 //   warp 0    TMA producer: the Q tiles once, then K / V tiles of 128 rows (double buffered)
 //   warp 1    MMA issuer (one thread): per KV tile  S_t = Q_t K^T (M128 N128 K=hd, own TMEM buffer per tile) and
 //             O_t += P_t V (M128 N=hd K128; P_t is read from tensor memory, where it overwrote S_t)
-//   warps 2-9 softmax.  ALL eight warps work on ONE tile at a time and alternate between the two tiles: warp w owns TMEM
-//             lane quadrant w%4 (32 query rows) and column half (w-2)/4 (64 of the 128 KV columns), i.e. two threads
-//             share a row.  So a tile's softmax takes half as long, and while the tensor pipe runs PV_t / S_t(next) the
+//   warps 2-17 softmax (4*NSPLIT warps, NSPLIT = 4).  ALL of them work on ONE tile at a time and alternate between the two
+//             tiles: warp w owns TMEM lane quadrant w%4 (32 query rows) and column part (w-2)/4 (128/NSPLIT of the 128 KV
+//             columns), i.e. NSPLIT threads share a row (2 -> 4 threads per row: +2 % standalone, more warps per scheduler
+//             to hide the MUFU / tcgen05.ld latencies).  So a tile's softmax takes half as long, and while the tensor pipe runs PV_t / S_t(next) the
 //             whole softmax crew is busy with the other tile - the r01 kernel gave each tile its own four warps, both
 //             tiles' softmaxes ran concurrently at half speed each and every tile waited for its own MMAs afterwards
 //             (ablation: MMA time and softmax time were additive).
@@ -44,6 +45,9 @@ __device__ unsigned long long g_fa_trace[FA_TRACE_ROLES * FA_TRACE_EVENTS];
 
 // exp2 on the FMA pipe for a pair of values (x <= ~2^7): Cody-Waite split with the 1.5*2^23 rounding trick, degree-3
 // minimax polynomial of 2^f on [-0.5, 0.5] (max relative error 7.5e-5), exponent added with integer arithmetic.
+#ifndef SPB_FA_NSPLIT
+#define SPB_FA_NSPLIT 4  // softmax threads per query row: 2 (8 softmax warps) or 4 (16 softmax warps)
+#endif
 #ifndef SPB_FA_POLY_EVERY
 #define SPB_FA_POLY_EVERY 2  // one pair of every 2nd group of four elements = 25 % of the exps; 0 disables
 #endif
@@ -82,14 +86,16 @@ struct FaFwdCfg {
   static constexpr int OFF_Q = 0;
   static constexpr int OFF_K = OFF_Q + NT * TILE_BYTES;
   static constexpr int OFF_V = OFF_K + KST * TILE_BYTES;
-  static constexpr int OFF_X = OFF_V + VST * TILE_BYTES;   // row-max / row-sum exchange: [2 buffers][2 halves][128 rows] fp32
-  static constexpr int OFF_BAR = OFF_X + 2 * 2 * 128 * 4;
+  static constexpr int OFF_X = OFF_V + VST * TILE_BYTES;   // row-max / row-sum exchange: [2 buffers][NSPLIT parts][128 rows] fp32
+  static constexpr int NSPLIT = SPB_FA_NSPLIT;            // softmax threads per query row (each owns 128/NSPLIT KV columns)
+  static constexpr int CW = 128 / NSPLIT;                 // S / P columns per softmax thread
+  static constexpr int OFF_BAR = OFF_X + 2 * NSPLIT * 128 * 4;
   static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
   static constexpr int TMEM_COLS = 512;
   static constexpr int TM_O0 = (NT == 2) ? 256 : 128;     // O_t at TM_O0 + t*128 (NT=2) / one 256-column O at 128 (NT=1)
-  static constexpr int SM_WARPS = 8;                      // softmax warps
+  static constexpr int SM_WARPS = 4 * NSPLIT;             // softmax warps
   static constexpr int THREADS = 64 + SM_WARPS * 32;
-  static constexpr int OH = HD / 2;                       // O columns per softmax thread (two threads share a row)
+  static constexpr int OH = HD / NSPLIT;                  // O columns per softmax thread
 };
 
 struct FaFwdArgs {
@@ -268,7 +274,8 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
   } else {
     // ------------------------------------------------------------------ softmax + epilogue: warps 2-9, one tile at a time
     const int qd = warp & 3;            // TMEM lane quadrant this warp may touch (hardware rule: warp % 4)
-    const int half = (warp - 2) >> 2;   // which 64 KV columns of S/P and which hd/2 columns of O this thread owns
+    const int half = (warp - 2) >> 2;   // column part: which CW KV columns of S/P and which hd/NSPLIT columns of O this thread owns
+    constexpr int NSPLIT = Cfg::NSPLIT, CW = Cfg::CW, SM_THREADS = Cfg::SM_WARPS * 32;
     const int r = qd * 32 + lane;       // row inside the tile = TMEM lane
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
     float m_t[2] = {-INFINITY, -INFINITY}, l_t[2] = {0.f, 0.f};
@@ -280,12 +287,16 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
 #else
 #define FA_TRACE_S(id)
 #endif
-    auto exchange = [&](float mine) -> float {  // combine a per-row value of the two column halves (all 256 threads call it)
-      float* buf = sX + xbuf * 256;
+    // combine a per-row value over the row's NSPLIT threads (every softmax thread calls it): max or sum of all parts
+    auto exchange = [&](float mine, bool is_max) -> float {
+      float* buf = sX + xbuf * (NSPLIT * 128);
       buf[half * 128 + r] = mine;
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(SM_THREADS) : "memory");
       xbuf ^= 1;
-      return buf[(half ^ 1) * 128 + r];
+      float acc = buf[r];
+#pragma unroll
+      for (int pp = 1; pp < NSPLIT; ++pp) acc = is_max ? fmaxf(acc, buf[pp * 128 + r]) : acc + buf[pp * 128 + r];
+      return acc;
     };
     // visible columns of this thread's 64 in unit (j,t): n_valid leading ones when the tile needs masking at all
     auto geometry = [&](int j, int t, bool& need_mask, int& n_valid) {
@@ -293,20 +304,20 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
       need_mask = (p.causal && kv0 + 127 > q0 + t * 128) || (kv0 + 128 > p.T);
       n_valid = p.T - kv0;
       if (p.causal) n_valid = min(n_valid, q0 + t * 128 + r - kv0 + 1);
-      n_valid -= half * 64;
+      n_valid -= half * CW;
     };
-    auto row_max = [&](const uint32_t(&s)[64], bool need_mask, int n_valid) -> float {
-      // row max of the raw scores over the visible ones of 64 columns (scale > 0, so scaling commutes with max)
+    auto row_max = [&](const uint32_t(&s)[CW], bool need_mask, int n_valid) -> float {
+      // row max of the raw scores over the visible ones of CW columns (scale > 0, so scaling commutes with max)
       float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
       if (!need_mask) {
 #pragma unroll
-        for (int i = 0; i < 64; i += 8) {
+        for (int i = 0; i < CW; i += 8) {
 #pragma unroll
           for (int c = 0; c < 4; ++c) mx[c] = fmaxf(mx[c], fmaxf(__uint_as_float(s[i + 2 * c]), __uint_as_float(s[i + 2 * c + 1])));
         }
       } else {
 #pragma unroll
-        for (int i = 0; i < 64; ++i) mx[i & 3] = fmaxf(mx[i & 3], i < n_valid ? __uint_as_float(s[i]) : -INFINITY);
+        for (int i = 0; i < CW; ++i) mx[i & 3] = fmaxf(mx[i & 3], i < n_valid ? __uint_as_float(s[i]) : -INFINITY);
       }
       return fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
     };
@@ -314,16 +325,16 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
 #pragma unroll
       for (int t = 0; t < NT; ++t) {
         if (j >= n_kv_t[t]) continue;  // CTA-uniform
-        const uint32_t tS = lane_base + (uint32_t)(t * 128 + half * 64);
-        const uint32_t tP = lane_base + (uint32_t)(t * 128 + half * 32);
+        const uint32_t tS = lane_base + (uint32_t)(t * 128 + half * CW);
+        const uint32_t tP = lane_base + (uint32_t)(t * 128 + half * (CW / 2));
         const uint32_t tO = lane_base + (uint32_t)(Cfg::TM_O0 + t * 128 + half * Cfg::OH);
         FA_TRACE_S(20 + t);  // start waiting for S_t
         mbar_wait(&s_full[t], j & 1);
         FA_TRACE_S(22 + t);  // S_t seen
         tc_fence_after();
-        uint32_t s[64];
+        uint32_t s[CW];
         SPB_TMEM_LD_32(tS, s);
-        SPB_TMEM_LD_32(tS + 32u, (s + 32));
+        if (CW > 32) SPB_TMEM_LD_32(tS + 32u, (s + (CW > 32 ? 32 : 0)));
         tmem_ld_wait();
         bool need_mask;
         int n_valid;
@@ -331,7 +342,7 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
         const float mine = row_max(s, need_mask, n_valid);
         FA_TRACE_S(25);  // local max done
         // the barrier inside also orders every S load of this tile before any P store below (P aliases S)
-        const float tmax = fmaxf(mine, exchange(mine)) * p.scale_log2;
+        const float tmax = exchange(mine, true) * p.scale_log2;
         FA_TRACE_S(26);  // exchanged
         float m = m_t[t];
         if (j == 0) {
@@ -369,7 +380,7 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
         const float2 nm2 = make_float2(-m, -m);
         float2 sum2 = make_float2(0.f, 0.f), sum2b = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int q = 0; q < 2; ++q) {  // 32 columns -> 16 packed words per tcgen05.st
+        for (int q = 0; q < CW / 32; ++q) {  // 32 columns -> 16 packed words per tcgen05.st
           uint32_t pk[16];
           int mode = 0;  // 0 = all 32 visible, 1 = masked per element, 2 = none visible (warp-uniform)
           const int lq = n_valid - 32 * q;
@@ -420,7 +431,7 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
     for (int t = 0; t < NT; ++t) {
       const int n_mine = n_kv_t[t];
       if (n_mine == 0) continue;  // CTA-uniform
-      const float l = l_t[t] + exchange(l_t[t]);
+      const float l = exchange(l_t[t], false);
       const uint32_t tO = lane_base + (uint32_t)(Cfg::TM_O0 + t * 128 + half * Cfg::OH);
       const int q_idx = q0 + t * 128 + r;
       mbar_wait(&pv_done[t], (n_mine - 1) & 1);
@@ -429,19 +440,19 @@ __global__ void __launch_bounds__(FaFwdCfg<HD>::THREADS, 1)
       const bool valid = q_idx < p.T;
       __nv_bfloat16* orow = p.o + ((int64_t)b * p.T + q_idx) * p.ldo + (int64_t)h * HD + half * Cfg::OH;
 #pragma unroll
-      for (int c = 0; c < Cfg::OH / 32; ++c) {
-        uint32_t o[32];
-        SPB_TMEM_LD_32(tO + (uint32_t)(c * 32), o);
+      for (int c = 0; c < Cfg::OH / 16; ++c) {
+        uint32_t o[16];
+        SPB_TMEM_LD_16(tO + (uint32_t)(c * 16), o);
         tmem_ld_wait();
         if (valid) {
 #pragma unroll
-          for (int i = 0; i < 32; i += 8) {
+          for (int i = 0; i < 16; i += 8) {
             uint4 v;
             v.x = pack_bf16(__uint_as_float(o[i]) * inv, __uint_as_float(o[i + 1]) * inv);
             v.y = pack_bf16(__uint_as_float(o[i + 2]) * inv, __uint_as_float(o[i + 3]) * inv);
             v.z = pack_bf16(__uint_as_float(o[i + 4]) * inv, __uint_as_float(o[i + 5]) * inv);
             v.w = pack_bf16(__uint_as_float(o[i + 6]) * inv, __uint_as_float(o[i + 7]) * inv);
-            *reinterpret_cast<uint4*>(orow + c * 32 + i) = v;
+            *reinterpret_cast<uint4*>(orow + c * 16 + i) = v;
           }
         }
       }
