@@ -373,8 +373,10 @@ def run_ours(args):
         dxd = [torch.empty_like(x) for _ in range(2)]
         main = torch.cuda.current_stream()
         s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
-        ev_in = [torch.cuda.Event() for _ in range(2)]      # inputs of slot landed
+        ev_x = [torch.cuda.Event() for _ in range(2)]       # x of slot landed (the forward needs only x)
+        ev_dy = [torch.cuda.Event() for _ in range(2)]      # dy of slot landed (needed by the backward)
         ev_free = [torch.cuda.Event() for _ in range(2)]    # kernels that read slot's inputs are done
+        ev_fwd = [torch.cuda.Event() for _ in range(2)]     # forward of slot complete: y can leave while the backward runs
         ev_done = [torch.cuda.Event() for _ in range(2)]    # step results of slot complete
         ev_out = [torch.cuda.Event() for _ in range(2)]     # slot's results copied out
 
@@ -388,21 +390,25 @@ def run_ours(args):
                     if i >= 2:
                         s_in.wait_event(ev_free[sl])
                     xd[sl].copy_(xh, non_blocking=True)
+                    ev_x[sl].record(s_in)
                     dyd[sl].copy_(dyh, non_blocking=True)
-                    ev_in[sl].record(s_in)
-                main.wait_event(ev_in[sl])
+                    ev_dy[sl].record(s_in)
+                main.wait_event(ev_x[sl])
+                y = blk.forward(xd[sl], params)
+                ev_fwd[sl].record(main)
+                main.wait_event(ev_dy[sl])
                 if i >= 2:
                     main.wait_event(ev_out[sl])          # dx slot has been read back
-                y = blk.forward(xd[sl], params)
                 grads["dx"] = dxd[sl]
                 blk.backward(dyd[sl], grads=grads)
                 ev_free[sl].record(main)
                 ev_done[sl].record(main)
                 keep.append(y)
                 with torch.cuda.stream(s_out):
-                    s_out.wait_event(ev_done[sl])
+                    s_out.wait_event(ev_fwd[sl])
                     y.record_stream(s_out)  # y is allocated on the main stream and read by the copy stream
                     yh.copy_(y, non_blocking=True)
+                    s_out.wait_event(ev_done[sl])
                     dxh.copy_(dxd[sl], non_blocking=True)
                     ev_out[sl].record(s_out)
                     if i == nsteps - 1 and last_event is not None:
@@ -424,8 +430,8 @@ def run_ours(args):
         e2e = {"value": tokens_local * world * K / (float(t2.item()) * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": 2 * nbytes,
                "d2h_bytes_per_step": 2 * nbytes, "ms_per_step": float(t2.item()) / K, "host_affinity": host_affinity,
                "what": "every step: pinned host x,dy -> device, spb_block_fwd+bwd via AttentionBlock, y,dx -> pinned host; copies on their "
-                       "own streams with double-buffered staging (overlap with the previous/next step's kernels); weights and weight "
-                       "grads stay in HBM"}
+                       "own streams with double-buffered staging (overlap with the previous/next step's kernels; the forward starts when "
+                       "x has landed, y leaves while the backward runs); weights and weight grads stay in HBM"}
         grads["dx"] = dxd[0]
 
     # ---- roofline of the dominant kernel family (tcgen05 GEMM; FLOPs per SURVEY 8d: 3*F_gemm per step)
