@@ -270,6 +270,17 @@ int spb_ffn_fwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, v
 int spb_ffn_bwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, const void* dy, void* ws,
                 const spb_ffn_grads* g, void* comm, spb_stream_t stream);
 
+/* ---- the loss head's memory-bound half --------------------------------------- */
+/* llama3:959-967  loss = -mean(take_along_axis(log_softmax(logits), targets[:, None], axis=1)) over logits [N, V] (row pitch ld
+ * >= V elements; V = 50257 in the notebook).  lse[N] and row_nll[N] are fp32 outputs (lse is the backward's residual);
+ * `loss` (one fp32, may be NULL) receives the mean.  The logits GEMM of llama3:930 and its backward GEMMs are spb_gemm
+ * (the tcgen05 path needs leading dimensions that are multiples of 8: pad the vocabulary axis of the weight and of logits). */
+int spb_nll_fwd(int dtype, const void* logits, int64_t ld, const int64_t* targets, int64_t N, int32_t V, float* lse,
+                float* row_nll, float* loss, spb_stream_t stream);
+/* dlogits[n, j] = (softmax(logits)[n, j] - [j == targets[n]]) * dloss / N; may run in place (dlogits == logits, ldd == ld). */
+int spb_nll_bwd(int dtype, const void* logits, int64_t ld, const int64_t* targets, int64_t N, int32_t V, const float* lse,
+                float dloss, void* dlogits, int64_t ldd, spb_stream_t stream);
+
 /* ---- data parallelism: batch-sharded, weight gradients all-reduced (no reference precedent) ---- */
 int spb_comm_unique_id(void* out128);                        /* HOST buffer, 128 bytes (ncclUniqueId)      */
 int spb_comm_init_rank(const void* id128, int nranks, int rank, void** comm_out);

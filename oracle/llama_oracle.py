@@ -189,3 +189,19 @@ def transformer_block(params, x, mask, freqs_cis, n_heads, n_kv_heads):
     h = x + attn_output
     ffn_output = feed_forward(params["ffn"], rms_norm(h, params["ffn_norm"]))
     return h + ffn_output, new_cache
+
+
+# ---- the loss head -------------------------------------------------------------------
+def nll_loss(logits, targets):
+    """llama3/LLaMA-jax.ipynb:959-967: logits.reshape(-1, V); targets.reshape(-1);
+    ``loss = -mean(take_along_axis(log_softmax(logits), targets[:, None], axis=1))``."""
+    V = logits.shape[-1]
+    lg = logits.reshape(-1, V)
+    tg = targets.reshape(-1).long()
+    lp = torch.log_softmax(lg, dim=-1)
+    return -torch.mean(torch.gather(lp, 1, tg[:, None]))
+
+
+def loss_head(norm_f, output_w, h, targets):
+    """llama3/LLaMA-jax.ipynb:929-930 + :959-967: ``logits = dot(rms_norm(h, norm_f), output)`` then the NLL above."""
+    return nll_loss(torch.matmul(rms_norm(h, norm_f), output_w), targets)

@@ -89,6 +89,8 @@ SIGNATURES = {
     "spb_ffn_ws_layout": (C.c_int, [C.POINTER(FfnDesc), C.POINTER(FfnWs)]),
     "spb_ffn_fwd": (C.c_int, [C.POINTER(FfnDesc), C.POINTER(FfnParams), vp, vp, vp, vp]),
     "spb_ffn_bwd": (C.c_int, [C.POINTER(FfnDesc), C.POINTER(FfnParams), vp, vp, vp, C.POINTER(FfnGrads), vp, vp]),
+    "spb_nll_fwd": (C.c_int, [C.c_int, vp, i64, vp, i64, i32, vp, vp, vp, vp]),
+    "spb_nll_bwd": (C.c_int, [C.c_int, vp, i64, vp, i64, i32, vp, f32, vp, i64, vp]),
     "spb_comm_unique_id": (C.c_int, [vp]),
     "spb_comm_init_rank": (C.c_int, [vp, C.c_int, C.c_int, C.POINTER(vp)]),
     "spb_comm_allreduce_f32": (C.c_int, [vp, C.POINTER(vp), C.POINTER(sz), C.c_int, vp]),

@@ -116,3 +116,45 @@ def transformer_block(params, x, mask, freqs_cis, n_heads, n_kv_heads, cache=Non
     h, new_cache = attention_block(params, x, mask, freqs_cis, n_heads, n_kv_heads, comm=comm, residual=True)
     out = ffn_block(params, h, comm=comm, residual=True)
     return out, new_cache
+
+
+class _NllFn(torch.autograd.Function):
+    """-mean(log_softmax(logits)[targets]) over logits [N, V] (llama3/LLaMA-jax.ipynb:959-967) through spb_nll_fwd / spb_nll_bwd."""
+
+    @staticmethod
+    def forward(ctx, logits, targets):
+        import ctypes as C
+        lib = L.load()
+        N, V = logits.shape
+        if logits.stride(1) != 1:
+            logits = logits.contiguous()
+        tg = targets.to(torch.int64).contiguous()
+        f32 = dict(dtype=torch.float32, device=logits.device)
+        lse, row_nll, loss = torch.empty(N, **f32), torch.empty(N, **f32), torch.empty((), **f32)
+        dt = L.F32 if logits.dtype == torch.float32 else L.BF16
+        st = C.c_void_p(torch.cuda.current_stream(logits.device).cuda_stream)
+        p = lambda t: C.c_void_p(t.data_ptr())
+        L.check(lib.spb_nll_fwd(dt, p(logits), logits.stride(0), p(tg), N, V, p(lse), p(row_nll), p(loss), st), "spb_nll_fwd")
+        ctx.save_for_backward(logits, tg, lse)
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        import ctypes as C
+        logits, tg, lse = ctx.saved_tensors
+        lib = L.load()
+        N, V = logits.shape
+        dlogits = torch.empty_like(logits)
+        dt = L.F32 if logits.dtype == torch.float32 else L.BF16
+        st = C.c_void_p(torch.cuda.current_stream(logits.device).cuda_stream)
+        p = lambda t: C.c_void_p(t.data_ptr())
+        L.check(lib.spb_nll_bwd(dt, p(logits), logits.stride(0), p(tg), N, V, p(lse), float(dloss), p(dlogits), dlogits.stride(0), st),
+                "spb_nll_bwd")
+        return dlogits, None
+
+
+def nll_loss(logits, targets):
+    """llama3/LLaMA-jax.ipynb:959-967: ``-mean(take_along_axis(log_softmax(logits), targets[:, None], axis=1))``;
+    logits [..., V] are flattened to [N, V] like the notebook's reshape (:959-960)."""
+    V = logits.shape[-1]
+    return _NllFn.apply(logits.reshape(-1, V), targets.reshape(-1))

@@ -103,3 +103,26 @@ def flash_bwd(q, k, v, o, do, lse, causal, scale, impl=L.IMPL_AUTO):
                               _ptr(delta), _ptr(dq), dq.stride(1), _ptr(dk), dk.stride(1), _ptr(dv), dv.stride(1),
                               _ptr(dq_acc), _stream()), "spb_flash_bwd")
     return dq, dk, dv
+
+
+class _MatmulFn(torch.autograd.Function):
+    """y = x @ w with w stored [in, out] (``jnp.dot(h, params['output'])``, llama3:930): forward and both backward GEMMs through
+    spb_gemm (tcgen05 for bf16, FFMA for fp32); the weight gradient is accumulated in fp32."""
+
+    @staticmethod
+    def forward(ctx, x, w):
+        ctx.save_for_backward(x, w)
+        return gemm(x, w)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dy = dy.contiguous()
+        dx = gemm(dy, w, transB=True)
+        dw = gemm(x, dy, transA=True, out_dtype=torch.float32)
+        return dx, dw.to(w.dtype)
+
+
+def matmul(x, w):
+    """Differentiable 2-D matmul on the library's GEMMs: x [N, K] @ w [K, M]."""
+    return _MatmulFn.apply(x.contiguous(), w.contiguous())

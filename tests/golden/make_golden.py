@@ -202,6 +202,31 @@ def make_llama_ffn(tag, B, T, C, seed):
     print("llama ffn", tag, "out", out32.shape, "max|out|", np.abs(out32).max())
 
 
+def make_llama_loss(tag, B, T, V, seed):
+    """SURVEY 8 row f4: the notebook's own compute_loss cell (c28, llama3:956-968) executed with jnp bound to numpy;
+    model_forward is replaced by a stub that returns the given logits, so exactly the reshape / log_softmax / take_along_axis /
+    mean lines of the notebook run."""
+    rng = np.random.default_rng(seed)
+    logits = (rng.standard_normal((B, T, V)) * 3).astype(np.float32)
+    targets = rng.integers(0, V, size=(B, T))
+    out = dict(logits=logits, targets=targets, meta=np.array([B, T, V], dtype=np.int64))
+    for high, key in ((False, "loss"), (True, "loss64")):
+        ns = llama_namespace(high)
+
+        def log_softmax(x, axis=-1):
+            m = np.max(x, axis=axis, keepdims=True)
+            return x - m - np.log(np.sum(np.exp(x - m), axis=axis, keepdims=True))
+
+        ns["jax"].nn.log_softmax = log_softmax
+        lg = logits.astype(np.float64) if high else logits
+        ns["model_forward"] = lambda params, inputs, config, lg=lg: (lg, None)
+        ns["config"] = types.SimpleNamespace(vocab_size=V)
+        exec(cell_src("llama3/LLaMA-jax.ipynb", 28), ns)
+        out[key] = np.asarray(ns["compute_loss"](None, (None, targets)))
+    np.savez_compressed(os.path.join(OUT, f"llama_loss_{tag}.npz"), **out)
+    print("llama loss", tag, float(out["loss"]), float(out["loss64"]))
+
+
 # --------------------------------------------------------------------------- gemma
 def make_gemma(tag, B, T, D, seed):
     ns = {}
@@ -327,6 +352,7 @@ if __name__ == "__main__":
     make_llama("mha_nomask", B=1, T=9, C=32, H=2, Hkv=2, causal=False, seed=1)
     make_llama("mqa_causal", B=2, T=12, C=64, H=4, Hkv=1, causal=True, seed=2)
     make_llama_ffn("small", B=2, T=12, C=32, seed=5)
+    make_llama_loss("small", B=2, T=16, V=257, seed=7)
     make_gemma("small", B=2, T=16, D=64, seed=3)
     make_gemma_geglu("small", B=2, T=12, D=32, seed=6)
     print("gemma MQA default param count", gemma_param_count_pin())

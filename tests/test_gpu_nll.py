@@ -1,0 +1,64 @@
+"""GPU parity of the loss head's memory-bound half: spb_nll_fwd / spb_nll_bwd against the oracle's
+restatement of llama3:959-967 (log_softmax + take_along_axis + mean), incl. the notebook's vocabulary 50257 (not a multiple of
+the 128-bit vector width) and a padded row pitch."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import llama_oracle, max_rel_err
+from oracle.metrics import TOL_BF16, TOL_F32
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("N,V,pad", [(64, 50257, 0), (64, 50257, 7), (37, 1000, 0), (5, 33, 0), (300, 4096, 0)])
+def test_nll_loss_and_gradient(dtype, N, V, pad):
+    from solvingpapers_b200 import llama as spl
+    rng = np.random.default_rng(N + V)
+    lg = torch.from_numpy((rng.standard_normal((N, V)) * 3).astype(np.float32)).to(dtype)
+    tg = torch.from_numpy(rng.integers(0, V, size=(N,)))
+    ref_in = lg.float().requires_grad_(True)
+    ref = llama_oracle.nll_loss(ref_in, tg)
+    ref.backward()
+    buf = torch.zeros(N, V + pad, dtype=dtype, device="cuda")
+    buf[:, :V] = lg.cuda()
+    x = buf[:, :V].detach().requires_grad_(True)  # row pitch V + pad
+    loss = spl.nll_loss(x, tg.cuda())
+    loss.backward()
+    torch.cuda.synchronize()
+    tol = TOL_BF16 if dtype == torch.bfloat16 else TOL_F32
+    assert abs(float(loss) - float(ref)) <= tol * abs(float(ref)), (float(loss), float(ref))
+    assert max_rel_err(x.grad, ref_in.grad) < tol
+
+
+def test_loss_head_end_to_end_fp32():
+    """rms_norm -> logits GEMM -> NLL through the library's ops (llama3:929-930, 959-967), forward + gradients of h and the weights."""
+    from solvingpapers_b200 import llama as spl, ops
+    rng = np.random.default_rng(3)
+    B, T, C, V = 2, 32, 64, 1000
+    h = torch.from_numpy(rng.standard_normal((B, T, C)).astype(np.float32))
+    nw = torch.from_numpy(rng.standard_normal((C,)).astype(np.float32))
+    w = torch.from_numpy((rng.standard_normal((C, V)) / 8).astype(np.float32))
+    tg = torch.from_numpy(rng.integers(0, V, size=(B, T)))
+    hr, nr, wr = (t.clone().requires_grad_(True) for t in (h, nw, w))
+    ref = llama_oracle.loss_head(nr, wr, hr, tg)
+    ref.backward()
+    hd, nd, wd = (t.cuda().requires_grad_(True) for t in (h, nw, w))
+    logits = ops.matmul(spl.rms_norm(hd, nd).reshape(-1, C), wd)
+    loss = spl.nll_loss(logits, tg.cuda())
+    loss.backward()
+    torch.cuda.synchronize()
+    assert abs(float(loss) - float(ref)) <= TOL_F32 * abs(float(ref))
+    for got, want in ((hd.grad, hr.grad), (nd.grad, nr.grad), (wd.grad, wr.grad)):
+        assert max_rel_err(got, want) < TOL_F32
+
+
+def test_nll_against_golden_from_notebook_source(golden_dir):
+    """the notebook's own compute_loss lines (llama3:959-967, executed for tests/golden/llama_loss_small.npz)"""
+    from solvingpapers_b200 import llama as spl
+    g = dict(np.load(os.path.join(golden_dir, "llama_loss_small.npz")))
+    loss = spl.nll_loss(torch.from_numpy(g["logits"]).cuda(), torch.from_numpy(g["targets"]).cuda())
+    assert abs(float(loss) - float(g["loss64"])) < TOL_F32 * abs(float(g["loss64"]))

@@ -65,6 +65,14 @@ def test_llama_ffn_matches_literal_notebook_source_and_its_finite_differences(go
             assert abs(an - fd) <= 2e-6 * max(1.0, abs(fd)) + 1e-7, (name, an, fd)
 
 
+def test_llama_loss_matches_literal_notebook_source(golden_dir):
+    """oracle nll_loss against the notebook's own compute_loss lines (llama3:959-967), fp32 and fp64."""
+    g = _load(golden_dir, "llama_loss_small.npz")
+    lg, tg = T(g["logits"]), T(g["targets"])
+    assert abs(float(llama_oracle.nll_loss(lg, tg)) - float(g["loss"])) < 2e-6 * abs(float(g["loss"]))
+    assert abs(float(llama_oracle.nll_loss(lg.double(), tg)) - float(g["loss64"])) < 1e-12 * abs(float(g["loss64"]))
+
+
 def test_llama_freq_exponent_quirk(golden_dir):
     """f_j = theta^(-j/hd), not the paper's theta^(-2j/hd) (llama3:564)."""
     g = _load(golden_dir, "llama_gqa_causal.npz")
