@@ -53,23 +53,32 @@ __global__ void __launch_bounds__(NLL_THREADS) nll_fwd_kernel(const T* __restric
   const int64_t n = blockIdx.x;
   const T* row = logits + n * ld;
   float m = -INFINITY, s = 0.f;
-  for (int j = threadIdx.x * VN; j < V; j += NLL_THREADS * VN) {
-    float f[VN];
-    if (VEC && j + VN <= V) {
-      NllVec<T>::load(row + j, f);
-    } else {
+  // two vectors per trip: twice the loads in flight per thread (a bf16 row of 50257 logits is only 25 trips of 4 KB per CTA)
+  for (int j0 = threadIdx.x * VN; j0 < V; j0 += 2 * NLL_THREADS * VN) {
+    float f[2][VN];
 #pragma unroll
-      for (int e = 0; e < VN; ++e) f[e] = (j + e < V) ? to_f32<T>(row[j + e]) : -INFINITY;
+    for (int u = 0; u < 2; ++u) {
+      const int j = j0 + u * NLL_THREADS * VN;
+      if (VEC && j + VN <= V) {
+        NllVec<T>::load(row + j, f[u]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < VN; ++e) f[u][e] = (j + e < V) ? to_f32<T>(row[j + e]) : -INFINITY;
+      }
     }
-    float cm = f[0];
+    float cm = f[0][0];
 #pragma unroll
-    for (int e = 1; e < VN; ++e) cm = fmaxf(cm, f[e]);
+    for (int u = 0; u < 2; ++u)
+#pragma unroll
+      for (int e = 0; e < VN; ++e) cm = fmaxf(cm, f[u][e]);
     if (cm > m) {
       s = (m == -INFINITY) ? 0.f : s * __expf(m - cm);
       m = cm;
     }
 #pragma unroll
-    for (int e = 0; e < VN; ++e) s += __expf(f[e] - m);
+    for (int u = 0; u < 2; ++u)
+#pragma unroll
+      for (int e = 0; e < VN; ++e) s += __expf(f[u][e] - m);
   }
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) nll_merge(m, s, __shfl_xor_sync(0xffffffffu, m, off), __shfl_xor_sync(0xffffffffu, s, off));
