@@ -411,6 +411,50 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
   prof_mark("gemm_dattn", st);
   rc = spb_gemm(dt, dt, gimpl, N, Nq, d->C, dy, d->C, 0, p->wo, p->ldw_o, in_out ? 1 : 0, w8 + L.dattn_o, Nq, nullptr, 0, stream);
   if (rc) return rc;
+  static const bool dwo_early = [] {
+    const char* e = getenv("SPB_BWD_DWO_EARLY");
+    return e == nullptr || atoi(e) != 0;
+  }();
+  // 2. dwo, dbo (+ their all-reduce on the side stream).  Two positions (SPB_BWD_DWO_EARLY, timing experiments / tuning):
+  //    early (default): right after the dattn GEMM - its all-reduce hides under the (non-persistent) attention backward
+  //                     (8 GPUs: 2.59-2.60 ms per step vs 2.62-2.64 ms late; 1 GPU: no difference);
+  //    late           : between the dWqkv and dx GEMMs - d(attn_o) goes straight into the attention backward.
+  auto do_dwo = [&]() -> int {
+    prof_mark("gemm_dwo", st);
+    if (g->dwo) {
+      if (in_out) rc = spb_gemm(dt, SPB_F32, gimpl, Nq, d->C, N, w8 + L.attn_o, Nq, 1, dy, d->C, 0, g->dwo, g->ldw_o, nullptr, 0, stream);
+      else rc = spb_gemm(dt, SPB_F32, gimpl, d->C, Nq, N, dy, d->C, 1, w8 + L.attn_o, Nq, 0, g->dwo, g->ldw_o, nullptr, 0, stream);
+      if (rc) return rc;
+    }
+    prof_mark("bias_grad", st);
+    if (g->dbo) {
+      rc = spb_colsum(dt, dy, d->C, N, d->C, g->dbo, partial, stream);
+      if (rc) return rc;
+    }
+    // data parallelism: dwo's all-reduce overlaps the dx GEMM and the norm backward (SURVEY 8e "Overlap")
+    if (comm != nullptr && (g->dwo || g->dbo)) {
+      float* ptrs[2];
+      size_t counts[2];
+      int n = 0;
+      if (g->dwo) {
+        const int64_t rows = in_out ? Nq : d->C, cols = in_out ? d->C : Nq;
+        SPB_CHECK_ARG(g->ldw_o == cols, SPB_E_UNSUPPORTED, "spb_block_bwd: all-reduce needs a contiguous dwo");
+        ptrs[n] = g->dwo;
+        counts[n++] = (size_t)(rows * cols);
+      }
+      if (g->dbo) {
+        ptrs[n] = g->dbo;
+        counts[n++] = (size_t)d->C;
+      }
+      rc = comm_allreduce_side(comm, ptrs, counts, n, st);
+      if (rc) return rc;
+    }
+    return 0;
+  };
+  if (dwo_early) {
+    rc = do_dwo();
+    if (rc) return rc;
+  }
   // 3. attention backward -> dq|dk|dv (post-rotary gradients)
   prof_mark("flash_bwd", st);
   // 4. rotary VJP on dq, dk: fused into the attention backward (dK epilogue + dQ fp32->bf16 conversion)
@@ -445,6 +489,9 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
     if (in_out) return spb_gemm(dt, SPB_F32, gimpl, d->C, width, N, xin, d->C, 1, dcols, Ntot, 0, dw, ldw, nullptr, 0, stream);
     return spb_gemm(dt, SPB_F32, gimpl, width, d->C, N, dcols, Ntot, 1, xin, d->C, 0, dw, ldw, nullptr, 0, stream);
   };
+  // (measured and not adopted: cutting the packed dWqkv GEMM into two row halves so that the first half's all-reduce starts
+  // earlier - at 8 GPUs the exposed all-reduce fell from 0.23 to 0.05 ms but the dWqkv and dx GEMMs, now both sharing the GPU
+  // with NCCL, got 0.06 + 0.2 ms slower: 2.588 vs 2.593 ms per step)
   if (gpacked) {
     rc = dw_gemm(g->dwq, g->ldw_q, dqkv, Ntot);
     if (rc) return rc;
@@ -486,36 +533,8 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
       if (rc) return rc;
     }
   }
-  // 2. dwo, dbo - scheduled here, between the dWqkv and dx GEMMs: both gradient all-reduces (dWqkv 100 MB, dWo 64 MB at C3)
-  // then have GEMM work behind them to hide under (with dWo right after the dattn GEMM the large dWqkv all-reduce only had
-  // the dx GEMM + norm backward left and ~0.1 ms of it was exposed), and d(attn_o) goes straight into the attention backward
-  prof_mark("gemm_dwo", st);
-  if (g->dwo) {
-    if (in_out) rc = spb_gemm(dt, SPB_F32, gimpl, Nq, d->C, N, w8 + L.attn_o, Nq, 1, dy, d->C, 0, g->dwo, g->ldw_o, nullptr, 0, stream);
-    else rc = spb_gemm(dt, SPB_F32, gimpl, d->C, Nq, N, dy, d->C, 1, w8 + L.attn_o, Nq, 0, g->dwo, g->ldw_o, nullptr, 0, stream);
-    if (rc) return rc;
-  }
-  prof_mark("bias_grad", st);
-  if (g->dbo) {
-    rc = spb_colsum(dt, dy, d->C, N, d->C, g->dbo, partial, stream);
-    if (rc) return rc;
-  }
-  // data parallelism: dwo's all-reduce overlaps the dx GEMM and the norm backward (SURVEY 8e "Overlap")
-  if (comm != nullptr && (g->dwo || g->dbo)) {
-    float* ptrs[2];
-    size_t counts[2];
-    int n = 0;
-    if (g->dwo) {
-      const int64_t rows = in_out ? Nq : d->C, cols = in_out ? d->C : Nq;
-      SPB_CHECK_ARG(g->ldw_o == cols, SPB_E_UNSUPPORTED, "spb_block_bwd: all-reduce needs a contiguous dwo");
-      ptrs[n] = g->dwo;
-      counts[n++] = (size_t)(rows * cols);
-    }
-    if (g->dbo) {
-      ptrs[n] = g->dbo;
-      counts[n++] = (size_t)d->C;
-    }
-    rc = comm_allreduce_side(comm, ptrs, counts, n, st);
+  if (!dwo_early) {
+    rc = do_dwo();
     if (rc) return rc;
   }
   // 6. d(xhat) = dqkv . Wqkv^T
