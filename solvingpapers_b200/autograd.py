@@ -7,16 +7,65 @@ import torch
 from . import _lib as L
 from .block import AttentionBlock, BlockConfig, _ptr, _stream
 
-_BLOCKS = {}
+class WorkspacePool:
+    """Free-list of workspace owners (AttentionBlock / FeedForward objects) keyed by (config, device, communicator).
+
+    The reference trains through ``model_forward``, which calls ``transformer_block`` once per entry of ``params['blocks']``
+    with identical shapes (llama3/LLaMA-jax.ipynb:925-927), so several forwards of one shape are alive at the same time and
+    each needs its OWN residual storage until its backward has run.  Every forward leases an owner from the pool (creating
+    one when the free-list is empty) and the lease returns it after the backward - or when the autograd node is dropped
+    without a backward (inference).  A model with L same-shape layers therefore settles at L workspaces, reused every step."""
+
+    def __init__(self, factory):
+        self._factory = factory
+        self._free = {}
+        self.created = 0
+
+    def lease(self, cfg, device, comm):
+        key = (_cfg_key(cfg), str(device), comm)
+        free = self._free.setdefault(key, [])
+        if free:
+            owner = free.pop()
+        else:
+            owner = self._factory(cfg, device, comm)
+            self.created += 1
+        return Lease(self, key, owner)
+
+    def _give_back(self, key, owner):
+        self._free.setdefault(key, []).append(owner)
+
+    def clear(self):
+        self._free.clear()
+
+
+class Lease:
+    """Exclusive use of one workspace owner between a forward and its backward."""
+
+    def __init__(self, pool, key, owner):
+        self.pool, self.key, self.owner = pool, key, owner
+
+    def release(self):
+        if self.owner is not None:
+            self.pool._give_back(self.key, self.owner)
+            self.owner = None
+
+    def __del__(self):  # autograd node dropped without a backward
+        try:
+            self.release()
+        except Exception:
+            pass
+
+
+def _cfg_key(cfg):
+    return (type(cfg).__name__,) + tuple(sorted(cfg.__dict__.items(), key=lambda kv: kv[0]))
+
+
+BLOCK_POOL = WorkspacePool(lambda cfg, device, comm: AttentionBlock(cfg, device=device, comm=comm))
 
 
 def get_block(cfg: BlockConfig, device, comm=None) -> AttentionBlock:
-    key = (tuple(sorted(cfg.__dict__.items(), key=lambda kv: kv[0])), str(device), comm)
-    blk = _BLOCKS.get(key)
-    if blk is None:
-        blk = AttentionBlock(cfg, device=device, comm=comm)
-        _BLOCKS[key] = blk
-    return blk
+    """A private AttentionBlock (own workspace) for callers that drive forward/backward themselves."""
+    return AttentionBlock(cfg, device=device, comm=comm)
 
 
 class BlockFn(torch.autograd.Function):
@@ -25,24 +74,24 @@ class BlockFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, cfg, names, comm, x, *tensors):
         params = dict(zip(names, tensors))
-        blk = get_block(cfg, x.device, comm)
+        lease = BLOCK_POOL.lease(cfg, x.device, comm)
+        blk = lease.owner
         y = blk.forward(x.contiguous(), params)
-        ctx.blk, ctx.names, ctx.params = blk, names, params
+        ctx.lease, ctx.names, ctx.params = lease, names, params
         ctx.save_for_backward(x, *tensors)
-        # residuals live in the block's workspace: a second forward with the same config before this backward
-        # would overwrite them, so remember which forward owns the workspace.
-        blk._owner = ctx
-        k, v = blk.kv_cache()
+        # (k, v) of llama3:819 are returned as tensors that own their memory: the workspace they were computed in goes
+        # back to the pool after the backward and is overwritten by a later forward
+        k, v = (t.clone() for t in blk.kv_cache())
         ctx.mark_non_differentiable(k, v)
         return y, k, v
 
     @staticmethod
     def backward(ctx, dy, _dk, _dv):
-        blk = ctx.blk
-        if getattr(blk, "_owner", None) is not ctx:
-            raise L.SpbError("the block workspace was overwritten by a later forward with the same shape; "
-                             "run backward before the next forward of an identically-shaped block")
-        g = blk.backward(dy.contiguous())
+        lease = ctx.lease
+        if lease is None or lease.owner is None:
+            raise L.SpbError("this block's residuals were already released by an earlier backward (retain_graph is not supported)")
+        g = lease.owner.backward(dy.contiguous())
+        lease.release()
         out = []
         for n in ctx.names:
             p = ctx.params[n]

@@ -314,19 +314,29 @@ int spb_block_ws_layout(const spb_block_desc* d, spb_ws_layout* out) {
   return 0;
 }
 
+// Pointer and alignment checks shared by spb_block_fwd and spb_block_bwd: both directions take the same descriptor,
+// weights and workspace, and a mismatch between the two calls must be an error return, not a device fault.
+static int check_block_params(const char* who, const spb_block_desc* d, const spb_block_params* p, const void* x, const void* ws) {
+  SPB_CHECK_ARG(p && x && ws, SPB_E_INVALID, "%s: null pointer", who);
+  SPB_CHECK_ARG(p->wq && p->wk && p->wv && p->wo, SPB_E_INVALID, "%s: null weight", who);
+  SPB_CHECK_ARG(d->norm_kind == SPB_NORM_NONE || p->norm_w, SPB_E_INVALID, "%s: norm weight is NULL", who);
+  SPB_CHECK_ARG(d->rope_kind == SPB_ROPE_NONE || p->rope, SPB_E_INVALID, "%s: rope table is NULL", who);
+  SPB_CHECK_ARG(d->rope_kind == SPB_ROPE_NONE || (uintptr_t)p->rope % 16 == 0, SPB_E_INVALID, "%s: rope table must be 16-byte aligned", who);
+  SPB_CHECK_ARG(!d->qkv_bias || (p->bq && p->bk && p->bv), SPB_E_INVALID, "%s: qkv_bias set but a bias pointer is NULL", who);
+  SPB_CHECK_ARG(!d->out_bias || p->bo, SPB_E_INVALID, "%s: out_bias set but bo is NULL", who);
+  SPB_CHECK_ARG((uintptr_t)ws % 256 == 0, SPB_E_INVALID, "%s: workspace must be 256-byte aligned", who);
+  return 0;
+}
+
 int spb_block_fwd(const spb_block_desc* d, const spb_block_params* p, const void* x, void* y, void* ws, spb_stream_t stream) {
   int rc = check_desc(d);
   if (rc) return rc;
-  SPB_CHECK_ARG(p && x && y && ws, SPB_E_INVALID, "spb_block_fwd: null pointer");
-  SPB_CHECK_ARG(p->wq && p->wk && p->wv && p->wo, SPB_E_INVALID, "spb_block_fwd: null weight");
-  SPB_CHECK_ARG(d->norm_kind == SPB_NORM_NONE || p->norm_w, SPB_E_INVALID, "spb_block_fwd: norm weight is NULL");
-  SPB_CHECK_ARG(d->rope_kind == SPB_ROPE_NONE || p->rope, SPB_E_INVALID, "spb_block_fwd: rope table is NULL");
-  SPB_CHECK_ARG(!d->qkv_bias || (p->bq && p->bk && p->bv), SPB_E_INVALID, "spb_block_fwd: qkv_bias set but a bias pointer is NULL");
-  SPB_CHECK_ARG(!d->out_bias || p->bo, SPB_E_INVALID, "spb_block_fwd: out_bias set but bo is NULL");
+  SPB_CHECK_ARG(y != nullptr, SPB_E_INVALID, "spb_block_fwd: y is NULL");
+  rc = check_block_params("spb_block_fwd", d, p, x, ws);
+  if (rc) return rc;
   spb_ws_layout L;
   rc = spb_block_ws_layout(d, &L);
   if (rc) return rc;
-  SPB_CHECK_ARG((uintptr_t)ws % 256 == 0, SPB_E_INVALID, "spb_block_fwd: workspace must be 256-byte aligned");
   char* w8 = (char*)ws;
   const int64_t N = (int64_t)d->B * d->T;
   const int64_t Nq = (int64_t)d->Hq * d->hd, Nkv = (int64_t)d->Hkv * d->hd, Ntot = Nq + 2 * Nkv;
@@ -386,11 +396,24 @@ int spb_block_fwd(const spb_block_desc* d, const spb_block_params* p, const void
   return rc;
 }
 
+static int block_bwd_impl(const spb_block_desc* d, const spb_block_params* p, const void* x, const void* dy, void* ws,
+                          const spb_block_grads* g, void* comm, spb_stream_t stream);
+
 int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void* x, const void* dy, void* ws,
                   const spb_block_grads* g, void* comm, spb_stream_t stream) {
+  const int rc = block_bwd_impl(d, p, x, dy, ws, g, comm, stream);
+  // an error return after a side-stream all-reduce was issued must not leave that work un-joined
+  if (rc != 0 && comm != nullptr) comm_side_cleanup(comm, (cudaStream_t)stream);
+  return rc;
+}
+
+static int block_bwd_impl(const spb_block_desc* d, const spb_block_params* p, const void* x, const void* dy, void* ws,
+                          const spb_block_grads* g, void* comm, spb_stream_t stream) {
   int rc = check_desc(d);
   if (rc) return rc;
-  SPB_CHECK_ARG(p && x && dy && ws && g, SPB_E_INVALID, "spb_block_bwd: null pointer");
+  SPB_CHECK_ARG(dy && g, SPB_E_INVALID, "spb_block_bwd: null pointer");
+  rc = check_block_params("spb_block_bwd", d, p, x, ws);
+  if (rc) return rc;
   spb_ws_layout L;
   rc = spb_block_ws_layout(d, &L);
   if (rc) return rc;
@@ -431,7 +454,7 @@ int spb_block_bwd(const spb_block_desc* d, const spb_block_params* p, const void
       rc = spb_colsum(dt, dy, d->C, N, d->C, g->dbo, partial, stream);
       if (rc) return rc;
     }
-    // data parallelism: dwo's all-reduce overlaps the dx GEMM and the norm backward (SURVEY 8e "Overlap")
+    // data parallelism: dwo's all-reduce runs on the side stream under the attention backward (SURVEY 8e "Overlap")
     if (comm != nullptr && (g->dwo || g->dbo)) {
       float* ptrs[2];
       size_t counts[2];
@@ -672,12 +695,24 @@ int spb_ffn_fwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, v
                   d->residual ? x : nullptr, C);
 }
 
+static int ffn_bwd_impl(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, const void* dy, void* ws, const spb_ffn_grads* g,
+                        void* comm, spb_stream_t stream);
+
 int spb_ffn_bwd(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, const void* dy, void* ws, const spb_ffn_grads* g,
                 void* comm, spb_stream_t stream) {
+  const int rc = ffn_bwd_impl(d, p, x, dy, ws, g, comm, stream);
+  if (rc != 0 && comm != nullptr) comm_side_cleanup(comm, (cudaStream_t)stream);
+  return rc;
+}
+
+static int ffn_bwd_impl(const spb_ffn_desc* d, const spb_ffn_params* p, const void* x, const void* dy, void* ws, const spb_ffn_grads* g,
+                        void* comm, spb_stream_t stream) {
   int rc = check_ffn_desc(d);
   if (rc) return rc;
   const bool gated = d->act != SPB_ACT_GELU_TANH;
   SPB_CHECK_ARG(p && x && dy && ws && g && p->w1 && (p->w3 || !gated) && p->w2, SPB_E_INVALID, "spb_ffn_bwd: null pointer");
+  SPB_CHECK_ARG(d->norm_kind == SPB_NORM_NONE || p->norm_w, SPB_E_INVALID, "spb_ffn_bwd: norm_w is NULL");
+  SPB_CHECK_ARG((uintptr_t)ws % 256 == 0, SPB_E_INVALID, "spb_ffn_bwd: workspace must be 256-byte aligned");
   spb_ffn_ws L;
   rc = spb_ffn_ws_layout(d, &L);
   if (rc) return rc;

@@ -102,6 +102,14 @@ int comm_allreduce_join(void* comm, float* const* ptrs, const size_t* counts, in
   return 0;
 }
 
+void comm_side_cleanup(void* comm, cudaStream_t main) {
+  Comm* c = (Comm*)comm;
+  if (c != nullptr && c->side_pending) {
+    cudaStreamWaitEvent(main, c->ev_side, 0);
+    c->side_pending = false;
+  }
+}
+
 }  // namespace spb
 
 using namespace spb;

@@ -46,6 +46,15 @@ __device__ unsigned long long g_fb_trace[FB_TRACE_ROLES * FB_TRACE_EVENTS];
 #define FB_TRACE(id)
 #endif
 
+// Ablation switches for timing experiments (tools/diag_ablate.py): they skip MMAs or the dQ reduce, so the results become
+// WRONG.  Compiled in only with -DSPB_FB_ABLATE (tools/build_variant.sh), into a separate library; the product build has
+// neither the switches nor the getenv that reads them.
+#ifdef SPB_FB_ABLATE
+#define FB_ABL(bit) ((p.ablate & (bit)) != 0)
+#else
+#define FB_ABL(bit) false
+#endif
+
 constexpr int FB_AGROUPS = 2;                         // element-wise warpgroups; each owns 64 / FB_AGROUPS query columns
 constexpr int FB_ACOLS = 64 / FB_AGROUPS;
 constexpr int FB_ATHREADS = FB_AGROUPS * 128;
@@ -110,8 +119,10 @@ struct FaBwdArgs {
   int T, Hq, Hkv, causal;
   float scale, scale_log2;
   const float4* rope;  // optional: apply the rotary VJP (M^T) to dK rows in the epilogue (dQ gets it in the convert kernel)
-  int ablate;          // timing experiments only (env SPB_FB_ABLATE, results become wrong): 1 skip dV MMAs, 2 skip dK MMAs,
-                       // 4 skip dQ^T MMAs, 8 skip the dQ smem staging + TMA reduce, 16 skip the dP^T MMAs, 32 skip exp/dS math
+#ifdef SPB_FB_ABLATE
+  int ablate;          // 1 skip dV MMAs, 2 skip dK MMAs, 4 skip dQ^T MMAs, 8 skip the dQ smem staging + TMA reduce,
+                       // 16 skip the dP^T MMAs, 32 skip exp/dS math
+#endif
 };
 
 template <int HD>
@@ -245,7 +256,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
           const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
           umma_bf16_w(tmem_base + Cfg::TM_ST, dK_k + (aoff >> 4), dQ_k + (boff >> 4), idesc_s, kk > 0 ? 1u : 0u);
         }
-        if (!(p.ablate & 16))
+        if (!FB_ABL(16))
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
           const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
@@ -263,15 +274,15 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         tc_fence_after();
         const uint64_t dDO_mn = umma_desc_mnmajor(smem_u32(sDO + st * Cfg::Q_BYTES) + z * Cfg::ZCH * 8192, 64);
         const uint64_t dQ_mn = umma_desc_mnmajor(smem_u32(sQ + st * Cfg::Q_BYTES) + z * Cfg::ZCH * 8192, 64);
-        if (!(p.ablate & 1))
+        if (!FB_ABL(1))
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dV += P^T dO
           umma_bf16_ts_w(tmem_base + Cfg::TM_DV, tmem_base + Cfg::TM_P + kk * 8, dDO_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
-        if (!(p.ablate & 2))
+        if (!FB_ABL(2))
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dK += dS^T Q
           umma_bf16_ts_w(tmem_base + Cfg::TM_DK, tmem_base + Cfg::TM_DS + kk * 8, dQ_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
-        if (!(p.ablate & 4))
+        if (!FB_ABL(4))
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)  // dQ^T = K^T dS
           umma_bf16_w(tmem_base + Cfg::TM_DQT, dK_mn + ((kk * 2048) >> 4), dDST_mn + ((kk * 2048) >> 4), idesc_q, kk > 0 ? 1u : 0u);
@@ -367,7 +378,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
           pkd[i >> 1] = pack_bf16(ds.x, ds.y);
         }
       };
-      if (p.ablate & 32) {
+      if (FB_ABL(32)) {
 #pragma unroll
         for (int i = 0; i < FB_ACOLS / 2; ++i) pkp[i] = pkd[i] = rs[i] ^ rd[i];
       } else if (need_mask) {
@@ -461,7 +472,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         // transpose through shared memory ([q][d] fp32, lanes write consecutive d: conflict-free) and let the TMA engine do
         // ONE bulk reduce-add of the 64 x hd tile into the fp32 dq accumulator (per-thread fp32 atomics were the v2
         // bottleneck: ~1 float atomic / clk / SM).  Rows past the sequence end hold exact zeros (their P^T is masked).
-        if (p.ablate & 8) continue;
+        if (FB_ABL(8)) continue;
         constexpr int NB = Cfg::DQ_WARPS * 32;
         const bool leader = (qd == 0 && lane == 0);
 #pragma unroll
@@ -611,10 +622,12 @@ static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
   a.scale = scale;
   a.scale_log2 = scale * FB_LOG2E;
   a.rope = (const float4*)rope;
+#ifdef SPB_FB_ABLATE
   {
     const char* ab = getenv("SPB_FB_ABLATE");
     a.ablate = ab ? atoi(ab) : 0;
   }
+#endif
   SPB_CUDA(cudaFuncSetAttribute(flash_bwd_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
   dim3 grid(Hkv * Cfg::HS, B, (Tn + 127) / 128);
   flash_bwd_tc_kernel<HD><<<grid, FB_THREADS, Cfg::SMEM_BYTES, st>>>(tmK, tmV, tmQ, tmDO, tmDQ, a);

@@ -388,7 +388,8 @@ __global__ void gemm_tc_zero_tail_kernel(const GemmTcArgs p);
 // only HALF of B (128 of the 256 N rows) per k-block - 32 KB instead of 48 KB per 128 x 256 x 64 MACs - which cuts the
 // shared-memory fill traffic and the L2->SM bytes per FLOP by a third and leaves room for 6 pipeline stages.  The leader
 // CTA (rank 0) issues every MMA for the pair; commits are multicast to both CTAs' barriers; each CTA drains its own
-// 128 x 256 TMEM accumulator.  Full-K tiles only (no K-split), BN = 256.
+// 128 x 256 TMEM accumulator.  BN = 256.  Whole waves run full-K tiles; the tail wave of an fp32 weight-gradient GEMM is split
+// along K and leaves through TMA bulk reduce-adds into pre-zeroed tiles (gemm_tc2_item / gemm_tc_reduce_chunk).
 struct GemmTc2Cfg {
   static constexpr int BN = 256;
   static constexpr int STAGES = 6;

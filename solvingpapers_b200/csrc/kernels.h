@@ -42,5 +42,7 @@ int norm_bwd_add(int dtype, int norm_kind, int upcast, const void* x, const void
 int comm_allreduce_side(void* comm, float* const* ptrs, const size_t* counts, int n, cudaStream_t main);
 // all-reduce on `main`, then make `main` wait for the side stream's outstanding all-reduce
 int comm_allreduce_join(void* comm, float* const* ptrs, const size_t* counts, int n, cudaStream_t main);
+// error path: if a side-stream all-reduce is outstanding, make `main` wait for it and forget it
+void comm_side_cleanup(void* comm, cudaStream_t main);
 
 }  // namespace spb

@@ -75,6 +75,8 @@ __global__ void __launch_bounds__(NLL_THREADS) nll_fwd_kernel(const T* __restric
       s = (m == -INFINITY) ? 0.f : s * __expf(m - cm);
       m = cm;
     }
+    // everything seen so far is -inf (vocabulary-masked logits): exp(-inf - (-inf)) would be NaN, and the sum stays 0
+    if (m == -INFINITY) continue;
 #pragma unroll
     for (int u = 0; u < 2; ++u)
 #pragma unroll

@@ -154,34 +154,45 @@ class FeedForward:
         return g
 
 
-_cache = {}
+def _make_ffn(cfg, device, comm):
+    return FeedForward(cfg, device=device, comm=comm)
+
+
+def _pool():
+    from .autograd import WorkspacePool
+    global _POOL
+    if _POOL is None:
+        _POOL = WorkspacePool(_make_ffn)
+    return _POOL
+
+
+_POOL = None
 
 
 def get_ffn(cfg, device, comm=None):
-    key = (cfg, str(device), comm)
-    if key not in _cache:
-        _cache[key] = FeedForward(cfg, device=device, comm=comm)
-    return _cache[key]
+    """A private FeedForward (own workspace) for callers that drive forward/backward themselves."""
+    return FeedForward(cfg, device=device, comm=comm)
 
 
 class FfnFn(torch.autograd.Function):
-    """y = ffn(x; weights) as a differentiable torch op.  `names` lists the keys of the tensors that follow."""
+    """y = ffn(x; weights) as a differentiable torch op.  `names` lists the keys of the tensors that follow.
+    Every forward leases its own workspace (autograd.WorkspacePool): same-shape layers of one model do not share residuals."""
 
     @staticmethod
     def forward(ctx, cfg, names, comm, x, *tensors):
         params = dict(zip(names, tensors))
-        ff = get_ffn(cfg, x.device, comm)
-        y = ff.forward(x.contiguous(), params)
-        ctx.ff, ctx.names, ctx.params = ff, names, params
-        ff._owner = ctx
+        lease = _pool().lease(cfg, x.device, comm)
+        y = lease.owner.forward(x.contiguous(), params)
+        ctx.lease, ctx.names, ctx.params = lease, names, params
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        ff = ctx.ff
-        if getattr(ff, "_owner", None) is not ctx:
-            raise L.SpbError("the feed-forward workspace was overwritten by a later forward with the same shape")
-        g = ff.backward(dy.contiguous())
+        lease = ctx.lease
+        if lease is None or lease.owner is None:
+            raise L.SpbError("this feed-forward's residuals were already released by an earlier backward (retain_graph is not supported)")
+        g = lease.owner.backward(dy.contiguous())
+        lease.release()
         out = []
         for n in ctx.names:
             gn = {"w13": "dw13", "w1": "dw1", "w3": "dw3", "w2": "dw2", "norm_w": "dnorm_w", "norm_b": "dnorm_b", "b1": "db1",

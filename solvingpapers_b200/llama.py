@@ -1,7 +1,7 @@
 """Drop-in for the hot-path functions of llama3/LLaMA-jax.ipynb: SAME names, argument order, defaults and error
 behaviour as the notebook's cells (c15 rms_norm :536, c16 precompute_freqs_cis :563, c17 apply_rotary_emb :592,
 c18 repeat_kv :626, c24 attention :809) - arrays are torch CUDA tensors because JAX is not installable in this
-image (the jax.ffi face of the same library is in jax_ffi.py / INTEGRATION.md).  Differentiable through
+image (the jax.ffi face of the same library is ffi/spb_jax_ffi.cc + ffi/spb_jax.py).  Differentiable through
 torch.autograd the way the notebook's functions are through jax.value_and_grad (:995).
 
 Contract carried over from tracing: under jit the mask is a tracer whose values cannot be read, so

@@ -97,3 +97,76 @@ def test_vit_module_call_surface(golden_dir):
     h = vit.layer_norm(T_(g["ln_weight"]).to(DEV), T_(g["ln_bias"]).to(DEV), x)
     y = mha(params, h, h, h)[0]  # ViT.ipynb:221
     assert max_rel_err(y, T_(g["y"])) < TOL_F32
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_two_same_shape_layers_train_through_transformer_block(dtype):
+    """model_forward (llama3/LLaMA-jax.ipynb:925-930) calls transformer_block once per layer with identical shapes, then
+    the loss head; every layer's gradients and new_cache entry must survive the other layers' forwards."""
+    from solvingpapers_b200 import llama, ops
+    from solvingpapers_b200.autograd import BLOCK_POOL
+    tol = TOL_BF16 if dtype == torch.bfloat16 else TOL_F32
+    rng = np.random.default_rng(11)
+    B, T, C, H, Hkv, V, NL = 2, 64, 128, 4, 2, 256, 3
+    hd = C // H
+    rd = lambda t: t.to(dtype).float()
+
+    def rd_tree(t):
+        return {k: rd_tree(v) for k, v in t.items()} if isinstance(t, dict) else rd(t)
+
+    layers = []
+    for _ in range(NL):
+        p = llama_oracle.init_block_params(rng, C, H, Hkv)
+        p.update(llama_oracle.init_ffn_params(rng, C))
+        layers.append(rd_tree(p))
+    norm_f = rd(T_(rng.standard_normal(C).astype(np.float32)))
+    w_out = rd(T_((rng.standard_normal((C, V)) / math.sqrt(C)).astype(np.float32)))
+    x = rd(T_(rng.standard_normal((B, T, C)).astype(np.float32)))
+    targets = T_(rng.integers(0, V, size=(B, T)))
+
+    # ---- oracle: the notebook's op sequence with autograd
+    def leaf(t):
+        return {k: leaf(v) for k, v in t.items()} if isinstance(t, dict) else t.clone().requires_grad_(True)
+
+    o_layers, o_nf, o_wo, o_x = [leaf(p) for p in layers], leaf(norm_f), leaf(w_out), leaf(x)
+    fc = llama_oracle.precompute_freqs_cis(hd, T)
+    mask = llama_oracle.make_mask(T)
+    h, o_caches = o_x, []
+    for p in o_layers:
+        h, c = llama_oracle.transformer_block(p, h, mask, fc, H, Hkv)
+        o_caches.append(c)
+    o_loss = llama_oracle.loss_head(o_nf, o_wo, h, targets)
+    o_loss.backward()
+
+    # ---- the drop-in on the GPU, same call sequence
+    def dev(t):
+        return {k: dev(v) for k, v in t.items()} if isinstance(t, dict) else t.to(dtype).to(DEV).requires_grad_(True)
+
+    g_layers, g_nf, g_wo, g_x = [dev(p) for p in layers], dev(norm_f), dev(w_out), dev(x)
+    freqs_cis = llama.precompute_freqs_cis(hd, T)
+    gmask = torch.zeros(1, 1, T, T, device=DEV)
+    created0 = BLOCK_POOL.created
+    for step in range(2):  # the second step must reuse the first step's workspaces, not allocate new ones
+        for t in [g_nf, g_wo, g_x] + [w for p in g_layers for w in (list(p["attention"].values()) + list(p["ffn"].values()) + [p["attention_norm"], p["ffn_norm"]])]:
+            t.grad = None
+        h, caches = g_x, []
+        for p in g_layers:
+            h, c = llama.transformer_block(p, h, gmask, freqs_cis, H, Hkv)
+            caches.append(c)
+        logits = ops.matmul(llama.rms_norm(h, g_nf).reshape(B * T, C), g_wo)
+        loss = llama.nll_loss(logits, targets.to(DEV))
+        loss.backward()
+    assert BLOCK_POOL.created - created0 == NL, "one workspace per simultaneously-live layer, reused across steps"
+    assert abs(loss.item() - o_loss.item()) < tol * max(1.0, abs(o_loss.item()))
+    gtol = 3 * tol  # three chained layers + the loss head accumulate rounding
+    assert max_rel_err(g_x.grad, o_x.grad) < gtol
+    for li, (gp, op, gc, oc) in enumerate(zip(g_layers, o_layers, caches, o_caches)):
+        assert max_rel_err(gc[0], oc[0]) < gtol and max_rel_err(gc[1], oc[1]) < gtol, f"layer {li} cache"
+        for n in ("wq", "wk", "wv", "wo"):
+            assert max_rel_err(gp["attention"][n].grad, op["attention"][n].grad) < gtol, (li, n)
+        for n in ("w1", "w2", "w3"):
+            assert max_rel_err(gp["ffn"][n].grad, op["ffn"][n].grad) < gtol, (li, n)
+        assert max_rel_err(gp["attention_norm"].grad, op["attention_norm"].grad) < gtol, li
+        assert max_rel_err(gp["ffn_norm"].grad, op["ffn_norm"].grad) < gtol, li
+    # distinct layers own distinct caches
+    assert caches[0][0].data_ptr() != caches[1][0].data_ptr()

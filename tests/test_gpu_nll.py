@@ -62,3 +62,31 @@ def test_nll_against_golden_from_notebook_source(golden_dir):
     g = dict(np.load(os.path.join(golden_dir, "llama_loss_small.npz")))
     loss = spl.nll_loss(torch.from_numpy(g["logits"]).cuda(), torch.from_numpy(g["targets"]).cuda())
     assert abs(float(loss) - float(g["loss64"])) < TOL_F32 * abs(float(g["loss64"]))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_nll_with_vocabulary_masked_logits(dtype):
+    """-inf logits (masked vocabulary entries), including whole leading vector chunks and whole thread strides of -inf:
+    loss and gradient stay finite and equal log_softmax's (the per-thread online max used to produce exp(-inf+inf) = NaN)."""
+    from solvingpapers_b200 import llama as spl
+    rng = np.random.default_rng(5)
+    N, V = 9, 9000
+    lg = torch.from_numpy((rng.standard_normal((N, V)) * 2).astype(np.float32)).to(dtype)
+    lg[0, :4100] = -float("inf")       # more than one full pass of the CTA (256 threads x 8 x 2 = 4096 columns)
+    lg[1, :16] = -float("inf")         # a thread's first two vectors
+    lg[2, ::2] = -float("inf")
+    lg[3, 100:] = -float("inf")        # only the head of the row is live
+    tg = torch.from_numpy(rng.integers(0, 100, size=(N,)))
+    tg[0] = 5000
+    tg[2] = 1
+    ref_in = lg.float().requires_grad_(True)
+    ref = llama_oracle.nll_loss(ref_in, tg)
+    ref.backward()
+    x = lg.cuda().requires_grad_(True)
+    loss = spl.nll_loss(x, tg.cuda())
+    loss.backward()
+    torch.cuda.synchronize()
+    tol = TOL_BF16 if dtype == torch.bfloat16 else TOL_F32
+    assert torch.isfinite(loss) and torch.isfinite(x.grad).all()
+    assert abs(float(loss) - float(ref)) <= tol * abs(float(ref))
+    assert max_rel_err(x.grad, ref_in.grad) < tol

@@ -95,3 +95,27 @@ def test_dropin_error_behaviour_is_checked_before_any_kernel():
         vit.MultiheadAttention(8, 2)({}, x, torch.zeros(1, 4, 8), x)
     with pytest.raises(AssertionError):
         gpt.CausalSelfAttention(10, 3, 0.0)
+
+
+def test_workspace_pool_gives_every_live_forward_its_own_workspace():
+    """llama3/LLaMA-jax.ipynb:925-927 calls transformer_block once per layer with identical shapes: leases of one
+    config must be distinct while alive and be reused once released (no GPU needed: the factory is a stand-in)."""
+    from solvingpapers_b200.autograd import WorkspacePool
+
+    class Owner:
+        pass
+
+    pool = WorkspacePool(lambda cfg, device, comm: Owner())
+    cfg = sp.BlockConfig(2, 64, 128, 4, 2, 32)
+    a, b = pool.lease(cfg, "cuda:0", None), pool.lease(cfg, "cuda:0", None)
+    assert a.owner is not b.owner and pool.created == 2
+    first, second = a.owner, b.owner
+    a.release()
+    a.release()                                   # idempotent
+    c = pool.lease(cfg, "cuda:0", None)
+    assert c.owner is first and pool.created == 2  # reused, not re-created
+    other = pool.lease(sp.BlockConfig(2, 64, 128, 4, 4, 32), "cuda:0", None)
+    assert other.owner is not first and other.owner is not second and pool.created == 3
+    del b                                          # dropped without a backward: goes back to the pool
+    d = pool.lease(cfg, "cuda:0", None)
+    assert d.owner is second and pool.created == 3

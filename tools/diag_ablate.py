@@ -1,4 +1,5 @@
-"""GPU timing experiment (not a test): flash backward with parts switched off (SPB_FB_ABLATE), C3 shape."""
+"""GPU timing experiment (not a test): flash backward with parts switched off (SPB_FB_ABLATE), C3 shape.
+The switches exist only in a library built with `tools/build_variant.sh ablate -DSPB_FB_ABLATE`; point SPB_LIB_PATH at it."""
 import math, os, sys, subprocess
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 if len(sys.argv) > 1:
