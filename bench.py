@@ -53,6 +53,10 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--sustain-s", type=float, default=3.0,
+                    help="also run the step back to back for this many seconds (untimed warm-up excluded) and report the power-limited "
+                         "steady state as `sustained` next to the short timed region (0 = skip)")
+    ap.add_argument("--no-host-ceiling", action="store_true", help="skip the copy-only measurement of the host<->device ceiling")
     ap.add_argument("--residual", default="off", choices=["off", "fused", "separate"],
                     help="SURVEY 8 row f1: also produce h = x + block(x) and dx + dy - inside the kernels' epilogues (fused) or "
                          "with two extra element-wise passes after the block (separate); off = the block alone (headline)")
@@ -269,6 +273,89 @@ def run_reference(args):
     return 0
 
 
+def measure_host_ceiling(torch, dist, x, world, barrier, iters=8):
+    """Copy-only counterpart of the e2e step: per iteration 2 x |x| bytes pinned host -> device on one stream and 2 x |x|
+    bytes device -> pinned host on another, all ranks at once, no kernels.  Returns aggregate GB/s each way and the per-step
+    floor this puts under e2e (max over ranks)."""
+    nbytes = x.numel() * x.element_size()
+    hin = [torch.empty(x.shape, dtype=x.dtype).pin_memory() for _ in range(2)]
+    hout = [torch.empty(x.shape, dtype=x.dtype).pin_memory() for _ in range(2)]
+    din = [torch.empty_like(x) for _ in range(2)]
+    dout = [torch.empty_like(x) for _ in range(2)]
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def run(n, ev0=None, ev1=None):
+        if ev0 is not None:
+            ev0[0].record(s_in)
+            ev0[1].record(s_out)
+        for _ in range(n):
+            with torch.cuda.stream(s_in):
+                for j in range(2):
+                    din[j].copy_(hin[j], non_blocking=True)
+            with torch.cuda.stream(s_out):
+                for j in range(2):
+                    hout[j].copy_(dout[j], non_blocking=True)
+        if ev1 is not None:
+            ev1[0].record(s_in)
+            ev1[1].record(s_out)
+
+    run(2)
+    barrier()
+    a = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    b = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    run(iters, a, b)
+    barrier()
+    t = torch.tensor([a[0].elapsed_time(b[0]), a[1].elapsed_time(b[1])], dtype=torch.float64, device=x.device)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_in, ms_out = float(t[0].item()) / iters, float(t[1].item()) / iters
+    return {"h2d": world * 2 * nbytes / (ms_in * 1e-3) / 1e9, "d2h": world * 2 * nbytes / (ms_out * 1e-3) / 1e9, "ranks": world,
+            "bytes_each_way_per_rank_per_step": 2 * nbytes, "copy_only_ms_per_step": max(ms_in, ms_out),
+            "what": "aggregate over ranks, both directions concurrently, pinned host memory, no kernels (max time over ranks)"}
+
+
+def dp_check(torch, dist, blk, cfg, params, x, dy, grads, world):
+    from solvingpapers_b200 import _lib as L, ops
+    blk.forward(x, params)
+    blk.backward(dy, grads=grads)          # weight gradients all-reduced inside spb_block_bwd
+    torch.cuda.synchronize()
+    v = blk.residual_views()
+    xin = v["xhat"] if cfg.norm_kind != L.NORM_NONE else x.reshape(-1, cfg.C)
+    dy2 = dy.reshape(-1, cfg.C)
+    in_out = cfg.weight_layout == L.W_IN_OUT
+    local = {}
+    if in_out:
+        local["dwqkv"] = ops.gemm(xin, v["dqkv"], transA=True, out_dtype=torch.float32)
+        local["dwo"] = ops.gemm(v["attn_o"], dy2, transA=True, out_dtype=torch.float32)
+    else:
+        local["dwqkv"] = ops.gemm(v["dqkv"], xin, transA=True, out_dtype=torch.float32)
+        local["dwo"] = ops.gemm(dy2, v["attn_o"], transA=True, out_dtype=torch.float32)
+    if cfg.norm_kind != L.NORM_NONE:
+        _, dw, db = ops.norm_bwd(x.reshape(-1, cfg.C), params["norm_w"], v["stats"], v["dxhat"], kind=cfg.norm_kind,
+                                 upcast=cfg.norm_upcast, want_db=cfg.norm_kind == L.NORM_LAYER)
+        local["dnorm_w"] = dw
+        if db is not None and "dnorm_b" in grads:
+            local["dnorm_b"] = db
+    if cfg.qkv_bias:
+        local["dbqkv"] = ops.colsum(v["dqkv"])
+    if cfg.out_bias:
+        local["dbo"] = ops.colsum(dy2)
+    worst, per = 0.0, {}
+    for name, t in local.items():
+        if name not in grads:
+            continue
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)   # the checker's sum over ranks
+        ref = t.double()
+        err = float((grads[name].double() - ref).abs().max() / ref.abs().max().clamp_min(1e-30))
+        per[name] = err
+        worst = max(worst, err)
+    w = torch.tensor([worst], dtype=torch.float64, device=x.device)
+    dist.all_reduce(w, op=dist.ReduceOp.MAX)
+    return {"max_rel_err": float(w.item()), "ranks": world, "per_tensor_rank0": per,
+            "what": "library-reduced weight gradients vs torch.distributed SUM of the per-rank gradients recomputed from the same "
+                    "workspace operands; metric max|a-b|/max|b|"}
+
+
 # ------------------------------------------------------------------------------------------------ ours
 GEMM_STAGES = ("gemm_qkv", "gemm_out", "gemm_dattn", "gemm_dwo", "gemm_dx", "gemm_dwqkv")
 
@@ -434,6 +521,46 @@ def run_ours(args):
                        "x has landed, y leaves while the backward runs); weights and weight grads stay in HBM"}
         grads["dx"] = dxd[0]
 
+    # ---- host ceiling: the same bytes the e2e step moves (2 x |x| in, 2 x |x| out per rank), both directions at once, NO
+    # kernels - what the PCIe / host-memory side of this box gives N ranks at the same time.  e2e cannot beat
+    # tokens / max(step time, this copy time).
+    host_ceiling = None
+    if e2e is not None and not args.no_host_ceiling:
+        host_ceiling = measure_host_ceiling(torch, dist if world > 1 else None, x, world, barrier)
+        e2e["host_ceiling_gbs"] = host_ceiling
+
+    # ---- sustained leg: the same step back to back for --sustain-s seconds, so the power-limited steady state sits on the
+    # line next to the short (burst-clock) timed region
+    sustained = None
+    if args.sustain_s > 0:
+        n_sus = max(K, int(args.sustain_s * 1e3 / max(ms_step, 1e-3)))
+        if world > 1:  # every rank must run the same number of collectives
+            t_n = torch.tensor([n_sus], dtype=torch.int64, device=device)
+            dist.all_reduce(t_n, op=dist.ReduceOp.MAX)
+            n_sus = int(t_n.item())
+        half = n_sus // 2
+        sampler2 = ClockSampler(local_rank)
+        s0, s1, s2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        barrier()
+        sampler2.start()
+        s0.record()
+        for _ in range(half):
+            step()
+        s1.record()
+        for _ in range(n_sus - half):
+            step()
+        s2.record()
+        barrier()
+        clocks2 = sampler2.stop()
+        t_all = torch.tensor([s0.elapsed_time(s2), s1.elapsed_time(s2)], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(t_all, op=dist.ReduceOp.MAX)
+        ms_all, ms_tail = float(t_all[0].item()), float(t_all[1].item())
+        tail_steps = n_sus - half
+        sustained = {"seconds": ms_all * 1e-3, "steps": n_sus, "ms_per_step": ms_all / n_sus, "tok_s": tokens_local * world * n_sus / (ms_all * 1e-3),
+                     "ms_per_step_second_half": ms_tail / tail_steps, "tok_s_second_half": tokens_local * world * tail_steps / (ms_tail * 1e-3),
+                     "sm_mhz_median": clocks2.get("sm_mhz"), "reasons": clocks2.get("reasons")}
+
     # ---- roofline of the dominant kernel family (tcgen05 GEMM; FLOPs per SURVEY 8d: 3*F_gemm per step)
     pk = peaks()
     N = B * T
@@ -444,36 +571,75 @@ def run_ours(args):
                   (N * nq_ + N * Cm) * e_ + nq_ * Cm * 4 + (N * nt_ + Cm * nt_ + N * Cm) * e_ + (N * Cm + N * nt_) * e_ + Cm * nt_ * 4)  # A+B+D of the 6 GEMMs
     n_gemm = 6
     total_flops = cfg.flops_fwd_bwd()
-    # traffic: DRAM bytes per launch of the dominant kernel from the committed ncu --set full summary (tools/ncu_summary.py)
-    traffic = None
+    # traffic: DRAM bytes per launch of the dominant kernel from the committed ncu --set full summary (tools/ncu_summary.py).
+    # The summary records the stamp of the library sources it was captured from; a different library prints no traffic.
+    traffic, traffic_src = None, None
     try:
-        summ = json.load(open(os.path.join(ROOT, "profiles", "ncu_summary_latest.json")))["kernels"]
+        from solvingpapers_b200 import build as spbuild
+        summ_path = os.path.join(ROOT, "profiles", "ncu_summary_latest.json")
+        summ_all = json.load(open(summ_path))
+        summ = summ_all["kernels"]
+        stamp_now = spbuild._stamp()
         gk = [v for k, v in summ.items() if "gemm_tc" in k and "zero" not in k]
         if gk and dt == "bf16" and args.workload == "c3":
-            traffic = sum(v["dram_bytes_per_launch"] * v["launches"] for v in gk) / sum(v["launches"] for v in gk)
-    except Exception:
-        traffic = None
+            if summ_all.get("lib_stamp") == stamp_now:
+                traffic = sum(v["dram_bytes_per_launch"] * v["launches"] for v in gk) / sum(v["launches"] for v in gk)
+                traffic_src = {"file": "profiles/ncu_summary_latest.json", "lib_stamp": stamp_now[:16], "capture": summ_all.get("capture")}
+            else:
+                traffic_src = {"file": "profiles/ncu_summary_latest.json", "stale": True, "lib_stamp_file": str(summ_all.get("lib_stamp"))[:16],
+                               "lib_stamp_loaded": stamp_now[:16]}
+    except Exception as ex:
+        traffic_src = {"error": f"{type(ex).__name__}: {ex}"}
+    # Denominator: the timed region is K short steps.  When the SM clock sat at (or near) its maximum during it, the burst
+    # cuBLAS figure is the peak that applies; when the region ran power-limited, the sustained one.
+    sm, smx = clocks.get("sm_mhz"), clocks.get("sm_max_mhz")
+    at_burst_clock = bool(sm and smx and sm >= 0.93 * smx)
+    peak_kind = "burst" if at_burst_clock else "sustained"
     roof = {"bound": "tensor", "kernel": "gemm_tc kernels (tcgen05, all 6 GEMM stages of a step)" if dt == "bf16" else "gemm_simt_kernel (fp32 FFMA)",
-            "achieved": (f_gemm / 1e12) / (gemm_ms * 1e-3) if gemm_ms > 0 else None, "peak": pk["sustained"], "unit": "TFLOP/s",
-            "frac": None, "traffic": traffic, "traffic_unit": "DRAM bytes per GEMM launch (ncu, profiles/ncu_summary_latest.json)",
+            "achieved": (f_gemm / 1e12) / (gemm_ms * 1e-3) if gemm_ms > 0 else None, "peak": pk[peak_kind], "unit": "TFLOP/s",
+            "frac": None, "traffic": traffic, "traffic_unit": "DRAM bytes per GEMM launch (ncu --set full)", "traffic_source": traffic_src,
             "algorithmic_bytes_per_launch": gemm_bytes / n_gemm,
-            "peak_kind": "sustained bf16 cuBLAS, " + pk["source"], "peak_burst": pk["burst"],
+            "peak_kind": f"{peak_kind} bf16 cuBLAS ({pk['source']}); chosen because the SM clock median in the timed region was "
+                         f"{sm} of {smx} MHz", "peak_burst": pk["burst"], "peak_sustained": pk["sustained"],
             "flops_per_launch": f_gemm / n_gemm, "avg_launch_ms": gemm_ms / n_gemm, "share_of_step": gemm_ms / ms_step if ms_step else None}
     if roof["achieved"]:
         roof["frac"] = roof["achieved"] / roof["peak"]
-        # the GEMM stages alternate with memory-bound kernels inside the step, so they run above the all-GEMM sustained figure;
-        # against the burst figure (a kernel timed alone) the same throughput reads:
-        roof["frac_of_burst"] = roof["achieved"] / pk["burst"] if pk.get("burst") else None
+        roof["frac_of_burst"] = roof["achieved"] / pk["burst"]
+        roof["frac_of_sustained"] = roof["achieved"] / pk["sustained"]
         roof["frac_of_nominal_2250"] = roof["achieved"] / 2250.0 if dt == "bf16" else None
-    whole = {"tflops": total_flops * world / 1e12 / (ms_step * 1e-3), "frac_of_sustained_peak_per_gpu": total_flops / 1e12 / (ms_step * 1e-3) / pk["sustained"],
-             "frac_of_burst_peak_per_gpu": total_flops / 1e12 / (ms_step * 1e-3) / pk["burst"]}
+    block_tf = total_flops / 1e12 / (ms_step * 1e-3)
+    whole = {"tflops": block_tf * world, "tflops_per_gpu": block_tf, "frac_of_sustained_peak_per_gpu": block_tf / pk["sustained"],
+             "frac_of_burst_peak_per_gpu": block_tf / pk["burst"], "flops_per_step_per_gpu": total_flops}
+    # per-stage achieved rates, so the table in VERDICT/BASELINE falls out of the line without a calculator
+    f_a = 4.0 * B * Hq * T * T * hd * ((T + 1) / (2.0 * T) if cfg.causal else 1.0)
+    stage_rates = {}
+    for nm, fl in (("flash_fwd", f_a), ("flash_bwd", 2.5 * f_a)):
+        if stage_ms.get(nm):
+            tf = fl / 1e12 / (stage_ms[nm] * 1e-3)
+            stage_rates[nm] = {"tflops": tf, "frac_of_burst": tf / pk["burst"]}
+    for nm, byts in (("norm_fwd", 2.0 * N * Cm * e_), ("norm_bwd", 3.0 * N * Cm * e_)):
+        if stage_ms.get(nm) and cfg.norm_kind != 0:
+            gbs = byts / 1e9 / (stage_ms[nm] * 1e-3)
+            stage_rates[nm] = {"gbs": gbs, "frac_of_hbm": gbs / pk["hbm"]}
+    if sustained is not None:
+        sus_tf = total_flops / 1e12 / (sustained["ms_per_step_second_half"] * 1e-3)
+        sustained["block_tflops_per_gpu_second_half"] = sus_tf
+        sustained["frac_of_sustained"] = sus_tf / pk["sustained"]
+        sustained["frac_of_burst"] = sus_tf / pk["burst"]
 
     out = {"metric": "attn_block_fwd_bwd_tokens_per_s", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": K, "warmup": W,
            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dt, "data": "synthetic",
            "config": {"workload": desc, "global_batch": B * world, "seq_len": T, "parallelism": f"dp{world}" if world > 1 else "single",
                       "l2": "per-step working set > 126 MB L2, no flush", "attn_impl": "auto", "residual": args.residual, "flops_per_step_per_gpu": total_flops},
            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "block_tflops": whole,
-           "stages_ms": {k: round(v, 4) for k, v in sorted(stage_ms.items())}}
+           "stages_ms": {k: round(v, 4) for k, v in sorted(stage_ms.items())}, "stage_rates": stage_rates, "sustained": sustained}
+
+    # ---- multi-rank correctness (untimed): one more step through the library's own all-reduce, then the LOCAL weight
+    # gradients are recomputed from the operands that step left in the workspace (dW = xhat^T . dqkv, dWo = attn_o^T . dy,
+    # dnorm from the norm VJP), summed over ranks by torch.distributed as the checker, and compared with what
+    # spb_block_bwd returned.  Both sides see the same operands, so the difference is fp32 summation order only.
+    if world > 1:
+        out["dp_check"] = dp_check(torch, dist, blk, cfg, params, x, dy, grads, world)
 
     # ---- CPU baseline on rank 0 at N=1 only (bounded sample)
     unbind_cpus()  # the CPU baseline below uses every host core

@@ -129,6 +129,16 @@ class AttentionBlock:
         v = qkv[..., c.n_q + c.n_kv:].unflatten(-1, (c.Hkv, c.hd))
         return k, v
 
+    def residual_views(self):
+        """2-D views of what forward/backward left in the workspace (spb_ws_layout): the operands of the weight-gradient
+        GEMMs.  Used by bench.py's multi-rank check to recompute the LOCAL gradients after an all-reduced backward."""
+        c = self.cfg
+        N = c.B * c.T
+        lay = self.layout
+        return {"xhat": self._view(lay.xhat, (N, c.C), c.dtype), "stats": self._view(lay.stats, (N, 2), torch.float32),
+                "qkv": self._view(lay.qkv, (N, c.n_tot), c.dtype), "attn_o": self._view(lay.attn_o, (N, c.n_q), c.dtype),
+                "dqkv": self._view(lay.dqkv, (N, c.n_tot), c.dtype), "dxhat": self._view(lay.dxhat, (N, c.C), c.dtype)}
+
     def lse_view(self):
         c = self.cfg
         return self._view(self.layout.lse, (c.B, c.Hq, c.T), torch.float32)

@@ -53,6 +53,7 @@ def main():
     ap.add_argument("reports", nargs="+")
     ap.add_argument("-o", "--out", required=True)
     ap.add_argument("--note", default="")
+    ap.add_argument("--capture", default="", help="what was captured (command line / round tag); stored for bench.py's traffic_source")
     a = ap.parse_args()
     launches = []
     for rep in a.reports:
@@ -74,7 +75,13 @@ def main():
             k["dram_bytes_per_launch"] = k["dram_read"] + k["dram_write"]
             if k.get("duration"):
                 k["dram_gbs_under_ncu"] = k["dram_bytes_per_launch"] / k["duration"] / 1e9
-    json.dump({"note": a.note or "per-launch averages from ncu --set full (cold-cache, serialised launches)", "kernels": agg},
+    import os
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from solvingpapers_b200 import build as spbuild
+    # lib_stamp: hash of the library sources at summary time.  bench.py prints roofline.traffic only while the loaded
+    # library still has this stamp - run this script right after the capture, before touching csrc/.
+    json.dump({"note": a.note or "per-launch averages from ncu --set full (cold-cache, serialised launches)", "lib_stamp": spbuild._stamp(),
+               "capture": a.capture, "kernels": agg},
               open(a.out, "w"), indent=1, sort_keys=True)
     for name, k in sorted(agg.items(), key=lambda kv: -kv[1].get("duration", 0) * kv[1]["launches"]):
         print(f"{name[:60]:60s} n={k['launches']:2d} {k.get('duration', 0)*1e6:9.1f} us  dram {k.get('dram_bytes_per_launch', 0)/1e6:8.1f} MB  "
