@@ -17,10 +17,12 @@ Pinning status (see DESIGN.md "Oracle"):
              (cells c0,c1,c6,c7,c8; tests/golden/gemma_*.npz).
   * vit    : PINNED  against torch.nn.LayerNorm + torch.nn.MultiheadAttention as the
              notebook calls them (tests/golden/vit_*.npz).
-  * gpt    : parity UNPINNED - flax/jax are not installable here; the restatement
-             follows gpt/gpt-jax.ipynb:321-357 and flax's published LayerNorm /
-             Dense semantics and is cross-checked only against the ViT (torch MHA)
-             fixture where the math overlaps.
+  * gpt    : PINNED  against the notebook's own module cells (gpt/gpt-jax.ipynb c9
+             CausalSelfAttention, c10 MLP, c11 DecoderBlock) exec'd with jnp -> numpy and
+             nn -> a numpy stand-in for the flax.linen names they use; forward in fp32 and
+             fp64, gradients by finite differences of that source (tests/golden/gpt_*.npz).
+             flax itself is not installable: its Dense / LayerNorm / gelu semantics are what
+             the stand-in restates (third-party, version unpinned by the reference).
 """
 from .metrics import max_rel_err  # noqa: F401
 from . import llama_oracle, gpt_oracle, gemma_oracle, vit_oracle  # noqa: F401

@@ -1,12 +1,14 @@
 """Oracle (TEST INFRASTRUCTURE, never on the product path): torch-CPU restatement of
 the GPT pre-LN causal attention block of ``gpt/gpt-jax.ipynb``.
 
-Parity UNPINNED by the reference: flax/jax cannot be installed here (no network),
-the notebook stores no tensors, and flax's version is never printed.
-Third-party semantics restated from flax.linen's published behaviour:
+Pinned by tests/golden/gpt_*.npz: fixtures made by executing the notebook's own cells c9 (CausalSelfAttention),
+c10 (MLP) and c11 (DecoderBlock) with ``jnp`` bound to numpy and ``nn`` bound to a numpy stand-in for flax.linen
+(tests/golden/make_golden.py: flax/jax cannot be installed here).  What stays restated rather than executed is
+flax's own third-party arithmetic, from its published behaviour (version never printed by the notebook):
   * ``nn.LayerNorm()``: eps 1e-6, biased variance over the last axis, learnable
     scale (init ones) and bias (init zeros): (x-mean)*rsqrt(var+eps)*scale+bias.
   * ``nn.Dense(n, use_bias)``: x @ kernel[in,out] (+ bias).
+  * ``nn.gelu``: approximate=True (tanh form).
 """
 import math
 import numpy as np

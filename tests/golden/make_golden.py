@@ -22,6 +22,15 @@ What is executed:
             Gradients by torch autograd THROUGH THE NOTEBOOK'S MODULES.
   * vit   : ``nn.LayerNorm`` + ``nn.MultiheadAttention(E,H,batch_first=True)`` called
             exactly like ViT.ipynb:217-221; gradients by autograd.
+  * gpt   : the notebook's own module cells (gpt/gpt-jax.ipynb c9 CausalSelfAttention,
+            c10 MLP, c11 DecoderBlock) exec'd with ``jnp`` bound to numpy and ``nn``
+            bound to a small numpy stand-in for the flax.linen names the cells use
+            (Module with annotated fields + setup(), Dense, LayerNorm, Dropout, softmax,
+            gelu) - so the split order, head reshapes/transposes, /sqrt(head_dim),
+            ``where(mask == 0, -1e4, .)`` and the pre-LN residual structure that run are the
+            notebook's own lines; flax's third-party semantics (Dense = x @ kernel + bias,
+            LayerNorm eps 1e-6 / biased variance, gelu approximate=True) are what the
+            stand-in restates.  Gradients: finite differences of that source in fp64.
 """
 import json
 import math
@@ -345,6 +354,141 @@ def make_vit(tag, B, T, E, H, seed):
     print("vit", tag, "y", tuple(y.shape))
 
 
+# --------------------------------------------------------------------------- gpt
+def flax_standin(dtype):
+    """numpy stand-in for the handful of flax.linen names gpt/gpt-jax.ipynb cells c9-c11 use.  Parameters are plain
+    attributes (``kernel``, ``bias``, ``scale``) set by the caller after construction."""
+    nn = types.ModuleType("flax_linen_standin")
+
+    class Module:
+        def __init__(self, *args, **kw):
+            fields = list(getattr(type(self), "__annotations__", {}))
+            for name, val in zip(fields, args):
+                setattr(self, name, val)
+            for name, val in kw.items():
+                setattr(self, name, val)
+            self.setup()
+
+        def setup(self):
+            pass
+
+    class Dense(Module):  # flax.linen.Dense: y = x @ kernel[in, out] (+ bias), use_bias defaults to True
+        def __init__(self, features, use_bias=True):
+            self.features, self.use_bias, self.kernel, self.bias = features, use_bias, None, None
+
+        def __call__(self, x):
+            assert self.kernel.shape[-1] == self.features
+            y = np.matmul(x, self.kernel)
+            return y + self.bias if self.use_bias else y
+
+    class LayerNorm(Module):  # flax.linen.LayerNorm defaults: epsilon 1e-6, biased variance over the last axis, scale + bias
+        def __init__(self, epsilon=1e-6):
+            self.epsilon, self.scale, self.bias = epsilon, None, None
+
+        def __call__(self, x):
+            mean = np.mean(x, axis=-1, keepdims=True)
+            var = np.mean(np.square(x), axis=-1, keepdims=True) - np.square(mean)  # flax: E[x^2] - E[x]^2 (use_fast_variance)
+            var = np.maximum(var, 0.0)
+            return ((x - mean) * (1.0 / np.sqrt(var + self.epsilon)) * self.scale + self.bias).astype(dtype)
+
+    class Dropout(Module):
+        def __init__(self, rate):
+            self.rate = rate
+
+        def __call__(self, x, deterministic=True):
+            assert deterministic, "dropout has no reproducible RNG stream here; the bench/parity path is deterministic=True"
+            return x
+
+    def gelu(x, approximate=True):  # flax.linen.gelu default approximate=True (tanh form)
+        assert approximate
+        return 0.5 * x * (1.0 + np.tanh(math.sqrt(2.0 / math.pi) * (x + 0.044715 * x ** 3)))
+
+    nn.Module, nn.Dense, nn.LayerNorm, nn.Dropout, nn.softmax, nn.gelu = Module, Dense, LayerNorm, Dropout, _softmax, gelu
+    return nn
+
+
+def gpt_namespace(dtype):
+    jnp = types.ModuleType("jnp_as_numpy")
+    for name in dir(np):
+        if not name.startswith("__"):
+            setattr(jnp, name, getattr(np, name))
+    # jax: jnp.sqrt of a Python int is a (weakly typed) float32 scalar, so `x / jnp.sqrt(head_dim)` keeps x's dtype; numpy's
+    # np.float64 scalar would promote an fp32 x to fp64
+    jnp.sqrt = lambda v: dtype(np.sqrt(v)) if isinstance(v, (int, float)) else np.sqrt(v)
+    ns = {"jnp": jnp, "nn": flax_standin(dtype), "np": np}
+    for c in (9, 10, 11):
+        exec(cell_src("gpt/gpt-jax.ipynb", c), ns)
+    return ns
+
+
+def make_gpt(tag, B, T, C, H, seed):
+    """Fixtures for a11 (CausalSelfAttention behind ln1, with and without the DecoderBlock residual) and the GELU-MLP third
+    of f2 (MLP behind ln2 + residual), from the notebook's own DecoderBlock.__call__ lines (gpt/gpt-jax.ipynb:419-422)."""
+    rng = np.random.default_rng(seed)
+    f32 = np.float32
+    x = rng.standard_normal((B, T, C)).astype(f32)
+    dy = rng.standard_normal((B, T, C)).astype(f32)
+    p = {"ln1_scale": (1.0 + 0.3 * rng.standard_normal(C)).astype(f32), "ln1_bias": (0.3 * rng.standard_normal(C)).astype(f32),
+         "qkv_kernel": (rng.standard_normal((C, 3 * C)) / math.sqrt(C)).astype(f32),
+         "proj_kernel": (rng.standard_normal((C, C)) / math.sqrt(C)).astype(f32), "proj_bias": (0.5 * rng.standard_normal(C)).astype(f32),
+         "ln2_scale": (1.0 + 0.3 * rng.standard_normal(C)).astype(f32), "ln2_bias": (0.3 * rng.standard_normal(C)).astype(f32),
+         "fc1_kernel": (rng.standard_normal((C, 4 * C)) / math.sqrt(C)).astype(f32), "fc1_bias": (0.1 * rng.standard_normal(4 * C)).astype(f32),
+         "fc2_kernel": (rng.standard_normal((4 * C, C)) / math.sqrt(4 * C)).astype(f32), "fc2_bias": (0.1 * rng.standard_normal(C)).astype(f32)}
+
+    def build(dtype, pp):
+        ns = gpt_namespace(dtype)
+        blk = ns["DecoderBlock"](C, H, 0.1)
+        blk.ln1.scale, blk.ln1.bias = pp["ln1_scale"], pp["ln1_bias"]
+        blk.attn.qkv.kernel = pp["qkv_kernel"]
+        blk.attn.proj.kernel, blk.attn.proj.bias = pp["proj_kernel"], pp["proj_bias"]
+        blk.ln2.scale, blk.ln2.bias = pp["ln2_scale"], pp["ln2_bias"]
+        blk.mlp.fc1.kernel, blk.mlp.fc1.bias = pp["fc1_kernel"], pp["fc1_bias"]
+        blk.mlp.fc2.kernel, blk.mlp.fc2.bias = pp["fc2_kernel"], pp["fc2_bias"]
+        return blk
+
+    def run(blk, x_):
+        attn = blk.attn(blk.ln1(x_), deterministic=True)          # the call inside gpt:420
+        mlp = blk.mlp(blk.ln2(x_), deterministic=True)            # the call inside gpt:421 (on the same x_, stand-alone)
+        full = blk(x_, deterministic=True)                        # gpt:419-422 both halves chained
+        return attn, mlp, full
+
+    attn32, mlp32, full32 = run(build(f32, p), x)
+    assert attn32.dtype == np.float32 and mlp32.dtype == np.float32 and full32.dtype == np.float32, (attn32.dtype, mlp32.dtype, full32.dtype)
+    p64 = {k: v.astype(np.float64) for k, v in p.items()}
+    x64, dy64 = x.astype(np.float64), dy.astype(np.float64)
+    attn64, mlp64, full64 = run(build(np.float64, p64), x64)
+    out = dict(x=x, dy=dy, attn=attn32, mlp=mlp32, block=full32, attn64=attn64, mlp64=mlp64, block64=full64,
+               meta=np.array([B, T, C, H], dtype=np.int64), **p)
+    hstep = 1e-5
+    # directional derivatives of <attn(ln1(x)), dy>, <mlp(ln2(x)), dy> and <block(x), dy> in fp64
+    for which, idx, names in (("attn", 0, ("x", "ln1_scale", "ln1_bias", "qkv_kernel", "proj_kernel", "proj_bias")),
+                              ("mlp", 1, ("x", "ln2_scale", "ln2_bias", "fc1_kernel", "fc1_bias", "fc2_kernel", "fc2_bias")),
+                              ("block", 2, ("x", "qkv_kernel", "fc1_kernel"))):
+        def loss(x_, pp):
+            return float(np.sum(run(build(np.float64, pp), x_)[idx] * dy64))
+
+        for name in names:
+            base = x64 if name == "x" else p64[name]
+            dirs, vals = [], []
+            for _ in range(2):
+                u = rng.standard_normal(base.shape)
+                u /= np.linalg.norm(u)
+
+                def at(eps):
+                    if name == "x":
+                        return loss(x64 + eps * u, p64)
+                    pp = dict(p64)
+                    pp[name] = p64[name] + eps * u
+                    return loss(x64, pp)
+
+                vals.append((-at(2 * hstep) + 8 * at(hstep) - 8 * at(-hstep) + at(-2 * hstep)) / (12 * hstep))
+                dirs.append(u)
+            out[f"fd_dir_{which}_{name}"] = np.stack(dirs)
+            out[f"fd_val_{which}_{name}"] = np.array(vals)
+    np.savez_compressed(os.path.join(OUT, f"gpt_{tag}.npz"), **out)
+    print("gpt", tag, "attn", attn32.shape, "max|attn|", np.abs(attn32).max(), "max|block|", np.abs(full32).max())
+
+
 if __name__ == "__main__":
     if not os.path.isdir(REF):
         sys.exit("needs /root/reference (build container only)")
@@ -357,3 +501,5 @@ if __name__ == "__main__":
     make_gemma_geglu("small", B=2, T=12, D=32, seed=6)
     print("gemma MQA default param count", gemma_param_count_pin())
     make_vit("nb", B=3, T=17, E=64, H=4, seed=4)  # the notebook's literal shape
+    make_gpt("mha", B=2, T=12, C=32, H=2, seed=8)
+    make_gpt("one_head", B=1, T=16, C=32, H=1, seed=9)  # the notebook's own num_heads = 1 (gpt:296)

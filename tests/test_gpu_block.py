@@ -181,6 +181,35 @@ def test_gpt_block(dtype, B, T, C, H):
     _check(got, ref, dtype, tuple(got.keys()))
 
 
+@pytest.mark.parametrize("tag", ["mha", "one_head"])
+def test_gpt_block_fp32_against_golden_from_notebook_source(golden_dir, tag):
+    """a11 against fixtures made by exec'ing the notebook's own CausalSelfAttention / DecoderBlock cells (gpt c9, c11):
+    y = attn(ln1(x)) and x + attn(ln1(x)) (gpt:420) in fp32 mode, gradients against fp64 finite differences of that source."""
+    sp, L = _sp()
+    g = dict(np.load(os.path.join(golden_dir, f"gpt_{tag}.npz")))
+    B, Tn, C, H = (int(v) for v in g["meta"])
+    for residual in (False, True):
+        cfg = sp.BlockConfig(B=B, T=Tn, C=C, Hq=H, Hkv=H, hd=C // H, dtype=torch.float32, norm_kind=L.NORM_LAYER, norm_eps=1e-6,
+                             rope=False, causal=True, weight_layout=L.W_IN_OUT, out_bias=True, residual=residual)
+        blk = sp.AttentionBlock(cfg)
+        p = {"wqkv": T_(g["qkv_kernel"]).to(DEV), "wo": T_(g["proj_kernel"]).to(DEV), "bo": T_(g["proj_bias"]).to(DEV),
+             "norm_w": T_(g["ln1_scale"]).to(DEV), "norm_b": T_(g["ln1_bias"]).to(DEV)}
+        y = blk.forward(T_(g["x"]).to(DEV), p)
+        want = T_(g["attn64"]) + (T_(g["x"]).double() if residual else 0.0)
+        assert max_rel_err(y, want) < TOL_F32, residual
+        gr = blk.backward(T_(g["dy"]).to(DEV))
+        torch.cuda.synchronize()
+        names = {"x": "dx", "ln1_scale": "dnorm_w", "ln1_bias": "dnorm_b", "qkv_kernel": "dwqkv", "proj_kernel": "dwo", "proj_bias": "dbo"}
+        for name, gname in names.items():
+            grad = gr[gname].double().cpu().numpy()
+            for u, fd in zip(g["fd_dir_attn_" + name], g["fd_val_attn_" + name]):
+                an = float(np.sum(grad * u))
+                if residual and name == "x":
+                    an -= float(np.sum(g["dy"].astype(np.float64) * u))   # d(x + f(x)) = dy + f'(x)^T dy
+                scale = float(np.linalg.norm(grad))  # directional derivative of a unit direction: compare on the gradient's scale
+                assert abs(an - fd) <= TOL_F32 * max(scale, abs(fd)), (name, an, fd, residual)
+
+
 # ------------------------------------------------------------------------------------------------ Gemma (C4 literal shape, small)
 def test_gemma_block_fp32_against_golden_from_notebook_modules(golden_dir):
     sp, L = _sp()

@@ -218,3 +218,32 @@ def test_ffn_rejects_unknown_activation_and_bad_shapes():
     assert b"activation" in lib.spb_last_error()
     d = L.FfnDesc(0, 64, 256, L.F32, L.NORM_RMS, 1e-6, 0, 0, L.W_IN_OUT, 0, 0)
     assert lib.spb_ffn_ws_layout(C.byref(d), C.byref(ws)) == -1
+
+
+def test_gpt_mlp_fp32_against_golden_from_notebook_source(golden_dir):
+    """GELU-MLP third of f2 against fixtures from the notebook's own MLP / DecoderBlock cells (gpt c10, c11):
+    ``x + mlp(ln2(x))`` (gpt:421) through spb_ffn_fwd/bwd with the LayerNorm in front and the residual in the w2 epilogue."""
+    import os
+    import solvingpapers_b200 as sp
+    from solvingpapers_b200 import _lib as L
+    g = dict(np.load(os.path.join(golden_dir, "gpt_mha.npz")))
+    B, Tn, C, H = (int(v) for v in g["meta"])
+    T_ = torch.from_numpy
+    cfg = sp.FfnConfig(N=B * Tn, C=C, H=4 * C, dtype=torch.float32, norm_kind=L.NORM_LAYER, norm_eps=1e-6, act=L.ACT_GELU_TANH, residual=True)
+    ff = sp.FeedForward(cfg)
+    p = {"w1": T_(g["fc1_kernel"]).cuda(), "b1": T_(g["fc1_bias"]).cuda(), "w2": T_(g["fc2_kernel"]).cuda(), "b2": T_(g["fc2_bias"]).cuda(),
+         "norm_w": T_(g["ln2_scale"]).cuda(), "norm_b": T_(g["ln2_bias"]).cuda()}
+    x = T_(g["x"]).cuda().reshape(B * Tn, C)
+    y = ff.forward(x, p)
+    want = T_(g["mlp64"]) + T_(g["x"]).double()
+    assert max_rel_err(y.reshape(B, Tn, C), want) < TOL_F32
+    gr = ff.backward(T_(g["dy"]).cuda().reshape(B * Tn, C))
+    torch.cuda.synchronize()
+    names = {"x": "dx", "ln2_scale": "dnorm_w", "ln2_bias": "dnorm_b", "fc1_kernel": "dw1", "fc1_bias": "db1", "fc2_kernel": "dw2", "fc2_bias": "db2"}
+    for name, gname in names.items():
+        grad = gr[gname].double().cpu().numpy().reshape(g["fd_dir_mlp_" + name][0].shape)
+        for u, fd in zip(g["fd_dir_mlp_" + name], g["fd_val_mlp_" + name]):
+            an = float(np.sum(grad * u))
+            if name == "x":
+                an -= float(np.sum(g["dy"].astype(np.float64) * u))
+            assert abs(an - fd) <= TOL_F32 * max(float(np.linalg.norm(grad)), abs(fd)), (name, an, fd)

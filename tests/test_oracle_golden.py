@@ -117,6 +117,47 @@ def test_gemma_geglu_matches_notebook_module(golden_dir):
         assert max_rel_err(r[k], T(g[ref])) < 5e-6, k
 
 
+@pytest.mark.parametrize("tag", ["mha", "one_head"])
+def test_gpt_matches_literal_notebook_source(golden_dir, tag):
+    """a11 + the GELU-MLP third of f2: gpt_oracle against the notebook's own CausalSelfAttention / MLP / DecoderBlock cells
+    (gpt/gpt-jax.ipynb c9-c11, exec'd over a numpy stand-in for flax.linen by tests/golden/make_golden.py): fp32 and fp64
+    forward values, and fp64 directional derivatives by finite differences of that source."""
+    g = _load(golden_dir, f"gpt_{tag}.npz")
+    B, Tn, C, H = (int(v) for v in g["meta"])
+    for dt, sfx, tol in ((torch.float32, "", 3e-6), (torch.float64, "64", 1e-12)):
+        x = T(g["x"]).to(dt)
+        pa = {"qkv_kernel": T(g["qkv_kernel"]).to(dt), "proj_kernel": T(g["proj_kernel"]).to(dt), "proj_bias": T(g["proj_bias"]).to(dt),
+              "ln_scale": T(g["ln1_scale"]).to(dt), "ln_bias": T(g["ln1_bias"]).to(dt)}
+        pm = {k: T(g[k]).to(dt) for k in ("fc1_kernel", "fc1_bias", "fc2_kernel", "fc2_bias")}
+        attn = gpt_oracle.attention_block(pa, x, H)
+        assert max_rel_err(attn, T(g["attn" + sfx])) < tol
+        mlp = gpt_oracle.mlp(pm, gpt_oracle.layer_norm(x, T(g["ln2_scale"]).to(dt), T(g["ln2_bias"]).to(dt)))
+        assert max_rel_err(mlp, T(g["mlp" + sfx])) < tol
+        h = x + attn                                                                             # gpt:420
+        full = h + gpt_oracle.mlp(pm, gpt_oracle.layer_norm(h, T(g["ln2_scale"]).to(dt), T(g["ln2_bias"]).to(dt)))  # gpt:421
+        assert max_rel_err(full, T(g["block" + sfx])) < tol
+    # gradients (fp64): autograd of the restatement vs finite differences of the notebook source
+    dy = T(g["dy"]).double()
+    pa64 = {"qkv_kernel": T(g["qkv_kernel"]), "proj_kernel": T(g["proj_kernel"]), "proj_bias": T(g["proj_bias"]),
+            "ln_scale": T(g["ln1_scale"]), "ln_bias": T(g["ln1_bias"])}
+    r = gpt_oracle.block_fwd_bwd(pa64, T(g["x"]), dy, H, dtype=torch.float64)
+    names = {"x": "dx", "ln1_scale": "dln_scale", "ln1_bias": "dln_bias", "qkv_kernel": "dqkv_kernel", "proj_kernel": "dproj_kernel",
+             "proj_bias": "dproj_bias"}
+    for name, gname in names.items():
+        for u, fd in zip(g["fd_dir_attn_" + name], g["fd_val_attn_" + name]):
+            an = float(np.sum(r[gname].numpy() * u))
+            assert abs(an - fd) <= 2e-6 * max(1.0, abs(fd)) + 1e-7, (name, an, fd)
+    # MLP behind ln2: leaves = x, ln2 params, fc weights
+    leaves = {k: T(g[k]).double().requires_grad_(True) for k in ("x", "ln2_scale", "ln2_bias", "fc1_kernel", "fc1_bias", "fc2_kernel", "fc2_bias")}
+    y = gpt_oracle.mlp({k: leaves[k] for k in ("fc1_kernel", "fc1_bias", "fc2_kernel", "fc2_bias")},
+                       gpt_oracle.layer_norm(leaves["x"], leaves["ln2_scale"], leaves["ln2_bias"]))
+    y.backward(dy)
+    for name, t in leaves.items():
+        for u, fd in zip(g["fd_dir_mlp_" + name], g["fd_val_mlp_" + name]):
+            an = float(np.sum(t.grad.numpy() * u))
+            assert abs(an - fd) <= 2e-6 * max(1.0, abs(fd)) + 1e-7, (name, an, fd)
+
+
 def test_gpt_mlp_restatement_finite_differences():
     """The flax MLP (gpt:376-389) cannot run here (no jax/flax): the restatement's backward is checked by fp64 central differences
     and its tanh-GELU against the closed form flax documents for approximate=True."""
