@@ -79,10 +79,10 @@ def test_nll_with_vocabulary_masked_logits(dtype):
     tg = torch.from_numpy(rng.integers(0, 100, size=(N,)))
     tg[0] = 5000
     tg[2] = 1
-    ref_in = lg.float().requires_grad_(True)
+    ref_in = lg.float().clone().requires_grad_(True)
     ref = llama_oracle.nll_loss(ref_in, tg)
     ref.backward()
-    x = lg.cuda().requires_grad_(True)
+    x = lg.detach().cuda().requires_grad_(True)
     loss = spl.nll_loss(x, tg.cuda())
     loss.backward()
     torch.cuda.synchronize()
