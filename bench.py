@@ -44,12 +44,20 @@ WORKLOADS = {
 }
 
 
+# decode workloads: name -> (B, Tk cache length incl. the new token, C, Hq, Hkv, hd, dtype, description)
+DECODE_WORKLOADS = {
+    "c3dec": (4, 2048, 4096, 32, 8, 128, "bf16", "C3-decode: one new token per sequence, Llama-3-8B-shaped block d4096 32Q/8KVx128, 2047-token KV cache, B=4, bf16"),
+    "c3dec32": (32, 2048, 4096, 32, 8, 128, "bf16", "C3-decode B=32: as c3dec with 32 sequences (cache-read bound instead of weight-read bound)"),
+    "c1dec": (16, 128, 256, 4, 2, 64, "f32", "C1-decode: llama notebook dims d256 4Q/2KVx64, 127-token cache, B=16, fp32 (what `generate` would run with the cache)"),
+}
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS) + sorted(DECODE_WORKLOADS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -659,6 +667,148 @@ def run_ours(args):
     return 0
 
 
+def run_decode(args):
+    """KV-cache decode step: spb_block_decode = RMSNorm -> q|k|v projections -> rotary at `position` ->
+    in-place cache append -> attention over the cache -> output projection (+x).  HBM-bound: algorithmic bytes per step =
+    every weight once + the K and V caches once (+ O(B*C) activations)."""
+    import torch
+    import solvingpapers_b200 as sp
+    from solvingpapers_b200 import _lib as L, ops
+    if args.gpus != 1:
+        raise SystemExit("decode workloads are single-GPU bench lines (sequences are independent: replicas only)")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (B200); there is no CPU fallback for the product path")
+    B, Tk, Cm, Hq, Hkv, hd, dt, desc = DECODE_WORKLOADS[args.workload]
+    dtype = torch.bfloat16 if dt == "bf16" else torch.float32
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    lib = L.load()
+    gen = torch.Generator(device=dev).manual_seed(7)
+    n = lambda *shape, scale=1.0: (torch.randn(*shape, generator=gen, device=dev, dtype=torch.float32) * scale).to(dtype)
+    nq, nkv = Hq * hd, Hkv * hd
+    ntot = nq + 2 * nkv
+    cfg = sp.BlockConfig(B, 1, Cm, Hq, Hkv, hd, dtype=dtype, norm_kind=L.NORM_RMS, rope=True, causal=False, residual=True)
+    j = torch.arange(0, hd // 2, dtype=torch.float32)
+    ang = torch.outer(torch.arange(Tk, dtype=torch.float32), 1.0 / (10000.0 ** (j / hd)))
+    rope = sp.llama_rope_table(torch.cos(ang), torch.sin(ang)).to(dev)
+    e = 2 if dt == "bf16" else 4
+    w_bytes = (Cm * ntot + nq * Cm) * e
+    kv_bytes = 2 * B * Tk * nkv * e
+    act_bytes = B * (2 * Cm + ntot + nq) * e * 2
+    step_bytes = w_bytes + kv_bytes + act_bytes
+    # rotating copies so that no step finds its weights or cache in the 126 MB L2
+    ncopy = max(2, int(math.ceil(400e6 / (w_bytes + kv_bytes))) + 1)
+    ncopy = min(ncopy, 64)
+    sets = []
+    for _ in range(ncopy):
+        p = {"wqkv": n(Cm, ntot, scale=1 / math.sqrt(Cm)), "wo": n(nq, Cm, scale=1 / math.sqrt(nq)), "norm_w": n(Cm), "rope": rope}
+        cache = sp.KVCache(B, Tk, Hkv, hd, dtype=dtype, device=dev)
+        cache.kbuf.copy_(n(B, Tk, Hkv, hd))
+        cache.vbuf.copy_(n(B, Tk, Hkv, hd))
+        sets.append((p, cache))
+    dec = sp.DecodeBlock(cfg, Tk, device=dev)
+    x = n(B, 1, Cm)
+    it = [0]
+
+    def step(xin=x):
+        p, cache = sets[it[0] % ncopy]
+        it[0] += 1
+        cache.length = Tk - 1          # every step appends token Tk-1 and attends to Tk keys
+        return dec.step(xin, p, cache)
+
+    K, W = args.steps, max(args.warmup, 3)
+    for _ in range(W):
+        step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0)
+    sampler.start()
+    time.sleep(0.25)
+    l0 = lib.spb_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    launches = lib.spb_launch_count() - l0
+    ms_step = e0.elapsed_time(e1) / K
+    clocks = sampler.stop()
+    # the attention kernel alone (K, V read once), same rotation
+    q = n(B, 1, Hq, hd)
+    for i in range(3):
+        ops.attn_decode(q, sets[i % ncopy][1].kbuf, sets[i % ncopy][1].vbuf, Tk, 1 / math.sqrt(hd))
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0.record()
+    for i in range(K):
+        ops.attn_decode(q, sets[i % ncopy][1].kbuf, sets[i % ncopy][1].vbuf, Tk, 1 / math.sqrt(hd))
+    a1.record()
+    torch.cuda.synchronize()
+    ms_attn = a0.elapsed_time(a1) / K
+    # e2e: host x in, y out every step
+    xh = x.cpu().pin_memory()
+    yh = torch.empty_like(xh).pin_memory()
+    xd = torch.empty_like(x)
+    for _ in range(3):
+        xd.copy_(xh, non_blocking=True)
+        yh.copy_(step(xd), non_blocking=True)
+    torch.cuda.synchronize()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for _ in range(K):
+        xd.copy_(xh, non_blocking=True)
+        yh.copy_(step(xd), non_blocking=True)
+    f1.record()
+    torch.cuda.synchronize()
+    ms_e2e = f0.elapsed_time(f1) / K
+    pk = peaks()
+    ach = step_bytes / 1e9 / (ms_step * 1e-3)
+    out = {"metric": "attn_block_decode_tokens_per_s", "value": B / (ms_step * 1e-3), "unit": "tokens/s", "n_gpus": 1, "steps": K, "warmup": W,
+           "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dt, "data": "synthetic",
+           "config": {"workload": desc, "global_batch": B, "cache_len": Tk, "parallelism": "single",
+                      "l2": f"{ncopy} rotating copies of weights + KV cache ({ncopy * (w_bytes + kv_bytes) / 1e6:.0f} MB) so no step hits the 126 MB L2"},
+           "clocks": clocks,
+           "e2e": {"value": B / (ms_e2e * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": x.numel() * e, "d2h_bytes_per_step": x.numel() * e,
+                   "ms_per_step": ms_e2e, "what": "pinned host x -> device, spb_block_decode via DecodeBlock.step, y -> pinned host, every step"},
+           "gpu_launches": int(launches),
+           "roofline": {"bound": "hbm", "kernel": "whole decode step: small_m_gemm_kernel (weights) + attn_decode_kernel (K, V cache) + small kernels",
+                        "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"], "traffic": None,
+                        "algorithmic_bytes_per_step": step_bytes, "weight_bytes": w_bytes, "kv_cache_bytes": kv_bytes,
+                        "peak_kind": "HBM copy bandwidth, " + pk["source"],
+                        "attn_decode_kernel": {"ms": ms_attn, "gbs": kv_bytes / 1e9 / (ms_attn * 1e-3), "frac": kv_bytes / 1e9 / (ms_attn * 1e-3) / pk["hbm"],
+                                               "note": "spb_attn_decode alone (decode + combine kernels), K and V read once"}}}
+    if not args.no_cpu_baseline:
+        try:
+            import numpy as np
+            from oracle import llama_oracle
+            torch.set_num_threads(os.cpu_count() or 1)
+            rng = np.random.default_rng(0)
+            bp = llama_oracle.init_block_params(rng, Cm, Hq, Hkv)
+            xc = torch.from_numpy(rng.standard_normal((B, 1, Cm)).astype(np.float32))
+            ck = torch.from_numpy(rng.standard_normal((B, Tk - 1, Hkv, hd)).astype(np.float32))
+            cv = torch.from_numpy(rng.standard_normal((B, Tk - 1, Hkv, hd)).astype(np.float32))
+            fc = llama_oracle.precompute_freqs_cis(hd, Tk)
+            fn = lambda: llama_oracle.attention(bp["attention"], llama_oracle.rms_norm(xc, bp["attention_norm"]), None, fc, Hq, Hkv, cache=(ck, cv),
+                                                position=Tk - 1)
+            with torch.no_grad():
+                fn()
+                t0 = time.perf_counter()
+                done = 0
+                while done < 20 and time.perf_counter() - t0 < 15.0:
+                    fn()
+                    done += 1
+                dtc = time.perf_counter() - t0
+            out["cpu_baseline"] = {"value": B * done / dtc, "unit": "tokens/s", "cores": torch.get_num_threads(), "kind": "port",
+                                   "sample": f"{done} decode steps of the oracle's cache branch (llama3:815-829), B={B}, {Tk - 1}-token cache, fp32 torch CPU"}
+        except Exception as ex:
+            out["cpu_baseline"] = {"value": None, "unit": "tokens/s", "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {ex}"}
+    print(json.dumps(out), flush=True)
+    return 0
+
+
 if __name__ == "__main__":
     a = parse()
+    if a.workload in DECODE_WORKLOADS:
+        if a.impl == "reference":
+            raise SystemExit("--impl reference covers the training workloads; the decode line carries its own cpu_baseline")
+        sys.exit(run_decode(a))
     sys.exit(run_reference(a) if a.impl == "reference" else run_ours(a))

@@ -281,6 +281,37 @@ int spb_nll_fwd(int dtype, const void* logits, int64_t ld, const int64_t* target
 int spb_nll_bwd(int dtype, const void* logits, int64_t ld, const int64_t* targets, int64_t N, int32_t V, const float* lse,
                 float dloss, void* dlogits, int64_t ldd, spb_stream_t stream);
 
+/* ---- KV-cache decode ----------------------------------------------------------- */
+/* llama3:815-829 with cache != None: Tq new query rows per sequence (already rotated) against Tk cached keys/values
+ * (the new tokens' own k, v included: the caller - or spb_block_decode - appended them first).  No mask: every query row
+ * sees all Tk keys, which is what the notebook computes for the shapes its cache branch accepts (Tq = 1, or mask=None).
+ * q [B*Tq, ldq], head h at column h*hd; caches: token j of batch b at b*batch_stride + j*ld (elements), kv head g at
+ * column g*hd; o [B*Tq, ldo]; lse [B, Hq, Tq] fp32 or NULL; scratch = spb_attn_decode_scratch_bytes(...) bytes.
+ * fp32 or bf16, hd in {64, 128, 256}.  Bound by HBM bandwidth: reads the K and V caches once.                          */
+size_t spb_attn_decode_scratch_bytes(int32_t B, int32_t Tq, int32_t Hq, int32_t Hkv, int32_t hd, int32_t Tk);
+int spb_attn_decode(int dtype, int32_t B, int32_t Tq, int32_t Hq, int32_t Hkv, int32_t hd, int32_t Tk, float scale, const void* q,
+                    int64_t ldq, const void* k_cache, int64_t ldk, int64_t k_batch_stride, const void* v_cache, int64_t ldv,
+                    int64_t v_batch_stride, void* o, int64_t ldo, float* lse, void* scratch, spb_stream_t stream);
+
+/* One decode step of the block: attention(params, norm(x), mask, freqs_cis, n_heads, n_kv_heads, cache=(k_cache, v_cache),
+ * position=cache_len) of llama3:809-829 for x [B, Tq, C] with d->T = Tq.  The new tokens' k (rotated at positions
+ * cache_len .. cache_len+Tq-1) and v are APPENDED IN PLACE into the caches [B, Tmax, Hkv, hd] (the notebook's
+ * jnp.concatenate, :817-818, without copying the old rows); afterwards the caches hold cache_len + Tq valid rows.
+ * p->rope must cover positions [0, cache_len + Tq).  d->causal with Tq > 1 is SPB_E_UNSUPPORTED (the notebook's own code
+ * cannot express it: its mask slice does not broadcast against [.., Tq, Tk]).  SPB_W_IN_OUT weights; M = B*Tq <= 64.
+ * Workspace offsets: spb_block_decode_ws_layout (Tmax bounds the attention scratch).                                   */
+typedef struct spb_decode_ws {
+  size_t total;
+  size_t xhat;       /* [M, C] dtype                                */
+  size_t qkv;        /* [M, (Hq+2Hkv)*hd] dtype, q rotated          */
+  size_t attn_o;     /* [M, Hq*hd] dtype                            */
+  size_t gemm_part;  /* fp32 K-split partial sums of the projections */
+  size_t attn_part;  /* fp32 partial (O, m, l) of the key splits    */
+} spb_decode_ws;
+int spb_block_decode_ws_layout(const spb_block_desc* d, int32_t Tmax, spb_decode_ws* out);
+int spb_block_decode(const spb_block_desc* d, const spb_block_params* p, const void* x, void* k_cache, void* v_cache,
+                     int32_t cache_len, int32_t Tmax, void* y, void* ws, spb_stream_t stream);
+
 /* ---- data parallelism: batch-sharded, weight gradients all-reduced (no reference precedent) ---- */
 int spb_comm_unique_id(void* out128);                        /* HOST buffer, 128 bytes (ncclUniqueId)      */
 int spb_comm_init_rank(const void* id128, int nranks, int rank, void** comm_out);

@@ -3,7 +3,7 @@
 Product code only: hand-written CUDA in csrc/ behind the C ABI of include/spb200.h, plus thin host-side mirrors of
 the reference's functions (llama, gpt, gemma, vit).  No CPU fallback, no oracle import."""
 from . import _lib  # noqa: F401
-from .block import AttentionBlock, BlockConfig, llama_rope_table, gemma_rope_table  # noqa: F401
+from .block import AttentionBlock, BlockConfig, DecodeBlock, KVCache, llama_rope_table, gemma_rope_table  # noqa: F401
 from .ffn import FeedForward, FfnConfig  # noqa: F401
 
-__all__ = ["AttentionBlock", "BlockConfig", "FeedForward", "FfnConfig", "llama_rope_table", "gemma_rope_table"]
+__all__ = ["AttentionBlock", "BlockConfig", "DecodeBlock", "KVCache", "FeedForward", "FfnConfig", "llama_rope_table", "gemma_rope_table"]

@@ -60,6 +60,10 @@ class FfnWs(C.Structure):
                 ("partial", sz), ("partial_bytes", sz)]
 
 
+class DecodeWs(C.Structure):
+    _fields_ = [("total", sz), ("xhat", sz), ("qkv", sz), ("attn_o", sz), ("gemm_part", sz), ("attn_part", sz)]
+
+
 ACT_SWIGLU, ACT_GEGLU, ACT_GELU_TANH = 0, 1, 2
 
 # name -> (restype, argtypes); every symbol include/spb200.h declares
@@ -91,6 +95,10 @@ SIGNATURES = {
     "spb_ffn_bwd": (C.c_int, [C.POINTER(FfnDesc), C.POINTER(FfnParams), vp, vp, vp, C.POINTER(FfnGrads), vp, vp]),
     "spb_nll_fwd": (C.c_int, [C.c_int, vp, i64, vp, i64, i32, vp, vp, vp, vp]),
     "spb_nll_bwd": (C.c_int, [C.c_int, vp, i64, vp, i64, i32, vp, f32, vp, i64, vp]),
+    "spb_attn_decode_scratch_bytes": (sz, [i32, i32, i32, i32, i32, i32]),
+    "spb_attn_decode": (C.c_int, [C.c_int, i32, i32, i32, i32, i32, i32, f32, vp, i64, vp, i64, i64, vp, i64, i64, vp, i64, vp, vp, vp]),
+    "spb_block_decode_ws_layout": (C.c_int, [C.POINTER(BlockDesc), i32, C.POINTER(DecodeWs)]),
+    "spb_block_decode": (C.c_int, [C.POINTER(BlockDesc), C.POINTER(BlockParams), vp, vp, vp, i32, i32, vp, vp, vp]),
     "spb_comm_unique_id": (C.c_int, [vp]),
     "spb_comm_init_rank": (C.c_int, [vp, C.c_int, C.c_int, C.POINTER(vp)]),
     "spb_comm_allreduce_f32": (C.c_int, [vp, C.POINTER(vp), C.POINTER(sz), C.c_int, vp]),

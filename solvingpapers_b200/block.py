@@ -144,7 +144,7 @@ class AttentionBlock:
         return self._view(self.layout.lse, (c.B, c.Hq, c.T), torch.float32)
 
     # ---- params ----------------------------------------------------------------------------------------
-    def _params(self, p):
+    def _params(self, p, check_rope=True):
         c = self.cfg
         P = L.BlockParams()
         keep = []
@@ -189,7 +189,7 @@ class AttentionBlock:
                 P.norm_b = _ptr(chk(p["norm_b"], "norm_b"))
         if c.rope:
             r = p["rope"]
-            if r.dtype != torch.float32 or tuple(r.shape) != (c.T, c.hd // 2, 4) or not r.is_contiguous():
+            if check_rope and (r.dtype != torch.float32 or tuple(r.shape) != (c.T, c.hd // 2, 4) or not r.is_contiguous()):
                 raise L.SpbError(f"rope table must be contiguous fp32 [T, hd/2, 4], got {tuple(r.shape)} {r.dtype}")
             keep.append(r)
             P.rope = _ptr(r)
@@ -265,3 +265,75 @@ class AttentionBlock:
         L.check(self.lib.spb_block_bwd(C.byref(self.d), C.byref(P), _ptr(x), _ptr(dy), _ptr(self.ws), C.byref(G), comm,
                                        _stream()), "spb_block_bwd")
         return g
+
+
+class KVCache:
+    """Preallocated key/value cache [B, Tmax, Hkv, hd] that spb_block_decode appends to in place - the O(1)-per-token form of
+    the notebook's ``cache`` tuple, whose ``jnp.concatenate`` (llama3/LLaMA-jax.ipynb:817-818) copies every old row on every
+    step.  ``length`` rows are valid; ``k`` / ``v`` are views of them."""
+
+    def __init__(self, B, Tmax, Hkv, hd, dtype=torch.bfloat16, device="cuda"):
+        self.kbuf = torch.zeros((B, Tmax, Hkv, hd), dtype=dtype, device=device)
+        self.vbuf = torch.zeros((B, Tmax, Hkv, hd), dtype=dtype, device=device)
+        self.length = 0
+
+    @property
+    def capacity(self):
+        return self.kbuf.shape[1]
+
+    @property
+    def k(self):
+        return self.kbuf[:, :self.length]
+
+    @property
+    def v(self):
+        return self.vbuf[:, :self.length]
+
+    @classmethod
+    def from_tensors(cls, k, v, extra):
+        """A cache holding the rows of the notebook-style ``(k, v)`` tuple ([B, Tc, Hkv, hd]) with room for ``extra`` more."""
+        B, Tc, Hkv, hd = k.shape
+        c = cls(B, Tc + extra, Hkv, hd, dtype=k.dtype, device=k.device)
+        c.kbuf[:, :Tc].copy_(k)
+        c.vbuf[:, :Tc].copy_(v)
+        c.length = Tc
+        return c
+
+
+class DecodeBlock:
+    """One decode step of the block bound to fixed shapes (B sequences, Tq new tokens each, cache capacity Tmax):
+    spb_block_decode.  The config's T is Tq.  Weights are passed per call like AttentionBlock's."""
+
+    def __init__(self, cfg: BlockConfig, Tmax: int, device="cuda"):
+        if not torch.cuda.is_available():
+            raise L.SpbError("solvingpapers_b200 needs a CUDA device (B200, sm_100a); there is no CPU path")
+        self.cfg, self.Tmax = cfg, int(Tmax)
+        self.lib = L.load()
+        self.device = torch.device(device)
+        self.d = cfg.desc()
+        self.layout = L.DecodeWs()
+        L.check(self.lib.spb_block_decode_ws_layout(C.byref(self.d), self.Tmax, C.byref(self.layout)), "spb_block_decode_ws_layout")
+        self.ws = torch.empty(self.layout.total, dtype=torch.uint8, device=self.device)
+        self._marshal = AttentionBlock._params  # same parameter packing rules
+
+    def step(self, x, params, cache: KVCache):
+        c = self.cfg
+        if tuple(x.shape) != (c.B, c.T, c.C) or x.dtype != c.dtype or not x.is_contiguous():
+            raise L.SpbError(f"x must be contiguous {c.dtype} [{c.B},{c.T},{c.C}], got {tuple(x.shape)} {x.dtype}")
+        if cache.capacity != self.Tmax or cache.kbuf.dtype != c.dtype or tuple(cache.kbuf.shape) != (c.B, self.Tmax, c.Hkv, c.hd):
+            raise L.SpbError("cache does not match this DecodeBlock (shape / capacity / dtype)")
+        if c.rope:
+            need = cache.length + c.T
+            r = params["rope"]
+            if r.dtype != torch.float32 or r.dim() != 3 or r.shape[0] < need or tuple(r.shape[1:]) != (c.hd // 2, 4) or not r.is_contiguous():
+                raise L.SpbError(f"rope table must be contiguous fp32 [>= {need}, hd/2, 4]")
+        P, keep = self._marshal(self, params, check_rope=False)
+        y = torch.empty_like(x)
+        L.check(self.lib.spb_block_decode(C.byref(self.d), C.byref(P), _ptr(x), _ptr(cache.kbuf), _ptr(cache.vbuf), cache.length, self.Tmax,
+                                          _ptr(y), _ptr(self.ws), _stream()), "spb_block_decode")
+        cache.length += c.T
+        return y
+
+    def weight_bytes(self):
+        c = self.cfg
+        return (c.C * c.n_tot + c.n_q * c.C) * (2 if c.dtype == torch.bfloat16 else 4)

@@ -834,4 +834,115 @@ static int ffn_bwd_impl(const spb_ffn_desc* d, const spb_ffn_params* p, const vo
   return 0;
 }
 
+
+// ------------------------------------------------------------------------------------------------ KV-cache decode
+size_t spb_attn_decode_scratch_bytes(int32_t B, int32_t Tq, int32_t Hq, int32_t Hkv, int32_t hd, int32_t Tk) {
+  if (B <= 0 || Tq <= 0 || Hq <= 0 || Hkv <= 0 || hd <= 0 || Tk <= 0 || Hq % Hkv != 0) return 0;
+  return attn_decode_scratch_bytes(B, Tq, Hq, Hkv, hd, Tk);
+}
+
+int spb_attn_decode(int dtype, int32_t B, int32_t Tq, int32_t Hq, int32_t Hkv, int32_t hd, int32_t Tk, float scale, const void* q, int64_t ldq,
+                    const void* k_cache, int64_t ldk, int64_t k_batch_stride, const void* v_cache, int64_t ldv, int64_t v_batch_stride, void* o,
+                    int64_t ldo, float* lse, void* scratch, spb_stream_t stream) {
+  SPB_CHECK_ARG(q && k_cache && v_cache && o && scratch, SPB_E_INVALID, "spb_attn_decode: null pointer");
+  SPB_CHECK_ARG(B > 0 && Tq > 0 && Hq > 0 && Hkv > 0 && hd > 0 && Tk > 0 && Hq % Hkv == 0, SPB_E_INVALID, "spb_attn_decode: bad shape");
+  SPB_CHECK_ARG(ldq >= (int64_t)Hq * hd && ldo >= (int64_t)Hq * hd && ldk >= (int64_t)Hkv * hd && ldv >= (int64_t)Hkv * hd, SPB_E_INVALID,
+                "spb_attn_decode: leading dimension smaller than heads*hd");
+  SPB_CHECK_ARG((uintptr_t)scratch % 16 == 0, SPB_E_INVALID, "spb_attn_decode: scratch must be 16-byte aligned");
+  return attn_decode(dtype, B, Tq, Hq, Hkv, hd, Tk, scale, q, ldq, k_cache, ldk, k_batch_stride, v_cache, ldv, v_batch_stride, o, ldo, lse, scratch,
+                     (cudaStream_t)stream);
+}
+
+int spb_block_decode_ws_layout(const spb_block_desc* d, int32_t Tmax, spb_decode_ws* out) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  SPB_CHECK_ARG(out != nullptr && Tmax >= d->T, SPB_E_INVALID, "spb_block_decode_ws_layout: bad argument (Tmax=%d Tq=%d)", Tmax, d->T);
+  const size_t M = (size_t)d->B * d->T, e = esize(d->dtype);
+  const size_t Nq = (size_t)d->Hq * d->hd, Nkv = (size_t)d->Hkv * d->hd, Ntot = Nq + 2 * Nkv;
+  SPB_CHECK_ARG(M <= 64, SPB_E_LIMIT, "decode: B*Tq = %zu rows; at most 64 (longer inputs go through spb_block_fwd)", M);
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off = align_up(off + bytes, 256);
+    return o;
+  };
+  memset(out, 0, sizeof(*out));
+  out->xhat = take(M * d->C * e);
+  out->qkv = take(M * Ntot * e);
+  out->attn_o = take(M * Nq * e);
+  size_t part = small_m_gemm_scratch_bytes((int)M, (int)Ntot, d->C, d->dtype);
+  const size_t part_o = small_m_gemm_scratch_bytes((int)M, d->C, (int)Nq, d->dtype);
+  if (part_o > part) part = part_o;
+  out->gemm_part = take(part);
+  // the split plan depends on Tk; the scratch grows with the number of key splits, which is capped - take the worst over Tk <= Tmax
+  size_t ap = 0;
+  for (int tk = 128; ; tk *= 2) {
+    const int t = tk < Tmax ? tk : Tmax;
+    const size_t b = attn_decode_scratch_bytes(d->B, d->T, d->Hq, d->Hkv, d->hd, t);
+    if (b > ap) ap = b;
+    if (t == Tmax) break;
+  }
+  out->attn_part = take(ap);
+  out->total = off;
+  return 0;
+}
+
+int spb_block_decode(const spb_block_desc* d, const spb_block_params* p, const void* x, void* k_cache, void* v_cache, int32_t cache_len,
+                     int32_t Tmax, void* y, void* ws, spb_stream_t stream) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  SPB_CHECK_ARG(y && k_cache && v_cache, SPB_E_INVALID, "spb_block_decode: null pointer");
+  rc = check_block_params("spb_block_decode", d, p, x, ws);
+  if (rc) return rc;
+  SPB_CHECK_ARG(cache_len >= 0 && cache_len + d->T <= Tmax, SPB_E_INVALID, "spb_block_decode: cache_len %d + Tq %d exceeds the cache capacity %d",
+                cache_len, d->T, Tmax);
+  SPB_CHECK_ARG(d->weight_layout == SPB_W_IN_OUT, SPB_E_UNSUPPORTED, "spb_block_decode: [in,out] weights only (the cache branch is the Llama notebook's)");
+  SPB_CHECK_ARG(!(d->causal && d->T > 1), SPB_E_UNSUPPORTED,
+                "spb_block_decode: a causal mask over Tq > 1 new tokens has no counterpart in llama3:824-825 (its mask slice does not broadcast)");
+  SPB_CHECK_ARG(attn_decode_supported(d->dtype, d->hd), SPB_E_UNSUPPORTED, "spb_block_decode: head dim %d (64, 128, 256)", d->hd);
+  spb_decode_ws L;
+  rc = spb_block_decode_ws_layout(d, Tmax, &L);
+  if (rc) return rc;
+  char* w8 = (char*)ws;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int M = d->B * d->T, dt = d->dtype;
+  const int64_t Nq = (int64_t)d->Hq * d->hd, Nkv = (int64_t)d->Hkv * d->hd, Ntot = Nq + 2 * Nkv;
+  const size_t e = esize(dt);
+  // 1. norm
+  const void* xin = x;
+  if (d->norm_kind != SPB_NORM_NONE) {
+    rc = spb_norm_fwd(dt, d->norm_kind, d->norm_upcast, d->norm_eps, x, p->norm_w, p->norm_b, w8 + L.xhat, nullptr, M, d->C, stream);
+    if (rc) return rc;
+    xin = w8 + L.xhat;
+  }
+  // 2. q | k | v projections: weight-read-bound small-M GEMMs
+  char* qkv = w8 + L.qkv;
+  float* part = (float*)(w8 + L.gemm_part);
+  const char *wq = (const char*)p->wq, *wk = (const char*)p->wk, *wv = (const char*)p->wv;
+  bool packed = p->ldw_q == p->ldw_k && p->ldw_k == p->ldw_v && wk == wq + Nq * e && wv == wk + Nkv * e;
+  if (d->qkv_bias) packed = packed && (const char*)p->bk == (const char*)p->bq + Nq * e && (const char*)p->bv == (const char*)p->bk + Nkv * e;
+  if (packed) {
+    rc = small_m_gemm(dt, M, (int)Ntot, d->C, xin, d->C, wq, p->ldw_q, qkv, Ntot, d->qkv_bias ? p->bq : nullptr, nullptr, 0, part, st);
+    if (rc) return rc;
+  } else {
+    rc = small_m_gemm(dt, M, (int)Nq, d->C, xin, d->C, wq, p->ldw_q, qkv, Ntot, d->qkv_bias ? p->bq : nullptr, nullptr, 0, part, st);
+    if (rc) return rc;
+    rc = small_m_gemm(dt, M, (int)Nkv, d->C, xin, d->C, wk, p->ldw_k, qkv + Nq * e, Ntot, d->qkv_bias ? p->bk : nullptr, nullptr, 0, part, st);
+    if (rc) return rc;
+    rc = small_m_gemm(dt, M, (int)Nkv, d->C, xin, d->C, wv, p->ldw_v, qkv + (Nq + Nkv) * e, Ntot, d->qkv_bias ? p->bv : nullptr, nullptr, 0, part, st);
+    if (rc) return rc;
+  }
+  // 3. rotary at positions cache_len .. and the in-place append of the new k, v rows
+  rc = decode_rope_append(dt, qkv, Ntot, d->B, d->T, d->Hq, d->Hkv, d->hd, d->rope_kind == SPB_ROPE_TABLE ? p->rope : nullptr, cache_len, k_cache,
+                          v_cache, Nkv, (int64_t)Tmax * Nkv, st);
+  if (rc) return rc;
+  // 4. attention of the new rows over the whole cache
+  rc = attn_decode(dt, d->B, d->T, d->Hq, d->Hkv, d->hd, cache_len + d->T, d->scale, qkv, Ntot, k_cache, Nkv, (int64_t)Tmax * Nkv, v_cache, Nkv,
+                   (int64_t)Tmax * Nkv, w8 + L.attn_o, Nq, nullptr, w8 + L.attn_part, st);
+  if (rc) return rc;
+  // 5. output projection (+ bias, + x)
+  return small_m_gemm(dt, M, d->C, (int)Nq, w8 + L.attn_o, Nq, p->wo, p->ldw_o, y, d->C, d->out_bias ? p->bo : nullptr, d->residual ? x : nullptr,
+                      d->C, part, st);
+}
+
 }  // extern "C"

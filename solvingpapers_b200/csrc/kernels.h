@@ -45,4 +45,15 @@ int comm_allreduce_join(void* comm, float* const* ptrs, const size_t* counts, in
 // error path: if a side-stream all-reduce is outstanding, make `main` wait for it and forget it
 void comm_side_cleanup(void* comm, cudaStream_t main);
 
+// decode.cu
+size_t small_m_gemm_scratch_bytes(int M, int N, int K, int dtype);
+int small_m_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, const void* W, int64_t ldw, void* D, int64_t ldd, const void* bias,
+                 const void* res, int64_t ldr, float* part, cudaStream_t st);
+bool attn_decode_supported(int dtype, int hd);
+size_t attn_decode_scratch_bytes(int B, int Tq, int Hq, int Hkv, int hd, int Tk);
+int attn_decode(int dtype, int B, int Tq, int Hq, int Hkv, int hd, int Tk, float scale, const void* q, int64_t ldq, const void* k, int64_t ldk,
+                int64_t kbs, const void* v, int64_t ldv, int64_t vbs, void* o, int64_t ldo, float* lse, void* scratch, cudaStream_t st);
+int decode_rope_append(int dtype, void* qkv, int64_t ld, int B, int Tq, int Hq, int Hkv, int hd, const float* rope, int pos0, void* kc, void* vc,
+                       int64_t ldc, int64_t cbs, cudaStream_t st);
+
 }  // namespace spb

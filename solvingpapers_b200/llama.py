@@ -6,8 +6,8 @@ torch.autograd the way the notebook's functions are through jax.value_and_grad (
 
 Contract carried over from tracing: under jit the mask is a tracer whose values cannot be read, so
 ``mask is not None`` means CAUSAL and ``None`` means bidirectional; the tensor itself is ignored.
-``cache is not None`` or ``position != 0`` raise: the notebook never exercises that branch and the library has
-no slow path.
+``cache`` / ``position`` select the KV-cache decode step (llama3:815-819, spb_block_decode); combinations the
+notebook's own code cannot compute (a mask with several new tokens, position without a cache) raise.
 """
 import math
 
@@ -56,10 +56,51 @@ def _cfg(x, n_heads, n_kv_heads, head_dim, mask, norm, eps=1e-6, attn_impl=L.IMP
                        attn_impl=attn_impl, gemm_impl=gemm_impl, residual=residual)
 
 
+_DECODERS = {}
+
+
+def _decode(params, x, mask, freqs_cis, n_heads, n_kv_heads, cache, position, norm_w=None, eps=1e-6, residual=False):
+    """The cache branch of llama3/LLaMA-jax.ipynb:815-819 through spb_block_decode (no autograd: the notebook only samples
+    with it).  ``cache`` is the notebook's ``(k, v)`` tuple ([B, Tc, Hkv, hd]; a new, longer tuple is returned, as
+    ``jnp.concatenate`` does) or a ``KVCache`` (appended in place; its views are returned)."""
+    from .block import DecodeBlock, KVCache
+    B, T, C = x.shape
+    hd = C // n_heads
+    in_place = isinstance(cache, KVCache)
+    if in_place:
+        kv = cache
+    else:
+        if cache[0].shape[1] != position:
+            raise ValueError(f"cache holds {cache[0].shape[1]} tokens but position = {position} (llama3:815 slices freqs_cis from `position`)")
+        kv = KVCache.from_tensors(cache[0], cache[1], extra=T)
+    if kv.length != position:
+        raise ValueError(f"cache holds {kv.length} tokens but position = {position}")
+    if mask is not None and T > 1:
+        # llama3:824-825 adds mask[:, :, :T, :T] to scores [B, H, T, Tc + T]: that only broadcasts for T == 1
+        raise ValueError("a mask with a non-empty cache is only defined for a single new token (llama3:824-825 does not broadcast otherwise)")
+    cfg = BlockConfig(B=B, T=T, C=C, Hq=n_heads, Hkv=n_kv_heads, hd=hd, dtype=x.dtype, norm_kind=L.NORM_RMS if norm_w is not None else L.NORM_NONE,
+                      norm_eps=eps, rope=True, causal=False, scale=1.0 / math.sqrt(hd), weight_layout=L.W_IN_OUT, residual=residual)
+    key = (tuple(sorted(cfg.__dict__.items())), kv.capacity, str(x.device))
+    dec = _DECODERS.get(key)
+    if dec is None:
+        if len(_DECODERS) > 8:
+            _DECODERS.clear()
+        dec = _DECODERS[key] = DecodeBlock(cfg, kv.capacity, device=x.device)
+    p = {"wq": params["wq"], "wk": params["wk"], "wv": params["wv"], "wo": params["wo"], "rope": _table(freqs_cis[:position + T])}
+    if norm_w is not None:
+        p["norm_w"] = norm_w
+    with torch.no_grad():
+        y = dec.step(x.contiguous(), p, kv)
+    return y, (kv.k, kv.v)
+
+
 def attention(params, x, mask, freqs_cis, n_heads, n_kv_heads, cache=None, position=0, comm=None):
-    """llama3/LLaMA-jax.ipynb:809-829.  Returns (out [B,T,C], (k, v)) with k, v post-rotary, un-repeated."""
-    if cache is not None or position != 0:
-        raise NotImplementedError("KV-cache decode (cache / position) is not on the training hot path and has no kernel")
+    """llama3/LLaMA-jax.ipynb:809-829.  Returns (out [B,T,C], (k, v)) with k, v post-rotary, un-repeated.
+    ``cache=None, position=0`` is the training / prefill path (differentiable); with a cache it is one decode step."""
+    if cache is not None:
+        return _decode(params, x, mask, freqs_cis, n_heads, n_kv_heads, cache, position)
+    if position != 0:
+        raise ValueError("position != 0 without a cache: llama3:815 would rotate at `position` but attend to nothing before it")
     B, T, C = x.shape
     cfg = _cfg(x, n_heads, n_kv_heads, C // n_heads, mask, norm=False)
     tab = _table(freqs_cis[position:position + T])
@@ -111,8 +152,12 @@ def transformer_block(params, x, mask, freqs_cis, n_heads, n_kv_heads, cache=Non
     The notebook always calls it with ``training=False`` (:927; ``dropout_rate=0.0`` :358): the dropout branch has no kernel."""
     if training and dropout_rate != 0.0:
         raise NotImplementedError("dropout inside transformer_block is dead code in the notebook (training=False, llama3:927) and has no kernel")
-    if cache is not None or position != 0:
-        raise NotImplementedError("KV-cache decode (cache / position) is not on the training hot path and has no kernel")
+    if cache is not None:
+        # decode step: h = x + attention(rms_norm(x), cache, position) in one spb_block_decode call, then the feed-forward half
+        h, new_cache = _decode(params["attention"], x, mask, freqs_cis, n_heads, n_kv_heads, cache, position, norm_w=params["attention_norm"],
+                               residual=True)
+        with torch.no_grad():
+            return ffn_block(params, h, comm=comm, residual=True), new_cache
     h, new_cache = attention_block(params, x, mask, freqs_cis, n_heads, n_kv_heads, comm=comm, residual=True)
     out = ffn_block(params, h, comm=comm, residual=True)
     return out, new_cache

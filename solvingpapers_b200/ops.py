@@ -105,6 +105,25 @@ def flash_bwd(q, k, v, o, do, lse, causal, scale, impl=L.IMPL_AUTO):
     return dq, dk, dv
 
 
+def attn_decode(q, k_cache, v_cache, Tk, scale, want_lse=False):
+    """llama3:815-829 with a cache: q [B,Tq,Hq,hd] (rotated) against the first Tk rows of k_cache / v_cache [B,Tmax,Hkv,hd]
+    (any token / batch strides, last dim contiguous) -> o [B,Tq,Hq,hd] (and lse [B,Hq,Tq])."""
+    lib = L.load()
+    B, Tq, Hq, hd = q.shape
+    Hkv = k_cache.shape[2]
+    if q.stride(3) != 1 or q.stride(2) != hd or k_cache.stride(3) != 1 or k_cache.stride(2) != hd or v_cache.stride(3) != 1 or v_cache.stride(2) != hd:
+        raise L.SpbError("attn_decode: heads must be contiguous [.., H, hd]")
+    if q.stride(0) != Tq * q.stride(1):
+        raise L.SpbError("attn_decode: q rows must have one stride")
+    o = torch.empty((B, Tq, Hq, hd), dtype=q.dtype, device=q.device)
+    lse = torch.empty((B, Hq, Tq), dtype=torch.float32, device=q.device) if want_lse else None
+    scratch = torch.empty(lib.spb_attn_decode_scratch_bytes(B, Tq, Hq, Hkv, hd, Tk), dtype=torch.uint8, device=q.device)
+    L.check(lib.spb_attn_decode(_dt(q.dtype), B, Tq, Hq, Hkv, hd, Tk, scale, _ptr(q), q.stride(1), _ptr(k_cache), k_cache.stride(1),
+                                k_cache.stride(0), _ptr(v_cache), v_cache.stride(1), v_cache.stride(0), _ptr(o), o.stride(1), _ptr(lse),
+                                _ptr(scratch), _stream()), "spb_attn_decode")
+    return (o, lse) if want_lse else o
+
+
 class _MatmulFn(torch.autograd.Function):
     """y = x @ w with w stored [in, out] (``jnp.dot(h, params['output'])``, llama3:930): forward and both backward GEMMs through
     spb_gemm (tcgen05 for bf16, FFMA for fp32); the weight gradient is accumulated in fp32."""

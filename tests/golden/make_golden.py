@@ -151,6 +151,36 @@ def make_llama(tag, B, T, C, H, Hkv, causal, seed):
     print("llama", tag, "y", y.shape, "max|y|", np.abs(y).max())
 
 
+def make_llama_decode(tag, B, Tc, Tq, C, H, Hkv, use_mask, seed):
+    """the notebook's own attention cell (c24) run through its cache branch (llama3:815-819): a prefill of Tc
+    tokens with cache=None gives (k, v); then Tq new tokens with cache=(k, v), position=Tc.  use_mask passes the model's
+    causal mask (only valid for Tq = 1: the cell adds mask[:, :, :T, :T] to scores [B, H, T, Tc+T])."""
+    rng = np.random.default_rng(seed)
+    hd = C // H
+    f32 = np.float32
+    Tm = Tc + Tq
+    x0 = rng.standard_normal((B, Tc, C)).astype(f32)
+    x1 = rng.standard_normal((B, Tq, C)).astype(f32)
+    p = {"wq": (rng.standard_normal((C, H * hd)) / math.sqrt(C)).astype(f32), "wk": (rng.standard_normal((C, Hkv * hd)) / math.sqrt(C)).astype(f32),
+         "wv": (rng.standard_normal((C, Hkv * hd)) / math.sqrt(C)).astype(f32), "wo": (rng.standard_normal((H * hd, C)) / math.sqrt(H * hd)).astype(f32)}
+    nw = rng.standard_normal((C,)).astype(f32)
+    out = dict(x0=x0, x1=x1, norm_w=nw, meta=np.array([B, Tc, Tq, C, H, Hkv, int(use_mask)], dtype=np.int64), **p)
+    for high, sfx in ((False, ""), (True, "64")):
+        ns = llama_namespace(high)
+        dt = np.float64 if high else f32
+        cast = lambda a: a.astype(dt)
+        pp = {k_: cast(v_) for k_, v_ in p.items()}
+        fc = ns["precompute_freqs_cis"](hd, Tm)
+        mask = np.where(np.tril(np.ones((Tm, Tm))) == 0, -1e9, 0.0).astype(dt)[None, None, :, :]  # llama3:920-923
+        _, cache = ns["attention"](pp, ns["rms_norm"](cast(x0), cast(nw)), mask, fc, H, Hkv)          # prefill, cache=None
+        y, (k, v) = ns["attention"](pp, ns["rms_norm"](cast(x1), cast(nw)), mask if use_mask else None, fc, H, Hkv, cache=cache, position=Tc)
+        assert k.shape == (B, Tm, Hkv, hd) and y.shape == (B, Tq, C)
+        out["cache_k" + sfx], out["cache_v" + sfx] = cache
+        out["y" + sfx], out["k" + sfx], out["v" + sfx] = y, k, v
+    np.savez_compressed(os.path.join(OUT, f"llama_decode_{tag}.npz"), **out)
+    print("llama decode", tag, "y", out["y"].shape, "max|y|", np.abs(out["y"]).max())
+
+
 def make_llama_ffn(tag, B, T, C, seed):
     """the notebook's own feed_forward cell (c25) and the two lines of transformer_block that use it
     (llama3/LLaMA-jax.ipynb:886,890: ffn_output = feed_forward(params['ffn'], rms_norm(h, params['ffn_norm'])); out = h + ffn_output),
@@ -495,6 +525,8 @@ if __name__ == "__main__":
     make_llama("gqa_causal", B=2, T=16, C=64, H=4, Hkv=2, causal=True, seed=0)
     make_llama("mha_nomask", B=1, T=9, C=32, H=2, Hkv=2, causal=False, seed=1)
     make_llama("mqa_causal", B=2, T=12, C=64, H=4, Hkv=1, causal=True, seed=2)
+    make_llama_decode("one_token", B=2, Tc=21, Tq=1, C=128, H=2, Hkv=1, use_mask=True, seed=10)   # hd 64 like the notebook
+    make_llama_decode("chunk_nomask", B=1, Tc=9, Tq=3, C=128, H=2, Hkv=2, use_mask=False, seed=11)
     make_llama_ffn("small", B=2, T=12, C=32, seed=5)
     make_llama_loss("small", B=2, T=16, V=257, seed=7)
     make_gemma("small", B=2, T=16, D=64, seed=3)

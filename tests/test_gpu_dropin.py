@@ -55,7 +55,7 @@ def test_llama_functions_read_like_the_notebook(dtype):
     assert llama.repeat_kv(rk, 2).shape == (B, T, 2 * Hkv, hd)
 
 
-def test_llama_attention_mask_none_is_bidirectional_and_cache_raises():
+def test_llama_attention_mask_none_is_bidirectional():
     from solvingpapers_b200 import llama
     rng = np.random.default_rng(1)
     B, T, C, H, Hkv = 1, 32, 64, 2, 2
@@ -66,8 +66,6 @@ def test_llama_attention_mask_none_is_bidirectional_and_cache_raises():
     p = {k: v.to(DEV) for k, v in bp["attention"].items()}
     out, _ = llama.attention(p, x.to(DEV), None, llama.precompute_freqs_cis(C // H, T), H, Hkv)
     assert max_rel_err(out, ref) < TOL_F32
-    with pytest.raises(NotImplementedError):
-        llama.attention(p, x.to(DEV), None, llama.precompute_freqs_cis(C // H, T), H, Hkv, cache=(x, x))
 
 
 def test_gpt_module_call_surface():

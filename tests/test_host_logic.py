@@ -85,9 +85,10 @@ def test_shard_bounds():
 def test_dropin_error_behaviour_is_checked_before_any_kernel():
     from solvingpapers_b200 import llama, gpt, vit
     x = torch.zeros(1, 4, 8)
-    with pytest.raises(NotImplementedError):
-        llama.attention({}, x, None, None, 2, 1, cache=(x, x))
-    with pytest.raises(NotImplementedError):
+    kv = torch.zeros(1, 5, 1, 4)
+    with pytest.raises(ValueError):  # cache length and position disagree (llama3:815 slices the table from `position`)
+        llama.attention({}, x, None, None, 2, 1, cache=(kv, kv), position=3)
+    with pytest.raises(ValueError):  # position without a cache
         llama.attention({}, x, None, None, 2, 1, position=3)
     with pytest.raises(NotImplementedError):
         gpt.CausalSelfAttention(8, 2, 0.1)({}, x, deterministic=False)

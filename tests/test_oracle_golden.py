@@ -241,3 +241,23 @@ def test_oracle_self_check_finite_difference_gemma_and_gpt():
     f = lambda xx: float((gpt_oracle.attention_block(p, xx, 2) * dy).sum())
     fd = (f(x + h * u) - f(x - h * u)) / (2 * h)
     assert abs(fd - float((r["dx"] * u).sum())) < 1e-6 * max(1, abs(fd))
+
+
+@pytest.mark.parametrize("tag", ["one_token", "chunk_nomask"])
+def test_llama_cache_branch_matches_literal_notebook_source(golden_dir, tag):
+    """the oracle's cache branch (llama3:815-819) against the notebook's own attention cell run with
+    cache=(k, v), position=Tc - prefill cache, decode output and the grown cache, fp32 and fp64."""
+    g = _load(golden_dir, f"llama_decode_{tag}.npz")
+    B, Tc, Tq, C, H, Hkv, use_mask = (int(v) for v in g["meta"])
+    hd = C // H
+    for dt, sfx, tol in ((torch.float32, "", 3e-6), (torch.float64, "64", 1e-6)):
+        p = {k: T(g[k]).to(dt) for k in ("wq", "wk", "wv", "wo")}
+        nw = T(g["norm_w"]).to(dt)
+        fc = llama_oracle.precompute_freqs_cis(hd, Tc + Tq, dtype=dt)
+        mask = llama_oracle.make_mask(Tc + Tq, dt)
+        _, cache = llama_oracle.attention(p, llama_oracle.rms_norm(T(g["x0"]).to(dt), nw), mask, fc, H, Hkv)
+        assert max_rel_err(cache[0], T(g["cache_k" + sfx])) < tol and max_rel_err(cache[1], T(g["cache_v" + sfx])) < tol
+        y, (k, v) = llama_oracle.attention(p, llama_oracle.rms_norm(T(g["x1"]).to(dt), nw), mask if use_mask else None, fc, H, Hkv,
+                                           cache=cache, position=Tc)
+        assert k.shape == (B, Tc + Tq, Hkv, hd)
+        assert max_rel_err(y, T(g["y" + sfx])) < tol and max_rel_err(k, T(g["k" + sfx])) < tol and max_rel_err(v, T(g["v" + sfx])) < tol
