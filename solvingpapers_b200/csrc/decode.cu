@@ -45,57 +45,116 @@ struct Vec16<__nv_bfloat16> {
   }
 };
 
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+template <typename T>
+__device__ __forceinline__ void smem_vec(const uint8_t* p, float* f);
+template <>
+__device__ __forceinline__ void smem_vec<float>(const uint8_t* p, float* f) {
+  const float4 v = *reinterpret_cast<const float4*>(p);
+  f[0] = v.x; f[1] = v.y; f[2] = v.z; f[3] = v.w;
+}
+template <>
+__device__ __forceinline__ void smem_vec<__nv_bfloat16>(const uint8_t* p, float* f) {
+  const uint4 v = *reinterpret_cast<const uint4*>(p);
+  const float2 a = unpack_bf16(v.x), b = unpack_bf16(v.y), c = unpack_bf16(v.z), d = unpack_bf16(v.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+
 // ------------------------------------------------------------------------------------------------ K5: small-M GEMM
-// grid (column panels, k splits, row groups of MB); W is [K, N] row-major (row stride ldw): SPB_W_IN_OUT
+// 1-D TMA bulk copy (no tensor map): `bytes` contiguous bytes global -> shared, completion credited to an mbarrier
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)), "l"(gsrc),
+               "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+constexpr int SMG_ROWS = 16;    // weight rows per pipeline stage
+constexpr int SMG_STAGES = 4;   // stages in flight: 4 x 16 rows x 2 KB = 128 KB of weight bytes per SM
+constexpr int SMG_PANEL_BYTES = DEC_THREADS * 16;
+
+// grid (column panels, k splits, row groups of MB); W is [K, N] row-major (row stride ldw): SPB_W_IN_OUT.
+// One CTA per (panel, k slice): thread 0 keeps SMG_STAGES stages of 16 weight-row segments (2 KB each, contiguous in
+// HBM) in flight with bulk copies; all 128 threads consume a stage from shared memory (thread = one 16-byte column piece)
+// against the MB activation rows held in shared memory as fp32.
 template <typename T, int MB>
 __global__ void __launch_bounds__(DEC_THREADS) small_m_gemm_kernel(const T* __restrict__ A, int64_t lda, const T* __restrict__ W, int64_t ldw,
                                                                   float* __restrict__ part, int M, int N, int K, int k_per_split) {
   constexpr int VE = Vec16<T>::N;
-  constexpr int KC = 64;  // k rows staged per shared-memory refill
-  __shared__ float xs[MB][KC];
+  extern __shared__ __align__(128) uint8_t smg[];
+  uint8_t* stages = smg;                                                        // [SMG_STAGES][SMG_ROWS][SMG_PANEL_BYTES]
+  float* xs = reinterpret_cast<float*>(smg + SMG_STAGES * SMG_ROWS * SMG_PANEL_BYTES);  // [MB][k_per_split]
+  __shared__ uint64_t full[SMG_STAGES];
   const int m0 = blockIdx.z * MB;
-  const int col = (blockIdx.x * DEC_THREADS + threadIdx.x) * VE;
+  const int col0 = blockIdx.x * DEC_THREADS * VE;
+  const int col = col0 + threadIdx.x * VE;
   const int kb = blockIdx.y * k_per_split, ke = min(K, kb + k_per_split);
+  const int klen = ke - kb;
+  const int ncols = min(DEC_THREADS * VE, N - col0);
+  const uint32_t row_bytes = (uint32_t)ncols * sizeof(T);
   const bool live = col < N;  // N % VE == 0 is checked by the launcher
+  const int nst = (klen + SMG_ROWS - 1) / SMG_ROWS;
+
+  auto issue = [&](int st) {  // thread 0: rows [st*16, st*16+16) of the slice -> stage st % SMG_STAGES
+    const int r0 = st * SMG_ROWS, rn = min(SMG_ROWS, klen - r0);
+    uint64_t* bar = &full[st % SMG_STAGES];
+    mbar_arrive_expect_tx(bar, rn * row_bytes);
+    uint8_t* dst = stages + (size_t)(st % SMG_STAGES) * SMG_ROWS * SMG_PANEL_BYTES;
+    for (int r = 0; r < rn; ++r) bulk_load(dst + r * SMG_PANEL_BYTES, W + (int64_t)(kb + r0 + r) * ldw + col0, row_bytes, bar);
+  };
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < SMG_STAGES; ++i) mbar_init(&full[i], 1);
+    fence_barrier_init();
+    for (int st = 0; st < min(nst, SMG_STAGES); ++st) issue(st);
+  }
+  for (int i = threadIdx.x; i < MB * klen; i += DEC_THREADS) {
+    const int m = i / klen, kk = i % klen;
+    xs[m * k_per_split + kk] = (m0 + m < M) ? to_f32<T>(A[(int64_t)(m0 + m) * lda + kb + kk]) : 0.f;
+  }
   float acc[MB][VE];
 #pragma unroll
   for (int m = 0; m < MB; ++m)
 #pragma unroll
     for (int e = 0; e < VE; ++e) acc[m][e] = 0.f;
-  for (int k0 = kb; k0 < ke; k0 += KC) {
-    const int kn = min(KC, ke - k0);
-    __syncthreads();
-    for (int i = threadIdx.x; i < MB * KC; i += DEC_THREADS) {
-      const int m = i / KC, kk = i % KC;
-      xs[m][kk] = (m0 + m < M && kk < kn) ? to_f32<T>(A[(int64_t)(m0 + m) * lda + k0 + kk]) : 0.f;
-    }
-    __syncthreads();
-    if (!live) continue;
-    const T* wp = W + (int64_t)k0 * ldw + col;
-    int kk = 0;
-    for (; kk + 4 <= kn; kk += 4) {  // four weight rows in flight per thread
-      float w[4][VE];
+  __syncthreads();  // barriers initialised, xs complete
+  for (int st = 0; st < nst; ++st) {
+    const int r0 = st * SMG_ROWS, rn = min(SMG_ROWS, klen - r0);
+    mbar_wait(&full[st % SMG_STAGES], (st / SMG_STAGES) & 1);
+    if (live) {
+      const uint8_t* src = stages + (size_t)(st % SMG_STAGES) * SMG_ROWS * SMG_PANEL_BYTES + threadIdx.x * 16;
+      if (rn == SMG_ROWS) {
 #pragma unroll
-      for (int u = 0; u < 4; ++u) Vec16<T>::load(wp + (int64_t)(kk + u) * ldw, w[u]);
+        for (int r = 0; r < SMG_ROWS; ++r) {
+          float w[VE];
+          smem_vec<T>(src + r * SMG_PANEL_BYTES, w);
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
+          for (int m = 0; m < MB; ++m) {
+            const float xv = xs[m * k_per_split + r0 + r];
 #pragma unroll
-        for (int m = 0; m < MB; ++m) {
-          const float xv = xs[m][kk + u];
-#pragma unroll
-          for (int e = 0; e < VE; ++e) acc[m][e] = fmaf(xv, w[u][e], acc[m][e]);
+            for (int e = 0; e < VE; ++e) acc[m][e] = fmaf(xv, w[e], acc[m][e]);
+          }
         }
-    }
-    for (; kk < kn; ++kk) {
-      float w[VE];
-      Vec16<T>::load(wp + (int64_t)kk * ldw, w);
+      } else {
+        for (int r = 0; r < rn; ++r) {
+          float w[VE];
+          smem_vec<T>(src + r * SMG_PANEL_BYTES, w);
 #pragma unroll
-      for (int m = 0; m < MB; ++m) {
-        const float xv = xs[m][kk];
+          for (int m = 0; m < MB; ++m) {
+            const float xv = xs[m * k_per_split + r0 + r];
 #pragma unroll
-        for (int e = 0; e < VE; ++e) acc[m][e] = fmaf(xv, w[e], acc[m][e]);
+            for (int e = 0; e < VE; ++e) acc[m][e] = fmaf(xv, w[e], acc[m][e]);
+          }
+        }
       }
     }
+    __syncthreads();  // everyone is done with this stage: refill it
+    if (threadIdx.x == 0 && st + SMG_STAGES < nst) issue(st + SMG_STAGES);
   }
   if (!live) return;
 #pragma unroll
@@ -123,7 +182,7 @@ __global__ void __launch_bounds__(256) small_m_reduce_kernel(const float* __rest
 
 static int small_m_splits(int M, int N, int K, int ve) {
   const int panels = (N + DEC_THREADS * ve - 1) / (DEC_THREADS * ve);
-  int want = (2 * sm_count() + panels - 1) / panels;
+  int want = sm_count() / panels;  // one CTA per SM (each keeps 128 KB of weight bytes in flight), the whole grid in ONE wave
   int max_splits = K / 32;
   if (max_splits < 1) max_splits = 1;
   if (want > max_splits) want = max_splits;
@@ -147,10 +206,18 @@ static int small_m_gemm_t(int M, int N, int K, const T* A, int64_t lda, const T*
   const int nsplit = (K + k_per - 1) / k_per;
   const int MB = M >= 8 ? 8 : (M > 2 ? 4 : (M > 1 ? 2 : 1));
   dim3 grid((N + DEC_THREADS * VE - 1) / (DEC_THREADS * VE), nsplit, (M + MB - 1) / MB);
-  if (MB == 8) small_m_gemm_kernel<T, 8><<<grid, DEC_THREADS, 0, st>>>(A, lda, W, ldw, part, M, N, K, k_per);
-  else if (MB == 4) small_m_gemm_kernel<T, 4><<<grid, DEC_THREADS, 0, st>>>(A, lda, W, ldw, part, M, N, K, k_per);
-  else if (MB == 2) small_m_gemm_kernel<T, 2><<<grid, DEC_THREADS, 0, st>>>(A, lda, W, ldw, part, M, N, K, k_per);
-  else small_m_gemm_kernel<T, 1><<<grid, DEC_THREADS, 0, st>>>(A, lda, W, ldw, part, M, N, K, k_per);
+  const size_t dyn = (size_t)SMG_STAGES * SMG_ROWS * SMG_PANEL_BYTES + (size_t)MB * k_per * sizeof(float);
+  SPB_CHECK_ARG(dyn <= 200 * 1024, SPB_E_LIMIT, "small-M GEMM: K slice of %d rows does not fit shared memory", k_per);
+#define SPB_SMG_LAUNCH(MBV)                                                                                                      \
+  do {                                                                                                                           \
+    SPB_CUDA(cudaFuncSetAttribute(small_m_gemm_kernel<T, MBV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));          \
+    small_m_gemm_kernel<T, MBV><<<grid, DEC_THREADS, dyn, st>>>(A, lda, W, ldw, part, M, N, K, k_per);                           \
+  } while (0)
+  if (MB == 8) SPB_SMG_LAUNCH(8);
+  else if (MB == 4) SPB_SMG_LAUNCH(4);
+  else if (MB == 2) SPB_SMG_LAUNCH(2);
+  else SPB_SMG_LAUNCH(1);
+#undef SPB_SMG_LAUNCH
   SPB_LAUNCH_CHECK();
   const int64_t total = (int64_t)M * N;
   small_m_reduce_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(part, nsplit, D, ldd, bias, res, ldr, M, N);
@@ -162,6 +229,19 @@ static int small_m_gemm_t(int M, int N, int K, const T* A, int64_t lda, const T*
 int small_m_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, const void* W, int64_t ldw, void* D, int64_t ldd, const void* bias,
                  const void* res, int64_t ldr, float* part, cudaStream_t st) {
   SPB_CHECK_ARG(M >= 1 && M <= 64 && N >= 1 && K >= 1, SPB_E_LIMIT, "small-M GEMM: M=%d rows (1..64 supported; longer inputs go through the prefill path)", M);
+  // bf16: the tcgen05 GEMM with its K-split for few-tile problems (one 128-row tile, N/256 column tiles, K cut into up to 8
+  // parts that TMA-reduce into a zeroed fp32 [M, N]) streams the weight at HBM speed with no CUDA-core arithmetic at all -
+  // the SIMT kernel below is bound by FMA issue on one warp per scheduler (ncu r02d: 28 % issue-active, 34 k cycles for 50 MB).
+  // The fp32 result is finished (bias, residual, conversion) by the reduce kernel with one "split".
+  if (dtype == SPB_BF16 && lda % 8 == 0 && ldw % 8 == 0 && (uintptr_t)A % 16 == 0 && (uintptr_t)W % 16 == 0 && N % 4 == 0 && K >= 1024) {
+    int rc = gemm_tc(SPB_F32, M, N, K, A, lda, 0, W, ldw, 0, part, N, nullptr, 0, st);
+    if (rc) return rc;
+    const int64_t total = (int64_t)M * N;
+    small_m_reduce_kernel<__nv_bfloat16><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(part, 1, (__nv_bfloat16*)D, ldd, (const __nv_bfloat16*)bias,
+                                                                                      (const __nv_bfloat16*)res, ldr, M, N);
+    SPB_LAUNCH_CHECK();
+    return 0;
+  }
   if (dtype == SPB_BF16)
     return small_m_gemm_t<__nv_bfloat16>(M, N, K, (const __nv_bfloat16*)A, lda, (const __nv_bfloat16*)W, ldw, (__nv_bfloat16*)D, ldd,
                                          (const __nv_bfloat16*)bias, (const __nv_bfloat16*)res, ldr, part, st);
@@ -217,17 +297,33 @@ struct DecArgs {
   float scale;
 };
 
+// A CTA of 256 threads streams its slice of the cache in tiles of KT keys through a two-stage shared-memory ring filled with
+// 16-byte cp.async copies (coalesced: TPR consecutive threads cover one head row; a whole tile of K and of V - none of it
+// through registers - is in flight while the previous tile is being used).  Scores: two threads per key (interleaved 16-byte
+// pieces, one shuffle to combine); P.V: thread = 16-byte column piece of every G-th key.  Rows are padded by 32 bytes so
+// that both access patterns are free of bank conflicts.  One CTA per SM (the ring takes most of the shared memory); the
+// host picks the key split so that the grid is a single wave where it can.
+constexpr int DA_THREADS = 256;
+template <typename T, int HD>
+struct DecTile {
+  static constexpr int ROWB = HD * (int)sizeof(T) + 32;            // padded row pitch in bytes
+  static constexpr int KT = (2 * 2 * 128 * ROWB <= 200 * 1024) ? 128 : ((2 * 2 * 64 * ROWB <= 200 * 1024) ? 64 : 32);  // two stages of K and V must fit
+  static constexpr int STAGE_BYTES = 2 * KT * ROWB;
+};
+
 template <typename T, int HD, int RB>
-__global__ void __launch_bounds__(DEC_THREADS) attn_decode_kernel(const DecArgs p) {
+__global__ void __launch_bounds__(DA_THREADS) attn_decode_kernel(const DecArgs p) {
   constexpr int VE = Vec16<T>::N;
-  constexpr int TPR = HD / VE;              // threads per V row
-  constexpr int G = DEC_THREADS / TPR;      // V rows in flight
-  constexpr int KT = DEC_THREADS;           // keys per tile
-  static_assert(DEC_THREADS % TPR == 0 && TPR >= 1, "head dim does not tile the CTA");
+  constexpr int TPR = HD / VE;              // 16-byte pieces (threads) per head row
+  constexpr int G = DA_THREADS / TPR;       // rows covered per pass of the CTA
+  constexpr int KT = DecTile<T, HD>::KT;
+  constexpr int ROWB = DecTile<T, HD>::ROWB;
+  constexpr int NW = DA_THREADS / 32;
+  static_assert(DA_THREADS % TPR == 0 && TPR % 2 == 0, "head dim does not tile the CTA");
   __shared__ float qs[RB][HD];
   __shared__ float ps[RB][KT];
-  __shared__ float red[2][4][RB];
-  extern __shared__ float osum[];  // [G][RB][HD] for the final cross-group reduction
+  __shared__ float red[2][NW][RB];
+  extern __shared__ __align__(16) uint8_t dsm[];  // [2 stages][K tile [KT][ROWB] | V tile [KT][ROWB]]; reused for the final reduction
 
   const int split = blockIdx.x;
   const int g = blockIdx.y / p.row_groups, rg = blockIdx.y % p.row_groups;
@@ -237,9 +333,27 @@ __global__ void __launch_bounds__(DEC_THREADS) attn_decode_kernel(const DecArgs 
   const int r0 = rg * RB;
   const int nr = min(RB, rtot - r0);
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const T* kbase = (const T*)p.k + (int64_t)b * p.kbs + (int64_t)g * HD;
+  const T* vbase = (const T*)p.v + (int64_t)b * p.vbs + (int64_t)g * HD;
+  const int vg = t / TPR, vc = (t % TPR) * VE;
+  const int tile0 = split * p.tiles_per_split;
+  const int tile1 = min(tile0 + p.tiles_per_split, (p.Tk + KT - 1) / KT);
+
+  auto stage_tile = [&](int tile) {  // one cp.async group per tile: K and V rows of the tile -> stage (tile - tile0) & 1
+    const int k0 = tile * KT, kn = min(KT, p.Tk - k0);
+    uint8_t* sK = dsm + ((tile - tile0) & 1) * DecTile<T, HD>::STAGE_BYTES;
+    uint8_t* sV = sK + KT * ROWB;
+    for (int jj = vg; jj < kn; jj += G) {
+      cp_async16(sK + jj * ROWB + vc * (int)sizeof(T), kbase + (int64_t)(k0 + jj) * p.ldk + vc);
+      cp_async16(sV + jj * ROWB + vc * (int)sizeof(T), vbase + (int64_t)(k0 + jj) * p.ldv + vc);
+    }
+    cp_async_commit();
+  };
+  if (tile0 < tile1) stage_tile(tile0);
+  if (tile0 + 1 < tile1) stage_tile(tile0 + 1);
 
   // the group's query rows -> shared memory, pre-multiplied by the score scale.  Row r = (local q head, tq).
-  for (int i = t; i < RB * HD; i += DEC_THREADS) {
+  for (int i = t; i < RB * HD; i += DA_THREADS) {
     const int r = i / HD, d = i % HD;
     float qv = 0.f;
     if (r < nr) {
@@ -248,11 +362,7 @@ __global__ void __launch_bounds__(DEC_THREADS) attn_decode_kernel(const DecArgs 
     }
     qs[r][d] = qv;
   }
-  __syncthreads();
 
-  const T* kbase = (const T*)p.k + (int64_t)b * p.kbs + (int64_t)g * HD;
-  const T* vbase = (const T*)p.v + (int64_t)b * p.vbs + (int64_t)g * HD;
-  const int vg = t / TPR, vc = (t % TPR) * VE;
   float m_run[RB], l_run[RB], acc[RB][VE];
 #pragma unroll
   for (int r = 0; r < RB; ++r) {
@@ -261,85 +371,75 @@ __global__ void __launch_bounds__(DEC_THREADS) attn_decode_kernel(const DecArgs 
 #pragma unroll
     for (int e = 0; e < VE; ++e) acc[r][e] = 0.f;
   }
-  const int tile0 = split * p.tiles_per_split;
-  const int tile1 = min(tile0 + p.tiles_per_split, (p.Tk + KT - 1) / KT);
+  const int key = t >> 1, half = t & 1;  // score phase: two threads per key, 16-byte pieces 2i + half
   for (int tile = tile0; tile < tile1; ++tile) {
     const int k0 = tile * KT;
-    const int j = k0 + t;
-    // ---- scores of key j against the group's rows
+    const int kn = min(KT, p.Tk - k0);
+    const uint8_t* sK = dsm + ((tile - tile0) & 1) * DecTile<T, HD>::STAGE_BYTES;
+    const uint8_t* sV = sK + KT * ROWB;
+    if (tile + 1 < tile1) cp_async_wait<1>(); else cp_async_wait<0>();  // this thread's copies of this tile have landed
+    __syncthreads();                                                    // everybody's (and qs)
+    // ---- scores
     float s[RB];
 #pragma unroll
     for (int r = 0; r < RB; ++r) s[r] = 0.f;
-    if (j < p.Tk) {
-      const T* kr = kbase + (int64_t)j * p.ldk;
-      constexpr int NV = HD / VE;
-      constexpr int CH = NV < 8 ? NV : 8;  // 16-byte loads in flight per thread
+    if (key < kn) {
+      const uint8_t* kr = sK + key * ROWB;
 #pragma unroll
-      for (int c0 = 0; c0 < NV; c0 += CH) {
-        float kv[CH][VE];
+      for (int i = 0; i < TPR / 2; ++i) {
+        const int c = 2 * i + half;
+        float kv[VE];
+        smem_vec<T>(kr + c * 16, kv);
 #pragma unroll
-        for (int c = 0; c < CH; ++c) Vec16<T>::load(kr + (c0 + c) * VE, kv[c]);
+        for (int e = 0; e < VE; e += 4) {
 #pragma unroll
-        for (int c = 0; c < CH; ++c)
-#pragma unroll
-          for (int e = 0; e < VE; e += 4) {
-#pragma unroll
-            for (int r = 0; r < RB; ++r) {
-              const float4 qv = *reinterpret_cast<const float4*>(&qs[r][(c0 + c) * VE + e]);
-              s[r] = fmaf(qv.x, kv[c][e], fmaf(qv.y, kv[c][e + 1], fmaf(qv.z, kv[c][e + 2], fmaf(qv.w, kv[c][e + 3], s[r]))));
-            }
+          for (int r = 0; r < RB; ++r) {
+            const float4 qv = *reinterpret_cast<const float4*>(&qs[r][c * VE + e]);
+            s[r] = fmaf(qv.x, kv[e], fmaf(qv.y, kv[e + 1], fmaf(qv.z, kv[e + 2], fmaf(qv.w, kv[e + 3], s[r]))));
           }
+        }
       }
-    } else {
-#pragma unroll
-      for (int r = 0; r < RB; ++r) s[r] = -INFINITY;
     }
-    // ---- tile max per row
+#pragma unroll
+    for (int r = 0; r < RB; ++r) {  // the two halves of a key (all lanes take part: no shuffle under divergence)
+      s[r] += __shfl_xor_sync(0xffffffffu, s[r], 1);
+      if (key >= kn) s[r] = -INFINITY;
+    }
+    // ---- tile max per row (both threads of a key hold the same score)
 #pragma unroll
     for (int r = 0; r < RB; ++r) {
       const float wm = warp_max(s[r]);
       if (lane == 0) red[0][warp][r] = wm;
     }
-    __syncthreads();  // also: the previous tile's P*V readers are done with ps
+    __syncthreads();
     float alpha[RB];
 #pragma unroll
     for (int r = 0; r < RB; ++r) {
-      const float tm = fmaxf(fmaxf(red[0][0][r], red[0][1][r]), fmaxf(red[0][2][r], red[0][3][r]));
+      float tm = red[0][0][r];
+#pragma unroll
+      for (int w = 1; w < NW; ++w) tm = fmaxf(tm, red[0][w][r]);
       const float mn = fmaxf(m_run[r], tm);
       alpha[r] = (m_run[r] == -INFINITY) ? 0.f : __expf(m_run[r] - mn);
       m_run[r] = mn;
-      const float pv = (s[r] == -INFINITY) ? 0.f : __expf(s[r] - mn);
-      ps[r][t] = pv;
+      const float pv = (s[r] == -INFINITY || half) ? 0.f : __expf(s[r] - mn);  // one of the two threads of a key contributes
+      if (!half && key < KT) ps[r][key] = pv;
       const float wsum = warp_sum(pv);
       if (lane == 0) red[1][warp][r] = wsum;
     }
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < RB; ++r) {
-      l_run[r] = l_run[r] * alpha[r] + (red[1][0][r] + red[1][1][r] + red[1][2][r] + red[1][3][r]);
+      float ts = red[1][0][r];
+#pragma unroll
+      for (int w = 1; w < NW; ++w) ts += red[1][w][r];
+      l_run[r] = l_run[r] * alpha[r] + ts;
 #pragma unroll
       for (int e = 0; e < VE; ++e) acc[r][e] *= alpha[r];
     }
-    // ---- acc[r][.] += sum_j P[r][j] * V[j][vc ..]: thread owns a 16-byte column piece, G keys in flight per pass
-    const int kn = min(KT, p.Tk - k0);
-    constexpr int UN = 4;
-    int jj = vg;
-    for (; jj + (UN - 1) * G < kn; jj += UN * G) {
-      float vv[UN][VE];
-#pragma unroll
-      for (int u = 0; u < UN; ++u) Vec16<T>::load(vbase + (int64_t)(k0 + jj + u * G) * p.ldv + vc, vv[u]);
-#pragma unroll
-      for (int u = 0; u < UN; ++u)
-#pragma unroll
-        for (int r = 0; r < RB; ++r) {
-          const float pv = ps[r][jj + u * G];
-#pragma unroll
-          for (int e = 0; e < VE; ++e) acc[r][e] = fmaf(pv, vv[u][e], acc[r][e]);
-        }
-    }
-    for (; jj < kn; jj += G) {
+    // ---- acc[r][.] += sum_j P[r][j] * V[j][vc ..]: thread owns a 16-byte column piece of every G-th key
+    for (int jj = vg; jj < kn; jj += G) {
       float vv[VE];
-      Vec16<T>::load(vbase + (int64_t)(k0 + jj) * p.ldv + vc, vv);
+      smem_vec<T>(sV + jj * ROWB + vc * (int)sizeof(T), vv);
 #pragma unroll
       for (int r = 0; r < RB; ++r) {
         const float pv = ps[r][jj];
@@ -347,15 +447,17 @@ __global__ void __launch_bounds__(DEC_THREADS) attn_decode_kernel(const DecArgs 
         for (int e = 0; e < VE; ++e) acc[r][e] = fmaf(pv, vv[e], acc[r][e]);
       }
     }
+    __syncthreads();  // this stage (and ps) is free again
+    if (tile + 2 < tile1) stage_tile(tile + 2);
   }
-  // ---- sum the G key groups' accumulators, write this split's partial (unnormalised O, m, l)
-  __syncthreads();
+  // ---- sum the G key groups' accumulators (through the tile buffer), write this split's partial (unnormalised O, m, l)
+  float* osum = reinterpret_cast<float*>(dsm);  // [G][RB][HD]
 #pragma unroll
   for (int r = 0; r < RB; ++r)
 #pragma unroll
     for (int e = 0; e < VE; ++e) osum[((int64_t)vg * RB + r) * HD + vc + e] = acc[r][e];
   __syncthreads();
-  for (int i = t; i < nr * HD; i += DEC_THREADS) {
+  for (int i = t; i < nr * HD; i += DA_THREADS) {
     const int r = i / HD, d = i % HD;
     float o = 0.f;
 #pragma unroll
@@ -401,24 +503,38 @@ __global__ void __launch_bounds__(128) attn_decode_combine_kernel(const float* _
   if (lse != nullptr && threadIdx.x == 0) lse[row] = M + logf(L);
 }
 
-static void decode_plan(int B, int Tq, int Hq, int Hkv, int Tk, int& RB, int& row_groups, int& splits, int& tiles_per_split) {
+static int decode_kt(int dtype, int hd) {  // DecTile<T, HD>::KT on the host
+  const int rowb = hd * (dtype == SPB_BF16 ? 2 : 4) + 32;
+  return (2 * 2 * 128 * rowb <= 200 * 1024) ? 128 : ((2 * 2 * 64 * rowb <= 200 * 1024) ? 64 : 32);
+}
+
+// One CTA per SM: choose the key split so that the grid is one wave (or whole waves) of the machine where the tile count allows.
+static void decode_plan(int dtype, int hd, int B, int Tq, int Hq, int Hkv, int Tk, int& RB, int& row_groups, int& splits, int& tiles_per_split) {
   const int rtot = (Hq / Hkv) * Tq;
   RB = rtot >= 8 ? 8 : (rtot > 2 ? 4 : (rtot > 1 ? 2 : 1));
   row_groups = (rtot + RB - 1) / RB;
-  const int tiles = (Tk + DEC_THREADS - 1) / DEC_THREADS;
+  const int kt = decode_kt(dtype, hd);
+  const int tiles = (Tk + kt - 1) / kt;
   const int ctas = B * Hkv * row_groups;
-  int want = (4 * sm_count() + ctas - 1) / ctas;  // ~4 CTAs per SM
+  const int sms = sm_count();
+  int want = sms / ctas;               // splits that still fit one wave
+  if (want < 1) want = 1;
   if (want > tiles) want = tiles;
   if (want > 64) want = 64;
-  if (want < 1) want = 1;
   tiles_per_split = (tiles + want - 1) / want;
   splits = (tiles + tiles_per_split - 1) / tiles_per_split;
 }
 
 size_t attn_decode_scratch_bytes(int B, int Tq, int Hq, int Hkv, int hd, int Tk) {
-  int RB, rgs, splits, tps;
-  decode_plan(B, Tq, Hq, Hkv, Tk, RB, rgs, splits, tps);
-  return (size_t)B * Hq * Tq * splits * ((size_t)hd + 2) * sizeof(float) + 256;
+  // worst case over both element types (the split count does not depend on the type except through the tile height)
+  size_t worst = 0;
+  for (int dtype = 0; dtype < 2; ++dtype) {
+    int RB, rgs, splits, tps;
+    decode_plan(dtype, hd, B, Tq, Hq, Hkv, Tk, RB, rgs, splits, tps);
+    const size_t b = (size_t)B * Hq * Tq * splits * ((size_t)hd + 2) * sizeof(float) + 256;
+    if (b > worst) worst = b;
+  }
+  return worst;
 }
 
 bool attn_decode_supported(int dtype, int hd) {
@@ -427,11 +543,12 @@ bool attn_decode_supported(int dtype, int hd) {
 
 template <typename T, int HD, int RB>
 static int attn_decode_launch_rb(const DecArgs& a, cudaStream_t st) {
-  constexpr int G = DEC_THREADS / (HD / Vec16<T>::N);
-  const size_t dyn = (size_t)G * RB * HD * sizeof(float);
+  constexpr int G = DA_THREADS / (HD / Vec16<T>::N);
+  size_t dyn = 2 * (size_t)DecTile<T, HD>::STAGE_BYTES;
+  if ((size_t)G * RB * HD * sizeof(float) > dyn) dyn = (size_t)G * RB * HD * sizeof(float);  // final reduction reuses the buffer
   SPB_CUDA(cudaFuncSetAttribute(attn_decode_kernel<T, HD, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
   dim3 grid(a.splits, a.Hkv * a.row_groups, a.B);
-  attn_decode_kernel<T, HD, RB><<<grid, DEC_THREADS, dyn, st>>>(a);
+  attn_decode_kernel<T, HD, RB><<<grid, DA_THREADS, dyn, st>>>(a);
   SPB_LAUNCH_CHECK();
   return 0;
 }
@@ -458,7 +575,7 @@ int attn_decode(int dtype, int B, int Tq, int Hq, int Hkv, int hd, int Tk, float
   SPB_CHECK_ARG((int64_t)B * Hq * Tq < (1LL << 31) && B <= 65535 && Tq >= 1 && Tk >= 1, SPB_E_LIMIT, "attention decode: size beyond the grid limits");
   DecArgs a;
   int RB;
-  decode_plan(B, Tq, Hq, Hkv, Tk, RB, a.row_groups, a.splits, a.tiles_per_split);
+  decode_plan(dtype, hd, B, Tq, Hq, Hkv, Tk, RB, a.row_groups, a.splits, a.tiles_per_split);
   SPB_CHECK_ARG((int64_t)Hkv * a.row_groups <= 65535, SPB_E_LIMIT, "attention decode: too many query rows per kv head");
   a.q = q; a.ldq = ldq; a.k = k; a.v = v; a.ldk = ldk; a.ldv = ldv; a.kbs = kbs; a.vbs = vbs;
   a.B = B; a.Tq = Tq; a.Hq = Hq; a.Hkv = Hkv; a.Tk = Tk; a.scale = scale;

@@ -211,6 +211,7 @@ template <int NCOLS>
 __device__ __forceinline__ void gemm_tc_drain(const GemmTcArgs& p, const CUtensorMap* tmD, int atomic, int m0, int n0, uint32_t taddr,
                                               uint8_t* warp_buf, int q, int lane) {
   const int row = m0 + q * 32 + lane;
+  if (m0 + q * 32 >= p.M) return;  // warp-uniform: this warp's 32 rows lie past the last row (small-M problems)
 #pragma unroll 1
       for (int c = 0; c < NCOLS / 32; ++c) {
         const int col0 = n0 + c * 32;
