@@ -430,9 +430,31 @@ static int block_bwd_impl(const spb_block_desc* d, const spb_block_params* p, co
   void* partial = w8 + L.partial;
   cudaStream_t st = (cudaStream_t)stream;
 
-  // 1. d(attn_o) = dy . wo^T
+  // 1. d(attn_o) = dy . wo^T.  When both the GEMM and the attention backward are the tcgen05 kernels, the backward's
+  //    preparation (delta = rowsum(dO * O) per head, zeroed fp32 dq accumulator) rides in this GEMM's epilogue: its threads
+  //    hold each dO row anyway, the epilogue has > 10x slack under the main loop, and two passes over HBM (a 134 MB memset and a
+  //    kernel over o and dO: ~50 us of the C3 step) disappear.  SPB_BWD_FUSE_PREP=0 keeps them separate (A/B timing).
   prof_mark("gemm_dattn", st);
-  rc = spb_gemm(dt, dt, gimpl, N, Nq, d->C, dy, d->C, 0, p->wo, p->ldw_o, in_out ? 1 : 0, w8 + L.dattn_o, Nq, nullptr, 0, stream);
+  static const bool fuse_prep_env = [] {
+    const char* e = getenv("SPB_BWD_FUSE_PREP");
+    return e == nullptr || atoi(e) != 0;
+  }();
+  const bool fuse_prep = fuse_prep_env && dt == SPB_BF16 && pick_gemm_impl(gimpl, dt) == SPB_IMPL_TCGEN05 &&
+                         pick_attn_bwd_impl(d->attn_impl, dt, d->hd) == SPB_IMPL_TCGEN05 && flash_bwd_tc_supported(dt, d->hd);
+  if (fuse_prep) {
+    GemmTcFuse fz;
+    fz.o = w8 + L.attn_o;
+    fz.ldo = Nq;
+    fz.delta = (float*)(w8 + L.delta);
+    fz.zero = (float*)(w8 + L.dq_acc);
+    fz.ldz = Nq;
+    fz.hd = d->hd;
+    fz.T = d->T;
+    fz.H = d->Hq;
+    rc = gemm_tc(dt, N, Nq, d->C, dy, d->C, 0, p->wo, p->ldw_o, in_out ? 1 : 0, w8 + L.dattn_o, Nq, nullptr, 0, st, nullptr, 0, 0, 0, nullptr, 0, &fz);
+  } else {
+    rc = spb_gemm(dt, dt, gimpl, N, Nq, d->C, dy, d->C, 0, p->wo, p->ldw_o, in_out ? 1 : 0, w8 + L.dattn_o, Nq, nullptr, 0, stream);
+  }
   if (rc) return rc;
   static const bool dwo_early = [] {
     const char* e = getenv("SPB_BWD_DWO_EARLY");
@@ -484,7 +506,7 @@ static int block_bwd_impl(const spb_block_desc* d, const spb_block_params* p, co
   rc = flash_bwd_any(dt, d->attn_impl, d->B, d->T, d->Hq, d->Hkv, d->hd, d->causal, d->scale, qkv, Ntot, qkv + Nq * e, Ntot,
                      qkv + (Nq + Nkv) * e, Ntot, w8 + L.attn_o, Nq, w8 + L.dattn_o, Nq, (const float*)(w8 + L.lse),
                      (float*)(w8 + L.delta), dqkv, Ntot, dqkv + Nq * e, Ntot, dqkv + (Nq + Nkv) * e, Ntot, (float*)(w8 + L.dq_acc), stream,
-                     d->rope_kind == SPB_ROPE_TABLE ? p->rope : nullptr);
+                     d->rope_kind == SPB_ROPE_TABLE ? p->rope : nullptr, fuse_prep ? FB_PHASE_MAIN : (FB_PHASE_PRE | FB_PHASE_MAIN));
   if (rc) return rc;
   // 5. qkv bias gradients
   prof_mark("bias_grad", st);

@@ -14,6 +14,7 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "kernels.h"
 
 namespace spb {
 
@@ -31,6 +32,14 @@ struct GemmTcArgs {
   int64_t ld_add;      //            (the residual stream: y = x + attn . wo)
   int M, N;
   int a_mn, b_mn;
+  // optional attention-backward preparation fused into the d(attn_o) = dy . wo^T GEMM (GemmTcFuse): while a thread holds the
+  // fp32 accumulators of its row it also forms delta[b,h,t] = sum_c dO[n,c] * O[n,c] per head and zeroes the fp32 dq accumulator
+  const __nv_bfloat16* fuse_o;
+  int64_t fuse_ldo;
+  float* fuse_delta;
+  float* fuse_zero;
+  int64_t fuse_ldz;
+  int fuse_hd, fuse_T, fuse_H;
   // work items: the first `full_tiles` tiles (whole waves) run over the whole K range; the remaining tail tiles are each
   // split along K into `tail_parts` parts that add into a pre-zeroed fp32 output with atomics, so the last, partial wave
   // costs 1/tail_parts of a wave (also covers few-tile weight gradients: full_tiles = 0).
@@ -212,12 +221,23 @@ __device__ __forceinline__ void gemm_tc_drain(const GemmTcArgs& p, const CUtenso
                                               uint8_t* warp_buf, int q, int lane) {
   const int row = m0 + q * 32 + lane;
   if (m0 + q * 32 >= p.M) return;  // warp-uniform: this warp's 32 rows lie past the last row (small-M problems)
+  float dsum = 0.f;  // running sum_c dO * O of the current head (fuse_o != NULL)
 #pragma unroll 1
       for (int c = 0; c < NCOLS / 32; ++c) {
         const int col0 = n0 + c * 32;
         if (col0 >= p.N) break;  // warp-uniform
         uint32_t r[32];
         SPB_TMEM_LD_32(taddr + (uint32_t)(c * 32), r);
+        uint4 ov[4];
+        const bool fuse = p.fuse_o != nullptr && row < p.M;  // N % 32 == 0 and 16-byte aligned rows are checked by the launcher
+        if (fuse) {  // the O chunk of this row: in flight while the accumulators arrive from tensor memory
+          const uint4* op = reinterpret_cast<const uint4*>(p.fuse_o + (int64_t)row * p.fuse_ldo + col0);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) ov[i] = __ldg(op + i);
+          float4* zp = reinterpret_cast<float4*>(p.fuse_zero + (int64_t)row * p.fuse_ldz + col0);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) zp[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         const uint8_t* rope_row = nullptr;
         if (p.rope != nullptr && col0 < p.rope_cols) {  // warp-uniform
           // stage table[t(row)][pair0 .. pair0+15] for the warp's 32 rows: 2 rows (2 x 256 B) per load instruction
@@ -241,6 +261,24 @@ __device__ __forceinline__ void gemm_tc_drain(const GemmTcArgs& p, const CUtenso
           rope_row = wbuf;
         }
         tmem_ld_wait();
+        if (fuse) {
+          // the same rounding the attention backward sees: dO as the bf16 value that is stored
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint32_t w[4] = {ov[i].x, ov[i].y, ov[i].z, ov[i].w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float2 o2 = unpack_bf16(w[j]);
+              const float2 d2 = unpack_bf16(pack_bf16(__uint_as_float(r[i * 8 + 2 * j]), __uint_as_float(r[i * 8 + 2 * j + 1])));
+              dsum = fmaf(o2.x, d2.x, fmaf(o2.y, d2.y, dsum));
+            }
+          }
+          if ((col0 + 32) % p.fuse_hd == 0) {  // last chunk of a head
+            const int h = col0 / p.fuse_hd;
+            p.fuse_delta[((int64_t)(row / p.fuse_T) * p.fuse_H + h) * p.fuse_T + row % p.fuse_T] = dsum;
+            dsum = 0.f;
+          }
+        }
         if (atomic && p.vec_ok) gemm_tc_reduce_chunk(tmD, m0 + q * 32, col0, r, warp_buf, c, lane);
         else if (atomic) gemm_tc_atomic_chunk(p, m0 + q * 32, col0, r, reinterpret_cast<float*>(warp_buf), lane);
         else if (row < p.M) gemm_tc_store_chunk(p, row, col0, r, rope_row, lane, 0);
@@ -699,7 +737,7 @@ static double gemm_tc_wave_eff(int64_t M, int64_t N, int bn, int G) {
 
 int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb,
             int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st, const float* rope, int rope_cols,
-            int rope_T, int rope_hd, const void* residual, int64_t ldr) {
+            int rope_T, int rope_hd, const void* residual, int64_t ldr, const GemmTcFuse* fuse) {
   SPB_CHECK_ARG(M < (1LL << 31) && N < (1LL << 31) && K < (1LL << 31), SPB_E_LIMIT, "gemm_tc: dimension beyond 2^31");
   SPB_CHECK_ARG(M > 0 && N > 0 && K > 0, SPB_E_INVALID, "gemm_tc: empty problem");
   SPB_CHECK_ARG(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && (lda % 8 == 0) && (ldb % 8 == 0), SPB_E_UNSUPPORTED,
@@ -722,6 +760,22 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
   args.ld_add = ldr;
   args.M = (int)M;
   args.N = (int)N;
+  if (fuse != nullptr) {
+    SPB_CHECK_ARG(out_dtype == SPB_BF16 && bias == nullptr && rope == nullptr && !accumulate && residual == nullptr, SPB_E_INVALID,
+                  "gemm_tc: the attention-backward preparation epilogue takes a plain bf16 GEMM");
+    SPB_CHECK_ARG(fuse->hd % 32 == 0 && N % fuse->hd == 0 && (256 % fuse->hd == 0 || fuse->hd % 256 == 0) && M % fuse->T == 0 && N == (int64_t)fuse->H * fuse->hd,
+                  SPB_E_INVALID, "gemm_tc: fused delta needs hd %% 32 == 0, N = H*hd and M = B*T");
+    SPB_CHECK_ARG((uintptr_t)fuse->o % 16 == 0 && fuse->ldo % 8 == 0 && (uintptr_t)fuse->zero % 16 == 0 && fuse->ldz % 4 == 0, SPB_E_INVALID,
+                  "gemm_tc: fused delta operands must be 16-byte aligned");
+    args.fuse_o = (const __nv_bfloat16*)fuse->o;
+    args.fuse_ldo = fuse->ldo;
+    args.fuse_delta = fuse->delta;
+    args.fuse_zero = fuse->zero;
+    args.fuse_ldz = fuse->ldz;
+    args.fuse_hd = fuse->hd;
+    args.fuse_T = fuse->T;
+    args.fuse_H = fuse->H;
+  }
   // transA=0: A stored [M,K] -> K-major.  transA=1: stored [K,M] -> MN-major.
   // transB=0: B stored [K,N] -> MN-major (N contiguous).  transB=1: stored [N,K] -> K-major.
   args.a_mn = transA ? 1 : 0;

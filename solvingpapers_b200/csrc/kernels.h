@@ -8,10 +8,22 @@ namespace spb {
 int gemm_simt(int in_dtype, int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B,
               int64_t ldb, int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st,
               const void* residual = nullptr, int64_t ldr = 0);
+// Attention-backward preparation fused into the epilogue of the d(attn_o) = dy . wo^T GEMM (D = dO [B*T, H*hd] bf16):
+// delta[b,h,t] = sum_c dO[n, h*hd + c] * o[n, h*hd + c] and zero[n, :] = 0 (the fp32 dq accumulator) - what
+// flash_bwd_tc's FB_PHASE_PRE (a memset + a kernel over o and dO) otherwise does in two extra passes over HBM.
+struct GemmTcFuse {
+  const void* o;   // attention output [B*T, H*hd] bf16, row stride ldo
+  int64_t ldo;
+  float* delta;    // [B, H, T] fp32
+  float* zero;     // [B*T, H*hd] fp32, row stride ldz
+  int64_t ldz;
+  int hd, T, H;
+};
 // rope != nullptr: fused rotary epilogue on output columns < rope_cols (row n has position n % rope_T)
 int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb,
             int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st, const float* rope = nullptr,
-            int rope_cols = 0, int rope_T = 0, int rope_hd = 0, const void* residual = nullptr, int64_t ldr = 0);
+            int rope_cols = 0, int rope_T = 0, int rope_hd = 0, const void* residual = nullptr, int64_t ldr = 0,
+            const GemmTcFuse* fuse = nullptr);
 // residual != nullptr (both GEMMs): D = A.B (+bias) + residual, residual [M,N] of D's type with row stride ldr
 
 int attn_simt_fwd(int dtype, int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq,
