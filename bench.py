@@ -65,6 +65,9 @@ def parse():
                     help="also run the step back to back for this many seconds (untimed warm-up excluded) and report the power-limited "
                          "steady state as `sustained` next to the short timed region (0 = skip)")
     ap.add_argument("--no-host-ceiling", action="store_true", help="skip the copy-only measurement of the host<->device ceiling")
+    ap.add_argument("--reg-grads", default="on", choices=["on", "off"],
+                    help="N > 1: weight-gradient buffers from spb_comm_alloc (NCCL allocator + registration: the all-reduce works in place) "
+                         "or plain torch allocations")
     ap.add_argument("--residual", default="off", choices=["off", "fused", "separate"],
                     help="SURVEY 8 row f1: also produce h = x + block(x) and dx + dy - inside the kernels' epilogues (fused) or "
                          "with two extra element-wise passes after the block (separate); off = the block alone (headline)")
@@ -401,6 +404,12 @@ def run_ours(args):
     blk = sp.AttentionBlock(cfg, device=device, comm=comm.handle if comm else None)
     grads = blk.alloc_grads(params)
     grads["dx"] = torch.empty_like(x)
+    grad_mem = "torch allocator"
+    if comm is not None and args.reg_grads == "on":
+        for name in ("dwqkv", "dwo"):
+            if name in grads:
+                grads[name] = comm.alloc(tuple(grads[name].shape))
+        grad_mem = "spb_comm_alloc: " + comm.buffer_kind(grads["dwo"])
     tokens_local = B * T
     h_sep = torch.empty_like(x) if args.residual == "separate" else None
 
@@ -638,7 +647,7 @@ def run_ours(args):
     out = {"metric": "attn_block_fwd_bwd_tokens_per_s", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": K, "warmup": W,
            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dt, "data": "synthetic",
            "config": {"workload": desc, "global_batch": B * world, "seq_len": T, "parallelism": f"dp{world}" if world > 1 else "single",
-                      "l2": "per-step working set > 126 MB L2, no flush", "attn_impl": "auto", "residual": args.residual, "flops_per_step_per_gpu": total_flops},
+                      "l2": "per-step working set > 126 MB L2, no flush", "attn_impl": "auto", "residual": args.residual, "grad_buffers": grad_mem, "flops_per_step_per_gpu": total_flops},
            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "block_tflops": whole,
            "stages_ms": {k: round(v, 4) for k, v in sorted(stage_ms.items())}, "stage_rates": stage_rates, "sustained": sustained}
 

@@ -317,6 +317,18 @@ int spb_comm_unique_id(void* out128);                        /* HOST buffer, 128
 int spb_comm_init_rank(const void* id128, int nranks, int rank, void** comm_out);
 int spb_comm_allreduce_f32(void* comm, float* const* ptrs, const size_t* counts, int n, spb_stream_t stream);
 int spb_comm_destroy(void* comm);
+/* one communicator per device 0..ndev-1 of THIS process (ncclCommInitAll): the single-process harness of SURVEY 8b/8e.
+ * A communicator handle is used by one host thread at a time (XLA calls from one thread per device: one handle each).  */
+int spb_comm_init_all(int ndev, void** comms_out);
+/* Gradient buffers the all-reduce can work on IN PLACE: memory from NCCL's allocator (cuMem, multicast-capable) registered
+ * with the communicator (symmetric window where this NCCL offers it, plain registration otherwise), so the NVLink-switch
+ * reduction reads and writes the gradients directly instead of staging them through NCCL's own buffers - fewer CTAs taken
+ * from the GEMM the all-reduce overlaps, less HBM traffic.  Collective: every rank calls spb_comm_alloc in the same order with
+ * the same size.  Any device pointer still works with spb_block_bwd; registered ones are faster.  Freed by spb_comm_free or
+ * spb_comm_destroy.  spb_comm_buffer_kind: 0 not registered, 1 registered, 2 symmetric window.                          */
+int spb_comm_alloc(void* comm, size_t bytes, void** ptr_out);
+int spb_comm_free(void* comm, void* ptr);
+int spb_comm_buffer_kind(void* comm, const void* ptr);
 
 #ifdef __cplusplus
 }

@@ -103,6 +103,10 @@ SIGNATURES = {
     "spb_comm_init_rank": (C.c_int, [vp, C.c_int, C.c_int, C.POINTER(vp)]),
     "spb_comm_allreduce_f32": (C.c_int, [vp, C.POINTER(vp), C.POINTER(sz), C.c_int, vp]),
     "spb_comm_destroy": (C.c_int, [vp]),
+    "spb_comm_init_all": (C.c_int, [C.c_int, C.POINTER(vp)]),
+    "spb_comm_alloc": (C.c_int, [vp, sz, C.POINTER(vp)]),
+    "spb_comm_free": (C.c_int, [vp, vp]),
+    "spb_comm_buffer_kind": (C.c_int, [vp, vp]),
 }
 
 _lib = None

@@ -582,13 +582,24 @@ static int block_bwd_impl(const spb_block_desc* d, const spb_block_params* p, co
     rc = do_dwo();
     if (rc) return rc;
   }
-  // 6. d(xhat) = dqkv . Wqkv^T
+  // 6. d(xhat) = dqkv . Wqkv^T.  With a communicator this GEMM shares the SMs with dWqkv's all-reduce on the side stream:
+  //    short-lived clusters instead of the persistent grid (8 GPUs, r02h: 0.365 -> 0.31 ms; the weight-gradient GEMMs keep
+  //    the persistent kernel and its K-split tail - the high-priority side stream gets dWo's all-reduce out of their way).
+  struct SharedSmHint {
+    bool on;
+    explicit SharedSmHint(bool o) : on(o) {
+      static const int tiles = [] { const char* e = getenv("SPB_GEMM_SHARED_TILES"); return e ? atoi(e) : 2; }();
+      if (on) gemm_tc_hint_shared_sms(tiles);
+    }
+    ~SharedSmHint() { if (on) gemm_tc_hint_shared_sms(0); }
+  };
   prof_mark("gemm_dx", st);
   void* dxhat = (d->norm_kind != SPB_NORM_NONE) ? (void*)(w8 + L.dxhat) : g->dx;
   const int tBx = in_out ? 1 : 0;
   // residual = 1: dx = d(block)/dx + dy; without a norm the dx GEMM's epilogue adds dy, with one the norm VJP's dx store does
   const void* dx_res = (d->residual && d->norm_kind == SPB_NORM_NONE) ? dy : nullptr;
   if (dxhat != nullptr) {
+    SharedSmHint shared_sm_hint(comm != nullptr);
     if (packed) {
       rc = gemm_any(dt, dt, gimpl, N, d->C, Ntot, dqkv, Ntot, 0, wq, p->ldw_q, tBx, dxhat, d->C, nullptr, 0, st, nullptr, 0, 0, 0, dx_res, d->C);
       if (rc) return rc;

@@ -600,6 +600,14 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
   if (warp == 1) tmem_dealloc_2sm(tmem_base, Cfg::TMEM_COLS);
 }
 
+// Launch hint (thread-local, set by the block backward around the GEMMs that run while an all-reduce holds some SMs).
+// The persistent kernel hands tiles out statically (tile = pair, pair + npairs, ...): a cluster that cannot become resident
+// until the collective's CTAs leave still owns its full share, so the GEMM ends "collective time + own time" later
+// (8 GPUs, r02g: dWqkv 0.29 -> 0.52 ms).  With the hint the grid has one cluster per `tiles_per_cluster` tiles and the
+// hardware's block scheduler does the balancing: late SMs simply take fewer clusters.
+static thread_local int g_shared_sm_tiles = 0;
+void gemm_tc_hint_shared_sms(int tiles_per_cluster) { g_shared_sm_tiles = tiles_per_cluster; }
+
 static int gemm_tc2_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int64_t K, GemmTcArgs args, bool may_split,
                            cudaStream_t st) {
   using Cfg = GemmTc2Cfg;
@@ -610,6 +618,10 @@ static int gemm_tc2_launch(const void* A, int64_t lda, const void* B, int64_t ld
   const int tiles = args.num_m * args.num_n;
   int pairs = G / 2;
   if (pairs > tiles) pairs = tiles;
+  if (g_shared_sm_tiles > 0 && tiles > pairs) {  // SMs are shared with a collective: many short-lived clusters instead of a persistent grid
+    pairs = (tiles + g_shared_sm_tiles - 1) / g_shared_sm_tiles;
+    may_split = false;
+  }
   args.full_tiles = tiles;
   args.tail_parts = 1;
   args.kb_per_part = args.kb_total;

@@ -24,6 +24,8 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
             int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st, const float* rope = nullptr,
             int rope_cols = 0, int rope_T = 0, int rope_hd = 0, const void* residual = nullptr, int64_t ldr = 0,
             const GemmTcFuse* fuse = nullptr);
+// > 0: the CTA-pair GEMMs launched by this host thread use one cluster per `tiles_per_cluster` tiles (SMs shared with a collective)
+void gemm_tc_hint_shared_sms(int tiles_per_cluster);
 // residual != nullptr (both GEMMs): D = A.B (+bias) + residual, residual [M,N] of D's type with row stride ldr
 
 int attn_simt_fwd(int dtype, int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq,

@@ -58,6 +58,31 @@ class Communicator:
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         L.check(self.lib.spb_comm_allreduce_f32(C.c_void_p(self.handle), ptrs, counts, n, st), "spb_comm_allreduce_f32")
 
+    def alloc(self, shape, dtype=torch.float32):
+        """A tensor in memory that the communicator's all-reduce works on in place (spb_comm_alloc: NCCL allocator + window /
+        buffer registration).  Collective: every rank allocates the same sizes in the same order.  Lives until close()."""
+        n = 1
+        for d in shape:
+            n *= int(d)
+        esz = torch.empty((), dtype=dtype).element_size()
+        ptr = C.c_void_p()
+        L.check(self.lib.spb_comm_alloc(C.c_void_p(self.handle), n * esz, C.byref(ptr)), "spb_comm_alloc")
+        typestr = {torch.float32: "<f4", torch.bfloat16: "<u2", torch.uint8: "|u1"}[dtype]
+
+        class _Raw:
+            __cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr.value, False), "version": 2}
+
+        t = torch.as_tensor(_Raw(), device=torch.device("cuda", torch.cuda.current_device()))
+        if dtype == torch.bfloat16:
+            t = t.view(torch.bfloat16)
+        t = t.view(*shape)
+        self._bufs = getattr(self, "_bufs", [])
+        self._bufs.append(t)
+        return t
+
+    def buffer_kind(self, t):
+        return {0: "unregistered", 1: "registered", 2: "symmetric window"}[self.lib.spb_comm_buffer_kind(C.c_void_p(self.handle), C.c_void_p(t.data_ptr()))]
+
     def close(self):
         if getattr(self, "handle", None):
             self.lib.spb_comm_destroy(C.c_void_p(self.handle))
