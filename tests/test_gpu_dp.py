@@ -42,6 +42,27 @@ def test_block_bwd_with_size1_communicator_matches_no_communicator():
         comm.close()
 
 
+def test_registered_gradient_buffers_size1_communicator():
+    """spb_comm_alloc / spb_comm_free: memory from NCCL's allocator registered with the communicator, usable as an ordinary
+    tensor (the weight-gradient GEMMs write it, the all-reduce works on it in place)."""
+    from solvingpapers_b200 import dist as spd, ops
+    comm = spd.Communicator(0, 1)
+    try:
+        g = comm.alloc((256, 384))
+        assert g.shape == (256, 384) and g.dtype == torch.float32 and g.is_cuda and g.data_ptr() % 4096 == 0
+        assert comm.buffer_kind(g) in ("registered", "symmetric window", "unregistered")
+        a = torch.randn(512, 256, device="cuda").bfloat16()
+        b = torch.randn(512, 384, device="cuda").bfloat16()
+        ops.gemm(a, b, transA=True, out=g)                      # a weight-gradient GEMM straight into the registered buffer
+        ref = a.float().t() @ b.float()
+        comm.allreduce_([g])                                     # size-1 SUM: unchanged
+        torch.cuda.synchronize()
+        assert max_rel_err(g, ref) < 1e-5
+        assert comm.buffer_kind(torch.empty(4, device="cuda")) == "unregistered"
+    finally:
+        comm.close()
+
+
 def _two_rank_worker(rank, world, port, out):
     import os
     import torch.distributed as tdist
