@@ -66,7 +66,8 @@ typedef struct spb_block_desc {
   int32_t weight_layout;  /* SPB_W_IN_OUT | SPB_W_OUT_IN */
   int32_t qkv_bias;       /* 1: bq,bk,bv present (ViT in_proj_bias) */
   int32_t out_bias;       /* 1: bo present (GPT proj bias, ViT out_proj.bias) */
-  int32_t attn_impl;      /* SPB_IMPL_*: AUTO = tcgen05 flash kernels when dtype==bf16 and hd in {64,128,256}, else SIMT */
+  int32_t attn_impl;      /* SPB_IMPL_*: AUTO = tcgen05 flash kernels when dtype==bf16 and hd in {64,128,256}, the tcgen05 GEMM
+                             pipeline of spb_attn_wide_* when dtype==bf16 and hd > 256, else SIMT */
   int32_t gemm_impl;      /* SPB_IMPL_*: AUTO = tcgen05 GEMM when dtype==bf16, SIMT fp32 GEMM when dtype==f32 */
   int32_t residual;       /* 0: y = block(x) (what `attention` returns, llama3:809-829).  1: y = x + block(x), the caller's
                              `h = x + attention(...)` (llama3:885, gpt:420, gemma:335, ViT:222) fused into the output
@@ -120,6 +121,8 @@ typedef struct spb_ws_layout {
   size_t partial;  /* f32 partial sums (norm-weight / bias column reductions)                         */
   size_t partial_bytes;
   int64_t ld_qkv;  /* (Hq + 2*Hkv) * hd */
+  size_t attn_scratch;        /* scratch of the wide-head attention path (bf16, hd > 256); 0 bytes otherwise   */
+  size_t attn_scratch_bytes;
 } spb_ws_layout;
 
 /* ---- library ------------------------------------------------------------------------------------ */
@@ -196,6 +199,21 @@ int spb_flash_bwd(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, int32_t
                   const void* o, int64_t ldo, const void* d_o, int64_t lddo, const float* lse, float* delta,
                   void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv, float* dq_acc,
                   spb_stream_t stream);
+
+/* Attention for head dims the fused kernels cannot hold on chip (bf16, hd > 256, hd % 8 == 0; gemma/gemma.ipynb:218-259
+ * literal: 2 q heads and one shared k/v of width 768).  Same arguments and results as spb_flash_fwd / spb_flash_bwd plus
+ * `scratch` (spb_attn_wide_scratch_bytes, 256-byte aligned): per (batch, q head) and block of 2048 query rows the scores
+ * of the keys the block can see go through HBM once - S = Q K^T, softmax, O = P V, and in the backward dP = dO V^T,
+ * dV += P^T dO, dK += dS^T Q, dQ = dS K - with every contraction on the tcgen05 GEMM.  Scratch is O(2048 * T + T * hd),
+ * independent of B and the head counts; nothing O(T^2) is kept between forward and backward.                         */
+size_t spb_attn_wide_scratch_bytes(int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd);
+int spb_attn_wide_fwd(int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal, float scale, const void* q, int64_t ldq,
+                      const void* k, int64_t ldk, const void* v, int64_t ldv, void* o, int64_t ldo, float* lse, void* scratch,
+                      spb_stream_t stream);
+int spb_attn_wide_bwd(int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal, float scale, const void* q, int64_t ldq,
+                      const void* k, int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o, int64_t lddo,
+                      const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
+                      void* scratch, spb_stream_t stream);
 
 /* ---- the block ---------------------------------------------------------------------------------- */
 int spb_block_ws_layout(const spb_block_desc* d, spb_ws_layout* out);

@@ -37,7 +37,7 @@ class BlockGrads(C.Structure):
 class WsLayout(C.Structure):
     _fields_ = [("total", sz), ("xhat", sz), ("stats", sz), ("qkv", sz), ("attn_o", sz), ("lse", sz), ("delta", sz),
                 ("dattn_o", sz), ("dqkv", sz), ("dq_acc", sz), ("dxhat", sz), ("partial", sz), ("partial_bytes", sz),
-                ("ld_qkv", i64)]
+                ("ld_qkv", i64), ("attn_scratch", sz), ("attn_scratch_bytes", sz)]
 
 
 class FfnDesc(C.Structure):
@@ -87,6 +87,10 @@ SIGNATURES = {
                                 i64, vp, vp]),
     "spb_flash_bwd": (C.c_int, [C.c_int, C.c_int, i32, i32, i32, i32, i32, C.c_int, f32, vp, i64, vp, i64, vp, i64, vp,
                                 i64, vp, i64, vp, vp, vp, i64, vp, i64, vp, i64, vp, vp]),
+    "spb_attn_wide_scratch_bytes": (sz, [i32, i32, i32, i32, i32]),
+    "spb_attn_wide_fwd": (C.c_int, [i32, i32, i32, i32, i32, C.c_int, f32, vp, i64, vp, i64, vp, i64, vp, i64, vp, vp, vp]),
+    "spb_attn_wide_bwd": (C.c_int, [i32, i32, i32, i32, i32, C.c_int, f32, vp, i64, vp, i64, vp, i64, vp, i64, vp, i64, vp, vp, vp, i64, vp, i64,
+                                    vp, i64, vp, vp]),
     "spb_block_ws_layout": (C.c_int, [C.POINTER(BlockDesc), C.POINTER(WsLayout)]),
     "spb_block_fwd": (C.c_int, [C.POINTER(BlockDesc), C.POINTER(BlockParams), vp, vp, vp, vp]),
     "spb_block_bwd": (C.c_int, [C.POINTER(BlockDesc), C.POINTER(BlockParams), vp, vp, vp, C.POINTER(BlockGrads), vp, vp]),

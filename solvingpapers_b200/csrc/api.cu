@@ -127,6 +127,12 @@ static int pick_attn_bwd_impl(int impl, int dtype, int hd) {
   return impl;
 }
 
+// bf16 blocks whose head dim exceeds what the fused attention kernels hold on chip take the tcgen05 GEMM pipeline of attn_wide.cu
+static bool block_uses_wide_attn(const spb_block_desc* d) {
+  return (d->attn_impl == SPB_IMPL_AUTO || d->attn_impl == SPB_IMPL_TCGEN05) && attn_wide_supported(d->dtype, d->hd) &&
+         !flash_tc_supported(d->dtype, d->hd);
+}
+
 // GEMM dispatch shared by spb_gemm and the block: with `rope` the rotary runs as the in-place kernel right after the GEMM
 // (default) or in the tcgen05 epilogue on the fp32 accumulators (SPB_ROPE_FUSE=1).
 static int gemm_any(int in_dtype, int out_dtype, int impl, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA,
@@ -282,6 +288,29 @@ static int flash_bwd_any(int dtype, int impl, int32_t B, int32_t T, int32_t Hq, 
   return spb_rope_apply(dtype, dk, lddk, (int64_t)B * T, T, Hkv, hd, rope, 1, stream);
 }
 
+size_t spb_attn_wide_scratch_bytes(int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd) {
+  if (B <= 0 || T <= 0 || Hq <= 0 || Hkv <= 0 || hd <= 0) return 0;
+  return attn_wide_scratch_bytes(B, T, Hq, Hkv, hd);
+}
+
+int spb_attn_wide_fwd(int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal, float scale, const void* q, int64_t ldq, const void* k,
+                      int64_t ldk, const void* v, int64_t ldv, void* o, int64_t ldo, float* lse, void* scratch, spb_stream_t stream) {
+  SPB_CHECK_ARG(q && k && v && o && lse && scratch, SPB_E_INVALID, "spb_attn_wide_fwd: null pointer");
+  SPB_CHECK_ARG(B > 0 && T > 0 && Hq > 0 && Hkv > 0 && hd > 0 && Hq % Hkv == 0, SPB_E_INVALID, "spb_attn_wide_fwd: bad shape");
+  SPB_CHECK_ARG(attn_wide_supported(SPB_BF16, hd), SPB_E_UNSUPPORTED, "spb_attn_wide_fwd: bf16 with hd > 256 and hd %% 8 == 0 (hd=%d); smaller heads use spb_flash_fwd", hd);
+  return attn_wide_fwd(B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, scratch, (cudaStream_t)stream);
+}
+
+int spb_attn_wide_bwd(int32_t B, int32_t T, int32_t Hq, int32_t Hkv, int32_t hd, int causal, float scale, const void* q, int64_t ldq, const void* k,
+                      int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o, int64_t lddo, const float* lse,
+                      float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv, void* scratch, spb_stream_t stream) {
+  SPB_CHECK_ARG(q && k && v && o && d_o && lse && delta && dq && dk && dv && scratch, SPB_E_INVALID, "spb_attn_wide_bwd: null pointer");
+  SPB_CHECK_ARG(B > 0 && T > 0 && Hq > 0 && Hkv > 0 && hd > 0 && Hq % Hkv == 0, SPB_E_INVALID, "spb_attn_wide_bwd: bad shape");
+  SPB_CHECK_ARG(attn_wide_supported(SPB_BF16, hd), SPB_E_UNSUPPORTED, "spb_attn_wide_bwd: bf16 with hd > 256 and hd %% 8 == 0 (hd=%d)", hd);
+  return attn_wide_bwd(B, T, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk, dv, lddv, scratch,
+                       (cudaStream_t)stream);
+}
+
 // ------------------------------------------------------------------------------------------------ block
 int spb_block_ws_layout(const spb_block_desc* d, spb_ws_layout* out) {
   int rc = check_desc(d);
@@ -310,6 +339,10 @@ int spb_block_ws_layout(const spb_block_desc* d, spb_ws_layout* out) {
   size_t widest = Ntot > (size_t)d->C ? Ntot : (size_t)d->C;
   out->partial_bytes = spb_norm_bwd_partial_bytes((int64_t)N, (int32_t)widest);
   out->partial = take(out->partial_bytes);
+  if (block_uses_wide_attn(d)) {
+    out->attn_scratch_bytes = attn_wide_scratch_bytes(d->B, d->T, d->Hq, d->Hkv, d->hd);
+    out->attn_scratch = take(out->attn_scratch_bytes);
+  }
   out->total = off;
   return 0;
 }
@@ -384,8 +417,12 @@ int spb_block_fwd(const spb_block_desc* d, const spb_block_params* p, const void
   }
   // 4. attention
   prof_mark("flash_fwd", pst);
-  rc = spb_flash_fwd(dt, d->attn_impl, d->B, d->T, d->Hq, d->Hkv, d->hd, d->causal, d->scale, qkv, Ntot, qkv + Nq * e, Ntot,
-                     qkv + (Nq + Nkv) * e, Ntot, w8 + L.attn_o, Nq, (float*)(w8 + L.lse), stream);
+  if (block_uses_wide_attn(d))
+    rc = attn_wide_fwd(d->B, d->T, d->Hq, d->Hkv, d->hd, d->causal, d->scale, qkv, Ntot, qkv + Nq * e, Ntot, qkv + (Nq + Nkv) * e, Ntot,
+                       w8 + L.attn_o, Nq, (float*)(w8 + L.lse), w8 + L.attn_scratch, pst);
+  else
+    rc = spb_flash_fwd(dt, d->attn_impl, d->B, d->T, d->Hq, d->Hkv, d->hd, d->causal, d->scale, qkv, Ntot, qkv + Nq * e, Ntot,
+                       qkv + (Nq + Nkv) * e, Ntot, w8 + L.attn_o, Nq, (float*)(w8 + L.lse), stream);
   if (rc) return rc;
   // 5. output projection
   prof_mark("gemm_out", pst);
@@ -503,6 +540,18 @@ static int block_bwd_impl(const spb_block_desc* d, const spb_block_params* p, co
   // 3. attention backward -> dq|dk|dv (post-rotary gradients)
   prof_mark("flash_bwd", st);
   // 4. rotary VJP on dq, dk: fused into the attention backward (dK epilogue + dQ fp32->bf16 conversion)
+  if (block_uses_wide_attn(d)) {
+    rc = attn_wide_bwd(d->B, d->T, d->Hq, d->Hkv, d->hd, d->causal, d->scale, qkv, Ntot, qkv + Nq * e, Ntot, qkv + (Nq + Nkv) * e, Ntot,
+                       w8 + L.attn_o, Nq, w8 + L.dattn_o, Nq, (const float*)(w8 + L.lse), (float*)(w8 + L.delta), dqkv, Ntot, dqkv + Nq * e, Ntot,
+                       dqkv + (Nq + Nkv) * e, Ntot, w8 + L.attn_scratch, st);
+    if (rc) return rc;
+    if (d->rope_kind == SPB_ROPE_TABLE) {  // rotary VJP on dq and dk, in place
+      rc = spb_rope_apply(dt, dqkv, Ntot, N, d->T, d->Hq, d->hd, p->rope, 1, stream);
+      if (rc) return rc;
+      rc = spb_rope_apply(dt, dqkv + Nq * e, Ntot, N, d->T, d->Hkv, d->hd, p->rope, 1, stream);
+      if (rc) return rc;
+    }
+  } else
   rc = flash_bwd_any(dt, d->attn_impl, d->B, d->T, d->Hq, d->Hkv, d->hd, d->causal, d->scale, qkv, Ntot, qkv + Nq * e, Ntot,
                      qkv + (Nq + Nkv) * e, Ntot, w8 + L.attn_o, Nq, w8 + L.dattn_o, Nq, (const float*)(w8 + L.lse),
                      (float*)(w8 + L.delta), dqkv, Ntot, dqkv + Nq * e, Ntot, dqkv + (Nq + Nkv) * e, Ntot, (float*)(w8 + L.dq_acc), stream,

@@ -807,6 +807,12 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
     // efficiency (lower arithmetic intensity per smem byte), so it is only taken for a much larger gain
     if (gemm_tc_wave_eff(M, N, 192, G) > gemm_tc_wave_eff(M, N, 256, G) + 0.15) BN = 192;
   }
+  // few-tile problems (e.g. the [T, 768] outputs of the wide-head attention: 48 tiles of 128 x 256 on 148 SMs): the 128-wide tile
+  // doubles the number of CTAs; taken when that fills the machine clearly better and the pair kernel is out of reach
+  if (BN == 256 && ((M + 255) / 256) * ((N + 255) / 256) < sm_count() / 2) {
+    const int G = sm_count();
+    if (gemm_tc_wave_eff(M, N, 128, G) > gemm_tc_wave_eff(M, N, 256, G) + 0.15) BN = 128;
+  }
   // CTA-pair kernel: large problems with at least one 256 x 256 tile per pair (SPB_GEMM_2CTA=0 forces the single-CTA kernel)
   static const int use_pair = [] { const char* e = getenv("SPB_GEMM_2CTA"); return e ? atoi(e) : 1; }();
   if (use_pair && BN == 256 && M >= 256 && N >= 256 && ((M + 255) / 256) * ((N + 255) / 256) >= sm_count() / 2)

@@ -59,6 +59,15 @@ int comm_allreduce_join(void* comm, float* const* ptrs, const size_t* counts, in
 // error path: if a side-stream all-reduce is outstanding, make `main` wait for it and forget it
 void comm_side_cleanup(void* comm, cudaStream_t main);
 
+// attn_wide.cu: bf16 attention for head dims > 256 (Gemma literal, hd 768) as per-(batch, head) tcgen05 GEMM pipelines
+bool attn_wide_supported(int dtype, int hd);
+size_t attn_wide_scratch_bytes(int B, int T, int Hq, int Hkv, int hd);
+int attn_wide_fwd(int B, int T, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k, int64_t ldk,
+                  const void* v, int64_t ldv, void* o, int64_t ldo, float* lse, void* scratch, cudaStream_t st);
+int attn_wide_bwd(int B, int T, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k, int64_t ldk,
+                  const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o, int64_t lddo, const float* lse, float* delta, void* dq,
+                  int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv, void* scratch, cudaStream_t st);
+
 // decode.cu
 size_t small_m_gemm_scratch_bytes(int M, int N, int K, int dtype);
 int small_m_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, const void* W, int64_t ldw, void* D, int64_t ldd, const void* bias,

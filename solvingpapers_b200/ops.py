@@ -105,6 +105,34 @@ def flash_bwd(q, k, v, o, do, lse, causal, scale, impl=L.IMPL_AUTO):
     return dq, dk, dv
 
 
+def attn_wide_fwd(q, k, v, causal, scale):
+    """Wide-head attention (bf16, hd > 256): q [B,T,Hq,hd], k/v [B,T,Hkv,hd] -> o, lse through spb_attn_wide_fwd."""
+    lib = L.load()
+    B, T, Hq, hd = q.shape
+    Hkv = k.shape[2]
+    o = torch.empty((B, T, Hq, hd), dtype=q.dtype, device=q.device)
+    lse = torch.empty((B, Hq, T), dtype=torch.float32, device=q.device)
+    scratch = torch.empty(lib.spb_attn_wide_scratch_bytes(B, T, Hq, Hkv, hd), dtype=torch.uint8, device=q.device)
+    L.check(lib.spb_attn_wide_fwd(B, T, Hq, Hkv, hd, int(causal), scale, _ptr(q), q.stride(1), _ptr(k), k.stride(1), _ptr(v), v.stride(1),
+                                  _ptr(o), o.stride(1), _ptr(lse), _ptr(scratch), _stream()), "spb_attn_wide_fwd")
+    return o, lse
+
+
+def attn_wide_bwd(q, k, v, o, do, lse, causal, scale):
+    lib = L.load()
+    B, T, Hq, hd = q.shape
+    Hkv = k.shape[2]
+    dq = torch.empty((B, T, Hq, hd), dtype=q.dtype, device=q.device)
+    dk = torch.empty((B, T, Hkv, hd), dtype=q.dtype, device=q.device)
+    dv = torch.empty((B, T, Hkv, hd), dtype=q.dtype, device=q.device)
+    delta = torch.empty((B, Hq, T), dtype=torch.float32, device=q.device)
+    scratch = torch.empty(lib.spb_attn_wide_scratch_bytes(B, T, Hq, Hkv, hd), dtype=torch.uint8, device=q.device)
+    L.check(lib.spb_attn_wide_bwd(B, T, Hq, Hkv, hd, int(causal), scale, _ptr(q), q.stride(1), _ptr(k), k.stride(1), _ptr(v), v.stride(1),
+                                  _ptr(o), o.stride(1), _ptr(do), do.stride(1), _ptr(lse), _ptr(delta), _ptr(dq), dq.stride(1), _ptr(dk),
+                                  dk.stride(1), _ptr(dv), dv.stride(1), _ptr(scratch), _stream()), "spb_attn_wide_bwd")
+    return dq, dk, dv
+
+
 def attn_decode(q, k_cache, v_cache, Tk, scale, want_lse=False):
     """llama3:815-829 with a cache: q [B,Tq,Hq,hd] (rotated) against the first Tk rows of k_cache / v_cache [B,Tmax,Hkv,hd]
     (any token / batch strides, last dim contiguous) -> o [B,Tq,Hq,hd] (and lse [B,Hq,Tq])."""

@@ -270,3 +270,29 @@ def test_attention_tcgen05_is_deterministic_forward_and_rejects_unsupported():
     q768 = rnd((1, 64, 1, 768), 4, torch.bfloat16).to(DEV)
     with pytest.raises(L.SpbError):  # hd 768 (Gemma literal) has no tcgen05 tiling: explicit request is an error
         ops.flash_fwd(q768, q768, q768, True, 0.1, impl=L.IMPL_TCGEN05)
+
+
+# ------------------------------------------------------------------------------------------------ wide heads (Gemma literal, hd 768)
+@pytest.mark.parametrize("B,T,Hq,Hkv,hd,causal", [
+    (1, 64, 2, 1, 768, True),      # Gemma literal geometry: 2 q heads share one 768-wide k/v
+    (2, 200, 2, 1, 768, True),     # ragged T
+    (1, 2300, 2, 1, 768, True),    # more than one 2048-row block: causal key ranges differ per block
+    (1, 130, 2, 2, 512, False),    # bidirectional, MHA
+    (1, 96, 4, 2, 320, True),      # a width that is not a power of two
+])
+def test_attention_wide_heads_tcgen05_gemm_pipeline(B, T, Hq, Hkv, hd, causal):
+    """spb_attn_wide_fwd / bwd (bf16, hd > 256: every contraction on the tcgen05 GEMM) against the oracle math in fp64."""
+    ops = _ops()
+    q, k, v, do = (rnd((B, T, h, hd), 31 + i, torch.bfloat16) for i, h in enumerate((Hq, Hkv, Hkv, Hq)))
+    scale = 1.0 / math.sqrt(hd)
+    qr, kr, vr = (t.float().double().requires_grad_(True) for t in (q, k, v))
+    oref, lseref = _attn_ref(qr, kr, vr, causal, scale)
+    oref.backward(do.float().double())
+    qd, kd, vd, dod = (t.to(DEV) for t in (q, k, v, do))
+    o, lse = ops.attn_wide_fwd(qd, kd, vd, causal, scale)
+    dq, dk, dv = ops.attn_wide_bwd(qd, kd, vd, o, dod, lse, causal, scale)
+    torch.cuda.synchronize()
+    errs = {"o": max_rel_err(o, oref), "lse": max_rel_err(lse, lseref), "dq": max_rel_err(dq, qr.grad), "dk": max_rel_err(dk, kr.grad),
+            "dv": max_rel_err(dv, vr.grad)}
+    for name, e in errs.items():
+        assert e < TOL_BF16, (name, errs)
