@@ -299,6 +299,20 @@ int spb_nll_fwd(int dtype, const void* logits, int64_t ld, const int64_t* target
 int spb_nll_bwd(int dtype, const void* logits, int64_t ld, const int64_t* targets, int64_t N, int32_t V, const float* lse,
                 float dloss, void* dlogits, int64_t ldd, spb_stream_t stream);
 
+/* The whole loss head, llama3:930 + :959-967: loss = nll(dot(h, w), targets) with h [N, C] (row stride ldh) and the output weight
+ * w [C, V] as the notebook stores it (row stride ldw; V = 50257 there: NOT a multiple of 8 - the library pads the vocabulary axis of
+ * a private copy in `ws` when the pitch is not TMA-addressable, the caller pads nothing).  bf16.  The [N, V] logits are never
+ * written: the forward GEMM's epilogue keeps the online (max, sum exp, target logit) of llama3:961-965 per row and 256-column tile
+ * and a small kernel merges them (lse, row_nll [N] fp32, loss = mean); the backward recomputes each logits tile from h, w and lse
+ * and emits dlogits = (softmax - onehot) * dloss / N in bf16 straight from the epilogue for the two gradient GEMMs
+ * (dh [N, C] dtype or NULL; dw [C, V] fp32, row stride lddw, or NULL).  ws: spb_loss_head_ws_bytes(N, C, V), 256-byte aligned. */
+size_t spb_loss_head_ws_bytes(int64_t N, int32_t C, int32_t V);
+int spb_loss_head_fwd(int dtype, const void* h, int64_t ldh, const void* w, int64_t ldw, const int64_t* targets, int64_t N, int32_t C,
+                      int32_t V, float* lse, float* row_nll, float* loss, void* ws, spb_stream_t stream);
+int spb_loss_head_bwd(int dtype, const void* h, int64_t ldh, const void* w, int64_t ldw, const int64_t* targets, int64_t N, int32_t C,
+                      int32_t V, const float* lse, float dloss, void* dh, int64_t lddh, float* dw, int64_t lddw, void* ws,
+                      spb_stream_t stream);
+
 /* ---- KV-cache decode ----------------------------------------------------------- */
 /* llama3:815-829 with cache != None: Tq new query rows per sequence (already rotated) against Tk cached keys/values
  * (the new tokens' own k, v included: the caller - or spb_block_decode - appended them first).  No mask: every query row

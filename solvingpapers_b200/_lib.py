@@ -99,6 +99,9 @@ SIGNATURES = {
     "spb_ffn_bwd": (C.c_int, [C.POINTER(FfnDesc), C.POINTER(FfnParams), vp, vp, vp, C.POINTER(FfnGrads), vp, vp]),
     "spb_nll_fwd": (C.c_int, [C.c_int, vp, i64, vp, i64, i32, vp, vp, vp, vp]),
     "spb_nll_bwd": (C.c_int, [C.c_int, vp, i64, vp, i64, i32, vp, f32, vp, i64, vp]),
+    "spb_loss_head_ws_bytes": (sz, [i64, i32, i32]),
+    "spb_loss_head_fwd": (C.c_int, [C.c_int, vp, i64, vp, i64, vp, i64, i32, i32, vp, vp, vp, vp, vp]),
+    "spb_loss_head_bwd": (C.c_int, [C.c_int, vp, i64, vp, i64, vp, i64, i32, i32, vp, f32, vp, i64, vp, i64, vp, vp]),
     "spb_attn_decode_scratch_bytes": (sz, [i32, i32, i32, i32, i32, i32]),
     "spb_attn_decode": (C.c_int, [C.c_int, i32, i32, i32, i32, i32, i32, f32, vp, i64, vp, i64, i64, vp, i64, i64, vp, i64, vp, vp, vp]),
     "spb_block_decode_ws_layout": (C.c_int, [C.POINTER(BlockDesc), i32, C.POINTER(DecodeWs)]),

@@ -27,6 +27,7 @@ struct GemmTcArgs {
   const float4* rope;  // optional fused rotary epilogue (llama3:592-601): table [T, hd/2] of (a,b,c,d), applied to columns < rope_cols
   int rope_cols, rope_T, rope_hd;
   int out_f32, accumulate, atomic, vec_ok;
+  int bias_vec;        // bias pointer is 16-byte aligned
   int group_m;         // tile raster: row-blocks per group (see gemm_tc_tile_coords)
   const void* addsrc;  // accumulate: what is added to the product - D itself (NULL) or a separate [M,N] array of D's type
   int64_t ld_add;      //            (the residual stream: y = x + attn . wo)
@@ -40,6 +41,14 @@ struct GemmTcArgs {
   float* fuse_zero;
   int64_t fuse_ldz;
   int fuse_hd, fuse_T, fuse_H;
+  // loss-head epilogues (GemmTcHead): mode 1 = no D store, per (row, 256-column tile) online (max, sum exp) partials +
+  // the target's logit; mode 2 = D = (exp(acc - lse[row]) - [col == target[row]]) * gscale (dlogits, bf16)
+  int head_mode;
+  float2* head_part;
+  float* head_tgt;
+  const int64_t* head_targets;
+  const float* head_lse;
+  float head_gscale;
   // work items: the first `full_tiles` tiles (whole waves) run over the whole K range; the remaining tail tiles are each
   // split along K into `tail_parts` parts that add into a pre-zeroed fp32 output with atomics, so the last, partial wave
   // costs 1/tail_parts of a wave (also covers few-tile weight gradients: full_tiles = 0).
@@ -114,9 +123,20 @@ __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
   if (p.bias != nullptr) {
+    if (ncol == 32 && p.bias_vec) {  // 16-byte aligned bias: four 128-bit loads instead of 32 scalar ones
+      const uint4* bp = reinterpret_cast<const uint4*>(p.bias + col0);
 #pragma unroll
-    for (int i = 0; i < 32; ++i)
-      if (i < ncol) v[i] += __bfloat162float(p.bias[col0 + i]);
+      for (int i = 0; i < 4; ++i) {
+        const uint4 b = __ldg(bp + i);
+        const float2 b0 = unpack_bf16(b.x), b1 = unpack_bf16(b.y), b2 = unpack_bf16(b.z), b3 = unpack_bf16(b.w);
+        v[8 * i] += b0.x; v[8 * i + 1] += b0.y; v[8 * i + 2] += b1.x; v[8 * i + 3] += b1.y;
+        v[8 * i + 4] += b2.x; v[8 * i + 5] += b2.y; v[8 * i + 6] += b3.x; v[8 * i + 7] += b3.y;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (i < ncol) v[i] += __bfloat162float(p.bias[col0 + i]);
+    }
   }
   if (rope_row != nullptr) {
     // adjacent pairs (2j, 2j+1) of one head live in this thread's registers; rotate the fp32 accumulators in place.
@@ -222,6 +242,7 @@ __device__ __forceinline__ void gemm_tc_drain(const GemmTcArgs& p, const CUtenso
   const int row = m0 + q * 32 + lane;
   if (m0 + q * 32 >= p.M) return;  // warp-uniform: this warp's 32 rows lie past the last row (small-M problems)
   float dsum = 0.f;  // running sum_c dO * O of the current head (fuse_o != NULL)
+  float hm = -INFINITY, hs = 0.f;  // loss-head mode 1: online (max, sum exp) of this row over the tile's columns
 #pragma unroll 1
       for (int c = 0; c < NCOLS / 32; ++c) {
         const int col0 = n0 + c * 32;
@@ -279,10 +300,43 @@ __device__ __forceinline__ void gemm_tc_drain(const GemmTcArgs& p, const CUtenso
             dsum = 0.f;
           }
         }
+        if (p.head_mode != 0) {
+          if (row < p.M) {
+            const int ncolv = min(32, p.N - col0);
+            const int tgt = (int)p.head_targets[row];
+            if (p.head_mode == 1) {
+              float cm = -INFINITY;
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (i < ncolv) cm = fmaxf(cm, __uint_as_float(r[i]));
+              if (cm > hm) {
+                hs = (hm == -INFINITY) ? 0.f : hs * __expf(hm - cm);
+                hm = cm;
+              }
+              if (hm != -INFINITY) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                  if (i < ncolv) hs += __expf(__uint_as_float(r[i]) - hm);
+              }
+              if (tgt >= col0 && tgt < col0 + ncolv) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                  if (col0 + i == tgt) p.head_tgt[row] = __uint_as_float(r[i]);
+              }
+            } else {
+              const float l = p.head_lse[row];
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                r[i] = __float_as_uint((__expf(__uint_as_float(r[i]) - l) - ((col0 + i == tgt) ? 1.0f : 0.0f)) * p.head_gscale);
+            }
+          }
+          if (p.head_mode == 1) continue;  // warp-uniform: nothing is stored
+        }
         if (atomic && p.vec_ok) gemm_tc_reduce_chunk(tmD, m0 + q * 32, col0, r, warp_buf, c, lane);
         else if (atomic) gemm_tc_atomic_chunk(p, m0 + q * 32, col0, r, reinterpret_cast<float*>(warp_buf), lane);
         else if (row < p.M) gemm_tc_store_chunk(p, row, col0, r, rope_row, lane, 0);
       }
+  if (p.head_mode == 1 && row < p.M) p.head_part[(int64_t)row * p.num_n + n0 / NCOLS] = make_float2(hm, hs);
 }
 
 template <int BN>
@@ -749,7 +803,7 @@ static double gemm_tc_wave_eff(int64_t M, int64_t N, int bn, int G) {
 
 int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb,
             int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st, const float* rope, int rope_cols,
-            int rope_T, int rope_hd, const void* residual, int64_t ldr, const GemmTcFuse* fuse) {
+            int rope_T, int rope_hd, const void* residual, int64_t ldr, const GemmTcFuse* fuse, const GemmTcHead* head) {
   SPB_CHECK_ARG(M < (1LL << 31) && N < (1LL << 31) && K < (1LL << 31), SPB_E_LIMIT, "gemm_tc: dimension beyond 2^31");
   SPB_CHECK_ARG(M > 0 && N > 0 && K > 0, SPB_E_INVALID, "gemm_tc: empty problem");
   SPB_CHECK_ARG(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && (lda % 8 == 0) && (ldb % 8 == 0), SPB_E_UNSUPPORTED,
@@ -760,6 +814,7 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
   args.D = D;
   args.ldd = ldd;
   args.bias = (const __nv_bfloat16*)bias;
+  args.bias_vec = bias != nullptr && (uintptr_t)bias % 16 == 0;
   args.rope = (const float4*)rope;
   args.rope_cols = rope_cols;
   args.rope_T = rope_T > 0 ? rope_T : 1;
@@ -788,6 +843,17 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
     args.fuse_T = fuse->T;
     args.fuse_H = fuse->H;
   }
+  if (head != nullptr) {
+    SPB_CHECK_ARG(bias == nullptr && rope == nullptr && !accumulate && residual == nullptr && fuse == nullptr && N > 128, SPB_E_INVALID,
+                  "gemm_tc: the loss-head epilogues take a plain GEMM with more than 128 output columns");
+    SPB_CHECK_ARG(head->mode == 1 || (head->mode == 2 && out_dtype == SPB_BF16), SPB_E_INVALID, "gemm_tc: loss-head mode %d", head->mode);
+    args.head_mode = head->mode;
+    args.head_part = (float2*)head->part;
+    args.head_tgt = head->tgt_logit;
+    args.head_targets = head->targets;
+    args.head_lse = head->lse;
+    args.head_gscale = head->gscale;
+  }
   // transA=0: A stored [M,K] -> K-major.  transA=1: stored [K,M] -> MN-major.
   // transB=0: B stored [K,N] -> MN-major (N contiguous).  transB=1: stored [N,K] -> K-major.
   args.a_mn = transA ? 1 : 0;
@@ -798,10 +864,10 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
   args.vec_ok = ((uintptr_t)D % 16 == 0) && ((ldd * esz) % 16 == 0) &&
                 (residual == nullptr || (((uintptr_t)residual % 16 == 0) && ((ldr * esz) % 16 == 0)));
   // K-split of the tail wave needs a plain fp32 output (weight gradients)
-  const bool may_split = args.out_f32 && bias == nullptr && rope == nullptr && !args.accumulate;
+  const bool may_split = args.out_f32 && bias == nullptr && rope == nullptr && !args.accumulate && head == nullptr;
   // tile width: 256 unless a 192-wide tile fills the waves of this problem clearly better (e.g. 8192 x 6144: 94 % -> 99 %)
   int BN = (N > 128) ? 256 : 128;
-  if (BN == 256 && !may_split) {
+  if (BN == 256 && !may_split && head == nullptr) {  // (the loss-head partials are laid out per 256-column tile)
     const int G = sm_count();
     // measured (r01d): the 192-wide tile runs at 1219 TF/s vs 1342 TF/s for 256 on 8192x6144x4096 despite 99 % vs 94 % wave
     // efficiency (lower arithmetic intensity per smem byte), so it is only taken for a much larger gain
@@ -809,7 +875,7 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
   }
   // few-tile problems (e.g. the [T, 768] outputs of the wide-head attention: 48 tiles of 128 x 256 on 148 SMs): the 128-wide tile
   // doubles the number of CTAs; taken when that fills the machine clearly better and the pair kernel is out of reach
-  if (BN == 256 && ((M + 255) / 256) * ((N + 255) / 256) < sm_count() / 2) {
+  if (BN == 256 && head == nullptr && ((M + 255) / 256) * ((N + 255) / 256) < sm_count() / 2) {
     const int G = sm_count();
     if (gemm_tc_wave_eff(M, N, 128, G) > gemm_tc_wave_eff(M, N, 256, G) + 0.15) BN = 128;
   }

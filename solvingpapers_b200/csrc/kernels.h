@@ -19,11 +19,23 @@ struct GemmTcFuse {
   int64_t ldz;
   int hd, T, H;
 };
+// Loss-head epilogues of the logits GEMM (llama3:930 + :959-967): the [N, V] logits never reach memory.
+//  mode 1 (forward): no D store; per (row, 256-column tile) the online (max, sum exp) of the fp32 logits -> part[row][tile] (float2,
+//          ceil(N/256) tiles per row) and the logit of targets[row] -> tgt_logit[row]
+//  mode 2 (backward): D = (exp(logit - lse[row]) - [col == targets[row]]) * gscale in bf16 (dlogits for the dh / dW GEMMs)
+struct GemmTcHead {
+  int mode;
+  void* part;
+  float* tgt_logit;
+  const int64_t* targets;
+  const float* lse;
+  float gscale;
+};
 // rope != nullptr: fused rotary epilogue on output columns < rope_cols (row n has position n % rope_T)
 int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb,
             int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st, const float* rope = nullptr,
             int rope_cols = 0, int rope_T = 0, int rope_hd = 0, const void* residual = nullptr, int64_t ldr = 0,
-            const GemmTcFuse* fuse = nullptr);
+            const GemmTcFuse* fuse = nullptr, const GemmTcHead* head = nullptr);
 // > 0: the CTA-pair GEMMs launched by this host thread use one cluster per `tiles_per_cluster` tiles (SMs shared with a collective)
 void gemm_tc_hint_shared_sms(int tiles_per_cluster);
 // residual != nullptr (both GEMMs): D = A.B (+bias) + residual, residual [M,N] of D's type with row stride ldr

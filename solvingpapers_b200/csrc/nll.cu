@@ -165,9 +165,139 @@ static int nll_launch(bool bwd, const void* logits, int64_t ld, const int64_t* t
   return 0;
 }
 
+// ---- fused loss head (logits GEMM + NLL): merge the GEMM epilogue's per-tile partials ------------------------------
+// lse[n] = log sum_j exp(logit[n, j]) from part[n][tile] = (max, sum exp(x - max)); row_nll[n] = lse[n] - logit[n, target[n]]
+__global__ void __launch_bounds__(256) head_merge_kernel(const float2* __restrict__ part, int tiles, const float* __restrict__ tgt_logit,
+                                                         const int64_t* __restrict__ targets, int V, int64_t N, float* __restrict__ lse,
+                                                         float* __restrict__ row_nll) {
+  const int64_t n = (int64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (n >= N) return;
+  float m = -INFINITY, s = 0.f;
+  for (int t = lane; t < tiles; t += 32) {
+    const float2 p = part[n * tiles + t];
+    nll_merge(m, s, p.x, p.y);
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) nll_merge(m, s, __shfl_xor_sync(0xffffffffu, m, off), __shfl_xor_sync(0xffffffffu, s, off));
+  if (lane == 0) {
+    const float l = m + logf(s);
+    lse[n] = l;
+    const int64_t t = targets[n];
+    row_nll[n] = (t >= 0 && t < V) ? l - tgt_logit[n] : 0.f;
+  }
+}
+
+static inline size_t head_align(size_t v) { return (v + 255) / 256 * 256; }
+static inline int64_t head_vp(int V) { return ((int64_t)V + 7) / 8 * 8; }
+struct HeadWs {
+  size_t w_pad, part, tgt, dlogits, total;
+};
+static HeadWs head_ws(int64_t N, int C, int V) {
+  HeadWs w;
+  size_t off = 0;
+  auto take = [&](size_t b) { size_t o = off; off = head_align(off + b); return o; };
+  w.w_pad = take((size_t)C * head_vp(V) * 2);                       // [C, Vp] bf16 copy of the weight when its pitch is not TMA-addressable
+  w.part = take((size_t)N * ((V + 255) / 256) * sizeof(float2));    // (max, sum) per (row, 256-column tile)
+  w.tgt = take((size_t)N * sizeof(float));
+  w.dlogits = take((size_t)N * head_vp(V) * 2);                     // backward only: dlogits [N, Vp] bf16
+  w.total = off;
+  return w;
+}
+
+// the weight as the tcgen05 GEMM can address it: itself, or a copy with the vocabulary axis padded to a multiple of 8 elements
+static int head_weight(const void* w, int64_t ldw, int C, int V, char* ws, const HeadWs& L, const void** w_out, int64_t* ld_out, cudaStream_t st) {
+  if (ldw % 8 == 0 && (uintptr_t)w % 16 == 0) {
+    *w_out = w;
+    *ld_out = ldw;
+    return 0;
+  }
+  const int64_t vp = head_vp(V);
+  SPB_CUDA(cudaMemcpy2DAsync(ws + L.w_pad, (size_t)vp * 2, w, (size_t)ldw * 2, (size_t)V * 2, (size_t)C, cudaMemcpyDeviceToDevice, st));
+  *w_out = ws + L.w_pad;
+  *ld_out = vp;
+  return 0;
+}
+
 }  // namespace spb
 
 extern "C" {
+
+size_t spb_loss_head_ws_bytes(int64_t N, int32_t C, int32_t V) {
+  if (N <= 0 || C <= 0 || V <= 0) return 0;
+  return spb::head_ws(N, C, V).total;
+}
+
+int spb_loss_head_fwd(int dtype, const void* h, int64_t ldh, const void* w, int64_t ldw, const int64_t* targets, int64_t N, int32_t C, int32_t V,
+                      float* lse, float* row_nll, float* loss, void* ws, spb_stream_t stream) {
+  using namespace spb;
+  SPB_CHECK_ARG(h && w && targets && lse && row_nll && ws, SPB_E_INVALID, "spb_loss_head_fwd: null pointer");
+  SPB_CHECK_ARG(N > 0 && N < (1LL << 31) && C > 0 && V > 128 && ldh >= C && ldw >= V, SPB_E_INVALID, "spb_loss_head_fwd: bad shape (N=%lld C=%d V=%d)",
+                (long long)N, C, V);
+  SPB_CHECK_ARG(dtype == SPB_BF16, SPB_E_UNSUPPORTED, "spb_loss_head_fwd: the fused head runs on the bf16 tcgen05 GEMM (fp32: spb_gemm + spb_nll_fwd)");
+  SPB_CHECK_ARG((uintptr_t)ws % 256 == 0, SPB_E_INVALID, "spb_loss_head_fwd: workspace must be 256-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  char* w8 = (char*)ws;
+  const HeadWs L = head_ws(N, C, V);
+  const void* wp;
+  int64_t ldp;
+  int rc = head_weight(w, ldw, C, V, w8, L, &wp, &ldp, st);
+  if (rc) return rc;
+  GemmTcHead hd;
+  hd.mode = 1;
+  hd.part = w8 + L.part;
+  hd.tgt_logit = (float*)(w8 + L.tgt);
+  hd.targets = targets;
+  hd.lse = nullptr;
+  hd.gscale = 0.f;
+  // logits = h . w (llama3:930) with the reduction of llama3:961-965 in the epilogue: nothing [N, V]-sized is written
+  rc = gemm_tc(SPB_BF16, N, V, C, h, ldh, 0, wp, ldp, 0, w8 + L.part, head_vp(V), nullptr, 0, st, nullptr, 0, 0, 0, nullptr, 0, nullptr, &hd);
+  if (rc) return rc;
+  head_merge_kernel<<<(unsigned)((N + 7) / 8), 256, 0, st>>>((const float2*)(w8 + L.part), (V + 255) / 256, (const float*)(w8 + L.tgt), targets, V, N, lse,
+                                                             row_nll);
+  SPB_LAUNCH_CHECK();
+  if (loss != nullptr) {
+    nll_mean_kernel<<<1, 1024, 0, st>>>(row_nll, N, loss);
+    SPB_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+int spb_loss_head_bwd(int dtype, const void* h, int64_t ldh, const void* w, int64_t ldw, const int64_t* targets, int64_t N, int32_t C, int32_t V,
+                      const float* lse, float dloss, void* dh, int64_t lddh, float* dw, int64_t lddw, void* ws, spb_stream_t stream) {
+  using namespace spb;
+  SPB_CHECK_ARG(h && w && targets && lse && ws && (dh || dw), SPB_E_INVALID, "spb_loss_head_bwd: null pointer");
+  SPB_CHECK_ARG(N > 0 && N < (1LL << 31) && C > 0 && V > 128 && ldh >= C && ldw >= V, SPB_E_INVALID, "spb_loss_head_bwd: bad shape");
+  SPB_CHECK_ARG(dtype == SPB_BF16, SPB_E_UNSUPPORTED, "spb_loss_head_bwd: the fused head runs on the bf16 tcgen05 GEMM");
+  SPB_CHECK_ARG((uintptr_t)ws % 256 == 0, SPB_E_INVALID, "spb_loss_head_bwd: workspace must be 256-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  char* w8 = (char*)ws;
+  const HeadWs L = head_ws(N, C, V);
+  const int64_t vp = head_vp(V);
+  const void* wp;
+  int64_t ldp;
+  int rc = head_weight(w, ldw, C, V, w8, L, &wp, &ldp, st);
+  if (rc) return rc;
+  GemmTcHead hd;
+  hd.mode = 2;
+  hd.part = nullptr;
+  hd.tgt_logit = nullptr;
+  hd.targets = targets;
+  hd.lse = lse;
+  hd.gscale = dloss / (float)N;
+  // dlogits = (softmax(h . w) - onehot) * dloss / N, recomputed tile by tile from h, w and lse: the logits are never stored
+  rc = gemm_tc(SPB_BF16, N, V, C, h, ldh, 0, wp, ldp, 0, w8 + L.dlogits, vp, nullptr, 0, st, nullptr, 0, 0, 0, nullptr, 0, nullptr, &hd);
+  if (rc) return rc;
+  if (dh != nullptr) {  // dh = dlogits . w^T
+    rc = gemm_tc(SPB_BF16, N, C, V, w8 + L.dlogits, vp, 0, wp, ldp, 1, dh, lddh, nullptr, 0, st);
+    if (rc) return rc;
+  }
+  if (dw != nullptr) {  // dw = h^T . dlogits (fp32, the weight's own [C, V] layout)
+    rc = gemm_tc(SPB_F32, C, V, N, h, ldh, 1, w8 + L.dlogits, vp, 0, dw, lddw, nullptr, 0, st);
+    if (rc) return rc;
+  }
+  return 0;
+}
 
 int spb_nll_fwd(int dtype, const void* logits, int64_t ld, const int64_t* targets, int64_t N, int32_t V, float* lse, float* row_nll,
                 float* loss, spb_stream_t stream) {

@@ -203,3 +203,58 @@ def nll_loss(logits, targets):
     logits [..., V] are flattened to [N, V] like the notebook's reshape (:959-960)."""
     V = logits.shape[-1]
     return _NllFn.apply(logits.reshape(-1, V), targets.reshape(-1))
+
+
+class _LossHeadFn(torch.autograd.Function):
+    """loss = nll(h @ w, targets) (llama3/LLaMA-jax.ipynb:930 + :959-967) through spb_loss_head_fwd / spb_loss_head_bwd: the [N, V]
+    logits are never written (forward: online max / sum-exp / target logit in the GEMM epilogue; backward: dlogits recomputed tile by
+    tile straight into the two gradient GEMMs' operand).  bf16; the vocabulary need not be a multiple of 8."""
+
+    @staticmethod
+    def forward(ctx, h, w, targets):
+        import ctypes as C
+        lib = L.load()
+        N, Cm = h.shape
+        V = w.shape[1]
+        if h.dtype != torch.bfloat16 or w.dtype != torch.bfloat16:
+            raise L.SpbError("loss_head: the fused head is bf16 (fp32: ops.matmul + nll_loss)")
+        h, w = h.contiguous(), w.contiguous()
+        tg = targets.to(torch.int64).contiguous()
+        f32 = dict(dtype=torch.float32, device=h.device)
+        lse, row_nll, loss = torch.empty(N, **f32), torch.empty(N, **f32), torch.empty((), **f32)
+        ws = torch.empty(lib.spb_loss_head_ws_bytes(N, Cm, V), dtype=torch.uint8, device=h.device)
+        st = C.c_void_p(torch.cuda.current_stream(h.device).cuda_stream)
+        p = lambda t: C.c_void_p(t.data_ptr())
+        L.check(lib.spb_loss_head_fwd(L.BF16, p(h), h.stride(0), p(w), w.stride(0), p(tg), N, Cm, V, p(lse), p(row_nll), p(loss), p(ws), st),
+                "spb_loss_head_fwd")
+        ctx.save_for_backward(h, w, tg, lse)
+        ctx.ws = ws
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        import ctypes as C
+        h, w, tg, lse = ctx.saved_tensors
+        lib = L.load()
+        N, Cm = h.shape
+        V = w.shape[1]
+        dh = torch.empty_like(h)
+        dw = torch.empty((Cm, V), dtype=torch.float32, device=h.device)
+        st = C.c_void_p(torch.cuda.current_stream(h.device).cuda_stream)
+        p = lambda t: C.c_void_p(t.data_ptr())
+        L.check(lib.spb_loss_head_bwd(L.BF16, p(h), h.stride(0), p(w), w.stride(0), p(tg), N, Cm, V, p(lse), float(dloss), p(dh), dh.stride(0),
+                                      p(dw), dw.stride(0), p(ctx.ws), st), "spb_loss_head_bwd")
+        ctx.ws = None
+        return dh, dw.to(w.dtype), None
+
+
+def loss_head(norm_f, output_w, h, targets):
+    """The end of model_forward + compute_loss (llama3/LLaMA-jax.ipynb:929-930, 959-967):
+    ``logits = dot(rms_norm(h, norm_f), output)``; ``loss = -mean(log_softmax(logits)[targets])`` - bf16: fused (no logits in memory);
+    fp32: the rms_norm / matmul / nll_loss kernels one after the other."""
+    Cm = h.shape[-1]
+    hn = rms_norm(h, norm_f).reshape(-1, Cm)
+    if h.dtype == torch.bfloat16:
+        return _LossHeadFn.apply(hn, output_w, targets.reshape(-1))
+    from .ops import matmul
+    return nll_loss(matmul(hn, output_w), targets)

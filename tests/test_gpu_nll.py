@@ -90,3 +90,48 @@ def test_nll_with_vocabulary_masked_logits(dtype):
     assert torch.isfinite(loss) and torch.isfinite(x.grad).all()
     assert abs(float(loss) - float(ref)) <= tol * abs(float(ref))
     assert max_rel_err(x.grad, ref_in.grad) < tol
+
+
+@pytest.mark.parametrize("N,C,V", [(256, 256, 50257), (300, 64, 1000), (2048, 256, 4096), (64, 128, 257)])
+def test_fused_loss_head_bf16_never_writes_logits(N, C, V):
+    """spb_loss_head_fwd / bwd (logits GEMM + NLL fused) against the oracle's loss_head (llama3:929-930, 959-967) on
+    bf16-rounded inputs: loss, dh (through the final rms_norm: dh and dnorm_f) and the [C, V] weight gradient; V = 50257 is the
+    notebook's vocabulary (not a multiple of 8: the library pads a private copy)."""
+    from solvingpapers_b200 import llama as spl
+    rng = np.random.default_rng(V + N)
+    rd = lambda t: t.to(torch.bfloat16).float()
+    h = rd(torch.from_numpy(rng.standard_normal((N, C)).astype(np.float32)))
+    nw = rd(torch.from_numpy(rng.standard_normal((C,)).astype(np.float32)))
+    w = rd(torch.from_numpy((rng.standard_normal((C, V)) / np.sqrt(C)).astype(np.float32)))
+    tg = torch.from_numpy(rng.integers(0, V, size=(N,)))
+    tg[0], tg[-1] = V - 1, 0
+    hr, nr, wr = (t.clone().requires_grad_(True) for t in (h, nw, w))
+    ref = llama_oracle.loss_head(nr, wr, hr, tg)
+    ref.backward()
+    hd, nd, wd = (t.to(torch.bfloat16).cuda().requires_grad_(True) for t in (h, nw, w))
+    loss = spl.loss_head(nd, wd, hd, tg.cuda())
+    loss.backward()
+    torch.cuda.synchronize()
+    assert abs(float(loss) - float(ref)) <= TOL_BF16 * abs(float(ref)), (float(loss), float(ref))
+    for name, got, want in (("dh", hd.grad, hr.grad), ("dnorm_f", nd.grad, nr.grad), ("dw", wd.grad, wr.grad)):
+        assert max_rel_err(got, want) < TOL_BF16, name
+
+
+def test_fused_loss_head_matches_unfused_kernels():
+    """same inputs through ops.matmul + nll_loss (logits materialised) and through the fused head: the loss agrees to fp32 rounding of
+    the bf16 logits, the gradients to bf16 rounding"""
+    from solvingpapers_b200 import llama as spl, ops
+    rng = np.random.default_rng(9)
+    N, C, V = 512, 256, 8192
+    h = torch.from_numpy(rng.standard_normal((N, C)).astype(np.float32)).bfloat16().cuda()
+    w = torch.from_numpy((rng.standard_normal((C, V)) / 16).astype(np.float32)).bfloat16().cuda()
+    tg = torch.from_numpy(rng.integers(0, V, size=(N,))).cuda()
+    h1, w1 = h.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    l1 = spl.nll_loss(ops.matmul(h1, w1), tg)
+    l1.backward()
+    h2, w2 = h.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    l2 = spl._LossHeadFn.apply(h2, w2, tg)
+    l2.backward()
+    torch.cuda.synchronize()
+    assert abs(float(l1) - float(l2)) < 5e-3 * abs(float(l1))
+    assert max_rel_err(h2.grad, h1.grad) < TOL_BF16 and max_rel_err(w2.grad, w1.grad) < TOL_BF16
