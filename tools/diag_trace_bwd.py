@@ -9,7 +9,7 @@ from solvingpapers_b200 import _lib as L, ops
 NAMES = {1: "prod qdo_empty ok", 10: "mma qdo_full seen", 11: "mma sdp_empty seen", 12: "mma S,dP issued", 13: "mma pds_full seen", 14: "mma dq_empty seen",
          15: "mma dV,dK,dQ issued", 20: "ew bar", 21: "ew sdp_full seen", 22: "ew S,dP in regs", 23: "ew math done", 24: "ew pds_empty seen",
          25: "ew P,dS stored+arrived", 30: "dr dq_full seen", 31: "dr dQ in regs", 32: "dr staged", 33: "dr reduce issued"}
-B, T, Hq, Hkv, hd = 4, 2048, 32, 8, 128
+B, T, Hq, Hkv, hd = (int(os.environ.get(k, d)) for k, d in (('TR_B', 4), ('TR_T', 2048), ('TR_HQ', 32), ('TR_HKV', 8), ('TR_HD', 128)))
 causal = os.environ.get("FA_CAUSAL", "1") == "1"
 g = torch.Generator(device="cuda").manual_seed(1)
 mk = lambda h: torch.randn(B, T, h, hd, generator=g, device="cuda").bfloat16()
