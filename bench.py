@@ -406,10 +406,15 @@ def run_ours(args):
     grads["dx"] = torch.empty_like(x)
     grad_mem = "torch allocator"
     if comm is not None and args.reg_grads == "on":
-        for name in ("dwqkv", "dwo"):
-            if name in grads:
-                grads[name] = comm.alloc(tuple(grads[name].shape))
-        grad_mem = "spb_comm_alloc: " + comm.buffer_kind(grads["dwo"])
+        try:
+            for name in ("dwqkv", "dwo"):
+                if name in grads:
+                    grads[name] = comm.alloc(tuple(grads[name].shape))
+            grad_mem = "spb_comm_alloc: " + comm.buffer_kind(grads["dwo"])
+        except Exception as ex:  # e.g. an NCCL build without ncclMemAlloc: plain buffers still work, only slower
+            grads = blk.alloc_grads(params)
+            grads["dx"] = torch.empty_like(x)
+            grad_mem = f"torch allocator (spb_comm_alloc failed: {ex})"
     tokens_local = B * T
     h_sep = torch.empty_like(x) if args.residual == "separate" else None
 

@@ -938,7 +938,7 @@ int spb_attn_decode(int dtype, int32_t B, int32_t Tq, int32_t Hq, int32_t Hkv, i
 int spb_block_decode_ws_layout(const spb_block_desc* d, int32_t Tmax, spb_decode_ws* out) {
   int rc = check_desc(d);
   if (rc) return rc;
-  SPB_CHECK_ARG(out != nullptr && Tmax >= d->T, SPB_E_INVALID, "spb_block_decode_ws_layout: bad argument (Tmax=%d Tq=%d)", Tmax, d->T);
+  SPB_CHECK_ARG(out != nullptr && Tmax >= d->T && Tmax <= (1 << 24), SPB_E_INVALID, "spb_block_decode_ws_layout: bad argument (Tmax=%d Tq=%d)", Tmax, d->T);
   const size_t M = (size_t)d->B * d->T, e = esize(d->dtype);
   const size_t Nq = (size_t)d->Hq * d->hd, Nkv = (size_t)d->Hkv * d->hd, Ntot = Nq + 2 * Nkv;
   SPB_CHECK_ARG(M <= 64, SPB_E_LIMIT, "decode: B*Tq = %zu rows; at most 64 (longer inputs go through spb_block_fwd)", M);

@@ -3,7 +3,10 @@
 // Never materialises scores or repeated K/V in HBM (llama3:820-828, :626-627): one warp owns one query row (forward and
 // dQ) or one key row (dK/dV); the row of scores lives in shared memory; GQA is an index (kv head = q head / n_rep) and the
 // dK/dV group sum happens in registers by looping over the group's q heads.  Deterministic (no atomics).
+#include <cstdlib>
+
 #include "common.cuh"
+#include "kernels.h"
 
 namespace spb {
 
@@ -244,6 +247,12 @@ static int attn_simt_bwd_t(int B, int Tn, int Hq, int Hkv, int hd, int causal, f
 
 int attn_simt_fwd(int dtype, int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq,
                   const void* k, int64_t ldk, const void* v, int64_t ldv, void* o, int64_t ldo, float* lse, cudaStream_t st) {
+  {  // fp32 with a tile-able head dim: the register-tiled kernels of attn_ffma.cu (SPB_ATTN_FFMA=0: the warp-per-row kernels below)
+    static const bool use_ffma = [] { const char* e = getenv("SPB_ATTN_FFMA"); return e == nullptr || atoi(e) != 0; }();
+    const void* ptrs[4] = {q, k, v, o};
+    const int64_t lds[4] = {ldq, ldk, ldv, ldo};
+    if (use_ffma && attn_ffma_supported(dtype, hd, ptrs, lds, 4)) return attn_ffma_fwd(B, Tn, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st);
+  }
   SPB_CHECK_ARG(hd <= 32 * AS_MAXC, SPB_E_UNSUPPORTED, "attention (SIMT): hd %d > %d", hd, 32 * AS_MAXC);
   SPB_CHECK_ARG((size_t)AS_WARPS * Tn * sizeof(float) <= 200 * 1024, SPB_E_UNSUPPORTED, "attention (SIMT): T %d > 12800", Tn);
 #define SPB_AF(TT, NCC) return attn_simt_fwd_t<TT, NCC>(B, Tn, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, lse, st)
@@ -266,6 +275,13 @@ int attn_simt_bwd(int dtype, int B, int Tn, int Hq, int Hkv, int hd, int causal,
                   const void* k, int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o,
                   int64_t lddo, const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv,
                   int64_t lddv, cudaStream_t st) {
+  {
+    static const bool use_ffma = [] { const char* e = getenv("SPB_ATTN_FFMA"); return e == nullptr || atoi(e) != 0; }();
+    const void* ptrs[8] = {q, k, v, o, d_o, dq, dk, dv};
+    const int64_t lds[8] = {ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv};
+    if (use_ffma && attn_ffma_supported(dtype, hd, ptrs, lds, 8))
+      return attn_ffma_bwd(B, Tn, Hq, Hkv, hd, causal, scale, q, ldq, k, ldk, v, ldv, o, ldo, d_o, lddo, lse, delta, dq, lddq, dk, lddk, dv, lddv, st);
+  }
   SPB_CHECK_ARG(hd <= 32 * AS_MAXC, SPB_E_UNSUPPORTED, "attention (SIMT): hd %d > %d", hd, 32 * AS_MAXC);
   SPB_CHECK_ARG((size_t)AS_WARPS * Tn * sizeof(float) <= 200 * 1024, SPB_E_UNSUPPORTED, "attention (SIMT): T %d > 12800", Tn);
 #define SPB_AB(TT, NCC)                                                                                                   \

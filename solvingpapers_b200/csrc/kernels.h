@@ -47,6 +47,14 @@ int attn_simt_bwd(int dtype, int B, int Tn, int Hq, int Hkv, int hd, int causal,
                   int64_t lddo, const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv,
                   int64_t lddv, cudaStream_t st);
 
+// attn_ffma.cu: register-tiled fp32 attention (hd in {64, 128, 256}, 16-byte aligned operands), used by attn_simt_fwd / bwd
+bool attn_ffma_supported(int dtype, int hd, const void* const* ptrs, const int64_t* lds, int n);
+int attn_ffma_fwd(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k, int64_t ldk,
+                  const void* v, int64_t ldv, void* o, int64_t ldo, float* lse, cudaStream_t st);
+int attn_ffma_bwd(int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq, const void* k, int64_t ldk,
+                  const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o, int64_t lddo, const float* lse, float* delta, void* dq,
+                  int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv, cudaStream_t st);
+
 // tcgen05 flash attention (bf16, hd in {64,128})
 bool flash_tc_supported(int dtype, int hd);
 bool flash_bwd_tc_supported(int dtype, int hd);
