@@ -40,7 +40,7 @@ class _BlockDesc(ctypes.Structure):  # spb_block_desc (include/spb200.h)
 class _WsLayout(ctypes.Structure):  # spb_ws_layout
     _fields_ = [(n, ctypes.c_size_t) for n in ("total", "xhat", "stats", "qkv", "attn_o", "lse", "delta", "dattn_o", "dqkv", "dq_acc",
                                                 "dxhat", "partial", "partial_bytes")] + [("ld_qkv", ctypes.c_int64)] + \
-               [(n, ctypes.c_size_t) for n in ("attn_scratch", "attn_scratch_bytes")]
+               [(n, ctypes.c_size_t) for n in ("attn_scratch", "attn_scratch_bytes", "gemm_scratch", "gemm_scratch_bytes")]
 
 
 def register():

@@ -68,7 +68,9 @@ typedef struct spb_block_desc {
   int32_t out_bias;       /* 1: bo present (GPT proj bias, ViT out_proj.bias) */
   int32_t attn_impl;      /* SPB_IMPL_*: AUTO = tcgen05 flash kernels when dtype==bf16 and hd in {64,128,256}, the tcgen05 GEMM
                              pipeline of spb_attn_wide_* when dtype==bf16 and hd > 256, else SIMT */
-  int32_t gemm_impl;      /* SPB_IMPL_*: AUTO = tcgen05 GEMM when dtype==bf16, SIMT fp32 GEMM when dtype==f32 */
+  int32_t gemm_impl;      /* SPB_IMPL_*: AUTO = tcgen05 GEMM; for dtype==f32 on two-term bf16 splits of both operands (three
+                             products in one GEMM, fp32 accumulation: within the 1e-4 tolerance), FFMA GEMM where a shape or a
+                             bias rules that out.  SIMT = FFMA GEMM always */
   int32_t residual;       /* 0: y = block(x) (what `attention` returns, llama3:809-829).  1: y = x + block(x), the caller's
                              `h = x + attention(...)` (llama3:885, gpt:420, gemma:335, ViT:222) fused into the output
                              projection's epilogue; spb_block_bwd then returns dx = d block/dx + dy (fused into the norm
@@ -123,6 +125,8 @@ typedef struct spb_ws_layout {
   int64_t ld_qkv;  /* (Hq + 2*Hkv) * hd */
   size_t attn_scratch;        /* scratch of the wide-head attention path (bf16, hd > 256); 0 bytes otherwise   */
   size_t attn_scratch_bytes;
+  size_t gemm_scratch;        /* fp32 mode: bf16 hi/lo splits of the operands of the block's GEMMs (tensor-core fp32 path)     */
+  size_t gemm_scratch_bytes;
 } spb_ws_layout;
 
 /* ---- library ------------------------------------------------------------------------------------ */

@@ -37,7 +37,8 @@ class BlockGrads(C.Structure):
 class WsLayout(C.Structure):
     _fields_ = [("total", sz), ("xhat", sz), ("stats", sz), ("qkv", sz), ("attn_o", sz), ("lse", sz), ("delta", sz),
                 ("dattn_o", sz), ("dqkv", sz), ("dq_acc", sz), ("dxhat", sz), ("partial", sz), ("partial_bytes", sz),
-                ("ld_qkv", i64), ("attn_scratch", sz), ("attn_scratch_bytes", sz)]
+                ("ld_qkv", i64), ("attn_scratch", sz), ("attn_scratch_bytes", sz), ("gemm_scratch", sz),
+                ("gemm_scratch_bytes", sz)]
 
 
 class FfnDesc(C.Structure):

@@ -133,13 +133,32 @@ static bool block_uses_wide_attn(const spb_block_desc* d) {
          !flash_tc_supported(d->dtype, d->hd);
 }
 
+// scratch of the fp32 split GEMM: set for the duration of a block call by the host thread that runs it (SplitScratch guard)
+static thread_local void* g_split_ws = nullptr;
+static thread_local size_t g_split_bytes = 0;
+struct SplitScratch {
+  SplitScratch(void* ws, size_t bytes) { g_split_ws = bytes ? ws : nullptr; g_split_bytes = bytes; }
+  ~SplitScratch() { g_split_ws = nullptr; g_split_bytes = 0; }
+};
+
 // GEMM dispatch shared by spb_gemm and the block: with `rope` the rotary runs as the in-place kernel right after the GEMM
 // (default) or in the tcgen05 epilogue on the fp32 accumulators (SPB_ROPE_FUSE=1).
 static int gemm_any(int in_dtype, int out_dtype, int impl, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA,
                     const void* Bm, int64_t ldb, int transB, void* D, int64_t ldd, const void* bias, int accumulate, cudaStream_t st,
                     const float* rope, int rope_cols, int rope_T, int rope_hd, const void* residual = nullptr, int64_t ldr = 0) {
-  const int use = pick_gemm_impl(impl, in_dtype);
   SPB_CHECK_ARG(residual == nullptr || rope == nullptr, SPB_E_INVALID, "gemm: residual and rotary epilogues are exclusive");
+  // fp32 mode inside a block that reserved split scratch: the tcgen05 GEMM on two-term bf16 splits of both operands
+  // (gemm_split.cu; SPB_F32_TC=0 keeps the FFMA GEMM)
+  if (in_dtype == SPB_F32 && out_dtype == SPB_F32 && impl != SPB_IMPL_SIMT && g_split_ws != nullptr) {
+    static const bool f32_tc = [] { const char* e = getenv("SPB_F32_TC"); return e == nullptr || atoi(e) != 0; }();
+    if (f32_tc && gemm_f32_split_ok(M, N, K, A, lda, transA, Bm, ldb, transB) && g_split_bytes >= gemm_f32_split_scratch_bytes(M, N, K) &&
+        (uintptr_t)D % 16 == 0 && ldd % 4 == 0) {
+      int rc = gemm_f32_split(M, N, K, A, lda, transA, Bm, ldb, transB, D, ldd, bias, accumulate, residual, ldr, g_split_ws, g_split_bytes, st);
+      if (rc || rope == nullptr) return rc;
+      return spb_rope_apply(out_dtype, D, ldd, M, rope_T, rope_cols / rope_hd, rope_hd, rope, 0, (spb_stream_t)st);
+    }
+  }
+  const int use = pick_gemm_impl(impl, in_dtype);
   if (use == SPB_IMPL_TCGEN05) {
     SPB_CHECK_ARG(in_dtype == SPB_BF16, SPB_E_UNSUPPORTED, "spb_gemm: the tcgen05 GEMM takes bf16 operands (fp32 mode uses the FFMA GEMM)");
     // Measured at C3 after the GEMM reached ~1.6 PFLOP/s in-step: GEMM + the head-looping in-place rotary kernel (0.303 ms)
@@ -343,6 +362,17 @@ int spb_block_ws_layout(const spb_block_desc* d, spb_ws_layout* out) {
     out->attn_scratch_bytes = attn_wide_scratch_bytes(d->B, d->T, d->Hq, d->Hkv, d->hd);
     out->attn_scratch = take(out->attn_scratch_bytes);
   }
+  if (d->dtype == SPB_F32 && d->gemm_impl != SPB_IMPL_SIMT) {  // fp32 mode: split scratch for the largest GEMM of the block
+    const int64_t Nn = (int64_t)N, Cc = d->C, Nt = (int64_t)Ntot, Nqq = (int64_t)Nq;
+    const int64_t shapes[6][3] = {{Nn, Nt, Cc}, {Nn, Cc, Nqq}, {Nn, Nqq, Cc}, {Nqq, Cc, Nn}, {Cc, Nt, Nn}, {Nn, Cc, Nt}};
+    size_t worst = 0;
+    for (auto& sh : shapes) {
+      const size_t b = gemm_f32_split_scratch_bytes(sh[0], sh[1], sh[2]);
+      if (b > worst) worst = b;
+    }
+    out->gemm_scratch_bytes = worst;
+    out->gemm_scratch = take(worst);
+  }
   out->total = off;
   return 0;
 }
@@ -371,6 +401,7 @@ int spb_block_fwd(const spb_block_desc* d, const spb_block_params* p, const void
   rc = spb_block_ws_layout(d, &L);
   if (rc) return rc;
   char* w8 = (char*)ws;
+  SplitScratch split_guard(w8 + L.gemm_scratch, L.gemm_scratch_bytes);
   const int64_t N = (int64_t)d->B * d->T;
   const int64_t Nq = (int64_t)d->Hq * d->hd, Nkv = (int64_t)d->Hkv * d->hd, Ntot = Nq + 2 * Nkv;
   const size_t e = esize(d->dtype);
@@ -455,6 +486,7 @@ static int block_bwd_impl(const spb_block_desc* d, const spb_block_params* p, co
   rc = spb_block_ws_layout(d, &L);
   if (rc) return rc;
   char* w8 = (char*)ws;
+  SplitScratch split_guard(w8 + L.gemm_scratch, L.gemm_scratch_bytes);
   const int64_t N = (int64_t)d->B * d->T;
   const int64_t Nq = (int64_t)d->Hq * d->hd, Nkv = (int64_t)d->Hkv * d->hd, Ntot = Nq + 2 * Nkv;
   const size_t e = esize(d->dtype);

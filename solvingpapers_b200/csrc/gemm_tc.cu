@@ -28,6 +28,7 @@ struct GemmTcArgs {
   int rope_cols, rope_T, rope_hd;
   int out_f32, accumulate, atomic, vec_ok;
   int bias_vec;        // bias pointer is 16-byte aligned
+  int bias_f32;        // bias elements are fp32 (else bf16)
   int group_m;         // tile raster: row-blocks per group (see gemm_tc_tile_coords)
   const void* addsrc;  // accumulate: what is added to the product - D itself (NULL) or a separate [M,N] array of D's type
   int64_t ld_add;      //            (the residual stream: y = x + attn . wo)
@@ -122,7 +123,12 @@ __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row
   float v[32];
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-  if (p.bias != nullptr) {
+  if (p.bias != nullptr && p.bias_f32) {  // fp32 mode (gemm_split.cu): the bias stays fp32
+    const float* bf = reinterpret_cast<const float*>(p.bias) + col0;
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (i < ncol) v[i] += __ldg(bf + i);
+  } else if (p.bias != nullptr) {
     if (ncol == 32 && p.bias_vec) {  // 16-byte aligned bias: four 128-bit loads instead of 32 scalar ones
       const uint4* bp = reinterpret_cast<const uint4*>(p.bias + col0);
 #pragma unroll
@@ -659,6 +665,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
 // until the collective's CTAs leave still owns its full share, so the GEMM ends "collective time + own time" later
 // (8 GPUs, r02g: dWqkv 0.29 -> 0.52 ms).  With the hint the grid has one cluster per `tiles_per_cluster` tiles and the
 // hardware's block scheduler does the balancing: late SMs simply take fewer clusters.
+static thread_local int g_bias_f32 = 0;  // set by gemm_f32_split around its call: the bias pointer holds fp32 values
+void gemm_tc_hint_bias_f32(int on) { g_bias_f32 = on; }
 static thread_local int g_shared_sm_tiles = 0;
 void gemm_tc_hint_shared_sms(int tiles_per_cluster) { g_shared_sm_tiles = tiles_per_cluster; }
 
@@ -815,6 +823,7 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
   args.ldd = ldd;
   args.bias = (const __nv_bfloat16*)bias;
   args.bias_vec = bias != nullptr && (uintptr_t)bias % 16 == 0;
+  args.bias_f32 = g_bias_f32;
   args.rope = (const float4*)rope;
   args.rope_cols = rope_cols;
   args.rope_T = rope_T > 0 ? rope_T : 1;

@@ -38,6 +38,7 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
             const GemmTcFuse* fuse = nullptr, const GemmTcHead* head = nullptr);
 // > 0: the CTA-pair GEMMs launched by this host thread use one cluster per `tiles_per_cluster` tiles (SMs shared with a collective)
 void gemm_tc_hint_shared_sms(int tiles_per_cluster);
+void gemm_tc_hint_bias_f32(int on);  // the next gemm_tc calls of this host thread read `bias` as fp32
 // residual != nullptr (both GEMMs): D = A.B (+bias) + residual, residual [M,N] of D's type with row stride ldr
 
 int attn_simt_fwd(int dtype, int B, int Tn, int Hq, int Hkv, int hd, int causal, float scale, const void* q, int64_t ldq,
@@ -46,6 +47,13 @@ int attn_simt_bwd(int dtype, int B, int Tn, int Hq, int Hkv, int hd, int causal,
                   const void* k, int64_t ldk, const void* v, int64_t ldv, const void* o, int64_t ldo, const void* d_o,
                   int64_t lddo, const float* lse, float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv,
                   int64_t lddv, cudaStream_t st);
+
+// gemm_split.cu: fp32 GEMM on the tcgen05 tensor cores through a two-term bf16 split of both operands (three products in one
+// GEMM over a 3x longer contraction axis); scratch = gemm_f32_split_scratch_bytes(M, N, K)
+size_t gemm_f32_split_scratch_bytes(int64_t M, int64_t N, int64_t K);
+bool gemm_f32_split_ok(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb, int transB);
+int gemm_f32_split(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, int transA, const void* B, int64_t ldb, int transB, void* D,
+                   int64_t ldd, const void* bias, int accumulate, const void* residual, int64_t ldr, void* scratch, size_t scratch_bytes, cudaStream_t st);
 
 // attn_ffma.cu: register-tiled fp32 attention (hd in {64, 128, 256}, 16-byte aligned operands), used by attn_simt_fwd / bwd
 bool attn_ffma_supported(int dtype, int hd, const void* const* ptrs, const int64_t* lds, int n);

@@ -37,7 +37,7 @@ def test_struct_sizes_match_header():
     assert ctypes.sizeof(_lib.BlockDesc) == 19 * 4
     assert ctypes.sizeof(_lib.BlockParams) == 15 * 8
     assert ctypes.sizeof(_lib.BlockGrads) == 15 * 8
-    assert ctypes.sizeof(_lib.WsLayout) == 16 * 8
+    assert ctypes.sizeof(_lib.WsLayout) == 18 * 8
 
 
 def test_version_and_argument_errors_without_a_gpu():
