@@ -769,9 +769,25 @@ static int gemm_tc_launch(const void* A, int64_t lda, const void* B, int64_t ldb
   args.kb_per_part = args.kb_total;
   if (may_split) {
     const int full = (tiles / G) * G, R = tiles - full;
-    if (R > 0 && R * 2 <= G && args.kb_total >= 16) {
+    if (R > 0 && (R * 2 <= G || full == 0) && args.kb_total >= 16) {
       int parts = G / R;
       const int max_parts = args.kb_total / 8;  // at least 8 k-blocks (512 k) per part
+      if (full == 0) {
+        // fewer tiles than SMs (weight gradients of narrow models: K = tokens is long, the output small): every tile is split, and
+        // the part count is the one whose items fill whole waves best (54 tiles: 2 parts = 108 items = 73 % of a wave; 11 parts = 4.01 waves)
+        int best = parts < 1 ? 1 : parts;
+        double best_eff = 0.0;
+        const int hi = (8 * G) / R < max_parts ? (8 * G) / R : max_parts;
+        for (int c = best; c <= hi; ++c) {
+          const int items = R * c;
+          const double eff = (double)items / ((double)((items + G - 1) / G) * G);
+          if (eff > best_eff + 0.02) {
+            best_eff = eff;
+            best = c;
+          }
+        }
+        parts = best;
+      }
       if (parts > max_parts) parts = max_parts;
       if (parts > 1) {
         args.kb_per_part = (args.kb_total + parts - 1) / parts;

@@ -337,3 +337,28 @@ def test_c3_shape_properties_bf16():
     g2 = {k: v.clone() for k, v in blk.backward((2 * dy.float()).to(dtype)).items() if v is not None}
     for k in g1:
         assert max_rel_err(g2[k].float(), 2 * g1[k].float()) < 5e-3, k   # VJP is linear in dy
+
+
+def test_llama_block_fp32_ffma_gemm_path_still_matches():
+    """fp32 blocks take the tensor-core split GEMM by default; gemm_impl = SIMT keeps the FFMA GEMM (and its tighter error)."""
+    sp, L = _sp()
+    rng = np.random.default_rng(21)
+    B, T, C, H, Hkv = 2, 96, 256, 4, 2
+    hd = C // H
+    bp = llama_oracle.init_block_params(rng, C, H, Hkv)
+    x = T_(rng.standard_normal((B, T, C)).astype(np.float32))
+    dy = T_(rng.standard_normal((B, T, C)).astype(np.float32))
+    ref = llama_oracle.block_fwd_bwd(bp, x, dy, H, Hkv, causal=True, dtype=torch.float64)
+    cos, sin = llama_oracle.precompute_freqs_cis(hd, T)
+    a = bp["attention"]
+    p = {"wqkv": torch.cat([a["wq"], a["wk"], a["wv"]], dim=1).to(DEV), "wo": a["wo"].to(DEV), "norm_w": bp["attention_norm"].to(DEV),
+         "rope": sp.llama_rope_table(cos, sin).to(DEV)}
+    errs = {}
+    for name, impl in (("split", L.IMPL_AUTO), ("ffma", L.IMPL_SIMT)):
+        blk = sp.AttentionBlock(sp.BlockConfig(B, T, C, H, Hkv, hd, dtype=torch.float32, norm_kind=L.NORM_RMS, rope=True, causal=True, gemm_impl=impl))
+        y = blk.forward(x.to(DEV), p)
+        g = blk.backward(dy.to(DEV))
+        torch.cuda.synchronize()
+        errs[name] = max(max_rel_err(y, ref["y"]), max_rel_err(g["dx"], ref["dx"]), max_rel_err(g["dwo"], ref["dwo"]),
+                         max_rel_err(g["dwqkv"][:, :H * hd], ref["dwq"]), max_rel_err(g["dnorm_w"], ref["dnorm"]))
+    assert errs["split"] < TOL_F32 and errs["ffma"] < TOL_F32 / 10, errs
