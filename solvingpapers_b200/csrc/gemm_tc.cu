@@ -777,11 +777,11 @@ static int gemm_tc_launch(const void* A, int64_t lda, const void* B, int64_t ldb
         // the part count is the one whose items fill whole waves best (54 tiles: 2 parts = 108 items = 73 % of a wave; 11 parts = 4.01 waves)
         int best = parts < 1 ? 1 : parts;
         double best_eff = 0.0;
-        const int hi = (8 * G) / R < max_parts ? (8 * G) / R : max_parts;
-        for (int c = best; c <= hi; ++c) {
+        const int hi = 6 * best < max_parts ? 6 * best : max_parts;
+        for (int c = best; c <= hi; ++c) {  // more parts = more reduce-add traffic: a later candidate must fill the waves 10 % better
           const int items = R * c;
           const double eff = (double)items / ((double)((items + G - 1) / G) * G);
-          if (eff > best_eff + 0.02) {
+          if (eff > best_eff + (c == best ? 0.0 : 0.10)) {
             best_eff = eff;
             best = c;
           }
