@@ -61,6 +61,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--graph", choices=("auto", "on", "off"), default="auto",
+                    help="also time the step as a CUDA-graph replay (auto: only when the eager step is launch-bound, < 0.6 ms)")
     ap.add_argument("--sustain-s", type=float, default=3.0,
                     help="also run the step back to back for this many seconds (untimed warm-up excluded) and report the power-limited "
                          "steady state as `sustained` next to the short timed region (0 = skip)")
@@ -583,6 +585,33 @@ def run_ours(args):
                      "ms_per_step_second_half": ms_tail / tail_steps, "tok_s_second_half": tokens_local * world * tail_steps / (ms_tail * 1e-3),
                      "sm_mhz_median": clocks2.get("sm_mhz"), "reasons": clocks2.get("reasons")}
 
+    # ---- CUDA-graph leg: launch-bound shapes (a step of ~25 kernels that each run a few microseconds) replayed as one
+    # recorded graph (AttentionBlock.capture_step).  Same kernels, same buffers; only the per-launch host cost goes.
+    graph_leg = None
+    use_graph = world == 1 and h_sep is None and (args.graph == "on" or (args.graph == "auto" and ms_step < 0.6))
+    if use_graph:
+        try:
+            cap = blk.capture_step(x, dy, params, grads)
+            for _ in range(W):
+                cap.replay()
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            g0.record()
+            for _ in range(K):
+                cap.replay()
+            g1.record()
+            torch.cuda.synchronize()
+            g_ms = g0.elapsed_time(g1) / K
+            graph_leg = {"ms_per_step": g_ms, "tok_s": tokens_local / (g_ms * 1e-3), "eager_ms_per_step": ms_step,
+                         "what": "forward+backward recorded once with torch.cuda.graph, timed as K replays"}
+        except Exception as ex:  # capture is an extra leg: a failure is reported, the eager number stands
+            graph_leg = {"error": f"{type(ex).__name__}: {ex}"}
+    ws_mb = (int(blk.ws.numel()) * blk.ws.element_size() + 4 * x.numel() * x.element_size() +
+             sum(int(v.numel()) * v.element_size() for v in params.values() if hasattr(v, "numel")) +
+             sum(int(v.numel()) * v.element_size() for v in grads.values() if hasattr(v, "numel"))) / 1e6
+    l2_note = (f"per-step working set {ws_mb:.0f} MB > 126 MB L2, no flush" if ws_mb > 126 else
+               f"per-step working set {ws_mb:.1f} MB fits the 126 MB L2 and stays there between steps (no flush): an L2-warm number")
+
     # ---- roofline of the dominant kernel family (tcgen05 GEMM; FLOPs per SURVEY 8d: 3*F_gemm per step)
     pk = peaks()
     N = B * T
@@ -652,9 +681,15 @@ def run_ours(args):
     out = {"metric": "attn_block_fwd_bwd_tokens_per_s", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": K, "warmup": W,
            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dt, "data": "synthetic",
            "config": {"workload": desc, "global_batch": B * world, "seq_len": T, "parallelism": f"dp{world}" if world > 1 else "single",
-                      "l2": "per-step working set > 126 MB L2, no flush", "attn_impl": "auto", "residual": args.residual, "grad_buffers": grad_mem, "flops_per_step_per_gpu": total_flops},
+                      "l2": l2_note, "attn_impl": "auto", "residual": args.residual, "grad_buffers": grad_mem, "flops_per_step_per_gpu": total_flops},
            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "block_tflops": whole,
            "stages_ms": {k: round(v, 4) for k, v in sorted(stage_ms.items())}, "stage_rates": stage_rates, "sustained": sustained}
+    if graph_leg is not None:
+        out["graph"] = graph_leg
+        if "ms_per_step" in graph_leg and graph_leg["ms_per_step"] < ms_step:
+            # the replay is the faster way to run this step: it is the headline, the eager loop stays beside it
+            out["value"], out["ms_per_step"] = graph_leg["tok_s"], graph_leg["ms_per_step"]
+            out["config"]["launch"] = "cuda graph replay (eager loop in graph.eager_ms_per_step)"
 
     # ---- multi-rank correctness (untimed): one more step through the library's own all-reduce, then the LOCAL weight
     # gradients are recomputed from the operands that step left in the workspace (dW = xhat^T . dqkv, dWo = attn_o^T . dy,

@@ -267,6 +267,42 @@ class AttentionBlock:
         return g
 
 
+    def capture_step(self, x, dy, params, grads=None, warmup=3):
+        """Forward + backward over fixed buffers recorded once into a CUDA graph; ``replay()`` then re-launches the whole step
+        with one driver call.  For launch-bound shapes (the notebook's own dims: ~25 kernels of a few microseconds each) the
+        replay removes the per-launch host cost; at the headline shape the step is device-bound and it changes nothing.  The
+        buffers are the ones passed here: refill ``x`` / ``dy`` / the weights in place between replays."""
+        if self.comm:
+            raise L.SpbError("capture_step: the gradient all-reduce is not captured; use forward()/backward() with a communicator")
+        g = grads if grads is not None else self.alloc_grads(params)
+        if g.get("dx") is None:
+            g["dx"] = torch.empty_like(x)
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(max(warmup, 1)):          # first-use set-up (function attributes, tensor maps) happens outside capture
+                self.forward(x, params)
+                self.backward(dy, grads=g)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            y = self.forward(x, params)
+            self.backward(dy, grads=g)
+        return CapturedStep(graph, y, g)
+
+
+class CapturedStep:
+    """A recorded forward+backward (AttentionBlock.capture_step): ``y`` and ``grads`` are rewritten by every ``replay()``."""
+
+    def __init__(self, graph, y, grads):
+        self.graph, self.y, self.grads = graph, y, grads
+
+    def replay(self):
+        self.graph.replay()
+        return self.y, self.grads
+
+
 class KVCache:
     """Preallocated key/value cache [B, Tmax, Hkv, hd] that spb_block_decode appends to in place - the O(1)-per-token form of
     the notebook's ``cache`` tuple, whose ``jnp.concatenate`` (llama3/LLaMA-jax.ipynb:817-818) copies every old row on every

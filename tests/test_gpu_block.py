@@ -362,3 +362,37 @@ def test_llama_block_fp32_ffma_gemm_path_still_matches():
         errs[name] = max(max_rel_err(y, ref["y"]), max_rel_err(g["dx"], ref["dx"]), max_rel_err(g["dwo"], ref["dwo"]),
                          max_rel_err(g["dwqkv"][:, :H * hd], ref["dwq"]), max_rel_err(g["dnorm_w"], ref["dnorm"]))
     assert errs["split"] < TOL_F32 and errs["ffma"] < TOL_F32 / 10, errs
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_captured_step_replays_the_same_numbers_on_new_inputs(dtype):
+    """AttentionBlock.capture_step: the recorded forward+backward, replayed after x / dy were refilled in place, gives what
+    the eager calls give on those inputs (C1 dims)."""
+    sp, L = _sp()
+    B, T, C, H, Hkv = 16, 128, 256, 4, 2
+    hd = C // H
+    g = torch.Generator(device="cpu").manual_seed(5)
+    r = lambda *s: torch.randn(*s, generator=g)
+    cfg = sp.BlockConfig(B=B, T=T, C=C, Hq=H, Hkv=Hkv, hd=hd, dtype=dtype, norm_kind=L.NORM_RMS, norm_eps=1e-6, rope=True,
+                         causal=True, weight_layout=L.W_IN_OUT, residual=True)
+    cos, sin = llama_oracle.precompute_freqs_cis(hd, T)
+    p = {"wqkv": (r(C, (H + 2 * Hkv) * hd) * 0.05).to(dtype).to(DEV), "wo": (r(H * hd, C) * 0.05).to(dtype).to(DEV),
+         "norm_w": torch.ones(C, dtype=dtype, device=DEV), "rope": sp.llama_rope_table(cos, sin).to(DEV)}
+    x, dy = r(B, T, C).to(dtype).to(DEV), r(B, T, C).to(dtype).to(DEV)
+    blk = sp.AttentionBlock(cfg)
+    cap = blk.capture_step(x, dy, p)
+    x2, dy2 = r(B, T, C).to(dtype).to(DEV), r(B, T, C).to(dtype).to(DEV)
+    x.copy_(x2)
+    dy.copy_(dy2)
+    y, gr = cap.replay()
+    torch.cuda.synchronize()
+    got = {"y": y.clone(), **{k: v.clone() for k, v in gr.items()}}
+    eager = sp.AttentionBlock(cfg)
+    y_e = eager.forward(x2, p)
+    g_e = eager.backward(dy2)
+    torch.cuda.synchronize()
+    ref = {"y": y_e, **g_e}
+    for k in ref:
+        # same kernels on the same inputs; only the order of the fp32 reduce-adds (dQ) may differ between two runs
+        assert max_rel_err(got[k], ref[k]) < (1e-5 if dtype == torch.float32 else 1e-2), k
+    assert torch.isfinite(got["dx"].float()).all()
