@@ -62,7 +62,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--graph", choices=("auto", "on", "off"), default="auto",
-                    help="also time the step as a CUDA-graph replay (auto: only when the eager step is launch-bound, < 0.6 ms)")
+                    help="also time the step as a CUDA-graph replay (auto: only when the eager step is shorter than 2 ms, where launch gaps are a visible share)")
     ap.add_argument("--sustain-s", type=float, default=3.0,
                     help="also run the step back to back for this many seconds (untimed warm-up excluded) and report the power-limited "
                          "steady state as `sustained` next to the short timed region (0 = skip)")
@@ -588,7 +588,7 @@ def run_ours(args):
     # ---- CUDA-graph leg: launch-bound shapes (a step of ~25 kernels that each run a few microseconds) replayed as one
     # recorded graph (AttentionBlock.capture_step).  Same kernels, same buffers; only the per-launch host cost goes.
     graph_leg = None
-    use_graph = world == 1 and h_sep is None and (args.graph == "on" or (args.graph == "auto" and ms_step < 0.6))
+    use_graph = world == 1 and h_sep is None and (args.graph == "on" or (args.graph == "auto" and ms_step < 2.0))
     if use_graph:
         try:
             cap = blk.capture_step(x, dy, params, grads)
