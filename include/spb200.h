@@ -347,6 +347,14 @@ typedef struct spb_decode_ws {
 int spb_block_decode_ws_layout(const spb_block_desc* d, int32_t Tmax, spb_decode_ws* out);
 int spb_block_decode(const spb_block_desc* d, const spb_block_params* p, const void* x, void* k_cache, void* v_cache,
                      int32_t cache_len, int32_t Tmax, void* y, void* ws, spb_stream_t stream);
+/* The same step with the cache length in DEVICE memory (one int32 the caller owns and initialises): the kernels read it,
+ * and the step's last kernel advances it by Tq (never past Tmax).  No launch parameter depends on the length - the grids
+ * are sized for Tmax and share the valid key tiles evenly - so a step recorded once into a CUDA graph
+ * (llama3:499-511 `generate` loops over it) is replayed for every token: one driver call instead of seven launches, which
+ * is what bounds the eager step.  p->rope must cover positions [0, Tmax).  A step that would pass Tmax writes no cache row
+ * and attends to Tmax keys: keep the host's own count and do not replay past the capacity.                                */
+int spb_block_decode_dev(const spb_block_desc* d, const spb_block_params* p, const void* x, void* k_cache, void* v_cache,
+                         int32_t* cache_len_dev, int32_t Tmax, void* y, void* ws, spb_stream_t stream);
 
 /* ---- data parallelism: batch-sharded, weight gradients all-reduced (no reference precedent) ---- */
 int spb_comm_unique_id(void* out128);                        /* HOST buffer, 128 bytes (ncclUniqueId)      */

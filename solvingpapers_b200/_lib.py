@@ -107,6 +107,7 @@ SIGNATURES = {
     "spb_attn_decode": (C.c_int, [C.c_int, i32, i32, i32, i32, i32, i32, f32, vp, i64, vp, i64, i64, vp, i64, i64, vp, i64, vp, vp, vp]),
     "spb_block_decode_ws_layout": (C.c_int, [C.POINTER(BlockDesc), i32, C.POINTER(DecodeWs)]),
     "spb_block_decode": (C.c_int, [C.POINTER(BlockDesc), C.POINTER(BlockParams), vp, vp, vp, i32, i32, vp, vp, vp]),
+    "spb_block_decode_dev": (C.c_int, [C.POINTER(BlockDesc), C.POINTER(BlockParams), vp, vp, vp, vp, i32, vp, vp, vp]),
     "spb_comm_unique_id": (C.c_int, [vp]),
     "spb_comm_init_rank": (C.c_int, [vp, C.c_int, C.c_int, C.POINTER(vp)]),
     "spb_comm_allreduce_f32": (C.c_int, [vp, C.POINTER(vp), C.POINTER(sz), C.c_int, vp]),

@@ -312,6 +312,19 @@ class KVCache:
         self.kbuf = torch.zeros((B, Tmax, Hkv, hd), dtype=dtype, device=device)
         self.vbuf = torch.zeros((B, Tmax, Hkv, hd), dtype=dtype, device=device)
         self.length = 0
+        self._len_dev = None     # int32 on the device, read and advanced by recorded steps (DecodeBlock.capture)
+        self._len_dev_is = -1    # the value the device copy is known to hold
+
+    def length_dev(self):
+        """The cache length as one int32 in device memory, brought up to date with ``length`` (a copy only when eager steps
+        or the caller changed ``length`` since the last recorded step)."""
+        if self._len_dev is None:
+            self._len_dev = torch.zeros(1, dtype=torch.int32, device=self.kbuf.device)
+            self._len_dev_is = 0
+        if self._len_dev_is != self.length:
+            self._len_dev.fill_(self.length)
+            self._len_dev_is = self.length
+        return self._len_dev
 
     @property
     def capacity(self):
@@ -370,6 +383,59 @@ class DecodeBlock:
         cache.length += c.T
         return y
 
+    def capture(self, x, params, cache: KVCache):
+        """Record one decode step over fixed buffers (``x``, the weights, ``cache``) into a CUDA graph through
+        spb_block_decode_dev: the cache length is read from device memory and advanced by the step itself, so the same graph
+        serves every token.  ``replay()`` -> y (a fixed buffer, rewritten by every replay); refill ``x`` in place between
+        replays.  The eager step is bound by the cost of its seven launches; the replay is one driver call."""
+        c = self.cfg
+        if tuple(x.shape) != (c.B, c.T, c.C) or x.dtype != c.dtype or not x.is_contiguous():
+            raise L.SpbError(f"x must be contiguous {c.dtype} [{c.B},{c.T},{c.C}], got {tuple(x.shape)} {x.dtype}")
+        if cache.capacity != self.Tmax or cache.kbuf.dtype != c.dtype or tuple(cache.kbuf.shape) != (c.B, self.Tmax, c.Hkv, c.hd):
+            raise L.SpbError("cache does not match this DecodeBlock (shape / capacity / dtype)")
+        if c.rope:
+            r = params["rope"]
+            if r.dtype != torch.float32 or r.dim() != 3 or r.shape[0] < self.Tmax or tuple(r.shape[1:]) != (c.hd // 2, 4) or not r.is_contiguous():
+                raise L.SpbError(f"rope table must be contiguous fp32 [>= Tmax = {self.Tmax}, hd/2, 4] for a recorded step")
+        P, keep = self._marshal(self, params, check_rope=False)
+        y = torch.empty_like(x)
+        start = cache.length
+        len_dev = cache.length_dev()
+
+        def run():
+            L.check(self.lib.spb_block_decode_dev(C.byref(self.d), C.byref(P), _ptr(x), _ptr(cache.kbuf), _ptr(cache.vbuf), _ptr(len_dev),
+                                                  self.Tmax, _ptr(y), _ptr(self.ws), _stream()), "spb_block_decode_dev")
+
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            run()                      # first-use set-up (function attributes) outside the capture; it appends a row ...
+            len_dev.fill_(start)       # ... which the first replay overwrites: the length goes back to where it was
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            run()
+        return CapturedDecode(self, graph, y, cache, (x, params, keep, len_dev))
+
     def weight_bytes(self):
         c = self.cfg
         return (c.C * c.n_tot + c.n_q * c.C) * (2 if c.dtype == torch.bfloat16 else 4)
+
+
+class CapturedDecode:
+    """A recorded decode step (DecodeBlock.capture).  The host mirrors the cache length so that ``cache.length`` / ``cache.k``
+    stay usable and a replay past the capacity is refused."""
+
+    def __init__(self, block, graph, y, cache, keep):
+        self.block, self.graph, self.y, self.cache, self._keep = block, graph, y, cache, keep
+
+    def replay(self):
+        c, cache = self.block.cfg, self.cache
+        if cache.length + c.T > cache.capacity:
+            raise L.SpbError(f"decode replay: cache_len {cache.length} + Tq {c.T} exceeds the cache capacity {cache.capacity}")
+        cache.length_dev()            # re-synchronise if eager steps moved the length since the last replay
+        self.graph.replay()
+        cache.length += c.T
+        cache._len_dev_is = cache.length
+        return self.y

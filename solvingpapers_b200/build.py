@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_build")
 LIB = os.path.join(HERE, "libspb200.so")
-SOURCES = ["api.cu", "norm_rope.cu", "gemm_simt.cu", "gemm_tc.cu", "attn_simt.cu", "flash_tc.cu", "flash_bwd_tc.cu", "ffn.cu", "nll.cu", "comm.cu", "decode.cu", "attn_wide.cu", "attn_ffma.cu", "gemm_split.cu"]
+SOURCES = ["api.cu", "norm_rope.cu", "gemm_simt.cu", "gemm_tc.cu", "attn_simt.cu", "flash_tc.cu", "flash_bwd_tc.cu", "ffn.cu", "nll.cu", "comm.cu", "decode.cu", "attn_decode_mma.cu", "decode_gemm_mma.cu", "attn_wide.cu", "attn_ffma.cu", "gemm_split.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "--expt-relaxed-constexpr"]
 

@@ -987,6 +987,11 @@ int spb_block_decode_ws_layout(const spb_block_desc* d, int32_t Tmax, spb_decode
   size_t part = small_m_gemm_scratch_bytes((int)M, (int)Ntot, d->C, d->dtype);
   const size_t part_o = small_m_gemm_scratch_bytes((int)M, d->C, (int)Nq, d->dtype);
   if (part_o > part) part = part_o;
+  {  // unpacked weights project q, k, v one after the other through the same scratch: their split plans differ from the packed one
+    const size_t pq = small_m_gemm_scratch_bytes((int)M, (int)Nq, d->C, d->dtype), pk = small_m_gemm_scratch_bytes((int)M, (int)Nkv, d->C, d->dtype);
+    if (pq > part) part = pq;
+    if (pk > part) part = pk;
+  }
   out->gemm_part = take(part);
   // the split plan depends on Tk; the scratch grows with the number of key splits, which is capped - take the worst over Tk <= Tmax
   size_t ap = 0;
@@ -1001,15 +1006,18 @@ int spb_block_decode_ws_layout(const spb_block_desc* d, int32_t Tmax, spb_decode
   return 0;
 }
 
-int spb_block_decode(const spb_block_desc* d, const spb_block_params* p, const void* x, void* k_cache, void* v_cache, int32_t cache_len,
-                     int32_t Tmax, void* y, void* ws, spb_stream_t stream) {
+// len_dev == nullptr: the cache length is the host value `cache_len`.  len_dev != nullptr (spb_block_decode_dev): the length is
+// read from device memory by the kernels and advanced by Tq at the end of the step, so nothing in the launches depends on it.
+static int block_decode_impl(const spb_block_desc* d, const spb_block_params* p, const void* x, void* k_cache, void* v_cache, int32_t cache_len,
+                             int32_t* len_dev, int32_t Tmax, void* y, void* ws, spb_stream_t stream) {
   int rc = check_desc(d);
   if (rc) return rc;
   SPB_CHECK_ARG(y && k_cache && v_cache, SPB_E_INVALID, "spb_block_decode: null pointer");
   rc = check_block_params("spb_block_decode", d, p, x, ws);
   if (rc) return rc;
-  SPB_CHECK_ARG(cache_len >= 0 && cache_len + d->T <= Tmax, SPB_E_INVALID, "spb_block_decode: cache_len %d + Tq %d exceeds the cache capacity %d",
-                cache_len, d->T, Tmax);
+  SPB_CHECK_ARG(Tmax >= d->T, SPB_E_INVALID, "spb_block_decode: cache capacity %d below Tq %d", Tmax, d->T);
+  SPB_CHECK_ARG(len_dev != nullptr || (cache_len >= 0 && cache_len + d->T <= Tmax), SPB_E_INVALID,
+                "spb_block_decode: cache_len %d + Tq %d exceeds the cache capacity %d", cache_len, d->T, Tmax);
   SPB_CHECK_ARG(d->weight_layout == SPB_W_IN_OUT, SPB_E_UNSUPPORTED, "spb_block_decode: [in,out] weights only (the cache branch is the Llama notebook's)");
   SPB_CHECK_ARG(!(d->causal && d->T > 1), SPB_E_UNSUPPORTED,
                 "spb_block_decode: a causal mask over Tq > 1 new tokens has no counterpart in llama3:824-825 (its mask slice does not broadcast)");
@@ -1035,7 +1043,11 @@ int spb_block_decode(const spb_block_desc* d, const spb_block_params* p, const v
   const char *wq = (const char*)p->wq, *wk = (const char*)p->wk, *wv = (const char*)p->wv;
   bool packed = p->ldw_q == p->ldw_k && p->ldw_k == p->ldw_v && wk == wq + Nq * e && wv == wk + Nkv * e;
   if (d->qkv_bias) packed = packed && (const char*)p->bk == (const char*)p->bq + Nq * e && (const char*)p->bv == (const char*)p->bk + Nkv * e;
-  if (packed) {
+  int fused_splits = 0;  // > 0: the projection left K-slice partials in `part`; the rotary/append kernel finishes it
+  if (packed && small_m_mma_ok(dt, M, (int)Ntot, d->C, xin, d->C, wq, p->ldw_q)) {
+    rc = small_m_mma(M, (int)Ntot, d->C, xin, d->C, wq, p->ldw_q, part, &fused_splits, st);
+    if (rc) return rc;
+  } else if (packed) {
     rc = small_m_gemm(dt, M, (int)Ntot, d->C, xin, d->C, wq, p->ldw_q, qkv, Ntot, d->qkv_bias ? p->bq : nullptr, nullptr, 0, part, st);
     if (rc) return rc;
   } else {
@@ -1048,15 +1060,27 @@ int spb_block_decode(const spb_block_desc* d, const spb_block_params* p, const v
   }
   // 3. rotary at positions cache_len .. and the in-place append of the new k, v rows
   rc = decode_rope_append(dt, qkv, Ntot, d->B, d->T, d->Hq, d->Hkv, d->hd, d->rope_kind == SPB_ROPE_TABLE ? p->rope : nullptr, cache_len, k_cache,
-                          v_cache, Nkv, (int64_t)Tmax * Nkv, st);
+                          v_cache, Nkv, (int64_t)Tmax * Nkv, st, fused_splits > 0 ? part : nullptr, fused_splits, d->qkv_bias ? p->bq : nullptr,
+                          len_dev, Tmax);
   if (rc) return rc;
   // 4. attention of the new rows over the whole cache
-  rc = attn_decode(dt, d->B, d->T, d->Hq, d->Hkv, d->hd, cache_len + d->T, d->scale, qkv, Ntot, k_cache, Nkv, (int64_t)Tmax * Nkv, v_cache, Nkv,
-                   (int64_t)Tmax * Nkv, w8 + L.attn_o, Nq, nullptr, w8 + L.attn_part, st);
+  rc = attn_decode(dt, d->B, d->T, d->Hq, d->Hkv, d->hd, len_dev ? Tmax : cache_len + d->T, d->scale, qkv, Ntot, k_cache, Nkv, (int64_t)Tmax * Nkv,
+                   v_cache, Nkv, (int64_t)Tmax * Nkv, w8 + L.attn_o, Nq, nullptr, w8 + L.attn_part, st, len_dev, d->T);
   if (rc) return rc;
-  // 5. output projection (+ bias, + x)
+  // 5. output projection (+ bias, + x); its finishing kernel advances the device-side length
   return small_m_gemm(dt, M, d->C, (int)Nq, w8 + L.attn_o, Nq, p->wo, p->ldw_o, y, d->C, d->out_bias ? p->bo : nullptr, d->residual ? x : nullptr,
-                      d->C, part, st);
+                      d->C, part, st, len_dev, d->T, Tmax);
+}
+
+int spb_block_decode(const spb_block_desc* d, const spb_block_params* p, const void* x, void* k_cache, void* v_cache, int32_t cache_len,
+                     int32_t Tmax, void* y, void* ws, spb_stream_t stream) {
+  return block_decode_impl(d, p, x, k_cache, v_cache, cache_len, nullptr, Tmax, y, ws, stream);
+}
+
+int spb_block_decode_dev(const spb_block_desc* d, const spb_block_params* p, const void* x, void* k_cache, void* v_cache, int32_t* cache_len_dev,
+                         int32_t Tmax, void* y, void* ws, spb_stream_t stream) {
+  SPB_CHECK_ARG(cache_len_dev != nullptr, SPB_E_INVALID, "spb_block_decode_dev: null cache_len_dev");
+  return block_decode_impl(d, p, x, k_cache, v_cache, 0, cache_len_dev, Tmax, y, ws, stream);
 }
 
 }  // extern "C"

@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../include/spb200.h"
 
@@ -33,6 +34,33 @@ int sm_count();
       return (int)e__;                                                                       \
     }                                                                                        \
   } while (0)
+
+// Programmatic dependent launch (decode chain: eight short kernels back to back).  A kernel launched with launch_pdl may
+// start while its predecessor in the stream is still running; everything it reads from that predecessor must come after
+// pdl_wait() (returns when the predecessor grid has completed and its writes are visible).  pdl_launch_dependents() lets
+// the NEXT kernel start being scheduled.  Both are no-ops in a kernel launched the ordinary way.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool pdl, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+inline bool decode_pdl_enabled() {  // SPB_DECODE_PDL=0: ordinary launches
+  static const bool on = [] { const char* e = getenv("SPB_DECODE_PDL"); return !(e && e[0] == '0'); }();
+  return on;
+}
+#endif
 
 #define SPB_LAUNCH_CHECK()                                                                   \
   do {                                                                                       \

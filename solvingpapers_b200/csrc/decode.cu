@@ -169,8 +169,12 @@ __global__ void __launch_bounds__(DEC_THREADS) small_m_gemm_kernel(const T* __re
 // out[m, n] = sum_s part[s, m, n] (+ bias[n]) (+ res[m, n]); fixed summation order
 template <typename T>
 __global__ void __launch_bounds__(256) small_m_reduce_kernel(const float* __restrict__ part, int splits, T* __restrict__ out, int64_t ldo,
-                                                            const T* __restrict__ bias, const T* __restrict__ res, int64_t ldr, int M, int N) {
+                                                            const T* __restrict__ bias, const T* __restrict__ res, int64_t ldr, int M, int N,
+                                                            int* __restrict__ advance, int by, int cap) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (advance != nullptr && i == 0) *advance = min(*advance + by, cap);  // every reader of the length in this step is complete (stream order)
   if (i >= (int64_t)M * N) return;
   const int m = (int)(i / N), n = (int)(i % N);
   float s = 0.f;
@@ -192,12 +196,17 @@ static int small_m_splits(int M, int N, int K, int ve) {
 }
 
 size_t small_m_gemm_scratch_bytes(int M, int N, int K, int dtype) {
-  return (size_t)small_m_splits(M, N, K, dtype == SPB_BF16 ? 8 : 4) * M * N * sizeof(float);
+  size_t b = (size_t)small_m_splits(M, N, K, dtype == SPB_BF16 ? 8 : 4) * M * N * sizeof(float);
+  if (dtype == SPB_BF16 && M <= 64) {
+    const size_t m = small_m_mma_scratch_bytes(M, N, K);
+    if (m > b) b = m;
+  }
+  return b;
 }
 
 template <typename T>
 static int small_m_gemm_t(int M, int N, int K, const T* A, int64_t lda, const T* W, int64_t ldw, T* D, int64_t ldd, const T* bias, const T* res,
-                          int64_t ldr, float* part, cudaStream_t st) {
+                          int64_t ldr, float* part, cudaStream_t st, int* advance, int by, int cap) {
   constexpr int VE = Vec16<T>::N;
   SPB_CHECK_ARG(N % VE == 0 && ldw % VE == 0 && (uintptr_t)W % 16 == 0, SPB_E_UNSUPPORTED,
                 "small-M GEMM: the weight needs 16-byte aligned rows (N=%d ldw=%lld)", N, (long long)ldw);
@@ -220,16 +229,27 @@ static int small_m_gemm_t(int M, int N, int K, const T* A, int64_t lda, const T*
 #undef SPB_SMG_LAUNCH
   SPB_LAUNCH_CHECK();
   const int64_t total = (int64_t)M * N;
-  small_m_reduce_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(part, nsplit, D, ldd, bias, res, ldr, M, N);
+  small_m_reduce_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(part, nsplit, D, ldd, bias, res, ldr, M, N, advance, by, cap);
   SPB_LAUNCH_CHECK();
   return 0;
 }
 
 // D[M,N] = A[M,K] . W[K,N] (+bias) (+res); M <= 64 rows; `part` = small_m_gemm_scratch_bytes(M, N, K, dtype)
 int small_m_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, const void* W, int64_t ldw, void* D, int64_t ldd, const void* bias,
-                 const void* res, int64_t ldr, float* part, cudaStream_t st) {
+                 const void* res, int64_t ldr, float* part, cudaStream_t st, int* advance, int by, int cap) {
   SPB_CHECK_ARG(M >= 1 && M <= 64 && N >= 1 && K >= 1, SPB_E_LIMIT, "small-M GEMM: M=%d rows (1..64 supported; longer inputs go through the prefill path)", M);
-  // bf16: the tcgen05 GEMM with its K-split for few-tile problems (one 128-row tile, N/256 column tiles, K cut into up to 8
+  // bf16: the weight stream on mma.sync (decode_gemm_mma.cu): K slices -> fp32 partials, summed below
+  if (small_m_mma_ok(dtype, M, N, K, A, lda, W, ldw)) {
+    int nsplit = 1;
+    int rc = small_m_mma(M, N, K, A, lda, W, ldw, part, &nsplit, st);
+    if (rc) return rc;
+    const int64_t total = (int64_t)M * N;
+    SPB_CUDA(launch_pdl(small_m_reduce_kernel<__nv_bfloat16>, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, decode_pdl_enabled(),
+                        (const float*)part, nsplit, (__nv_bfloat16*)D, ldd, (const __nv_bfloat16*)bias, (const __nv_bfloat16*)res, ldr, M, N, advance, by, cap));
+    SPB_LAUNCH_CHECK();
+    return 0;
+  }
+  // SPB_DECODE_GEMM_MMA=0: the tcgen05 GEMM with its K-split for few-tile problems (one 128-row tile, N/256 column tiles, K cut into up to 8
   // parts that TMA-reduce into a zeroed fp32 [M, N]) streams the weight at HBM speed with no CUDA-core arithmetic at all -
   // the SIMT kernel below is bound by FMA issue on one warp per scheduler (ncu r02d: 28 % issue-active, 34 k cycles for 50 MB).
   // The fp32 result is finished (bias, residual, conversion) by the reduce kernel with one "split".
@@ -238,23 +258,32 @@ int small_m_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, con
     if (rc) return rc;
     const int64_t total = (int64_t)M * N;
     small_m_reduce_kernel<__nv_bfloat16><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(part, 1, (__nv_bfloat16*)D, ldd, (const __nv_bfloat16*)bias,
-                                                                                      (const __nv_bfloat16*)res, ldr, M, N);
+                                                                                      (const __nv_bfloat16*)res, ldr, M, N, advance, by, cap);
     SPB_LAUNCH_CHECK();
     return 0;
   }
   if (dtype == SPB_BF16)
     return small_m_gemm_t<__nv_bfloat16>(M, N, K, (const __nv_bfloat16*)A, lda, (const __nv_bfloat16*)W, ldw, (__nv_bfloat16*)D, ldd,
-                                         (const __nv_bfloat16*)bias, (const __nv_bfloat16*)res, ldr, part, st);
-  return small_m_gemm_t<float>(M, N, K, (const float*)A, lda, (const float*)W, ldw, (float*)D, ldd, (const float*)bias, (const float*)res, ldr, part, st);
+                                         (const __nv_bfloat16*)bias, (const __nv_bfloat16*)res, ldr, part, st, advance, by, cap);
+  return small_m_gemm_t<float>(M, N, K, (const float*)A, lda, (const float*)W, ldw, (float*)D, ldd, (const float*)bias, (const float*)res, ldr, part, st,
+                               advance, by, cap);
 }
 
 // ------------------------------------------------------------------------------------------------ K6: rotary + cache append
 // qkv [B*Tq, ld] (q | k | v columns).  q is rotated in place; k is rotated and written, v copied, into the caches at token
 // rows pos0 .. pos0+Tq-1 of each batch entry.  One thread per adjacent pair (2j, 2j+1) of a (row, head).
+// With `part` != nullptr the kernel is also the finish of the projection: the pair is first summed over the K slices'
+// fp32 partials [nsplit][B*Tq][ld] (+ bias) and rounded to T - what small_m_reduce_kernel would have stored - so the
+// projection's reduce pass and this one are a single launch.
 template <typename T>
 __global__ void __launch_bounds__(256) decode_rope_append_kernel(T* __restrict__ qkv, int64_t ld, int B, int Tq, int Hq, int Hkv, int hd,
                                                                 const float4* __restrict__ rope, int pos0, T* __restrict__ kc,
-                                                                T* __restrict__ vc, int64_t ldc, int64_t cache_batch_stride) {
+                                                                T* __restrict__ vc, int64_t ldc, int64_t cache_batch_stride,
+                                                                const float* __restrict__ part, int nsplit, const T* __restrict__ bias,
+                                                                const int* __restrict__ pos0_dev, int cap) {
+  pdl_launch_dependents();
+  pdl_wait();
+  if (pos0_dev != nullptr) pos0 = *pos0_dev;  // recorded step: the cache length is read here, not baked into the launch
   const int hp = hd / 2;
   const int heads = Hq + 2 * Hkv;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -264,8 +293,28 @@ __global__ void __launch_bounds__(256) decode_rope_append_kernel(T* __restrict__
   const int h = (int)((idx / hp) % heads);
   const int64_t row = idx / ((int64_t)hp * heads);  // b * Tq + t
   const int t = (int)(row % Tq), b = (int)(row / Tq);
+  if (pos0_dev != nullptr && pos0 + t >= cap) return;  // a replay past the capacity writes nothing (the host wrapper refuses it first)
   T* src = qkv + row * ld + (int64_t)h * hd + 2 * j;
-  float xe = to_f32<T>(src[0]), xo = to_f32<T>(src[1]);
+  float xe, xo;
+  if (part != nullptr) {
+    const int64_t col = (int64_t)h * hd + 2 * j;
+    const int64_t slab = (int64_t)B * Tq * ld;
+    float se = 0.f, so = 0.f;
+    for (int p = 0; p < nsplit; ++p) {
+      const float2 v = *reinterpret_cast<const float2*>(part + p * slab + row * ld + col);
+      se += v.x;
+      so += v.y;
+    }
+    if (bias != nullptr) {
+      se += to_f32<T>(bias[col]);
+      so += to_f32<T>(bias[col + 1]);
+    }
+    xe = to_f32<T>(from_f32<T>(se));
+    xo = to_f32<T>(from_f32<T>(so));
+  } else {
+    xe = to_f32<T>(src[0]);
+    xo = to_f32<T>(src[1]);
+  }
   if (h < Hq + Hkv && rope != nullptr) {  // q and k heads: pair <- 2x2 block of the table row of position pos0 + t
     const float4 m = rope[(int64_t)(pos0 + t) * hp + j];
     const float e2 = m.x * xe + m.y * xo, o2 = m.z * xe + m.w * xo;
@@ -295,6 +344,8 @@ struct DecArgs {
   float* pml;         // partial (m, l) [B, Hq, Tq, splits, 2]
   int B, Tq, Hq, Hkv, Tk, splits, tiles_per_split, row_groups;
   float scale;
+  const int* tk_dev;  // != nullptr: valid keys = min(*tk_dev + tk_add, Tk), read on the device (a recorded step)
+  int tk_add;
 };
 
 // A CTA of 256 threads streams its slice of the cache in tiles of KT keys through a two-stage shared-memory ring filled with
@@ -336,11 +387,16 @@ __global__ void __launch_bounds__(DA_THREADS) attn_decode_kernel(const DecArgs p
   const T* kbase = (const T*)p.k + (int64_t)b * p.kbs + (int64_t)g * HD;
   const T* vbase = (const T*)p.v + (int64_t)b * p.vbs + (int64_t)g * HD;
   const int vg = t / TPR, vc = (t % TPR) * VE;
-  const int tile0 = split * p.tiles_per_split;
-  const int tile1 = min(tile0 + p.tiles_per_split, (p.Tk + KT - 1) / KT);
+  int Tk = p.Tk, tps = p.tiles_per_split;
+  if (p.tk_dev != nullptr) {  // grid sized for the capacity: share the tiles that exist evenly over its splits
+    Tk = min(*p.tk_dev + p.tk_add, p.Tk);
+    tps = ((Tk + KT - 1) / KT + p.splits - 1) / p.splits;
+  }
+  const int tile0 = split * tps;
+  const int tile1 = min(tile0 + tps, (Tk + KT - 1) / KT);
 
   auto stage_tile = [&](int tile) {  // one cp.async group per tile: K and V rows of the tile -> stage (tile - tile0) & 1
-    const int k0 = tile * KT, kn = min(KT, p.Tk - k0);
+    const int k0 = tile * KT, kn = min(KT, Tk - k0);
     uint8_t* sK = dsm + ((tile - tile0) & 1) * DecTile<T, HD>::STAGE_BYTES;
     uint8_t* sV = sK + KT * ROWB;
     for (int jj = vg; jj < kn; jj += G) {
@@ -374,7 +430,7 @@ __global__ void __launch_bounds__(DA_THREADS) attn_decode_kernel(const DecArgs p
   const int key = t >> 1, half = t & 1;  // score phase: two threads per key, 16-byte pieces 2i + half
   for (int tile = tile0; tile < tile1; ++tile) {
     const int k0 = tile * KT;
-    const int kn = min(KT, p.Tk - k0);
+    const int kn = min(KT, Tk - k0);
     const uint8_t* sK = dsm + ((tile - tile0) & 1) * DecTile<T, HD>::STAGE_BYTES;
     const uint8_t* sV = sK + KT * ROWB;
     if (tile + 1 < tile1) cp_async_wait<1>(); else cp_async_wait<0>();  // this thread's copies of this tile have landed
@@ -482,25 +538,54 @@ __global__ void __launch_bounds__(DA_THREADS) attn_decode_kernel(const DecArgs p
 template <typename T>
 __global__ void __launch_bounds__(128) attn_decode_combine_kernel(const float* __restrict__ po, const float* __restrict__ pml, T* __restrict__ o,
                                                                   int64_t ldo, float* __restrict__ lse, int B, int Tq, int Hq, int hd, int splits) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t row = blockIdx.x;  // (b * Hq + hq) * Tq + tq
   const int tq = (int)(row % Tq), hq = (int)((row / Tq) % Hq), b = (int)(row / ((int64_t)Tq * Hq));
-  float M = -INFINITY;
-  for (int s = 0; s < splits; ++s) M = fmaxf(M, pml[(row * splits + s) * 2]);
-  float L = 0.f;
-  for (int s = 0; s < splits; ++s) {
-    const float m = pml[(row * splits + s) * 2];
-    if (m != -INFINITY) L += __expf(m - M) * pml[(row * splits + s) * 2 + 1];
+  // the splits' (m, l) once into shared memory (splits <= 64 < blockDim), then w_s = exp(m_s - M) and w_s * l_s once per split
+  __shared__ float sm_m[64], sm_w[64], sm_wl[64];
+  const int t = threadIdx.x;
+  float lv = 0.f;
+  if (t < splits) {
+    const float2 ml = *reinterpret_cast<const float2*>(pml + (row * splits + t) * 2);
+    sm_m[t] = ml.x;
+    lv = ml.y;
   }
+  __syncthreads();
+  float M = -INFINITY;
+  for (int s = 0; s < splits; ++s) M = fmaxf(M, sm_m[s]);
+  if (t < splits) {
+    const float w = (sm_m[t] == -INFINITY) ? 0.f : __expf(sm_m[t] - M);
+    sm_w[t] = w;
+    sm_wl[t] = w * lv;
+  }
+  __syncthreads();
+  float L = 0.f;
+  for (int s = 0; s < splits; ++s) L += sm_wl[s];  // fixed order, every thread the same sum
   const float inv = 1.0f / L;
-  for (int d = threadIdx.x; d < hd; d += blockDim.x) {
+  for (int d = t; d < hd; d += blockDim.x) {
     float acc = 0.f;
+#pragma unroll 4
     for (int s = 0; s < splits; ++s) {
-      const float m = pml[(row * splits + s) * 2];
-      if (m != -INFINITY) acc += __expf(m - M) * po[(row * splits + s) * hd + d];
+      const float w = sm_w[s];
+      if (w != 0.f) acc += w * po[(row * splits + s) * hd + d];
     }
     o[((int64_t)b * Tq + tq) * ldo + (int64_t)hq * hd + d] = from_f32<T>(acc * inv);
   }
-  if (lse != nullptr && threadIdx.x == 0) lse[row] = M + logf(L);
+  if (lse != nullptr && t == 0) lse[row] = M + logf(L);
+}
+
+int attn_decode_combine(int dtype, const float* po, const float* pml, void* o, int64_t ldo, float* lse, int B, int Tq, int Hq, int hd, int splits,
+                        cudaStream_t st) {
+  const unsigned rows = (unsigned)((int64_t)B * Hq * Tq);
+  if (dtype == SPB_BF16)
+    SPB_CUDA(launch_pdl(attn_decode_combine_kernel<__nv_bfloat16>, dim3(rows), dim3(128), 0, st, decode_pdl_enabled(), po, pml, (__nv_bfloat16*)o, ldo, lse, B,
+                        Tq, Hq, hd, splits));
+  else
+    SPB_CUDA(launch_pdl(attn_decode_combine_kernel<float>, dim3(rows), dim3(128), 0, st, decode_pdl_enabled(), po, pml, (float*)o, ldo, lse, B, Tq, Hq, hd,
+                        splits));
+  SPB_LAUNCH_CHECK();
+  return 0;
 }
 
 static int decode_kt(int dtype, int hd) {  // DecTile<T, HD>::KT on the host
@@ -532,6 +617,10 @@ size_t attn_decode_scratch_bytes(int B, int Tq, int Hq, int Hkv, int hd, int Tk)
     int RB, rgs, splits, tps;
     decode_plan(dtype, hd, B, Tq, Hq, Hkv, Tk, RB, rgs, splits, tps);
     const size_t b = (size_t)B * Hq * Tq * splits * ((size_t)hd + 2) * sizeof(float) + 256;
+    if (b > worst) worst = b;
+  }
+  if (attn_decode_mma_supported(SPB_BF16, hd)) {
+    const size_t b = attn_decode_mma_scratch_bytes(B, Tq, Hq, Hkv, hd, Tk);
     if (b > worst) worst = b;
   }
   return worst;
@@ -567,18 +656,22 @@ static int attn_decode_launch(DecArgs a, int RB, void* o, int64_t ldo, float* ls
 }
 
 int attn_decode(int dtype, int B, int Tq, int Hq, int Hkv, int hd, int Tk, float scale, const void* q, int64_t ldq, const void* k, int64_t ldk,
-                int64_t kbs, const void* v, int64_t ldv, int64_t vbs, void* o, int64_t ldo, float* lse, void* scratch, cudaStream_t st) {
+                int64_t kbs, const void* v, int64_t ldv, int64_t vbs, void* o, int64_t ldo, float* lse, void* scratch, cudaStream_t st,
+                const int* tk_dev, int tk_add) {
   SPB_CHECK_ARG(attn_decode_supported(dtype, hd), SPB_E_UNSUPPORTED, "attention decode: dtype %d / head dim %d (fp32 or bf16; 64, 128, 256)", dtype, hd);
   const int ve = dtype == SPB_BF16 ? 8 : 4;
   SPB_CHECK_ARG(ldk % ve == 0 && ldv % ve == 0 && kbs % ve == 0 && vbs % ve == 0 && (uintptr_t)k % 16 == 0 && (uintptr_t)v % 16 == 0, SPB_E_UNSUPPORTED,
                 "attention decode: the caches need 16-byte aligned rows");
   SPB_CHECK_ARG((int64_t)B * Hq * Tq < (1LL << 31) && B <= 65535 && Tq >= 1 && Tk >= 1, SPB_E_LIMIT, "attention decode: size beyond the grid limits");
+  if (attn_decode_mma_supported(dtype, hd) && ldq % 8 == 0 && (uintptr_t)q % 16 == 0)  // bf16: the tensor-core kernel (attn_decode_mma.cu)
+    return attn_decode_mma(B, Tq, Hq, Hkv, hd, Tk, scale, q, ldq, k, ldk, kbs, v, ldv, vbs, o, ldo, lse, scratch, st, tk_dev, tk_add);
   DecArgs a;
   int RB;
   decode_plan(dtype, hd, B, Tq, Hq, Hkv, Tk, RB, a.row_groups, a.splits, a.tiles_per_split);
   SPB_CHECK_ARG((int64_t)Hkv * a.row_groups <= 65535, SPB_E_LIMIT, "attention decode: too many query rows per kv head");
   a.q = q; a.ldq = ldq; a.k = k; a.v = v; a.ldk = ldk; a.ldv = ldv; a.kbs = kbs; a.vbs = vbs;
   a.B = B; a.Tq = Tq; a.Hq = Hq; a.Hkv = Hkv; a.Tk = Tk; a.scale = scale;
+  a.tk_dev = tk_dev; a.tk_add = tk_add;
   a.po = (float*)scratch;
   a.pml = a.po + (size_t)B * Hq * Tq * a.splits * hd;
 #define SPB_DEC_CASE(TY, HDV) return attn_decode_launch<TY, HDV>(a, RB, o, ldo, lse, st)
@@ -595,19 +688,20 @@ int attn_decode(int dtype, int B, int Tq, int Hq, int Hkv, int hd, int Tk, float
 
 template <typename T>
 static int rope_append_t(void* qkv, int64_t ld, int B, int Tq, int Hq, int Hkv, int hd, const float* rope, int pos0, void* kc, void* vc,
-                         int64_t ldc, int64_t cbs, cudaStream_t st) {
+                         int64_t ldc, int64_t cbs, const float* part, int nsplit, const void* bias, const int* pos0_dev, int cap, cudaStream_t st) {
   const int64_t total = (int64_t)B * Tq * (Hq + 2 * Hkv) * (hd / 2);
-  decode_rope_append_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((T*)qkv, ld, B, Tq, Hq, Hkv, hd, (const float4*)rope, pos0, (T*)kc,
-                                                                             (T*)vc, ldc, cbs);
+  SPB_CUDA(launch_pdl(decode_rope_append_kernel<T>, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, decode_pdl_enabled(), (T*)qkv, ld, B, Tq, Hq,
+                      Hkv, hd, (const float4*)rope, pos0, (T*)kc, (T*)vc, ldc, cbs, part, nsplit, (const T*)bias, pos0_dev, cap));
   SPB_LAUNCH_CHECK();
   return 0;
 }
 
 int decode_rope_append(int dtype, void* qkv, int64_t ld, int B, int Tq, int Hq, int Hkv, int hd, const float* rope, int pos0, void* kc, void* vc,
-                       int64_t ldc, int64_t cbs, cudaStream_t st) {
+                       int64_t ldc, int64_t cbs, cudaStream_t st, const float* part, int nsplit, const void* bias, const int* pos0_dev, int cap) {
   SPB_CHECK_ARG(hd % 2 == 0, SPB_E_INVALID, "decode: odd head dim");
-  if (dtype == SPB_BF16) return rope_append_t<__nv_bfloat16>(qkv, ld, B, Tq, Hq, Hkv, hd, rope, pos0, kc, vc, ldc, cbs, st);
-  return rope_append_t<float>(qkv, ld, B, Tq, Hq, Hkv, hd, rope, pos0, kc, vc, ldc, cbs, st);
+  if (dtype == SPB_BF16)
+    return rope_append_t<__nv_bfloat16>(qkv, ld, B, Tq, Hq, Hkv, hd, rope, pos0, kc, vc, ldc, cbs, part, nsplit, bias, pos0_dev, cap, st);
+  return rope_append_t<float>(qkv, ld, B, Tq, Hq, Hkv, hd, rope, pos0, kc, vc, ldc, cbs, part, nsplit, bias, pos0_dev, cap, st);
 }
 
 }  // namespace spb

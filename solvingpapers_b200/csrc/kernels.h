@@ -98,13 +98,31 @@ int attn_wide_bwd(int B, int T, int Hq, int Hkv, int hd, int causal, float scale
 
 // decode.cu
 size_t small_m_gemm_scratch_bytes(int M, int N, int K, int dtype);
+// advance != nullptr: the finishing kernel also does *advance = min(*advance + by, cap) (the device-side cache length of a recorded step)
 int small_m_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, const void* W, int64_t ldw, void* D, int64_t ldd, const void* bias,
-                 const void* res, int64_t ldr, float* part, cudaStream_t st);
+                 const void* res, int64_t ldr, float* part, cudaStream_t st, int* advance = nullptr, int by = 0, int cap = 0);
 bool attn_decode_supported(int dtype, int hd);
 size_t attn_decode_scratch_bytes(int B, int Tq, int Hq, int Hkv, int hd, int Tk);
+// tk_dev != nullptr: the number of valid keys is min(*tk_dev + tk_add, Tk), read on the device (a step recorded in a CUDA graph);
+// Tk is then the cache capacity the grid and the scratch are sized for
 int attn_decode(int dtype, int B, int Tq, int Hq, int Hkv, int hd, int Tk, float scale, const void* q, int64_t ldq, const void* k, int64_t ldk,
-                int64_t kbs, const void* v, int64_t ldv, int64_t vbs, void* o, int64_t ldo, float* lse, void* scratch, cudaStream_t st);
+                int64_t kbs, const void* v, int64_t ldv, int64_t vbs, void* o, int64_t ldo, float* lse, void* scratch, cudaStream_t st,
+                const int* tk_dev = nullptr, int tk_add = 0);
+// decode_gemm_mma.cu: bf16 D[M <= 64, N] = A . W[K, N] as a weight stream on mma.sync; fp32 partials per K slice
+bool small_m_mma_ok(int dtype, int M, int N, int K, const void* A, int64_t lda, const void* W, int64_t ldw);
+size_t small_m_mma_scratch_bytes(int M, int N, int K);
+int small_m_mma(int M, int N, int K, const void* A, int64_t lda, const void* W, int64_t ldw, float* part, int* nsplit_out, cudaStream_t st);
+// attn_decode_mma.cu: bf16 decode attention on mma.sync (16 query rows per kv head and CTA); partials merged by attn_decode_combine
+bool attn_decode_mma_supported(int dtype, int hd);
+size_t attn_decode_mma_scratch_bytes(int B, int Tq, int Hq, int Hkv, int hd, int Tk);
+int attn_decode_mma(int B, int Tq, int Hq, int Hkv, int hd, int Tk, float scale, const void* q, int64_t ldq, const void* k, int64_t ldk, int64_t kbs,
+                    const void* v, int64_t ldv, int64_t vbs, void* o, int64_t ldo, float* lse, void* scratch, cudaStream_t st,
+                    const int* tk_dev = nullptr, int tk_add = 0);
+int attn_decode_combine(int dtype, const float* po, const float* pml, void* o, int64_t ldo, float* lse, int B, int Tq, int Hq, int hd, int splits,
+                        cudaStream_t st);
+// part != nullptr: also sums the projection's K-slice partials [nsplit][B*Tq][ld] (+ bias) - the reduce pass and the rotary/append in one launch
 int decode_rope_append(int dtype, void* qkv, int64_t ld, int B, int Tq, int Hq, int Hkv, int hd, const float* rope, int pos0, void* kc, void* vc,
-                       int64_t ldc, int64_t cbs, cudaStream_t st);
+                       int64_t ldc, int64_t cbs, cudaStream_t st, const float* part = nullptr, int nsplit = 0, const void* bias = nullptr,
+                       const int* pos0_dev = nullptr, int cap = 0);
 
 }  // namespace spb

@@ -67,6 +67,7 @@ __global__ void __launch_bounds__(NR_THREADS) norm_fwd_kernel(const T* __restric
   constexpr int VN = Vec<T>::N;
   constexpr int RPC = 8 / WPR;
   __shared__ float red[2][8];
+  pdl_launch_dependents();  // a kernel launched with launch_pdl behind this one may begin its own prologue
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int w_in = warp % WPR;
   const int64_t row = (int64_t)blockIdx.x * RPC + warp / WPR;

@@ -33,6 +33,8 @@ def tol(dtype):
     (2, 3, 4, 1, 64, 131),      # several new tokens, MQA: 12 query rows per kv head -> two row groups
     (1, 1, 1, 1, 256, 300),     # one head of 256
     (3, 2, 2, 2, 64, 1),        # a single key
+    (2, 5, 8, 2, 128, 777),     # 20 query rows per kv head: more than the 16 rows of one MMA tile -> two row groups (bf16 path)
+    (1, 2, 4, 1, 256, 1500),    # wide heads, several key tiles, MQA
 ])
 def test_attn_decode_against_oracle_math(dtype, B, Tq, Hq, Hkv, hd, Tk):
     from solvingpapers_b200 import ops
@@ -151,6 +153,67 @@ def test_block_decode_c3_shape_bf16_against_oracle():
     assert max_rel_err(y, ref) < TOL_BF16
     assert max_rel_err(cache.k[:, -1:], kref[:, -1:]) < TOL_BF16 and max_rel_err(cache.v[:, -1:], vref[:, -1:]) < TOL_BF16
     assert torch.equal(cache.k[:, :-1].cpu(), dev(ck).cpu())   # old rows untouched
+
+
+@pytest.mark.parametrize("dtype,B,C,H,Hkv,Tc,steps", [
+    (torch.bfloat16, 4, 1024, 8, 2, 300, 9),     # crosses a 64-key tile boundary (300 -> 309 .. 320 would; 9 steps stay inside one more tile)
+    (torch.bfloat16, 2, 512, 4, 4, 60, 8),       # 60 -> 68: the tile count of the valid range changes under the recorded grid
+    (torch.float32, 16, 256, 4, 2, 22, 6),       # the notebook's dims (C1-decode), fp32 kernels
+])
+def test_recorded_decode_step_replays_like_eager_steps(dtype, B, C, H, Hkv, Tc, steps):
+    """DecodeBlock.capture (spb_block_decode_dev in a CUDA graph: length in device memory, advanced by the step) against the
+    same number of eager spb_block_decode steps on a twin cache: outputs per token, the appended rows and the final length."""
+    import solvingpapers_b200 as sp
+    from solvingpapers_b200 import _lib as L
+    hd = C // H
+    rng = np.random.default_rng(11)
+    bp = llama_oracle.init_block_params(rng, C, H, Hkv)
+    a = bp["attention"]
+    dev = lambda t: t.to(dtype).to(DEV)
+    Tmax = Tc + steps + 3
+    fc = llama_oracle.precompute_freqs_cis(hd, Tmax)
+    p = {"wqkv": dev(torch.cat([a["wq"], a["wk"], a["wv"]], dim=1)), "wo": dev(a["wo"]), "norm_w": dev(bp["attention_norm"]),
+         "rope": sp.llama_rope_table(*fc).to(DEV)}
+    ck = dev(T_(rng.standard_normal((B, Tc, Hkv, hd)).astype(np.float32)))
+    cv = dev(T_(rng.standard_normal((B, Tc, Hkv, hd)).astype(np.float32)))
+    xs = [dev(T_(rng.standard_normal((B, 1, C)).astype(np.float32))) for _ in range(steps)]
+    cfg = sp.BlockConfig(B, 1, C, H, Hkv, hd, dtype=dtype, norm_kind=L.NORM_RMS, rope=True, causal=False, residual=True)
+    # eager
+    cache_e = sp.KVCache.from_tensors(ck, cv, extra=Tmax - Tc)
+    dec_e = sp.DecodeBlock(cfg, Tmax)
+    ys_e = [dec_e.step(x, p, cache_e).clone() for x in xs]
+    # recorded
+    cache_g = sp.KVCache.from_tensors(ck, cv, extra=Tmax - Tc)
+    dec_g = sp.DecodeBlock(cfg, Tmax)
+    xbuf = torch.empty_like(xs[0])
+    cap = dec_g.capture(xbuf, p, cache_g)
+    assert cache_g.length == Tc                      # recording appends nothing that stays
+    ys_g = []
+    for x in xs:
+        xbuf.copy_(x)
+        ys_g.append(cap.replay().clone())
+    torch.cuda.synchronize()
+    assert cache_g.length == cache_e.length == Tc + steps
+    assert int(cache_g.length_dev().item()) == Tc + steps
+    tol_same = 1e-5 if dtype == torch.float32 else 1e-2   # same kernels; the key splits (and so the fp32 merge order) differ
+    for i, (ye, yg) in enumerate(zip(ys_e, ys_g)):
+        assert max_rel_err(yg, ye) < tol_same, i
+    assert max_rel_err(cache_g.k, cache_e.k) < tol_same and max_rel_err(cache_g.v, cache_e.v) < tol_same
+    assert torch.equal(cache_g.k[:, :Tc].cpu(), ck.cpu())
+    # an eager step in between moves the length on the host only: the next replay re-synchronises the device copy
+    x_extra = xs[0]
+    y_e = dec_e.step(x_extra, p, cache_e)
+    y_mixed = dec_g.step(x_extra, p, cache_g)
+    assert max_rel_err(y_mixed, y_e) < tol_same
+    xbuf.copy_(xs[1])
+    y_g2 = cap.replay().clone()
+    y_e2 = dec_e.step(xs[1], p, cache_e)
+    torch.cuda.synchronize()
+    assert cache_g.length == cache_e.length == Tc + steps + 2
+    assert max_rel_err(y_g2, y_e2) < tol_same
+    with pytest.raises(L.SpbError, match="exceeds the cache capacity"):
+        for _ in range(3):
+            cap.replay()
 
 
 def test_decode_rejects_what_it_cannot_do():
