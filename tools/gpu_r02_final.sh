@@ -15,3 +15,12 @@ timeout 900 ncu --set full --clock-control none --import-source on -k "regex:gem
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:flash_ -s 9 -c 3 -o gpurun_out/${T}_prof_flash -f $CMD > gpurun_out/${T}_ncu_flash.log 2>&1; echo "ncu flash rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"norm_|colsum_|rope_" -s 12 -c 4 -o gpurun_out/${T}_prof_norm -f $CMD > gpurun_out/${T}_ncu_norm.log 2>&1; echo "ncu norm rc=$?"
 ls -la gpurun_out/${T}_*.ncu-rep
+# decode: plain run, then the full capture of its two streaming kernels
+DCMD="python bench.py --workload c3dec32 --steps 4 --warmup 3 --graph off --no-cpu-baseline"
+timeout 600 $DCMD > gpurun_out/${T}_plain_dec.log 2>&1 &&
+timeout 900 ncu --set full --clock-control none --import-source on -k "regex:attn_decode_mma_kernel|small_m_mma_kernel" -s 9 -c 3 -o gpurun_out/${T}_prof_decode -f $DCMD > gpurun_out/${T}_ncu_decode.log 2>&1; echo "ncu decode rc=$?"
+# the other configs and the decode lines on the final library, and the per-shape cuBLAS comparison
+for wl in c1 c2 c2lit c4 c4lit c5 c3dec c3dec32 c1dec; do
+  timeout 600 python bench.py --workload $wl --steps 20 --warmup 5 --sustain-s 0 > gpurun_out/${T}_bench_$wl.json 2>> gpurun_out/${T}_bench.err; echo "$wl rc=$?"
+done
+timeout 300 python tools/diag_gemm_vs_cublas.py > gpurun_out/${T}_gemm_vs_cublas.jsonl 2>> gpurun_out/${T}_bench.err; tail -1 gpurun_out/${T}_gemm_vs_cublas.jsonl
