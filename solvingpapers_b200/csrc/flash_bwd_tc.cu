@@ -578,6 +578,437 @@ __global__ void __launch_bounds__(256) flash_bwd_dq_convert_kernel(const float* 
   }
 }
 
+// ------------------------------------------------------------------------------------------------ hd = 256: two ROLES per KV tile
+// dV + dK at hd 256 are 512 TMEM columns: they cannot live in one CTA next to S^T, dP^T and dQ^T.  The first version above
+// splits the OUTPUT columns over two CTAs (z = 0, 1), and both recompute the full S^T and dP^T (7 matmul units for 5) with a
+// single Q/dO stage each (K and V resident: no shared memory for a second one), so every iteration is a serial chain
+// TMA -> S^T/dP^T -> element-wise -> dV/dK/dQ^T (6100 clk, tensor pipe 29 % busy; profiles/README.md).
+// Here the two CTAs of a KV tile split the WORK instead:
+//   role V: dV (all 256 columns).  Needs only K resident (S^T) -> two Q/dO stages fit and the iteration pipelines like the
+//           hd-128 kernel: S^T(it+1) runs while the element-wise groups turn S^T(it) into P^T.  No dP^T, no dS^T, no dQ.
+//           2 matmul units per iteration.
+//   role K: dK (all 256 columns) and dQ (both 128-row halves of dQ^T).  K and V resident, one stage; dS^T feeds the dK MMA
+//           from shared memory (the tensor-memory columns the TS form would need hold the second dQ^T half).  4 units.
+// 6 units instead of 7, and a third of them in a pipelined CTA.  SPB_BWD256_ROLES=0 keeps the column split.
+template <int ROLE>
+struct Fb256Cfg {
+  static constexpr int HD = 256, CH = 4;
+  static constexpr int NS = (ROLE == 1) ? 2 : 1;
+  static constexpr int K_BYTES = 65536;
+  static constexpr int V_BYTES = (ROLE == 2) ? 65536 : 0;
+  static constexpr int Q_BYTES = 32768;                    // 64 rows x 256
+  static constexpr int OFF_K = 0;
+  static constexpr int OFF_V = OFF_K + K_BYTES;
+  static constexpr int OFF_Q = OFF_V + V_BYTES;
+  static constexpr int OFF_DO = OFF_Q + NS * Q_BYTES;
+  static constexpr int OFF_DST = OFF_DO + NS * Q_BYTES;    // role K: dS^T [128 kv][64 q] bf16, UMMA K-major, 128B swizzle
+  static constexpr int DST_BYTES = (ROLE == 2) ? 16384 : 0;
+  static constexpr int OFF_DQS = OFF_DST + DST_BYTES;      // role K: fp32 [32 q rows][128 hd] staging of a quarter dQ tile
+  static constexpr int DQS_BYTES = (ROLE == 2) ? 16384 : 0;
+  static constexpr int OFF_LSE = OFF_DQS + DQS_BYTES;      // [2][64] lse*log2e, [2][64] delta
+  static constexpr int OFF_BAR = OFF_LSE + 4 * 64 * 4;
+  static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
+  static constexpr int TM_ST = 0, TM_DPT = 64, TM_ACC = 128 /* dV or dK: 256 columns */, TM_DQT = 384 /* role K: 2 x 64 */, TM_P = 448 /* role V */;
+};
+
+template <int ROLE>
+__device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtensorMap& tmV, const CUtensorMap& tmQ, const CUtensorMap& tmDO,
+                                           const CUtensorMap& tmDQ, const FaBwdArgs& p, uint8_t* smem, const int g, const int rank, const int S) {
+  using Cfg = Fb256Cfg<ROLE>;
+  constexpr int HD = 256;
+  constexpr int NS = Cfg::NS;
+  uint8_t* sK = smem + Cfg::OFF_K;
+  uint8_t* sV = smem + Cfg::OFF_V;
+  uint8_t* sQ = smem + Cfg::OFF_Q;
+  uint8_t* sDO = smem + Cfg::OFF_DO;
+  uint8_t* sDST = smem + Cfg::OFF_DST;
+  float* sDQ = reinterpret_cast<float*>(smem + Cfg::OFF_DQS);
+  float* sLse = reinterpret_cast<float*>(smem + Cfg::OFF_LSE);
+  float* sDelta = sLse + 128;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
+  uint64_t* kv_full = bars;
+  uint64_t* qdo_full = bars + 1;          // [NS]
+  uint64_t* qdo_empty = bars + 1 + NS;    // [NS]
+  uint64_t* sdp_full = bars + 1 + 2 * NS;
+  uint64_t* sdp_empty = sdp_full + 1;
+  uint64_t* pds_full = sdp_full + 2;
+  uint64_t* pds_empty = sdp_full + 3;
+  uint64_t* dq_full = sdp_full + 4;
+  uint64_t* dq_empty = sdp_full + 5;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sdp_full + 6);
+
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+  const int nt = blockIdx.z, b = blockIdx.y;
+  const int kv0 = nt * 128;
+  const int n_rep = p.Hq / p.Hkv;
+  const int n_q64 = (p.T + 63) / 64;
+  const int i_start = p.causal ? (kv0 / 64) : 0;
+  const int n_i = n_q64 - i_start;
+  // S == 2: the two CTAs of a cluster share this role of this KV tile; rank r takes the iterations r, r+2, ... (local index j,
+  // global iteration rank + j*S) and the partial dV / dK of rank 1 is added into rank 0's through distributed shared memory
+  const int n_it = (n_rep * n_i - rank + S - 1) / S;
+  auto giter = [&](int j) { return rank + j * S; };
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmK);
+    prefetch_tmap(&tmQ);
+    prefetch_tmap(&tmDO);
+    if (ROLE == 2) {
+      prefetch_tmap(&tmV);
+      prefetch_tmap(&tmDQ);
+    }
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(kv_full, 1);
+      for (int i = 0; i < NS; ++i) {
+        mbar_init(&qdo_full[i], 1);
+        mbar_init(&qdo_empty[i], 1);
+      }
+      mbar_init(sdp_full, 1);
+      mbar_init(sdp_empty, 4 * FB_AGROUPS);
+      mbar_init(pds_full, 4 * FB_AGROUPS);
+      mbar_init(pds_empty, 1);
+      mbar_init(dq_full, 1);
+      mbar_init(dq_empty, 4);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      const int row_kv = b * p.T + kv0;
+      mbar_arrive_expect_tx(kv_full, (ROLE == 2 ? 2 : 1) * 4 * 16384);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        tma_load_2d(sK + c * 16384, &tmK, kv_full, g * HD + c * 64, row_kv);
+        if (ROLE == 2) tma_load_2d(sV + c * 16384, &tmV, kv_full, g * HD + c * 64, row_kv);
+      }
+      for (int it = 0; it < n_it; ++it) {
+        const int st = it % NS;
+        const uint32_t u = (it / NS) & 1;
+        const int h = g * n_rep + giter(it) / n_i;
+        const int row_q = b * p.T + (i_start + giter(it) % n_i) * 64;
+        mbar_wait(&qdo_empty[st], u ^ 1);
+        mbar_arrive_expect_tx(&qdo_full[st], 2 * Cfg::Q_BYTES);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          tma_load_2d(sQ + st * Cfg::Q_BYTES + c * 8192, &tmQ, &qdo_full[st], h * HD + c * 64, row_q);
+          tma_load_2d(sDO + st * Cfg::Q_BYTES + c * 8192, &tmDO, &qdo_full[st], h * HD + c * 64, row_q);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    const uint32_t idesc_s = umma_idesc_bf16(128, 64, 0, 0);
+    const uint32_t idesc_g = umma_idesc_bf16(128, 256, 0, 1);   // dV / dK: N = all 256 head columns, B MN-major (the Q / dO stage)
+    const uint32_t idesc_q = umma_idesc_bf16(128, 64, 1, 1);
+    const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV);
+    const uint64_t dK_k = umma_desc_kmajor(k_addr), dV_k = umma_desc_kmajor(v_addr);
+    const uint64_t dDST_k = umma_desc_kmajor(smem_u32(sDST));
+    const uint64_t dDST_mn = umma_desc_mnmajor(smem_u32(sDST), 128);
+    mbar_wait(kv_full, 0);
+    auto issue_s = [&](int it) {
+      const int st = it % NS;
+      mbar_wait(&qdo_full[st], (it / NS) & 1);
+      mbar_wait(sdp_empty, (it & 1) ^ 1);
+      tc_fence_after();
+      const uint64_t dQ_k = umma_desc_kmajor(smem_u32(sQ + st * Cfg::Q_BYTES)), dDO_k = umma_desc_kmajor(smem_u32(sDO + st * Cfg::Q_BYTES));
+#pragma unroll
+      for (int kk = 0; kk < HD / 16; ++kk) {
+        const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
+        umma_bf16_w(tmem_base + Cfg::TM_ST, dK_k + (aoff >> 4), dQ_k + (boff >> 4), idesc_s, kk > 0 ? 1u : 0u);
+      }
+      if (ROLE == 2) {
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
+          umma_bf16_w(tmem_base + Cfg::TM_DPT, dV_k + (aoff >> 4), dDO_k + (boff >> 4), idesc_s, kk > 0 ? 1u : 0u);
+        }
+      }
+      umma_commit_w(sdp_full);
+    };
+    auto issue_g = [&](int it) {
+      const int st = it % NS;
+      mbar_wait(pds_full, it & 1);
+      if (ROLE == 2) mbar_wait(dq_empty, (it & 1) ^ 1);
+      tc_fence_after();
+      if (ROLE == 1) {
+        const uint64_t dDO_mn = umma_desc_mnmajor(smem_u32(sDO + st * Cfg::Q_BYTES), 64);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)  // dV += P^T dO, P^T from tensor memory
+          umma_bf16_ts_w(tmem_base + Cfg::TM_ACC, tmem_base + Cfg::TM_P + kk * 8, dDO_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
+        umma_commit_w(&qdo_empty[st]);
+        umma_commit_w(pds_empty);
+      } else {
+        const uint64_t dQ_mn = umma_desc_mnmajor(smem_u32(sQ + st * Cfg::Q_BYTES), 64);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)  // dK += dS^T Q, dS^T from shared memory (K-major, 16 q columns = 32 B per k-step)
+          umma_bf16_w(tmem_base + Cfg::TM_ACC, dDST_k + ((kk * 32) >> 4), dQ_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {  // dQ^T = K^T dS, head dims hh*128 .. hh*128+127 as the M rows
+          const uint64_t dK_mn = umma_desc_mnmajor(k_addr + hh * 2 * 16384, 128);
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk)
+            umma_bf16_w(tmem_base + Cfg::TM_DQT + hh * 64, dK_mn + ((kk * 2048) >> 4), dDST_mn + ((kk * 2048) >> 4), idesc_q, kk > 0 ? 1u : 0u);
+        }
+        umma_commit_w(&qdo_empty[st]);
+        umma_commit_w(pds_empty);
+        umma_commit_w(dq_full);
+      }
+    };
+    if (n_it > 0) issue_s(0);
+    for (int it = 0; it < n_it; ++it) {
+      if (NS >= 2) {
+        if (it + 1 < n_it) issue_s(it + 1);
+        issue_g(it);
+      } else {
+        issue_g(it);
+        if (it + 1 < n_it) issue_s(it + 1);
+      }
+    }
+    __syncwarp();
+  } else if (warp < 2 + 4 * FB_AGROUPS) {
+    // ------------------------------------------------------------------ element-wise groups
+    const int wg = (warp - 2) >> 2;
+    const int qd = warp & 3;
+    const int r = qd * 32 + lane;
+    const int ct = threadIdx.x - 64;
+    const int kv_idx = kv0 + r;
+    const int cbase = wg * FB_ACOLS;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
+    auto fetch_stat = [&](int it) -> float {
+      if (ct >= (ROLE == 2 ? 128 : 64) || it >= n_it) return 0.f;
+      const int h = g * n_rep + giter(it) / n_i;
+      const int qi = (i_start + giter(it) % n_i) * 64 + (ct & 63);
+      if (qi >= p.T) return 0.f;
+      return ((ct < 64) ? p.lse : p.delta)[((int64_t)b * p.Hq + h) * p.T + qi];
+    };
+    auto put_stat = [&](int it, float v) {
+      if (ct < 64) sLse[(it & 1) * 64 + ct] = v * FB_LOG2E;
+      else if (ct < 128) sDelta[(it & 1) * 64 + (ct - 64)] = v;
+    };
+    put_stat(0, fetch_stat(0));
+    const float2 sc2 = make_float2(p.scale_log2, p.scale_log2);
+    const float2 scale2 = make_float2(p.scale, p.scale);
+    for (int it = 0; it < n_it; ++it) {
+      const int st = it & 1;
+      const int q0 = (i_start + giter(it) % n_i) * 64;
+      const float stat_next = fetch_stat(it + 1);
+      asm volatile("bar.sync 1, %0;" ::"n"(FB_ATHREADS) : "memory");
+      mbar_wait(sdp_full, it & 1);
+      tc_fence_after();
+      uint32_t rs[FB_ACOLS], rd[FB_ACOLS];
+      SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_ST + cbase), rs);
+      if (ROLE == 2) SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_DPT + cbase), rd);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(sdp_empty);
+
+      const bool need_mask = (p.causal && q0 < kv0 + 128) || (q0 + 64 > p.T) || (kv0 + 128 > p.T);
+      const float2* lse2 = reinterpret_cast<const float2*>(sLse + st * 64 + cbase);
+      const float2* del2 = reinterpret_cast<const float2*>(sDelta + st * 64 + cbase);
+      uint32_t pk[FB_ACOLS / 2];  // role V: P^T; role K: dS^T
+      auto elementwise = [&](auto masked) {
+        constexpr bool MASKED = decltype(masked)::value;
+#pragma unroll
+        for (int i = 0; i < FB_ACOLS; i += 2) {
+          const float2 l2 = lse2[i >> 1];
+          const float2 x = __ffma2_rn(make_float2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, make_float2(-l2.x, -l2.y));
+          float2 pv = make_float2(fb_exp2(x.x), fb_exp2(x.y));
+          if (MASKED) {
+            const int qi = q0 + cbase + i;
+            const bool kv_dead = kv_idx >= p.T;
+            if (kv_dead || qi >= p.T || (p.causal && kv_idx > qi)) pv.x = 0.f;
+            if (kv_dead || qi + 1 >= p.T || (p.causal && kv_idx > qi + 1)) pv.y = 0.f;
+          }
+          if (ROLE == 1) {
+            pk[i >> 1] = pack_bf16(pv.x, pv.y);
+          } else {
+            const float2 d2 = del2[i >> 1];
+            const float2 dd = __fadd2_rn(make_float2(__uint_as_float(rd[i]), __uint_as_float(rd[i + 1])), make_float2(-d2.x, -d2.y));
+            const float2 ds = __fmul2_rn(__fmul2_rn(pv, dd), scale2);
+            pk[i >> 1] = pack_bf16(ds.x, ds.y);
+          }
+        }
+      };
+      if (need_mask) elementwise(std::true_type{});
+      else elementwise(std::false_type{});
+      put_stat(it + 1, stat_next);
+      mbar_wait(pds_empty, (it & 1) ^ 1);  // the MMA group of iteration it-1 has finished reading P^T / dS^T
+      if (ROLE == 1) {
+        SPB_TMEM_ST_16(lane_base + (uint32_t)(Cfg::TM_P + cbase / 2), pk);
+        tmem_st_wait();
+      } else {
+        uint8_t* drow = sDST + r * 128;
+#pragma unroll
+        for (int c = 0; c < FB_ACOLS / 8; ++c) {
+          const int slot = ((wg * (FB_ACOLS / 8) + c) ^ (r & 7)) << 4;
+          *reinterpret_cast<uint4*>(drow + slot) = make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
+        }
+        fence_proxy_async_smem();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pds_full);
+    }
+    if (n_it > 0) {
+      mbar_wait(pds_empty, (n_it - 1) & 1);  // the last commit covers every MMA issued before it
+      tc_fence_after();
+    }
+  } else if (ROLE == 2) {
+    // ------------------------------------------------------------------ drain group (role K): reduce both halves of dQ^T every iteration
+    const int qd = warp & 3;
+    const int r = qd * 32 + lane;  // head dim inside the half = TMEM lane of dQ^T
+    const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
+    const bool leader = (qd == 0 && lane == 0);
+    for (int it = 0; it < n_it; ++it) {
+      const int h = g * n_rep + giter(it) / n_i;
+      const int q0 = (i_start + giter(it) % n_i) * 64;
+      mbar_wait(dq_full, it & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int hh = 0; hh < 2; ++hh) {
+        float dq[64];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t raw[32];
+          SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_DQT + hh * 64 + c * 32), raw);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) dq[c * 32 + i] = __uint_as_float(raw[i]);
+        }
+        if (hh == 1) {  // both halves are in registers / on their way: the next iteration may overwrite dQ^T
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(dq_empty);
+        }
+#pragma unroll
+        for (int rd = 0; rd < 2; ++rd) {  // 32 query rows at a time through the 16 KB staging tile
+          if (leader && (it > 0 || hh > 0 || rd > 0)) tma_store_wait_read<0>();
+          asm volatile("bar.sync 2, 128;" ::: "memory");
+#pragma unroll
+          for (int i = 0; i < 32; ++i) sDQ[i * 128 + r] = dq[rd * 32 + i];
+          fence_proxy_async_smem();
+          asm volatile("bar.sync 2, 128;" ::: "memory");
+          if (leader) {
+            tma_reduce_add_2d(&tmDQ, sDQ, h * HD + hh * 128, b * p.T + q0 + rd * 32);
+            tma_store_commit();
+          }
+        }
+      }
+    }
+    if (leader) tma_store_wait_read<0>();
+  }
+
+  // ---- epilogue: the role's accumulator (dV or dK); element-wise group wg owns head columns wg*128 .. wg*128+127 of kv row r.
+  // S == 2: rank 1 ships its partial sums into rank 0's shared memory (the K | V / K | stage region, 128 KB, free by now:
+  // float4 j of row r at (j * 128 + r) * 16 B, so a warp's accesses are consecutive on both sides), rank 0 adds and stores.
+  const bool ew = warp >= 2 && warp < 2 + 4 * FB_AGROUPS;
+  const int wg = (warp - 2) >> 2, qd = warp & 3;
+  const int r = qd * 32 + lane;
+  const int kv_idx = kv0 + r;
+  const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
+  if (S == 2) {
+    cluster_sync_all();  // every MMA of both CTAs has completed (the element-wise warps arrive after their last pds_empty wait)
+    if (rank == 1 && ew) {
+      tc_fence_after();
+      uint32_t remote;
+      asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(remote) : "r"(smem_u32(smem)));
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t o[32];
+        if (n_it > 0) {
+          SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_ACC + wg * 128 + c * 32), o);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[i] = 0u;
+        }
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          const uint32_t j = (uint32_t)(wg * 32 + c * 8 + (i >> 2));
+          asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(remote + (j * 128u + (uint32_t)r) * 16u), "r"(o[i]), "r"(o[i + 1]),
+                       "r"(o[i + 2]), "r"(o[i + 3])
+                       : "memory");
+        }
+      }
+    }
+    cluster_sync_all();  // release / acquire: rank 1's stores are visible to rank 0
+  }
+  if (ew && rank == 0) {
+    tc_fence_after();
+    const bool valid = kv_idx < p.T;
+    __nv_bfloat16* orow = (ROLE == 2 ? p.dk + ((int64_t)b * p.T + kv_idx) * p.lddk : p.dv + ((int64_t)b * p.T + kv_idx) * p.lddv) + (int64_t)g * HD + wg * 128;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      uint32_t o[32];
+      SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_ACC + wg * 128 + c * 32), o);
+      tmem_ld_wait();
+      if (S == 2) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          const int j = wg * 32 + c * 8 + (i >> 2);
+          const float4 add = *reinterpret_cast<const float4*>(smem + ((size_t)j * 128 + r) * 16);
+          o[i] = __float_as_uint(__uint_as_float(o[i]) + add.x);
+          o[i + 1] = __float_as_uint(__uint_as_float(o[i + 1]) + add.y);
+          o[i + 2] = __float_as_uint(__uint_as_float(o[i + 2]) + add.z);
+          o[i + 3] = __float_as_uint(__uint_as_float(o[i + 3]) + add.w);
+        }
+      }
+      if (valid) {
+        if (ROLE == 2 && p.rope != nullptr) {  // dK: transpose of the 2x2 rotary block, table row = position kv_idx
+          const float4* tab = p.rope + (int64_t)kv_idx * (HD / 2) + wg * 64 + c * 16;
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            const float4 m = tab[i >> 1];
+            const float xe = __uint_as_float(o[i]), xo = __uint_as_float(o[i + 1]);
+            o[i] = __float_as_uint(m.x * xe + m.z * xo);
+            o[i + 1] = __float_as_uint(m.y * xe + m.w * xo);
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 32; i += 8) {
+          uint4 v;
+          v.x = pack_bf16(__uint_as_float(o[i]), __uint_as_float(o[i + 1]));
+          v.y = pack_bf16(__uint_as_float(o[i + 2]), __uint_as_float(o[i + 3]));
+          v.z = pack_bf16(__uint_as_float(o[i + 4]), __uint_as_float(o[i + 5]));
+          v.w = pack_bf16(__uint_as_float(o[i + 6]), __uint_as_float(o[i + 7]));
+          *reinterpret_cast<uint4*>(orow + c * 32 + i) = v;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+__global__ void __launch_bounds__(FB_THREADS, 1)
+    flash_bwd256_roles_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
+                              const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmDO,
+                              const __grid_constant__ CUtensorMap tmDQ, const FaBwdArgs p, const int S) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  // blockIdx.x = (kv head * 2 + role bit) * S + rank; role K first: it is the longer of the two
+  const int rank = S == 2 ? (int)(blockIdx.x & 1) : 0;
+  const int rg = S == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  if ((rg & 1) == 0) fb256_body<2>(tmK, tmV, tmQ, tmDO, tmDQ, p, smem, rg >> 1, rank, S);
+  else fb256_body<1>(tmK, tmV, tmQ, tmDO, tmDQ, p, smem, rg >> 1, rank, S);
+}
+
 bool flash_bwd_tc_supported(int dtype, int hd) { return dtype == SPB_BF16 && (hd == 64 || hd == 128 || hd == 256); }
 
 template <int HD>
@@ -628,9 +1059,33 @@ static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
     a.ablate = ab ? atoi(ab) : 0;
   }
 #endif
-  SPB_CUDA(cudaFuncSetAttribute(flash_bwd_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
   dim3 grid(Hkv * Cfg::HS, B, (Tn + 127) / 128);
-  flash_bwd_tc_kernel<HD><<<grid, FB_THREADS, Cfg::SMEM_BYTES, st>>>(tmK, tmV, tmQ, tmDO, tmDQ, a);
+  static const bool roles_off = [] { const char* e = getenv("SPB_BWD256_ROLES"); return e && e[0] == '0'; }();
+  if (HD == 256 && !roles_off) {  // two roles per KV tile (dV | dK + dQ) instead of two column halves; same dQ staging box
+    constexpr int SM = Fb256Cfg<2>::SMEM_BYTES > Fb256Cfg<1>::SMEM_BYTES ? Fb256Cfg<2>::SMEM_BYTES : Fb256Cfg<1>::SMEM_BYTES;
+    SPB_CUDA(cudaFuncSetAttribute(flash_bwd256_roles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SM));
+    // few KV tiles (one CTA per role and tile would leave the machine to the heaviest role-K CTA): each role of a tile is a
+    // cluster of two CTAs that take alternate iterations and merge their partial dV / dK through distributed shared memory
+    static const int force_split = [] { const char* e = getenv("SPB_BWD256_SPLIT"); return e ? atoi(e) : 0; }();
+    const int64_t role_ctas = (int64_t)grid.x * grid.y * grid.z;
+    const int S = force_split ? (force_split == 2 ? 2 : 1) : (role_ctas < 4 * (int64_t)sm_count() ? 2 : 1);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid.x * S, grid.y, grid.z);
+    cfg.blockDim = dim3(FB_THREADS);
+    cfg.dynamicSmemBytes = SM;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = S;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    SPB_CUDA(cudaLaunchKernelEx(&cfg, flash_bwd256_roles_kernel, tmK, tmV, tmQ, tmDO, tmDQ, a, S));
+  } else {
+    SPB_CUDA(cudaFuncSetAttribute(flash_bwd_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    flash_bwd_tc_kernel<HD><<<grid, FB_THREADS, Cfg::SMEM_BYTES, st>>>(tmK, tmV, tmQ, tmDO, tmDQ, a);
+  }
   SPB_LAUNCH_CHECK();
   {
     constexpr int HPT = 4;
