@@ -645,8 +645,8 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
   const int n_q64 = (p.T + 63) / 64;
   const int i_start = p.causal ? (kv0 / 64) : 0;
   const int n_i = n_q64 - i_start;
-  // S == 2: the two CTAs of a cluster share this role of this KV tile; rank r takes the iterations r, r+2, ... (local index j,
-  // global iteration rank + j*S) and the partial dV / dK of rank 1 is added into rank 0's through distributed shared memory
+  // S > 1: the S CTAs of a cluster share this role of this KV tile; rank r takes the iterations r, r+S, ... (local index j,
+  // global iteration rank + j*S) and the partial dV / dK of ranks 1.. are added into rank 0's through distributed shared memory
   const int n_it = (n_rep * n_i - rank + S - 1) / S;
   auto giter = [&](int j) { return rank + j * S; };
 
@@ -913,16 +913,18 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
   }
 
   // ---- epilogue: the role's accumulator (dV or dK); element-wise group wg owns head columns wg*128 .. wg*128+127 of kv row r.
-  // S == 2: rank 1 ships its partial sums into rank 0's shared memory (the K | V / K | stage region, 128 KB, free by now:
-  // float4 j of row r at (j * 128 + r) * 16 B, so a warp's accesses are consecutive on both sides), rank 0 adds and stores.
+  // The exchange buffer is rank 0's K | V (role V: K | first stage) region, 128 KB, free by now: float4 j of row r at
+  // (j * 128 + r) * 16 B, so a warp's accesses are consecutive on both sides.
   const bool ew = warp >= 2 && warp < 2 + 4 * FB_AGROUPS;
   const int wg = (warp - 2) >> 2, qd = warp & 3;
   const int r = qd * 32 + lane;
   const int kv_idx = kv0 + r;
   const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
-  if (S == 2) {
-    cluster_sync_all();  // every MMA of both CTAs has completed (the element-wise warps arrive after their last pds_empty wait)
-    if (rank == 1 && ew) {
+  // S > 1: ranks 1 .. S-1 ship their partial sums, one rank per round, into rank 0's shared memory; rank 0 adds each round into
+  // its tensor-memory accumulator.  The barrier at the top of a round also says that rank 0 is done reading the previous one.
+  for (int src = 1; src < S; ++src) {
+    cluster_sync_all();  // round 1: every MMA of every CTA has completed (the element-wise warps arrive after their last pds_empty wait)
+    if (rank == src && ew) {
       tc_fence_after();
       uint32_t remote;
       asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(remote) : "r"(smem_u32(smem)));
@@ -945,7 +947,29 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
         }
       }
     }
-    cluster_sync_all();  // release / acquire: rank 1's stores are visible to rank 0
+    cluster_sync_all();  // release / acquire: the stores are visible to rank 0
+    if (rank == 0 && ew) {
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t o[32];
+        SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_ACC + wg * 128 + c * 32), o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          const int j = wg * 32 + c * 8 + (i >> 2);
+          const float4 add = *reinterpret_cast<const float4*>(smem + ((size_t)j * 128 + r) * 16);
+          o[i] = __float_as_uint(__uint_as_float(o[i]) + add.x);
+          o[i + 1] = __float_as_uint(__uint_as_float(o[i + 1]) + add.y);
+          o[i + 2] = __float_as_uint(__uint_as_float(o[i + 2]) + add.z);
+          o[i + 3] = __float_as_uint(__uint_as_float(o[i + 3]) + add.w);
+        }
+        SPB_TMEM_ST_16(lane_base + (uint32_t)(Cfg::TM_ACC + wg * 128 + c * 32), o);
+        SPB_TMEM_ST_16(lane_base + (uint32_t)(Cfg::TM_ACC + wg * 128 + c * 32 + 16), (o + 16));
+      }
+      tmem_st_wait();
+      tc_fence_before();
+    }
   }
   if (ew && rank == 0) {
     tc_fence_after();
@@ -956,17 +980,6 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
       uint32_t o[32];
       SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_ACC + wg * 128 + c * 32), o);
       tmem_ld_wait();
-      if (S == 2) {
-#pragma unroll
-        for (int i = 0; i < 32; i += 4) {
-          const int j = wg * 32 + c * 8 + (i >> 2);
-          const float4 add = *reinterpret_cast<const float4*>(smem + ((size_t)j * 128 + r) * 16);
-          o[i] = __float_as_uint(__uint_as_float(o[i]) + add.x);
-          o[i + 1] = __float_as_uint(__uint_as_float(o[i + 1]) + add.y);
-          o[i + 2] = __float_as_uint(__uint_as_float(o[i + 2]) + add.z);
-          o[i + 3] = __float_as_uint(__uint_as_float(o[i + 3]) + add.w);
-        }
-      }
       if (valid) {
         if (ROLE == 2 && p.rope != nullptr) {  // dK: transpose of the 2x2 rotary block, table row = position kv_idx
           const float4* tab = p.rope + (int64_t)kv_idx * (HD / 2) + wg * 64 + c * 16;
@@ -1003,8 +1016,8 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   // blockIdx.x = (kv head * 2 + role bit) * S + rank; role K first: it is the longer of the two
-  const int rank = S == 2 ? (int)(blockIdx.x & 1) : 0;
-  const int rg = S == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int rank = (int)(blockIdx.x % (unsigned)S);
+  const int rg = (int)(blockIdx.x / (unsigned)S);
   if ((rg & 1) == 0) fb256_body<2>(tmK, tmV, tmQ, tmDO, tmDQ, p, smem, rg >> 1, rank, S);
   else fb256_body<1>(tmK, tmV, tmQ, tmDO, tmDQ, p, smem, rg >> 1, rank, S);
 }
@@ -1065,10 +1078,11 @@ static int flash_bwd_tc_launch(int B, int Tn, int Hq, int Hkv, int causal, float
     constexpr int SM = Fb256Cfg<2>::SMEM_BYTES > Fb256Cfg<1>::SMEM_BYTES ? Fb256Cfg<2>::SMEM_BYTES : Fb256Cfg<1>::SMEM_BYTES;
     SPB_CUDA(cudaFuncSetAttribute(flash_bwd256_roles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SM));
     // few KV tiles (one CTA per role and tile would leave the machine to the heaviest role-K CTA): each role of a tile is a
-    // cluster of two CTAs that take alternate iterations and merge their partial dV / dK through distributed shared memory
+    // cluster of two or four CTAs that take alternate iterations and merge their partial dV / dK through distributed shared memory
     static const int force_split = [] { const char* e = getenv("SPB_BWD256_SPLIT"); return e ? atoi(e) : 0; }();
     const int64_t role_ctas = (int64_t)grid.x * grid.y * grid.z;
-    const int S = force_split ? (force_split == 2 ? 2 : 1) : (role_ctas < 4 * (int64_t)sm_count() ? 2 : 1);
+    const int S = force_split ? (force_split == 4 ? 4 : (force_split == 2 ? 2 : 1))
+                              : (role_ctas < 4 * (int64_t)sm_count() ? 2 : 1);  // clusters of four measured slower (C4: 1.59 vs 1.33 ms)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid.x * S, grid.y, grid.z);
     cfg.blockDim = dim3(FB_THREADS);

@@ -4,9 +4,9 @@ mkdir -p gpurun_out
 K="256 or gemma or c4 or C4 or timed or flash or gpt"
 timeout 600 python -m pytest tests -q -x -m gpu -k "$K" -p no:cacheprovider 2>&1 | tail -2
 SPB_BWD256_SPLIT=2 timeout 600 python -m pytest tests -q -x -m gpu -k "$K" -p no:cacheprovider 2>&1 | tail -2
-SPB_BWD256_SPLIT=1 timeout 600 python -m pytest tests -q -x -m gpu -k "$K" -p no:cacheprovider 2>&1 | tail -2
+SPB_BWD256_SPLIT=4 timeout 600 python -m pytest tests -q -x -m gpu -k "$K" -p no:cacheprovider 2>&1 | tail -2
 for wl in c4 c2; do
-  for sp in 0 1 2; do
+  for sp in 0 2 4; do
     SPB_BWD256_SPLIT=$sp timeout 300 python bench.py --workload $wl --steps 20 --warmup 5 --no-e2e --sustain-s 0 --no-cpu-baseline --graph off > gpurun_out/r02ab_${wl}_s$sp.json 2>> gpurun_out/r02ab.err
   done
   SPB_BWD256_ROLES=0 timeout 300 python bench.py --workload $wl --steps 20 --warmup 5 --no-e2e --sustain-s 0 --no-cpu-baseline --graph off > gpurun_out/r02ab_${wl}_cols.json 2>> gpurun_out/r02ab.err
@@ -14,7 +14,7 @@ done
 python - <<'PY'
 import json
 for wl in ("c4","c2"):
-  for f in ("s0","s1","s2","cols"):
+  for f in ("s0","s2","s4","cols"):
     try:
         d=json.loads(open(f"gpurun_out/r02ab_{wl}_{f}.json").read().strip().splitlines()[-1])
         print(wl, f, round(d["ms_per_step"],4), "flash_bwd", d["stages_ms"].get("flash_bwd"))
