@@ -626,16 +626,22 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
   float* sLse = reinterpret_cast<float*>(smem + Cfg::OFF_LSE);
   float* sDelta = sLse + 128;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
+  // role V: q_full / q_empty cover a whole stage (Q_i and dO_i).  Role K has one stage and runs as a serial chain, so its two
+  // halves are tracked apart: dO_i is free as soon as dP^T is done (reloaded under the element-wise phase), Q_i as soon as the
+  // dK MMAs are done (reloaded under the dQ^T MMAs), and the element-wise groups start on S^T while dP^T is still running.
   uint64_t* kv_full = bars;
-  uint64_t* qdo_full = bars + 1;          // [NS]
-  uint64_t* qdo_empty = bars + 1 + NS;    // [NS]
-  uint64_t* sdp_full = bars + 1 + 2 * NS;
-  uint64_t* sdp_empty = sdp_full + 1;
-  uint64_t* pds_full = sdp_full + 2;
-  uint64_t* pds_empty = sdp_full + 3;
-  uint64_t* dq_full = sdp_full + 4;
-  uint64_t* dq_empty = sdp_full + 5;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sdp_full + 6);
+  uint64_t* q_full = bars + 1;            // [NS]
+  uint64_t* q_empty = bars + 1 + NS;      // [NS]
+  uint64_t* do_full = bars + 1 + 2 * NS;  // role K
+  uint64_t* do_empty = do_full + 1;       // role K
+  uint64_t* s_full = do_full + 2;         // S^T complete
+  uint64_t* dp_full = do_full + 3;        // role K: dP^T complete
+  uint64_t* sdp_empty = do_full + 4;
+  uint64_t* pds_full = do_full + 5;
+  uint64_t* pds_empty = do_full + 6;
+  uint64_t* dq_full = do_full + 7;
+  uint64_t* dq_empty = do_full + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(do_full + 9);
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -663,10 +669,13 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
     if (lane == 0) {
       mbar_init(kv_full, 1);
       for (int i = 0; i < NS; ++i) {
-        mbar_init(&qdo_full[i], 1);
-        mbar_init(&qdo_empty[i], 1);
+        mbar_init(&q_full[i], 1);
+        mbar_init(&q_empty[i], 1);
       }
-      mbar_init(sdp_full, 1);
+      mbar_init(do_full, 1);
+      mbar_init(do_empty, 1);
+      mbar_init(s_full, 1);
+      mbar_init(dp_full, 1);
       mbar_init(sdp_empty, 4 * FB_AGROUPS);
       mbar_init(pds_full, 4 * FB_AGROUPS);
       mbar_init(pds_empty, 1);
@@ -698,12 +707,23 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
         const uint32_t u = (it / NS) & 1;
         const int h = g * n_rep + giter(it) / n_i;
         const int row_q = b * p.T + (i_start + giter(it) % n_i) * 64;
-        mbar_wait(&qdo_empty[st], u ^ 1);
-        mbar_arrive_expect_tx(&qdo_full[st], 2 * Cfg::Q_BYTES);
+        if (ROLE == 1) {
+          mbar_wait(&q_empty[st], u ^ 1);
+          mbar_arrive_expect_tx(&q_full[st], 2 * Cfg::Q_BYTES);
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          tma_load_2d(sQ + st * Cfg::Q_BYTES + c * 8192, &tmQ, &qdo_full[st], h * HD + c * 64, row_q);
-          tma_load_2d(sDO + st * Cfg::Q_BYTES + c * 8192, &tmDO, &qdo_full[st], h * HD + c * 64, row_q);
+          for (int c = 0; c < 4; ++c) {
+            tma_load_2d(sQ + st * Cfg::Q_BYTES + c * 8192, &tmQ, &q_full[st], h * HD + c * 64, row_q);
+            tma_load_2d(sDO + st * Cfg::Q_BYTES + c * 8192, &tmDO, &q_full[st], h * HD + c * 64, row_q);
+          }
+        } else {
+          mbar_wait(do_empty, (it & 1) ^ 1);  // released first (after dP^T of the previous iteration)
+          mbar_arrive_expect_tx(do_full, Cfg::Q_BYTES);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) tma_load_2d(sDO + c * 8192, &tmDO, do_full, h * HD + c * 64, row_q);
+          mbar_wait(&q_empty[0], (it & 1) ^ 1);  // released after the dK MMAs of the previous iteration
+          mbar_arrive_expect_tx(&q_full[0], Cfg::Q_BYTES);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) tma_load_2d(sQ + c * 8192, &tmQ, &q_full[0], h * HD + c * 64, row_q);
         }
       }
     }
@@ -720,7 +740,7 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
     mbar_wait(kv_full, 0);
     auto issue_s = [&](int it) {
       const int st = it % NS;
-      mbar_wait(&qdo_full[st], (it / NS) & 1);
+      mbar_wait(&q_full[st], (it / NS) & 1);
       mbar_wait(sdp_empty, (it & 1) ^ 1);
       tc_fence_after();
       const uint64_t dQ_k = umma_desc_kmajor(smem_u32(sQ + st * Cfg::Q_BYTES)), dDO_k = umma_desc_kmajor(smem_u32(sDO + st * Cfg::Q_BYTES));
@@ -729,14 +749,18 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
         const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
         umma_bf16_w(tmem_base + Cfg::TM_ST, dK_k + (aoff >> 4), dQ_k + (boff >> 4), idesc_s, kk > 0 ? 1u : 0u);
       }
+      umma_commit_w(s_full);
       if (ROLE == 2) {
+        mbar_wait(do_full, it & 1);
+        tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
           const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
           umma_bf16_w(tmem_base + Cfg::TM_DPT, dV_k + (aoff >> 4), dDO_k + (boff >> 4), idesc_s, kk > 0 ? 1u : 0u);
         }
+        umma_commit_w(dp_full);
+        umma_commit_w(do_empty);  // nothing else in this role reads dO_i
       }
-      umma_commit_w(sdp_full);
     };
     auto issue_g = [&](int it) {
       const int st = it % NS;
@@ -748,13 +772,14 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dV += P^T dO, P^T from tensor memory
           umma_bf16_ts_w(tmem_base + Cfg::TM_ACC, tmem_base + Cfg::TM_P + kk * 8, dDO_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
-        umma_commit_w(&qdo_empty[st]);
+        umma_commit_w(&q_empty[st]);
         umma_commit_w(pds_empty);
       } else {
         const uint64_t dQ_mn = umma_desc_mnmajor(smem_u32(sQ + st * Cfg::Q_BYTES), 64);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dK += dS^T Q, dS^T from shared memory (K-major, 16 q columns = 32 B per k-step)
           umma_bf16_w(tmem_base + Cfg::TM_ACC, dDST_k + ((kk * 32) >> 4), dQ_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
+        umma_commit_w(&q_empty[0]);  // Q_i is free: its reload runs under the dQ^T MMAs
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {  // dQ^T = K^T dS, head dims hh*128 .. hh*128+127 as the M rows
           const uint64_t dK_mn = umma_desc_mnmajor(k_addr + hh * 2 * 16384, 128);
@@ -762,7 +787,6 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
           for (int kk = 0; kk < 8; ++kk)
             umma_bf16_w(tmem_base + Cfg::TM_DQT + hh * 64, dK_mn + ((kk * 2048) >> 4), dDST_mn + ((kk * 2048) >> 4), idesc_q, kk > 0 ? 1u : 0u);
         }
-        umma_commit_w(&qdo_empty[st]);
         umma_commit_w(pds_empty);
         umma_commit_w(dq_full);
       }
@@ -806,21 +830,23 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
       const int q0 = (i_start + giter(it) % n_i) * 64;
       const float stat_next = fetch_stat(it + 1);
       asm volatile("bar.sync 1, %0;" ::"n"(FB_ATHREADS) : "memory");
-      mbar_wait(sdp_full, it & 1);
+      mbar_wait(s_full, it & 1);
       tc_fence_after();
       uint32_t rs[FB_ACOLS], rd[FB_ACOLS];
       SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_ST + cbase), rs);
-      if (ROLE == 2) SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_DPT + cbase), rd);
       tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(sdp_empty);
+      if (ROLE == 1) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(sdp_empty);
+      }
 
       const bool need_mask = (p.causal && q0 < kv0 + 128) || (q0 + 64 > p.T) || (kv0 + 128 > p.T);
       const float2* lse2 = reinterpret_cast<const float2*>(sLse + st * 64 + cbase);
       const float2* del2 = reinterpret_cast<const float2*>(sDelta + st * 64 + cbase);
       uint32_t pk[FB_ACOLS / 2];  // role V: P^T; role K: dS^T
-      auto elementwise = [&](auto masked) {
+      float2 pvv[FB_ACOLS / 2];   // role K: P^T in fp32 until dP^T has arrived
+      auto probs = [&](auto masked) {
         constexpr bool MASKED = decltype(masked)::value;
 #pragma unroll
         for (int i = 0; i < FB_ACOLS; i += 2) {
@@ -833,18 +859,28 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
             if (kv_dead || qi >= p.T || (p.causal && kv_idx > qi)) pv.x = 0.f;
             if (kv_dead || qi + 1 >= p.T || (p.causal && kv_idx > qi + 1)) pv.y = 0.f;
           }
-          if (ROLE == 1) {
-            pk[i >> 1] = pack_bf16(pv.x, pv.y);
-          } else {
-            const float2 d2 = del2[i >> 1];
-            const float2 dd = __fadd2_rn(make_float2(__uint_as_float(rd[i]), __uint_as_float(rd[i + 1])), make_float2(-d2.x, -d2.y));
-            const float2 ds = __fmul2_rn(__fmul2_rn(pv, dd), scale2);
-            pk[i >> 1] = pack_bf16(ds.x, ds.y);
-          }
+          if (ROLE == 1) pk[i >> 1] = pack_bf16(pv.x, pv.y);
+          else pvv[i >> 1] = pv;
         }
       };
-      if (need_mask) elementwise(std::true_type{});
-      else elementwise(std::false_type{});
+      if (need_mask) probs(std::true_type{});
+      else probs(std::false_type{});
+      if (ROLE == 2) {  // the exps above ran while the tensor pipe was still on dP^T
+        mbar_wait(dp_full, it & 1);
+        tc_fence_after();
+        SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_DPT + cbase), rd);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(sdp_empty);
+#pragma unroll
+        for (int i = 0; i < FB_ACOLS; i += 2) {
+          const float2 d2 = del2[i >> 1];
+          const float2 dd = __fadd2_rn(make_float2(__uint_as_float(rd[i]), __uint_as_float(rd[i + 1])), make_float2(-d2.x, -d2.y));
+          const float2 ds = __fmul2_rn(__fmul2_rn(pvv[i >> 1], dd), scale2);
+          pk[i >> 1] = pack_bf16(ds.x, ds.y);
+        }
+      }
       put_stat(it + 1, stat_next);
       mbar_wait(pds_empty, (it & 1) ^ 1);  // the MMA group of iteration it-1 has finished reading P^T / dS^T
       if (ROLE == 1) {
