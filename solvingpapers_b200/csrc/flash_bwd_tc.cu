@@ -152,7 +152,8 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
   uint64_t* pds_empty = sdp_full + 3;
   uint64_t* dq_full = sdp_full + 4;
   uint64_t* dq_empty = sdp_full + 5;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sdp_full + 6);
+  uint64_t* dp_full = sdp_full + 6;       // dP^T complete (sdp_full: S^T complete - the exps start while dP^T is still running)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sdp_full + 7);
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -180,6 +181,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
         mbar_init(&qdo_empty[i], 1);
       }
       mbar_init(sdp_full, 1);
+      mbar_init(dp_full, 1);
       mbar_init(sdp_empty, 4 * FB_AGROUPS);
       mbar_init(pds_full, 4 * FB_AGROUPS);
       mbar_init(pds_empty, 1);
@@ -256,13 +258,14 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
           const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
           umma_bf16_w(tmem_base + Cfg::TM_ST, dK_k + (aoff >> 4), dQ_k + (boff >> 4), idesc_s, kk > 0 ? 1u : 0u);
         }
+        umma_commit_w(sdp_full);
         if (!FB_ABL(16))
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
           const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
           umma_bf16_w(tmem_base + Cfg::TM_DPT, dV_k + (aoff >> 4), dDO_k + (boff >> 4), idesc_s, kk > 0 ? 1u : 0u);
         }
-        umma_commit_w(sdp_full);
+        umma_commit_w(dp_full);
         FB_TRACE(12);
       };
       auto issue_g = [&](int it) {
@@ -342,28 +345,24 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
       uint32_t rs[FB_ACOLS], rd[FB_ACOLS];
       if (FB_ACOLS == 32) {
         SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_ST + cbase), rs);
-        SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_DPT + cbase), rd);
       } else {
         SPB_TMEM_LD_16(lane_base + (uint32_t)(Cfg::TM_ST + cbase), rs);
-        SPB_TMEM_LD_16(lane_base + (uint32_t)(Cfg::TM_DPT + cbase), rd);
       }
       tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(sdp_empty);  // S^T / dP^T may be overwritten by iteration it+1
       FB_TRACE(22);
 
       const bool need_mask = (p.causal && q0 < kv0 + 128) || (q0 + 64 > p.T) || (kv0 + 128 > p.T);
       const float2* lse2 = reinterpret_cast<const float2*>(sLse + st * 64 + cbase);
       const float2* del2 = reinterpret_cast<const float2*>(sDelta + st * 64 + cbase);
       uint32_t pkp[FB_ACOLS / 2], pkd[FB_ACOLS / 2];
-      // two explicit instantiations: left to one loop with `if (need_mask)` inside, the compiler if-converts the mask and
+      // Phase 1 (S^T only): P^T = exp2(S^T c - lse); the fp32 values go back into rs for phase 2, the bf16 ones into pkp.
+      // Two explicit instantiations: left to one loop with `if (need_mask)` inside, the compiler if-converts the mask and
       // every tile pays its compares and selects (ncu r01h: 1.4 ISETP/PLOP3 per exp); only diagonal/ragged tiles need them
-      auto elementwise = [&](auto masked) {
+      auto probs = [&](auto masked) {
         constexpr bool MASKED = decltype(masked)::value;
 #pragma unroll
         for (int i = 0; i < FB_ACOLS; i += 2) {
-          const float2 l2 = lse2[i >> 1], d2 = del2[i >> 1];
+          const float2 l2 = lse2[i >> 1];
           const float2 x = __ffma2_rn(make_float2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, make_float2(-l2.x, -l2.y));
           float2 pv = make_float2(fb_exp2(x.x), fb_exp2(x.y));
           if (MASKED) {
@@ -372,19 +371,42 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
             if (kv_dead || qi >= p.T || (p.causal && kv_idx > qi)) pv.x = 0.f;
             if (kv_dead || qi + 1 >= p.T || (p.causal && kv_idx > qi + 1)) pv.y = 0.f;
           }
-          const float2 dd = __fadd2_rn(make_float2(__uint_as_float(rd[i]), __uint_as_float(rd[i + 1])), make_float2(-d2.x, -d2.y));
-          const float2 ds = __fmul2_rn(__fmul2_rn(pv, dd), scale2);
+          rs[i] = __float_as_uint(pv.x);
+          rs[i + 1] = __float_as_uint(pv.y);
           pkp[i >> 1] = pack_bf16(pv.x, pv.y);
-          pkd[i >> 1] = pack_bf16(ds.x, ds.y);
         }
       };
       if (FB_ABL(32)) {
 #pragma unroll
-        for (int i = 0; i < FB_ACOLS / 2; ++i) pkp[i] = pkd[i] = rs[i] ^ rd[i];
+        for (int i = 0; i < FB_ACOLS / 2; ++i) pkp[i] = rs[i];
       } else if (need_mask) {
-        elementwise(std::true_type{});
+        probs(std::true_type{});
       } else {
-        elementwise(std::false_type{});
+        probs(std::false_type{});
+      }
+      // Phase 2: dP^T has been running on the tensor pipe meanwhile; dS^T = P^T o (dP^T - delta) * scale
+      mbar_wait(dp_full, it & 1);
+      tc_fence_after();
+      if (FB_ACOLS == 32) {
+        SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_DPT + cbase), rd);
+      } else {
+        SPB_TMEM_LD_16(lane_base + (uint32_t)(Cfg::TM_DPT + cbase), rd);
+      }
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(sdp_empty);  // S^T / dP^T may be overwritten by iteration it+1
+      if (FB_ABL(32)) {
+#pragma unroll
+        for (int i = 0; i < FB_ACOLS / 2; ++i) pkd[i] = rs[i] ^ rd[i];
+      } else {
+#pragma unroll
+        for (int i = 0; i < FB_ACOLS; i += 2) {
+          const float2 d2 = del2[i >> 1];
+          const float2 dd = __fadd2_rn(make_float2(__uint_as_float(rd[i]), __uint_as_float(rd[i + 1])), make_float2(-d2.x, -d2.y));
+          const float2 ds = __fmul2_rn(__fmul2_rn(make_float2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), dd), scale2);
+          pkd[i >> 1] = pack_bf16(ds.x, ds.y);
+        }
       }
       FB_TRACE(23);
       put_stat(it + 1, stat_next);  // visible to everyone after the next iteration's bar.sync
