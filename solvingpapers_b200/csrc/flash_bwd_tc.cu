@@ -648,22 +648,24 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
   float* sLse = reinterpret_cast<float*>(smem + Cfg::OFF_LSE);
   float* sDelta = sLse + 128;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
-  // role V: q_full / q_empty cover a whole stage (Q_i and dO_i).  Role K has one stage and runs as a serial chain, so its two
-  // halves are tracked apart: dO_i is free as soon as dP^T is done (reloaded under the element-wise phase), Q_i as soon as the
-  // dK MMAs are done (reloaded under the dQ^T MMAs), and the element-wise groups start on S^T while dP^T is still running.
+  // The Q_i and dO_i halves of a stage are tracked apart, because they die at different times.  Role K (one stage, a serial
+  // chain): dO_i is free as soon as dP^T is done (reloaded under the element-wise phase), Q_i as soon as the dK MMAs are done
+  // (reloaded under the dQ^T MMAs), and the element-wise groups start on S^T while dP^T is still running.  Role V (two
+  // stages): Q_i is free right after S^T - long before the dV MMAs release dO_i - so its reload starts a phase earlier; the
+  // two streams have their own producer threads (warp 0: K, Q; first drain warp: dO).
   uint64_t* kv_full = bars;
   uint64_t* q_full = bars + 1;            // [NS]
   uint64_t* q_empty = bars + 1 + NS;      // [NS]
-  uint64_t* do_full = bars + 1 + 2 * NS;  // role K
-  uint64_t* do_empty = do_full + 1;       // role K
-  uint64_t* s_full = do_full + 2;         // S^T complete
-  uint64_t* dp_full = do_full + 3;        // role K: dP^T complete
-  uint64_t* sdp_empty = do_full + 4;
-  uint64_t* pds_full = do_full + 5;
-  uint64_t* pds_empty = do_full + 6;
-  uint64_t* dq_full = do_full + 7;
-  uint64_t* dq_empty = do_full + 8;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(do_full + 9);
+  uint64_t* do_full = bars + 1 + 2 * NS;  // [NS]
+  uint64_t* do_empty = bars + 1 + 3 * NS; // [NS]
+  uint64_t* s_full = bars + 1 + 4 * NS;   // S^T complete
+  uint64_t* dp_full = s_full + 1;         // role K: dP^T complete
+  uint64_t* sdp_empty = s_full + 2;
+  uint64_t* pds_full = s_full + 3;
+  uint64_t* pds_empty = s_full + 4;
+  uint64_t* dq_full = s_full + 5;
+  uint64_t* dq_empty = s_full + 6;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_full + 7);
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -693,9 +695,9 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
       for (int i = 0; i < NS; ++i) {
         mbar_init(&q_full[i], 1);
         mbar_init(&q_empty[i], 1);
+        mbar_init(&do_full[i], 1);
+        mbar_init(&do_empty[i], 1);
       }
-      mbar_init(do_full, 1);
-      mbar_init(do_empty, 1);
       mbar_init(s_full, 1);
       mbar_init(dp_full, 1);
       mbar_init(sdp_empty, 4 * FB_AGROUPS);
@@ -716,6 +718,7 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
+    FB_TRACE_DECL(0, true);
     if (lane == 0) {
       const int row_kv = b * p.T + kv0;
       mbar_arrive_expect_tx(kv_full, (ROLE == 2 ? 2 : 1) * 4 * 16384);
@@ -729,20 +732,30 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
         const uint32_t u = (it / NS) & 1;
         const int h = g * n_rep + giter(it) / n_i;
         const int row_q = b * p.T + (i_start + giter(it) % n_i) * 64;
-        if (ROLE == 1) {
+        const bool more = it + 1 < n_it;
+        const int h_n = g * n_rep + giter(it + 1) / n_i;
+        const int row_n = b * p.T + (i_start + giter(it + 1) % n_i) * 64;
+        if (ROLE == 1) {  // the Q stream (the dO stream has its own thread below)
           mbar_wait(&q_empty[st], u ^ 1);
-          mbar_arrive_expect_tx(&q_full[st], 2 * Cfg::Q_BYTES);
+          FB_TRACE(1);
+          mbar_arrive_expect_tx(&q_full[st], Cfg::Q_BYTES);
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            tma_load_2d(sQ + st * Cfg::Q_BYTES + c * 8192, &tmQ, &q_full[st], h * HD + c * 64, row_q);
-            tma_load_2d(sDO + st * Cfg::Q_BYTES + c * 8192, &tmDO, &q_full[st], h * HD + c * 64, row_q);
-          }
+          for (int c = 0; c < 4; ++c) tma_load_2d(sQ + st * Cfg::Q_BYTES + c * 8192, &tmQ, &q_full[st], h * HD + c * 64, row_q);
         } else {
-          mbar_wait(do_empty, (it & 1) ^ 1);  // released first (after dP^T of the previous iteration)
-          mbar_arrive_expect_tx(do_full, Cfg::Q_BYTES);
+          mbar_wait(&do_empty[0], (it & 1) ^ 1);  // released first (after dP^T of the previous iteration)
+          FB_TRACE(1);
+          mbar_arrive_expect_tx(&do_full[0], Cfg::Q_BYTES);
 #pragma unroll
-          for (int c = 0; c < 4; ++c) tma_load_2d(sDO + c * 8192, &tmDO, do_full, h * HD + c * 64, row_q);
+          for (int c = 0; c < 4; ++c) tma_load_2d(sDO + c * 8192, &tmDO, &do_full[0], h * HD + c * 64, row_q);
+          if (more) {  // the next tiles into L2 now: their loads sit on the serial chain of the next iteration
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              tma_prefetch_2d(&tmQ, h_n * HD + c * 64, row_n);
+              tma_prefetch_2d(&tmDO, h_n * HD + c * 64, row_n);
+            }
+          }
           mbar_wait(&q_empty[0], (it & 1) ^ 1);  // released after the dK MMAs of the previous iteration
+          FB_TRACE(2);
           mbar_arrive_expect_tx(&q_full[0], Cfg::Q_BYTES);
 #pragma unroll
           for (int c = 0; c < 4; ++c) tma_load_2d(sQ + c * 8192, &tmQ, &q_full[0], h * HD + c * 64, row_q);
@@ -752,6 +765,7 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
+    FB_TRACE_DECL(1, true);
     const uint32_t idesc_s = umma_idesc_bf16(128, 64, 0, 0);
     const uint32_t idesc_g = umma_idesc_bf16(128, 256, 0, 1);   // dV / dK: N = all 256 head columns, B MN-major (the Q / dO stage)
     const uint32_t idesc_q = umma_idesc_bf16(128, 64, 1, 1);
@@ -763,7 +777,9 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
     auto issue_s = [&](int it) {
       const int st = it % NS;
       mbar_wait(&q_full[st], (it / NS) & 1);
+      FB_TRACE(10);
       mbar_wait(sdp_empty, (it & 1) ^ 1);
+      FB_TRACE(11);
       tc_fence_after();
       const uint64_t dQ_k = umma_desc_kmajor(smem_u32(sQ + st * Cfg::Q_BYTES)), dDO_k = umma_desc_kmajor(smem_u32(sDO + st * Cfg::Q_BYTES));
 #pragma unroll
@@ -772,8 +788,11 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
         umma_bf16_w(tmem_base + Cfg::TM_ST, dK_k + (aoff >> 4), dQ_k + (boff >> 4), idesc_s, kk > 0 ? 1u : 0u);
       }
       umma_commit_w(s_full);
+      if (ROLE == 1) umma_commit_w(&q_empty[st]);  // role V reads Q_i only here
+      FB_TRACE(12);
       if (ROLE == 2) {
-        mbar_wait(do_full, it & 1);
+        mbar_wait(&do_full[0], it & 1);
+        FB_TRACE(16);
         tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
@@ -781,20 +800,25 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
           umma_bf16_w(tmem_base + Cfg::TM_DPT, dV_k + (aoff >> 4), dDO_k + (boff >> 4), idesc_s, kk > 0 ? 1u : 0u);
         }
         umma_commit_w(dp_full);
-        umma_commit_w(do_empty);  // nothing else in this role reads dO_i
+        umma_commit_w(&do_empty[0]);  // nothing else in this role reads dO_i
+        FB_TRACE(17);
       }
     };
     auto issue_g = [&](int it) {
       const int st = it % NS;
       mbar_wait(pds_full, it & 1);
+      FB_TRACE(13);
       if (ROLE == 2) mbar_wait(dq_empty, (it & 1) ^ 1);
+      FB_TRACE(14);
       tc_fence_after();
       if (ROLE == 1) {
+        mbar_wait(&do_full[st], (it / NS) & 1);
+        tc_fence_after();
         const uint64_t dDO_mn = umma_desc_mnmajor(smem_u32(sDO + st * Cfg::Q_BYTES), 64);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dV += P^T dO, P^T from tensor memory
           umma_bf16_ts_w(tmem_base + Cfg::TM_ACC, tmem_base + Cfg::TM_P + kk * 8, dDO_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
-        umma_commit_w(&q_empty[st]);
+        umma_commit_w(&do_empty[st]);
         umma_commit_w(pds_empty);
       } else {
         const uint64_t dQ_mn = umma_desc_mnmajor(smem_u32(sQ + st * Cfg::Q_BYTES), 64);
@@ -812,6 +836,7 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
         umma_commit_w(pds_empty);
         umma_commit_w(dq_full);
       }
+      FB_TRACE(15);
     };
     if (n_it > 0) issue_s(0);
     for (int it = 0; it < n_it; ++it) {
@@ -844,6 +869,7 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
       if (ct < 64) sLse[(it & 1) * 64 + ct] = v * FB_LOG2E;
       else if (ct < 128) sDelta[(it & 1) * 64 + (ct - 64)] = v;
     };
+    FB_TRACE_DECL(2, warp == 2);
     put_stat(0, fetch_stat(0));
     const float2 sc2 = make_float2(p.scale_log2, p.scale_log2);
     const float2 scale2 = make_float2(p.scale, p.scale);
@@ -852,7 +878,9 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
       const int q0 = (i_start + giter(it) % n_i) * 64;
       const float stat_next = fetch_stat(it + 1);
       asm volatile("bar.sync 1, %0;" ::"n"(FB_ATHREADS) : "memory");
+      FB_TRACE(20);
       mbar_wait(s_full, it & 1);
+      FB_TRACE(21);
       tc_fence_after();
       uint32_t rs[FB_ACOLS], rd[FB_ACOLS];
       SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_ST + cbase), rs);
@@ -887,8 +915,10 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
       };
       if (need_mask) probs(std::true_type{});
       else probs(std::false_type{});
+      FB_TRACE(26);
       if (ROLE == 2) {  // the exps above ran while the tensor pipe was still on dP^T
         mbar_wait(dp_full, it & 1);
+        FB_TRACE(27);
         tc_fence_after();
         SPB_TMEM_LD_32(lane_base + (uint32_t)(Cfg::TM_DPT + cbase), rd);
         tmem_ld_wait();
@@ -903,8 +933,10 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
           pk[i >> 1] = pack_bf16(ds.x, ds.y);
         }
       }
+      FB_TRACE(23);
       put_stat(it + 1, stat_next);
       mbar_wait(pds_empty, (it & 1) ^ 1);  // the MMA group of iteration it-1 has finished reading P^T / dS^T
+      FB_TRACE(24);
       if (ROLE == 1) {
         SPB_TMEM_ST_16(lane_base + (uint32_t)(Cfg::TM_P + cbase / 2), pk);
         tmem_st_wait();
@@ -920,21 +952,38 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(pds_full);
+      FB_TRACE(25);
     }
     if (n_it > 0) {
       mbar_wait(pds_empty, (n_it - 1) & 1);  // the last commit covers every MMA issued before it
       tc_fence_after();
     }
-  } else if (ROLE == 2) {
+  } else if (ROLE == 1) {
+    // ------------------------------------------------------------------ role V: the first of the (otherwise idle) drain warps streams dO_i
+    if (warp == 2 + 4 * FB_AGROUPS && lane == 0) {
+      for (int it = 0; it < n_it; ++it) {
+        const int st = it % NS;
+        const int h = g * n_rep + giter(it) / n_i;
+        const int row_q = b * p.T + (i_start + giter(it) % n_i) * 64;
+        mbar_wait(&do_empty[st], ((it / NS) & 1) ^ 1);
+        mbar_arrive_expect_tx(&do_full[st], Cfg::Q_BYTES);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) tma_load_2d(sDO + st * Cfg::Q_BYTES + c * 8192, &tmDO, &do_full[st], h * HD + c * 64, row_q);
+      }
+    }
+    __syncwarp();
+  } else {
     // ------------------------------------------------------------------ drain group (role K): reduce both halves of dQ^T every iteration
     const int qd = warp & 3;
     const int r = qd * 32 + lane;  // head dim inside the half = TMEM lane of dQ^T
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
     const bool leader = (qd == 0 && lane == 0);
+    FB_TRACE_DECL(3, qd == 0);
     for (int it = 0; it < n_it; ++it) {
       const int h = g * n_rep + giter(it) / n_i;
       const int q0 = (i_start + giter(it) % n_i) * 64;
       mbar_wait(dq_full, it & 1);
+      FB_TRACE(30);
       tc_fence_after();
 #pragma unroll 1
       for (int hh = 0; hh < 2; ++hh) {
@@ -951,6 +1000,7 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(dq_empty);
+          FB_TRACE(31);
         }
 #pragma unroll
         for (int rd = 0; rd < 2; ++rd) {  // 32 query rows at a time through the 16 KB staging tile
@@ -966,6 +1016,7 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
           }
         }
       }
+      FB_TRACE(33);
     }
     if (leader) tma_store_wait_read<0>();
   }
@@ -1076,8 +1127,13 @@ __global__ void __launch_bounds__(FB_THREADS, 1)
   // blockIdx.x = (kv head * 2 + role bit) * S + rank; role K first: it is the longer of the two
   const int rank = (int)(blockIdx.x % (unsigned)S);
   const int rg = (int)(blockIdx.x / (unsigned)S);
+#ifdef SPB_FB_TRACE_ROLE_V  // development: the traced CTA (0,0,0) becomes a role-V one
+  if ((rg & 1) == 1) fb256_body<2>(tmK, tmV, tmQ, tmDO, tmDQ, p, smem, rg >> 1, rank, S);
+  else fb256_body<1>(tmK, tmV, tmQ, tmDO, tmDQ, p, smem, rg >> 1, rank, S);
+#else
   if ((rg & 1) == 0) fb256_body<2>(tmK, tmV, tmQ, tmDO, tmDQ, p, smem, rg >> 1, rank, S);
   else fb256_body<1>(tmK, tmV, tmQ, tmDO, tmDQ, p, smem, rg >> 1, rank, S);
+#endif
 }
 
 bool flash_bwd_tc_supported(int dtype, int hd) { return dtype == SPB_BF16 && (hd == 64 || hd == 128 || hd == 256); }

@@ -6,7 +6,8 @@ os.environ.setdefault("SPB_LIB_PATH", os.path.join(os.path.dirname(os.path.dirna
 import torch
 from solvingpapers_b200 import _lib as L, ops
 
-NAMES = {1: "prod qdo_empty ok", 10: "mma qdo_full seen", 11: "mma sdp_empty seen", 12: "mma S,dP issued", 13: "mma pds_full seen", 14: "mma dq_empty seen",
+NAMES = {2: "prod q_empty ok (hd256 role K)", 16: "mma do_full seen", 17: "mma dP issued", 26: "ew exps done", 27: "ew dp_full seen",
+         1: "prod qdo_empty / do_empty ok", 10: "mma qdo_full seen", 11: "mma sdp_empty seen", 12: "mma S,dP issued", 13: "mma pds_full seen", 14: "mma dq_empty seen",
          15: "mma dV,dK,dQ issued", 20: "ew bar", 21: "ew sdp_full seen", 22: "ew S,dP in regs", 23: "ew math done", 24: "ew pds_empty seen",
          25: "ew P,dS stored+arrived", 30: "dr dq_full seen", 31: "dr dQ in regs", 32: "dr staged", 33: "dr reduce issued"}
 B, T, Hq, Hkv, hd = (int(os.environ.get(k, d)) for k, d in (('TR_B', 4), ('TR_T', 2048), ('TR_HQ', 32), ('TR_HKV', 8), ('TR_HD', 128)))
