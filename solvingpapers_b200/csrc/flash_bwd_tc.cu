@@ -742,23 +742,32 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
 #pragma unroll
           for (int c = 0; c < 4; ++c) tma_load_2d(sQ + st * Cfg::Q_BYTES + c * 8192, &tmQ, &q_full[st], h * HD + c * 64, row_q);
         } else {
-          mbar_wait(&do_empty[0], (it & 1) ^ 1);  // released first (after dP^T of the previous iteration)
-          FB_TRACE(1);
-          mbar_arrive_expect_tx(&do_full[0], Cfg::Q_BYTES);
-#pragma unroll
-          for (int c = 0; c < 4; ++c) tma_load_2d(sDO + c * 8192, &tmDO, &do_full[0], h * HD + c * 64, row_q);
-          if (more) {  // the next tiles into L2 now: their loads sit on the serial chain of the next iteration
+          // Role K keeps ONE stage, but its two 32 KB halves swap jobs every iteration: Q_it sits in half (it & 1), dO_it in
+          // the other.  dO_it dies early (after dP^T) - Q_{it+1} is loaded over it while the element-wise phase runs - and Q_it
+          // dies after the dK MMAs - dO_{it+1} is loaded over it and lands under S^T_{it+1}.  Neither load is on the chain.
+          if (it == 0) {
+            mbar_arrive_expect_tx(&q_full[0], Cfg::Q_BYTES);
+            mbar_arrive_expect_tx(&do_full[0], Cfg::Q_BYTES);
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-              tma_prefetch_2d(&tmQ, h_n * HD + c * 64, row_n);
-              tma_prefetch_2d(&tmDO, h_n * HD + c * 64, row_n);
+              tma_load_2d(sQ + c * 8192, &tmQ, &q_full[0], h * HD + c * 64, row_q);
+              tma_load_2d(sQ + Cfg::Q_BYTES + c * 8192, &tmDO, &do_full[0], h * HD + c * 64, row_q);
             }
           }
-          mbar_wait(&q_empty[0], (it & 1) ^ 1);  // released after the dK MMAs of the previous iteration
-          FB_TRACE(2);
-          mbar_arrive_expect_tx(&q_full[0], Cfg::Q_BYTES);
+          if (more) {
+            uint8_t* half_q = sQ + (it & 1) * Cfg::Q_BYTES;         // holds Q_it
+            uint8_t* half_do = sQ + ((it & 1) ^ 1) * Cfg::Q_BYTES;  // holds dO_it
+            mbar_wait(&do_empty[0], it & 1);  // dP^T of iteration it is done
+            FB_TRACE(1);
+            mbar_arrive_expect_tx(&q_full[0], Cfg::Q_BYTES);
 #pragma unroll
-          for (int c = 0; c < 4; ++c) tma_load_2d(sQ + c * 8192, &tmQ, &q_full[0], h * HD + c * 64, row_q);
+            for (int c = 0; c < 4; ++c) tma_load_2d(half_do + c * 8192, &tmQ, &q_full[0], h_n * HD + c * 64, row_n);
+            mbar_wait(&q_empty[0], it & 1);   // the dK MMAs of iteration it are done
+            FB_TRACE(2);
+            mbar_arrive_expect_tx(&do_full[0], Cfg::Q_BYTES);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) tma_load_2d(half_q + c * 8192, &tmDO, &do_full[0], h_n * HD + c * 64, row_n);
+          }
         }
       }
     }
@@ -781,7 +790,10 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
       mbar_wait(sdp_empty, (it & 1) ^ 1);
       FB_TRACE(11);
       tc_fence_after();
-      const uint64_t dQ_k = umma_desc_kmajor(smem_u32(sQ + st * Cfg::Q_BYTES)), dDO_k = umma_desc_kmajor(smem_u32(sDO + st * Cfg::Q_BYTES));
+      // role K: the two halves of its single stage swap jobs every iteration (see the producer)
+      const uint8_t* bq = ROLE == 2 ? sQ + (it & 1) * Cfg::Q_BYTES : sQ + st * Cfg::Q_BYTES;
+      const uint8_t* bdo = ROLE == 2 ? sQ + ((it & 1) ^ 1) * Cfg::Q_BYTES : sDO + st * Cfg::Q_BYTES;
+      const uint64_t dQ_k = umma_desc_kmajor(smem_u32(bq)), dDO_k = umma_desc_kmajor(smem_u32(bdo));
 #pragma unroll
       for (int kk = 0; kk < HD / 16; ++kk) {
         const uint32_t aoff = (kk >> 2) * 16384 + (kk & 3) * 32, boff = (kk >> 2) * 8192 + (kk & 3) * 32;
@@ -821,7 +833,7 @@ __device__ __forceinline__ void fb256_body(const CUtensorMap& tmK, const CUtenso
         umma_commit_w(&do_empty[st]);
         umma_commit_w(pds_empty);
       } else {
-        const uint64_t dQ_mn = umma_desc_mnmajor(smem_u32(sQ + st * Cfg::Q_BYTES), 64);
+        const uint64_t dQ_mn = umma_desc_mnmajor(smem_u32(sQ + (it & 1) * Cfg::Q_BYTES), 64);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // dK += dS^T Q, dS^T from shared memory (K-major, 16 q columns = 32 B per k-step)
           umma_bf16_w(tmem_base + Cfg::TM_ACC, dDST_k + ((kk * 32) >> 4), dQ_mn + ((kk * 2048) >> 4), idesc_g, (it > 0 || kk > 0) ? 1u : 0u);
