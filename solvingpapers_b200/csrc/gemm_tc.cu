@@ -27,6 +27,7 @@ struct GemmTcArgs {
   const float4* rope;  // optional fused rotary epilogue (llama3:592-601): table [T, hd/2] of (a,b,c,d), applied to columns < rope_cols
   int rope_cols, rope_T, rope_hd;
   int out_f32, accumulate, atomic, vec_ok;
+  int tma_store;       // plain (non-accumulating) output tiles leave through shared memory + TMA bulk stores (see gemm_tc_tma_store_chunk)
   int bias_vec;        // bias pointer is 16-byte aligned
   int bias_f32;        // bias elements are fp32 (else bf16)
   int group_m;         // tile raster: row-blocks per group (see gemm_tc_tile_coords)
@@ -116,8 +117,58 @@ struct GemmTcCfg {
   static constexpr int TMEM_COLS = (BN == 192) ? 512 : 2 * BN;  // power of two; accumulator stage a sits at column a*BN
 };
 
+// Output through shared memory + TMA (cp.async.bulk.tensor store).  A thread owns one output ROW of the chunk, so direct stores
+// are 32 scattered 16-byte pieces per warp instruction - partial sectors on 32 different lines - and the epilogue, not the
+// main loop, sets the pace of short-K GEMMs (K = 768: 13 k clk per 256x256 tile against a 6 k clk main loop).  Here the warp
+// stages its 32 rows in its shared-memory buffer (rows of 128 B, 128B-swizzled: conflict-free) and one TMA store writes
+// whole lines; the TMA unit clips rows / columns past M / N.  bf16: two chunks (64 columns) per store; fp32: one (32 columns).
+__device__ __forceinline__ void gemm_tc_tma_store_chunk(const GemmTcArgs& p, const CUtensorMap* tmD, int row0, int col0, const float* v,
+                                                        uint8_t* wbuf2, int c, int lane, bool last) {
+  if (p.out_f32) {
+    uint8_t* wbuf = wbuf2 + (c & 1) * 4096;
+    if (lane == 0) tma_store_wait_read<1>();  // the store issued two chunks ago has finished reading this buffer
+    __syncwarp();
+    uint8_t* rowp = wbuf + lane * 128;
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      *reinterpret_cast<float4*>(rowp + ((u ^ (lane & 7)) << 4)) = make_float4(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]);
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      tma_store_2d(tmD, wbuf, col0, row0);
+      tma_store_commit();
+    }
+  } else {
+    const int half = c & 1;  // which 64-byte half of the 128-byte staged row this chunk fills
+    uint8_t* wbuf = wbuf2 + ((c >> 1) & 1) * 4096;
+    if (half == 0) {
+      if (lane == 0) tma_store_wait_read<1>();
+      __syncwarp();
+    }
+    uint8_t* rowp = wbuf + lane * 128;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      uint4 o;
+      o.x = pack_bf16(v[8 * u], v[8 * u + 1]);
+      o.y = pack_bf16(v[8 * u + 2], v[8 * u + 3]);
+      o.z = pack_bf16(v[8 * u + 4], v[8 * u + 5]);
+      o.w = pack_bf16(v[8 * u + 6], v[8 * u + 7]);
+      *reinterpret_cast<uint4*>(rowp + (((half * 4 + u) ^ (lane & 7)) << 4)) = o;
+    }
+    if (half == 1 || last) {  // `last` with half == 0: the tile ends inside this 64-column box; the stale right half lies past N and is clipped
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_2d(tmD, wbuf, col0 - half * 32, row0);
+        tma_store_commit();
+      }
+    }
+  }
+}
+
 __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row, int col0, const uint32_t* r,
-                                                    const uint8_t* rope_row, int lane_in_warp, int atomic) {
+                                                    const uint8_t* rope_row, int lane_in_warp, int atomic, const CUtensorMap* tmD = nullptr,
+                                                    uint8_t* wbuf2 = nullptr, int c = 0, int row0 = 0, bool last = false) {
   // 32 consecutive fp32 accumulator columns of one output row
   const int ncol = min(32, p.N - col0);
   float v[32];
@@ -156,6 +207,10 @@ __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row
         v[i + 1] = m.z * xe + m.w * xo;
       }
     }
+  }
+  if (p.tma_store) {
+    gemm_tc_tma_store_chunk(p, tmD, row0, col0, v, wbuf2, c, lane_in_warp, last);
+    return;
   }
   if (p.out_f32) {
     float* d = reinterpret_cast<float*>(p.D) + (int64_t)row * p.ldd + col0;
@@ -247,6 +302,12 @@ __device__ __forceinline__ void gemm_tc_drain(const GemmTcArgs& p, const CUtenso
                                               uint8_t* warp_buf, int q, int lane) {
   const int row = m0 + q * 32 + lane;
   if (m0 + q * 32 >= p.M) return;  // warp-uniform: this warp's 32 rows lie past the last row (small-M problems)
+  if (p.tma_store || atomic) {
+    // the staging halves alternate with the chunk index; a tile that ended on an odd count (N edge, 192-wide tiles) would hand
+    // the next tile a half whose store may still be reading it - start every tile with both halves free
+    if (lane == 0) tma_store_wait_read<0>();
+    __syncwarp();
+  }
   float dsum = 0.f;  // running sum_c dO * O of the current head (fuse_o != NULL)
   float hm = -INFINITY, hs = 0.f;  // loss-head mode 1: online (max, sum exp) of this row over the tile's columns
 #pragma unroll 1
@@ -340,6 +401,8 @@ __device__ __forceinline__ void gemm_tc_drain(const GemmTcArgs& p, const CUtenso
         }
         if (atomic && p.vec_ok) gemm_tc_reduce_chunk(tmD, m0 + q * 32, col0, r, warp_buf, c, lane);
         else if (atomic) gemm_tc_atomic_chunk(p, m0 + q * 32, col0, r, reinterpret_cast<float*>(warp_buf), lane);
+        else if (p.tma_store)  // whole warp: the rows past M are clipped by the TMA unit
+          gemm_tc_store_chunk(p, row, col0, r, rope_row, lane, 0, tmD, warp_buf, c, m0 + q * 32, (c == NCOLS / 32 - 1) || (col0 + 32 >= p.N));
         else if (row < p.M) gemm_tc_store_chunk(p, row, col0, r, rope_row, lane, 0);
       }
   if (p.head_mode == 1 && row < p.M) p.head_part[(int64_t)row * p.num_n + n0 / NCOLS] = make_float2(hm, hs);
@@ -709,9 +772,13 @@ static int gemm_tc2_launch(const void* A, int64_t lda, const void* B, int64_t ld
   if (!args.b_mn) rc = make_tmap_2d(&tmB, B, 2, (uint64_t)args.N, (uint64_t)K, (uint64_t)ldb, Cfg::BN / 2, GT_BK, true, false);
   else rc = make_tmap_2d(&tmB, B, 2, (uint64_t)K, (uint64_t)args.N, (uint64_t)ldb, GT_BK, 64, true, false);
   if (rc) return rc;
-  CUtensorMap tmD = tmA;  // only dereferenced by K-split tail parts
+  CUtensorMap tmD = tmA;  // dereferenced by K-split tail parts (fp32 reduce-add) and by the TMA-store epilogue
+  if (args.out_f32 && args.vec_ok && (args.tail_parts > 1 || args.tma_store)) {
+    if ((rc = make_tmap_2d(&tmD, args.D, 4, (uint64_t)args.M, (uint64_t)args.N, (uint64_t)args.ldd, 32, 32, true, true))) return rc;
+  } else if (args.tma_store) {
+    if ((rc = make_tmap_2d(&tmD, args.D, 2, (uint64_t)args.M, (uint64_t)args.N, (uint64_t)args.ldd, 32, 64, true, false))) return rc;
+  }
   if (args.tail_parts > 1) {
-    if (args.vec_ok && (rc = make_tmap_2d(&tmD, args.D, 4, (uint64_t)args.M, (uint64_t)args.N, (uint64_t)args.ldd, 32, 32, true, true))) return rc;
     gemm_tc_zero_tail_kernel<Cfg::BN, 256><<<dim3(tiles - args.full_tiles, 256 / 32), 256, 0, st>>>(args);
     SPB_LAUNCH_CHECK();
   }
@@ -805,9 +872,13 @@ static int gemm_tc_launch(const void* A, int64_t lda, const void* B, int64_t ldb
   if (!args.b_mn) rc = make_tmap_2d(&tmB, B, 2, (uint64_t)args.N, (uint64_t)K, (uint64_t)ldb, (uint32_t)BN, GT_BK, true, false);
   else rc = make_tmap_2d(&tmB, B, 2, (uint64_t)K, (uint64_t)args.N, (uint64_t)ldb, GT_BK, 64, true, false);
   if (rc) return rc;
-  CUtensorMap tmD = tmA;  // only dereferenced by K-split tail parts
+  CUtensorMap tmD = tmA;  // dereferenced by K-split tail parts (fp32 reduce-add) and by the TMA-store epilogue
+  if (args.out_f32 && args.vec_ok && (args.tail_parts > 1 || args.tma_store)) {
+    if ((rc = make_tmap_2d(&tmD, args.D, 4, (uint64_t)args.M, (uint64_t)args.N, (uint64_t)args.ldd, 32, 32, true, true))) return rc;
+  } else if (args.tma_store) {
+    if ((rc = make_tmap_2d(&tmD, args.D, 2, (uint64_t)args.M, (uint64_t)args.N, (uint64_t)args.ldd, 32, 64, true, false))) return rc;
+  }
   if (args.tail_parts > 1) {
-    if (args.vec_ok && (rc = make_tmap_2d(&tmD, args.D, 4, (uint64_t)args.M, (uint64_t)args.N, (uint64_t)args.ldd, 32, 32, true, true))) return rc;
     gemm_tc_zero_tail_kernel<BN><<<dim3(tiles - args.full_tiles, GT_BM / 32), 256, 0, st>>>(args);
     SPB_LAUNCH_CHECK();
   }
@@ -888,6 +959,11 @@ int gemm_tc(int out_dtype, int64_t M, int64_t N, int64_t K, const void* A, int64
   const int esz = args.out_f32 ? 4 : 2;
   args.vec_ok = ((uintptr_t)D % 16 == 0) && ((ldd * esz) % 16 == 0) &&
                 (residual == nullptr || (((uintptr_t)residual % 16 == 0) && ((ldr * esz) % 16 == 0)));
+  // TMA-store epilogue: plain stores only (no read-modify-write of D, no loss-head partial mode), output addressable by TMA
+  // (16-byte aligned rows), and the warp staging buffer not taken by the fused rotary table.  SPB_GEMM_TMA_STORE=0: direct stores.
+  static const bool tma_store_off = [] { const char* e = getenv("SPB_GEMM_TMA_STORE"); return e && e[0] == '0'; }();
+  args.tma_store = (!tma_store_off && args.vec_ok && !args.accumulate && residual == nullptr && rope == nullptr &&
+                    !(head != nullptr && head->mode == 1)) ? 1 : 0;
   // K-split of the tail wave needs a plain fp32 output (weight gradients)
   const bool may_split = args.out_f32 && bias == nullptr && rope == nullptr && !args.accumulate && head == nullptr;
   // tile width: 256 unless a 192-wide tile fills the waves of this problem clearly better (e.g. 8192 x 6144: 94 % -> 99 %)

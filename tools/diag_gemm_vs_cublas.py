@@ -24,6 +24,17 @@ SHAPES = [
 ]
 
 
+# short-K shapes of the other configs (SHAPES=c5 / c4): where the epilogue, not the main loop, sets the pace
+if os.environ.get("SHAPES") == "c5":   # ViT-B/16: 256 x 197 tokens, d 768
+    N_TOK = 256 * 197
+    SHAPES = [("c5 gemm_qkv", N_TOK, 2304, 768, False, True, torch.bfloat16), ("c5 gemm_out", N_TOK, 768, 768, False, True, torch.bfloat16),
+              ("c5 gemm_dx", N_TOK, 768, 2304, False, False, torch.bfloat16), ("c5 gemm_dwqkv (fp32 out)", 2304, 768, N_TOK, True, False, torch.float32)]
+elif os.environ.get("SHAPES") == "c4":  # Gemma-2B-shaped: 16384 tokens, d 2048, 8 q heads + 1 kv head of 256
+    N_TOK = 16384
+    SHAPES = [("c4 gemm_qkv", N_TOK, 2560, 2048, False, False, torch.bfloat16), ("c4 gemm_out", N_TOK, 2048, 2048, False, False, torch.bfloat16),
+              ("c4 gemm_dx", N_TOK, 2048, 2560, False, True, torch.bfloat16), ("c4 gemm_dwqkv (fp32 out)", 2048, 2560, N_TOK, True, False, torch.float32)]
+
+
 def timed(fn, reps=10):
     for _ in range(3):
         fn(0)
