@@ -168,7 +168,8 @@ __device__ __forceinline__ void gemm_tc_tma_store_chunk(const GemmTcArgs& p, con
 
 __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row, int col0, const uint32_t* r,
                                                     const uint8_t* rope_row, int lane_in_warp, int atomic, const CUtensorMap* tmD = nullptr,
-                                                    uint8_t* wbuf2 = nullptr, int c = 0, int row0 = 0, bool last = false) {
+                                                    uint8_t* wbuf2 = nullptr, int c = 0, int row0 = 0, bool last = false,
+                                                    const uint4* bias_pre = nullptr) {
   // 32 consecutive fp32 accumulator columns of one output row
   const int ncol = min(32, p.N - col0);
   float v[32];
@@ -184,7 +185,7 @@ __device__ __forceinline__ void gemm_tc_store_chunk(const GemmTcArgs& p, int row
       const uint4* bp = reinterpret_cast<const uint4*>(p.bias + col0);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        const uint4 b = __ldg(bp + i);
+        const uint4 b = bias_pre != nullptr ? bias_pre[i] : __ldg(bp + i);  // preloaded while the accumulators were on their way
         const float2 b0 = unpack_bf16(b.x), b1 = unpack_bf16(b.y), b2 = unpack_bf16(b.z), b3 = unpack_bf16(b.w);
         v[8 * i] += b0.x; v[8 * i + 1] += b0.y; v[8 * i + 2] += b1.x; v[8 * i + 3] += b1.y;
         v[8 * i + 4] += b2.x; v[8 * i + 5] += b2.y; v[8 * i + 6] += b3.x; v[8 * i + 7] += b3.y;
@@ -348,6 +349,13 @@ __device__ __forceinline__ void gemm_tc_drain(const GemmTcArgs& p, const CUtenso
           __syncwarp();
           rope_row = wbuf;
         }
+        uint4 bpre[4];
+        const bool bias_early = p.bias != nullptr && p.bias_vec && !p.bias_f32 && col0 + 32 <= p.N;  // warp-uniform
+        if (bias_early) {
+          const uint4* bp = reinterpret_cast<const uint4*>(p.bias + col0);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) bpre[i] = __ldg(bp + i);
+        }
         tmem_ld_wait();
         if (fuse) {
           // the same rounding the attention backward sees: dO as the bf16 value that is stored
@@ -402,8 +410,10 @@ __device__ __forceinline__ void gemm_tc_drain(const GemmTcArgs& p, const CUtenso
         if (atomic && p.vec_ok) gemm_tc_reduce_chunk(tmD, m0 + q * 32, col0, r, warp_buf, c, lane);
         else if (atomic) gemm_tc_atomic_chunk(p, m0 + q * 32, col0, r, reinterpret_cast<float*>(warp_buf), lane);
         else if (p.tma_store)  // whole warp: the rows past M are clipped by the TMA unit
-          gemm_tc_store_chunk(p, row, col0, r, rope_row, lane, 0, tmD, warp_buf, c, m0 + q * 32, (c == NCOLS / 32 - 1) || (col0 + 32 >= p.N));
-        else if (row < p.M) gemm_tc_store_chunk(p, row, col0, r, rope_row, lane, 0);
+          gemm_tc_store_chunk(p, row, col0, r, rope_row, lane, 0, tmD, warp_buf, c, m0 + q * 32, (c == NCOLS / 32 - 1) || (col0 + 32 >= p.N),
+                              bias_early ? bpre : nullptr);
+        else if (row < p.M)
+          gemm_tc_store_chunk(p, row, col0, r, rope_row, lane, 0, nullptr, nullptr, 0, 0, false, bias_early ? bpre : nullptr);
       }
   if (p.head_mode == 1 && row < p.M) p.head_part[(int64_t)row * p.num_n + n0 / NCOLS] = make_float2(hm, hs);
 }
