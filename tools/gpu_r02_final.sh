@@ -19,6 +19,11 @@ ls -la gpurun_out/${T}_*.ncu-rep
 DCMD="python bench.py --workload c3dec32 --steps 4 --warmup 3 --graph off --no-cpu-baseline"
 timeout 600 $DCMD > gpurun_out/${T}_plain_dec.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k "regex:attn_decode_mma_kernel|small_m_mma_kernel" -s 9 -c 3 -o gpurun_out/${T}_prof_decode -f $DCMD > gpurun_out/${T}_ncu_decode.log 2>&1; echo "ncu decode rc=$?"
+# hd-256 backward: the legacy column split still passes; full capture of the role kernel at C4
+SPB_BWD256_ROLES=0 timeout 600 python -m pytest tests -q -m gpu -k "256 or c4 or C4 or gemma" -p no:cacheprovider 2>&1 | tail -1
+C4CMD="python bench.py --workload c4 --steps 2 --warmup 3 --graph off --no-cpu-baseline --no-e2e --sustain-s 0"
+timeout 600 $C4CMD > gpurun_out/${T}_plain_c4.log 2>&1 &&
+timeout 900 ncu --set full --clock-control none --import-source on -k "regex:flash_bwd256_roles_kernel" -s 3 -c 1 -o gpurun_out/${T}_prof_bwd256 -f $C4CMD > gpurun_out/${T}_ncu_bwd256.log 2>&1; echo "ncu bwd256 rc=$?"
 # the other configs and the decode lines on the final library, and the per-shape cuBLAS comparison
 for wl in c1 c2 c2lit c4 c4lit c5 c3dec c3dec32 c1dec; do
   timeout 600 python bench.py --workload $wl --steps 20 --warmup 5 --sustain-s 0 > gpurun_out/${T}_bench_$wl.json 2>> gpurun_out/${T}_bench.err; echo "$wl rc=$?"
