@@ -12,7 +12,9 @@ module is shipped as source: tests/test_ffi_source.py checks it against include/
     from spb_jax import rms_norm, apply_rotary_emb, repeat_kv, attention      # replaces cells c15, c17, c18, c24
 
 Contract carried over from tracing: the mask is a tracer whose values cannot be read, so ``mask is not None``
-means causal and ``None`` bidirectional.  ``cache is not None`` or ``position != 0`` raise (no slow path).
+means causal and ``None`` bidirectional.  ``cache is not None`` or ``position != 0`` raise in ``attention`` (no slow path);
+the KV-cache step of the same function (llama3:815-829, caller ``generate`` :499-511) is ``attention_decode``: fixed-capacity
+caches appended in place, the number of valid rows a device scalar - one trace under jit serves every token.
 """
 import ctypes
 import os
@@ -43,6 +45,10 @@ class _WsLayout(ctypes.Structure):  # spb_ws_layout
                [(n, ctypes.c_size_t) for n in ("attn_scratch", "attn_scratch_bytes", "gemm_scratch", "gemm_scratch_bytes")]
 
 
+class _DecodeWs(ctypes.Structure):  # spb_decode_ws
+    _fields_ = [(n, ctypes.c_size_t) for n in ("total", "xhat", "qkv", "attn_o", "gemm_part", "attn_part")]
+
+
 def register():
     """Load both libraries and register the FFI targets (idempotent)."""
     global _core, _registered
@@ -51,11 +57,13 @@ def register():
     _core = ctypes.CDLL(_CORE, mode=ctypes.RTLD_GLOBAL)  # the shim links against it
     _core.spb_block_ws_layout.restype = ctypes.c_int
     _core.spb_block_ws_layout.argtypes = [ctypes.POINTER(_BlockDesc), ctypes.POINTER(_WsLayout)]
+    _core.spb_block_decode_ws_layout.restype = ctypes.c_int
+    _core.spb_block_decode_ws_layout.argtypes = [ctypes.POINTER(_BlockDesc), ctypes.c_int32, ctypes.POINTER(_DecodeWs)]
     _core.spb_norm_bwd_partial_bytes.restype = ctypes.c_size_t
     _core.spb_norm_bwd_partial_bytes.argtypes = [ctypes.c_int64, ctypes.c_int32]
     shim = ctypes.CDLL(_SHIM)
-    for target, sym in (("spb_block_fwd", "SpbBlockFwd"), ("spb_block_bwd", "SpbBlockBwd"), ("spb_rms_norm", "SpbRmsNorm"),
-                        ("spb_rms_norm_bwd", "SpbRmsNormBwd"), ("spb_rope", "SpbRope")):
+    for target, sym in (("spb_block_fwd", "SpbBlockFwd"), ("spb_block_bwd", "SpbBlockBwd"), ("spb_block_decode", "SpbBlockDecode"),
+                        ("spb_rms_norm", "SpbRmsNorm"), ("spb_rms_norm_bwd", "SpbRmsNormBwd"), ("spb_rope", "SpbRope")):
         jax.ffi.register_ffi_target(target, jax.ffi.pycapsule(getattr(shim, sym)), platform="CUDA")
     _registered = True
 
@@ -77,6 +85,19 @@ def _workspace_bytes(B, T, C, n_heads, n_kv_heads, dtype, norm, residual):
     rc = _core.spb_block_ws_layout(ctypes.byref(d), ctypes.byref(lay))
     if rc != 0:
         raise ValueError(f"spb_block_ws_layout failed with code {rc}")
+    return int(lay.total)
+
+
+def _decode_workspace_bytes(B, Tq, C, n_heads, n_kv_heads, dtype, norm, residual, Tmax):
+    """Host-side, at trace time: spb_block_decode_ws_layout(desc, Tmax).total."""
+    hd = C // n_heads
+    d = _BlockDesc(B=B, T=Tq, C=C, Hq=n_heads, Hkv=n_kv_heads, hd=hd, dtype=1 if dtype == jnp.bfloat16 else 0, norm_kind=1 if norm else 0,
+                   norm_eps=1e-6, norm_upcast=0, rope_kind=1, causal=0, scale=1.0 / float(np.sqrt(hd)), weight_layout=0, qkv_bias=0,
+                   out_bias=0, attn_impl=0, gemm_impl=0, residual=int(residual))
+    lay = _DecodeWs()
+    rc = _core.spb_block_decode_ws_layout(ctypes.byref(d), int(Tmax), ctypes.byref(lay))
+    if rc != 0:
+        raise ValueError(f"spb_block_decode_ws_layout failed with code {rc}")
     return int(lay.total)
 
 
@@ -181,7 +202,7 @@ def repeat_kv(x, n_rep):
 def attention(params, x, mask, freqs_cis, n_heads, n_kv_heads, cache=None, position=0):
     """llama3/LLaMA-jax.ipynb:809-829: returns (out [B,T,C], (k, v)), k and v post-rotary and un-repeated."""
     if cache is not None or position != 0:
-        raise NotImplementedError("the jax.ffi face covers the training path (cache=None, position=0); decode goes through spb_attn_decode")
+        raise NotImplementedError("attention() is the training path (cache=None, position=0); the KV-cache step is attention_decode()")
     T = x.shape[1]
     dummy_w = jnp.ones((x.shape[-1],), x.dtype)
     y, k, v = _block(x, params["wq"], params["wk"], params["wv"], params["wo"], dummy_w, _rope_table(freqs_cis[position:position + T]),
@@ -198,3 +219,26 @@ def attention_block(block_params, x, mask, freqs_cis, n_heads, n_kv_heads, eps=1
     y, k, v = _block(x, a["wq"], a["wk"], a["wv"], a["wo"], block_params["attention_norm"], _rope_table(freqs_cis[:T]), n_heads, n_kv_heads,
                      eps, mask is not None, True, residual)
     return y, (k, v)
+
+
+def attention_decode(block_params, x, k_cache, v_cache, cache_len, freqs_cis, n_heads, n_kv_heads, eps=1e-6, norm=True, residual=False):
+    """The KV-cache branch of ``attention`` (llama3/LLaMA-jax.ipynb:815-829) as ``generate`` (:499-511) drives it, for one or a few
+    new tokens ``x [B, Tq, C]``: ``attention(params['attention'], rms_norm(x, params['attention_norm']), None, freqs_cis, n_heads,
+    n_kv_heads, cache=(k, v), position=cache_len)``.  The notebook grows ``(k, v)`` by ``jnp.concatenate`` every step (a new shape,
+    hence a new trace, per token); here the caches have a fixed capacity ``[B, Tmax, n_kv_heads, head_dim]``, the new rows are
+    appended in place and ``cache_len`` (int32[1], on the device) is advanced by the call itself, so one jitted step serves every
+    token.  ``freqs_cis`` must cover ``Tmax`` positions.  Returns ``(out, (k_cache, v_cache, cache_len))``; not differentiable
+    (the notebook only decodes under ``generate``).  ``norm=False`` takes ``x`` as already normalised, ``residual=True`` adds ``x``."""
+    a = block_params["attention"] if "attention" in block_params else block_params
+    B, Tq, C = x.shape
+    Tmax = k_cache.shape[1]
+    norm_w = block_params["attention_norm"] if norm else jnp.ones((C,), x.dtype)
+    ws_bytes = _decode_workspace_bytes(B, Tq, C, n_heads, n_kv_heads, x.dtype, norm, residual, Tmax)
+    y, k_cache, v_cache, cache_len, _ = jax.ffi.ffi_call(
+        "spb_block_decode",
+        (jax.ShapeDtypeStruct(x.shape, x.dtype), jax.ShapeDtypeStruct(k_cache.shape, k_cache.dtype),
+         jax.ShapeDtypeStruct(v_cache.shape, v_cache.dtype), jax.ShapeDtypeStruct((1,), jnp.int32), jax.ShapeDtypeStruct((ws_bytes,), jnp.uint8)),
+        input_output_aliases={7: 1, 8: 2, 9: 3},  # the caches and the length are updated in place
+    )(x, a["wq"], a["wk"], a["wv"], a["wo"], norm_w, _rope_table(freqs_cis[:Tmax]), k_cache, v_cache, cache_len.astype(jnp.int32).reshape(1),
+      n_heads=np.int32(n_heads), n_kv_heads=np.int32(n_kv_heads), eps=np.float32(eps), norm=bool(norm), residual=bool(residual))
+    return y, (k_cache, v_cache, cache_len)

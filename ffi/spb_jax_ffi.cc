@@ -1,8 +1,9 @@
 // spb_jax_ffi.cc - XLA FFI handlers over the C ABI of libspb200.so: the jax.ffi face of the attention block.
 //
 // What it replaces in the reference: the body of `attention(...)` behind `rms_norm(...)` as transformer_block calls it
-// (llama3/LLaMA-jax.ipynb:881, traced under jit + value_and_grad at :993-995).  ffi/spb_jax.py registers the two
-// symbols below and wraps them in a jax.custom_vjp with the notebook's own function signatures.
+// (llama3/LLaMA-jax.ipynb:881, traced under jit + value_and_grad at :993-995).  ffi/spb_jax.py registers the
+// symbols below and wraps them in a jax.custom_vjp with the notebook's own function signatures; SpbBlockDecode is the
+// KV-cache step of the same function (:815-829) over fixed-capacity caches.
 //
 // Build where JAX is installed (this image has neither jax nor the xla/ffi headers, so the file is shipped as source
 // and is not compiled by build.py):
@@ -172,6 +173,48 @@ ffi::Error BlockBwdImpl(cudaStream_t stream, ffi::AnyBuffer x, ffi::AnyBuffer dy
   return ffi::Error::Success();
 }
 
+// ---- KV-cache decode step ---------------------------------------------------------------------------------------------
+// attention(params, rms_norm(x, w), mask, freqs_cis, n_heads, n_kv_heads, cache=(k, v), position=p) of llama3:815-829 as
+// `generate` (:499-511) calls it, for caches of FIXED capacity [B, Tmax, Hkv, hd] that are appended in place, with the number
+// of valid rows in device memory (spb_block_decode_dev): nothing in the call depends on the length, so the step traces once
+// under jit and serves every token (the notebook's concatenate-per-step form retraces for every new length).
+// args   : x [B,Tq,C], wq, wk, wv, wo, norm_w, rope [>= Tmax, hd/2, 4] f32, k_cache, v_cache [B,Tmax,Hkv,hd], cache_len s32[1]
+// results: y [B,Tq,C], k_cache, v_cache, cache_len (aliases of the three inputs: input_output_aliases in ffi/spb_jax.py),
+//          ws u8[spb_block_decode_ws_layout().total]
+ffi::Error BlockDecodeImpl(cudaStream_t stream, ffi::AnyBuffer x, ffi::AnyBuffer wq, ffi::AnyBuffer wk, ffi::AnyBuffer wv, ffi::AnyBuffer wo,
+                           ffi::AnyBuffer norm_w, ffi::Buffer<ffi::F32> rope, ffi::AnyBuffer k_in, ffi::AnyBuffer v_in,
+                           ffi::Buffer<ffi::S32> len_in, ffi::Result<ffi::AnyBuffer> y, ffi::Result<ffi::AnyBuffer> k_cache,
+                           ffi::Result<ffi::AnyBuffer> v_cache, ffi::Result<ffi::Buffer<ffi::S32>> cache_len,
+                           ffi::Result<ffi::Buffer<ffi::U8>> ws, int32_t n_heads, int32_t n_kv_heads, float eps, bool norm, bool residual) {
+  auto sh = make_desc(x, n_heads, n_kv_heads, eps, /*causal=*/false, norm, residual);  // the cache branch applies no mask (llama3:824-825)
+  if (sh.has_error()) return sh.error();
+  const Shapes& s = sh.value();
+  auto kd = k_in.dimensions();
+  if (kd.size() != 4 || kd[0] != s.d.B || kd[2] != s.d.Hkv || kd[3] != s.d.hd)
+    return ffi::Error(ffi::ErrorCode::kInvalidArgument, "spb: k_cache / v_cache must be [B, Tmax, n_kv_heads, head_dim]");
+  const int32_t Tmax = (int32_t)kd[1];
+  if (rope.dimensions().size() != 3 || rope.dimensions()[0] < Tmax)
+    return ffi::Error(ffi::ErrorCode::kInvalidArgument, "spb: the rope table must cover every position of the cache ([>= Tmax, hd/2, 4])");
+  spb_decode_ws lay;
+  int rc = spb_block_decode_ws_layout(&s.d, Tmax, &lay);
+  if (rc) return fail("spb_block_decode_ws_layout", rc);
+  if (ws->size_bytes() < lay.total) return ffi::Error(ffi::ErrorCode::kInvalidArgument, "spb: workspace result is smaller than spb_block_decode_ws_layout().total");
+  // XLA normally honours the aliases; when it does not (an operand still live elsewhere) the caches are brought over first
+  cudaError_t ce = cudaSuccess;
+  if (k_cache->untyped_data() != k_in.untyped_data())
+    ce = cudaMemcpyAsync(k_cache->untyped_data(), k_in.untyped_data(), k_in.size_bytes(), cudaMemcpyDeviceToDevice, stream);
+  if (ce == cudaSuccess && v_cache->untyped_data() != v_in.untyped_data())
+    ce = cudaMemcpyAsync(v_cache->untyped_data(), v_in.untyped_data(), v_in.size_bytes(), cudaMemcpyDeviceToDevice, stream);
+  if (ce == cudaSuccess && cache_len->typed_data() != len_in.typed_data())
+    ce = cudaMemcpyAsync(cache_len->typed_data(), len_in.typed_data(), sizeof(int32_t), cudaMemcpyDeviceToDevice, stream);
+  if (ce != cudaSuccess) return ffi::Error(ffi::ErrorCode::kInternal, std::string("spb: cache copy failed: ") + cudaGetErrorString(ce));
+  spb_block_params p = {};
+  fill_params(&p, s, wq, wk, wv, wo, norm_w, rope);
+  rc = spb_block_decode_dev(&s.d, &p, x.untyped_data(), k_cache->untyped_data(), v_cache->untyped_data(), cache_len->typed_data(), Tmax,
+                            y->untyped_data(), ws->typed_data(), stream);
+  return rc ? fail("spb_block_decode_dev", rc) : ffi::Error::Success();
+}
+
 // ---- the two stand-alone functions of the notebook (cells c15, c17) ---------------------------------------------------
 // rms_norm(x, weight, eps) llama3:536-538; stats [N, 2] f32 (mean, rstd) is the residual of its VJP
 ffi::Error RmsNormImpl(cudaStream_t stream, ffi::AnyBuffer x, ffi::AnyBuffer w, ffi::Result<ffi::AnyBuffer> y, ffi::Result<ffi::Buffer<ffi::F32>> stats,
@@ -266,6 +309,30 @@ XLA_FFI_DEFINE_HANDLER_SYMBOL(SpbBlockBwd, BlockBwdImpl,
                                   .Attr<bool>("norm")
                                   .Attr<bool>("residual")
                                   .Attr<int64_t>("comm"));
+
+XLA_FFI_DEFINE_HANDLER_SYMBOL(SpbBlockDecode, BlockDecodeImpl,
+                              ffi::Ffi::Bind()
+                                  .Ctx<ffi::PlatformStream<cudaStream_t>>()
+                                  .Arg<ffi::AnyBuffer>()          // x
+                                  .Arg<ffi::AnyBuffer>()          // wq
+                                  .Arg<ffi::AnyBuffer>()          // wk
+                                  .Arg<ffi::AnyBuffer>()          // wv
+                                  .Arg<ffi::AnyBuffer>()          // wo
+                                  .Arg<ffi::AnyBuffer>()          // norm_w
+                                  .Arg<ffi::Buffer<ffi::F32>>()   // rope
+                                  .Arg<ffi::AnyBuffer>()          // k_cache
+                                  .Arg<ffi::AnyBuffer>()          // v_cache
+                                  .Arg<ffi::Buffer<ffi::S32>>()   // cache_len
+                                  .Ret<ffi::AnyBuffer>()          // y
+                                  .Ret<ffi::AnyBuffer>()          // k_cache (alias)
+                                  .Ret<ffi::AnyBuffer>()          // v_cache (alias)
+                                  .Ret<ffi::Buffer<ffi::S32>>()   // cache_len (alias, advanced by Tq)
+                                  .Ret<ffi::Buffer<ffi::U8>>()    // ws
+                                  .Attr<int32_t>("n_heads")
+                                  .Attr<int32_t>("n_kv_heads")
+                                  .Attr<float>("eps")
+                                  .Attr<bool>("norm")
+                                  .Attr<bool>("residual"));
 
 XLA_FFI_DEFINE_HANDLER_SYMBOL(SpbRmsNorm, RmsNormImpl,
                               ffi::Ffi::Bind()

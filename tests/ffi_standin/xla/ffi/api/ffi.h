@@ -60,6 +60,7 @@ class AnyBuffer {
 template <DataType dt> struct NativeOf { using type = void; };
 template <> struct NativeOf<F32> { using type = float; };
 template <> struct NativeOf<U8> { using type = uint8_t; };
+template <> struct NativeOf<S32> { using type = int32_t; };
 
 template <DataType dt>
 class Buffer {

@@ -116,7 +116,7 @@ def test_struct_members_exist_in_the_header():
 def test_handlers_bind_what_their_implementations_take():
     cc = _strip_comments(CC)
     handlers = _handlers(cc)
-    assert {h[0] for h in handlers} == {"SpbBlockFwd", "SpbBlockBwd", "SpbRmsNorm", "SpbRmsNormBwd", "SpbRope"}
+    assert {h[0] for h in handlers} == {"SpbBlockFwd", "SpbBlockBwd", "SpbBlockDecode", "SpbRmsNorm", "SpbRmsNormBwd", "SpbRope"}
     for sym, impl, bind in handlers:
         n_bound = len(re.findall(r"\.(?:Ctx|Arg|Ret|Attr)<", bind))
         m = re.search(rf"ffi::Error {impl}\(", cc)
@@ -145,7 +145,8 @@ def test_python_side_registers_the_defined_symbols_and_mirrors_the_abi_structs()
     called = set(re.findall(r'ffi_call\(\s*"(\w+)"', PY))
     assert called == targets, (called, targets)
     names = {n.name for n in ast.walk(tree) if isinstance(n, ast.FunctionDef)}
-    assert {"rms_norm", "apply_rotary_emb", "repeat_kv", "attention", "attention_block", "_block_fwd", "_block_bwd", "register"} <= names
+    assert {"rms_norm", "apply_rotary_emb", "repeat_kv", "attention", "attention_block", "attention_decode", "_block_fwd", "_block_bwd",
+            "register"} <= names
     # attributes passed by the Python side = attributes bound by the C++ side
     for target, sym in re.findall(r'\("(spb_\w+)",\s*"(\w+)"\)', PY):
         bind = [h[2] for h in _handlers(_strip_comments(CC)) if h[0] == sym][0]
@@ -167,6 +168,7 @@ def test_python_side_registers_the_defined_symbols_and_mirrors_the_abi_structs()
     assert [f[0] for f in ns["_WsLayout"]._fields_] == [f[0] for f in L.WsLayout._fields_]
     import ctypes
     assert ctypes.sizeof(ns["_BlockDesc"]) == ctypes.sizeof(L.BlockDesc) and ctypes.sizeof(ns["_WsLayout"]) == ctypes.sizeof(L.WsLayout)
+    assert [f[0] for f in ns["_DecodeWs"]._fields_] == [f[0] for f in L.DecodeWs._fields_]
 
 
 def test_shim_compiles_against_an_api_stand_in():
