@@ -152,7 +152,10 @@ def test_gemm_simt_f32_accumulate_and_long_k():
 
 @pytest.mark.parametrize("tA,tB", [(False, True), (False, False), (True, False), (True, True)])
 @pytest.mark.parametrize("M,N,K", [(128, 256, 64), (128, 128, 128), (256, 512, 512), (384, 768, 256), (200, 136, 72),
-                                   (1024, 6144, 512)])
+                                   (1024, 6144, 512),
+                                   (256, 96, 128),     # N % 64 == 32: the last TMA store box of a tile is half stale, clipped at N
+                                   (136, 288, 64),     # 256 + 32 columns: the second tile ends on its first chunk; rows past M clipped
+                                   (8200, 160, 64)])   # many row tiles per CTA: the staging halves are reused across tiles
 def test_gemm_tcgen05_bf16(tA, tB, M, N, K):
     """All four operand-major combinations: (K-major, K-major) = dX; (K-major, MN-major) = forward with [in,out]
     weights; (MN, MN) = dW.  Ragged sizes exercise TMA zero fill and the predicated epilogue."""
@@ -168,6 +171,26 @@ def test_gemm_tcgen05_epilogues():
     assert _gemm_case(torch.bfloat16, 256, 512, 256, False, True, L.IMPL_TCGEN05, accumulate=True) < TOL_BF16 / 4
     assert _gemm_case(torch.bfloat16, 256, 512, 256, True, False, L.IMPL_TCGEN05, out_dtype=torch.float32) < 1e-3
     assert _gemm_case(torch.bfloat16, 200, 200, 200, True, False, L.IMPL_TCGEN05, out_dtype=torch.float32, accumulate=True) < 1e-3
+    # epilogue through shared memory + TMA stores (plain, non-accumulating tiles): ragged edges in both output types, with bias
+    assert _gemm_case(torch.bfloat16, 200, 232, 72, False, False, L.IMPL_TCGEN05, bias=True) < TOL_BF16 / 4
+    assert _gemm_case(torch.bfloat16, 328, 72, 136, True, False, L.IMPL_TCGEN05, out_dtype=torch.float32) < 1e-3
+    assert _gemm_case(torch.bfloat16, 4096, 2304, 768, False, True, L.IMPL_TCGEN05, bias=True) < TOL_BF16 / 4   # ViT QKV shape: CTA-pair kernel
+
+
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float32])
+def test_gemm_tcgen05_output_view_keeps_its_neighbours(out_dtype):
+    """D is a column range of a wider buffer (how the block writes q | k | v and the packed dW): the TMA-store epilogue's 64- /
+    32-column boxes overhang the range at its right edge and must be clipped there, not at the row pitch."""
+    ops, L = _ops(), _L()
+    M, N, K, LD = 264, 96, 128, 160
+    A, B = rnd((M, K), 3, torch.bfloat16), rnd((K, N), 4, torch.bfloat16, 1.0 / math.sqrt(K))
+    big = torch.full((M + 8, LD), 7.0, dtype=out_dtype, device=DEV)
+    out = big[:M, 32:32 + N]
+    ops.gemm(A.to(DEV), B.to(DEV), out=out, impl=L.IMPL_TCGEN05)
+    torch.cuda.synchronize()
+    ref = A.double() @ B.double()
+    assert max_rel_err(out, ref) < (TOL_BF16 / 4 if out_dtype == torch.bfloat16 else 1e-3)
+    assert torch.all(big[:M, :32] == 7.0) and torch.all(big[:M, 32 + N:] == 7.0) and torch.all(big[M:] == 7.0)
 
 
 def test_gemm_tcgen05_split_k_weight_gradient_shape():
