@@ -273,6 +273,8 @@ def test_attention_simt(dtype, B, T, Hq, Hkv, hd, causal):
     (2, 256, 1, 1, 256, True),    # GPT notebook geometry: one head of 256 (single-tile forward, hd-split backward)
     (1, 200, 4, 1, 256, True),    # Gemma-2B-shaped MQA, ragged
     (1, 128, 2, 2, 256, False),   # hd 256 bidirectional
+    (40, 1024, 1, 1, 256, True),  # hd 256 with >= 4 x SMs role-CTAs: one CTA per role (the small cases above run the cluster-of-two form)
+    (1, 64, 1, 1, 256, True),     # hd 256, one 64-row query tile: the second CTA of a role cluster has no iteration at all
 ])
 def test_attention_tcgen05_flash(B, T, Hq, Hkv, hd, causal):
     """tcgen05 flash forward + backward (bf16) against the oracle math; bf16-mode tolerance 2e-2."""
