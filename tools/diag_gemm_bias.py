@@ -1,5 +1,7 @@
+"""GPU timing (not a test): the ViT-B/16 QKV GEMM (50432 x 2304 x 768, torch [out,in] weight) through spb_gemm without / with the
+bias epilogue, and torch.addmm (cuBLAS) on the same operands - the shape on which the epilogue, not the main loop, sets the pace."""
 import os, sys, torch
-sys.path.insert(0, "/root/repo")
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from solvingpapers_b200 import _lib as L, ops
 M,N,K=50432,2304,768
 A=[torch.randn(M,K,device="cuda").bfloat16() for _ in range(3)]
